@@ -1,0 +1,357 @@
+"""dynolog-1_b200: B200-native perf_event decode + aggregation for dynolog/hbt.
+
+The product is the C-ABI shared library ``libhbt_b200.so`` (built in-tree from
+``csrc/`` for sm_100a, declared in ``include/hbt_b200.h``).  This package is the
+thin Python binding (ctypes) that tests and ``bench.py`` drive it through; the
+C++ mirror of the reference's host classes lives in ``host/``.
+
+There is no CPU fallback: importing works anywhere, but every compute entry
+point needs the library and a B200; a missing library raises at first use.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+REPO_ROOT = os.path.dirname(_HERE)
+LIB_PATH = os.path.join(_HERE, "libhbt_b200.so")
+
+# ---- constants of include/hbt_b200.h -------------------------------------------
+ABI_VERSION = 1
+MAX_CPUS = 512
+MAX_EVENTS = 64
+NUM_COUNTERS = 11
+(CNT_LOST, CNT_COMM, CNT_EXIT, CNT_THROTTLE, CNT_UNTHROTTLE, CNT_FORK, CNT_SAMPLE, CNT_READ,
+ CNT_AUX, CNT_ITRACE_START, CNT_SWITCH_CPU_WIDE) = range(11)
+H_LOST, H_COMM, H_EXIT, H_FORK, H_SAMPLE, H_READ, H_AUX, H_ITRACE_START, H_SWITCH_CPU_WIDE = (
+    1 << i for i in range(9))
+MODE_SAMPLING = H_LOST | H_READ | H_SAMPLE
+MODE_CONTEXT_SWITCH = H_LOST | H_COMM | H_EXIT | H_FORK | H_SWITCH_CPU_WIDE
+MODE_AUX_SPACE = H_AUX | H_ITRACE_START
+MODE_MIXED = MODE_CONTEXT_SWITCH | H_SAMPLE | H_READ
+SAMPLE_GROUP, SAMPLE_IP = 0, 1
+AGG_NONE, AGG_COUNT_DELTAS, AGG_IP_HISTOGRAM = 0, 1, 2
+DRAIN = 0xFFFFFFFF
+INVALID_TS = 0xFFFFFFFFFFFFFFFF
+
+
+class TscParams(C.Structure):
+    _fields_ = [("time_zero", C.c_uint64), ("time_mult", C.c_uint32),
+                ("time_shift", C.c_uint16), ("pad_", C.c_uint16)]
+
+
+class DecodeDesc(C.Structure):
+    _fields_ = [("handled_mask", C.c_uint32), ("sample_layout", C.c_uint32),
+                ("aggregate", C.c_uint32), ("n_events", C.c_uint32),
+                ("ip_sample_bytes", C.c_uint32), ("max_records", C.c_uint32),
+                ("tsc_transform_mask", C.c_uint64), ("tsc", TscParams)]
+
+
+class CpuResult(C.Structure):
+    _fields_ = [("ret", C.c_int64), ("n_records", C.c_uint64), ("new_tail", C.c_uint64),
+                ("n_rows", C.c_uint64), ("counters", C.c_uint64 * NUM_COUNTERS),
+                ("num_unknown_count_interval", C.c_uint64), ("carry_tstamp", C.c_uint64)]
+
+
+class HistEntry(C.Structure):
+    _fields_ = [("ip", C.c_uint64), ("pid", C.c_uint32), ("cpu", C.c_uint32),
+                ("count", C.c_uint64)]
+
+
+class Ratio(C.Structure):
+    _fields_ = [("num_event", C.c_uint32), ("den_event", C.c_uint32)]
+
+
+HIST_DTYPE = np.dtype([("ip", "<u8"), ("pid", "<u4"), ("cpu", "<u4"), ("count", "<u8")])
+RESULT_DTYPE = np.dtype([("ret", "<i8"), ("n_records", "<u8"), ("new_tail", "<u8"),
+                         ("n_rows", "<u8"), ("counters", "<u8", (NUM_COUNTERS,)),
+                         ("num_unknown_count_interval", "<u8"), ("carry_tstamp", "<u8")])
+assert HIST_DTYPE.itemsize == C.sizeof(HistEntry)
+assert RESULT_DTYPE.itemsize == C.sizeof(CpuResult)
+
+# Every symbol include/hbt_b200.h declares: (name, restype, argtypes)
+_P = C.c_void_p
+_U64P = C.POINTER(C.c_uint64)
+EXPORTS = [
+    ("hbt_abi_version", C.c_int, []),
+    ("hbt_create", C.c_int, [C.POINTER(_P), C.c_int, C.c_uint32, C.c_uint32]),
+    ("hbt_destroy", None, [_P]),
+    ("hbt_last_error", C.c_char_p, [_P]),
+    ("hbt_set_stream", C.c_int, [_P, _P]),
+    ("hbt_sync", C.c_int, [_P]),
+    ("hbt_launch_count", C.c_uint64, [_P]),
+    ("hbt_set_cpu_base", C.c_int, [_P, C.c_uint32]),
+    ("hbt_ring_configure", C.c_int, [_P, C.c_uint32, C.c_uint64]),
+    ("hbt_submit_ring", C.c_int, [_P, C.c_uint32, _P, C.c_size_t, _P, C.c_size_t, C.c_uint64]),
+    ("hbt_submit_ring_dev", C.c_int, [_P, C.c_uint32, _P, C.c_uint64, C.c_uint64, C.c_uint64]),
+    ("hbt_ring_reset_state", C.c_int, [_P, C.c_uint64]),
+    ("hbt_decode", C.c_int, [_P, C.POINTER(DecodeDesc)]),
+    ("hbt_fetch_results", C.c_int, [_P, _P, C.c_uint32]),
+    ("hbt_decode_reruns", C.c_uint32, [_P]),
+    ("hbt_decode_slow_tiles", C.c_uint64, [_P]),
+    ("hbt_fetch_rows", C.c_int64, [_P, C.c_uint32, _P, C.c_uint64]),
+    ("hbt_rows_slabs_dev", C.c_int, [_P, C.c_uint32, C.POINTER(_P), _U64P, C.POINTER(C.c_uint32)]),
+    ("hbt_rows_max_slabs", C.c_uint32, [_P]),
+    ("hbt_fetch_carry", C.c_int, [_P, C.c_uint32, _P, C.c_uint32]),
+    ("hbt_hist_configure", C.c_int, [_P, C.c_uint64]),
+    ("hbt_hist_clear", C.c_int, [_P]),
+    ("hbt_hist_size", C.c_int64, [_P]),
+    ("hbt_hist_fetch", C.c_int64, [_P, _P, C.c_uint64]),
+    ("hbt_hist_table_dev", C.c_int, [_P, C.POINTER(_P), _U64P]),
+    ("hbt_counts_reduce_dev", C.c_int, [_P, _P, C.c_uint64, C.c_uint32, C.c_uint32, _P]),
+    ("hbt_counts_scale_dev", C.c_int,
+     [_P, _P, C.c_uint64, C.c_uint32, _P, C.c_uint32, _P, _P, _P, _P, _P]),
+    ("hbt_counts_pipeline_dev", C.c_int,
+     [_P, _P, C.c_uint64, C.c_uint32, C.c_uint32, _P, C.c_uint32, _P, _P, _P, _P, _P]),
+    ("hbt_counts_pipeline_host", C.c_int,
+     [_P, _P, C.c_uint64, C.c_uint32, C.c_uint32, _P, C.c_uint32, _P, _P, _P, _P, _P]),
+]
+
+_lib = None
+
+
+def load_library(path: str = LIB_PATH) -> C.CDLL:
+    """dlopen libhbt_b200.so and type every export.  Raises if it is missing:
+    there is no other implementation to fall back to."""
+    global _lib
+    if _lib is not None and path == LIB_PATH:
+        return _lib
+    if not os.path.exists(path):
+        raise RuntimeError(
+            f"{path} is missing: build it with `python -c 'import __graft_entry__ as g; "
+            "g.build()'` (nvcc, sm_100a).  There is no CPU fallback.")
+    lib = C.CDLL(path)
+    for name, restype, argtypes in EXPORTS:
+        fn = getattr(lib, name)  # AttributeError if the symbol is not exported
+        fn.restype = restype
+        fn.argtypes = argtypes
+    if lib.hbt_abi_version() != ABI_VERSION:
+        raise RuntimeError("libhbt_b200.so ABI version mismatch")
+    if path == LIB_PATH:
+        _lib = lib
+    return lib
+
+
+class HbtError(RuntimeError):
+    def __init__(self, code: int, msg: str):
+        super().__init__(f"hbt error {code} ({os.strerror(-code) if code < 0 else code}): {msg}")
+        self.code = code
+
+
+def _ptr(x):
+    """Raw pointer of a numpy array / torch tensor / int / None."""
+    if x is None:
+        return None
+    if isinstance(x, int):
+        return C.c_void_p(x)
+    if isinstance(x, np.ndarray):
+        assert x.flags["C_CONTIGUOUS"]
+        return C.c_void_p(x.ctypes.data)
+    if hasattr(x, "data_ptr"):  # torch tensor
+        assert x.is_contiguous()
+        return C.c_void_p(x.data_ptr())
+    raise TypeError(type(x))
+
+
+def make_ratios(pairs):
+    arr = (Ratio * max(1, len(pairs)))()
+    for i, (a, b) in enumerate(pairs):
+        arr[i].num_event, arr[i].den_event = a, b
+    return arr
+
+
+class Context:
+    """One hbt_ctx: a (thread, device) handle on the GPU decode/aggregate path."""
+
+    def __init__(self, device: int = 0, max_cpus: int = MAX_CPUS, max_events: int = MAX_EVENTS):
+        self.lib = load_library()
+        h = C.c_void_p()
+        rc = self.lib.hbt_create(C.byref(h), device, max_cpus, max_events)
+        if rc != 0:
+            raise HbtError(rc, "hbt_create failed (no usable sm_100 CUDA device?)")
+        self.h = h
+        self.device = device
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.lib.hbt_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _ck(self, rc):
+        if rc < 0:
+            raise HbtError(int(rc), self.lib.hbt_last_error(self.h).decode())
+        return rc
+
+    # ---- plumbing
+    def set_stream(self, stream_ptr):
+        self._ck(self.lib.hbt_set_stream(self.h, C.c_void_p(stream_ptr) if stream_ptr else None))
+
+    def use_torch_stream(self):
+        import torch
+        self.set_stream(torch.cuda.current_stream(self.device).cuda_stream)
+
+    def sync(self):
+        self._ck(self.lib.hbt_sync(self.h))
+
+    @property
+    def launches(self) -> int:
+        return int(self.lib.hbt_launch_count(self.h))
+
+    def set_cpu_base(self, base: int):
+        self._ck(self.lib.hbt_set_cpu_base(self.h, base))
+
+    # ---- rings
+    def ring_configure(self, n_cpus: int, data_size: int = 0):
+        self._ck(self.lib.hbt_ring_configure(self.h, n_cpus, data_size))
+        self.n_cpus = n_cpus
+
+    def submit_ring(self, cpu: int, s1: np.ndarray, s2, tail: int):
+        self._ck(self.lib.hbt_submit_ring(self.h, cpu, _ptr(s1), s1.nbytes,
+                                          _ptr(s2) if s2 is not None and s2.nbytes else None,
+                                          s2.nbytes if s2 is not None else 0, tail))
+
+    def submit_ring_image(self, cpu: int, ring: np.ndarray, tail: int, head: int):
+        """Host ring image + window -> the two RbDataSlices the reference's
+        onCpuDataBufferRead would hand out (CpuEventsGroup.h:1524-1570)."""
+        ds = ring.nbytes
+        off = tail & (ds - 1)
+        n = head - tail
+        n1 = min(n, ds - off)
+        flat = ring.view(np.uint8).reshape(-1)
+        s1 = flat[off:off + n1]
+        s2 = flat[0:n - n1] if n > n1 else None
+        self.submit_ring(cpu, s1, s2, tail)
+
+    def submit_ring_dev(self, cpu: int, ring_ptr, data_size: int, tail: int, head: int):
+        self._ck(self.lib.hbt_submit_ring_dev(self.h, cpu, _ptr(ring_ptr), data_size, tail, head))
+
+    def reset_state(self, seed_tstamp: int = INVALID_TS):
+        self._ck(self.lib.hbt_ring_reset_state(self.h, seed_tstamp))
+
+    # ---- decode
+    def decode(self, desc: DecodeDesc):
+        self._ck(self.lib.hbt_decode(self.h, C.byref(desc)))
+
+    def fetch_results(self) -> np.ndarray:
+        out = np.zeros(self.n_cpus, dtype=RESULT_DTYPE)
+        self._ck(self.lib.hbt_fetch_results(self.h, _ptr(out), self.n_cpus))
+        return out
+
+    @property
+    def reruns(self) -> int:
+        return int(self.lib.hbt_decode_reruns(self.h))
+
+    @property
+    def slow_tiles(self) -> int:
+        return int(self.lib.hbt_decode_slow_tiles(self.h))
+
+    def fetch_rows(self, cpu: int, n_rows: int, n_events: int) -> np.ndarray:
+        out = np.zeros((max(1, n_rows), 2 + n_events), dtype=np.uint64)
+        n = self._ck(self.lib.hbt_fetch_rows(self.h, cpu, _ptr(out), out.shape[0]))
+        return out[:n]
+
+    def fetch_carry(self, cpu: int, n_events: int) -> np.ndarray:
+        out = np.zeros(n_events, dtype=np.uint64)
+        self._ck(self.lib.hbt_fetch_carry(self.h, cpu, _ptr(out), n_events))
+        return out
+
+    # ---- histogram
+    def hist_configure(self, capacity_slots: int):
+        self._ck(self.lib.hbt_hist_configure(self.h, capacity_slots))
+
+    def hist_clear(self):
+        self._ck(self.lib.hbt_hist_clear(self.h))
+
+    def hist_size(self) -> int:
+        return int(self._ck(self.lib.hbt_hist_size(self.h)))
+
+    def hist_fetch(self) -> np.ndarray:
+        n = self.hist_size()
+        out = np.zeros(max(1, n), dtype=HIST_DTYPE)
+        m = self._ck(self.lib.hbt_hist_fetch(self.h, _ptr(out), out.shape[0]))
+        return out[:m]
+
+    # ---- counter groups
+    def counts_reduce_dev(self, reads, n_intervals, n_cpus, n_events, sums):
+        self._ck(self.lib.hbt_counts_reduce_dev(self.h, _ptr(reads), n_intervals, n_cpus, n_events,
+                                                _ptr(sums)))
+
+    def counts_scale_dev(self, sums, n_intervals, n_events, ratios, prev_scaled=None, scaled=None,
+                         rates=None, ratio_out=None, deltas=None):
+        r = make_ratios(ratios)
+        self._ck(self.lib.hbt_counts_scale_dev(self.h, _ptr(sums), n_intervals, n_events,
+                                               C.cast(r, C.c_void_p), len(ratios),
+                                               _ptr(prev_scaled), _ptr(scaled), _ptr(rates),
+                                               _ptr(ratio_out), _ptr(deltas)))
+
+    def counts_pipeline_dev(self, reads, n_intervals, n_cpus, n_events, ratios, sums=None,
+                            scaled=None, rates=None, ratio_out=None, deltas=None):
+        r = make_ratios(ratios)
+        self._ck(self.lib.hbt_counts_pipeline_dev(self.h, _ptr(reads), n_intervals, n_cpus,
+                                                  n_events, C.cast(r, C.c_void_p), len(ratios),
+                                                  _ptr(sums), _ptr(scaled), _ptr(rates),
+                                                  _ptr(ratio_out), _ptr(deltas)))
+
+    def counts_pipeline_host(self, reads: np.ndarray, ratios=()):
+        """reads: [I][C][3+E] u64 on the host -> dict of host arrays."""
+        I, Cc, W = reads.shape
+        E = W - 3
+        R = len(ratios)
+        out = dict(sums=np.zeros((I, W), np.uint64), scaled=np.zeros((I, E), np.uint64),
+                   rates=np.zeros((I, E), np.float32), ratios=np.zeros((I, max(R, 1)), np.float64),
+                   deltas=np.zeros((I, E), np.uint64))
+        r = make_ratios(ratios)
+        self._ck(self.lib.hbt_counts_pipeline_host(
+            self.h, _ptr(np.ascontiguousarray(reads)), I, Cc, E, C.cast(r, C.c_void_p), R,
+            _ptr(out["sums"]), _ptr(out["scaled"]), _ptr(out["rates"]),
+            _ptr(out["ratios"]) if R else None, _ptr(out["deltas"])))
+        out["ratios"] = out["ratios"][:, :R]
+        return out
+
+
+def sampling_desc(n_events: int, aggregate: int = AGG_COUNT_DELTAS, max_records: int = DRAIN,
+                  tsc_mask: int = 0, tsc=(0, 1, 0), handled: int = MODE_SAMPLING) -> DecodeDesc:
+    d = DecodeDesc()
+    d.handled_mask = handled
+    d.sample_layout = SAMPLE_GROUP
+    d.aggregate = aggregate
+    d.n_events = n_events
+    d.ip_sample_bytes = 0
+    d.max_records = max_records
+    d.tsc_transform_mask = tsc_mask
+    d.tsc = TscParams(tsc[0], tsc[1], tsc[2], 0)
+    return d
+
+
+def ip_desc(ip_sample_bytes: int = 40, aggregate: int = AGG_IP_HISTOGRAM,
+            max_records: int = DRAIN) -> DecodeDesc:
+    d = DecodeDesc()
+    d.handled_mask = H_LOST | H_SAMPLE
+    d.sample_layout = SAMPLE_IP
+    d.aggregate = aggregate
+    d.n_events = 0
+    d.ip_sample_bytes = ip_sample_bytes
+    d.max_records = max_records
+    d.tsc = TscParams(0, 1, 0, 0)
+    return d
+
+
+def count_desc(handled: int, max_records: int = DRAIN, sample_layout: int = SAMPLE_GROUP,
+               ip_sample_bytes: int = 0) -> DecodeDesc:
+    d = DecodeDesc()
+    d.handled_mask = handled
+    d.sample_layout = sample_layout
+    d.aggregate = AGG_NONE
+    d.ip_sample_bytes = ip_sample_bytes
+    d.max_records = max_records
+    d.tsc = TscParams(0, 1, 0, 0)
+    return d

@@ -1,0 +1,1001 @@
+// Ring-buffer decode kernels (K1 boundary discovery, K2 dispatch + counters,
+// K3 per-interval deltas, K6 (cpu,pid,ip) histogram) and the per-CPU finalize.
+//
+// Replaces CpuEventsGroup<TImpl,TMode>::consume
+// (hbt/src/perf_event/CpuEventsGroup.h:1326-1522) and the handlers of
+// CpuCountSampleGenerator (hbt/src/perf_event/PerCpuCountSampleGenerator.h:110-202)
+// for all CPUs of a batch at once.
+//
+// Data layout in HBM.  One ring image per CPU (exactly the perf mmap data area,
+// power-of-two bytes) and an unread window [tail, head) in absolute positions;
+// physical offset = pos & (data_size-1), so the ring wrap (and the reference's
+// two-piece memcpy, :1358-1370) disappears into the address computation.  The
+// position space is cut into TILE-byte tiles aligned to TILE (a tile never
+// straddles the ring end) and each CPU's tiles into `n_seg` contiguous segments.
+// One CTA decodes one segment, tile after tile, with tiles staged in shared
+// memory by 1-D bulk async copies (TMA unit) three tiles deep.
+//
+// Boundary discovery.  `tail += header.size` (:1503) is a serial chain.  Inside a
+// tile every thread owns a 64..128-byte sub-chunk: it guesses the first record
+// start in it (first plausible header whose successor is plausible too), walks
+// its own records from there and reports where it left the sub-chunk.  A block
+// wide max-scan then checks that every guess equals the exit of the records
+// before it; by induction from the tile's exact entry the guesses are then the
+// true boundaries.  A tile that fails the check (or holds any record the fast
+// path does not want: bad size, timestamp regression, giant record) is decoded
+// by one thread with a literal sequential consume() -- exactness never depends
+// on the guess.  The same idea one level up: every segment but a CPU's first
+// guesses its entry; k_finalize chains exits to entries and, on a mismatch,
+// records the true entry so the host re-runs the batch with it forced.
+#pragma once
+#include <cstdint>
+#include "../../include/hbt_b200.h"
+#include "ptx.cuh"
+
+namespace hbt {
+
+constexpr uint32_t REC_LOST = 2, REC_COMM = 3, REC_EXIT = 4, REC_THROTTLE = 5,
+                   REC_UNTHROTTLE = 6, REC_FORK = 7, REC_READ = 8, REC_SAMPLE = 9, REC_AUX = 11,
+                   REC_ITRACE_START = 12, REC_SWITCH_CPU_WIDE = 15;
+
+constexpr uint64_t kNone = ~0ull;          // "no position"
+constexpr uint64_t kInvalidTs = ~0ull;     // kInvalidTimeStamp (System.h:97)
+constexpr uint64_t kPrevCarry = ~0ull - 1; // "previous sample" = carry from the last call
+
+constexpr int kTile = 16384;   // bytes per tile
+constexpr int kStages = 3;     // tiles resident per CTA
+constexpr int kThreads = 256;  // threads per CTA
+constexpr int kSubWords = kTile / 8 / kThreads;  // 8 words = 64 B per thread
+static_assert(kSubWords == 8, "skew formula below assumes 8-word sub-chunks");
+
+// Event kinds for the interval state machine of CpuCountSampleGenerator.
+constexpr uint32_t EV_NONE = 0, EV_SAMPLE = 1, EV_LOST = 2;
+__device__ __forceinline__ uint64_t ev_make(uint64_t pos, uint32_t kind) {
+  return ((pos + 1) << 2) | kind;
+}
+__device__ __forceinline__ uint32_t ev_kind(uint64_t ev) { return (uint32_t)(ev & 3); }
+__device__ __forceinline__ uint64_t ev_pos(uint64_t ev) { return (ev >> 2) - 1; }
+
+struct RingDesc {  // one per CPU
+  const uint8_t* base;
+  uint64_t mask;      // data_size - 1
+  uint64_t tail;
+  uint64_t head;      // effective head (clamped on a re-run)
+  uint64_t true_head; // head as submitted
+  uint32_t seg_begin; // first segment id of this CPU
+  uint32_t n_seg;
+  int64_t override_ret;  // 0 = none; else forced consume() return on a re-run
+  uint64_t* rows;        // row slab base for this CPU (COUNT_DELTAS)
+};
+
+struct SegDesc {  // one per CTA
+  uint32_t cpu;
+  uint32_t seg;          // index within the CPU
+  uint64_t tile_begin;   // first tile index (absolute)
+  uint64_t tile_end;     // one past the last tile index
+  uint64_t forced_entry; // kNone = guess
+  uint64_t* rows;        // slab: slot 0 is the seam row, rows follow
+  uint64_t rows_cap;     // rows after the seam slot
+};
+
+struct SegResult {
+  uint64_t entry;  // first record start decoded by this segment, kNone if none
+  uint64_t exit;   // start of the first record at or after the segment end, kNone if none
+  uint64_t n_records;
+  uint64_t counters[HBT_NUM_COUNTERS];
+  uint64_t n_rows;
+  uint64_t n_unknown;
+  uint64_t first_ev;  // first SAMPLE/LOST event of the segment (encoded), 0 = none
+  uint64_t last_ev;   // last SAMPLE/LOST event of the segment (encoded), 0 = none
+  uint64_t last_sample;  // position of the last SAMPLE of the segment, kNone if none
+  uint64_t err_pos;
+  int32_t err;        // 0 or negative errno: decoding stopped before err_pos
+  uint32_t slow_tiles;
+  uint32_t hist_overflow;
+  uint32_t pad_;
+};
+
+struct CpuState {  // generator state across calls
+  uint64_t counters[HBT_NUM_COUNTERS];
+  uint64_t num_unknown;
+  uint64_t carry_tstamp;
+  uint64_t carry_last[HBT_MAX_EVENTS];
+};
+
+struct HistTable {
+  ulonglong2* slots;      // {ip, pid | count<<32}; all-zero = empty
+  uint64_t slots_per_cpu; // power of two
+  uint64_t* zero_key;     // per-CPU count of key (ip=0, pid=0)
+  uint32_t* overflow;     // set when a probe sequence found no room / a count wrapped
+};
+
+struct DecodeParams {
+  const RingDesc* rings;
+  const SegDesc* segs;
+  SegResult* results;
+  const CpuState* state_in;
+  hbt_decode_desc d;
+  HistTable hist;
+  uint32_t hist_inc;  // +1, or 0xFFFFFFFF to take a failed attempt back out
+};
+
+// ---------------------------------------------------------------------------
+// Shared helpers
+// ---------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t hdr_type(uint64_t h) { return (uint32_t)h; }
+__device__ __forceinline__ uint32_t hdr_size(uint64_t h) { return (uint32_t)(h >> 48); }
+
+// Guess filter only (never decides results): a header the kernel could have
+// written -- small type id, u64-padded size.
+__device__ __forceinline__ bool plausible(uint64_t h) {
+  const uint32_t type = hdr_type(h), size = hdr_size(h);
+  return type >= 1 && type < 64 && size >= 8 && (size & 7) == 0;
+}
+
+__device__ __forceinline__ uint64_t ring_word_g(const RingDesc& r, uint64_t pos) {
+  return *reinterpret_cast<const uint64_t*>(r.base + (pos & r.mask));
+}
+
+// CpuEventsGroup::kernelTimeFromTsc (CpuEventsGroup.h:1577-1591).
+__device__ __forceinline__ uint64_t tsc_to_ktime(uint64_t tsc, const hbt_tsc_params& p) {
+  const uint64_t rem_flags = (1ull << p.time_shift) - 1;
+  const uint64_t quot = tsc >> p.time_shift;
+  const uint64_t rem = tsc & rem_flags;
+  return p.time_zero + quot * p.time_mult + ((rem * p.time_mult) >> p.time_shift);
+}
+
+__device__ __forceinline__ uint64_t xform(const hbt_decode_desc& d, uint32_t i, uint64_t v) {
+  return ((d.tsc_transform_mask >> i) & 1) ? tsc_to_ktime(v, d.tsc) : v;
+}
+
+// Counter index of a record type, -1 for types consume() only skips.
+__device__ __forceinline__ int counter_of(uint32_t type, uint32_t handled) {
+  switch (type) {
+    case REC_LOST: return (handled & HBT_H_LOST) ? HBT_CNT_LOST : -1;
+    case REC_COMM: return (handled & HBT_H_COMM) ? HBT_CNT_COMM : -1;
+    case REC_EXIT: return (handled & HBT_H_EXIT) ? HBT_CNT_EXIT : -1;
+    case REC_THROTTLE: return HBT_CNT_THROTTLE;
+    case REC_UNTHROTTLE: return HBT_CNT_UNTHROTTLE;
+    case REC_FORK: return (handled & HBT_H_FORK) ? HBT_CNT_FORK : -1;
+    case REC_SAMPLE: return (handled & HBT_H_SAMPLE) ? HBT_CNT_SAMPLE : -1;
+    case REC_READ: return (handled & HBT_H_READ) ? HBT_CNT_READ : -1;
+    case REC_AUX: return (handled & HBT_H_AUX) ? HBT_CNT_AUX : -1;
+    case REC_ITRACE_START: return (handled & HBT_H_ITRACE_START) ? HBT_CNT_ITRACE_START : -1;
+    case REC_SWITCH_CPU_WIDE:
+      return (handled & HBT_H_SWITCH_CPU_WIDE) ? HBT_CNT_SWITCH_CPU_WIDE : -1;
+    default: return -1;
+  }
+}
+
+// Global (cpu,pid,ip) table insert: lock-free, exact.  Slot = {ip, pid|count<<32},
+// claimed with one 128-bit CAS; the key (0,0) would look like an empty slot and
+// is counted in a per-CPU side counter instead.
+__device__ __forceinline__ void hist_insert_global(const HistTable& t, uint32_t cpu, uint64_t ip,
+                                                   uint32_t pid, uint32_t n) {
+  if (ip == 0 && pid == 0) {
+    atomicAdd(reinterpret_cast<unsigned long long*>(t.zero_key + cpu), (unsigned long long)n);
+    return;
+  }
+  ulonglong2* base = t.slots + (uint64_t)cpu * t.slots_per_cpu;
+  const uint64_t m = t.slots_per_cpu - 1;
+  uint64_t i = mix64(ip ^ ((uint64_t)pid * 0x9E3779B97F4A7C15ull)) & m;
+  for (uint64_t probe = 0; probe <= m; ++probe, i = (i + 1) & m) {
+    ulonglong2 s = ld_relaxed_v2u64(base + i);
+    if (s.x == 0 && s.y == 0) {
+      uint64_t olo, ohi;
+      cas128_global(base + i, 0, 0, ip, (uint64_t)pid, olo, ohi);
+      if (olo == 0 && ohi == 0) {
+        s.x = ip;
+        s.y = pid;
+      } else {
+        s.x = olo;
+        s.y = ohi;
+      }
+    }
+    if (s.x == ip && (uint32_t)s.y == pid) {
+      uint32_t* cnt = reinterpret_cast<uint32_t*>(base + i) + 3;
+      const uint32_t old = atomicAdd(cnt, n);
+      if ((int32_t)n > 0 && old + n < old) atomicExch(t.overflow, 2u);  // 32-bit count wrapped
+      return;
+    }
+  }
+  atomicExch(t.overflow, 1u);  // table full
+}
+
+// ---------------------------------------------------------------------------
+// Per-CTA decode state (shared memory)
+// ---------------------------------------------------------------------------
+struct SegState {
+  uint64_t pos;       // next record start; kNone while a segment still guesses
+  uint64_t ev;        // last SAMPLE/LOST event so far in this segment (encoded)
+  uint64_t first_ev;  // first SAMPLE of the segment when nothing precedes it (the seam)
+  uint64_t last_sample;  // position of the last SAMPLE so far, kNone if none
+  uint64_t entry;     // first record start decoded
+  unsigned long long n_rec, n_rows, n_unknown;
+  unsigned long long counters[HBT_NUM_COUNTERS];
+  uint64_t err_pos;
+  int32_t err;
+  uint32_t slow_tiles;
+  uint32_t anomaly;   // per-tile flag
+  uint32_t guess_min; // per-tile: smallest guessed entry (tile-relative), segment start only
+};
+
+// In-CTA privatised (pid,ip) table for one segment: open addressing, 16-byte
+// slots {ip, pid | count<<32}, state word per slot (0 empty, 1 being written, 2 ready).
+constexpr int kHistSlots = 2048;
+constexpr int kHistProbes = 4;
+
+struct Smem {
+  uint64_t bar[kStages];
+  SegState st;
+  int32_t warp_x[kThreads / 32];
+  uint64_t warp_ev[kThreads / 32];
+  uint32_t warp_rows[kThreads / 32];
+  uint32_t warp_ls[kThreads / 32];  // last SAMPLE start in the tile, relative + 1
+};
+
+// Sequential consume() over [st.pos, limit) by ONE thread: the slow path for
+// tiles the fast path declines and the definition of what the fast path must
+// equal.  Reads the ring through global memory.  Stops at `limit` (first record
+// start >= limit is left in st.pos) or at an error.
+template <int AGG>
+__device__ void consume_sequential(const DecodeParams& p, const RingDesc& ring,
+                                   const SegDesc& seg, SegState& st, uint64_t limit) {
+  const hbt_decode_desc& d = p.d;
+  uint64_t pos = st.pos;
+  while (pos < limit) {
+    const uint64_t h = ring_word_g(ring, pos);
+    const uint32_t type = hdr_type(h), size = hdr_size(h);
+    if (size < 8 || (size & 7)) {
+      st.err = -74;  // -EBADMSG
+      st.err_pos = pos;
+      break;
+    }
+    if (st.entry == kNone) st.entry = pos;
+    const int ci = counter_of(type, d.handled_mask);
+    if (type == REC_LOST && ci >= 0) {
+      st.counters[HBT_CNT_LOST] += ring_word_g(ring, pos + 16);
+      if (AGG == HBT_AGG_COUNT_DELTAS) st.ev = ev_make(pos, EV_LOST);
+    } else if (type == REC_SAMPLE && ci >= 0) {
+      if (d.sample_layout == HBT_SAMPLE_GROUP) {
+        const uint64_t nr = ring_word_g(ring, pos + 16);
+        if ((uint64_t)size != 40 + 8 * nr) {
+          st.err = -1;  // -EPERM
+          st.err_pos = pos;
+          break;
+        }
+        if (AGG == HBT_AGG_COUNT_DELTAS) {
+          const uint64_t ts = ring_word_g(ring, pos + 8);
+          const uint32_t k = ev_kind(st.ev);
+          if (k == EV_NONE) {
+            // nothing before in this segment: the seam with the previous segment
+            // (or the carry of the previous call) is resolved by k_finalize.
+            st.first_ev = ev_make(pos, EV_SAMPLE);
+          } else if (k == EV_LOST) {
+            ++st.n_unknown;  // re-seed, PerCpuCountSampleGenerator.h:135-154
+          } else {
+            const uint64_t ppos = ev_pos(st.ev);
+            const uint64_t pts = ring_word_g(ring, ppos + 8);
+            if (pts > ts) {  // :156-163
+              st.ev = ev_make(pos, EV_LOST);  // count_.tstamp = invalid
+              st.err = -1;
+              st.err_pos = pos;
+              break;
+            }
+            if (st.n_rows >= seg.rows_cap) {
+              // only reachable with nr != n_events records (the reference DCHECKs
+              // it, :133): behaves like a full output ring, :191-194
+              st.ev = ev_make(pos, EV_LOST);
+              st.err = -28;  // -ENOSPC
+              st.err_pos = pos;
+              break;
+            }
+            uint64_t* row = seg.rows + (1 + st.n_rows) * (2 + (uint64_t)d.n_events);
+            row[0] = pts;
+            row[1] = ts - pts;
+            for (uint32_t i = 0; i < d.n_events; ++i) {
+              const uint64_t v = xform(d, i, ring_word_g(ring, pos + 40 + 8ull * i));
+              const uint64_t pv = xform(d, i, ring_word_g(ring, ppos + 40 + 8ull * i));
+              row[2 + i] = v - pv;
+            }
+            ++st.n_rows;
+          }
+          st.ev = ev_make(pos, EV_SAMPLE);
+          st.last_sample = pos;
+        }
+      } else {
+        if (size != d.ip_sample_bytes) {
+          st.err = -1;
+          st.err_pos = pos;
+          break;
+        }
+        if (AGG == HBT_AGG_IP_HISTOGRAM) {
+          hist_insert_global(p.hist, seg.cpu, ring_word_g(ring, pos + 8),
+                             (uint32_t)ring_word_g(ring, pos + 16), p.hist_inc);
+        }
+      }
+      ++st.counters[HBT_CNT_SAMPLE];
+    } else if (type == REC_READ && ci >= 0) {
+      const uint64_t nr = ring_word_g(ring, pos + 16);
+      if ((uint64_t)size != 40 + 8 * nr) {
+        st.err = -1;
+        st.err_pos = pos;
+        break;
+      }
+      ++st.counters[HBT_CNT_READ];
+    } else if (ci >= 0) {
+      ++st.counters[ci];
+    }
+    ++st.n_rec;
+    pos += size;
+  }
+  st.pos = pos;
+}
+
+// Word of the stream at absolute position `pos`, from the staged tiles when
+// resident (tile `t` in stage sa, tile t+1 in stage sb), else from global.
+struct TileView {
+  const uint8_t* sa;
+  const uint8_t* sb;
+  uint64_t t_begin;  // absolute position of the tile start
+  const RingDesc* ring;
+  __device__ __forceinline__ uint64_t word(uint64_t pos) const {
+    const uint64_t off = pos - t_begin;  // wraps for pos < t_begin -> huge
+    if (off < (uint64_t)kTile) return *reinterpret_cast<const uint64_t*>(sa + off);
+    if (off < 2ull * kTile) return *reinterpret_cast<const uint64_t*>(sb + (off - kTile));
+    return ring_word_g(*ring, pos);
+  }
+  // same, for positions known to be inside [t_begin, t_begin + 2*kTile)
+  __device__ __forceinline__ uint64_t word_in(uint64_t pos) const {
+    const uint64_t off = pos - t_begin;
+    return *reinterpret_cast<const uint64_t*>((off < (uint64_t)kTile ? sa : sb - kTile) + off);
+  }
+};
+
+template <int AGG>
+__global__ void __launch_bounds__(kThreads) k_decode(const DecodeParams p) {
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  uint8_t* stages = smem_raw;  // kStages * kTile
+  Smem& sm = *reinterpret_cast<Smem*>(smem_raw + kStages * kTile);
+  // HIST: privatised table after Smem
+  ulonglong2* h_slots = reinterpret_cast<ulonglong2*>(
+      smem_raw + kStages * kTile + ((sizeof(Smem) + 15) & ~15ull));
+  uint32_t* h_state = reinterpret_cast<uint32_t*>(h_slots + kHistSlots);
+
+  const SegDesc seg = p.segs[blockIdx.x];
+  const RingDesc ring = p.rings[seg.cpu];
+  const hbt_decode_desc& d = p.d;
+  const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  SegState& st = sm.st;
+
+  if (tid == 0) {
+    for (int s = 0; s < kStages; ++s) mbar_init(&sm.bar[s], 1);
+    fence_mbar_init();
+    st.pos = seg.seg == 0 ? ring.tail : seg.forced_entry;
+    st.ev = 0;
+    st.first_ev = 0;
+    st.last_sample = kNone;
+    st.entry = kNone;
+    st.n_rec = st.n_rows = st.n_unknown = 0;
+    for (int i = 0; i < HBT_NUM_COUNTERS; ++i) st.counters[i] = 0;
+    st.err = 0;
+    st.err_pos = 0;
+    st.slow_tiles = 0;
+    st.anomaly = 0;
+    st.guess_min = 0xFFFFFFFFu;
+  }
+  if (AGG == HBT_AGG_IP_HISTOGRAM) {
+    for (int i = tid; i < kHistSlots; i += kThreads) {
+      h_slots[i] = make_ulonglong2(0, 0);
+      h_state[i] = 0;
+    }
+  }
+  __syncthreads();
+
+  const uint64_t n_tiles = seg.tile_end - seg.tile_begin;
+  // Records are decoded while they START before seg_limit.
+  const uint64_t seg_limit = min(seg.tile_end * (uint64_t)kTile, ring.head);
+
+  auto issue = [&](uint64_t k) {  // tile k of this segment (k == n_tiles: lookahead tile)
+    const uint64_t t = seg.tile_begin + k;
+    const int s = (int)(t % kStages);
+    mbar_arrive_expect_tx(&sm.bar[s], kTile);
+    bulk_g2s(stages + s * kTile, ring.base + ((t * (uint64_t)kTile) & ring.mask), kTile,
+             &sm.bar[s]);
+  };
+  if (tid == 0) {
+    issue(0);
+    issue(1);
+  }
+  uint32_t phase_bits = 0;  // mbarrier parity per stage
+
+  // thread-local totals over the fast-path tiles (added to st in the epilogue)
+  unsigned long long my_rec = 0, my_sample = 0;
+
+  for (uint64_t k = 0; k < n_tiles; ++k) {
+    const uint64_t t = seg.tile_begin + k;
+    const int sa_i = (int)(t % kStages), sb_i = (int)((t + 1) % kStages);
+    // refill the stage tile k-1 lived in; the trailing barrier of the previous
+    // round ordered every read of it before this copy
+    if (tid == 0 && k + 2 <= n_tiles) issue(k + 2);
+    if (k == 0) {
+      mbar_wait(&sm.bar[sa_i], (phase_bits >> sa_i) & 1);
+      phase_bits ^= 1u << sa_i;
+    }
+    mbar_wait(&sm.bar[sb_i], (phase_bits >> sb_i) & 1);
+    phase_bits ^= 1u << sb_i;
+
+    TileView tv{stages + sa_i * kTile, stages + sb_i * kTile, t * (uint64_t)kTile, &ring};
+    const uint64_t t_begin = tv.t_begin;
+    const uint64_t t_end = min(t_begin + kTile, seg_limit);  // record starts must be < t_end
+    const uint64_t look_end = t_begin + 2ull * kTile;        // end of the resident bytes
+    const uint64_t entry = st.pos;                           // exact, or kNone (still guessing)
+    const bool stopped = st.err != 0;
+
+    // ---- phase 1: guess + walk over the own sub-chunk -------------------------
+    // sub-chunk j = tile words [8j + skew(j), 8(j+1) + skew(j+1)); the skew spreads
+    // the lock-step header scan over all shared-memory banks.
+    const uint32_t skew0 = (tid >> 1) & 7, skew1 = ((tid + 1) >> 1) & 7;
+    const uint64_t sb = t_begin + 8ull * (kSubWords * tid + skew0);
+    uint64_t se = t_begin + 8ull * (kSubWords * (tid + 1) + (tid == kThreads - 1 ? 0 : skew1));
+    se = min(se, t_end);
+    const bool live = !stopped && sb < se;
+
+    uint64_t my_entry = kNone;  // first record start in my sub-chunk
+    if (live) {
+      if (entry != kNone && entry >= sb) {
+        if (entry < se) my_entry = entry;  // the tile's exact entry lies in my sub-chunk
+      } else {
+        for (uint64_t q = sb; q < se; q += 8) {
+          const uint64_t h = tv.word_in(q);
+          if (!plausible(h)) continue;
+          const uint64_t q2 = q + hdr_size(h);
+          if (q2 < look_end && q2 < ring.head && !plausible(tv.word_in(q2))) continue;
+          my_entry = q;
+          break;
+        }
+      }
+    }
+    uint32_t mask = 0;  // bit w: a record starts at sb + 8w
+    int32_t my_x = -1;  // where my walk left the sub-chunk, relative to t_begin
+    bool bad = false;
+    uint64_t first_ev = 0, last_ev = 0;
+    uint32_t my_ls = 0;  // last SAMPLE start, relative + 1
+    uint32_t rows_local = 0, unknown_local = 0;
+    uint64_t prev_ts = 0;
+    if (my_entry != kNone) {
+      uint64_t pos = my_entry;
+      while (pos < se) {
+        const uint64_t h = tv.word_in(pos);
+        const uint32_t type = hdr_type(h), size = hdr_size(h);
+        if (size < 8 || (size & 7) || pos + size > look_end) {
+          bad = true;
+          break;
+        }
+        if (type == REC_SAMPLE && (d.handled_mask & HBT_H_SAMPLE)) {
+          if (d.sample_layout == HBT_SAMPLE_GROUP) {
+            const uint64_t nr = tv.word_in(pos + 16);
+            if ((uint64_t)size != 40 + 8 * nr ||
+                (AGG == HBT_AGG_COUNT_DELTAS && nr != d.n_events)) {
+              bad = true;
+              break;
+            }
+            if (AGG == HBT_AGG_COUNT_DELTAS) {
+              const uint64_t ts = tv.word_in(pos + 8);
+              const uint32_t lk = ev_kind(last_ev);
+              if (lk == EV_SAMPLE) {
+                if (prev_ts > ts) {
+                  bad = true;
+                  break;
+                }
+                ++rows_local;
+              } else if (lk == EV_LOST) {
+                ++unknown_local;
+              }
+              last_ev = ev_make(pos, EV_SAMPLE);
+              if (first_ev == 0) first_ev = last_ev;
+              my_ls = (uint32_t)(pos - t_begin) + 1;
+              prev_ts = ts;
+            }
+          } else if (size != d.ip_sample_bytes) {
+            bad = true;
+            break;
+          }
+        } else if (type == REC_READ && (d.handled_mask & HBT_H_READ)) {
+          if ((uint64_t)size != 40 + 8 * tv.word_in(pos + 16)) {
+            bad = true;
+            break;
+          }
+        } else if (AGG == HBT_AGG_COUNT_DELTAS && type == REC_LOST &&
+                   (d.handled_mask & HBT_H_LOST)) {
+          last_ev = ev_make(pos, EV_LOST);
+          if (first_ev == 0) first_ev = last_ev;
+        }
+        mask |= 1u << (uint32_t)((pos - sb) >> 3);
+        pos += size;
+      }
+      my_x = (int32_t)(pos - t_begin);
+    }
+
+    // ---- phase 2: verify the guesses with a block-wide max-scan ----------------
+    // At a segment start without a known entry the smallest guess is the entry guess.
+    if (entry == kNone && my_entry != kNone)
+      atomicMin(&st.guess_min, (uint32_t)(my_entry - t_begin));
+    int32_t sx = my_x;
+    uint64_t sev = last_ev;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const int32_t ox = __shfl_up_sync(0xffffffffu, sx, o);
+      const uint64_t oe = __shfl_up_sync(0xffffffffu, sev, o);
+      if (lane >= o) {
+        sx = max(sx, ox);
+        sev = max(sev, oe);
+      }
+    }
+    const uint32_t wls = __reduce_max_sync(0xffffffffu, my_ls);
+    if (lane == 31) {
+      sm.warp_x[warp] = sx;
+      sm.warp_ev[warp] = sev;
+      sm.warp_ls[warp] = wls;
+    }
+    __syncthreads();
+    const uint64_t tile_entry =
+        entry != kNone ? entry
+                       : (st.guess_min != 0xFFFFFFFFu ? t_begin + st.guess_min : kNone);
+    int32_t px = __shfl_up_sync(0xffffffffu, sx, 1);  // exclusive prefixes
+    uint64_t pev = __shfl_up_sync(0xffffffffu, sev, 1);
+    if (lane == 0) {
+      px = -1;
+      pev = 0;
+    }
+    for (uint32_t w = 0; w < warp; ++w) {
+      px = max(px, sm.warp_x[w]);
+      pev = max(pev, sm.warp_ev[w]);
+    }
+    // position the record chain has reached before my sub-chunk
+    uint64_t reach = kNone;  // kNone: unknown (segment start and no guess yet)
+    if (tile_entry != kNone) {
+      reach = tile_entry;
+      if (px >= 0) reach = max(reach, t_begin + (uint64_t)px);
+    }
+    if (live) {
+      if (my_entry == kNone) {
+        if (reach != kNone && reach < se) bad = true;  // a start in (or before) my range
+      } else if (reach != my_entry) {
+        bad = true;
+      }
+    }
+    // interval state in front of my first SAMPLE
+    const uint64_t in_ev0 = max(st.ev, pev);
+    uint32_t rows_j = rows_local, unknown_j = unknown_local;
+    bool pending_seam = false;
+    if (AGG == HBT_AGG_COUNT_DELTAS && ev_kind(first_ev) == EV_SAMPLE) {
+      const uint32_t ik = ev_kind(in_ev0);
+      if (ik == EV_SAMPLE) {
+        if (tv.word(ev_pos(in_ev0) + 8) > tv.word_in(ev_pos(first_ev) + 8)) bad = true;
+        ++rows_j;
+      } else if (ik == EV_LOST) {
+        ++unknown_j;
+      } else {
+        pending_seam = true;  // resolved by k_finalize
+      }
+    }
+    uint32_t srow = rows_j;
+    if (AGG == HBT_AGG_COUNT_DELTAS) {
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        const uint32_t orow = __shfl_up_sync(0xffffffffu, srow, o);
+        if (lane >= o) srow += orow;
+      }
+      if (lane == 31) sm.warp_rows[warp] = srow;
+    }
+    if (bad) st.anomaly = 1;
+    __syncthreads();
+    const bool slow = st.anomaly != 0;
+
+    if (!stopped && !slow) {
+      // ---- phase 3: aggregate my records --------------------------------------
+      uint64_t row_i = st.n_rows + (srow - rows_j);
+      if (AGG == HBT_AGG_COUNT_DELTAS)
+        for (uint32_t w = 0; w < warp; ++w) row_i += sm.warp_rows[w];
+      uint64_t in_ev = in_ev0;
+      unsigned long long lost_sum = 0;
+      uint32_t m = mask;
+      while (m) {
+        const uint32_t w = __ffs(m) - 1;
+        m &= m - 1;
+        const uint64_t pos = sb + 8ull * w;
+        const uint64_t h = tv.word_in(pos);
+        const uint32_t type = hdr_type(h);
+        ++my_rec;
+        if (type == REC_SAMPLE && (d.handled_mask & HBT_H_SAMPLE)) {
+          ++my_sample;
+          if (AGG == HBT_AGG_IP_HISTOGRAM) {
+            const uint64_t ip = tv.word_in(pos + 8);
+            const uint32_t pid = (uint32_t)tv.word_in(pos + 16);
+            bool done = false;
+            if (!(ip == 0 && pid == 0)) {
+              uint32_t i = (uint32_t)mix64(ip ^ ((uint64_t)pid * 0x9E3779B97F4A7C15ull)) &
+                           (kHistSlots - 1);
+#pragma unroll 1
+              for (int pr = 0; pr < kHistProbes; ++pr, i = (i + 1) & (kHistSlots - 1)) {
+                uint32_t s = *reinterpret_cast<volatile uint32_t*>(h_state + i);
+                if (s == 0) {
+                  s = atomicCAS(h_state + i, 0u, 1u);
+                  if (s == 0) {  // claimed: publish the key, count = 1
+                    h_slots[i].x = ip;
+                    atomicAdd(reinterpret_cast<unsigned long long*>(&h_slots[i].y),
+                              (unsigned long long)pid | (1ull << 32));
+                    __threadfence_block();
+                    *reinterpret_cast<volatile uint32_t*>(h_state + i) = 2;
+                    done = true;
+                    break;
+                  }
+                }
+                if (s != 2) break;  // being written by another thread: count globally
+                const volatile ulonglong2* vs = h_slots + i;
+                if (vs->x == ip && (uint32_t)vs->y == pid) {
+                  atomicAdd(reinterpret_cast<unsigned long long*>(&h_slots[i].y), 1ull << 32);
+                  done = true;
+                  break;
+                }
+              }
+            }
+            if (!done) hist_insert_global(p.hist, seg.cpu, ip, pid, p.hist_inc);
+          } else if (AGG == HBT_AGG_COUNT_DELTAS) {
+            if (ev_kind(in_ev) == EV_SAMPLE) {
+              const uint64_t ppos = ev_pos(in_ev);
+              const uint64_t pts = tv.word(ppos + 8);
+              const uint64_t ts = tv.word_in(pos + 8);
+              uint64_t* row = seg.rows + (1 + row_i) * (2 + (uint64_t)d.n_events);
+              row[0] = pts;
+              row[1] = ts - pts;
+              for (uint32_t i = 0; i < d.n_events; ++i) {
+                const uint64_t v = xform(d, i, tv.word_in(pos + 40 + 8ull * i));
+                const uint64_t pv = xform(d, i, tv.word(ppos + 40 + 8ull * i));
+                row[2 + i] = v - pv;
+              }
+              ++row_i;
+            }
+            in_ev = ev_make(pos, EV_SAMPLE);
+          }
+        } else {
+          const int ci = counter_of(type, d.handled_mask);
+          if (ci == HBT_CNT_LOST) {
+            lost_sum += tv.word_in(pos + 16);
+            if (AGG == HBT_AGG_COUNT_DELTAS) in_ev = ev_make(pos, EV_LOST);
+          } else if (ci >= 0) {
+            atomicAdd(&st.counters[ci], 1ull);
+          }
+        }
+      }
+      if (lost_sum) atomicAdd(&st.counters[HBT_CNT_LOST], lost_sum);
+      if (unknown_j) atomicAdd(&st.n_unknown, (unsigned long long)unknown_j);
+      if (pending_seam) st.first_ev = first_ev;  // at most one thread per segment
+    }
+    __syncthreads();
+    if (tid == 0) {
+      if (!stopped) {
+        if (slow) {
+          // literal consume() over this tile by one thread
+          ++st.slow_tiles;
+          if (st.pos == kNone && st.guess_min != 0xFFFFFFFFu) st.pos = t_begin + st.guess_min;
+          if (st.pos != kNone) consume_sequential<AGG>(p, ring, seg, st, t_end);
+        } else {
+          if (tile_entry != kNone) {
+            int32_t all_x = -1;
+            for (uint32_t w = 0; w < kThreads / 32; ++w) all_x = max(all_x, sm.warp_x[w]);
+            uint64_t np = tile_entry;
+            if (all_x >= 0) np = max(np, t_begin + (uint64_t)all_x);
+            if (st.entry == kNone && tile_entry < t_end) st.entry = tile_entry;
+            st.pos = np;
+          }
+          uint64_t tev = 0;
+          uint32_t trows = 0, tls = 0;
+          for (uint32_t w = 0; w < kThreads / 32; ++w) {
+            tev = max(tev, sm.warp_ev[w]);
+            tls = max(tls, sm.warp_ls[w]);
+            if (AGG == HBT_AGG_COUNT_DELTAS) trows += sm.warp_rows[w];
+          }
+          st.ev = max(st.ev, tev);
+          if (tls) st.last_sample = t_begin + tls - 1;
+          st.n_rows += trows;
+        }
+      }
+      st.anomaly = 0;
+      st.guess_min = 0xFFFFFFFFu;
+    }
+    // every generic-proxy read of stage (t % kStages) is ordered before the bulk
+    // copy that thread 0 issues into it after this barrier
+    fence_proxy_async();
+    __syncthreads();
+  }
+
+  // ---- segment epilogue --------------------------------------------------------
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    my_rec += __shfl_xor_sync(0xffffffffu, my_rec, o);
+    my_sample += __shfl_xor_sync(0xffffffffu, my_sample, o);
+  }
+  if (lane == 0) {
+    atomicAdd(&st.n_rec, my_rec);
+    atomicAdd(&st.counters[HBT_CNT_SAMPLE], my_sample);
+  }
+  if (AGG == HBT_AGG_IP_HISTOGRAM) {
+    for (int i = tid; i < kHistSlots; i += kThreads) {
+      if (h_state[i] == 2) {
+        const ulonglong2 s = h_slots[i];
+        hist_insert_global(p.hist, seg.cpu, s.x, (uint32_t)s.y,
+                           (uint32_t)(s.y >> 32) * p.hist_inc);
+      }
+    }
+  }
+  __syncthreads();
+  if (tid == 0) {
+    SegResult& r = p.results[blockIdx.x];
+    r.entry = st.entry;
+    r.exit = st.pos;
+    r.n_records = st.n_rec;
+    for (int i = 0; i < HBT_NUM_COUNTERS; ++i) r.counters[i] = st.counters[i];
+    r.n_rows = st.n_rows;
+    r.n_unknown = st.n_unknown;
+    r.first_ev = st.first_ev;
+    r.last_ev = st.ev;
+    r.last_sample = st.last_sample;
+    r.err = st.err;
+    r.err_pos = st.err_pos;
+    r.slow_tiles = st.slow_tiles;
+    r.hist_overflow = 0;
+  }
+}
+
+// Rings too small to tile (data_size < 2*kTile): one thread per CPU runs the
+// literal consume() over the whole window.  Same outputs as k_decode.
+template <int AGG>
+__global__ void __launch_bounds__(32) k_decode_small(const DecodeParams p, uint32_t n_segs) {
+  const uint32_t g = blockIdx.x * blockDim.x + threadIdx.x;
+  if (g >= n_segs) return;
+  const SegDesc seg = p.segs[g];
+  const RingDesc ring = p.rings[seg.cpu];
+  SegState st;
+  st.pos = ring.tail;
+  st.ev = 0;
+  st.first_ev = 0;
+  st.last_sample = kNone;
+  st.entry = kNone;
+  st.n_rec = st.n_rows = st.n_unknown = 0;
+  for (int i = 0; i < HBT_NUM_COUNTERS; ++i) st.counters[i] = 0;
+  st.err = 0;
+  st.err_pos = 0;
+  st.slow_tiles = 1;
+  consume_sequential<AGG>(p, ring, seg, st, ring.head);
+  SegResult& r = p.results[g];
+  r.entry = st.entry;
+  r.exit = st.pos;
+  r.n_records = st.n_rec;
+  for (int i = 0; i < HBT_NUM_COUNTERS; ++i) r.counters[i] = st.counters[i];
+  r.n_rows = st.n_rows;
+  r.n_unknown = st.n_unknown;
+  r.first_ev = st.first_ev;
+  r.last_ev = st.ev;
+  r.last_sample = st.last_sample;
+  r.err = st.err;
+  r.err_pos = st.err_pos;
+  r.slow_tiles = 1;
+  r.hist_overflow = 0;
+}
+
+// ---------------------------------------------------------------------------
+// k_finalize: one thread per CPU chains the segments (exit == next entry),
+// resolves the seams between segments, and produces consume()'s return value
+// and the generator state after the call.
+// ---------------------------------------------------------------------------
+constexpr uint64_t kClampLocate = ~0ull - 1;  // clamp_head value: "locate record #max"
+
+struct FinalizeParams {
+  const RingDesc* rings;
+  const SegDesc* segs;
+  uint64_t* forced_out;  // per segment: true entry found for a wrongly guessed segment
+  const SegResult* results;
+  const CpuState* state_in;
+  CpuState* state_out;
+  hbt_cpu_result* out;
+  uint8_t* seam_valid;   // per segment
+  uint64_t* clamp_head;  // per CPU: kNone, kClampLocate, or where a re-run must stop
+  int64_t* clamp_ret;    // per CPU: return value to report after such a re-run
+  uint64_t* locate_from; // per CPU: record start to count from ...
+  uint64_t* locate_skip; // ... and how many records to skip to find the cut
+  uint32_t* flags;       // [0] re-run needed
+  uint32_t n_cpus;
+  hbt_decode_desc d;
+  int agg;
+  uint64_t seg_limit_tile;  // kTile, or 0 for the untiled small-ring path
+};
+
+__global__ void __launch_bounds__(64) k_finalize(const FinalizeParams p) {
+  const uint32_t c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= p.n_cpus) return;
+  const RingDesc ring = p.rings[c];
+  const hbt_decode_desc& d = p.d;
+  const CpuState& sin = p.state_in[c];
+  CpuState& sout = p.state_out[c];
+  hbt_cpu_result& out = p.out[c];
+
+  uint64_t counters[HBT_NUM_COUNTERS];
+  for (int i = 0; i < HBT_NUM_COUNTERS; ++i) counters[i] = sin.counters[i];
+  uint64_t unknown = sin.num_unknown;
+  uint64_t n_rec = 0, n_rows = 0;
+  uint64_t pos = ring.tail;
+  // interval state: previous sample position (kPrevCarry = carry arrays) or invalid
+  bool valid = sin.carry_tstamp != kInvalidTs;
+  uint64_t prev_pos = kPrevCarry;  // last SAMPLE seen (defines last_[])
+  int32_t err = 0;
+  bool redo = false;
+
+  auto prev_ts = [&]() {
+    return prev_pos == kPrevCarry ? sin.carry_tstamp : ring_word_g(ring, prev_pos + 8);
+  };
+  auto prev_val = [&](uint32_t i) {
+    return prev_pos == kPrevCarry ? sin.carry_last[i]
+                                  : xform(d, i, ring_word_g(ring, prev_pos + 40 + 8ull * i));
+  };
+
+  for (uint32_t s = 0; s < ring.n_seg; ++s) {
+    const uint32_t gi = ring.seg_begin + s;
+    const SegResult& r = p.results[gi];
+    const SegDesc& sd = p.segs[gi];
+    const uint64_t seg_limit =
+        p.seg_limit_tile ? min(sd.tile_end * p.seg_limit_tile, ring.head) : ring.head;
+    p.seam_valid[gi] = 0;
+    if (pos >= seg_limit) {
+      // the record chain jumps over this segment: nothing may start in it
+      if (r.entry != kNone) {
+        p.forced_out[gi] = pos;
+        redo = true;
+        break;
+      }
+      continue;
+    }
+    if (r.entry != pos) {
+      p.forced_out[gi] = pos;
+      redo = true;
+      break;
+    }
+    if (n_rec + r.n_records > (uint64_t)d.max_records) {
+      // consume(max_num_records) stops inside this segment: the host locates the
+      // cut (record #max) and re-runs with the window clamped there
+      p.clamp_head[c] = kClampLocate;
+      p.clamp_ret[c] = (int64_t)d.max_records;
+      p.locate_from[c] = pos;
+      p.locate_skip[c] = (uint64_t)d.max_records - n_rec;
+      redo = true;
+      break;
+    }
+    // seam: the segment's first SAMPLE had no SAMPLE/LOST before it in the segment
+    if (p.agg == HBT_AGG_COUNT_DELTAS && ev_kind(r.first_ev) == EV_SAMPLE) {
+      const uint64_t sp = ev_pos(r.first_ev);
+      const uint64_t ts = ring_word_g(ring, sp + 8);
+      if (!valid) {
+        ++unknown;  // re-seed (PerCpuCountSampleGenerator.h:135-154)
+      } else {
+        const uint64_t pts = prev_ts();
+        if (pts > ts) {
+          // timestamp regression exactly at a seam: re-run up to that record
+          p.clamp_head[c] = sp;
+          p.clamp_ret[c] = -1;  // -EPERM
+          redo = true;
+          break;
+        }
+        uint64_t* row = sd.rows;  // slot 0 of the slab
+        row[0] = pts;
+        row[1] = ts - pts;
+        for (uint32_t i = 0; i < d.n_events; ++i)
+          row[2 + i] = xform(d, i, ring_word_g(ring, sp + 40 + 8ull * i)) - prev_val(i);
+        p.seam_valid[gi] = 1;
+        ++n_rows;
+      }
+    }
+    n_rec += r.n_records;
+    n_rows += r.n_rows;
+    unknown += r.n_unknown;
+    for (int i = 0; i < HBT_NUM_COUNTERS; ++i) counters[i] += r.counters[i];
+    if (r.last_ev != 0) valid = ev_kind(r.last_ev) == EV_SAMPLE;
+    if (r.last_sample != kNone) prev_pos = r.last_sample;
+    pos = r.exit;
+    if (r.err) {
+      err = r.err;
+      pos = r.err_pos;
+      if (p.agg == HBT_AGG_IP_HISTOGRAM && s + 1 < ring.n_seg && ring.override_ret == 0) {
+        // later segments already added their samples to the shared table
+        p.clamp_head[c] = r.err_pos;
+        p.clamp_ret[c] = r.err;
+        redo = true;
+      }
+      break;
+    }
+  }
+  if (redo) {
+    atomicExch(&p.flags[0], 1u);
+    return;
+  }
+
+  out.n_records = n_rec;
+  out.new_tail = pos;
+  out.n_rows = n_rows;
+  for (int i = 0; i < HBT_NUM_COUNTERS; ++i) out.counters[i] = counters[i];
+  out.num_unknown_count_interval = unknown;
+  if (err) {
+    out.ret = err;
+  } else if (ring.override_ret > 0) {
+    out.ret = (int64_t)n_rec;  // stopped by max_num_records
+  } else if (ring.override_ret < 0) {
+    out.ret = ring.override_ret;
+  } else if (pos == ring.head && n_rec < (uint64_t)d.max_records) {
+    out.ret = -61;  // -ENODATA (CpuEventsGroup.h:1507-1509)
+  } else {
+    out.ret = (int64_t)n_rec;
+  }
+
+  // generator state after the call
+  for (int i = 0; i < HBT_NUM_COUNTERS; ++i) sout.counters[i] = counters[i];
+  sout.num_unknown = unknown;
+  uint64_t cts = sin.carry_tstamp;
+  if (p.agg == HBT_AGG_COUNT_DELTAS) {
+    // count_.tstamp: tstamp of the last SAMPLE, invalid after a LOST, a regression
+    // or a failed write (PerCpuCountSampleGenerator.h:122,161,192); last_[] keeps
+    // the (transformed) values of the last SAMPLE whatever followed it.
+    cts = valid ? prev_ts() : kInvalidTs;
+    // a regression found at a seam arrives here as the override of a clamped re-run
+    if (ring.override_ret == -1) cts = kInvalidTs;
+    for (uint32_t i = 0; i < d.n_events; ++i) sout.carry_last[i] = prev_val(i);
+    for (uint32_t i = d.n_events; i < HBT_MAX_EVENTS; ++i) sout.carry_last[i] = sin.carry_last[i];
+  } else {
+    for (uint32_t i = 0; i < HBT_MAX_EVENTS; ++i) sout.carry_last[i] = sin.carry_last[i];
+  }
+  sout.carry_tstamp = cts;
+  out.carry_tstamp = cts;
+}
+
+// Position of the record `skip` records after `from` (header walk by one thread
+// per flagged CPU); used only for a finite max_num_records.
+__global__ void __launch_bounds__(64)
+    k_locate(const RingDesc* rings, uint32_t n_cpus, uint64_t* clamp_head,
+             const uint64_t* locate_from, const uint64_t* locate_skip) {
+  const uint32_t c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= n_cpus || clamp_head[c] != kClampLocate) return;
+  const RingDesc ring = rings[c];
+  uint64_t pos = locate_from[c];
+  for (uint64_t k = 0; k < locate_skip[c]; ++k) pos += hdr_size(ring_word_g(ring, pos));
+  clamp_head[c] = pos;
+}
+
+// Compact the occupied slots of the table into entries (cpu = cpu_base + local).
+__global__ void __launch_bounds__(256)
+    k_hist_compact(const HistTable t, uint32_t n_cpus, uint32_t cpu_base, hbt_hist_entry* out,
+                   unsigned long long* n_out, uint64_t cap) {
+  const uint64_t total = t.slots_per_cpu * n_cpus;
+  for (uint64_t g = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; g < total + n_cpus;
+       g += (uint64_t)gridDim.x * blockDim.x) {
+    hbt_hist_entry e;
+    if (g < total) {
+      const ulonglong2 s = t.slots[g];
+      const uint32_t cnt = (uint32_t)(s.y >> 32);
+      if (cnt == 0) continue;
+      e.ip = s.x;
+      e.pid = (uint32_t)s.y;
+      e.cpu = cpu_base + (uint32_t)(g / t.slots_per_cpu);
+      e.count = cnt;
+    } else {
+      const uint32_t c = (uint32_t)(g - total);
+      if (t.zero_key[c] == 0) continue;
+      e.ip = 0;
+      e.pid = 0;
+      e.cpu = cpu_base + c;
+      e.count = t.zero_key[c];
+    }
+    const unsigned long long i = atomicAdd(n_out, 1ull);
+    if (out && i < cap) out[i] = e;
+  }
+}
+
+}  // namespace hbt

@@ -1,0 +1,994 @@
+// libhbt_b200.so: the C-ABI of include/hbt_b200.h over the sm_100a kernels in
+// counts.cuh / decode.cuh.  Host orchestration only: buffers, segment tables,
+// launches, and the (rare) exact re-run loop.  There is no CPU implementation of
+// any entry point: without a CUDA device hbt_create fails and nothing else runs.
+#include <cuda_runtime.h>
+#include <cerrno>
+#include <cstdarg>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "../../include/hbt_b200.h"
+#include "counts.cuh"
+#include "decode.cuh"
+
+using namespace hbt;
+
+namespace {
+
+constexpr int kMaxSegsPerCpu = 64;
+constexpr int kMaxRatios = 64;
+
+template <class T>
+struct DevBuf {
+  T* p = nullptr;
+  size_t n = 0;  // capacity in elements
+  cudaError_t reserve(size_t want) {
+    if (want <= n) return cudaSuccess;
+    if (p) cudaFree(p);
+    p = nullptr;
+    n = 0;
+    cudaError_t e = cudaMalloc(&p, want * sizeof(T));
+    if (e == cudaSuccess) n = want;
+    return e;
+  }
+  void release() {
+    if (p) cudaFree(p);
+    p = nullptr;
+    n = 0;
+  }
+};
+
+template <class T>
+struct PinBuf {
+  T* p = nullptr;
+  size_t n = 0;
+  cudaError_t reserve(size_t want) {
+    if (want <= n) return cudaSuccess;
+    if (p) cudaFreeHost(p);
+    p = nullptr;
+    n = 0;
+    cudaError_t e = cudaMallocHost(&p, want * sizeof(T));
+    if (e == cudaSuccess) n = want;
+    return e;
+  }
+  void release() {
+    if (p) cudaFreeHost(p);
+    p = nullptr;
+    n = 0;
+  }
+};
+
+struct Window {
+  const uint8_t* base = nullptr;
+  uint64_t data_size = 0;
+  uint64_t tail = 0, head = 0;
+  bool active = false;
+};
+
+}  // namespace
+
+struct hbt_ctx {
+  int device = 0;
+  int sm_count = 148;
+  uint32_t max_cpus = 0, max_events = 0;
+  cudaStream_t own_stream = nullptr;
+  cudaStream_t stream = nullptr;
+  std::string err;
+  uint64_t launches = 0;
+
+  // rings
+  uint32_t n_cpus = 0;
+  uint64_t data_size = 0;
+  DevBuf<uint8_t> ring_store;  // library-owned images
+  std::vector<Window> win;
+  uint32_t cpu_base = 0;
+
+  // generator state (double-buffered: [cur] is committed)
+  DevBuf<CpuState> state[2];
+  int cur = 0;
+
+  // decode scratch
+  DevBuf<RingDesc> d_rings;
+  DevBuf<SegDesc> d_segs;
+  DevBuf<SegResult> d_results;
+  DevBuf<hbt_cpu_result> d_out;
+  DevBuf<uint8_t> d_seam;
+  DevBuf<uint64_t> d_forced;
+  DevBuf<uint64_t> d_clamp_head, d_locate_from, d_locate_skip;
+  DevBuf<int64_t> d_clamp_ret;
+  DevBuf<uint32_t> d_flags;
+  DevBuf<uint64_t> d_rows;
+  PinBuf<RingDesc> h_rings;
+  PinBuf<SegDesc> h_segs;
+  PinBuf<SegResult> h_results;
+  PinBuf<hbt_cpu_result> h_out;
+  PinBuf<uint8_t> h_seam;
+  PinBuf<uint64_t> h_clamp_head;
+  PinBuf<int64_t> h_clamp_ret;
+  PinBuf<uint32_t> h_flags;
+  uint32_t n_segs = 0;
+  bool tiled = true;
+  bool attr_set[3] = {false, false, false};
+  bool pending = false;  // a decode was launched and not yet fetched
+  bool have_results = false;
+  hbt_decode_desc desc{};
+  uint32_t reruns = 0;
+
+  // histogram
+  DevBuf<ulonglong2> hist_slots;
+  DevBuf<uint64_t> hist_zero;
+  DevBuf<uint32_t> hist_overflow;
+  uint64_t hist_slots_per_cpu = 0;
+  DevBuf<hbt_hist_entry> hist_out;
+  DevBuf<unsigned long long> hist_n;
+
+  // counts scratch
+  DevBuf<hbt_ratio> d_ratios;
+  DevBuf<uint64_t> c_reads, c_sums, c_scaled, c_deltas;
+  DevBuf<float> c_rates;
+  DevBuf<double> c_ratio;
+};
+
+namespace {
+
+int fail(hbt_ctx* c, int code, const char* fmt, ...) {
+  char buf[512];
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(buf, sizeof(buf), fmt, ap);
+  va_end(ap);
+  if (c) c->err = buf;
+  return code;
+}
+
+int cuda_fail(hbt_ctx* c, cudaError_t e, const char* what) {
+  return fail(c, e == cudaErrorMemoryAllocation ? -ENOMEM : -EIO, "%s: %s", what,
+              cudaGetErrorString(e));
+}
+
+#define CU(call)                                       \
+  do {                                                 \
+    cudaError_t e__ = (call);                          \
+    if (e__ != cudaSuccess) return cuda_fail(ctx, e__, #call); \
+  } while (0)
+
+bool is_pow2(uint64_t x) { return x && !(x & (x - 1)); }
+
+size_t decode_smem_bytes(int agg) {
+  size_t s = (size_t)kStages * kTile + ((sizeof(Smem) + 15) & ~size_t(15));
+  if (agg == HBT_AGG_IP_HISTOGRAM) s += (size_t)kHistSlots * (16 + 4);
+  return s;
+}
+
+int validate_desc(hbt_ctx* ctx, const hbt_decode_desc* d) {
+  if (!d) return fail(ctx, -EINVAL, "desc is NULL");
+  if (d->sample_layout > HBT_SAMPLE_IP) return fail(ctx, -EINVAL, "bad sample_layout");
+  if (d->aggregate > HBT_AGG_IP_HISTOGRAM) return fail(ctx, -EINVAL, "bad aggregate");
+  if (d->aggregate == HBT_AGG_COUNT_DELTAS) {
+    if (d->sample_layout != HBT_SAMPLE_GROUP || !(d->handled_mask & HBT_H_SAMPLE))
+      return fail(ctx, -EINVAL, "COUNT_DELTAS needs handled group SAMPLE records");
+    if (d->n_events == 0 || d->n_events > ctx->max_events)
+      return fail(ctx, -EINVAL, "n_events %u outside 1..%u", d->n_events, ctx->max_events);
+    if (d->tsc_transform_mask && d->tsc.time_shift >= 64)
+      return fail(ctx, -EINVAL, "time_shift >= 64");
+  }
+  if (d->aggregate == HBT_AGG_IP_HISTOGRAM) {
+    if (d->sample_layout != HBT_SAMPLE_IP || !(d->handled_mask & HBT_H_SAMPLE))
+      return fail(ctx, -EINVAL, "IP_HISTOGRAM needs handled IP SAMPLE records");
+    if (ctx->hist_slots_per_cpu == 0) return fail(ctx, -EINVAL, "hbt_hist_configure first");
+  }
+  if (d->sample_layout == HBT_SAMPLE_IP &&
+      (d->ip_sample_bytes < 40 || (d->ip_sample_bytes & 7) || d->ip_sample_bytes > 65528))
+    return fail(ctx, -EINVAL, "bad ip_sample_bytes %u", d->ip_sample_bytes);
+  return 0;
+}
+
+// Build ring / segment tables for the current windows (+ clamps) into pinned
+// memory and upload them.
+int build_tables(hbt_ctx* ctx, const uint64_t* clamp_head, const int64_t* clamp_ret,
+                 const std::vector<SegDesc>* keep_forced) {
+  const hbt_decode_desc& d = ctx->desc;
+  const uint32_t C = ctx->n_cpus;
+  CU(ctx->h_rings.reserve(C));
+  CU(ctx->d_rings.reserve(C));
+
+  uint32_t active = 0;
+  bool any_small = false;
+  for (uint32_t c = 0; c < C; ++c) {
+    const Window& w = ctx->win[c];
+    if (w.active && w.head > w.tail) {
+      ++active;
+      if (w.data_size < 2ull * kTile) any_small = true;
+    }
+  }
+  ctx->tiled = !any_small;
+
+  // segments per CPU: enough CTAs to fill the machine a few times, at least
+  // 8 tiles (128 KiB) per segment
+  const uint64_t target_ctas = (uint64_t)ctx->sm_count * 8;
+  uint32_t segs_per_cpu = active ? (uint32_t)((target_ctas + active - 1) / active) : 1;
+  if (segs_per_cpu > kMaxSegsPerCpu) segs_per_cpu = kMaxSegsPerCpu;
+  if (segs_per_cpu < 1) segs_per_cpu = 1;
+
+  std::vector<SegDesc> segs;
+  segs.reserve((size_t)C * 4);
+  const uint64_t row_words = 2 + (uint64_t)d.n_events;
+  uint64_t rows_total_words = 0;
+  // first pass: segment geometry and row slab sizes
+  for (uint32_t c = 0; c < C; ++c) {
+    const Window& w = ctx->win[c];
+    RingDesc& r = ctx->h_rings.p[c];
+    memset(&r, 0, sizeof(r));
+    r.base = w.base;
+    r.mask = w.data_size ? w.data_size - 1 : 0;
+    r.tail = w.tail;
+    r.true_head = w.head;
+    r.head = w.head;
+    r.override_ret = 0;
+    if (clamp_head && clamp_head[c] != kNone) {
+      r.head = clamp_head[c] < w.head ? clamp_head[c] : w.head;
+      r.override_ret = clamp_ret[c];
+    }
+    r.seg_begin = (uint32_t)segs.size();
+    r.n_seg = 0;
+    if (!w.active || w.head <= w.tail) continue;  // geometry follows the TRUE window
+    if (!ctx->tiled) {
+      SegDesc s{};
+      s.cpu = c;
+      s.seg = 0;
+      s.tile_begin = 0;
+      s.tile_end = 0;
+      s.forced_entry = kNone;
+      s.rows_cap = (r.head - r.tail) / (40 + 8ull * d.n_events) + 2;
+      segs.push_back(s);
+      r.n_seg = 1;
+    } else {
+      const uint64_t t0 = r.tail / kTile;
+      // segment geometry is derived from the TRUE head so that a clamped re-run
+      // keeps the same segments (and the forced entries keep their meaning)
+      const uint64_t t1 = (w.head + kTile - 1) / kTile;
+      const uint64_t nt = t1 - t0;
+      uint64_t per = (nt + segs_per_cpu - 1) / segs_per_cpu;
+      if (per < 8) per = 8;
+      uint32_t k = 0;
+      for (uint64_t tb = t0; tb < t1; tb += per, ++k) {
+        SegDesc s{};
+        s.cpu = c;
+        s.seg = k;
+        s.tile_begin = tb;
+        s.tile_end = tb + per < t1 ? tb + per : t1;
+        s.forced_entry = kNone;
+        s.rows_cap = ((s.tile_end - s.tile_begin) * kTile) / (40 + 8ull * d.n_events) + 2;
+        segs.push_back(s);
+      }
+      r.n_seg = k;
+    }
+    if (d.aggregate == HBT_AGG_COUNT_DELTAS)
+      for (uint32_t k = 0; k < r.n_seg; ++k)
+        rows_total_words += (1 + segs[r.seg_begin + k].rows_cap) * row_words;
+  }
+  if (keep_forced && keep_forced->size() == segs.size())
+    for (size_t i = 0; i < segs.size(); ++i) segs[i].forced_entry = (*keep_forced)[i].forced_entry;
+
+  if (d.aggregate == HBT_AGG_COUNT_DELTAS) {
+    CU(ctx->d_rows.reserve(rows_total_words ? rows_total_words : 1));
+    uint64_t off = 0;
+    for (uint32_t c = 0; c < C; ++c) {
+      RingDesc& r = ctx->h_rings.p[c];
+      r.rows = ctx->d_rows.p + off;
+      for (uint32_t k = 0; k < r.n_seg; ++k) {
+        SegDesc& s = segs[r.seg_begin + k];
+        s.rows = ctx->d_rows.p + off;
+        off += (1 + s.rows_cap) * row_words;
+      }
+    }
+  }
+  ctx->n_segs = (uint32_t)segs.size();
+  const size_t ns = segs.size() ? segs.size() : 1;
+  CU(ctx->h_segs.reserve(ns));
+  CU(ctx->d_segs.reserve(ns));
+  CU(ctx->d_results.reserve(ns));
+  CU(ctx->h_results.reserve(ns));
+  CU(ctx->d_seam.reserve(ns));
+  CU(ctx->d_forced.reserve(ns));
+  CU(ctx->h_seam.reserve(ns));
+  if (!segs.empty()) memcpy(ctx->h_segs.p, segs.data(), segs.size() * sizeof(SegDesc));
+  CU(cudaMemcpyAsync(ctx->d_rings.p, ctx->h_rings.p, C * sizeof(RingDesc),
+                     cudaMemcpyHostToDevice, ctx->stream));
+  if (!segs.empty())
+    CU(cudaMemcpyAsync(ctx->d_segs.p, ctx->h_segs.p, segs.size() * sizeof(SegDesc),
+                       cudaMemcpyHostToDevice, ctx->stream));
+  return 0;
+}
+
+template <int AGG>
+int launch_decode_agg(hbt_ctx* ctx, uint32_t hist_inc) {
+  DecodeParams p{};
+  p.rings = ctx->d_rings.p;
+  p.segs = ctx->d_segs.p;
+  p.results = ctx->d_results.p;
+  p.state_in = ctx->state[ctx->cur].p;
+  p.d = ctx->desc;
+  p.hist.slots = ctx->hist_slots.p;
+  p.hist.slots_per_cpu = ctx->hist_slots_per_cpu;
+  p.hist.zero_key = ctx->hist_zero.p;
+  p.hist.overflow = ctx->hist_overflow.p;
+  p.hist_inc = hist_inc;
+  if (ctx->n_segs == 0) return 0;
+  if (ctx->tiled) {
+    const size_t smem = decode_smem_bytes(AGG);
+    if (!ctx->attr_set[AGG]) {
+      CU(cudaFuncSetAttribute(k_decode<AGG>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                              (int)smem));
+      ctx->attr_set[AGG] = true;
+    }
+    k_decode<AGG><<<ctx->n_segs, kThreads, smem, ctx->stream>>>(p);
+  } else {
+    k_decode_small<AGG><<<(ctx->n_segs + 31) / 32, 32, 0, ctx->stream>>>(p, ctx->n_segs);
+  }
+  ++ctx->launches;
+  CU(cudaGetLastError());
+  return 0;
+}
+
+int launch_decode(hbt_ctx* ctx, uint32_t hist_inc) {
+  switch (ctx->desc.aggregate) {
+    case HBT_AGG_NONE: return launch_decode_agg<HBT_AGG_NONE>(ctx, hist_inc);
+    case HBT_AGG_COUNT_DELTAS: return launch_decode_agg<HBT_AGG_COUNT_DELTAS>(ctx, hist_inc);
+    default: return launch_decode_agg<HBT_AGG_IP_HISTOGRAM>(ctx, hist_inc);
+  }
+}
+
+int launch_finalize(hbt_ctx* ctx) {
+  const uint32_t C = ctx->n_cpus;
+  FinalizeParams f{};
+  f.rings = ctx->d_rings.p;
+  f.segs = ctx->d_segs.p;
+  f.forced_out = ctx->d_forced.p;
+  f.results = ctx->d_results.p;
+  f.state_in = ctx->state[ctx->cur].p;
+  f.state_out = ctx->state[ctx->cur ^ 1].p;
+  f.out = ctx->d_out.p;
+  f.seam_valid = ctx->d_seam.p;
+  f.clamp_head = ctx->d_clamp_head.p;
+  f.clamp_ret = ctx->d_clamp_ret.p;
+  f.locate_from = ctx->d_locate_from.p;
+  f.locate_skip = ctx->d_locate_skip.p;
+  f.flags = ctx->d_flags.p;
+  f.n_cpus = C;
+  f.d = ctx->desc;
+  f.agg = (int)ctx->desc.aggregate;
+  f.seg_limit_tile = ctx->tiled ? kTile : 0;
+  k_finalize<<<(C + 63) / 64, 64, 0, ctx->stream>>>(f);
+  ++ctx->launches;
+  CU(cudaGetLastError());
+  return 0;
+}
+
+// Launch decode + finalize for the tables currently uploaded.
+int run_once(hbt_ctx* ctx, uint32_t hist_inc) {
+  CU(cudaMemsetAsync(ctx->d_flags.p, 0, 4 * sizeof(uint32_t), ctx->stream));
+  CU(cudaMemsetAsync(ctx->d_clamp_head.p, 0xFF, ctx->n_cpus * sizeof(uint64_t), ctx->stream));
+  CU(cudaMemsetAsync(ctx->d_forced.p, 0xFF, (ctx->n_segs ? ctx->n_segs : 1) * sizeof(uint64_t),
+                     ctx->stream));
+  int rc = launch_decode(ctx, hist_inc);
+  if (rc) return rc;
+  return launch_finalize(ctx);
+}
+
+}  // namespace
+
+static int complete_decode(hbt_ctx* ctx);
+
+extern "C" {
+
+int hbt_abi_version(void) { return HBT_B200_ABI_VERSION; }
+
+int hbt_create(hbt_ctx** out, int device, uint32_t max_cpus, uint32_t max_events) {
+  if (!out) return -EINVAL;
+  *out = nullptr;
+  if (max_cpus == 0 || max_cpus > HBT_MAX_CPUS || max_events == 0 || max_events > HBT_MAX_EVENTS)
+    return -EINVAL;
+  int n = 0;
+  if (cudaGetDeviceCount(&n) != cudaSuccess || n <= 0 || device < 0 || device >= n) {
+    cudaGetLastError();
+    return -ENODEV;
+  }
+  if (cudaSetDevice(device) != cudaSuccess) return -ENODEV;
+  cudaDeviceProp prop;
+  if (cudaGetDeviceProperties(&prop, device) != cudaSuccess) return -ENODEV;
+  if (prop.major < 10) return -ENODEV;  // sm_100a code only
+  hbt_ctx* ctx = new hbt_ctx();
+  ctx->device = device;
+  ctx->sm_count = prop.multiProcessorCount;
+  ctx->max_cpus = max_cpus;
+  ctx->max_events = max_events;
+  if (cudaStreamCreateWithFlags(&ctx->own_stream, cudaStreamNonBlocking) != cudaSuccess) {
+    delete ctx;
+    return -EIO;
+  }
+  ctx->stream = ctx->own_stream;
+  *out = ctx;
+  return 0;
+}
+
+void hbt_destroy(hbt_ctx* ctx) {
+  if (!ctx) return;
+  cudaSetDevice(ctx->device);
+  cudaStreamSynchronize(ctx->stream);
+  ctx->ring_store.release();
+  ctx->state[0].release();
+  ctx->state[1].release();
+  ctx->d_rings.release();
+  ctx->d_segs.release();
+  ctx->d_results.release();
+  ctx->d_out.release();
+  ctx->d_seam.release();
+  ctx->d_forced.release();
+  ctx->d_clamp_head.release();
+  ctx->d_locate_from.release();
+  ctx->d_locate_skip.release();
+  ctx->d_clamp_ret.release();
+  ctx->d_flags.release();
+  ctx->d_rows.release();
+  ctx->h_rings.release();
+  ctx->h_segs.release();
+  ctx->h_results.release();
+  ctx->h_out.release();
+  ctx->h_seam.release();
+  ctx->h_clamp_head.release();
+  ctx->h_clamp_ret.release();
+  ctx->h_flags.release();
+  ctx->hist_slots.release();
+  ctx->hist_zero.release();
+  ctx->hist_overflow.release();
+  ctx->hist_out.release();
+  ctx->hist_n.release();
+  ctx->d_ratios.release();
+  ctx->c_reads.release();
+  ctx->c_sums.release();
+  ctx->c_scaled.release();
+  ctx->c_deltas.release();
+  ctx->c_rates.release();
+  ctx->c_ratio.release();
+  if (ctx->own_stream) cudaStreamDestroy(ctx->own_stream);
+  delete ctx;
+}
+
+const char* hbt_last_error(const hbt_ctx* ctx) { return ctx ? ctx->err.c_str() : "no context"; }
+
+int hbt_set_stream(hbt_ctx* ctx, void* cuda_stream) {
+  if (!ctx) return -EINVAL;
+  ctx->stream = cuda_stream ? static_cast<cudaStream_t>(cuda_stream) : ctx->own_stream;
+  return 0;
+}
+
+int hbt_sync(hbt_ctx* ctx) {
+  if (!ctx) return -EINVAL;
+  CU(cudaStreamSynchronize(ctx->stream));
+  return 0;
+}
+
+uint64_t hbt_launch_count(const hbt_ctx* ctx) { return ctx ? ctx->launches : 0; }
+
+int hbt_set_cpu_base(hbt_ctx* ctx, uint32_t cpu_base) {
+  if (!ctx) return -EINVAL;
+  ctx->cpu_base = cpu_base;
+  return 0;
+}
+
+// ---- rings -----------------------------------------------------------------
+
+int hbt_ring_reset_state(hbt_ctx* ctx, uint64_t seed_tstamp) {
+  if (!ctx || ctx->n_cpus == 0) return fail(ctx, -EINVAL, "no rings configured");
+  std::vector<CpuState> init(ctx->n_cpus);
+  memset(init.data(), 0, init.size() * sizeof(CpuState));
+  for (auto& s : init) s.carry_tstamp = seed_tstamp;
+  CU(cudaMemcpyAsync(ctx->state[ctx->cur].p, init.data(), init.size() * sizeof(CpuState),
+                     cudaMemcpyHostToDevice, ctx->stream));
+  CU(cudaStreamSynchronize(ctx->stream));
+  for (auto& w : ctx->win) w.active = false;
+  ctx->pending = false;
+  ctx->have_results = false;
+  return 0;
+}
+
+static int configure_common(hbt_ctx* ctx, uint32_t n_cpus) {
+  ctx->n_cpus = n_cpus;
+  ctx->win.assign(n_cpus, Window());
+  CU(ctx->state[0].reserve(n_cpus));
+  CU(ctx->state[1].reserve(n_cpus));
+  CU(ctx->d_out.reserve(n_cpus));
+  CU(ctx->h_out.reserve(n_cpus));
+  CU(ctx->d_clamp_head.reserve(n_cpus));
+  CU(ctx->d_clamp_ret.reserve(n_cpus));
+  CU(ctx->d_locate_from.reserve(n_cpus));
+  CU(ctx->d_locate_skip.reserve(n_cpus));
+  CU(ctx->h_clamp_head.reserve(n_cpus));
+  CU(ctx->h_clamp_ret.reserve(n_cpus));
+  CU(ctx->d_flags.reserve(4));
+  CU(ctx->h_flags.reserve(4));
+  ctx->cur = 0;
+  return hbt_ring_reset_state(ctx, kInvalidTs);
+}
+
+int hbt_ring_configure(hbt_ctx* ctx, uint32_t n_cpus, uint64_t data_size) {
+  if (!ctx) return -EINVAL;
+  if (n_cpus == 0 || n_cpus > ctx->max_cpus) return fail(ctx, -EINVAL, "n_cpus %u", n_cpus);
+  if (data_size != 0 && (!is_pow2(data_size) || data_size < 4096))
+    return fail(ctx, -EINVAL, "data_size must be a power of two >= 4096");
+  CU(cudaSetDevice(ctx->device));
+  ctx->data_size = data_size;
+  if (data_size) {
+    CU(ctx->ring_store.reserve((size_t)n_cpus * data_size));
+  }
+  return configure_common(ctx, n_cpus);
+}
+
+int hbt_submit_ring(hbt_ctx* ctx, uint32_t cpu, const void* p1, size_t n1, const void* p2,
+                    size_t n2, uint64_t tail) {
+  if (!ctx || cpu >= ctx->n_cpus) return fail(ctx, -EINVAL, "cpu out of range");
+  if (int rc = complete_decode(ctx)) return rc;  // a possible re-run still reads the image
+  if (ctx->data_size == 0 || !ctx->ring_store.p)
+    return fail(ctx, -EINVAL, "hbt_ring_configure with a data_size first");
+  const uint64_t ds = ctx->data_size, mask = ds - 1;
+  if ((tail & 7) || (n1 & 7) || (n2 & 7)) return fail(ctx, -EINVAL, "unaligned slice");
+  if ((uint64_t)n1 + n2 > ds) return fail(ctx, -EINVAL, "slices larger than the ring");
+  uint8_t* img = ctx->ring_store.p + (size_t)cpu * ds;
+  const uint64_t off = tail & mask;
+  if (off + n1 > ds) return fail(ctx, -EINVAL, "first slice crosses the ring end");
+  if (n1) CU(cudaMemcpyAsync(img + off, p1, n1, cudaMemcpyHostToDevice, ctx->stream));
+  if (n2) {
+    // the second slice starts at data_start (RbDataSlices, CpuEventsGroup.h:1559-1561)
+    if (off + n1 != ds) return fail(ctx, -EINVAL, "second slice without a wrap");
+    if (n2 > off) return fail(ctx, -EINVAL, "second slice overlaps the first");
+    CU(cudaMemcpyAsync(img, p2, n2, cudaMemcpyHostToDevice, ctx->stream));
+  }
+  Window& w = ctx->win[cpu];
+  w.base = img;
+  w.data_size = ds;
+  w.tail = tail;
+  w.head = tail + n1 + n2;
+  w.active = true;
+  return 0;
+}
+
+int hbt_submit_ring_dev(hbt_ctx* ctx, uint32_t cpu, const void* ring_base, uint64_t data_size,
+                        uint64_t tail, uint64_t head) {
+  if (!ctx || cpu >= ctx->n_cpus) return fail(ctx, -EINVAL, "cpu out of range");
+  if (int rc = complete_decode(ctx)) return rc;
+  if (!ring_base || ((uintptr_t)ring_base & 15)) return fail(ctx, -EINVAL, "ring_base alignment");
+  if (!is_pow2(data_size) || data_size < 4096) return fail(ctx, -EINVAL, "bad data_size");
+  if ((tail & 7) || head < tail) return fail(ctx, -EINVAL, "bad window");
+  Window& w = ctx->win[cpu];
+  w.base = static_cast<const uint8_t*>(ring_base);
+  w.data_size = data_size;
+  w.tail = tail;
+  w.head = head;
+  w.active = true;
+  return 0;
+}
+
+// ---- decode ------------------------------------------------------------------
+
+int hbt_decode(hbt_ctx* ctx, const hbt_decode_desc* desc) {
+  if (!ctx || ctx->n_cpus == 0) return fail(ctx, -EINVAL, "no rings configured");
+  int rc = validate_desc(ctx, desc);
+  if (rc) return rc;
+  CU(cudaSetDevice(ctx->device));
+  rc = complete_decode(ctx);  // an unfetched decode still commits its state
+  if (rc) return rc;
+  ctx->desc = *desc;
+  if (ctx->desc.aggregate != HBT_AGG_COUNT_DELTAS) ctx->desc.n_events = 0;
+  rc = build_tables(ctx, nullptr, nullptr, nullptr);
+  if (rc) return rc;
+  rc = run_once(ctx, 1);
+  if (rc) return rc;
+  ctx->pending = true;
+  ctx->have_results = false;
+  ctx->reruns = 0;
+  return 0;
+}
+
+}  // extern "C"
+
+// Complete the pending decode: read the re-run flag; while set, take the failed
+// attempt back out of the histogram, apply forced entries / clamps and run again.
+static int complete_decode(hbt_ctx* ctx) {
+  if (!ctx->pending) return 0;
+  const uint32_t C = ctx->n_cpus;
+  std::vector<uint64_t> clamp_head(C, kNone);
+  std::vector<int64_t> clamp_ret(C, 0);
+  bool have_clamp = false;
+  for (int iter = 0;; ++iter) {
+    CU(cudaMemcpyAsync(ctx->h_flags.p, ctx->d_flags.p, 4 * sizeof(uint32_t),
+                       cudaMemcpyDeviceToHost, ctx->stream));
+    CU(cudaStreamSynchronize(ctx->stream));
+    if (ctx->h_flags.p[0] == 0) break;
+    if (iter > 4 * kMaxSegsPerCpu + 8) return fail(ctx, -EIO, "decode re-run did not converge");
+    ++ctx->reruns;
+    // take the failed attempt back out of the shared table
+    if (ctx->desc.aggregate == HBT_AGG_IP_HISTOGRAM) {
+      int rc = launch_decode(ctx, 0xFFFFFFFFu);
+      if (rc) return rc;
+    }
+    // locate cuts for a finite max_num_records, then fetch clamps + forced entries
+    k_locate<<<(C + 63) / 64, 64, 0, ctx->stream>>>(ctx->d_rings.p, C, ctx->d_clamp_head.p,
+                                                   ctx->d_locate_from.p, ctx->d_locate_skip.p);
+    ++ctx->launches;
+    CU(cudaGetLastError());
+    CU(cudaMemcpyAsync(ctx->h_clamp_head.p, ctx->d_clamp_head.p, C * sizeof(uint64_t),
+                       cudaMemcpyDeviceToHost, ctx->stream));
+    CU(cudaMemcpyAsync(ctx->h_clamp_ret.p, ctx->d_clamp_ret.p, C * sizeof(int64_t),
+                       cudaMemcpyDeviceToHost, ctx->stream));
+    std::vector<SegDesc> forced(ctx->h_segs.p, ctx->h_segs.p + ctx->n_segs);
+    std::vector<uint64_t> forced_new(ctx->n_segs, kNone);
+    if (ctx->n_segs)
+      CU(cudaMemcpyAsync(forced_new.data(), ctx->d_forced.p, ctx->n_segs * sizeof(uint64_t),
+                         cudaMemcpyDeviceToHost, ctx->stream));
+    CU(cudaStreamSynchronize(ctx->stream));
+    for (uint32_t i = 0; i < ctx->n_segs; ++i)
+      if (forced_new[i] != kNone) forced[i].forced_entry = forced_new[i];
+    for (uint32_t c = 0; c < C; ++c) {
+      if (ctx->h_clamp_head.p[c] != kNone) {
+        clamp_head[c] = ctx->h_clamp_head.p[c];
+        clamp_ret[c] = ctx->h_clamp_ret.p[c];
+        have_clamp = true;
+      }
+    }
+    int rc = build_tables(ctx, have_clamp ? clamp_head.data() : nullptr, clamp_ret.data(), &forced);
+    if (rc) return rc;
+    rc = run_once(ctx, 1);
+    if (rc) return rc;
+  }
+  // success: commit the generator state, fetch results
+  ctx->cur ^= 1;
+  CU(cudaMemcpyAsync(ctx->h_out.p, ctx->d_out.p, C * sizeof(hbt_cpu_result),
+                     cudaMemcpyDeviceToHost, ctx->stream));
+  if (ctx->n_segs) {
+    CU(cudaMemcpyAsync(ctx->h_results.p, ctx->d_results.p, ctx->n_segs * sizeof(SegResult),
+                       cudaMemcpyDeviceToHost, ctx->stream));
+    CU(cudaMemcpyAsync(ctx->h_seam.p, ctx->d_seam.p, ctx->n_segs, cudaMemcpyDeviceToHost,
+                       ctx->stream));
+  }
+  CU(cudaStreamSynchronize(ctx->stream));
+  // consumed windows: tail advances like writeDataTail (CpuEventsGroup.h:1520)
+  for (uint32_t c = 0; c < C; ++c) {
+    Window& w = ctx->win[c];
+    if (w.active) w.tail = ctx->h_out.p[c].new_tail;
+  }
+  ctx->pending = false;
+  ctx->have_results = true;
+  return 0;
+}
+
+extern "C" {
+
+int hbt_fetch_results(hbt_ctx* ctx, hbt_cpu_result* out, uint32_t cap) {
+  if (!ctx || !out) return -EINVAL;
+  int rc = complete_decode(ctx);
+  if (rc) return rc;
+  if (!ctx->have_results) return fail(ctx, -EINVAL, "no decode to fetch");
+  if (cap < ctx->n_cpus) return fail(ctx, -ENOSPC, "cap %u < n_cpus %u", cap, ctx->n_cpus);
+  memcpy(out, ctx->h_out.p, ctx->n_cpus * sizeof(hbt_cpu_result));
+  if (ctx->desc.aggregate == HBT_AGG_IP_HISTOGRAM) {
+    uint32_t ov = 0;
+    CU(cudaMemcpy(&ov, ctx->hist_overflow.p, sizeof(ov), cudaMemcpyDeviceToHost));
+    if (ov == 1) return fail(ctx, -ENOSPC, "histogram table full: hbt_hist_configure a larger one");
+    if (ov == 2) return fail(ctx, -EOVERFLOW, "a histogram count exceeded 2^32-1");
+  }
+  return (int)ctx->n_cpus;
+}
+
+uint32_t hbt_decode_reruns(const hbt_ctx* ctx) { return ctx ? ctx->reruns : 0; }
+
+uint64_t hbt_decode_slow_tiles(hbt_ctx* ctx) {
+  if (!ctx || !ctx->have_results) return 0;
+  uint64_t n = 0;
+  for (uint32_t i = 0; i < ctx->n_segs; ++i) n += ctx->h_results.p[i].slow_tiles;
+  return n;
+}
+
+uint32_t hbt_rows_max_slabs(const hbt_ctx* ctx) { (void)ctx; return 2 * kMaxSegsPerCpu; }
+
+int hbt_rows_slabs_dev(hbt_ctx* ctx, uint32_t cpu, const uint64_t** ptr, uint64_t* n_rows,
+                       uint32_t* n_slabs) {
+  if (!ctx || cpu >= ctx->n_cpus || !ptr || !n_rows || !n_slabs) return -EINVAL;
+  int rc = complete_decode(ctx);
+  if (rc) return rc;
+  if (!ctx->have_results || ctx->desc.aggregate != HBT_AGG_COUNT_DELTAS)
+    return fail(ctx, -EINVAL, "no COUNT_DELTAS decode to read");
+  const RingDesc& r = ctx->h_rings.p[cpu];
+  const uint64_t row_words = 2 + (uint64_t)ctx->desc.n_events;
+  uint32_t k = 0;
+  uint64_t remaining = ctx->h_out.p[cpu].n_rows;
+  for (uint32_t s = 0; s < r.n_seg && remaining; ++s) {
+    const uint32_t gi = r.seg_begin + s;
+    const SegDesc& sd = ctx->h_segs.p[gi];
+    if (ctx->h_seam.p[gi]) {
+      ptr[k] = sd.rows;
+      n_rows[k] = 1;
+      ++k;
+      --remaining;
+    }
+    uint64_t n = ctx->h_results.p[gi].n_rows;
+    if (n > remaining) n = remaining;
+    if (n) {
+      ptr[k] = sd.rows + row_words;
+      n_rows[k] = n;
+      ++k;
+      remaining -= n;
+    }
+  }
+  *n_slabs = k;
+  return 0;
+}
+
+int64_t hbt_fetch_rows(hbt_ctx* ctx, uint32_t cpu, uint64_t* rows, uint64_t cap_rows) {
+  if (!ctx || cpu >= ctx->n_cpus) return -EINVAL;
+  const uint64_t* ptr[2 * kMaxSegsPerCpu];
+  uint64_t n[2 * kMaxSegsPerCpu];
+  uint32_t k = 0;
+  int rc = hbt_rows_slabs_dev(ctx, cpu, ptr, n, &k);
+  if (rc) return rc;
+  const uint64_t total = ctx->h_out.p[cpu].n_rows;
+  if (total > cap_rows) return fail(ctx, -ENOSPC, "cap_rows %llu < %llu",
+                                    (unsigned long long)cap_rows, (unsigned long long)total);
+  const uint64_t row_words = 2 + (uint64_t)ctx->desc.n_events;
+  uint64_t off = 0;
+  for (uint32_t i = 0; i < k; ++i) {
+    CU(cudaMemcpyAsync(rows + off * row_words, ptr[i], n[i] * row_words * 8,
+                       cudaMemcpyDeviceToHost, ctx->stream));
+    off += n[i];
+  }
+  CU(cudaStreamSynchronize(ctx->stream));
+  return (int64_t)off;
+}
+
+int hbt_fetch_carry(hbt_ctx* ctx, uint32_t cpu, uint64_t* last, uint32_t n_events) {
+  if (!ctx || cpu >= ctx->n_cpus || !last || n_events > HBT_MAX_EVENTS) return -EINVAL;
+  int rc = complete_decode(ctx);
+  if (rc) return rc;
+  CU(cudaMemcpyAsync(last, ctx->state[ctx->cur].p[cpu].carry_last, n_events * 8,
+                     cudaMemcpyDeviceToHost, ctx->stream));
+  CU(cudaStreamSynchronize(ctx->stream));
+  return 0;
+}
+
+// ---- histogram -----------------------------------------------------------------
+
+int hbt_hist_clear(hbt_ctx* ctx) {
+  if (!ctx || ctx->hist_slots_per_cpu == 0) return fail(ctx, -EINVAL, "no histogram configured");
+  CU(cudaMemsetAsync(ctx->hist_slots.p, 0, ctx->hist_slots.n * sizeof(ulonglong2), ctx->stream));
+  CU(cudaMemsetAsync(ctx->hist_zero.p, 0, ctx->hist_zero.n * sizeof(uint64_t), ctx->stream));
+  CU(cudaMemsetAsync(ctx->hist_overflow.p, 0, sizeof(uint32_t), ctx->stream));
+  return 0;
+}
+
+int hbt_hist_configure(hbt_ctx* ctx, uint64_t capacity_slots) {
+  if (!ctx || ctx->n_cpus == 0) return fail(ctx, -EINVAL, "configure rings first");
+  if (!is_pow2(capacity_slots)) return fail(ctx, -EINVAL, "capacity must be a power of two");
+  uint64_t per = capacity_slots / ctx->n_cpus;
+  // largest power of two <= capacity / n_cpus
+  uint64_t p2 = 1;
+  while (p2 * 2 <= per) p2 *= 2;
+  if (per == 0 || p2 < 64) return fail(ctx, -EINVAL, "capacity too small for %u CPUs", ctx->n_cpus);
+  CU(cudaSetDevice(ctx->device));
+  CU(ctx->hist_slots.reserve((size_t)p2 * ctx->n_cpus));
+  CU(ctx->hist_zero.reserve(ctx->n_cpus));
+  CU(ctx->hist_overflow.reserve(1));
+  CU(ctx->hist_n.reserve(1));
+  ctx->hist_slots_per_cpu = p2;
+  return hbt_hist_clear(ctx);
+}
+
+static int64_t hist_collect(hbt_ctx* ctx, hbt_hist_entry* out, uint64_t cap) {
+  if (!ctx || ctx->hist_slots_per_cpu == 0) return fail(ctx, -EINVAL, "no histogram configured");
+  int rc = complete_decode(ctx);
+  if (rc) return rc;
+  if (out) CU(ctx->hist_out.reserve(cap ? cap : 1));
+  CU(cudaMemsetAsync(ctx->hist_n.p, 0, sizeof(unsigned long long), ctx->stream));
+  HistTable t{ctx->hist_slots.p, ctx->hist_slots_per_cpu, ctx->hist_zero.p, ctx->hist_overflow.p};
+  k_hist_compact<<<ctx->sm_count * 8, 256, 0, ctx->stream>>>(t, ctx->n_cpus, ctx->cpu_base,
+                                                            out ? ctx->hist_out.p : nullptr,
+                                                            ctx->hist_n.p, cap);
+  ++ctx->launches;
+  CU(cudaGetLastError());
+  unsigned long long n = 0;
+  CU(cudaMemcpyAsync(&n, ctx->hist_n.p, sizeof(n), cudaMemcpyDeviceToHost, ctx->stream));
+  CU(cudaStreamSynchronize(ctx->stream));
+  if (out) {
+    if (n > cap) return fail(ctx, -ENOSPC, "cap %llu < %llu entries", (unsigned long long)cap, n);
+    CU(cudaMemcpy(out, ctx->hist_out.p, n * sizeof(hbt_hist_entry), cudaMemcpyDeviceToHost));
+  }
+  return (int64_t)n;
+}
+
+int64_t hbt_hist_size(hbt_ctx* ctx) { return hist_collect(ctx, nullptr, 0); }
+
+int64_t hbt_hist_fetch(hbt_ctx* ctx, hbt_hist_entry* out, uint64_t cap) {
+  if (!out) return -EINVAL;
+  return hist_collect(ctx, out, cap);
+}
+
+int hbt_hist_table_dev(hbt_ctx* ctx, const void** slots, uint64_t* slots_per_cpu) {
+  if (!ctx || !slots || !slots_per_cpu || ctx->hist_slots_per_cpu == 0) return -EINVAL;
+  *slots = ctx->hist_slots.p;
+  *slots_per_cpu = ctx->hist_slots_per_cpu;
+  return 0;
+}
+
+// ---- counter groups -----------------------------------------------------------------
+
+static int counts_check(hbt_ctx* ctx, uint64_t n_intervals, uint32_t n_cpus, uint32_t n_events,
+                        uint32_t n_ratios, const hbt_ratio* ratios) {
+  if (!ctx) return -EINVAL;
+  if (n_cpus == 0 || n_cpus > HBT_MAX_CPUS) return fail(ctx, -EINVAL, "n_cpus %u", n_cpus);
+  if (n_events == 0 || n_events > ctx->max_events) return fail(ctx, -EINVAL, "n_events %u", n_events);
+  if (n_ratios > kMaxRatios) return fail(ctx, -EINVAL, "n_ratios %u > %d", n_ratios, kMaxRatios);
+  for (uint32_t r = 0; r < n_ratios; ++r)
+    if (!ratios || ratios[r].num_event >= n_events || ratios[r].den_event >= n_events)
+      return fail(ctx, -EINVAL, "ratio %u names an event out of range", r);
+  (void)n_intervals;
+  return 0;
+}
+
+static int upload_ratios(hbt_ctx* ctx, const hbt_ratio* ratios, uint32_t n_ratios) {
+  CU(ctx->d_ratios.reserve(kMaxRatios));
+  if (n_ratios)
+    CU(cudaMemcpyAsync(ctx->d_ratios.p, ratios, n_ratios * sizeof(hbt_ratio),
+                       cudaMemcpyHostToDevice, ctx->stream));
+  return 0;
+}
+
+static int counts_grid(const hbt_ctx* ctx, uint64_t n_intervals) {
+  uint64_t g = (uint64_t)ctx->sm_count * 8;
+  if (g > n_intervals) g = n_intervals;
+  return (int)(g ? g : 1);
+}
+
+static int counts_launch(hbt_ctx* ctx, const uint64_t* reads, uint64_t n_intervals,
+                         uint32_t n_cpus, uint32_t n_events, uint32_t n_ratios, uint64_t* sums,
+                         uint64_t* scaled, float* rates, double* ratio_out, uint64_t* deltas,
+                         int do_scale) {
+  if (n_intervals == 0) return 0;
+  CountsArgs a{};
+  a.reads = reads;
+  a.n_intervals = n_intervals;
+  a.n_cpus = n_cpus;
+  a.n_events = n_events;
+  a.ratios = ctx->d_ratios.p;
+  a.n_ratios = n_ratios;
+  a.sums = sums;
+  a.rates = rates;
+  a.ratio_out = ratio_out;
+  a.do_scale = do_scale;
+  a.scaled = scaled;
+  if (do_scale && deltas && !scaled) {
+    CU(ctx->c_scaled.reserve(n_intervals * n_events));
+    a.scaled = ctx->c_scaled.p;
+  }
+  k_counts_reduce<256><<<counts_grid(ctx, n_intervals), 256, 0, ctx->stream>>>(a);
+  ++ctx->launches;
+  CU(cudaGetLastError());
+  if (do_scale && deltas) {
+    const uint64_t total = n_intervals * n_events;
+    int g = (int)((total + 255) / 256);
+    if (g > ctx->sm_count * 16) g = ctx->sm_count * 16;
+    k_scaled_diff<<<g, 256, 0, ctx->stream>>>(a.scaled, nullptr, n_intervals, n_events, deltas);
+    ++ctx->launches;
+    CU(cudaGetLastError());
+  }
+  return 0;
+}
+
+int hbt_counts_reduce_dev(hbt_ctx* ctx, const uint64_t* reads, uint64_t n_intervals,
+                          uint32_t n_cpus, uint32_t n_events, uint64_t* sums) {
+  int rc = counts_check(ctx, n_intervals, n_cpus, n_events, 0, nullptr);
+  if (rc) return rc;
+  if (!reads || !sums) return fail(ctx, -EINVAL, "NULL buffer");
+  CU(cudaSetDevice(ctx->device));
+  return counts_launch(ctx, reads, n_intervals, n_cpus, n_events, 0, sums, nullptr, nullptr,
+                       nullptr, nullptr, 0);
+}
+
+int hbt_counts_scale_dev(hbt_ctx* ctx, const uint64_t* sums, uint64_t n_intervals,
+                         uint32_t n_events, const hbt_ratio* ratios, uint32_t n_ratios,
+                         const uint64_t* prev_scaled, uint64_t* scaled, float* rates,
+                         double* ratio_out, uint64_t* deltas) {
+  int rc = counts_check(ctx, n_intervals, 1, n_events, n_ratios, ratios);
+  if (rc) return rc;
+  if (!sums) return fail(ctx, -EINVAL, "NULL buffer");
+  if (n_intervals == 0) return 0;
+  CU(cudaSetDevice(ctx->device));
+  rc = upload_ratios(ctx, ratios, n_ratios);
+  if (rc) return rc;
+  ScaleArgs a{};
+  a.sums = sums;
+  a.n_intervals = n_intervals;
+  a.n_events = n_events;
+  a.ratios = ctx->d_ratios.p;
+  a.n_ratios = ratio_out ? n_ratios : 0;
+  a.scaled = scaled;
+  if (deltas && !scaled) {
+    CU(ctx->c_scaled.reserve(n_intervals * n_events));
+    a.scaled = ctx->c_scaled.p;
+  }
+  a.rates = rates;
+  a.ratio_out = ratio_out;
+  const uint64_t total = n_intervals * (n_events + a.n_ratios);
+  int g = (int)((total + 255) / 256);
+  if (g > ctx->sm_count * 16) g = ctx->sm_count * 16;
+  k_counts_scale<<<g, 256, 0, ctx->stream>>>(a);
+  ++ctx->launches;
+  CU(cudaGetLastError());
+  if (deltas) {
+    k_scaled_diff<<<g, 256, 0, ctx->stream>>>(a.scaled, prev_scaled, n_intervals, n_events, deltas);
+    ++ctx->launches;
+    CU(cudaGetLastError());
+  }
+  return 0;
+}
+
+int hbt_counts_pipeline_dev(hbt_ctx* ctx, const uint64_t* reads, uint64_t n_intervals,
+                            uint32_t n_cpus, uint32_t n_events, const hbt_ratio* ratios,
+                            uint32_t n_ratios, uint64_t* sums, uint64_t* scaled, float* rates,
+                            double* ratio_out, uint64_t* deltas) {
+  int rc = counts_check(ctx, n_intervals, n_cpus, n_events, n_ratios, ratios);
+  if (rc) return rc;
+  if (!reads) return fail(ctx, -EINVAL, "NULL buffer");
+  CU(cudaSetDevice(ctx->device));
+  rc = upload_ratios(ctx, ratios, n_ratios);
+  if (rc) return rc;
+  return counts_launch(ctx, reads, n_intervals, n_cpus, n_events, ratio_out ? n_ratios : 0, sums,
+                       scaled, rates, ratio_out, deltas, 1);
+}
+
+int hbt_counts_pipeline_host(hbt_ctx* ctx, const uint64_t* reads, uint64_t n_intervals,
+                             uint32_t n_cpus, uint32_t n_events, const hbt_ratio* ratios,
+                             uint32_t n_ratios, uint64_t* sums, uint64_t* scaled, float* rates,
+                             double* ratio_out, uint64_t* deltas) {
+  int rc = counts_check(ctx, n_intervals, n_cpus, n_events, n_ratios, ratios);
+  if (rc) return rc;
+  if (!reads) return fail(ctx, -EINVAL, "NULL buffer");
+  if (n_intervals == 0) return 0;
+  CU(cudaSetDevice(ctx->device));
+  const uint64_t W = 3 + (uint64_t)n_events;
+  const uint64_t n_in = n_intervals * n_cpus * W;
+  CU(ctx->c_reads.reserve(n_in));
+  CU(ctx->c_sums.reserve(n_intervals * W));
+  CU(ctx->c_scaled.reserve(n_intervals * n_events));
+  CU(ctx->c_deltas.reserve(n_intervals * n_events));
+  CU(ctx->c_rates.reserve(n_intervals * n_events));
+  CU(ctx->c_ratio.reserve(n_intervals * (n_ratios ? n_ratios : 1)));
+  CU(cudaMemcpyAsync(ctx->c_reads.p, reads, n_in * 8, cudaMemcpyHostToDevice, ctx->stream));
+  rc = upload_ratios(ctx, ratios, n_ratios);
+  if (rc) return rc;
+  rc = counts_launch(ctx, ctx->c_reads.p, n_intervals, n_cpus, n_events,
+                     ratio_out ? n_ratios : 0, sums ? ctx->c_sums.p : nullptr, ctx->c_scaled.p,
+                     rates ? ctx->c_rates.p : nullptr, ratio_out ? ctx->c_ratio.p : nullptr,
+                     deltas ? ctx->c_deltas.p : nullptr, 1);
+  if (rc) return rc;
+  if (sums)
+    CU(cudaMemcpyAsync(sums, ctx->c_sums.p, n_intervals * W * 8, cudaMemcpyDeviceToHost, ctx->stream));
+  if (scaled)
+    CU(cudaMemcpyAsync(scaled, ctx->c_scaled.p, n_intervals * n_events * 8, cudaMemcpyDeviceToHost,
+                       ctx->stream));
+  if (rates)
+    CU(cudaMemcpyAsync(rates, ctx->c_rates.p, n_intervals * n_events * 4, cudaMemcpyDeviceToHost,
+                       ctx->stream));
+  if (ratio_out && n_ratios)
+    CU(cudaMemcpyAsync(ratio_out, ctx->c_ratio.p, n_intervals * n_ratios * 8,
+                       cudaMemcpyDeviceToHost, ctx->stream));
+  if (deltas)
+    CU(cudaMemcpyAsync(deltas, ctx->c_deltas.p, n_intervals * n_events * 8, cudaMemcpyDeviceToHost,
+                       ctx->stream));
+  CU(cudaStreamSynchronize(ctx->stream));
+  return 0;
+}
+
+}  // extern "C"

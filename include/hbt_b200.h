@@ -1,0 +1,322 @@
+/*
+ * hbt_b200.h -- C-ABI of the B200-native perf_event decode/aggregate path.
+ *
+ * This is the drop-in boundary underneath dynolog/hbt's host C++ classes
+ * (hbt::perf_event::CpuEventsGroup / PerCpuCountReader / GroupReadValues,
+ * hbt::mon::Monitor, dynolog::PerfMonitor).  The reference has no FFI of its
+ * own; every entry point below names the reference function (file:line under
+ * the reference tree) whose work it replaces.  Host code in any language binds
+ * these with plain pointers and sizes; no C++ or torch type crosses the ABI.
+ *
+ * Conventions
+ *  - every call returns 0 / a non-negative count on success or a NEGATIVE errno
+ *    (the convention of CpuEventsGroup::consume and its handlers,
+ *    hbt/src/perf_event/CpuEventsGroup.h:1318-1326); no exception crosses.
+ *  - one hbt_ctx per (calling thread, device); a ctx is not thread-safe, the
+ *    same single-consumer rule the reference has for a CPU buffer.
+ *  - the caller owns host buffers; the library owns device buffers unless an
+ *    entry point is suffixed _dev, in which case the pointers are DEVICE
+ *    pointers owned by the caller (e.g. torch tensors) and the call is
+ *    asynchronous on the ctx stream.
+ *  - there is no CPU fallback: without a usable CUDA device hbt_create fails
+ *    with -ENODEV and nothing else can be called.
+ *  - all integers little-endian, layouts identical to the Linux uapi
+ *    (perf_event_header, read_format) and to GroupReadValues<TMode>::T
+ *    (CpuEventsGroup.h:371-379): device layout == host layout == kernel layout.
+ */
+#ifndef HBT_B200_H_
+#define HBT_B200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define HBT_B200_ABI_VERSION 1
+
+/* Limits taken from the reference: kMaxCpus (hbt/src/common/System.h:195),
+ * CpuCountSampleGenerator::kMaxNumEvents (PerCpuCountSampleGenerator.h:44). */
+#define HBT_MAX_CPUS 512
+#define HBT_MAX_EVENTS 64
+
+typedef struct hbt_ctx hbt_ctx;
+
+/* ------------------------------------------------------------------------ */
+/* Record model                                                             */
+/* ------------------------------------------------------------------------ */
+
+/* Index of the per-type record counters, in the order of the members
+ * num_record_*_ of CpuEventsGroup (CpuEventsGroup.h:822-832). */
+enum {
+  HBT_CNT_LOST = 0,       /* += num_lost, not ++ (CpuEventsGroup.h:1381) */
+  HBT_CNT_COMM = 1,
+  HBT_CNT_EXIT = 2,
+  HBT_CNT_THROTTLE = 3,
+  HBT_CNT_UNTHROTTLE = 4,
+  HBT_CNT_FORK = 5,
+  HBT_CNT_SAMPLE = 6,
+  HBT_CNT_READ = 7,
+  HBT_CNT_AUX = 8,
+  HBT_CNT_ITRACE_START = 9,
+  HBT_CNT_SWITCH_CPU_WIDE = 10,
+  HBT_NUM_COUNTERS = 11
+};
+
+/* Which record types have a (non-void) handler in the decode mode, i.e. which
+ * `if constexpr (!std::is_void<TRecordX>)` bodies of consume() exist
+ * (CpuEventsGroup.h:1372-1501).  A record of a type without handler is skipped
+ * by header.size and only counted in the total. */
+enum {
+  HBT_H_LOST = 1u << 0,
+  HBT_H_COMM = 1u << 1,
+  HBT_H_EXIT = 1u << 2,
+  HBT_H_FORK = 1u << 3,
+  HBT_H_SAMPLE = 1u << 4,
+  HBT_H_READ = 1u << 5,
+  HBT_H_AUX = 1u << 6,
+  HBT_H_ITRACE_START = 1u << 7,
+  HBT_H_SWITCH_CPU_WIDE = 1u << 8
+};
+
+/* Handler sets of the reference's modes (CpuEventsGroup.h:66-291). */
+#define HBT_MODE_SAMPLING (HBT_H_LOST | HBT_H_READ | HBT_H_SAMPLE)
+#define HBT_MODE_CONTEXT_SWITCH \
+  (HBT_H_LOST | HBT_H_COMM | HBT_H_EXIT | HBT_H_FORK | HBT_H_SWITCH_CPU_WIDE)
+#define HBT_MODE_AUX_SPACE (HBT_H_AUX | HBT_H_ITRACE_START)
+/* Mixed stream of BASELINE config 4: context-switch records plus SAMPLE. */
+#define HBT_MODE_MIXED (HBT_MODE_CONTEXT_SWITCH | HBT_H_SAMPLE | HBT_H_READ)
+
+/* Layout of PERF_RECORD_SAMPLE bodies. */
+enum {
+  /* mode::Sampling::Sample (CpuEventsGroup.h:268-281):
+   * hdr tstamp nr time_enabled time_running value[nr]; size must equal
+   * 40 + 8*nr (CpuEventsGroup.h:1435-1440) else -EPERM. */
+  HBT_SAMPLE_GROUP = 0,
+  /* sample_type = IP|TID|TIME|CPU in kernel order
+   * (/usr/include/linux/perf_event.h:958-967):
+   * hdr ip pid tid time cpu res [extra]; size must equal ip_sample_bytes.
+   * No counterpart in the reference (it never sets PERF_SAMPLE_IP). */
+  HBT_SAMPLE_IP = 1
+};
+
+/* What the SAMPLE handler does. */
+enum {
+  HBT_AGG_NONE = 0,        /* count only (handlers of CpuEventsGroupTest.cpp:58-88) */
+  /* CpuCountSampleGenerator::handleRecordSample / handleRecordLost
+   * (PerCpuCountSampleGenerator.h:110-202): rows {tstamp,duration,deltas[n]}. */
+  HBT_AGG_COUNT_DELTAS = 1,
+  /* (cpu,pid,ip) -> count table; needs HBT_SAMPLE_IP. */
+  HBT_AGG_IP_HISTOGRAM = 2
+};
+
+/* TSC -> kernel time parameters, TscConversionParams (System.h:175-179) and
+ * CpuEventsGroup::kernelTimeFromTsc (CpuEventsGroup.h:1577-1591). */
+typedef struct hbt_tsc_params {
+  uint64_t time_zero;
+  uint32_t time_mult;
+  uint16_t time_shift;
+  uint16_t pad_;
+} hbt_tsc_params;
+
+typedef struct hbt_decode_desc {
+  uint32_t handled_mask;    /* HBT_H_* bits */
+  uint32_t sample_layout;   /* HBT_SAMPLE_* */
+  uint32_t aggregate;       /* HBT_AGG_* */
+  uint32_t n_events;        /* HBT_AGG_COUNT_DELTAS: kNumEvents, 1..64 */
+  uint32_t ip_sample_bytes; /* HBT_SAMPLE_IP: required header.size (>= 40, %8 == 0) */
+  uint32_t max_records;     /* consume(max_num_records); 0xFFFFFFFF = drain */
+  /* bit i set: event i has EventValueTransforms::TscToKernelTime
+   * (PmuEvent.h:218-226, PerCpuCountSampleGenerator.h:171-173) */
+  uint64_t tsc_transform_mask;
+  hbt_tsc_params tsc;
+} hbt_decode_desc;
+
+/* Result of one decode call for one CPU: what consume() returned plus the
+ * object state it mutated.  counters[] and num_unknown_count_interval are the
+ * running totals since hbt_ring_reset_state, like the reference's members. */
+typedef struct hbt_cpu_result {
+  int64_t ret;       /* consume()'s return: #records, or -ENODATA (drained),
+                        -EPERM (bad SAMPLE/READ size, tstamp regression), -EBADMSG
+                        (header.size < 8: the reference would never return) */
+  uint64_t n_records;/* records consumed by this call (also when ret < 0) */
+  uint64_t new_tail; /* value consume() wrote to data_tail (CpuEventsGroup.h:1520) */
+  uint64_t n_rows;   /* HBT_AGG_COUNT_DELTAS: rows emitted by this call */
+  uint64_t counters[HBT_NUM_COUNTERS];
+  uint64_t num_unknown_count_interval; /* PerCpuCountSampleGenerator.h:152,230 */
+  uint64_t carry_tstamp; /* count_.tstamp after the call (UINT64_MAX = invalid) */
+} hbt_cpu_result;
+
+/* One entry of the (cpu,pid,ip) table. */
+typedef struct hbt_hist_entry {
+  uint64_t ip;
+  uint32_t pid;
+  uint32_t cpu;
+  uint64_t count;
+} hbt_hist_entry;
+
+/* ------------------------------------------------------------------------ */
+/* Lifecycle                                                                */
+/* ------------------------------------------------------------------------ */
+
+/* ABI version of the loaded library. */
+int hbt_abi_version(void);
+
+/* Create a context on CUDA device `device`.  -ENODEV when there is no usable
+ * sm_100 device, -EINVAL for max_cpus > HBT_MAX_CPUS or max_events > HBT_MAX_EVENTS.
+ * Replaces nothing in the reference; it is the GPU analogue of constructing
+ * the per-CPU generators (PerCpuBase.h:26-33). */
+int hbt_create(hbt_ctx** out, int device, uint32_t max_cpus, uint32_t max_events);
+void hbt_destroy(hbt_ctx* ctx);
+
+/* Human-readable description of the last failure on this ctx (never NULL). */
+const char* hbt_last_error(const hbt_ctx* ctx);
+
+/* Run every later call of this ctx on `cuda_stream` (a cudaStream_t); NULL
+ * restores the ctx's own stream. */
+int hbt_set_stream(hbt_ctx* ctx, void* cuda_stream);
+
+/* Block until all work queued by this ctx is complete. */
+int hbt_sync(hbt_ctx* ctx);
+
+/* Number of kernels this ctx launched since creation (bench.py's gpu_launches). */
+uint64_t hbt_launch_count(const hbt_ctx* ctx);
+
+/* CPU ids reported in hbt_hist_entry are cpu_base + the ctx-local index: a rank
+ * that holds the shard [cpu_base, cpu_base + n_cpus) of a larger machine sets it
+ * (sharding by CPU id, PerCpuBase.h:26 keeps one generator per CPU). */
+int hbt_set_cpu_base(hbt_ctx* ctx, uint32_t cpu_base);
+
+/* ------------------------------------------------------------------------ */
+/* Ring ingest: CpuEventsGroup::onCpuDataBufferRead (CpuEventsGroup.h:1524-1570)
+ * hands out the unread bytes of a CPU's ring as RbDataSlices (:44-63).       */
+/* ------------------------------------------------------------------------ */
+
+/* Library-owned device image of n_cpus rings of data_size bytes (power of two,
+ * >= 4096: CpuEventsGroup.h:1065-1068,1077-1078).  Re-configuring frees the
+ * previous images and resets all per-CPU state. */
+int hbt_ring_configure(hbt_ctx* ctx, uint32_t n_cpus, uint64_t data_size);
+
+/* Copy the two slices of one OnRbReadCallback invocation into the device image
+ * of `cpu` at ring position `tail & (data_size-1)` and set the unread window to
+ * [tail, tail+n1+n2).  p2/n2 may be NULL/0.  n2 is clamped as the reference's
+ * wrapped second slice must be (it reports data_size-n1, CpuEventsGroup.h:1561):
+ * pass the true count head-tail-n1.  Host pointers; async H2D on the ctx stream
+ * (pageable memory makes it synchronous). */
+int hbt_submit_ring(hbt_ctx* ctx, uint32_t cpu, const void* p1, size_t n1,
+                    const void* p2, size_t n2, uint64_t tail);
+
+/* Use caller-owned DEVICE memory as the ring image of `cpu` (zero copy):
+ * ring_base points at data_start (mmap_base + data_offset), data_size must be a
+ * power of two, [tail, head) is the unread window (perf_event_mmap_page
+ * data_tail / data_head, /usr/include/linux/perf_event.h:724-727).
+ * ring_base must be 16-byte aligned. */
+int hbt_submit_ring_dev(hbt_ctx* ctx, uint32_t cpu, const void* ring_base,
+                        uint64_t data_size, uint64_t tail, uint64_t head);
+
+/* Forget counters, carry (count_.tstamp, last_[]) and windows of all CPUs:
+ * the state after enable() (CpuEventsGroup.h:1240-1280, enableImpl
+ * PerCpuCountSampleGenerator.h:91-106).  seed_tstamp is the value enableImpl
+ * takes from now(); UINT64_MAX seeds an invalid (re-seeding) interval. */
+int hbt_ring_reset_state(hbt_ctx* ctx, uint64_t seed_tstamp);
+
+/* ------------------------------------------------------------------------ */
+/* Decode: CpuEventsGroup::consume (CpuEventsGroup.h:1326-1522) for every CPU
+ * with a submitted window, plus the SAMPLE/LOST handlers selected by
+ * desc->aggregate.                                                          */
+/* ------------------------------------------------------------------------ */
+
+/* Asynchronous on the ctx stream.  Returns 0 or -errno for invalid arguments /
+ * CUDA failures; per-CPU outcomes are in hbt_fetch_results. */
+int hbt_decode(hbt_ctx* ctx, const hbt_decode_desc* desc);
+
+/* Synchronise and copy out one hbt_cpu_result per configured CPU (CPUs without
+ * a window report ret = 0, n_records = 0).  Returns the number of CPUs. */
+int hbt_fetch_results(hbt_ctx* ctx, hbt_cpu_result* out, uint32_t cap);
+
+/* Diagnostics of the last fetched decode: how many times the batch had to be
+ * re-run with corrected segment entries / clamped windows, and how many tiles
+ * fell back to the one-thread sequential walk.  Both are 0 on well-formed streams. */
+uint32_t hbt_decode_reruns(const hbt_ctx* ctx);
+uint64_t hbt_decode_slow_tiles(hbt_ctx* ctx);
+
+/* Rows {tstamp, duration, deltas[n_events]} of the last decode for `cpu`, in
+ * stream order: the bytes CpuCountSampleGenerator writes to its output ring
+ * (PerCpuCountSampleGenerator.h:69,182).  Returns the number of rows copied,
+ * -ENOSPC if cap_rows is too small. */
+int64_t hbt_fetch_rows(hbt_ctx* ctx, uint32_t cpu, uint64_t* rows, uint64_t cap_rows);
+
+/* Device view of the same rows for downstream kernels: rows of `cpu` live in
+ * *n_slabs slabs; slab i has n_rows[i] rows at ptr[i].  Arrays must hold
+ * hbt_rows_max_slabs() entries. */
+int hbt_rows_slabs_dev(hbt_ctx* ctx, uint32_t cpu, const uint64_t** ptr,
+                       uint64_t* n_rows, uint32_t* n_slabs);
+uint32_t hbt_rows_max_slabs(const hbt_ctx* ctx);
+
+/* last_[] of `cpu` after the last decode (PerCpuCountSampleGenerator.h:228). */
+int hbt_fetch_carry(hbt_ctx* ctx, uint32_t cpu, uint64_t* last, uint32_t n_events);
+
+/* (cpu,pid,ip) table.  capacity_slots (a power of two) is split evenly between
+ * the configured CPUs; a decode that overflows a CPU's share makes
+ * hbt_fetch_results return -ENOSPC.  Counts are 32-bit in the table
+ * (-EOVERFLOW if one wraps) and accumulate until hbt_hist_clear. */
+int hbt_hist_configure(hbt_ctx* ctx, uint64_t capacity_slots);
+int hbt_hist_clear(hbt_ctx* ctx);
+/* Number of distinct keys, then the entries (unordered). */
+int64_t hbt_hist_size(hbt_ctx* ctx);
+int64_t hbt_hist_fetch(hbt_ctx* ctx, hbt_hist_entry* out, uint64_t cap);
+/* Device view: n_cpus consecutive sub-tables of *slots_per_cpu 16-byte slots
+ * {u64 ip; u32 pid; u32 count}; an all-zero slot is empty; the key (ip=0,pid=0)
+ * is kept outside the table and only appears in hbt_hist_fetch. */
+int hbt_hist_table_dev(hbt_ctx* ctx, const void** slots, uint64_t* slots_per_cpu);
+
+/* ------------------------------------------------------------------------ */
+/* Counter groups: PerCpuBase<T>::read (PerCpuBase.h:104-119) over a recorded
+ * trace of GroupReadValues<TMode>::T, then GroupReadValues::getCount
+ * (CpuEventsGroup.h:449-459) and PerfMonitor::log (PerfMonitor.cpp:52-67).  */
+/* ------------------------------------------------------------------------ */
+
+/* A derived ratio: double(getCount(num)) / double(getCount(den)), the
+ * convention of PerfMonitor.cpp:56-57 applied to the event pairs that
+ * BuiltinMetrics.cpp only describes (ipc :847-868, l3 misses/instr :508-532). */
+typedef struct hbt_ratio {
+  uint32_t num_event;
+  uint32_t den_event;
+} hbt_ratio;
+
+/* K4.  reads: [n_intervals][n_cpus][3+n_events] u64, one T per (interval,cpu).
+ * sums:  [n_intervals][3+n_events] u64 = zero() then accum() over the CPUs
+ * (CpuEventsGroup.h:508-522): word0 = n_events, time_enabled, time_running,
+ * count[].  A T whose word0 != n_events is a failed read: the interval's word0
+ * becomes 0 (PerCpuBase::read returns false, PerCpuCountReader::read nullopt). */
+int hbt_counts_reduce_dev(hbt_ctx* ctx, const uint64_t* reads, uint64_t n_intervals,
+                          uint32_t n_cpus, uint32_t n_events, uint64_t* sums);
+
+/* K5.  From summed triples: scaled[i][e] = getCount(e); rates[i][e] =
+ * float(double(scaled)*1e3/double(time_running)) (mips / mega_cycles_per_second);
+ * ratios[i][r]; deltas[i][e] = scaled[i][e] - scaled[i-1][e] (u64 wrap; interval
+ * 0 uses prev_scaled, or 0 when NULL): MetricSeries::diff convention
+ * (dynolog/src/metric_frame/MetricSeries.h:221-227).  Any output may be NULL. */
+int hbt_counts_scale_dev(hbt_ctx* ctx, const uint64_t* sums, uint64_t n_intervals,
+                         uint32_t n_events, const hbt_ratio* ratios, uint32_t n_ratios,
+                         const uint64_t* prev_scaled, uint64_t* scaled, float* rates,
+                         double* ratio_out, uint64_t* deltas);
+
+/* K4+K5 in one launch (single-GPU path: no reduction across ranks between). */
+int hbt_counts_pipeline_dev(hbt_ctx* ctx, const uint64_t* reads, uint64_t n_intervals,
+                            uint32_t n_cpus, uint32_t n_events, const hbt_ratio* ratios,
+                            uint32_t n_ratios, uint64_t* sums, uint64_t* scaled,
+                            float* rates, double* ratio_out, uint64_t* deltas);
+
+/* Same with HOST buffers: H2D of reads, kernels, D2H of every non-NULL output,
+ * then a sync.  This is what a PerCpuCountReader-shaped host adaptor calls. */
+int hbt_counts_pipeline_host(hbt_ctx* ctx, const uint64_t* reads, uint64_t n_intervals,
+                             uint32_t n_cpus, uint32_t n_events, const hbt_ratio* ratios,
+                             uint32_t n_ratios, uint64_t* sums, uint64_t* scaled,
+                             float* rates, double* ratio_out, uint64_t* deltas);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* HBT_B200_H_ */

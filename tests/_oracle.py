@@ -1,0 +1,234 @@
+"""ctypes access to the CHECKERS under oracle/ (test infrastructure only):
+liboracle.so (plain-C restatement) and _ref/libhbt_ref.so (the reference's own
+headers driven by oracle/ref_harness.cpp)."""
+import ctypes as C
+import os
+
+import numpy as np
+
+import dynolog_1_b200 as hbt
+
+ORACLE_DIR = os.path.join(hbt.REPO_ROOT, "oracle")
+PORT_PATH = os.path.join(ORACLE_DIR, "liboracle.so")
+REF_PATH = os.path.join(ORACLE_DIR, "_ref", "libhbt_ref.so")
+
+_P = C.c_void_p
+
+
+class Carry(C.Structure):
+    _fields_ = [("tstamp", C.c_uint64), ("last", C.c_uint64 * hbt.MAX_EVENTS)]
+
+
+def _np(a):
+    return C.c_void_p(a.ctypes.data) if a is not None else None
+
+
+_port = None
+_ref = None
+
+
+def port():
+    global _port
+    if _port is None:
+        lib = C.CDLL(PORT_PATH)
+        lib.hbt_oracle_consume.restype = C.c_int
+        lib.hbt_oracle_consume.argtypes = [_P, C.c_uint64, C.c_uint64, C.c_uint64,
+                                           C.POINTER(hbt.DecodeDesc), C.POINTER(Carry), _P,
+                                           C.c_uint64, _P, C.POINTER(hbt.CpuResult)]
+        lib.hbt_oracle_counts.restype = C.c_int
+        lib.hbt_oracle_counts.argtypes = [_P, C.c_uint64, C.c_uint32, C.c_uint32, _P, C.c_uint32,
+                                          _P, _P, _P, _P, _P]
+        lib.hbt_oracle_hist_new.restype = _P
+        lib.hbt_oracle_hist_free.argtypes = [_P]
+        lib.hbt_oracle_hist_size.restype = C.c_uint64
+        lib.hbt_oracle_hist_size.argtypes = [_P]
+        lib.hbt_oracle_hist_fetch.restype = C.c_uint64
+        lib.hbt_oracle_hist_fetch.argtypes = [_P, C.c_uint32, _P, C.c_uint64]
+        lib.hbt_oracle_kernel_time_from_tsc.restype = C.c_uint64
+        lib.hbt_oracle_kernel_time_from_tsc.argtypes = [C.c_uint64, C.POINTER(hbt.TscParams)]
+        _port = lib
+    return _port
+
+
+def have_ref():
+    return os.path.exists(REF_PATH)
+
+
+def ref():
+    global _ref
+    if _ref is None:
+        lib = C.CDLL(REF_PATH)
+        lib.hbtref_consume_count.restype = C.c_int
+        lib.hbtref_consume_count.argtypes = [_P, C.c_uint64, C.c_uint64, C.c_uint64, C.c_int,
+                                             C.c_uint32, C.POINTER(hbt.CpuResult)]
+        for name in ("hbtref_sample_deltas", "hbtref_mixed_deltas"):
+            fn = getattr(lib, name)
+            fn.restype = C.c_int
+            fn.argtypes = [_P, C.c_uint64, C.c_uint64, C.c_uint64, C.c_uint32, C.c_uint64,
+                           C.POINTER(hbt.TscParams), C.c_uint32, C.POINTER(C.c_uint64), _P, _P,
+                           C.c_uint64, C.POINTER(hbt.CpuResult)]
+        lib.hbtref_hist_new.restype = _P
+        lib.hbtref_hist_free.argtypes = [_P]
+        lib.hbtref_ip_hist.restype = C.c_double
+        lib.hbtref_ip_hist.argtypes = [_P, _P, C.c_uint64, _P, _P, C.c_uint32, C.c_uint32,
+                                       C.c_uint32, C.c_uint32, _P]
+        lib.hbtref_hist_size.restype = C.c_uint64
+        lib.hbtref_hist_size.argtypes = [_P]
+        lib.hbtref_hist_fetch.restype = C.c_uint64
+        lib.hbtref_hist_fetch.argtypes = [_P, _P, C.c_uint64]
+        lib.hbtref_sample_deltas_timed.restype = C.c_double
+        lib.hbtref_sample_deltas_timed.argtypes = [_P, C.c_uint64, _P, _P, C.c_uint32, C.c_uint32,
+                                                   C.c_uint32, C.POINTER(C.c_uint64),
+                                                   C.POINTER(C.c_uint64)]
+        lib.hbtref_counts.restype = C.c_double
+        lib.hbtref_counts.argtypes = [_P, C.c_uint64, C.c_uint32, C.c_uint32, _P, C.c_uint32, _P,
+                                      _P, _P, _P, _P, C.c_uint32]
+        lib.hbtref_kernel_time_from_tsc.restype = C.c_uint64
+        lib.hbtref_kernel_time_from_tsc.argtypes = [C.c_uint64, C.POINTER(hbt.TscParams)]
+        _ref = lib
+    return _ref
+
+
+MODE_INDEX = {hbt.MODE_SAMPLING: 0, hbt.MODE_CONTEXT_SWITCH: 1, hbt.MODE_AUX_SPACE: 2,
+              hbt.MODE_MIXED: 3}
+
+
+def result_dict(res: hbt.CpuResult, rows=None, carry_last=None, hist=None):
+    d = dict(ret=int(res.ret), n_records=int(res.n_records), new_tail=int(res.new_tail),
+             n_rows=int(res.n_rows), counters=[int(x) for x in res.counters],
+             num_unknown=int(res.num_unknown_count_interval),
+             carry_tstamp=int(res.carry_tstamp))
+    if rows is not None:
+        d["rows"] = rows
+    if carry_last is not None:
+        d["carry_last"] = carry_last
+    if hist is not None:
+        d["hist"] = hist
+    return d
+
+
+def hist_to_dict(entries: np.ndarray):
+    return {(int(e["cpu"]), int(e["pid"]), int(e["ip"])): int(e["count"]) for e in entries}
+
+
+def port_consume(ring: np.ndarray, tail: int, head: int, desc: hbt.DecodeDesc,
+                 carry_tstamp=hbt.INVALID_TS, carry_last=None, counters=None, num_unknown=0,
+                 cpu=0):
+    """oracle/hbt_oracle.c over one ring image (uint8/uint64 numpy array)."""
+    lib = port()
+    ring = np.ascontiguousarray(ring).view(np.uint8)
+    n = max(1, desc.n_events)
+    carry = Carry()
+    carry.tstamp = carry_tstamp
+    if carry_last is not None:
+        for i, v in enumerate(carry_last):
+            carry.last[i] = int(v)
+    res = hbt.CpuResult()
+    if counters is not None:
+        for i, v in enumerate(counters):
+            res.counters[i] = int(v)
+    res.num_unknown_count_interval = num_unknown
+    cap = (head - tail) // (40 + 8 * n) + 2
+    rows = np.zeros((cap, 2 + n), dtype=np.uint64)
+    h = lib.hbt_oracle_hist_new() if desc.aggregate == hbt.AGG_IP_HISTOGRAM else None
+    rc = lib.hbt_oracle_consume(_np(ring), ring.nbytes, tail, head, C.byref(desc), C.byref(carry),
+                                _np(rows), cap, h, C.byref(res))
+    assert rc == 0
+    hist = None
+    if h:
+        m = lib.hbt_oracle_hist_size(h)
+        ent = np.zeros(max(1, m), dtype=hbt.HIST_DTYPE)
+        k = lib.hbt_oracle_hist_fetch(h, cpu, _np(ent), ent.shape[0])
+        hist = hist_to_dict(ent[:k])
+        lib.hbt_oracle_hist_free(h)
+    return result_dict(res, rows[:res.n_rows].copy(),
+                       np.array([carry.last[i] for i in range(n)], dtype=np.uint64), hist)
+
+
+def ref_consume(ring: np.ndarray, tail: int, head: int, desc: hbt.DecodeDesc,
+                carry_tstamp=hbt.INVALID_TS, carry_last=None, counters=None, num_unknown=0,
+                cpu=0):
+    """The reference's own consume() (oracle/_ref) over one ring image."""
+    lib = ref()
+    ring = np.ascontiguousarray(ring).view(np.uint8)
+    res = hbt.CpuResult()
+    if counters is not None:
+        for i, v in enumerate(counters):
+            res.counters[i] = int(v)
+    res.num_unknown_count_interval = num_unknown
+    if desc.aggregate == hbt.AGG_NONE and desc.sample_layout == hbt.SAMPLE_GROUP:
+        rc = lib.hbtref_consume_count(_np(ring), ring.nbytes, tail, head,
+                                      MODE_INDEX[desc.handled_mask], desc.max_records,
+                                      C.byref(res))
+        assert rc == 0
+        res.carry_tstamp = hbt.INVALID_TS
+        return result_dict(res)
+    if desc.aggregate == hbt.AGG_COUNT_DELTAS:
+        n = desc.n_events
+        ts = C.c_uint64(carry_tstamp)
+        last = np.zeros(hbt.MAX_EVENTS, dtype=np.uint64)
+        if carry_last is not None:
+            last[:len(carry_last)] = carry_last
+        cap = (head - tail) // (40 + 8 * n) + 2
+        rows = np.zeros((cap, 2 + n), dtype=np.uint64)
+        fn = lib.hbtref_sample_deltas if desc.handled_mask == hbt.MODE_SAMPLING \
+            else lib.hbtref_mixed_deltas
+        rc = fn(_np(ring), ring.nbytes, tail, head, n, desc.tsc_transform_mask,
+                C.byref(desc.tsc), desc.max_records, C.byref(ts), _np(last), _np(rows), cap,
+                C.byref(res))
+        assert rc == 0, rc
+        return result_dict(res, rows[:res.n_rows].copy(), last[:n].copy())
+    # IP layouts
+    h = lib.hbtref_hist_new()
+    tails = np.array([tail], dtype=np.uint64)
+    heads = np.array([head], dtype=np.uint64)
+    resarr = (hbt.CpuResult * 1)()
+    if counters is not None:
+        for i, v in enumerate(counters):
+            resarr[0].counters[i] = int(v)
+    t = lib.hbtref_ip_hist(h, _np(ring), ring.nbytes, _np(tails), _np(heads), 1,
+                           desc.ip_sample_bytes, desc.max_records, 1, resarr)
+    assert t >= 0, t
+    m = lib.hbtref_hist_size(h)
+    ent = np.zeros(max(1, m), dtype=hbt.HIST_DTYPE)
+    k = lib.hbtref_hist_fetch(h, _np(ent), ent.shape[0])
+    ent = ent[:k]
+    ent["cpu"] = cpu
+    hist = hist_to_dict(ent) if desc.aggregate == hbt.AGG_IP_HISTOGRAM else None
+    lib.hbtref_hist_free(h)
+    resarr[0].carry_tstamp = hbt.INVALID_TS
+    return result_dict(resarr[0], hist=hist)
+
+
+def counts_outputs(I, E, R):
+    return dict(sums=np.zeros((I, 3 + E), np.uint64), scaled=np.zeros((I, E), np.uint64),
+                rates=np.zeros((I, E), np.float32), ratios=np.zeros((I, max(R, 1)), np.float64),
+                deltas=np.zeros((I, E), np.uint64))
+
+
+def port_counts(reads: np.ndarray, ratios=()):
+    I, Cc, W = reads.shape
+    E, R = W - 3, len(ratios)
+    o = counts_outputs(I, E, R)
+    r = hbt.make_ratios(ratios)
+    rc = port().hbt_oracle_counts(_np(np.ascontiguousarray(reads)), I, Cc, E,
+                                  C.cast(r, C.c_void_p), R, _np(o["sums"]), _np(o["scaled"]),
+                                  _np(o["rates"]), _np(o["ratios"]) if R else None,
+                                  _np(o["deltas"]))
+    assert rc == 0
+    o["ratios"] = o["ratios"][:, :R]
+    return o
+
+
+def ref_counts(reads: np.ndarray, ratios=(), threads=1):
+    I, Cc, W = reads.shape
+    E, R = W - 3, len(ratios)
+    o = counts_outputs(I, E, R)
+    r = hbt.make_ratios(ratios)
+    t = ref().hbtref_counts(_np(np.ascontiguousarray(reads)), I, Cc, E, C.cast(r, C.c_void_p), R,
+                            _np(o["sums"]), _np(o["scaled"]), _np(o["rates"]),
+                            _np(o["ratios"]) if R else None, _np(o["deltas"]), threads)
+    assert t >= 0, t
+    o["ratios"] = o["ratios"][:, :R]
+    o["seconds"] = t
+    return o
