@@ -1,0 +1,381 @@
+#!/usr/bin/env python
+"""bench.py -- records decoded+aggregated per second on synthetic perf_event traces.
+
+    python bench.py --gpus N --steps K --warmup W [--impl reference] [--workload ...]
+
+Default workload = BASELINE.json configs[1]: PERF_RECORD_SAMPLE ring-buffer decode
++ (cpu,pid,ip) histogram, 256 CPUs x 16 MiB rings per GPU (IP|TID|TIME|CPU samples
+of 40 B, pid ~ Zipf(1.1) over 4096, ip ~ Zipf(1.1) over 65536 addresses per pid).
+One "step" = one pass of decode+aggregate over that batch.  Under torchrun every
+rank holds its own 256-CPU shard (weak scaling, sharded by CPU id) and the
+per-type record counters are summed with one NCCL all-reduce per step.
+
+Prints ONE JSON line (rank 0).  `value` is measured with the traces resident in
+HBM; `e2e` goes through the host-buffer C-ABI calls with the H2D / D2H copies
+inside the timed region.  `--impl reference` times the reference's own consume()
+(oracle/_ref, built from the reference headers) on the host cores instead.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+import numpy as np  # noqa: E402
+import torch  # noqa: E402
+
+import dynolog_1_b200 as hbt  # noqa: E402
+from dynolog_1_b200 import tracegen as tg  # noqa: E402
+
+METRIC = "perf records decoded+aggregated/sec"
+UNIT = "records/s"
+
+
+def load_peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        with open(p) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json)"
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+class ClockSampler:
+    """nvidia-smi clocks + throttle reasons during the timed region."""
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index: int):
+        self.index = index
+        self.samples = []
+        self.proc = None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}",
+                 "--format=csv,noheader,nounits", "-lms", "100"],
+                stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._read, daemon=True)
+            self.thread.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.samples.append(line.strip())
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for s in self.samples:
+            parts = [x.strip() for x in s.split(",")]
+            if len(parts) < 6:
+                continue
+            try:
+                sm.append(float(parts[0]))
+                mx.append(float(parts[1]))
+            except ValueError:
+                continue
+            for n, v in zip(names, parts[2:6]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        return {"sm_mhz": statistics.median(sm) if sm else None,
+                "sm_max_mhz": max(mx) if mx else None, "reasons": sorted(reasons),
+                "samples": len(sm)}
+
+
+# ---------------------------------------------------------------------------
+# workload: config 2
+# ---------------------------------------------------------------------------
+def make_c2(n_cpus: int, ring_bytes: int, cpu_base: int, device, sample_words=5):
+    """n_cpus ring images on `device`; returns (imgs[int64 n_cpus x words], tails, heads, n_records)."""
+    imgs = torch.empty((n_cpus, ring_bytes // 8), dtype=torch.int64, device=device)
+    tails, heads = [], []
+    n = (ring_bytes - 65536) // (8 * sample_words)  # slack: the ring is not completely full
+    cdfs = (tg.zipf_cdf(4096, 1.1, device), tg.zipf_cdf(65536, 1.1, device))
+    for c in range(n_cpus):
+        cpu = cpu_base + c
+        seed = tg.stream_seed(2, cpu)
+        s = tg.ip_sample_stream(seed, n, cpu=cpu, device=device, sample_words=sample_words, cdfs=cdfs)
+        tail = tg.random_tail(seed, ring_bytes)  # not tile aligned: >= 1 record wraps the ring end
+        ring, head = tg.place_in_ring(s, ring_bytes, tail, fill_seed=seed ^ 0xABCDEF)
+        imgs[c] = ring
+        tails.append(tail)
+        heads.append(head)
+    return imgs, tails, heads, n * n_cpus
+
+
+def run_reference(args, rank, world):
+    """The reference's consume() (reference headers, oracle/_ref) + the harness's
+    (pid,ip) map, all host threads, on a bounded sample of the same workload."""
+    if rank != 0:
+        return
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import _oracle as orc
+    import ctypes as C
+    cores = os.cpu_count() or 1
+    kind = "reference"
+    if not orc.have_ref():
+        print(json.dumps({"impl": "reference", "unavailable":
+                          "oracle/_ref/libhbt_ref.so was not built (no reference tree at build time)"}))
+        return
+    lib = orc.ref()
+    ring_bytes = args.ring_mib << 20
+    # bounded sample: `sample_cpus` rings of the 256 (same generator, same seeds)
+    sample_cpus = min(args.cpus, args.ref_cpus)
+    imgs, tails, heads, n_rec = make_c2(sample_cpus, ring_bytes, 0, "cpu")
+    rings = imgs.numpy().view(np.uint8)
+    tails_a = np.array(tails, dtype=np.uint64)
+    heads_a = np.array(heads, dtype=np.uint64)
+    res = (hbt.CpuResult * sample_cpus)()
+    h = lib.hbtref_hist_new()
+    times = []
+    for it in range(args.warmup + args.steps):
+        for r in res:
+            for i in range(hbt.NUM_COUNTERS):
+                r.counters[i] = 0
+        t = lib.hbtref_ip_hist(h, rings.ctypes.data, ring_bytes, tails_a.ctypes.data,
+                               heads_a.ctypes.data, sample_cpus, 40, hbt.DRAIN, cores, res)
+        assert t > 0, t
+        if it >= args.warmup:
+            times.append(t)
+    got = sum(int(r.counters[hbt.CNT_SAMPLE]) for r in res)
+    assert got == n_rec, (got, n_rec)
+    lib.hbtref_hist_free(h)
+    dt = sum(times) / len(times)
+    value = n_rec / dt
+    sample = f"{sample_cpus} of {args.cpus} rings x {args.ring_mib} MiB per step"
+    line = {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt * 1e3,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u64",
+            "data": "synthetic",
+            "config": {"workload": "c2_ip_hist: SAMPLE ring decode + (cpu,pid,ip) histogram",
+                       "cpus": args.cpus, "ring_mib": args.ring_mib, "sample_bytes": 40,
+                       "note": "CPU reference arm: bounded sample of the workload per step"},
+            "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": kind,
+                             "sample": sample},
+            "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(line))
+
+
+def cpu_baseline_leg(args):
+    """Bounded CPU baseline beside the GPU number (rank 0, N=1 only)."""
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    try:
+        import _oracle as orc
+        if not orc.have_ref():
+            return None
+        lib = orc.ref()
+    except Exception:
+        return None
+    cores = os.cpu_count() or 1
+    ring_bytes = args.ring_mib << 20
+    sample_cpus = min(args.cpus, args.ref_cpus)
+    imgs, tails, heads, n_rec = make_c2(sample_cpus, ring_bytes, 0, "cpu")
+    rings = imgs.numpy().view(np.uint8)
+    tails_a = np.array(tails, dtype=np.uint64)
+    heads_a = np.array(heads, dtype=np.uint64)
+    res = (hbt.CpuResult * sample_cpus)()
+    h = lib.hbtref_hist_new()
+    best = None
+    for _ in range(2):
+        t = lib.hbtref_ip_hist(h, rings.ctypes.data, ring_bytes, tails_a.ctypes.data,
+                               heads_a.ctypes.data, sample_cpus, 40, hbt.DRAIN, cores, res)
+        best = t if best is None else min(best, t)
+    lib.hbtref_hist_free(h)
+    return {"value": n_rec / best, "unit": UNIT, "cores": cores, "kind": "reference",
+            "sample": f"{sample_cpus} of {args.cpus} rings x {args.ring_mib} MiB, best of 2; "
+                      "reference consume() + std::unordered_map handler"}
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--cpus", type=int, default=256)
+    ap.add_argument("--ring-mib", type=int, default=16)
+    ap.add_argument("--ref-cpus", type=int, default=32, help="rings in the bounded CPU sample")
+    ap.add_argument("--hist-slots-per-cpu", type=int, default=1 << 19)
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+
+    if args.impl == "reference":
+        run_reference(args, rank, world)
+        return
+
+    assert torch.cuda.is_available(), "bench.py needs a GPU (there is no CPU fallback)"
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist_
+        dist = dist_
+        dist.init_process_group("nccl", device_id=dev)
+
+    ring_bytes = args.ring_mib << 20
+    cpu_base = rank * args.cpus
+    imgs, tails, heads, n_rec = make_c2(args.cpus, ring_bytes, cpu_base, dev)
+    window_bytes = sum(h - t for t, h in zip(tails, heads))
+    torch.cuda.synchronize()
+
+    ctx = hbt.Context(local, max_cpus=args.cpus)
+    ctx.use_torch_stream()
+    ctx.ring_configure(args.cpus, 0)
+    ctx.set_cpu_base(cpu_base)
+    ctx.hist_configure(args.hist_slots_per_cpu * args.cpus)
+    desc = hbt.ip_desc(40)
+    counters_dev = torch.zeros(hbt.NUM_COUNTERS + 1, dtype=torch.int64, device=dev)
+
+    def step():
+        ctx.hist_clear()
+        ctx.reset_state(hbt.INVALID_TS) if False else None
+        for c in range(args.cpus):
+            ctx.submit_ring_dev(c, imgs[c], ring_bytes, tails[c], heads[c])
+        ctx.decode(desc)
+
+    def step_exchange():
+        # metric-table merge across the GPUs of the box: per-type record counters
+        if dist is not None:
+            dist.all_reduce(counters_dev)
+
+    # ---- warm-up + validation -------------------------------------------------
+    for _ in range(max(args.warmup, 3)):
+        step()
+        res = ctx.fetch_results()
+    total = int(res["n_records"].sum())
+    assert total == n_rec, (total, n_rec)
+    assert int(res["counters"][:, hbt.CNT_SAMPLE].sum()) == n_rec
+    distinct = ctx.hist_size()
+    slow, reruns = ctx.slow_tiles, ctx.reruns
+
+    # ---- timed region: device-resident ----------------------------------------
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    launches0 = ctx.launches
+    kernel_ms = []
+    if dist is not None:
+        dist.barrier()
+    torch.cuda.synchronize()
+    e0 = torch.cuda.Event(enable_timing=True)
+    e1 = torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(args.steps):
+        step()
+        step_exchange()
+        # completing the decode (re-run check) is part of the step; it syncs the stream
+        ctx.fetch_results()
+        kernel_ms.append(ctx.decode_kernel_ms)
+    e1.record()
+    torch.cuda.synchronize()
+    if dist is not None:
+        dist.barrier()
+    ms_total = e0.elapsed_time(e1)
+    launches = ctx.launches - launches0
+    clocks = sampler.stop() if rank == 0 else None
+
+    t = torch.tensor([ms_total], dtype=torch.float64, device=dev)
+    if dist is not None:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms_step = float(t.item()) / args.steps
+    value = n_rec * world / (ms_step * 1e-3)
+
+    # ---- end-to-end: host buffers through the C-ABI --------------------------------
+    e2e = None
+    if not args.no_e2e:
+        host = torch.empty((args.cpus, ring_bytes // 8), dtype=torch.int64).pin_memory()
+        host.copy_(imgs)
+        host_np = host.numpy()
+        ctx.ring_configure(args.cpus, ring_bytes)
+        ctx.hist_configure(args.hist_slots_per_cpu * args.cpus)
+        ent_dt = hbt.HIST_DTYPE.itemsize
+
+        def e2e_step():
+            ctx.hist_clear()
+            for c in range(args.cpus):
+                ctx.submit_ring_image(c, host_np[c], tails[c], heads[c])
+            ctx.decode(desc)
+            r = ctx.fetch_results()
+            ent = ctx.hist_fetch()
+            return r, ent
+
+        e2e_step()
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        for _ in range(max(1, min(args.steps, 3))):
+            r, ent = e2e_step()
+        torch.cuda.synchronize()
+        dt = (time.perf_counter() - t0) / max(1, min(args.steps, 3))
+        tt = torch.tensor([dt], dtype=torch.float64, device=dev)
+        if dist is not None:
+            dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        dt = float(tt.item())
+        assert int(r["n_records"].sum()) == n_rec
+        e2e = {"value": n_rec * world / dt, "unit": UNIT, "h2d_bytes_per_step": int(window_bytes),
+               "d2h_bytes_per_step": int(len(ent) * ent_dt + r.nbytes), "ms_per_step": dt * 1e3}
+
+    if rank != 0:
+        if dist is not None:
+            dist.destroy_process_group()
+        return
+
+    peak, peak_src = load_peaks()
+    k_ms = sum(kernel_ms) / len(kernel_ms)
+    algo_bytes = window_bytes + 16 * distinct  # ring bytes once + 16 B per distinct key
+    achieved = algo_bytes / (k_ms * 1e-3) / 1e9
+    line = {
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+        "warmup": max(args.warmup, 3), "ms_per_step": ms_step, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "u64", "data": "synthetic",
+        "config": {"workload": "c2_ip_hist: PERF_RECORD_SAMPLE ring decode + (cpu,pid,ip) histogram",
+                   "cpus_per_gpu": args.cpus, "ring_mib": args.ring_mib, "sample_bytes": 40,
+                   "records_per_gpu": n_rec, "distinct_keys_per_gpu": distinct,
+                   "window_bytes_per_gpu": int(window_bytes),
+                   "l2": "inputs (4 GiB/GPU) exceed L2; no flush needed",
+                   "sharding": "by CPU id, 256 CPUs per rank; NCCL all-reduce of record counters",
+                   "slow_tiles": slow, "reruns": reruns},
+        "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
+                     "frac": achieved / peak, "traffic": None, "kernel": "k_decode<IP_HISTOGRAM>",
+                     "kernel_ms": k_ms, "algorithmic_bytes": int(algo_bytes), "peak_source": peak_src,
+                     "frac_of_nominal_8000": achieved / 8000.0},
+        "gpu_launches": int(launches),
+        "clocks": clocks,
+    }
+    if e2e:
+        line["e2e"] = e2e
+    if world == 1 and not args.no_cpu_baseline:
+        cb = cpu_baseline_leg(args)
+        if cb:
+            line["cpu_baseline"] = cb
+    print(json.dumps(line))
+    if dist is not None:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -92,6 +92,7 @@ EXPORTS = [
     ("hbt_fetch_results", C.c_int, [_P, _P, C.c_uint32]),
     ("hbt_decode_reruns", C.c_uint32, [_P]),
     ("hbt_decode_slow_tiles", C.c_uint64, [_P]),
+    ("hbt_decode_kernel_ms", C.c_float, [_P]),
     ("hbt_fetch_rows", C.c_int64, [_P, C.c_uint32, _P, C.c_uint64]),
     ("hbt_rows_slabs_dev", C.c_int, [_P, C.c_uint32, C.POINTER(_P), _U64P, C.POINTER(C.c_uint32)]),
     ("hbt_rows_max_slabs", C.c_uint32, [_P]),
@@ -249,6 +250,10 @@ class Context:
     @property
     def reruns(self) -> int:
         return int(self.lib.hbt_decode_reruns(self.h))
+
+    @property
+    def decode_kernel_ms(self) -> float:
+        return float(self.lib.hbt_decode_kernel_ms(self.h))
 
     @property
     def slow_tiles(self) -> int:

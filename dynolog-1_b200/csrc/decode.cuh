@@ -173,7 +173,9 @@ __device__ __forceinline__ int counter_of(uint32_t type, uint32_t handled) {
 __device__ __forceinline__ void hist_insert_global(const HistTable& t, uint32_t cpu, uint64_t ip,
                                                    uint32_t pid, uint32_t n) {
   if (ip == 0 && pid == 0) {
-    atomicAdd(reinterpret_cast<unsigned long long*>(t.zero_key + cpu), (unsigned long long)n);
+    // n is a signed 32-bit increment (-k when a failed attempt is taken back out)
+    atomicAdd(reinterpret_cast<unsigned long long*>(t.zero_key + cpu),
+              (unsigned long long)(long long)(int32_t)n);
     return;
   }
   ulonglong2* base = t.slots + (uint64_t)cpu * t.slots_per_cpu;

@@ -117,6 +117,7 @@ struct hbt_ctx {
   bool have_results = false;
   hbt_decode_desc desc{};
   uint32_t reruns = 0;
+  cudaEvent_t ev_k0 = nullptr, ev_k1 = nullptr;  // around the decode kernel
 
   // histogram
   DevBuf<ulonglong2> hist_slots;
@@ -326,7 +327,9 @@ int launch_decode_agg(hbt_ctx* ctx, uint32_t hist_inc) {
                               (int)smem));
       ctx->attr_set[AGG] = true;
     }
+    if (hist_inc == 1) CU(cudaEventRecord(ctx->ev_k0, ctx->stream));
     k_decode<AGG><<<ctx->n_segs, kThreads, smem, ctx->stream>>>(p);
+    if (hist_inc == 1) CU(cudaEventRecord(ctx->ev_k1, ctx->stream));
   } else {
     k_decode_small<AGG><<<(ctx->n_segs + 31) / 32, 32, 0, ctx->stream>>>(p, ctx->n_segs);
   }
@@ -412,6 +415,8 @@ int hbt_create(hbt_ctx** out, int device, uint32_t max_cpus, uint32_t max_events
     return -EIO;
   }
   ctx->stream = ctx->own_stream;
+  cudaEventCreate(&ctx->ev_k0);
+  cudaEventCreate(&ctx->ev_k1);
   *out = ctx;
   return 0;
 }
@@ -455,6 +460,8 @@ void hbt_destroy(hbt_ctx* ctx) {
   ctx->c_deltas.release();
   ctx->c_rates.release();
   ctx->c_ratio.release();
+  if (ctx->ev_k0) cudaEventDestroy(ctx->ev_k0);
+  if (ctx->ev_k1) cudaEventDestroy(ctx->ev_k1);
   if (ctx->own_stream) cudaStreamDestroy(ctx->own_stream);
   delete ctx;
 }
@@ -685,6 +692,17 @@ int hbt_fetch_results(hbt_ctx* ctx, hbt_cpu_result* out, uint32_t cap) {
 }
 
 uint32_t hbt_decode_reruns(const hbt_ctx* ctx) { return ctx ? ctx->reruns : 0; }
+
+float hbt_decode_kernel_ms(hbt_ctx* ctx) {
+  if (!ctx || !ctx->tiled) return -1.0f;
+  float ms = -1.0f;
+  if (cudaEventSynchronize(ctx->ev_k1) != cudaSuccess) return -1.0f;
+  if (cudaEventElapsedTime(&ms, ctx->ev_k0, ctx->ev_k1) != cudaSuccess) {
+    cudaGetLastError();
+    return -1.0f;
+  }
+  return ms;
+}
 
 uint64_t hbt_decode_slow_tiles(hbt_ctx* ctx) {
   if (!ctx || !ctx->have_results) return 0;

@@ -240,6 +240,9 @@ int hbt_fetch_results(hbt_ctx* ctx, hbt_cpu_result* out, uint32_t cap);
  * fell back to the one-thread sequential walk.  Both are 0 on well-formed streams. */
 uint32_t hbt_decode_reruns(const hbt_ctx* ctx);
 uint64_t hbt_decode_slow_tiles(hbt_ctx* ctx);
+/* Device time of the last decode kernel launch (CUDA events on the ctx stream
+ * around that one launch; waits for it).  Negative when unavailable. */
+float hbt_decode_kernel_ms(hbt_ctx* ctx);
 
 /* Rows {tstamp, duration, deltas[n_events]} of the last decode for `cpu`, in
  * stream order: the bytes CpuCountSampleGenerator writes to its output ring

@@ -1,0 +1,454 @@
+"""Parity of the CUDA path (through the C-ABI, libhbt_b200.so) with the oracle
+(oracle/hbt_oracle.c, itself pinned to the reference by
+test_oracle_vs_reference.py / test_golden.py) on the same seeded inputs.
+Bit-exact for every integer output; f64 ratios within 1e-12 relative."""
+import numpy as np
+import pytest
+
+import dynolog_1_b200 as hbt
+from dynolog_1_b200 import tracegen as tg
+import _oracle as orc
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def ctx(built):
+    c = hbt.Context(0)
+    yield c
+    c.close()
+
+
+def ring_np(stream, ds, tail, fill=77):
+    ring, head = tg.place_in_ring(stream, ds, tail, fill_seed=fill)
+    return ring.numpy().view(np.uint64), head
+
+
+def gpu_decode(ctx, rings, desc, ds, seed_ts=hbt.INVALID_TS, reset=True, hist_slots=0):
+    if reset:
+        ctx.ring_configure(len(rings), ds)
+        ctx.reset_state(seed_ts)
+        if hist_slots:
+            ctx.hist_configure(hist_slots)
+    for cpu, (ring, tail, head) in enumerate(rings):
+        ctx.submit_ring_image(cpu, ring, tail, head)
+    ctx.decode(desc)
+    return ctx.fetch_results()
+
+
+def gpu_decode_full_images(ctx, rings, desc, ds, seed_ts=hbt.INVALID_TS, reset=True):
+    """Whole ring images on the device (hbt_submit_ring_dev): bytes outside
+    [tail, head) are there too, like in the kernel's mmap, so a record that starts
+    before head and runs past it reads the same bytes as in the reference."""
+    import torch
+    imgs = [torch.from_numpy(r.view(np.int64)).cuda() for r, _, _ in rings]
+    if reset:
+        ctx.ring_configure(len(rings), 0)
+        ctx.reset_state(seed_ts)
+    for cpu, (ring, tail, head) in enumerate(rings):
+        ctx.submit_ring_dev(cpu, imgs[cpu], ds, tail, head)
+    ctx.decode(desc)
+    res = ctx.fetch_results()
+    ctx._keep = imgs
+    return res
+
+
+def check_cpu(ctx, cpu, got, want, desc):
+    assert int(got["ret"]) == want["ret"], (cpu, int(got["ret"]), want["ret"])
+    assert int(got["n_records"]) == want["n_records"], cpu
+    assert int(got["new_tail"]) == want["new_tail"], cpu
+    assert [int(x) for x in got["counters"]] == want["counters"], cpu
+    if desc.aggregate == hbt.AGG_COUNT_DELTAS:
+        assert int(got["n_rows"]) == want["n_rows"], cpu
+        assert int(got["num_unknown_count_interval"]) == want["num_unknown"], cpu
+        assert int(got["carry_tstamp"]) == want["carry_tstamp"], cpu
+        rows = ctx.fetch_rows(cpu, int(got["n_rows"]), desc.n_events)
+        assert np.array_equal(rows, want["rows"]), f"rows differ on cpu {cpu}"
+        if want["counters"][hbt.CNT_SAMPLE]:
+            assert np.array_equal(ctx.fetch_carry(cpu, desc.n_events), want["carry_last"]), cpu
+
+
+# ---------------------------------------------------------------------------
+# counter groups (K4 + K5)
+# ---------------------------------------------------------------------------
+@pytest.mark.parametrize("I,C,E,mux", [(300, 64, 8, False), (200, 64, 8, True), (64, 7, 32, True),
+                                       (100, 3, 1, True), (9, 512, 2, True), (40, 16, 64, True),
+                                       (1, 1, 1, False), (1000, 256, 32, True)])
+def test_counts_pipeline(ctx, I, C, E, mux):
+    reads = tg.counts_trace(61 + E, I, C, E, multiplexed=mux).numpy().view(np.uint64)
+    ratios = [(min(1, E - 1), 0), (E - 1, min(1, E - 1))]
+    got, want = ctx.counts_pipeline_host(reads, ratios), orc.port_counts(reads, ratios)
+    for k in ("sums", "scaled", "deltas"):
+        assert np.array_equal(got[k], want[k]), k
+    assert np.array_equal(got["rates"], want["rates"])
+    # tolerance stated by the north star for f64 ratios
+    assert np.allclose(got["ratios"], want["ratios"], rtol=1e-12, atol=0.0)
+    assert np.array_equal(got["ratios"], want["ratios"])  # and in fact identical (IEEE div)
+
+
+def test_counts_edge_values(ctx):
+    I, C, E = 6, 4, 3
+    reads = tg.counts_trace(71, I, C, E, multiplexed=True).numpy().view(np.uint64).copy()
+    reads[1, :, 3] = np.uint64(2**62)
+    reads[2, :, 4] = np.uint64(2**60 + 12345)
+    reads[3, :, 1] = 0
+    reads[3, :, 2] = 0
+    reads[4, 2, 0] = 0
+    got, want = ctx.counts_pipeline_host(reads), orc.port_counts(reads)
+    assert np.array_equal(got["sums"], want["sums"])
+    assert got["sums"][4, 0] == 0
+    assert np.array_equal(got["scaled"], want["scaled"])
+    assert np.array_equal(got["deltas"], want["deltas"])
+    ok = [0, 1, 2, 5]  # rate of a 0/0 interval is NaN on both sides
+    assert np.array_equal(got["rates"][ok], want["rates"][ok])
+    assert np.all(np.isnan(got["rates"][3])) and np.all(np.isnan(want["rates"][3]))
+
+
+def test_counts_dev_split_equals_pipeline(ctx):
+    """K4 then K5 (the multi-GPU order: reduce, [NCCL sum], scale) == fused."""
+    import torch
+    I, C, E = 500, 128, 8
+    reads = tg.counts_trace(5, I, C, E, device="cuda", multiplexed=True)
+    sums = torch.zeros((I, 3 + E), dtype=torch.int64, device="cuda")
+    scaled = torch.zeros((I, E), dtype=torch.int64, device="cuda")
+    rates = torch.zeros((I, E), dtype=torch.float32, device="cuda")
+    ratio = torch.zeros((I, 1), dtype=torch.float64, device="cuda")
+    deltas = torch.zeros((I, E), dtype=torch.int64, device="cuda")
+    ctx.use_torch_stream()
+    try:
+        ctx.counts_reduce_dev(reads, I, C, E, sums)
+        ctx.counts_scale_dev(sums, I, E, [(1, 0)], None, scaled, rates, ratio, deltas)
+        ctx.sync()
+        want = orc.port_counts(reads.cpu().numpy().view(np.uint64), [(1, 0)])
+        assert np.array_equal(sums.cpu().numpy().view(np.uint64), want["sums"])
+        assert np.array_equal(scaled.cpu().numpy().view(np.uint64), want["scaled"])
+        assert np.array_equal(deltas.cpu().numpy().view(np.uint64), want["deltas"])
+        assert np.array_equal(rates.cpu().numpy(), want["rates"])
+        assert np.allclose(ratio.cpu().numpy(), want["ratios"], rtol=1e-12, atol=0.0)
+        # linearity: sums of a trace split by CPU add up (what the NCCL reduce relies on)
+        s0 = torch.zeros_like(sums)
+        s1 = torch.zeros_like(sums)
+        ctx.counts_reduce_dev(reads[:, :C // 2].contiguous(), I, C // 2, E, s0)
+        ctx.counts_reduce_dev(reads[:, C // 2:].contiguous(), I, C // 2, E, s1)
+        ctx.sync()
+        tot = s0 + s1
+        tot[:, 0] = E
+        assert torch.equal(tot, sums)
+    finally:
+        ctx.set_stream(None)
+
+
+# ---------------------------------------------------------------------------
+# ring decode + per-interval deltas (K1..K3)
+# ---------------------------------------------------------------------------
+@pytest.mark.parametrize("n_events,lost_every,ds,n_cpus", [
+    (8, 0, 1 << 17, 3), (8, 50, 1 << 17, 3), (1, 7, 1 << 16, 2), (32, 13, 1 << 18, 2),
+    (64, 0, 1 << 18, 2), (8, 1000, 1 << 22, 5), (32, 400, 1 << 23, 2), (2, 3, 1 << 20, 4)])
+def test_sample_deltas(ctx, n_events, lost_every, ds, n_cpus):
+    desc = hbt.sampling_desc(n_events)
+    rings = []
+    for cpu in range(n_cpus):
+        n = (ds - 4096 - 512 * cpu) // (40 + 8 * n_events + 24)
+        s = tg.group_sample_stream(tg.stream_seed(3, cpu) + n_events, n, n_events,
+                                   lost_every=lost_every)
+        tail = tg.random_tail(n_events + lost_every + cpu, ds)
+        ring, head = ring_np(s, ds, tail)
+        rings.append((ring, tail, head))
+    res = gpu_decode(ctx, rings, desc, ds)
+    for cpu, (ring, tail, head) in enumerate(rings):
+        check_cpu(ctx, cpu, res[cpu], orc.port_consume(ring, tail, head, desc), desc)
+    assert ctx.reruns == 0 and ctx.slow_tiles == 0, "well-formed streams must stay on the fast path"
+
+
+def test_carry_across_calls(ctx):
+    """A window decoded in three calls (new data submitted between them) equals
+    the oracle chained the same way: counters, carry tstamp / last_[] and rows."""
+    ds, E = 1 << 18, 4
+    s = tg.group_sample_stream(11, 3000, E, lost_every=170)
+    tail0 = tg.random_tail(5, ds)
+    ring, head = ring_np(s, ds, tail0)
+    cuts = [tail0, tail0 + 8 * (5 + E) * 1000, tail0 + 8 * (5 + E) * 1001 + 24 * 5, head]
+    desc = hbt.sampling_desc(E)
+    ctx.ring_configure(1, 0)
+    ctx.reset_state(777)
+    st = dict(carry_tstamp=777, carry_last=np.zeros(E, np.uint64), counters=[0] * 11, num_unknown=0)
+    a = tail0
+    for b in cuts[1:]:
+        # heads in the middle of a record: consume() takes the straddling record
+        # and the next window starts where it left the tail
+        if b <= a:
+            continue
+        want = orc.port_consume(ring, a, b, desc, st["carry_tstamp"], st["carry_last"],
+                                st["counters"], st["num_unknown"])
+        got = gpu_decode_full_images(ctx, [(ring, a, b)], desc, ds, reset=False)[0]
+        check_cpu(ctx, 0, got, want, desc)
+        st = dict(carry_tstamp=want["carry_tstamp"], carry_last=want["carry_last"],
+                  counters=want["counters"], num_unknown=want["num_unknown"])
+        a = want["new_tail"]
+
+
+@pytest.mark.parametrize("max_records", [0, 1, 100, 4321, 10**6])
+def test_max_records(ctx, max_records):
+    ds, E = 1 << 21, 8
+    rings = []
+    for cpu in range(3):
+        s = tg.group_sample_stream(100 + cpu, 15000 + 100 * cpu, E, lost_every=333)
+        tail = tg.random_tail(cpu + 40, ds)
+        ring, head = ring_np(s, ds, tail)
+        rings.append((ring, tail, head))
+    desc = hbt.sampling_desc(E, max_records=max_records)
+    res = gpu_decode(ctx, rings, desc, ds)
+    for cpu, (ring, tail, head) in enumerate(rings):
+        check_cpu(ctx, cpu, res[cpu], orc.port_consume(ring, tail, head, desc), desc)
+
+
+def test_timestamp_regression_and_bad_size(ctx):
+    ds, E = 1 << 20, 8
+    desc = hbt.sampling_desc(E)
+    cases = []
+    for at in (0, 1, 157, 158, 5000, 9998):  # in-tile, at tile and segment seams
+        s = tg.group_sample_stream(21 + at, 9999, E, regress_at=at if at else -1)
+        if at == 0:
+            s[(5 + E) * 4000 + 2] = E + 1  # header.size != 40 + 8*nr
+        cases.append(s)
+    rings = []
+    for i, s in enumerate(cases):
+        tail = tg.random_tail(i + 3, ds)
+        ring, head = ring_np(s, ds, tail)
+        rings.append((ring, tail, head))
+    res = gpu_decode(ctx, rings, desc, ds)
+    for cpu, (ring, tail, head) in enumerate(rings):
+        want = orc.port_consume(ring, tail, head, desc)
+        assert want["ret"] == -1
+        check_cpu(ctx, cpu, res[cpu], want, desc)
+
+
+def test_regression_at_every_position_small(ctx):
+    """Regression swept over every sample of a stream that spans several tiles and
+    two segments' worth of seams."""
+    ds, E = 1 << 16, 1
+    desc = hbt.sampling_desc(E)
+    for at in list(range(1, 12)) + [340, 341, 342, 343, 683, 1000]:
+        s = tg.group_sample_stream(900 + at, 1200, E, regress_at=at)
+        tail = 48 * 7
+        ring, head = ring_np(s, ds, tail)
+        res = gpu_decode(ctx, [(ring, tail, head)], desc, ds)
+        check_cpu(ctx, 0, res[0], orc.port_consume(ring, tail, head, desc), desc)
+
+
+def test_tsc_transform(ctx):
+    ds, E = 1 << 19, 6
+    s = tg.group_sample_stream(31, 4000, E, lost_every=90)
+    tail = 4096 * 3 + 64
+    ring, head = ring_np(s, ds, tail)
+    desc = hbt.sampling_desc(E, tsc_mask=0b100101, tsc=(987654321, 1234567, 21))
+    res = gpu_decode(ctx, [(ring, tail, head)], desc, ds)
+    check_cpu(ctx, 0, res[0], orc.port_consume(ring, tail, head, desc), desc)
+
+
+@pytest.mark.parametrize("mode", [hbt.MODE_SAMPLING, hbt.MODE_CONTEXT_SWITCH, hbt.MODE_AUX_SPACE,
+                                  hbt.MODE_MIXED])
+@pytest.mark.parametrize("max_records", [hbt.DRAIN, 7777])
+def test_mixed_stream_counters(ctx, mode, max_records):
+    ds, E = 1 << 21, 8
+    rings = []
+    for cpu in range(4):
+        s = tg.mixed_stream(41 + cpu, 18000, E)
+        tail = tg.random_tail(9 + cpu, ds)
+        ring, head = ring_np(s, ds, tail)
+        rings.append((ring, tail, head))
+    desc = hbt.count_desc(mode, max_records=max_records)
+    res = gpu_decode(ctx, rings, desc, ds)
+    for cpu, (ring, tail, head) in enumerate(rings):
+        check_cpu(ctx, cpu, res[cpu], orc.port_consume(ring, tail, head, desc), desc)
+
+
+def test_mixed_stream_deltas(ctx):
+    ds, E = 1 << 21, 8
+    mix = (("sample", 0.6), ("switch", 0.2), ("comm", 0.05), ("mmap", 0.05), ("lost", 0.02),
+           ("fork", 0.04), ("exit", 0.04))
+    rings = []
+    for cpu in range(3):
+        s = tg.mixed_stream(43 + cpu, 20000, E, mix=mix)
+        tail = tg.random_tail(10 + cpu, ds)
+        ring, head = ring_np(s, ds, tail)
+        rings.append((ring, tail, head))
+    desc = hbt.sampling_desc(E, handled=hbt.MODE_MIXED)
+    res = gpu_decode(ctx, rings, desc, ds)
+    for cpu, (ring, tail, head) in enumerate(rings):
+        check_cpu(ctx, cpu, res[cpu], orc.port_consume(ring, tail, head, desc), desc)
+
+
+# ---------------------------------------------------------------------------
+# (cpu,pid,ip) histogram (K6)
+# ---------------------------------------------------------------------------
+@pytest.mark.parametrize("words,ds,n_cpus,n_pids,n_ips", [
+    (5, 1 << 18, 3, 64, 256), (6, 1 << 20, 2, 512, 4096), (16, 1 << 20, 2, 16, 16),
+    (5, 1 << 22, 6, 4096, 65536)])
+def test_ip_histogram(ctx, words, ds, n_cpus, n_pids, n_ips):
+    desc = hbt.ip_desc(8 * words)
+    rings, want_hist, wants = [], {}, []
+    for cpu in range(n_cpus):
+        n = (ds - 8192 - 64 * cpu) // (8 * words)
+        s = tg.ip_sample_stream(51 + cpu, n, cpu=cpu, sample_words=words, n_pids=n_pids,
+                                n_ips=n_ips, lost_every=997)
+        tail = tg.random_tail(12 + cpu, ds)
+        ring, head = ring_np(s, ds, tail)
+        rings.append((ring, tail, head))
+        w = orc.port_consume(ring, tail, head, desc, cpu=cpu)
+        want_hist.update(w["hist"])
+        wants.append(w)
+    res = gpu_decode(ctx, rings, desc, ds, hist_slots=1 << 22)
+    for cpu in range(n_cpus):
+        check_cpu(ctx, cpu, res[cpu], wants[cpu], desc)
+    got = orc.hist_to_dict(ctx.hist_fetch())
+    assert len(got) == len(want_hist)
+    assert got == want_hist
+    # a second identical batch accumulates
+    for cpu, (ring, tail, head) in enumerate(rings):
+        ctx.submit_ring_image(cpu, ring, tail, head)
+    ctx.decode(desc)
+    ctx.fetch_results()
+    got2 = orc.hist_to_dict(ctx.hist_fetch())
+    assert got2 == {k: 2 * v for k, v in want_hist.items()}
+
+
+def test_ip_histogram_zero_key_and_error(ctx):
+    """Key (ip=0,pid=0) (kept outside the table) and a bad-size SAMPLE in the
+    middle: everything after it must be taken back out of the shared table."""
+    ds, words = 1 << 20, 5
+    n = 20000
+    s = tg.ip_sample_stream(7, n, cpu=0, n_pids=8, n_ips=8)
+    s = s.clone()
+    s[1::5][:50] = 0       # ip = 0
+    s[2::5][:50] = 0       # pid = tid = 0
+    bad_at = 12345
+    s[5 * bad_at] = tg.header(tg.REC_SAMPLE, 48)  # size != ip_sample_bytes
+    tail = tg.random_tail(3, ds)
+    ring, head = ring_np(s, ds, tail)
+    desc = hbt.ip_desc(40)
+    want = orc.port_consume(ring, tail, head, desc)
+    assert want["ret"] == -1 and want["n_records"] == bad_at
+    res = gpu_decode(ctx, [(ring, tail, head)], desc, ds, hist_slots=1 << 16)
+    check_cpu(ctx, 0, res[0], want, desc)
+    assert orc.hist_to_dict(ctx.hist_fetch()) == want["hist"]
+    assert (0, 0, 0) in want["hist"]
+
+
+# ---------------------------------------------------------------------------
+# hostile / degenerate inputs: exactness must not depend on the guesses
+# ---------------------------------------------------------------------------
+def test_payload_that_looks_like_headers(ctx):
+    """Counter values crafted to be plausible perf_event_headers whose chains even
+    validate: the guesses go wrong, the verification catches them, results stay exact."""
+    ds, E = 1 << 19, 8
+    s = tg.group_sample_stream(5, 4000, E).clone()
+    W = 5 + E
+    fake = tg.header(tg.REC_SAMPLE, 8 * W)  # a value equal to a real SAMPLE header
+    s[7::W] = fake                           # value[2] of every sample
+    s[9::W] = tg.header(tg.REC_LOST, 24)
+    tail = tg.random_tail(77, ds)
+    ring, head = ring_np(s, ds, tail, fill=0)
+    desc = hbt.sampling_desc(E)
+    res = gpu_decode(ctx, [(ring, tail, head)] * 2, desc, ds)
+    want = orc.port_consume(ring, tail, head, desc)
+    check_cpu(ctx, 0, res[0], want, desc)
+    check_cpu(ctx, 1, res[1], want, desc)
+
+
+def test_unknown_types_and_giant_records(ctx):
+    """Types the guess filter rejects (>= 64) and records larger than a tile take
+    the sequential path; consume() just skips them by size."""
+    ds = 1 << 20
+    words = []
+    rng = np.random.default_rng(1)
+    total = 0
+    while total < (ds - 70000) // 8:
+        k = rng.integers(0, 10)
+        if k == 0:
+            w = int(rng.integers(2100, 8191))          # 16.8..65.5 KB record, type 1000
+            rec = [1000 | (8 * w) << 48] + [int(x) for x in rng.integers(0, 2**40, w - 1)]
+        elif k < 4:
+            w = int(rng.integers(1, 40))
+            rec = [int(rng.integers(64, 5000)) | (8 * w) << 48] + [0] * (w - 1)
+        else:
+            rec = [9 | (8 * 7) << 48, 1000 + total, 2, 5, 5, total, 2 * total]
+        words += rec
+        total += len(rec)
+    import torch
+    s = torch.tensor(np.array(words, dtype=np.uint64).view(np.int64))
+    tail = tg.random_tail(8, ds)
+    ring, head = ring_np(s, ds, tail)
+    desc = hbt.sampling_desc(2)
+    res = gpu_decode(ctx, [(ring, tail, head)], desc, ds)
+    check_cpu(ctx, 0, res[0], orc.port_consume(ring, tail, head, desc), desc)
+
+
+def test_zero_size_record_stops(ctx):
+    ds, E = 1 << 17, 8
+    s = tg.group_sample_stream(5, 800, E).clone()
+    s[(5 + E) * 600] = 9  # SAMPLE header with size 0
+    ring, head = ring_np(s, ds, 0)
+    desc = hbt.sampling_desc(E)
+    res = gpu_decode(ctx, [(ring, 0, head)], desc, ds)
+    want = orc.port_consume(ring, 0, head, desc)
+    assert want["ret"] == -74 and want["n_records"] == 600
+    check_cpu(ctx, 0, res[0], want, desc)
+
+
+@pytest.mark.parametrize("ds", [4096, 8192, 16384, 32768])
+def test_small_rings_and_empty_windows(ctx, ds):
+    E = 2
+    desc = hbt.sampling_desc(E)
+    rings = []
+    for cpu in range(4):
+        n = 0 if cpu == 1 else (ds - 256) // (8 * (5 + E) + 3)
+        s = tg.group_sample_stream(cpu + 1, max(n, 1), E, lost_every=9)
+        if n == 0:
+            s = s[:0]
+        tail = 5 * ds + 8 * 13 * cpu
+        ring, head = ring_np(s, ds, tail)
+        rings.append((ring, tail, head))
+    res = gpu_decode(ctx, rings, desc, ds)
+    for cpu, (ring, tail, head) in enumerate(rings):
+        check_cpu(ctx, cpu, res[cpu], orc.port_consume(ring, tail, head, desc), desc)
+    assert int(res[1]["ret"]) == -61 and int(res[1]["n_records"]) == 0
+
+
+def test_window_overrunning_head(ctx):
+    """head in the middle of a record: consume() still takes the record that
+    starts before head and leaves tail past head (CpuEventsGroup.h:1348,1504)."""
+    ds, E = 1 << 18, 8
+    s = tg.group_sample_stream(3, 2000, E)
+    ring, head = ring_np(s, ds, 64)
+    desc = hbt.sampling_desc(E)
+    for cut in (8, 16, 96):
+        res = gpu_decode_full_images(ctx, [(ring, 64, head - cut)], desc, ds)
+        want = orc.port_consume(ring, 64, head - cut, desc)
+        assert want["new_tail"] > head - cut or cut % 104 == 0
+        check_cpu(ctx, 0, res[0], want, desc)
+
+
+def test_device_resident_rings(ctx):
+    """hbt_submit_ring_dev: caller-owned device images (the benchmark's path)."""
+    import torch
+    ds, E, n_cpus = 1 << 20, 8, 8
+    desc = hbt.sampling_desc(E)
+    imgs = torch.zeros((n_cpus, ds // 8), dtype=torch.int64, device="cuda")
+    meta = []
+    for cpu in range(n_cpus):
+        s = tg.group_sample_stream(300 + cpu, 9000, E, device="cuda", lost_every=250)
+        tail = tg.random_tail(cpu, ds)
+        ring, head = tg.place_in_ring(s, ds, tail, fill_seed=5)
+        imgs[cpu] = ring
+        meta.append((tail, head))
+    torch.cuda.synchronize()
+    ctx.ring_configure(n_cpus, 0)
+    ctx.reset_state(hbt.INVALID_TS)
+    for cpu, (tail, head) in enumerate(meta):
+        ctx.submit_ring_dev(cpu, imgs[cpu], ds, tail, head)
+    ctx.decode(desc)
+    res = ctx.fetch_results()
+    host = imgs.cpu().numpy().view(np.uint64)
+    for cpu, (tail, head) in enumerate(meta):
+        check_cpu(ctx, cpu, res[cpu], orc.port_consume(host[cpu], tail, head, desc), desc)
