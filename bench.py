@@ -214,6 +214,8 @@ def main():
     ap.add_argument("--ring-mib", type=int, default=16)
     ap.add_argument("--ref-cpus", type=int, default=32, help="rings in the bounded CPU sample")
     ap.add_argument("--hist-slots-per-cpu", type=int, default=1 << 19)
+    ap.add_argument("--agg", default="hist", choices=["hist", "none"],
+                    help="none: decode + counters only (diagnostic, not the headline workload)")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
@@ -246,12 +248,11 @@ def main():
     ctx.ring_configure(args.cpus, 0)
     ctx.set_cpu_base(cpu_base)
     ctx.hist_configure(args.hist_slots_per_cpu * args.cpus)
-    desc = hbt.ip_desc(40)
+    desc = hbt.ip_desc(40, aggregate=hbt.AGG_IP_HISTOGRAM if args.agg == "hist" else hbt.AGG_NONE)
     counters_dev = torch.zeros(hbt.NUM_COUNTERS + 1, dtype=torch.int64, device=dev)
 
     def step():
         ctx.hist_clear()
-        ctx.reset_state(hbt.INVALID_TS) if False else None
         for c in range(args.cpus):
             ctx.submit_ring_dev(c, imgs[c], ring_bytes, tails[c], heads[c])
         ctx.decode(desc)
@@ -262,13 +263,14 @@ def main():
             dist.all_reduce(counters_dev)
 
     # ---- warm-up + validation -------------------------------------------------
-    for _ in range(max(args.warmup, 3)):
+    for it in range(max(args.warmup, 3)):
         step()
         res = ctx.fetch_results()
+        # counters are running totals since reset_state, like the reference's members
+        assert int(res["counters"][:, hbt.CNT_SAMPLE].sum()) == n_rec * (it + 1)
     total = int(res["n_records"].sum())
     assert total == n_rec, (total, n_rec)
-    assert int(res["counters"][:, hbt.CNT_SAMPLE].sum()) == n_rec
-    distinct = ctx.hist_size()
+    distinct = ctx.hist_size() if args.agg == "hist" else 0
     slow, reruns = ctx.slow_tiles, ctx.reruns
 
     # ---- timed region: device-resident ----------------------------------------

@@ -104,7 +104,7 @@ struct CpuState {  // generator state across calls
 
 struct HistTable {
   ulonglong2* slots;      // {ip, pid | count<<32}; all-zero = empty
-  uint64_t slots_per_cpu; // power of two
+  uint64_t slots_per_cpu; // any size < 2^32
   uint64_t* zero_key;     // per-CPU count of key (ip=0, pid=0)
   uint32_t* overflow;     // set when a probe sequence found no room / a count wrapped
 };
@@ -167,41 +167,38 @@ __device__ __forceinline__ int counter_of(uint32_t type, uint32_t handled) {
   }
 }
 
-// Global (cpu,pid,ip) table insert: lock-free, exact.  Slot = {ip, pid|count<<32},
-// claimed with one 128-bit CAS; the key (0,0) would look like an empty slot and
-// is counted in a per-CPU side counter instead.
+// Global (cpu,pid,ip) table insert: lock-free, exact, one L2 round trip per new
+// key.  Slot = {u64 ip; u32 pid; u32 count}; all-zero = empty.  A 128-bit CAS of
+// the empty slot to {ip, pid, n} claims it and counts in one go; when the slot is
+// taken the CAS returns its key: same key -> fire-and-forget red.add on the
+// count, other key -> next slot (linear probing inside the CPU's sub-table, so
+// probes stay in the same 128-byte line most of the time).  The key (0,0) would
+// look like an empty slot and is counted in a per-CPU side counter instead.
+// n is a signed 32-bit increment (negative while a failed attempt is taken back
+// out); counts cannot wrap because the host refuses to add more than 2^32-1
+// samples to a table between two clears.
 __device__ __forceinline__ void hist_insert_global(const HistTable& t, uint32_t cpu, uint64_t ip,
                                                    uint32_t pid, uint32_t n) {
   if (ip == 0 && pid == 0) {
-    // n is a signed 32-bit increment (-k when a failed attempt is taken back out)
     atomicAdd(reinterpret_cast<unsigned long long*>(t.zero_key + cpu),
               (unsigned long long)(long long)(int32_t)n);
     return;
   }
-  ulonglong2* base = t.slots + (uint64_t)cpu * t.slots_per_cpu;
-  const uint64_t m = t.slots_per_cpu - 1;
-  uint64_t i = mix64(ip ^ ((uint64_t)pid * 0x9E3779B97F4A7C15ull)) & m;
-  for (uint64_t probe = 0; probe <= m; ++probe, i = (i + 1) & m) {
-    ulonglong2 s = ld_relaxed_v2u64(base + i);
-    if (s.x == 0 && s.y == 0) {
-      uint64_t olo, ohi;
-      cas128_global(base + i, 0, 0, ip, (uint64_t)pid, olo, ohi);
-      if (olo == 0 && ohi == 0) {
-        s.x = ip;
-        s.y = pid;
-      } else {
-        s.x = olo;
-        s.y = ohi;
-      }
-    }
-    if (s.x == ip && (uint32_t)s.y == pid) {
-      uint32_t* cnt = reinterpret_cast<uint32_t*>(base + i) + 3;
-      const uint32_t old = atomicAdd(cnt, n);
-      if ((int32_t)n > 0 && old + n < old) atomicExch(t.overflow, 2u);  // 32-bit count wrapped
+  const uint64_t S = t.slots_per_cpu;
+  ulonglong2* base = t.slots + (uint64_t)cpu * S;
+  const uint32_t h = (uint32_t)(mix64(ip ^ ((uint64_t)pid * 0x9E3779B97F4A7C15ull)) >> 32);
+  uint64_t i = ((uint64_t)h * S) >> 32;
+  for (uint64_t probe = 0; probe < S; ++probe) {
+    uint64_t olo, ohi;
+    cas128_global(base + i, 0, 0, ip, (uint64_t)pid | ((uint64_t)n << 32), olo, ohi);
+    if (olo == 0 && ohi == 0) return;  // claimed, count = n
+    if (olo == ip && (uint32_t)ohi == pid) {
+      red_add_u32(reinterpret_cast<uint32_t*>(base + i) + 3, n);
       return;
     }
+    i = (i + 1 == S) ? 0 : i + 1;
   }
-  atomicExch(t.overflow, 1u);  // table full
+  atomicExch(t.overflow, 1u);  // the CPU's sub-table is full
 }
 
 // ---------------------------------------------------------------------------
@@ -218,20 +215,17 @@ struct SegState {
   uint64_t err_pos;
   int32_t err;
   uint32_t slow_tiles;
-  uint32_t anomaly;   // per-tile flag
   uint32_t guess_min; // per-tile: smallest guessed entry (tile-relative), segment start only
+  uint32_t tile_x;    // per-tile: where the record chain left the tile (tile-relative)
 };
 
-// In-CTA privatised (pid,ip) table for one segment: open addressing, 16-byte
-// slots {ip, pid | count<<32}, state word per slot (0 empty, 1 being written, 2 ready).
-constexpr int kHistSlots = 2048;
-constexpr int kHistProbes = 4;
+constexpr uint32_t kNoRel = 0xFFFFFFFFu;  // "no tile-relative position"
 
 struct Smem {
   uint64_t bar[kStages];
   SegState st;
-  int32_t warp_x[kThreads / 32];
-  uint64_t warp_ev[kThreads / 32];
+  uint32_t expect[kThreads];  // expect[j]: a record was seen to start at this offset of sub-chunk j
+  uint32_t warp_ev[kThreads / 32];
   uint32_t warp_rows[kThreads / 32];
   uint32_t warp_ls[kThreads / 32];  // last SAMPLE start in the tile, relative + 1
 };
@@ -334,41 +328,51 @@ __device__ void consume_sequential(const DecodeParams& p, const RingDesc& ring,
   st.pos = pos;
 }
 
-// Word of the stream at absolute position `pos`, from the staged tiles when
-// resident (tile `t` in stage sa, tile t+1 in stage sb), else from global.
+// The staged bytes of tile `t` (stage a) and tile t+1 (stage b) addressed by
+// 32-bit tile-relative offsets: all hot-loop arithmetic is 32-bit.
 struct TileView {
-  const uint8_t* sa;
-  const uint8_t* sb;
-  uint64_t t_begin;  // absolute position of the tile start
+  uint32_t sa;  // shared-space address of tile t
+  uint32_t sb;  // shared-space address of tile t+1, minus kTile
+  uint64_t t_begin;
   const RingDesc* ring;
-  __device__ __forceinline__ uint64_t word(uint64_t pos) const {
+  // rel in [0, 2*kTile)
+  __device__ __forceinline__ uint64_t at(uint32_t rel) const {
+    return lds_u64((rel < (uint32_t)kTile ? sa : sb) + rel);
+  }
+  // any absolute position (older tiles / carry live in global memory)
+  __device__ __forceinline__ uint64_t word_abs(uint64_t pos) const {
     const uint64_t off = pos - t_begin;  // wraps for pos < t_begin -> huge
-    if (off < (uint64_t)kTile) return *reinterpret_cast<const uint64_t*>(sa + off);
-    if (off < 2ull * kTile) return *reinterpret_cast<const uint64_t*>(sb + (off - kTile));
+    if (off < 2ull * kTile) return at((uint32_t)off);
     return ring_word_g(*ring, pos);
   }
-  // same, for positions known to be inside [t_begin, t_begin + 2*kTile)
-  __device__ __forceinline__ uint64_t word_in(uint64_t pos) const {
-    const uint64_t off = pos - t_begin;
-    return *reinterpret_cast<const uint64_t*>((off < (uint64_t)kTile ? sa : sb - kTile) + off);
-  }
 };
+
+// First word (tile-relative, in 8-byte words) of sub-chunk j.  The skew spreads
+// the lock-step header scan of a warp over all shared-memory banks.
+__device__ __forceinline__ uint32_t sub_begin_word(uint32_t j) {
+  return kSubWords * j + ((j >> 1) & 7);
+}
+// Sub-chunk that holds tile word w.
+__device__ __forceinline__ uint32_t sub_of_word(uint32_t w) {
+  const uint32_t j = w >> 3;
+  return w < sub_begin_word(j) ? j - 1 : j;
+}
 
 template <int AGG>
 __global__ void __launch_bounds__(kThreads) k_decode(const DecodeParams p) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   uint8_t* stages = smem_raw;  // kStages * kTile
   Smem& sm = *reinterpret_cast<Smem*>(smem_raw + kStages * kTile);
-  // HIST: privatised table after Smem
-  ulonglong2* h_slots = reinterpret_cast<ulonglong2*>(
-      smem_raw + kStages * kTile + ((sizeof(Smem) + 15) & ~15ull));
-  uint32_t* h_state = reinterpret_cast<uint32_t*>(h_slots + kHistSlots);
 
   const SegDesc seg = p.segs[blockIdx.x];
   const RingDesc ring = p.rings[seg.cpu];
   const hbt_decode_desc& d = p.d;
   const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   SegState& st = sm.st;
+  const bool h_sample = (d.handled_mask & HBT_H_SAMPLE) != 0;
+  const bool h_read = (d.handled_mask & HBT_H_READ) != 0;
+  const bool h_lost = (d.handled_mask & HBT_H_LOST) != 0;
+  const bool group_layout = d.sample_layout == HBT_SAMPLE_GROUP;
 
   if (tid == 0) {
     for (int s = 0; s < kStages; ++s) mbar_init(&sm.bar[s], 1);
@@ -383,27 +387,23 @@ __global__ void __launch_bounds__(kThreads) k_decode(const DecodeParams p) {
     st.err = 0;
     st.err_pos = 0;
     st.slow_tiles = 0;
-    st.anomaly = 0;
-    st.guess_min = 0xFFFFFFFFu;
+    st.guess_min = kNoRel;
+    st.tile_x = kNoRel;
   }
-  if (AGG == HBT_AGG_IP_HISTOGRAM) {
-    for (int i = tid; i < kHistSlots; i += kThreads) {
-      h_slots[i] = make_ulonglong2(0, 0);
-      h_state[i] = 0;
-    }
-  }
+  sm.expect[tid] = kNoRel;
   __syncthreads();
 
   const uint64_t n_tiles = seg.tile_end - seg.tile_begin;
   // Records are decoded while they START before seg_limit.
   const uint64_t seg_limit = min(seg.tile_end * (uint64_t)kTile, ring.head);
+  const uint64_t policy = l2_policy_evict_first();
 
   auto issue = [&](uint64_t k) {  // tile k of this segment (k == n_tiles: lookahead tile)
     const uint64_t t = seg.tile_begin + k;
     const int s = (int)(t % kStages);
     mbar_arrive_expect_tx(&sm.bar[s], kTile);
-    bulk_g2s(stages + s * kTile, ring.base + ((t * (uint64_t)kTile) & ring.mask), kTile,
-             &sm.bar[s]);
+    bulk_g2s_hint(stages + s * kTile, ring.base + ((t * (uint64_t)kTile) & ring.mask), kTile,
+                  &sm.bar[s], policy);
   };
   if (tid == 0) {
     issue(0);
@@ -412,7 +412,11 @@ __global__ void __launch_bounds__(kThreads) k_decode(const DecodeParams p) {
   uint32_t phase_bits = 0;  // mbarrier parity per stage
 
   // thread-local totals over the fast-path tiles (added to st in the epilogue)
-  unsigned long long my_rec = 0, my_sample = 0;
+  uint32_t my_rec = 0, my_sample = 0;
+
+  // my sub-chunk, in tile-relative bytes
+  const uint32_t sb = 8u * sub_begin_word(tid);
+  const uint32_t se_full = tid == kThreads - 1 ? (uint32_t)kTile : 8u * sub_begin_word(tid + 1);
 
   for (uint64_t k = 0; k < n_tiles; ++k) {
     const uint64_t t = seg.tile_begin + k;
@@ -427,64 +431,72 @@ __global__ void __launch_bounds__(kThreads) k_decode(const DecodeParams p) {
     mbar_wait(&sm.bar[sb_i], (phase_bits >> sb_i) & 1);
     phase_bits ^= 1u << sb_i;
 
-    TileView tv{stages + sa_i * kTile, stages + sb_i * kTile, t * (uint64_t)kTile, &ring};
-    const uint64_t t_begin = tv.t_begin;
-    const uint64_t t_end = min(t_begin + kTile, seg_limit);  // record starts must be < t_end
-    const uint64_t look_end = t_begin + 2ull * kTile;        // end of the resident bytes
-    const uint64_t entry = st.pos;                           // exact, or kNone (still guessing)
+    const uint64_t t_begin = t * (uint64_t)kTile;
+    TileView tv{smem_u32(stages + sa_i * kTile), smem_u32(stages + sb_i * kTile) - (uint32_t)kTile,
+                t_begin, &ring};
+    // tile-uniform limits, tile-relative: record starts must be < lim; bytes up to
+    // look (< 2*kTile) are resident and inside the window
+    const uint32_t lim = seg_limit > t_begin ? (uint32_t)min((uint64_t)kTile, seg_limit - t_begin) : 0u;
+    const uint32_t look =
+        ring.head > t_begin ? (uint32_t)min((uint64_t)(2 * kTile), ring.head - t_begin) : 0u;
+    const uint64_t entry_abs = st.pos;  // exact, or kNone while the segment still guesses
     const bool stopped = st.err != 0;
+    // entry relative to the tile: kNoRel = unknown, >= kTile = beyond this tile
+    uint32_t erel;
+    if (entry_abs == kNone) erel = kNoRel;
+    else erel = (uint32_t)min(entry_abs - t_begin, (uint64_t)0x7FFFFFFFu);  // entry_abs >= t_begin
 
-    // ---- phase 1: guess + walk over the own sub-chunk -------------------------
-    // sub-chunk j = tile words [8j + skew(j), 8(j+1) + skew(j+1)); the skew spreads
-    // the lock-step header scan over all shared-memory banks.
-    const uint32_t skew0 = (tid >> 1) & 7, skew1 = ((tid + 1) >> 1) & 7;
-    const uint64_t sb = t_begin + 8ull * (kSubWords * tid + skew0);
-    uint64_t se = t_begin + 8ull * (kSubWords * (tid + 1) + (tid == kThreads - 1 ? 0 : skew1));
-    se = min(se, t_end);
+    // ---- phase 1: guess + walk over the own sub-chunk ---------------------------
+    const uint32_t se = min(se_full, lim);
     const bool live = !stopped && sb < se;
-
-    uint64_t my_entry = kNone;  // first record start in my sub-chunk
+    uint32_t my_entry = kNoRel;  // first record start in my sub-chunk
+    bool owner = false;          // my_entry is the tile's exact entry
     if (live) {
-      if (entry != kNone && entry >= sb) {
-        if (entry < se) my_entry = entry;  // the tile's exact entry lies in my sub-chunk
+      if (erel != kNoRel && erel >= sb) {
+        if (erel < se) {
+          my_entry = erel;
+          owner = true;
+        }
       } else {
-        for (uint64_t q = sb; q < se; q += 8) {
-          const uint64_t h = tv.word_in(q);
+#pragma unroll 1
+        for (uint32_t q = sb; q < se; q += 8) {
+          const uint64_t h = tv.at(q);
           if (!plausible(h)) continue;
-          const uint64_t q2 = q + hdr_size(h);
-          if (q2 < look_end && q2 < ring.head && !plausible(tv.word_in(q2))) continue;
+          const uint32_t q2 = q + hdr_size(h);
+          if (q2 < look && !plausible(tv.at(q2))) continue;
           my_entry = q;
           break;
         }
       }
     }
-    uint32_t mask = 0;  // bit w: a record starts at sb + 8w
-    int32_t my_x = -1;  // where my walk left the sub-chunk, relative to t_begin
+    uint32_t mask = 0;        // bit w: a record starts at sb + 8w
+    uint32_t my_x = kNoRel;   // where my walk left the sub-chunk
     bool bad = false;
-    uint64_t first_ev = 0, last_ev = 0;
-    uint32_t my_ls = 0;  // last SAMPLE start, relative + 1
+    uint32_t first_ev = 0, last_ev = 0;  // tile-relative encoded events ((rel+1)<<2 | kind)
+    uint32_t my_ls = 0;                  // last SAMPLE start, relative + 1
     uint32_t rows_local = 0, unknown_local = 0;
     uint64_t prev_ts = 0;
-    if (my_entry != kNone) {
-      uint64_t pos = my_entry;
+    if (my_entry != kNoRel) {
+      uint32_t pos = my_entry;
+#pragma unroll 1
       while (pos < se) {
-        const uint64_t h = tv.word_in(pos);
+        const uint64_t h = tv.at(pos);
         const uint32_t type = hdr_type(h), size = hdr_size(h);
-        if (size < 8 || (size & 7) || pos + size > look_end) {
+        if (size < 8 || (size & 7) || pos + size > 2u * kTile) {
           bad = true;
           break;
         }
-        if (type == REC_SAMPLE && (d.handled_mask & HBT_H_SAMPLE)) {
-          if (d.sample_layout == HBT_SAMPLE_GROUP) {
-            const uint64_t nr = tv.word_in(pos + 16);
+        if (type == REC_SAMPLE && h_sample) {
+          if (group_layout) {
+            const uint64_t nr = tv.at(pos + 16);
             if ((uint64_t)size != 40 + 8 * nr ||
                 (AGG == HBT_AGG_COUNT_DELTAS && nr != d.n_events)) {
               bad = true;
               break;
             }
             if (AGG == HBT_AGG_COUNT_DELTAS) {
-              const uint64_t ts = tv.word_in(pos + 8);
-              const uint32_t lk = ev_kind(last_ev);
+              const uint64_t ts = tv.at(pos + 8);
+              const uint32_t lk = last_ev & 3;
               if (lk == EV_SAMPLE) {
                 if (prev_ts > ts) {
                   bad = true;
@@ -494,96 +506,90 @@ __global__ void __launch_bounds__(kThreads) k_decode(const DecodeParams p) {
               } else if (lk == EV_LOST) {
                 ++unknown_local;
               }
-              last_ev = ev_make(pos, EV_SAMPLE);
+              last_ev = ((pos + 1) << 2) | EV_SAMPLE;
               if (first_ev == 0) first_ev = last_ev;
-              my_ls = (uint32_t)(pos - t_begin) + 1;
+              my_ls = pos + 1;
               prev_ts = ts;
             }
           } else if (size != d.ip_sample_bytes) {
             bad = true;
             break;
           }
-        } else if (type == REC_READ && (d.handled_mask & HBT_H_READ)) {
-          if ((uint64_t)size != 40 + 8 * tv.word_in(pos + 16)) {
+        } else if (type == REC_READ && h_read) {
+          if ((uint64_t)size != 40 + 8 * tv.at(pos + 16)) {
             bad = true;
             break;
           }
-        } else if (AGG == HBT_AGG_COUNT_DELTAS && type == REC_LOST &&
-                   (d.handled_mask & HBT_H_LOST)) {
-          last_ev = ev_make(pos, EV_LOST);
+        } else if (AGG == HBT_AGG_COUNT_DELTAS && type == REC_LOST && h_lost) {
+          last_ev = ((pos + 1) << 2) | EV_LOST;
           if (first_ev == 0) first_ev = last_ev;
         }
-        mask |= 1u << (uint32_t)((pos - sb) >> 3);
+        mask |= 1u << ((pos - sb) >> 3);
         pos += size;
       }
-      my_x = (int32_t)(pos - t_begin);
-    }
-
-    // ---- phase 2: verify the guesses with a block-wide max-scan ----------------
-    // At a segment start without a known entry the smallest guess is the entry guess.
-    if (entry == kNone && my_entry != kNone)
-      atomicMin(&st.guess_min, (uint32_t)(my_entry - t_begin));
-    int32_t sx = my_x;
-    uint64_t sev = last_ev;
-#pragma unroll
-    for (int o = 1; o < 32; o <<= 1) {
-      const int32_t ox = __shfl_up_sync(0xffffffffu, sx, o);
-      const uint64_t oe = __shfl_up_sync(0xffffffffu, sev, o);
-      if (lane >= o) {
-        sx = max(sx, ox);
-        sev = max(sev, oe);
+      my_x = pos;
+      // tell the sub-chunk the chain continues in what it should have found
+      if (!bad) {
+        if (pos < lim) sm.expect[sub_of_word(pos >> 3)] = pos;
+        else st.tile_x = pos;
       }
     }
-    const uint32_t wls = __reduce_max_sync(0xffffffffu, my_ls);
-    if (lane == 31) {
-      sm.warp_x[warp] = sx;
-      sm.warp_ev[warp] = sev;
-      sm.warp_ls[warp] = wls;
+    // At a segment start without a known entry the smallest guess is the entry guess.
+    if (erel == kNoRel && my_entry != kNoRel) atomicMin(&st.guess_min, my_entry);
+
+    // DELTAS: interval state needs the last event / row count before my sub-chunk
+    uint32_t sev = last_ev;
+    if (AGG == HBT_AGG_COUNT_DELTAS) {
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        const uint32_t oe = __shfl_up_sync(0xffffffffu, sev, o);
+        if (lane >= o) sev = max(sev, oe);
+      }
+      const uint32_t wls = __reduce_max_sync(0xffffffffu, my_ls);
+      if (lane == 31) {
+        sm.warp_ev[warp] = sev;
+        sm.warp_ls[warp] = wls;
+      }
     }
-    __syncthreads();
-    const uint64_t tile_entry =
-        entry != kNone ? entry
-                       : (st.guess_min != 0xFFFFFFFFu ? t_begin + st.guess_min : kNone);
-    int32_t px = __shfl_up_sync(0xffffffffu, sx, 1);  // exclusive prefixes
-    uint64_t pev = __shfl_up_sync(0xffffffffu, sev, 1);
-    if (lane == 0) {
-      px = -1;
-      pev = 0;
-    }
-    for (uint32_t w = 0; w < warp; ++w) {
-      px = max(px, sm.warp_x[w]);
-      pev = max(pev, sm.warp_ev[w]);
-    }
-    // position the record chain has reached before my sub-chunk
-    uint64_t reach = kNone;  // kNone: unknown (segment start and no guess yet)
-    if (tile_entry != kNone) {
-      reach = tile_entry;
-      if (px >= 0) reach = max(reach, t_begin + (uint64_t)px);
-    }
-    if (live) {
-      if (my_entry == kNone) {
-        if (reach != kNone && reach < se) bad = true;  // a start in (or before) my range
-      } else if (reach != my_entry) {
+    __syncthreads();  // A: expect[], tile_x, guess_min, warp_ev are complete
+
+    // ---- phase 2: every guess must be what the chain before it predicted --------
+    if (erel == kNoRel && my_entry != kNoRel && my_entry == st.guess_min) owner = true;
+    {
+      const uint32_t exp = sm.expect[tid];
+      sm.expect[tid] = kNoRel;  // only I read my slot: reset it for the next tile
+      if (live) {
+        if (owner) {
+          if (exp != kNoRel && exp != my_entry) bad = true;
+        } else if (exp != my_entry) {
+          bad = true;  // missed a start, or guessed one the chain does not reach
+        }
+      } else if (exp != kNoRel && !stopped) {
         bad = true;
       }
     }
     // interval state in front of my first SAMPLE
-    const uint64_t in_ev0 = max(st.ev, pev);
+    uint64_t in_ev0 = 0;  // absolute encoding
     uint32_t rows_j = rows_local, unknown_j = unknown_local;
     bool pending_seam = false;
-    if (AGG == HBT_AGG_COUNT_DELTAS && ev_kind(first_ev) == EV_SAMPLE) {
-      const uint32_t ik = ev_kind(in_ev0);
-      if (ik == EV_SAMPLE) {
-        if (tv.word(ev_pos(in_ev0) + 8) > tv.word_in(ev_pos(first_ev) + 8)) bad = true;
-        ++rows_j;
-      } else if (ik == EV_LOST) {
-        ++unknown_j;
-      } else {
-        pending_seam = true;  // resolved by k_finalize
-      }
-    }
-    uint32_t srow = rows_j;
+    uint32_t srow = 0;
     if (AGG == HBT_AGG_COUNT_DELTAS) {
+      uint32_t pev = __shfl_up_sync(0xffffffffu, sev, 1);
+      if (lane == 0) pev = 0;
+      for (uint32_t w = 0; w < warp; ++w) pev = max(pev, sm.warp_ev[w]);
+      in_ev0 = pev ? ev_make(t_begin + (pev >> 2) - 1, pev & 3) : st.ev;
+      if ((first_ev & 3) == EV_SAMPLE) {
+        const uint32_t ik = ev_kind(in_ev0);
+        if (ik == EV_SAMPLE) {
+          if (tv.word_abs(ev_pos(in_ev0) + 8) > tv.at((first_ev >> 2) - 1 + 8)) bad = true;
+          ++rows_j;
+        } else if (ik == EV_LOST) {
+          ++unknown_j;
+        } else {
+          pending_seam = true;  // resolved by k_finalize
+        }
+      }
+      srow = rows_j;
 #pragma unroll
       for (int o = 1; o < 32; o <<= 1) {
         const uint32_t orow = __shfl_up_sync(0xffffffffu, srow, o);
@@ -591,146 +597,107 @@ __global__ void __launch_bounds__(kThreads) k_decode(const DecodeParams p) {
       }
       if (lane == 31) sm.warp_rows[warp] = srow;
     }
-    if (bad) st.anomaly = 1;
-    __syncthreads();
-    const bool slow = st.anomaly != 0;
+    const bool slow = __syncthreads_or(bad) != 0;  // B
 
     if (!stopped && !slow) {
-      // ---- phase 3: aggregate my records --------------------------------------
-      uint64_t row_i = st.n_rows + (srow - rows_j);
-      if (AGG == HBT_AGG_COUNT_DELTAS)
-        for (uint32_t w = 0; w < warp; ++w) row_i += sm.warp_rows[w];
+      // ---- phase 3: aggregate my records ----------------------------------------
+      if (tid == 0) {
+        // chain bookkeeping for the next tile, overlapped with the other threads' work
+        uint32_t e = erel != kNoRel ? erel : st.guess_min;
+        if (e != kNoRel) {
+          if (st.entry == kNone && e < lim) st.entry = t_begin + e;
+          if (st.tile_x != kNoRel) st.pos = t_begin + st.tile_x;
+          else if (erel == kNoRel) st.pos = t_begin + e;  // cannot happen: a guess always walks
+        }
+        st.tile_x = kNoRel;
+        st.guess_min = kNoRel;
+      }
+      uint64_t row_i = 0;
       uint64_t in_ev = in_ev0;
+      if (AGG == HBT_AGG_COUNT_DELTAS) {
+        row_i = st.n_rows + (srow - rows_j);
+        for (uint32_t w = 0; w < warp; ++w) row_i += sm.warp_rows[w];
+      }
       unsigned long long lost_sum = 0;
       uint32_t m = mask;
+      my_rec += __popc(m);
       while (m) {
         const uint32_t w = __ffs(m) - 1;
         m &= m - 1;
-        const uint64_t pos = sb + 8ull * w;
-        const uint64_t h = tv.word_in(pos);
+        const uint32_t pos = sb + 8u * w;
+        const uint64_t h = tv.at(pos);
         const uint32_t type = hdr_type(h);
-        ++my_rec;
-        if (type == REC_SAMPLE && (d.handled_mask & HBT_H_SAMPLE)) {
+        if (type == REC_SAMPLE && h_sample) {
           ++my_sample;
           if (AGG == HBT_AGG_IP_HISTOGRAM) {
-            const uint64_t ip = tv.word_in(pos + 8);
-            const uint32_t pid = (uint32_t)tv.word_in(pos + 16);
-            bool done = false;
-            if (!(ip == 0 && pid == 0)) {
-              uint32_t i = (uint32_t)mix64(ip ^ ((uint64_t)pid * 0x9E3779B97F4A7C15ull)) &
-                           (kHistSlots - 1);
-#pragma unroll 1
-              for (int pr = 0; pr < kHistProbes; ++pr, i = (i + 1) & (kHistSlots - 1)) {
-                uint32_t s = *reinterpret_cast<volatile uint32_t*>(h_state + i);
-                if (s == 0) {
-                  s = atomicCAS(h_state + i, 0u, 1u);
-                  if (s == 0) {  // claimed: publish the key, count = 1
-                    h_slots[i].x = ip;
-                    atomicAdd(reinterpret_cast<unsigned long long*>(&h_slots[i].y),
-                              (unsigned long long)pid | (1ull << 32));
-                    __threadfence_block();
-                    *reinterpret_cast<volatile uint32_t*>(h_state + i) = 2;
-                    done = true;
-                    break;
-                  }
-                }
-                if (s != 2) break;  // being written by another thread: count globally
-                const volatile ulonglong2* vs = h_slots + i;
-                if (vs->x == ip && (uint32_t)vs->y == pid) {
-                  atomicAdd(reinterpret_cast<unsigned long long*>(&h_slots[i].y), 1ull << 32);
-                  done = true;
-                  break;
-                }
-              }
-            }
-            if (!done) hist_insert_global(p.hist, seg.cpu, ip, pid, p.hist_inc);
+            hist_insert_global(p.hist, seg.cpu, tv.at(pos + 8), (uint32_t)tv.at(pos + 16),
+                               p.hist_inc);
           } else if (AGG == HBT_AGG_COUNT_DELTAS) {
             if (ev_kind(in_ev) == EV_SAMPLE) {
               const uint64_t ppos = ev_pos(in_ev);
-              const uint64_t pts = tv.word(ppos + 8);
-              const uint64_t ts = tv.word_in(pos + 8);
+              const uint64_t pts = tv.word_abs(ppos + 8);
+              const uint64_t ts = tv.at(pos + 8);
               uint64_t* row = seg.rows + (1 + row_i) * (2 + (uint64_t)d.n_events);
               row[0] = pts;
               row[1] = ts - pts;
               for (uint32_t i = 0; i < d.n_events; ++i) {
-                const uint64_t v = xform(d, i, tv.word_in(pos + 40 + 8ull * i));
-                const uint64_t pv = xform(d, i, tv.word(ppos + 40 + 8ull * i));
+                const uint64_t v = xform(d, i, tv.at(pos + 40 + 8 * i));
+                const uint64_t pv = xform(d, i, tv.word_abs(ppos + 40 + 8ull * i));
                 row[2 + i] = v - pv;
               }
               ++row_i;
             }
-            in_ev = ev_make(pos, EV_SAMPLE);
+            in_ev = ev_make(t_begin + pos, EV_SAMPLE);
           }
         } else {
           const int ci = counter_of(type, d.handled_mask);
           if (ci == HBT_CNT_LOST) {
-            lost_sum += tv.word_in(pos + 16);
-            if (AGG == HBT_AGG_COUNT_DELTAS) in_ev = ev_make(pos, EV_LOST);
+            lost_sum += tv.at(pos + 16);
+            if (AGG == HBT_AGG_COUNT_DELTAS) in_ev = ev_make(t_begin + pos, EV_LOST);
           } else if (ci >= 0) {
             atomicAdd(&st.counters[ci], 1ull);
           }
         }
       }
       if (lost_sum) atomicAdd(&st.counters[HBT_CNT_LOST], lost_sum);
-      if (unknown_j) atomicAdd(&st.n_unknown, (unsigned long long)unknown_j);
-      if (pending_seam) st.first_ev = first_ev;  // at most one thread per segment
-    }
-    __syncthreads();
-    if (tid == 0) {
-      if (!stopped) {
-        if (slow) {
-          // literal consume() over this tile by one thread
-          ++st.slow_tiles;
-          if (st.pos == kNone && st.guess_min != 0xFFFFFFFFu) st.pos = t_begin + st.guess_min;
-          if (st.pos != kNone) consume_sequential<AGG>(p, ring, seg, st, t_end);
-        } else {
-          if (tile_entry != kNone) {
-            int32_t all_x = -1;
-            for (uint32_t w = 0; w < kThreads / 32; ++w) all_x = max(all_x, sm.warp_x[w]);
-            uint64_t np = tile_entry;
-            if (all_x >= 0) np = max(np, t_begin + (uint64_t)all_x);
-            if (st.entry == kNone && tile_entry < t_end) st.entry = tile_entry;
-            st.pos = np;
-          }
-          uint64_t tev = 0;
-          uint32_t trows = 0, tls = 0;
-          for (uint32_t w = 0; w < kThreads / 32; ++w) {
-            tev = max(tev, sm.warp_ev[w]);
-            tls = max(tls, sm.warp_ls[w]);
-            if (AGG == HBT_AGG_COUNT_DELTAS) trows += sm.warp_rows[w];
-          }
-          st.ev = max(st.ev, tev);
-          if (tls) st.last_sample = t_begin + tls - 1;
-          st.n_rows += trows;
-        }
+      if (AGG == HBT_AGG_COUNT_DELTAS) {
+        if (unknown_j) atomicAdd(&st.n_unknown, (unsigned long long)unknown_j);
+        if (pending_seam) st.first_ev = ev_make(t_begin + (first_ev >> 2) - 1, EV_SAMPLE);
       }
-      st.anomaly = 0;
-      st.guess_min = 0xFFFFFFFFu;
+    }
+    if (AGG == HBT_AGG_COUNT_DELTAS) __syncthreads();  // row_i readers before n_rows moves
+    if (tid == 0 && !stopped) {
+      if (slow) {
+        // literal consume() over this tile by one thread
+        ++st.slow_tiles;
+        if (st.pos == kNone && st.guess_min != kNoRel) st.pos = t_begin + st.guess_min;
+        if (st.pos != kNone) consume_sequential<AGG>(p, ring, seg, st, t_begin + lim);
+        st.tile_x = kNoRel;
+        st.guess_min = kNoRel;
+      } else if (AGG == HBT_AGG_COUNT_DELTAS) {
+        uint32_t tev = 0, trows = 0, tls = 0;
+        for (uint32_t w = 0; w < kThreads / 32; ++w) {
+          tev = max(tev, sm.warp_ev[w]);
+          tls = max(tls, sm.warp_ls[w]);
+          trows += sm.warp_rows[w];
+        }
+        if (tev) st.ev = ev_make(t_begin + (tev >> 2) - 1, tev & 3);
+        if (tls) st.last_sample = t_begin + tls - 1;
+        st.n_rows += trows;
+      }
     }
     // every generic-proxy read of stage (t % kStages) is ordered before the bulk
     // copy that thread 0 issues into it after this barrier
     fence_proxy_async();
-    __syncthreads();
+    __syncthreads();  // C
   }
 
   // ---- segment epilogue --------------------------------------------------------
-#pragma unroll
-  for (int o = 16; o > 0; o >>= 1) {
-    my_rec += __shfl_xor_sync(0xffffffffu, my_rec, o);
-    my_sample += __shfl_xor_sync(0xffffffffu, my_sample, o);
-  }
+  my_rec = __reduce_add_sync(0xffffffffu, my_rec);
+  my_sample = __reduce_add_sync(0xffffffffu, my_sample);
   if (lane == 0) {
-    atomicAdd(&st.n_rec, my_rec);
-    atomicAdd(&st.counters[HBT_CNT_SAMPLE], my_sample);
-  }
-  if (AGG == HBT_AGG_IP_HISTOGRAM) {
-    for (int i = tid; i < kHistSlots; i += kThreads) {
-      if (h_state[i] == 2) {
-        const ulonglong2 s = h_slots[i];
-        hist_insert_global(p.hist, seg.cpu, s.x, (uint32_t)s.y,
-                           (uint32_t)(s.y >> 32) * p.hist_inc);
-      }
-    }
+    atomicAdd(&st.n_rec, (unsigned long long)my_rec);
+    atomicAdd(&st.counters[HBT_CNT_SAMPLE], (unsigned long long)my_sample);
   }
   __syncthreads();
   if (tid == 0) {

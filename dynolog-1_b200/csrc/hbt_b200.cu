@@ -160,9 +160,8 @@ int cuda_fail(hbt_ctx* c, cudaError_t e, const char* what) {
 bool is_pow2(uint64_t x) { return x && !(x & (x - 1)); }
 
 size_t decode_smem_bytes(int agg) {
-  size_t s = (size_t)kStages * kTile + ((sizeof(Smem) + 15) & ~size_t(15));
-  if (agg == HBT_AGG_IP_HISTOGRAM) s += (size_t)kHistSlots * (16 + 4);
-  return s;
+  (void)agg;
+  return (size_t)kStages * kTile + ((sizeof(Smem) + 15) & ~size_t(15));
 }
 
 int validate_desc(hbt_ctx* ctx, const hbt_decode_desc* d) {
