@@ -17,7 +17,7 @@ import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 REPO_ROOT = os.path.dirname(_HERE)
-LIB_PATH = os.path.join(_HERE, "libhbt_b200.so")
+LIB_PATH = os.environ.get("HBT_B200_LIB") or os.path.join(_HERE, "libhbt_b200.so")  # env: tuning builds
 
 # ---- constants of include/hbt_b200.h -------------------------------------------
 ABI_VERSION = 1
@@ -87,6 +87,7 @@ EXPORTS = [
     ("hbt_ring_configure", C.c_int, [_P, C.c_uint32, C.c_uint64]),
     ("hbt_submit_ring", C.c_int, [_P, C.c_uint32, _P, C.c_size_t, _P, C.c_size_t, C.c_uint64]),
     ("hbt_submit_ring_dev", C.c_int, [_P, C.c_uint32, _P, C.c_uint64, C.c_uint64, C.c_uint64]),
+    ("hbt_submit_rings_dev", C.c_int, [_P, C.c_uint32, _P, C.c_uint64, _P, _P]),
     ("hbt_ring_reset_state", C.c_int, [_P, C.c_uint64]),
     ("hbt_decode", C.c_int, [_P, C.POINTER(DecodeDesc)]),
     ("hbt_fetch_results", C.c_int, [_P, _P, C.c_uint32]),
@@ -234,6 +235,12 @@ class Context:
 
     def submit_ring_dev(self, cpu: int, ring_ptr, data_size: int, tail: int, head: int):
         self._ck(self.lib.hbt_submit_ring_dev(self.h, cpu, _ptr(ring_ptr), data_size, tail, head))
+
+    def submit_rings_dev(self, bases: np.ndarray, data_size: int, tails: np.ndarray,
+                         heads: np.ndarray):
+        """bases/tails/heads: uint64 numpy arrays (device pointers, windows)."""
+        self._ck(self.lib.hbt_submit_rings_dev(self.h, len(bases), _ptr(bases), data_size,
+                                               _ptr(tails), _ptr(heads)))
 
     def reset_state(self, seed_tstamp: int = INVALID_TS):
         self._ck(self.lib.hbt_ring_reset_state(self.h, seed_tstamp))

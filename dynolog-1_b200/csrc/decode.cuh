@@ -106,7 +106,8 @@ struct HistTable {
   ulonglong2* slots;      // {ip, pid | count<<32}; all-zero = empty
   uint64_t slots_per_cpu; // any size < 2^32
   uint64_t* zero_key;     // per-CPU count of key (ip=0, pid=0)
-  uint32_t* overflow;     // set when a probe sequence found no room / a count wrapped
+  uint32_t* overflow;     // set when a probe sequence found no room
+  uint32_t* arrive;       // per-CPU: CTAs that finished zeroing their slice (zero_first)
 };
 
 struct DecodeParams {
@@ -117,6 +118,7 @@ struct DecodeParams {
   hbt_decode_desc d;
   HistTable hist;
   uint32_t hist_inc;  // +1, or 0xFFFFFFFF to take a failed attempt back out
+  uint32_t hist_zero_first;  // the table is cleared by this launch (lazy hbt_hist_clear)
 };
 
 // ---------------------------------------------------------------------------
@@ -177,17 +179,16 @@ __device__ __forceinline__ int counter_of(uint32_t type, uint32_t handled) {
 // n is a signed 32-bit increment (negative while a failed attempt is taken back
 // out); counts cannot wrap because the host refuses to add more than 2^32-1
 // samples to a table between two clears.
-__device__ __forceinline__ void hist_insert_global(const HistTable& t, uint32_t cpu, uint64_t ip,
-                                                   uint32_t pid, uint32_t n) {
-  if (ip == 0 && pid == 0) {
-    atomicAdd(reinterpret_cast<unsigned long long*>(t.zero_key + cpu),
-              (unsigned long long)(long long)(int32_t)n);
-    return;
-  }
+__device__ __forceinline__ uint64_t hist_home_slot(const HistTable& t, uint64_t ip, uint32_t pid) {
+  const uint32_t h = (uint32_t)(mix64(ip ^ ((uint64_t)pid * 0x9E3779B97F4A7C15ull)) >> 32);
+  return ((uint64_t)h * t.slots_per_cpu) >> 32;
+}
+
+// Probe from slot i on until the key is counted.
+__device__ __noinline__ void hist_probe_from(const HistTable& t, uint32_t cpu, uint64_t i,
+                                             uint64_t ip, uint32_t pid, uint32_t n) {
   const uint64_t S = t.slots_per_cpu;
   ulonglong2* base = t.slots + (uint64_t)cpu * S;
-  const uint32_t h = (uint32_t)(mix64(ip ^ ((uint64_t)pid * 0x9E3779B97F4A7C15ull)) >> 32);
-  uint64_t i = ((uint64_t)h * S) >> 32;
   for (uint64_t probe = 0; probe < S; ++probe) {
     uint64_t olo, ohi;
     cas128_global(base + i, 0, 0, ip, (uint64_t)pid | ((uint64_t)n << 32), olo, ohi);
@@ -199,6 +200,90 @@ __device__ __forceinline__ void hist_insert_global(const HistTable& t, uint32_t 
     i = (i + 1 == S) ? 0 : i + 1;
   }
   atomicExch(t.overflow, 1u);  // the CPU's sub-table is full
+}
+
+__device__ __forceinline__ void hist_insert_global(const HistTable& t, uint32_t cpu, uint64_t ip,
+                                                   uint32_t pid, uint32_t n) {
+  if (ip == 0 && pid == 0) {
+    atomicAdd(reinterpret_cast<unsigned long long*>(t.zero_key + cpu),
+              (unsigned long long)(long long)(int32_t)n);
+    return;
+  }
+  hist_probe_from(t, cpu, hist_home_slot(t, ip, pid), ip, pid, n);
+}
+
+// A table insert in flight (HBT_KPENDING > 0 only).  The claiming CAS is issued
+// and its answer is looked at one tile later, so the L2/DRAM round trip overlaps
+// the next tile's parsing; a collision re-issues the CAS on the next slot and waits
+// another tile.  Measured on B200 (profiles/r1_notes.md): no faster than inserting
+// synchronously, because the table's L2/HBM atomic rate is the limit, not the
+// latency seen by one thread -- so the default build keeps HBT_KPENDING = 0.
+#ifndef HBT_KPENDING
+#define HBT_KPENDING 0
+#endif
+#ifndef HBT_HIST_CTAS_PER_SM
+#define HBT_HIST_CTAS_PER_SM 4
+#endif
+constexpr int kPending = HBT_KPENDING;
+struct PendingInsert {
+  uint64_t ip, olo, ohi;
+  uint32_t slot, pid;
+  uint32_t probes;  // 0 = free
+};
+
+__device__ __forceinline__ void hist_cas(const HistTable& t, uint32_t cpu, uint32_t n,
+                                         PendingInsert& pd) {
+  cas128_global(t.slots + (uint64_t)cpu * t.slots_per_cpu + pd.slot, 0, 0, pd.ip,
+                (uint64_t)pd.pid | ((uint64_t)n << 32), pd.olo, pd.ohi);
+}
+
+__device__ __forceinline__ void hist_issue(const HistTable& t, uint32_t cpu, uint64_t ip,
+                                           uint32_t pid, uint32_t n, PendingInsert& pd) {
+  pd.slot = (uint32_t)hist_home_slot(t, ip, pid);
+  pd.ip = ip;
+  pd.pid = pid;
+  pd.probes = 1;
+  hist_cas(t, cpu, n, pd);
+}
+
+// Look at the answer of a pending CAS: done, count on the existing key, or move on.
+__device__ __forceinline__ void hist_advance(const HistTable& t, uint32_t cpu, uint32_t n,
+                                             PendingInsert& pd) {
+  if (pd.probes == 0) return;
+  if (pd.olo == 0 && pd.ohi == 0) {  // the CAS claimed the slot and counted
+    pd.probes = 0;
+    return;
+  }
+  if (pd.olo == pd.ip && (uint32_t)pd.ohi == pd.pid) {
+    red_add_u32(reinterpret_cast<uint32_t*>(t.slots + (uint64_t)cpu * t.slots_per_cpu + pd.slot) + 3,
+                n);
+    pd.probes = 0;
+    return;
+  }
+  if (pd.probes >= t.slots_per_cpu) {  // went all the way round: the sub-table is full
+    atomicExch(t.overflow, 1u);
+    pd.probes = 0;
+    return;
+  }
+  pd.slot = pd.slot + 1 == (uint32_t)t.slots_per_cpu ? 0 : pd.slot + 1;
+  ++pd.probes;
+  hist_cas(t, cpu, n, pd);
+}
+
+// Finish a pending insert synchronously (segment end).
+__device__ __forceinline__ void hist_drain(const HistTable& t, uint32_t cpu, uint32_t n,
+                                           PendingInsert& pd) {
+  if (pd.probes == 0) return;
+  if (!(pd.olo == 0 && pd.ohi == 0)) {
+    if (pd.olo == pd.ip && (uint32_t)pd.ohi == pd.pid) {
+      red_add_u32(
+          reinterpret_cast<uint32_t*>(t.slots + (uint64_t)cpu * t.slots_per_cpu + pd.slot) + 3, n);
+    } else {
+      const uint64_t nx = pd.slot + 1 == t.slots_per_cpu ? 0 : pd.slot + 1;
+      hist_probe_from(t, cpu, nx, pd.ip, pd.pid, n);
+    }
+  }
+  pd.probes = 0;
 }
 
 // ---------------------------------------------------------------------------
@@ -215,8 +300,11 @@ struct SegState {
   uint64_t err_pos;
   int32_t err;
   uint32_t slow_tiles;
-  uint32_t guess_min; // per-tile: smallest guessed entry (tile-relative), segment start only
-  uint32_t tile_x;    // per-tile: where the record chain left the tile (tile-relative)
+  // per-tile scratch, one copy per guessing attempt (0: stride-predicted, 1: scanned)
+  uint32_t guess_min[2];  // smallest guessed entry (tile-relative), segment start only
+  uint32_t tile_x[2];     // where the record chain left the tile (tile-relative)
+  uint32_t size_min, size_max;  // record sizes seen in the tile
+  uint32_t stride;    // record size when the previous tile held one size only, else 0
 };
 
 constexpr uint32_t kNoRel = 0xFFFFFFFFu;  // "no tile-relative position"
@@ -359,7 +447,7 @@ __device__ __forceinline__ uint32_t sub_of_word(uint32_t w) {
 }
 
 template <int AGG>
-__global__ void __launch_bounds__(kThreads) k_decode(const DecodeParams p) {
+__global__ void __launch_bounds__(kThreads, AGG == HBT_AGG_IP_HISTOGRAM ? HBT_HIST_CTAS_PER_SM : 4) k_decode(const DecodeParams p) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   uint8_t* stages = smem_raw;  // kStages * kTile
   Smem& sm = *reinterpret_cast<Smem*>(smem_raw + kStages * kTile);
@@ -387,29 +475,53 @@ __global__ void __launch_bounds__(kThreads) k_decode(const DecodeParams p) {
     st.err = 0;
     st.err_pos = 0;
     st.slow_tiles = 0;
-    st.guess_min = kNoRel;
-    st.tile_x = kNoRel;
+    st.guess_min[0] = st.guess_min[1] = kNoRel;
+    st.tile_x[0] = st.tile_x[1] = kNoRel;
+    st.stride = 0;
+    st.size_min = kNoRel;
+    st.size_max = 0;
   }
   sm.expect[tid] = kNoRel;
+  bool table_ready = true;
+  if (AGG == HBT_AGG_IP_HISTOGRAM && p.hist_zero_first) {
+    // Lazy hbt_hist_clear: the CTAs of a CPU zero that CPU's sub-table just before
+    // they fill it, so the lines are born in L2 instead of being written by a
+    // memset, evicted, and read back from HBM at first touch.  Relies on CTAs
+    // being dispatched in blockIdx order (the CTAs a CTA waits for have lower or
+    // neighbouring indices and never wait for later ones).
+    const uint64_t S = p.hist.slots_per_cpu;
+    const uint64_t lo = S * seg.seg / ring.n_seg, hi = S * (seg.seg + 1) / ring.n_seg;
+    ulonglong2* base = p.hist.slots + (uint64_t)seg.cpu * S;
+    for (uint64_t i = lo + tid; i < hi; i += kThreads) base[i] = make_ulonglong2(0, 0);
+    if (seg.seg == 0 && tid == 0) p.hist.zero_key[seg.cpu] = 0;
+    __threadfence();
+    table_ready = false;
+  }
   __syncthreads();
+  if (AGG == HBT_AGG_IP_HISTOGRAM && p.hist_zero_first && tid == 0)
+    atomicAdd(p.hist.arrive + seg.cpu, 1u);
+  PendingInsert pd[kPending > 0 ? kPending : 1];
+#pragma unroll
+  for (int i = 0; i < kPending; ++i) pd[i].probes = 0;
 
-  const uint64_t n_tiles = seg.tile_end - seg.tile_begin;
+  const uint32_t n_tiles = (uint32_t)(seg.tile_end - seg.tile_begin);
   // Records are decoded while they START before seg_limit.
   const uint64_t seg_limit = min(seg.tile_end * (uint64_t)kTile, ring.head);
   const uint64_t policy = l2_policy_evict_first();
 
-  auto issue = [&](uint64_t k) {  // tile k of this segment (k == n_tiles: lookahead tile)
+  auto issue = [&](uint32_t k, uint32_t stage) {  // tile k of this segment (k == n_tiles: lookahead)
     const uint64_t t = seg.tile_begin + k;
-    const int s = (int)(t % kStages);
-    mbar_arrive_expect_tx(&sm.bar[s], kTile);
-    bulk_g2s_hint(stages + s * kTile, ring.base + ((t * (uint64_t)kTile) & ring.mask), kTile,
-                  &sm.bar[s], policy);
+    mbar_arrive_expect_tx(&sm.bar[stage], kTile);
+    bulk_g2s_hint(stages + stage * kTile, ring.base + ((t * (uint64_t)kTile) & ring.mask), kTile,
+                  &sm.bar[stage], policy);
   };
+  // stage of tile k is k % kStages (tile numbering local to the segment)
   if (tid == 0) {
-    issue(0);
-    issue(1);
+    issue(0, 0);
+    issue(1, 1);
   }
   uint32_t phase_bits = 0;  // mbarrier parity per stage
+  uint32_t sa_i = 0;        // stage of the current tile
 
   // thread-local totals over the fast-path tiles (added to st in the epilogue)
   uint32_t my_rec = 0, my_sample = 0;
@@ -418,12 +530,13 @@ __global__ void __launch_bounds__(kThreads) k_decode(const DecodeParams p) {
   const uint32_t sb = 8u * sub_begin_word(tid);
   const uint32_t se_full = tid == kThreads - 1 ? (uint32_t)kTile : 8u * sub_begin_word(tid + 1);
 
-  for (uint64_t k = 0; k < n_tiles; ++k) {
-    const uint64_t t = seg.tile_begin + k;
-    const int sa_i = (int)(t % kStages), sb_i = (int)((t + 1) % kStages);
+#pragma unroll 1
+  for (uint32_t k = 0; k < n_tiles; ++k) {
+    const uint32_t sb_i = sa_i + 1 == kStages ? 0 : sa_i + 1;
+    const uint32_t sc_i = sb_i + 1 == kStages ? 0 : sb_i + 1;
     // refill the stage tile k-1 lived in; the trailing barrier of the previous
     // round ordered every read of it before this copy
-    if (tid == 0 && k + 2 <= n_tiles) issue(k + 2);
+    if (tid == 0 && k + 2 <= n_tiles) issue(k + 2, sc_i);
     if (k == 0) {
       mbar_wait(&sm.bar[sa_i], (phase_bits >> sa_i) & 1);
       phase_bits ^= 1u << sa_i;
@@ -431,12 +544,13 @@ __global__ void __launch_bounds__(kThreads) k_decode(const DecodeParams p) {
     mbar_wait(&sm.bar[sb_i], (phase_bits >> sb_i) & 1);
     phase_bits ^= 1u << sb_i;
 
-    const uint64_t t_begin = t * (uint64_t)kTile;
+    const uint64_t t_begin = (seg.tile_begin + k) * (uint64_t)kTile;
     TileView tv{smem_u32(stages + sa_i * kTile), smem_u32(stages + sb_i * kTile) - (uint32_t)kTile,
                 t_begin, &ring};
     // tile-uniform limits, tile-relative: record starts must be < lim; bytes up to
-    // look (< 2*kTile) are resident and inside the window
-    const uint32_t lim = seg_limit > t_begin ? (uint32_t)min((uint64_t)kTile, seg_limit - t_begin) : 0u;
+    // look (<= 2*kTile) are resident and inside the window
+    const uint32_t lim =
+        seg_limit > t_begin ? (uint32_t)min((uint64_t)kTile, seg_limit - t_begin) : 0u;
     const uint32_t look =
         ring.head > t_begin ? (uint32_t)min((uint64_t)(2 * kTile), ring.head - t_begin) : 0u;
     const uint64_t entry_abs = st.pos;  // exact, or kNone while the segment still guesses
@@ -445,210 +559,275 @@ __global__ void __launch_bounds__(kThreads) k_decode(const DecodeParams p) {
     uint32_t erel;
     if (entry_abs == kNone) erel = kNoRel;
     else erel = (uint32_t)min(entry_abs - t_begin, (uint64_t)0x7FFFFFFFu);  // entry_abs >= t_begin
+    // Stride prediction: when every record of the previous tile had the same size S
+    // the starts of this tile are guessed as entry + k*S (one header check each)
+    // instead of scanning for plausible headers.  Still only a guess.
+    const uint32_t S = st.stride;
+    const bool predict = S >= 8 && erel < (uint32_t)kTile;
+    const float rcpS = predict ? __frcp_rn((float)S) : 0.f;
 
-    // ---- phase 1: guess + walk over the own sub-chunk ---------------------------
     const uint32_t se = min(se_full, lim);
     const bool live = !stopped && sb < se;
-    uint32_t my_entry = kNoRel;  // first record start in my sub-chunk
-    bool owner = false;          // my_entry is the tile's exact entry
-    if (live) {
-      if (erel != kNoRel && erel >= sb) {
-        if (erel < se) {
-          my_entry = erel;
-          owner = true;
-        }
-      } else {
+
+    uint32_t my_entry, mask, smask, omask, my_x, first_ev, last_ev, my_ls, rows_local,
+        unknown_local, sev, srow, rows_j, unknown_j;
+    uint64_t in_ev0;
+    bool owner, pending_seam, slow;
+    uint32_t attempt = predict ? 0u : 1u;
 #pragma unroll 1
-        for (uint32_t q = sb; q < se; q += 8) {
-          const uint64_t h = tv.at(q);
-          if (!plausible(h)) continue;
-          const uint32_t q2 = q + hdr_size(h);
-          if (q2 < look && !plausible(tv.at(q2))) continue;
-          my_entry = q;
-          break;
+    for (;; ++attempt) {
+      // ---- phase 1: guess + walk over the own sub-chunk -------------------------
+      my_entry = kNoRel;  // first record start in my sub-chunk
+      owner = false;      // my_entry is the tile's exact entry
+      if (live) {
+        if (erel != kNoRel && erel >= sb) {
+          if (erel < se) {
+            my_entry = erel;
+            owner = true;
+          }
+        } else {
+          uint32_t q = sb;
+          if (attempt == 0) {
+            // smallest entry + k*S >= sb
+            const uint32_t kk = (uint32_t)((float)(sb - erel + S - 1) * rcpS);
+            q = erel + kk * S;
+            if (q < sb) q += S;
+            else if (q - sb >= S) q -= S;
+            if (q < se && plausible(tv.at(q))) my_entry = q;
+            else if (q < se) q = sb;  // prediction failed here: scan
+            else q = se;              // predicted: nothing starts in my sub-chunk
+          }
+          if (my_entry == kNoRel) {
+#pragma unroll 1
+            for (; q < se; q += 8) {
+              const uint64_t h = tv.at(q);
+              if (!plausible(h)) continue;
+              const uint32_t q2 = q + hdr_size(h);
+              if (q2 < look && !plausible(tv.at(q2))) continue;
+              my_entry = q;
+              break;
+            }
+          }
         }
       }
-    }
-    uint32_t mask = 0;        // bit w: a record starts at sb + 8w
-    uint32_t my_x = kNoRel;   // where my walk left the sub-chunk
-    bool bad = false;
-    uint32_t first_ev = 0, last_ev = 0;  // tile-relative encoded events ((rel+1)<<2 | kind)
-    uint32_t my_ls = 0;                  // last SAMPLE start, relative + 1
-    uint32_t rows_local = 0, unknown_local = 0;
-    uint64_t prev_ts = 0;
-    if (my_entry != kNoRel) {
-      uint32_t pos = my_entry;
+      mask = 0;        // bit w: a record starts at sb + 8w
+      smask = 0;       // ... and it is a handled SAMPLE
+      omask = 0;       // ... and it is another counted record type
+      my_x = kNoRel;   // where my walk left the sub-chunk
+      bool bad = false;
+      uint32_t smin = kNoRel, smax = 0;
+      first_ev = 0;    // tile-relative encoded events ((rel+1)<<2 | kind)
+      last_ev = 0;
+      my_ls = 0;       // last SAMPLE start, relative + 1
+      rows_local = 0;
+      unknown_local = 0;
+      uint64_t prev_ts = 0;
+      if (my_entry != kNoRel) {
+        uint32_t pos = my_entry;
 #pragma unroll 1
-      while (pos < se) {
-        const uint64_t h = tv.at(pos);
-        const uint32_t type = hdr_type(h), size = hdr_size(h);
-        if (size < 8 || (size & 7) || pos + size > 2u * kTile) {
-          bad = true;
-          break;
-        }
-        if (type == REC_SAMPLE && h_sample) {
-          if (group_layout) {
-            const uint64_t nr = tv.at(pos + 16);
-            if ((uint64_t)size != 40 + 8 * nr ||
-                (AGG == HBT_AGG_COUNT_DELTAS && nr != d.n_events)) {
+        while (pos < se) {
+          const uint64_t h = tv.at(pos);
+          const uint32_t type = hdr_type(h), size = hdr_size(h);
+          if (size < 8 || (size & 7) || pos + size > 2u * kTile) {
+            bad = true;
+            break;
+          }
+          const uint32_t bit = 1u << ((pos - sb) >> 3);
+          smin = min(smin, size);
+          smax = max(smax, size);
+          if (type == REC_SAMPLE && h_sample) {
+            if (group_layout) {
+              const uint64_t nr = tv.at(pos + 16);
+              if ((uint64_t)size != 40 + 8 * nr ||
+                  (AGG == HBT_AGG_COUNT_DELTAS && nr != d.n_events)) {
+                bad = true;
+                break;
+              }
+              if (AGG == HBT_AGG_COUNT_DELTAS) {
+                const uint64_t ts = tv.at(pos + 8);
+                const uint32_t lk = last_ev & 3;
+                if (lk == EV_SAMPLE) {
+                  if (prev_ts > ts) {
+                    bad = true;
+                    break;
+                  }
+                  ++rows_local;
+                } else if (lk == EV_LOST) {
+                  ++unknown_local;
+                }
+                last_ev = ((pos + 1) << 2) | EV_SAMPLE;
+                if (first_ev == 0) first_ev = last_ev;
+                my_ls = pos + 1;
+                prev_ts = ts;
+              }
+            } else if (size != d.ip_sample_bytes) {
               bad = true;
               break;
             }
-            if (AGG == HBT_AGG_COUNT_DELTAS) {
-              const uint64_t ts = tv.at(pos + 8);
-              const uint32_t lk = last_ev & 3;
-              if (lk == EV_SAMPLE) {
-                if (prev_ts > ts) {
-                  bad = true;
-                  break;
-                }
-                ++rows_local;
-              } else if (lk == EV_LOST) {
-                ++unknown_local;
-              }
-              last_ev = ((pos + 1) << 2) | EV_SAMPLE;
-              if (first_ev == 0) first_ev = last_ev;
-              my_ls = pos + 1;
-              prev_ts = ts;
+            smask |= bit;
+          } else if (type == REC_READ && h_read) {
+            if ((uint64_t)size != 40 + 8 * tv.at(pos + 16)) {
+              bad = true;
+              break;
             }
-          } else if (size != d.ip_sample_bytes) {
-            bad = true;
-            break;
+            omask |= bit;
+          } else {
+            if (AGG == HBT_AGG_COUNT_DELTAS && type == REC_LOST && h_lost) {
+              last_ev = ((pos + 1) << 2) | EV_LOST;
+              if (first_ev == 0) first_ev = last_ev;
+            }
+            if (counter_of(type, d.handled_mask) >= 0) omask |= bit;
           }
-        } else if (type == REC_READ && h_read) {
-          if ((uint64_t)size != 40 + 8 * tv.at(pos + 16)) {
-            bad = true;
-            break;
+          mask |= bit;
+          pos += size;
+        }
+        my_x = pos;
+        // tell the sub-chunk the chain continues in what it should have found
+        if (!bad) {
+          if (pos < lim) sm.expect[sub_of_word(pos >> 3)] = pos;
+          else st.tile_x[attempt] = pos;
+        }
+      }
+      {
+        const uint32_t wmin = __reduce_min_sync(0xffffffffu, smin);
+        const uint32_t wmax = __reduce_max_sync(0xffffffffu, smax);
+        if (lane == 0 && wmax) {
+          atomicMin(&st.size_min, wmin);
+          atomicMax(&st.size_max, wmax);
+        }
+      }
+      // At a segment start without a known entry the smallest guess is the entry guess.
+      if (erel == kNoRel && my_entry != kNoRel) atomicMin(&st.guess_min[attempt], my_entry);
+
+      // DELTAS: interval state needs the last event / row count before my sub-chunk
+      sev = last_ev;
+      if (AGG == HBT_AGG_COUNT_DELTAS) {
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+          const uint32_t oe = __shfl_up_sync(0xffffffffu, sev, o);
+          if (lane >= o) sev = max(sev, oe);
+        }
+        const uint32_t wls = __reduce_max_sync(0xffffffffu, my_ls);
+        if (lane == 31) {
+          sm.warp_ev[warp] = sev;
+          sm.warp_ls[warp] = wls;
+        }
+      }
+      __syncthreads();  // A: expect[], tile_x, guess_min, warp_ev are complete
+
+      // ---- phase 2: every guess must be what the chain before it predicted ------
+      if (erel == kNoRel && my_entry != kNoRel && my_entry == st.guess_min[attempt]) owner = true;
+      {
+        const uint32_t exp = sm.expect[tid];
+        sm.expect[tid] = kNoRel;  // only I read my slot: reset it for the next round
+        if (live) {
+          if (owner) {
+            if (exp != kNoRel && exp != my_entry) bad = true;
+          } else if (exp != my_entry) {
+            bad = true;  // missed a start, or guessed one the chain does not reach
           }
-        } else if (AGG == HBT_AGG_COUNT_DELTAS && type == REC_LOST && h_lost) {
-          last_ev = ((pos + 1) << 2) | EV_LOST;
-          if (first_ev == 0) first_ev = last_ev;
+        } else if (exp != kNoRel && !stopped) {
+          bad = true;
         }
-        mask |= 1u << ((pos - sb) >> 3);
-        pos += size;
       }
-      my_x = pos;
-      // tell the sub-chunk the chain continues in what it should have found
-      if (!bad) {
-        if (pos < lim) sm.expect[sub_of_word(pos >> 3)] = pos;
-        else st.tile_x = pos;
-      }
-    }
-    // At a segment start without a known entry the smallest guess is the entry guess.
-    if (erel == kNoRel && my_entry != kNoRel) atomicMin(&st.guess_min, my_entry);
-
-    // DELTAS: interval state needs the last event / row count before my sub-chunk
-    uint32_t sev = last_ev;
-    if (AGG == HBT_AGG_COUNT_DELTAS) {
+      // interval state in front of my first SAMPLE
+      in_ev0 = 0;  // absolute encoding
+      rows_j = rows_local;
+      unknown_j = unknown_local;
+      pending_seam = false;
+      srow = 0;
+      if (AGG == HBT_AGG_COUNT_DELTAS) {
+        uint32_t pev = __shfl_up_sync(0xffffffffu, sev, 1);
+        if (lane == 0) pev = 0;
+        for (uint32_t w = 0; w < warp; ++w) pev = max(pev, sm.warp_ev[w]);
+        in_ev0 = pev ? ev_make(t_begin + (pev >> 2) - 1, pev & 3) : st.ev;
+        if ((first_ev & 3) == EV_SAMPLE) {
+          const uint32_t ik = ev_kind(in_ev0);
+          if (ik == EV_SAMPLE) {
+            if (tv.word_abs(ev_pos(in_ev0) + 8) > tv.at((first_ev >> 2) - 1 + 8)) bad = true;
+            ++rows_j;
+          } else if (ik == EV_LOST) {
+            ++unknown_j;
+          } else {
+            pending_seam = true;  // resolved by k_finalize
+          }
+        }
+        srow = rows_j;
 #pragma unroll
-      for (int o = 1; o < 32; o <<= 1) {
-        const uint32_t oe = __shfl_up_sync(0xffffffffu, sev, o);
-        if (lane >= o) sev = max(sev, oe);
-      }
-      const uint32_t wls = __reduce_max_sync(0xffffffffu, my_ls);
-      if (lane == 31) {
-        sm.warp_ev[warp] = sev;
-        sm.warp_ls[warp] = wls;
-      }
-    }
-    __syncthreads();  // A: expect[], tile_x, guess_min, warp_ev are complete
-
-    // ---- phase 2: every guess must be what the chain before it predicted --------
-    if (erel == kNoRel && my_entry != kNoRel && my_entry == st.guess_min) owner = true;
-    {
-      const uint32_t exp = sm.expect[tid];
-      sm.expect[tid] = kNoRel;  // only I read my slot: reset it for the next tile
-      if (live) {
-        if (owner) {
-          if (exp != kNoRel && exp != my_entry) bad = true;
-        } else if (exp != my_entry) {
-          bad = true;  // missed a start, or guessed one the chain does not reach
+        for (int o = 1; o < 32; o <<= 1) {
+          const uint32_t orow = __shfl_up_sync(0xffffffffu, srow, o);
+          if (lane >= o) srow += orow;
         }
-      } else if (exp != kNoRel && !stopped) {
-        bad = true;
+        if (lane == 31) sm.warp_rows[warp] = srow;
       }
+      slow = __syncthreads_or(bad) != 0;  // B
+      if (!slow || attempt == 1) break;
+      // the stride prediction did not hold: guess again by scanning
     }
-    // interval state in front of my first SAMPLE
-    uint64_t in_ev0 = 0;  // absolute encoding
-    uint32_t rows_j = rows_local, unknown_j = unknown_local;
-    bool pending_seam = false;
-    uint32_t srow = 0;
-    if (AGG == HBT_AGG_COUNT_DELTAS) {
-      uint32_t pev = __shfl_up_sync(0xffffffffu, sev, 1);
-      if (lane == 0) pev = 0;
-      for (uint32_t w = 0; w < warp; ++w) pev = max(pev, sm.warp_ev[w]);
-      in_ev0 = pev ? ev_make(t_begin + (pev >> 2) - 1, pev & 3) : st.ev;
-      if ((first_ev & 3) == EV_SAMPLE) {
-        const uint32_t ik = ev_kind(in_ev0);
-        if (ik == EV_SAMPLE) {
-          if (tv.word_abs(ev_pos(in_ev0) + 8) > tv.at((first_ev >> 2) - 1 + 8)) bad = true;
-          ++rows_j;
-        } else if (ik == EV_LOST) {
-          ++unknown_j;
-        } else {
-          pending_seam = true;  // resolved by k_finalize
-        }
+    if (AGG == HBT_AGG_IP_HISTOGRAM && !table_ready) {
+      // before the first insert: every CTA of this CPU has zeroed its slice
+      if (tid == 0) {
+        while (ld_acquire_u32(p.hist.arrive + seg.cpu) < ring.n_seg) __nanosleep(64);
       }
-      srow = rows_j;
-#pragma unroll
-      for (int o = 1; o < 32; o <<= 1) {
-        const uint32_t orow = __shfl_up_sync(0xffffffffu, srow, o);
-        if (lane >= o) srow += orow;
-      }
-      if (lane == 31) sm.warp_rows[warp] = srow;
+      __syncthreads();
+      table_ready = true;
     }
-    const bool slow = __syncthreads_or(bad) != 0;  // B
-
     if (!stopped && !slow) {
       // ---- phase 3: aggregate my records ----------------------------------------
-      if (tid == 0) {
-        // chain bookkeeping for the next tile, overlapped with the other threads' work
-        uint32_t e = erel != kNoRel ? erel : st.guess_min;
-        if (e != kNoRel) {
-          if (st.entry == kNone && e < lim) st.entry = t_begin + e;
-          if (st.tile_x != kNoRel) st.pos = t_begin + st.tile_x;
-          else if (erel == kNoRel) st.pos = t_begin + e;  // cannot happen: a guess always walks
-        }
-        st.tile_x = kNoRel;
-        st.guess_min = kNoRel;
-      }
       uint64_t row_i = 0;
       uint64_t in_ev = in_ev0;
       if (AGG == HBT_AGG_COUNT_DELTAS) {
         row_i = st.n_rows + (srow - rows_j);
         for (uint32_t w = 0; w < warp; ++w) row_i += sm.warp_rows[w];
       }
+      my_rec += __popc(mask);
+      my_sample += __popc(smask);
+      if (AGG == HBT_AGG_IP_HISTOGRAM) {
+        // answers of the CASes issued one tile ago; collisions move on one slot
+#pragma unroll
+        for (int i = 0; i < kPending; ++i) hist_advance(p.hist, seg.cpu, p.hist_inc, pd[i]);
+        uint32_t m = smask;
+        while (m) {
+          const uint32_t pos = sb + 8u * (__ffs(m) - 1);
+          m &= m - 1;
+          const uint64_t ip = tv.at(pos + 8);
+          const uint32_t pid = (uint32_t)tv.at(pos + 16);
+          bool placed = false;
+          if (!(ip == 0 && pid == 0)) {
+#pragma unroll
+            for (int i = 0; i < kPending; ++i) {
+              if (!placed && pd[i].probes == 0) {
+                hist_issue(p.hist, seg.cpu, ip, pid, p.hist_inc, pd[i]);
+                placed = true;
+              }
+            }
+          }
+          if (!placed) hist_insert_global(p.hist, seg.cpu, ip, pid, p.hist_inc);
+        }
+      }
+      uint32_t m = AGG == HBT_AGG_COUNT_DELTAS ? (smask | omask) : omask;
       unsigned long long lost_sum = 0;
-      uint32_t m = mask;
-      my_rec += __popc(m);
       while (m) {
-        const uint32_t w = __ffs(m) - 1;
+        const uint32_t pos = sb + 8u * (__ffs(m) - 1);
         m &= m - 1;
-        const uint32_t pos = sb + 8u * w;
         const uint64_t h = tv.at(pos);
         const uint32_t type = hdr_type(h);
-        if (type == REC_SAMPLE && h_sample) {
-          ++my_sample;
-          if (AGG == HBT_AGG_IP_HISTOGRAM) {
-            hist_insert_global(p.hist, seg.cpu, tv.at(pos + 8), (uint32_t)tv.at(pos + 16),
-                               p.hist_inc);
-          } else if (AGG == HBT_AGG_COUNT_DELTAS) {
-            if (ev_kind(in_ev) == EV_SAMPLE) {
-              const uint64_t ppos = ev_pos(in_ev);
-              const uint64_t pts = tv.word_abs(ppos + 8);
-              const uint64_t ts = tv.at(pos + 8);
-              uint64_t* row = seg.rows + (1 + row_i) * (2 + (uint64_t)d.n_events);
-              row[0] = pts;
-              row[1] = ts - pts;
-              for (uint32_t i = 0; i < d.n_events; ++i) {
-                const uint64_t v = xform(d, i, tv.at(pos + 40 + 8 * i));
-                const uint64_t pv = xform(d, i, tv.word_abs(ppos + 40 + 8ull * i));
-                row[2 + i] = v - pv;
-              }
-              ++row_i;
+        if (AGG == HBT_AGG_COUNT_DELTAS && type == REC_SAMPLE && h_sample) {
+          if (ev_kind(in_ev) == EV_SAMPLE) {
+            const uint64_t ppos = ev_pos(in_ev);
+            const uint64_t pts = tv.word_abs(ppos + 8);
+            const uint64_t ts = tv.at(pos + 8);
+            uint64_t* row = seg.rows + (1 + row_i) * (2 + (uint64_t)d.n_events);
+            row[0] = pts;
+            row[1] = ts - pts;
+            for (uint32_t i = 0; i < d.n_events; ++i) {
+              const uint64_t v = xform(d, i, tv.at(pos + 40 + 8 * i));
+              const uint64_t pv = xform(d, i, tv.word_abs(ppos + 40 + 8ull * i));
+              row[2 + i] = v - pv;
             }
-            in_ev = ev_make(t_begin + pos, EV_SAMPLE);
+            ++row_i;
           }
+          in_ev = ev_make(t_begin + pos, EV_SAMPLE);
         } else {
           const int ci = counter_of(type, d.handled_mask);
           if (ci == HBT_CNT_LOST) {
@@ -666,33 +845,55 @@ __global__ void __launch_bounds__(kThreads) k_decode(const DecodeParams p) {
       }
     }
     if (AGG == HBT_AGG_COUNT_DELTAS) __syncthreads();  // row_i readers before n_rows moves
-    if (tid == 0 && !stopped) {
-      if (slow) {
-        // literal consume() over this tile by one thread
-        ++st.slow_tiles;
-        if (st.pos == kNone && st.guess_min != kNoRel) st.pos = t_begin + st.guess_min;
-        if (st.pos != kNone) consume_sequential<AGG>(p, ring, seg, st, t_begin + lim);
-        st.tile_x = kNoRel;
-        st.guess_min = kNoRel;
-      } else if (AGG == HBT_AGG_COUNT_DELTAS) {
-        uint32_t tev = 0, trows = 0, tls = 0;
-        for (uint32_t w = 0; w < kThreads / 32; ++w) {
-          tev = max(tev, sm.warp_ev[w]);
-          tls = max(tls, sm.warp_ls[w]);
-          trows += sm.warp_rows[w];
+    if (tid == 0) {
+      if (!stopped) {
+        const uint32_t a = attempt;  // the attempt whose scatter results were verified
+        if (slow) {
+          // literal consume() over this tile by one thread
+          ++st.slow_tiles;
+          const uint32_t g = min(st.guess_min[0], st.guess_min[1]);
+          if (st.pos == kNone && g != kNoRel) st.pos = t_begin + g;
+          if (st.pos != kNone) consume_sequential<AGG>(p, ring, seg, st, t_begin + lim);
+          st.stride = 0;
+        } else {
+          // chain bookkeeping for the next tile
+          const uint32_t e = erel != kNoRel ? erel : st.guess_min[a];
+          if (e != kNoRel) {
+            if (st.entry == kNone && e < lim) st.entry = t_begin + e;
+            if (st.tile_x[a] != kNoRel) st.pos = t_begin + st.tile_x[a];
+            else if (erel == kNoRel) st.pos = t_begin + e;
+          }
+          if (AGG == HBT_AGG_COUNT_DELTAS) {
+            uint32_t tev = 0, trows = 0, tls = 0;
+            for (uint32_t w = 0; w < kThreads / 32; ++w) {
+              tev = max(tev, sm.warp_ev[w]);
+              tls = max(tls, sm.warp_ls[w]);
+              trows += sm.warp_rows[w];
+            }
+            if (tev) st.ev = ev_make(t_begin + (tev >> 2) - 1, tev & 3);
+            if (tls) st.last_sample = t_begin + tls - 1;
+            st.n_rows += trows;
+          }
+          st.stride = st.size_min == st.size_max ? st.size_min : 0;
         }
-        if (tev) st.ev = ev_make(t_begin + (tev >> 2) - 1, tev & 3);
-        if (tls) st.last_sample = t_begin + tls - 1;
-        st.n_rows += trows;
       }
+      st.tile_x[0] = st.tile_x[1] = kNoRel;
+      st.guess_min[0] = st.guess_min[1] = kNoRel;
+      st.size_min = kNoRel;
+      st.size_max = 0;
     }
-    // every generic-proxy read of stage (t % kStages) is ordered before the bulk
-    // copy that thread 0 issues into it after this barrier
+    // every generic-proxy read of stage sa_i is ordered before the bulk copy that
+    // thread 0 issues into it after this barrier
     fence_proxy_async();
     __syncthreads();  // C
+    sa_i = sb_i;
   }
 
   // ---- segment epilogue --------------------------------------------------------
+  if (AGG == HBT_AGG_IP_HISTOGRAM) {
+#pragma unroll
+    for (int i = 0; i < kPending; ++i) hist_drain(p.hist, seg.cpu, p.hist_inc, pd[i]);
+  }
   my_rec = __reduce_add_sync(0xffffffffu, my_rec);
   my_sample = __reduce_add_sync(0xffffffffu, my_sample);
   if (lane == 0) {

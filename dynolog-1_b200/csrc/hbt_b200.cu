@@ -19,7 +19,7 @@ using namespace hbt;
 
 namespace {
 
-constexpr int kMaxSegsPerCpu = 64;
+constexpr int kMaxSegsPerCpu = 256;
 constexpr int kMaxRatios = 64;
 
 template <class T>
@@ -123,7 +123,12 @@ struct hbt_ctx {
   DevBuf<ulonglong2> hist_slots;
   DevBuf<uint64_t> hist_zero;
   DevBuf<uint32_t> hist_overflow;
+  DevBuf<uint32_t> hist_arrive;
   uint64_t hist_slots_per_cpu = 0;
+  bool hist_needs_zero = false;   // hbt_hist_clear is lazy: the next decode zeroes in-kernel
+  bool hist_zero_this_decode = false;
+  bool tiled_zero = true;
+  uint64_t hist_samples = 0;      // upper bound of samples added since the last clear
   DevBuf<hbt_hist_entry> hist_out;
   DevBuf<unsigned long long> hist_n;
 
@@ -211,6 +216,10 @@ int build_tables(hbt_ctx* ctx, const uint64_t* clamp_head, const int64_t* clamp_
   // 8 tiles (128 KiB) per segment
   const uint64_t target_ctas = (uint64_t)ctx->sm_count * 8;
   uint32_t segs_per_cpu = active ? (uint32_t)((target_ctas + active - 1) / active) : 1;
+  // the histogram wants few CPUs in flight at a time (their sub-tables share L2):
+  // more, shorter segments per CPU, dispatched CPU-major
+  if (d.aggregate == HBT_AGG_IP_HISTOGRAM && segs_per_cpu < 64) segs_per_cpu = 64;
+  if (const char* e = getenv("HBT_SEGS_PER_CPU")) segs_per_cpu = (uint32_t)atoi(e);  // tuning aid
   if (segs_per_cpu > kMaxSegsPerCpu) segs_per_cpu = kMaxSegsPerCpu;
   if (segs_per_cpu < 1) segs_per_cpu = 1;
 
@@ -253,7 +262,9 @@ int build_tables(hbt_ctx* ctx, const uint64_t* clamp_head, const int64_t* clamp_
       const uint64_t t1 = (w.head + kTile - 1) / kTile;
       const uint64_t nt = t1 - t0;
       uint64_t per = (nt + segs_per_cpu - 1) / segs_per_cpu;
-      if (per < 8) per = 8;
+      uint64_t min_per = 8;
+      if (const char* e = getenv("HBT_MIN_TILES_PER_SEG")) min_per = (uint64_t)atoi(e);  // tuning aid
+      if (per < min_per) per = min_per;
       uint32_t k = 0;
       for (uint64_t tb = t0; tb < t1; tb += per, ++k) {
         SegDesc s{};
@@ -317,7 +328,10 @@ int launch_decode_agg(hbt_ctx* ctx, uint32_t hist_inc) {
   p.hist.slots_per_cpu = ctx->hist_slots_per_cpu;
   p.hist.zero_key = ctx->hist_zero.p;
   p.hist.overflow = ctx->hist_overflow.p;
+  p.hist.arrive = ctx->hist_arrive.p;
   p.hist_inc = hist_inc;
+  p.hist_zero_first =
+      (AGG == HBT_AGG_IP_HISTOGRAM && ctx->hist_zero_this_decode && ctx->tiled && ctx->tiled_zero) ? 1 : 0;
   if (ctx->n_segs == 0) return 0;
   if (ctx->tiled) {
     const size_t smem = decode_smem_bytes(AGG);
@@ -377,8 +391,25 @@ int run_once(hbt_ctx* ctx, uint32_t hist_inc) {
   CU(cudaMemsetAsync(ctx->d_clamp_head.p, 0xFF, ctx->n_cpus * sizeof(uint64_t), ctx->stream));
   CU(cudaMemsetAsync(ctx->d_forced.p, 0xFF, (ctx->n_segs ? ctx->n_segs : 1) * sizeof(uint64_t),
                      ctx->stream));
+  if (ctx->desc.aggregate == HBT_AGG_IP_HISTOGRAM && ctx->hist_zero_this_decode) {
+    // lazy clear: tiled decodes zero each CPU's sub-table in-kernel; CPUs without a
+    // segment (and the untiled small-ring path) are cleared from here
+    const size_t per = ctx->hist_slots_per_cpu * sizeof(ulonglong2);
+    if (getenv("HBT_NO_ZERO_FIRST")) ctx->tiled_zero = false;  // tuning aid
+    if (!ctx->tiled || !ctx->tiled_zero) {
+      CU(cudaMemsetAsync(ctx->hist_slots.p, 0, per * ctx->n_cpus, ctx->stream));
+    } else {
+      CU(cudaMemsetAsync(ctx->hist_arrive.p, 0, ctx->n_cpus * sizeof(uint32_t), ctx->stream));
+      for (uint32_t c = 0; c < ctx->n_cpus; ++c)
+        if (ctx->h_rings.p[c].n_seg == 0)
+          CU(cudaMemsetAsync(ctx->hist_slots.p + (size_t)c * ctx->hist_slots_per_cpu, 0, per,
+                             ctx->stream));
+    }
+    CU(cudaMemsetAsync(ctx->hist_zero.p, 0, ctx->n_cpus * sizeof(uint64_t), ctx->stream));
+  }
   int rc = launch_decode(ctx, hist_inc);
   if (rc) return rc;
+  if (hist_inc != 1) return 0;  // taking a failed attempt back out: no finalize
   return launch_finalize(ctx);
 }
 
@@ -450,6 +481,7 @@ void hbt_destroy(hbt_ctx* ctx) {
   ctx->hist_slots.release();
   ctx->hist_zero.release();
   ctx->hist_overflow.release();
+  ctx->hist_arrive.release();
   ctx->hist_out.release();
   ctx->hist_n.release();
   ctx->d_ratios.release();
@@ -579,6 +611,26 @@ int hbt_submit_ring_dev(hbt_ctx* ctx, uint32_t cpu, const void* ring_base, uint6
   return 0;
 }
 
+int hbt_submit_rings_dev(hbt_ctx* ctx, uint32_t n, const void* const* ring_bases,
+                         uint64_t data_size, const uint64_t* tails, const uint64_t* heads) {
+  if (!ctx || n > ctx->n_cpus || !ring_bases || !tails || !heads) return fail(ctx, -EINVAL, "bad args");
+  if (int rc = complete_decode(ctx)) return rc;
+  if (!is_pow2(data_size) || data_size < 4096) return fail(ctx, -EINVAL, "bad data_size");
+  for (uint32_t c = 0; c < n; ++c) {
+    if (!ring_bases[c] || ((uintptr_t)ring_bases[c] & 15) || (tails[c] & 7) || heads[c] < tails[c])
+      return fail(ctx, -EINVAL, "bad ring %u", c);
+  }
+  for (uint32_t c = 0; c < n; ++c) {
+    Window& w = ctx->win[c];
+    w.base = static_cast<const uint8_t*>(ring_bases[c]);
+    w.data_size = data_size;
+    w.tail = tails[c];
+    w.head = heads[c];
+    w.active = true;
+  }
+  return 0;
+}
+
 // ---- decode ------------------------------------------------------------------
 
 int hbt_decode(hbt_ctx* ctx, const hbt_decode_desc* desc) {
@@ -590,6 +642,19 @@ int hbt_decode(hbt_ctx* ctx, const hbt_decode_desc* desc) {
   if (rc) return rc;
   ctx->desc = *desc;
   if (ctx->desc.aggregate != HBT_AGG_COUNT_DELTAS) ctx->desc.n_events = 0;
+  ctx->hist_zero_this_decode = false;
+  if (ctx->desc.aggregate == HBT_AGG_IP_HISTOGRAM) {
+    // 32-bit counts in the table: refuse anything that could wrap one
+    uint64_t bound = 0;
+    for (const Window& w : ctx->win)
+      if (w.active && w.head > w.tail) bound += (w.head - w.tail) / ctx->desc.ip_sample_bytes + 1;
+    if (ctx->hist_needs_zero) ctx->hist_samples = 0;
+    if (ctx->hist_samples + bound > 0xFFFFFFFFull)
+      return fail(ctx, -EOVERFLOW, "more than 2^32-1 samples since hbt_hist_clear");
+    ctx->hist_samples += bound;
+    ctx->hist_zero_this_decode = ctx->hist_needs_zero;
+    ctx->hist_needs_zero = false;
+  }
   rc = build_tables(ctx, nullptr, nullptr, nullptr);
   if (rc) return rc;
   rc = run_once(ctx, 1);
@@ -618,7 +683,8 @@ static int complete_decode(hbt_ctx* ctx) {
     if (iter > 4 * kMaxSegsPerCpu + 8) return fail(ctx, -EIO, "decode re-run did not converge");
     ++ctx->reruns;
     // take the failed attempt back out of the shared table
-    if (ctx->desc.aggregate == HBT_AGG_IP_HISTOGRAM) {
+    if (ctx->desc.aggregate == HBT_AGG_IP_HISTOGRAM && !ctx->hist_zero_this_decode) {
+      // (a decode that clears the table first simply clears it again)
       int rc = launch_decode(ctx, 0xFFFFFFFFu);
       if (rc) return rc;
     }
@@ -780,26 +846,38 @@ int hbt_fetch_carry(hbt_ctx* ctx, uint32_t cpu, uint64_t* last, uint32_t n_event
 
 int hbt_hist_clear(hbt_ctx* ctx) {
   if (!ctx || ctx->hist_slots_per_cpu == 0) return fail(ctx, -EINVAL, "no histogram configured");
-  CU(cudaMemsetAsync(ctx->hist_slots.p, 0, ctx->hist_slots.n * sizeof(ulonglong2), ctx->stream));
-  CU(cudaMemsetAsync(ctx->hist_zero.p, 0, ctx->hist_zero.n * sizeof(uint64_t), ctx->stream));
+  if (int rc = complete_decode(ctx)) return rc;
+  // Lazy: the next IP_HISTOGRAM decode zeroes each CPU's sub-table in-kernel, right
+  // before filling it; hist_flush_clear() does it eagerly if something reads first.
+  ctx->hist_needs_zero = true;
+  ctx->hist_samples = 0;
   CU(cudaMemsetAsync(ctx->hist_overflow.p, 0, sizeof(uint32_t), ctx->stream));
+  return 0;
+}
+
+static int hist_flush_clear(hbt_ctx* ctx) {
+  if (!ctx->hist_needs_zero) return 0;
+  CU(cudaMemsetAsync(ctx->hist_slots.p, 0,
+                     ctx->hist_slots_per_cpu * ctx->n_cpus * sizeof(ulonglong2), ctx->stream));
+  CU(cudaMemsetAsync(ctx->hist_zero.p, 0, ctx->n_cpus * sizeof(uint64_t), ctx->stream));
+  ctx->hist_needs_zero = false;
   return 0;
 }
 
 int hbt_hist_configure(hbt_ctx* ctx, uint64_t capacity_slots) {
   if (!ctx || ctx->n_cpus == 0) return fail(ctx, -EINVAL, "configure rings first");
-  if (!is_pow2(capacity_slots)) return fail(ctx, -EINVAL, "capacity must be a power of two");
-  uint64_t per = capacity_slots / ctx->n_cpus;
-  // largest power of two <= capacity / n_cpus
-  uint64_t p2 = 1;
-  while (p2 * 2 <= per) p2 *= 2;
-  if (per == 0 || p2 < 64) return fail(ctx, -EINVAL, "capacity too small for %u CPUs", ctx->n_cpus);
+  if (int rc = complete_decode(ctx)) return rc;
+  const uint64_t per = capacity_slots / ctx->n_cpus;
+  if (per < 64 || per >= (1ull << 32))
+    return fail(ctx, -EINVAL, "capacity %llu gives %llu slots per CPU (need 64..2^32-1)",
+                (unsigned long long)capacity_slots, (unsigned long long)per);
   CU(cudaSetDevice(ctx->device));
-  CU(ctx->hist_slots.reserve((size_t)p2 * ctx->n_cpus));
+  CU(ctx->hist_slots.reserve((size_t)per * ctx->n_cpus));
   CU(ctx->hist_zero.reserve(ctx->n_cpus));
   CU(ctx->hist_overflow.reserve(1));
+  CU(ctx->hist_arrive.reserve(ctx->n_cpus));
   CU(ctx->hist_n.reserve(1));
-  ctx->hist_slots_per_cpu = p2;
+  ctx->hist_slots_per_cpu = per;
   return hbt_hist_clear(ctx);
 }
 
@@ -807,9 +885,12 @@ static int64_t hist_collect(hbt_ctx* ctx, hbt_hist_entry* out, uint64_t cap) {
   if (!ctx || ctx->hist_slots_per_cpu == 0) return fail(ctx, -EINVAL, "no histogram configured");
   int rc = complete_decode(ctx);
   if (rc) return rc;
+  rc = hist_flush_clear(ctx);
+  if (rc) return rc;
   if (out) CU(ctx->hist_out.reserve(cap ? cap : 1));
   CU(cudaMemsetAsync(ctx->hist_n.p, 0, sizeof(unsigned long long), ctx->stream));
-  HistTable t{ctx->hist_slots.p, ctx->hist_slots_per_cpu, ctx->hist_zero.p, ctx->hist_overflow.p};
+  HistTable t{ctx->hist_slots.p, ctx->hist_slots_per_cpu, ctx->hist_zero.p, ctx->hist_overflow.p,
+              ctx->hist_arrive.p};
   k_hist_compact<<<ctx->sm_count * 8, 256, 0, ctx->stream>>>(t, ctx->n_cpus, ctx->cpu_base,
                                                             out ? ctx->hist_out.p : nullptr,
                                                             ctx->hist_n.p, cap);
@@ -834,6 +915,8 @@ int64_t hbt_hist_fetch(hbt_ctx* ctx, hbt_hist_entry* out, uint64_t cap) {
 
 int hbt_hist_table_dev(hbt_ctx* ctx, const void** slots, uint64_t* slots_per_cpu) {
   if (!ctx || !slots || !slots_per_cpu || ctx->hist_slots_per_cpu == 0) return -EINVAL;
+  if (int rc = complete_decode(ctx)) return rc;
+  if (int rc = hist_flush_clear(ctx)) return rc;
   *slots = ctx->hist_slots.p;
   *slots_per_cpu = ctx->hist_slots_per_cpu;
   return 0;

@@ -85,6 +85,12 @@ __device__ __forceinline__ uint64_t lds_u64(uint32_t saddr) {
   return v;
 }
 
+__device__ __forceinline__ uint32_t ld_acquire_u32(const uint32_t* p) {
+  uint32_t v;
+  asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+
 // Fire-and-forget global add (SASS RED): no return value, no round-trip wait.
 __device__ __forceinline__ void red_add_u32(uint32_t* p, uint32_t v) {
   asm volatile("red.global.add.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
@@ -108,6 +114,31 @@ __device__ __forceinline__ void cas128_global(void* addr, uint64_t clo, uint64_t
       : "=l"(olo), "=l"(ohi)
       : "l"(addr), "l"(clo), "l"(chi), "l"(nlo), "l"(nhi)
       : "memory");
+}
+
+// The same with an L2 eviction-priority hint (the histogram table is re-used,
+// the ring bytes streaming past it are not).
+__device__ __forceinline__ uint64_t l2_policy_evict_last() {
+  uint64_t pol;
+  asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(pol));
+  return pol;
+}
+__device__ __forceinline__ void cas128_global_hint(void* addr, uint64_t clo, uint64_t chi,
+                                                   uint64_t nlo, uint64_t nhi, uint64_t& olo,
+                                                   uint64_t& ohi, uint64_t policy) {
+  asm volatile(
+      "{\n\t.reg .b128 c, n, d;\n\t"
+      "mov.b128 c, {%3, %4};\n\t"
+      "mov.b128 n, {%5, %6};\n\t"
+      "atom.global.relaxed.gpu.cas.L2::cache_hint.b128 d, [%2], c, n, %7;\n\t"
+      "mov.b128 {%0, %1}, d;\n\t}"
+      : "=l"(olo), "=l"(ohi)
+      : "l"(addr), "l"(clo), "l"(chi), "l"(nlo), "l"(nhi), "l"(policy)
+      : "memory");
+}
+__device__ __forceinline__ void red_add_u32_hint(uint32_t* p, uint32_t v, uint64_t policy) {
+  asm volatile("red.global.add.L2::cache_hint.u32 [%0], %1, %2;" ::"l"(p), "r"(v), "l"(policy)
+               : "memory");
 }
 
 __device__ __forceinline__ ulonglong2 ld_relaxed_v2u64(const void* p) {

@@ -215,6 +215,10 @@ int hbt_submit_ring(hbt_ctx* ctx, uint32_t cpu, const void* p1, size_t n1,
 int hbt_submit_ring_dev(hbt_ctx* ctx, uint32_t cpu, const void* ring_base,
                         uint64_t data_size, uint64_t tail, uint64_t head);
 
+/* The same for rings 0..n-1 in one call (all of one data_size). */
+int hbt_submit_rings_dev(hbt_ctx* ctx, uint32_t n, const void* const* ring_bases,
+                         uint64_t data_size, const uint64_t* tails, const uint64_t* heads);
+
 /* Forget counters, carry (count_.tstamp, last_[]) and windows of all CPUs:
  * the state after enable() (CpuEventsGroup.h:1240-1280, enableImpl
  * PerCpuCountSampleGenerator.h:91-106).  seed_tstamp is the value enableImpl
@@ -260,10 +264,13 @@ uint32_t hbt_rows_max_slabs(const hbt_ctx* ctx);
 /* last_[] of `cpu` after the last decode (PerCpuCountSampleGenerator.h:228). */
 int hbt_fetch_carry(hbt_ctx* ctx, uint32_t cpu, uint64_t* last, uint32_t n_events);
 
-/* (cpu,pid,ip) table.  capacity_slots (a power of two) is split evenly between
- * the configured CPUs; a decode that overflows a CPU's share makes
- * hbt_fetch_results return -ENOSPC.  Counts are 32-bit in the table
- * (-EOVERFLOW if one wraps) and accumulate until hbt_hist_clear. */
+/* (cpu,pid,ip) table.  capacity_slots is split evenly between the configured
+ * CPUs (each CPU owns a contiguous sub-table, so a CPU's keys stay in L2 while
+ * that CPU's segments are decoded); a decode that overflows a CPU's share makes
+ * hbt_fetch_results return -ENOSPC.  Counts are 32-bit in the table and
+ * accumulate until hbt_hist_clear; hbt_decode returns -EOVERFLOW rather than let
+ * more than 2^32-1 samples accumulate.  hbt_hist_clear is lazy: the next
+ * HBT_AGG_IP_HISTOGRAM decode zeroes the table inside its kernel. */
 int hbt_hist_configure(hbt_ctx* ctx, uint64_t capacity_slots);
 int hbt_hist_clear(hbt_ctx* ctx);
 /* Number of distinct keys, then the entries (unordered). */
