@@ -1,0 +1,138 @@
+"""Golden vectors in tests/golden/*.npz were produced by the REFERENCE's own code
+(tests/golden/make_golden.py over oracle/_ref).  The oracle port must reproduce
+them anywhere (no GPU, no reference tree); the CUDA path must too (-m gpu)."""
+import glob
+import os
+
+import numpy as np
+import pytest
+
+import dynolog_1_b200 as hbt
+import _oracle as orc
+
+GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+DECODE_CASES = sorted(os.path.basename(p)[:-4] for p in glob.glob(os.path.join(GOLDEN, "*.npz"))
+                      if not os.path.basename(p).startswith("counts_"))
+COUNTS_CASES = ["counts_mux", "counts_c1_shape"]
+
+
+def load_desc(f):
+    v = [int(x) for x in f["desc"]]
+    d = hbt.DecodeDesc()
+    (d.handled_mask, d.sample_layout, d.aggregate, d.n_events, d.ip_sample_bytes, d.max_records,
+     d.tsc_transform_mask) = v[:7]
+    d.tsc = hbt.TscParams(v[7], v[8], v[9], 0)
+    return d
+
+
+def want_of(f):
+    w = dict(ret=int(f["ret"]), n_records=int(f["n_records"]), new_tail=int(f["new_tail"]),
+             n_rows=int(f["n_rows"]), counters=[int(x) for x in f["counters"]],
+             num_unknown=int(f["num_unknown"]), carry_tstamp=int(f["carry_tstamp"]))
+    if "rows" in f:
+        w["rows"] = f["rows"]
+        w["carry_last"] = f["carry_last"]
+    if "hist_keys" in f:
+        w["hist"] = {tuple(int(x) for x in k): int(c) for k, c in zip(f["hist_keys"], f["hist_counts"])}
+    return w
+
+
+def test_golden_files_present():
+    assert len(DECODE_CASES) >= 12
+
+
+@pytest.mark.parametrize("case", DECODE_CASES)
+def test_oracle_port_matches_reference_vectors(built, case):
+    f = np.load(os.path.join(GOLDEN, case + ".npz"))
+    d = load_desc(f)
+    tail, head = (int(x) for x in f["window"])
+    carry_last = f["carry_in_last"] if "carry_in_last" in f else None
+    got = orc.port_consume(f["ring"], tail, head, d, int(f["carry_in_tstamp"]), carry_last,
+                           cpu=int(f["cpu"]))
+    want = want_of(f)
+    keys = ["ret", "n_records", "new_tail", "counters"]
+    if d.aggregate == hbt.AGG_COUNT_DELTAS:
+        keys += ["n_rows", "num_unknown", "carry_tstamp"]
+    for k in keys:
+        assert got[k] == want[k], (case, k, got[k], want[k])
+    if "rows" in want:
+        assert np.array_equal(got["rows"], want["rows"])
+        assert np.array_equal(got["carry_last"], want["carry_last"])
+    if "hist" in want:
+        assert got["hist"] == want["hist"]
+
+
+@pytest.mark.parametrize("case", COUNTS_CASES)
+def test_oracle_counts_match_reference_vectors(built, case):
+    f = np.load(os.path.join(GOLDEN, case + ".npz"))
+    ratios = [tuple(int(x) for x in r) for r in f["ratios"]]
+    got = orc.port_counts(f["reads"], ratios)
+    ok = f["sums"][:, 0] != 0  # a failed read leaves the other words unspecified
+    assert np.array_equal(got["sums"][:, 0], f["sums"][:, 0])
+    assert np.array_equal(got["sums"][ok], f["sums"][ok])
+    assert np.array_equal(got["scaled"], f["scaled"])
+    assert np.array_equal(got["deltas"], f["deltas"])
+    assert np.array_equal(got["rates"], f["rates"], equal_nan=True)
+    assert np.array_equal(got["ratios"], f["ratio_out"], equal_nan=True)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("case", DECODE_CASES)
+def test_cuda_matches_reference_vectors(built, case):
+    import torch
+    f = np.load(os.path.join(GOLDEN, case + ".npz"))
+    d = load_desc(f)
+    tail, head = (int(x) for x in f["window"])
+    ring = f["ring"]
+    want = want_of(f)
+    ctx = hbt.Context(0)
+    try:
+        ctx.ring_configure(1, 0)
+        ctx.set_cpu_base(int(f["cpu"]))
+        # seed the generator state the vector was produced with
+        ctx.reset_state(int(f["carry_in_tstamp"]))
+        if "carry_in_last" in f:
+            pytest.skip("non-zero last_[] seed is covered by test_gpu_parity.test_carry_across_calls")
+        if d.aggregate == hbt.AGG_IP_HISTOGRAM:
+            ctx.hist_configure(1 << 12)
+        img = torch.from_numpy(ring.view(np.int64)).cuda()
+        ctx.submit_ring_dev(0, img, ring.nbytes, tail, head)
+        ctx.decode(d)
+        got = ctx.fetch_results()[0]
+        assert int(got["ret"]) == want["ret"]
+        assert int(got["n_records"]) == want["n_records"]
+        assert int(got["new_tail"]) == want["new_tail"]
+        assert [int(x) for x in got["counters"]] == want["counters"]
+        if d.aggregate == hbt.AGG_COUNT_DELTAS:
+            assert int(got["n_rows"]) == want["n_rows"]
+            assert int(got["num_unknown_count_interval"]) == want["num_unknown"]
+            assert int(got["carry_tstamp"]) == want["carry_tstamp"]
+            assert np.array_equal(ctx.fetch_rows(0, want["n_rows"], d.n_events), want["rows"])
+            assert np.array_equal(ctx.fetch_carry(0, d.n_events), want["carry_last"])
+        if "hist" in want:
+            assert orc.hist_to_dict(ctx.hist_fetch()) == want["hist"]
+    finally:
+        ctx.close()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("case", COUNTS_CASES)
+def test_cuda_counts_match_reference_vectors(built, case):
+    f = np.load(os.path.join(GOLDEN, case + ".npz"))
+    ratios = [tuple(int(x) for x in r) for r in f["ratios"]]
+    ctx = hbt.Context(0)
+    try:
+        got = ctx.counts_pipeline_host(f["reads"], ratios)
+    finally:
+        ctx.close()
+    ok = f["sums"][:, 0] != 0
+    assert np.array_equal(got["sums"][:, 0], f["sums"][:, 0])
+    assert np.array_equal(got["sums"][ok], f["sums"][ok])
+    assert np.array_equal(got["scaled"], f["scaled"])
+    assert np.array_equal(got["deltas"], f["deltas"])
+    finite = np.isfinite(f["rates"])
+    assert np.array_equal(got["rates"][finite], f["rates"][finite])
+    assert np.array_equal(np.isnan(got["rates"]), np.isnan(f["rates"]))
+    fin = np.isfinite(f["ratio_out"])
+    # north star: f64 ratios within 1e-12 relative
+    assert np.allclose(got["ratios"][fin], f["ratio_out"][fin], rtol=1e-12, atol=0.0)
