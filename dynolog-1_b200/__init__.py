@@ -110,6 +110,8 @@ EXPORTS = [
      [_P, _P, C.c_uint64, C.c_uint32, C.c_uint32, _P, C.c_uint32, _P, _P, _P, _P, _P]),
     ("hbt_counts_pipeline_host", C.c_int,
      [_P, _P, C.c_uint64, C.c_uint32, C.c_uint32, _P, C.c_uint32, _P, _P, _P, _P, _P]),
+    ("hbt_counts_deltas_static_dev", C.c_int,
+     [_P, C.c_uint64, C.c_uint32, C.c_uint32, _P, _P]),
 ]
 
 _lib = None
@@ -328,6 +330,19 @@ class Context:
             _ptr(out["ratios"]) if R else None, _ptr(out["deltas"])))
         out["ratios"] = out["ratios"][:, :R]
         return out
+
+
+STATIC_SCRATCH_WORDS = 512 * 1024
+
+
+def counts_deltas_static_dev(reads, n_intervals, n_cpus, n_events, deltas, stream_ptr=None) -> int:
+    """hbt_counts_deltas_static_dev: the allocation-free entry point (no Context).
+    reads / deltas are device tensors on the current device; returns the C return
+    code (0 or a negative errno) instead of raising, so callers can test -E2BIG."""
+    lib = load_library()
+    return int(lib.hbt_counts_deltas_static_dev(_ptr(reads), n_intervals, n_cpus, n_events,
+                                                _ptr(deltas),
+                                                C.c_void_p(stream_ptr) if stream_ptr else None))
 
 
 def sampling_desc(n_events: int, aggregate: int = AGG_COUNT_DELTAS, max_records: int = DRAIN,

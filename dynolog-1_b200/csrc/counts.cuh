@@ -129,7 +129,8 @@ struct ScaleArgs {
   double* ratio_out;
 };
 
-__global__ void __launch_bounds__(256) k_counts_scale(const ScaleArgs a) {
+// (static: this header is compiled into more than one translation unit)
+static __global__ void __launch_bounds__(256) k_counts_scale(const ScaleArgs a) {
   const uint32_t E = a.n_events;
   const uint32_t W = 3 + E;
   const uint32_t per = E + a.n_ratios;  // work items per interval
@@ -156,7 +157,7 @@ __global__ void __launch_bounds__(256) k_counts_scale(const ScaleArgs a) {
 
 // deltas[i][e] = scaled[i][e] - scaled[i-1][e] (u64 wrap): MetricSeries::diff
 // (dynolog/src/metric_frame/MetricSeries.h:221-227) over consecutive intervals.
-__global__ void __launch_bounds__(256)
+static __global__ void __launch_bounds__(256)
     k_scaled_diff(const uint64_t* scaled, const uint64_t* prev, uint64_t n_intervals, uint32_t E,
                   uint64_t* deltas) {
   const uint64_t total = n_intervals * E;

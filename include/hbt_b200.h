@@ -326,6 +326,43 @@ int hbt_counts_pipeline_host(hbt_ctx* ctx, const uint64_t* reads, uint64_t n_int
                              uint32_t n_ratios, uint64_t* sums, uint64_t* scaled,
                              float* rates, double* ratio_out, uint64_t* deltas);
 
+/* ------------------------------------------------------------------------ */
+/* Allocation-free variant                                                  */
+/* ------------------------------------------------------------------------ */
+
+/* Largest n_intervals * n_events hbt_counts_deltas_static_dev accepts: its
+ * working buffer is a fixed 4 MiB array inside the library image. */
+#define HBT_STATIC_SCRATCH_WORDS (512u * 1024u)
+
+/* No counterpart in the reference: this entry point exists for callers that must
+ * not allocate device memory while they sample -- a monitor sharing a GPU whose
+ * memory the watched job has all but exhausted (an allocation could fail, or push
+ * the job over the edge), or a collection loop that cannot absorb the
+ * device-wide stall a cudaMalloc/cudaFree causes.  It needs no hbt_ctx and calls
+ * no cudaMalloc, cudaFree or any other allocating routine.
+ *
+ * Computes what the `deltas` output of hbt_counts_pipeline_dev holds:
+ * deltas[i][e] = getCount(e) of interval i minus that of interval i-1 (interval 0
+ * against 0), from reads[n_intervals][n_cpus][3+n_events].  reads and deltas are
+ * DEVICE pointers on the CURRENT device; work is queued on `cuda_stream` (NULL =
+ * the default stream) and is complete when that stream reaches it.
+ *
+ * Limits and rules:
+ *  - n_intervals * n_events must not exceed HBT_STATIC_SCRATCH_WORDS; larger
+ *    requests are refused with -E2BIG (split the trace by interval ranges and
+ *    carry the last scaled values yourself, or use hbt_counts_pipeline_dev).
+ *  - the first call on each device looks up the device address of the scratch
+ *    array (cudaGetSymbolAddress); make that first call during start-up, before
+ *    any stream capture begins on that device.
+ *  - all calls on one device share the one scratch array: two calls whose GPU
+ *    work overlaps (different streams, or different threads) corrupt each other.
+ *    Serialise them on one stream.  The array keeps the previous call's values
+ *    between calls; no call depends on them.
+ * Returns 0, -EINVAL (bad arguments), -E2BIG (see above), -ENODEV (no current CUDA
+ * device), -EIO (launch failure). */
+int hbt_counts_deltas_static_dev(const uint64_t* reads, uint64_t n_intervals, uint32_t n_cpus,
+                                 uint32_t n_events, uint64_t* deltas, void* cuda_stream);
+
 #ifdef __cplusplus
 }
 #endif
