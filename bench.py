@@ -39,6 +39,16 @@ METRIC = "perf records decoded+aggregated/sec"
 UNIT = "records/s"
 
 
+def load_traffic(kernel: str):
+    """dram bytes per launch of `kernel` from the last committed ncu capture, or None."""
+    p = os.path.join(ROOT, "profiles", "traffic.json")
+    try:
+        with open(p) as f:
+            return json.load(f)[kernel]["traffic_bytes"]
+    except Exception:
+        return None
+
+
 def load_peaks():
     p = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(p):
@@ -366,7 +376,9 @@ def main():
                    "sharding": "by CPU id, 256 CPUs per rank; NCCL all-reduce of record counters",
                    "slow_tiles": slow, "reruns": reruns},
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                     "frac": achieved / peak, "traffic": None, "kernel": "k_decode<IP_HISTOGRAM>",
+                     "frac": achieved / peak,
+                     "traffic": load_traffic("k_decode<IP_HISTOGRAM>") if args.agg == "hist" else None,
+                     "kernel": "k_decode<IP_HISTOGRAM>" if args.agg == "hist" else "k_decode<NONE>",
                      "kernel_ms": k_ms, "algorithmic_bytes": int(algo_bytes), "peak_source": peak_src,
                      "frac_of_nominal_8000": achieved / 8000.0},
         "gpu_launches": int(launches),
