@@ -223,7 +223,8 @@ def main():
     ap.add_argument("--cpus", type=int, default=256)
     ap.add_argument("--ring-mib", type=int, default=16)
     ap.add_argument("--ref-cpus", type=int, default=32, help="rings in the bounded CPU sample")
-    ap.add_argument("--hist-slots-per-cpu", type=int, default=327680)
+    ap.add_argument("--hist-slots-per-cpu", type=int, default=1 << 20,
+                    help="list capacity per CPU: distinct keys + the samples of one decode")
     ap.add_argument("--agg", default="hist", choices=["hist", "none"],
                     help="none: decode + counters only (diagnostic, not the headline workload)")
     ap.add_argument("--no-e2e", action="store_true")
@@ -267,7 +268,7 @@ def main():
 
     def step():
         if args.agg == "hist":
-            ctx.hist_clear()  # lazy: the decode kernel zeroes the table it fills
+            ctx.hist_clear()
         ctx.submit_rings_dev(bases_a, ring_bytes, tails_a, heads_a)
         ctx.decode(desc)
 
@@ -292,7 +293,7 @@ def main():
     if rank == 0:
         sampler.start()
     launches0 = ctx.launches
-    kernel_ms = []
+    kernel_ms, fold_ms = [], []
     if dist is not None:
         dist.barrier()
     torch.cuda.synchronize()
@@ -305,6 +306,8 @@ def main():
         # completing the decode (re-run check) is part of the step; it syncs the stream
         ctx.fetch_results()
         kernel_ms.append(ctx.decode_kernel_ms)
+        if args.agg == "hist":
+            fold_ms.append(ctx.hist_fold_kernel_ms)
     e1.record()
     torch.cuda.synchronize()
     if dist is not None:
@@ -362,8 +365,10 @@ def main():
 
     peak, peak_src = load_peaks()
     k_ms = sum(kernel_ms) / len(kernel_ms)
+    f_ms = sum(fold_ms) / len(fold_ms) if fold_ms else 0.0
+    span_ms = k_ms + f_ms  # decode + fold: the whole decode+aggregate sequence
     algo_bytes = window_bytes + 16 * distinct  # ring bytes once + 16 B per distinct key
-    achieved = algo_bytes / (k_ms * 1e-3) / 1e9
+    achieved = algo_bytes / (span_ms * 1e-3) / 1e9
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
         "warmup": max(args.warmup, 3), "ms_per_step": ms_step, "higher_is_better": True,
@@ -378,8 +383,9 @@ def main():
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
                      "frac": achieved / peak,
                      "traffic": load_traffic("k_decode<IP_HISTOGRAM>") if args.agg == "hist" else None,
-                     "kernel": "k_decode<IP_HISTOGRAM>" if args.agg == "hist" else "k_decode<NONE>",
-                     "kernel_ms": k_ms, "algorithmic_bytes": int(algo_bytes), "peak_source": peak_src,
+                     "kernel": "k_decode<IP_HISTOGRAM> + k_hist_aggregate" if args.agg == "hist" else "k_decode<NONE>",
+                     "kernel_ms": span_ms, "decode_kernel_ms": k_ms, "fold_kernel_ms": f_ms,
+                     "algorithmic_bytes": int(algo_bytes), "peak_source": peak_src,
                      "frac_of_nominal_8000": achieved / 8000.0},
         "gpu_launches": int(launches),
         "clocks": clocks,

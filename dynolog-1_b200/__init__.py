@@ -94,6 +94,7 @@ EXPORTS = [
     ("hbt_decode_reruns", C.c_uint32, [_P]),
     ("hbt_decode_slow_tiles", C.c_uint64, [_P]),
     ("hbt_decode_kernel_ms", C.c_float, [_P]),
+    ("hbt_hist_fold_kernel_ms", C.c_float, [_P]),
     ("hbt_fetch_rows", C.c_int64, [_P, C.c_uint32, _P, C.c_uint64]),
     ("hbt_rows_slabs_dev", C.c_int, [_P, C.c_uint32, C.POINTER(_P), _U64P, C.POINTER(C.c_uint32)]),
     ("hbt_rows_max_slabs", C.c_uint32, [_P]),
@@ -102,7 +103,8 @@ EXPORTS = [
     ("hbt_hist_clear", C.c_int, [_P]),
     ("hbt_hist_size", C.c_int64, [_P]),
     ("hbt_hist_fetch", C.c_int64, [_P, _P, C.c_uint64]),
-    ("hbt_hist_table_dev", C.c_int, [_P, C.POINTER(_P), _U64P]),
+    ("hbt_hist_lists_dev", C.c_int,
+     [_P, C.POINTER(_P), C.POINTER(_P), C.POINTER(C.c_uint32), C.POINTER(C.c_uint32)]),
     ("hbt_counts_reduce_dev", C.c_int, [_P, _P, C.c_uint64, C.c_uint32, C.c_uint32, _P]),
     ("hbt_counts_scale_dev", C.c_int,
      [_P, _P, C.c_uint64, C.c_uint32, _P, C.c_uint32, _P, _P, _P, _P, _P]),
@@ -263,6 +265,10 @@ class Context:
     @property
     def decode_kernel_ms(self) -> float:
         return float(self.lib.hbt_decode_kernel_ms(self.h))
+
+    @property
+    def hist_fold_kernel_ms(self) -> float:
+        return float(self.lib.hbt_hist_fold_kernel_ms(self.h))
 
     @property
     def slow_tiles(self) -> int:

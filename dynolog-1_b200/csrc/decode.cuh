@@ -102,12 +102,17 @@ struct CpuState {  // generator state across calls
   uint64_t carry_last[HBT_MAX_EVENTS];
 };
 
-struct HistTable {
-  ulonglong2* slots;      // {ip, pid | count<<32}; all-zero = empty
-  uint64_t slots_per_cpu; // any size < 2^32
-  uint64_t* zero_key;     // per-CPU count of key (ip=0, pid=0)
-  uint32_t* overflow;     // set when a probe sequence found no room
-  uint32_t* arrive;       // per-CPU: CTAs that finished zeroing their slice (zero_first)
+// (cpu,pid,ip) histogram storage: every CPU owns `buckets` append-only lists of
+// 16-byte entries {u64 ip; u32 pid; u32 count}; a key always lands in the list
+// its hash selects.  The decode kernel appends one entry (count 1) per sample;
+// k_hist_aggregate then folds every list in shared memory into distinct keys,
+// in place.  Lists accumulate over decodes until hbt_hist_clear.
+struct HistLists {
+  ulonglong2* entries;   // [n_cpus][buckets][cap]
+  uint32_t* cursors;     // [n_cpus][buckets]: entries in each list
+  uint32_t buckets;      // lists per CPU
+  uint32_t cap;          // entries per list
+  uint32_t* overflow;    // 1: a list ran out of room
 };
 
 struct DecodeParams {
@@ -116,9 +121,7 @@ struct DecodeParams {
   SegResult* results;
   const CpuState* state_in;
   hbt_decode_desc d;
-  HistTable hist;
-  uint32_t hist_inc;  // +1, or 0xFFFFFFFF to take a failed attempt back out
-  uint32_t hist_zero_first;  // the table is cleared by this launch (lazy hbt_hist_clear)
+  HistLists hist;
 };
 
 // ---------------------------------------------------------------------------
@@ -169,121 +172,68 @@ __device__ __forceinline__ int counter_of(uint32_t type, uint32_t handled) {
   }
 }
 
-// Global (cpu,pid,ip) table insert: lock-free, exact, one L2 round trip per new
-// key.  Slot = {u64 ip; u32 pid; u32 count}; all-zero = empty.  A 128-bit CAS of
-// the empty slot to {ip, pid, n} claims it and counts in one go; when the slot is
-// taken the CAS returns its key: same key -> fire-and-forget red.add on the
-// count, other key -> next slot (linear probing inside the CPU's sub-table, so
-// probes stay in the same 128-byte line most of the time).  The key (0,0) would
-// look like an empty slot and is counted in a per-CPU side counter instead.
-// n is a signed 32-bit increment (negative while a failed attempt is taken back
-// out); counts cannot wrap because the host refuses to add more than 2^32-1
-// samples to a table between two clears.
-__device__ __forceinline__ uint64_t hist_home_slot(const HistTable& t, uint64_t ip, uint32_t pid) {
-  const uint32_t h = (uint32_t)(mix64(ip ^ ((uint64_t)pid * 0x9E3779B97F4A7C15ull)) >> 32);
-  return ((uint64_t)h * t.slots_per_cpu) >> 32;
+__device__ __forceinline__ uint32_t hist_hash(uint64_t ip, uint32_t pid) {
+  return (uint32_t)(mix64(ip ^ ((uint64_t)pid * 0x9E3779B97F4A7C15ull)) >> 32);
 }
 
-// Probe from slot i on until the key is counted.
-__device__ __noinline__ void hist_probe_from(const HistTable& t, uint32_t cpu, uint64_t i,
-                                             uint64_t ip, uint32_t pid, uint32_t n) {
-  const uint64_t S = t.slots_per_cpu;
-  ulonglong2* base = t.slots + (uint64_t)cpu * S;
-  for (uint64_t probe = 0; probe < S; ++probe) {
-    uint64_t olo, ohi;
-    cas128_global(base + i, 0, 0, ip, (uint64_t)pid | ((uint64_t)n << 32), olo, ohi);
-    if (olo == 0 && ohi == 0) return;  // claimed, count = n
-    if (olo == ip && (uint32_t)ohi == pid) {
-      red_add_u32(reinterpret_cast<uint32_t*>(base + i) + 3, n);
-      return;
-    }
-    i = (i + 1 == S) ? 0 : i + 1;
+// Append one sample to the list of its bucket: one atomic on a cursor that lives
+// in L2 (the cursors of the CPUs in flight are a few KB) and one 16-byte store.
+// Neighbouring entries of a list are written close in time, so L2 merges them
+// into full sectors before they reach HBM.
+__device__ __forceinline__ void hist_append(const HistLists& t, uint32_t cpu, uint64_t ip,
+                                            uint32_t pid, uint32_t weight, uint32_t hash) {
+  const uint32_t b = (uint32_t)(((uint64_t)hash * t.buckets) >> 32);
+  const uint32_t list = cpu * t.buckets + b;
+  const uint32_t pos = atomicAdd(t.cursors + list, 1u);
+  if (pos < t.cap) {
+    t.entries[(uint64_t)list * t.cap + pos] =
+        make_ulonglong2(ip, (uint64_t)pid | ((uint64_t)weight << 32));
+  } else {
+    atomicExch(t.overflow, 1u);
   }
-  atomicExch(t.overflow, 1u);  // the CPU's sub-table is full
 }
 
-__device__ __forceinline__ void hist_insert_global(const HistTable& t, uint32_t cpu, uint64_t ip,
-                                                   uint32_t pid, uint32_t n) {
-  if (ip == 0 && pid == 0) {
-    atomicAdd(reinterpret_cast<unsigned long long*>(t.zero_key + cpu),
-              (unsigned long long)(long long)(int32_t)n);
-    return;
-  }
-  hist_probe_from(t, cpu, hist_home_slot(t, ip, pid), ip, pid, n);
-}
+// Shared-memory privatised (pid,ip) cache of one segment.  Its job is the heavy
+// hitters: a key that occurs thousands of times in a CPU's window would otherwise
+// append thousands of entries to one list.  Two-way set associative, a state word
+// per slot (0 empty, 1 being written, 2 ready).  A sample whose two slots hold other
+// keys -- or one in the middle of being written -- bypasses the cache and is appended
+// to its list directly, so nothing ever spins and every sample is counted exactly once.
+// Frequent keys show up while the cache is still mostly empty and keep their slot
+// for the rest of the segment.  Flushed to the lists (weighted entries) at segment end.
+constexpr int kCacheSlots = 1024;
 
-// A table insert in flight (HBT_KPENDING > 0 only).  The claiming CAS is issued
-// and its answer is looked at one tile later, so the L2/DRAM round trip overlaps
-// the next tile's parsing; a collision re-issues the CAS on the next slot and waits
-// another tile.  Measured on B200 (profiles/r1_notes.md): no faster than inserting
-// synchronously, because the table's L2/HBM atomic rate is the limit, not the
-// latency seen by one thread -- so the default build keeps HBT_KPENDING = 0.
-#ifndef HBT_KPENDING
-#define HBT_KPENDING 0
-#endif
-#ifndef HBT_HIST_CTAS_PER_SM
-#define HBT_HIST_CTAS_PER_SM 4
-#endif
-constexpr int kPending = HBT_KPENDING;
-struct PendingInsert {
-  uint64_t ip, olo, ohi;
-  uint32_t slot, pid;
-  uint32_t probes;  // 0 = free
+struct HistCache {
+  ulonglong2 slots[kCacheSlots];  // {ip, pid | count << 32}
+  uint32_t state[kCacheSlots];
 };
 
-__device__ __forceinline__ void hist_cas(const HistTable& t, uint32_t cpu, uint32_t n,
-                                         PendingInsert& pd) {
-  cas128_global(t.slots + (uint64_t)cpu * t.slots_per_cpu + pd.slot, 0, 0, pd.ip,
-                (uint64_t)pd.pid | ((uint64_t)n << 32), pd.olo, pd.ohi);
-}
-
-__device__ __forceinline__ void hist_issue(const HistTable& t, uint32_t cpu, uint64_t ip,
-                                           uint32_t pid, uint32_t n, PendingInsert& pd) {
-  pd.slot = (uint32_t)hist_home_slot(t, ip, pid);
-  pd.ip = ip;
-  pd.pid = pid;
-  pd.probes = 1;
-  hist_cas(t, cpu, n, pd);
-}
-
-// Look at the answer of a pending CAS: done, count on the existing key, or move on.
-__device__ __forceinline__ void hist_advance(const HistTable& t, uint32_t cpu, uint32_t n,
-                                             PendingInsert& pd) {
-  if (pd.probes == 0) return;
-  if (pd.olo == 0 && pd.ohi == 0) {  // the CAS claimed the slot and counted
-    pd.probes = 0;
-    return;
-  }
-  if (pd.olo == pd.ip && (uint32_t)pd.ohi == pd.pid) {
-    red_add_u32(reinterpret_cast<uint32_t*>(t.slots + (uint64_t)cpu * t.slots_per_cpu + pd.slot) + 3,
-                n);
-    pd.probes = 0;
-    return;
-  }
-  if (pd.probes >= t.slots_per_cpu) {  // went all the way round: the sub-table is full
-    atomicExch(t.overflow, 1u);
-    pd.probes = 0;
-    return;
-  }
-  pd.slot = pd.slot + 1 == (uint32_t)t.slots_per_cpu ? 0 : pd.slot + 1;
-  ++pd.probes;
-  hist_cas(t, cpu, n, pd);
-}
-
-// Finish a pending insert synchronously (segment end).
-__device__ __forceinline__ void hist_drain(const HistTable& t, uint32_t cpu, uint32_t n,
-                                           PendingInsert& pd) {
-  if (pd.probes == 0) return;
-  if (!(pd.olo == 0 && pd.ohi == 0)) {
-    if (pd.olo == pd.ip && (uint32_t)pd.ohi == pd.pid) {
-      red_add_u32(
-          reinterpret_cast<uint32_t*>(t.slots + (uint64_t)cpu * t.slots_per_cpu + pd.slot) + 3, n);
-    } else {
-      const uint64_t nx = pd.slot + 1 == t.slots_per_cpu ? 0 : pd.slot + 1;
-      hist_probe_from(t, cpu, nx, pd.ip, pd.pid, n);
+__device__ __forceinline__ void hist_count(const HistLists& t, HistCache& c, uint32_t cpu,
+                                           uint64_t ip, uint32_t pid) {
+  const uint32_t hash = hist_hash(ip, pid);
+  uint32_t i = (hash ^ (hash >> 16)) & (kCacheSlots - 2);  // 2-way: slots i, i + 1
+#pragma unroll
+  for (int way = 0; way < 2; ++way, ++i) {
+    uint32_t st = *reinterpret_cast<volatile uint32_t*>(c.state + i);
+    if (st == 0) {
+      st = atomicCAS(c.state + i, 0u, 1u);
+      if (st == 0) {  // claimed: publish the key, count it
+        c.slots[i].x = ip;
+        reinterpret_cast<uint32_t*>(&c.slots[i].y)[0] = pid;
+        atomicAdd(reinterpret_cast<uint32_t*>(&c.slots[i].y) + 1, 1u);
+        __threadfence_block();
+        *reinterpret_cast<volatile uint32_t*>(c.state + i) = 2;
+        return;
+      }
+    }
+    if (st != 2) break;  // being written by another thread: do not wait for it
+    const volatile ulonglong2* vs = c.slots + i;
+    if (vs->x == ip && (uint32_t)vs->y == pid) {
+      atomicAdd(reinterpret_cast<uint32_t*>(&c.slots[i].y) + 1, 1u);
+      return;
     }
   }
-  pd.probes = 0;
+  hist_append(t, cpu, ip, pid, 1, hash);
 }
 
 // ---------------------------------------------------------------------------
@@ -394,8 +344,9 @@ __device__ void consume_sequential(const DecodeParams& p, const RingDesc& ring,
           break;
         }
         if (AGG == HBT_AGG_IP_HISTOGRAM) {
-          hist_insert_global(p.hist, seg.cpu, ring_word_g(ring, pos + 8),
-                             (uint32_t)ring_word_g(ring, pos + 16), p.hist_inc);
+          const uint64_t ip = ring_word_g(ring, pos + 8);
+          const uint32_t pid = (uint32_t)ring_word_g(ring, pos + 16);
+          hist_append(p.hist, seg.cpu, ip, pid, 1, hist_hash(ip, pid));
         }
       }
       ++st.counters[HBT_CNT_SAMPLE];
@@ -447,10 +398,12 @@ __device__ __forceinline__ uint32_t sub_of_word(uint32_t w) {
 }
 
 template <int AGG>
-__global__ void __launch_bounds__(kThreads, AGG == HBT_AGG_IP_HISTOGRAM ? HBT_HIST_CTAS_PER_SM : 4) k_decode(const DecodeParams p) {
+__global__ void __launch_bounds__(kThreads, 4) k_decode(const DecodeParams p) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   uint8_t* stages = smem_raw;  // kStages * kTile
   Smem& sm = *reinterpret_cast<Smem*>(smem_raw + kStages * kTile);
+  HistCache& cache =
+      *reinterpret_cast<HistCache*>(smem_raw + kStages * kTile + ((sizeof(Smem) + 15) & ~15ull));
 
   const SegDesc seg = p.segs[blockIdx.x];
   const RingDesc ring = p.rings[seg.cpu];
@@ -482,27 +435,13 @@ __global__ void __launch_bounds__(kThreads, AGG == HBT_AGG_IP_HISTOGRAM ? HBT_HI
     st.size_max = 0;
   }
   sm.expect[tid] = kNoRel;
-  bool table_ready = true;
-  if (AGG == HBT_AGG_IP_HISTOGRAM && p.hist_zero_first) {
-    // Lazy hbt_hist_clear: the CTAs of a CPU zero that CPU's sub-table just before
-    // they fill it, so the lines are born in L2 instead of being written by a
-    // memset, evicted, and read back from HBM at first touch.  Relies on CTAs
-    // being dispatched in blockIdx order (the CTAs a CTA waits for have lower or
-    // neighbouring indices and never wait for later ones).
-    const uint64_t S = p.hist.slots_per_cpu;
-    const uint64_t lo = S * seg.seg / ring.n_seg, hi = S * (seg.seg + 1) / ring.n_seg;
-    ulonglong2* base = p.hist.slots + (uint64_t)seg.cpu * S;
-    for (uint64_t i = lo + tid; i < hi; i += kThreads) base[i] = make_ulonglong2(0, 0);
-    if (seg.seg == 0 && tid == 0) p.hist.zero_key[seg.cpu] = 0;
-    __threadfence();
-    table_ready = false;
+  if (AGG == HBT_AGG_IP_HISTOGRAM) {
+    for (int i = tid; i < kCacheSlots; i += kThreads) {
+      cache.slots[i] = make_ulonglong2(0, 0);
+      cache.state[i] = 0;
+    }
   }
   __syncthreads();
-  if (AGG == HBT_AGG_IP_HISTOGRAM && p.hist_zero_first && tid == 0)
-    atomicAdd(p.hist.arrive + seg.cpu, 1u);
-  PendingInsert pd[kPending > 0 ? kPending : 1];
-#pragma unroll
-  for (int i = 0; i < kPending; ++i) pd[i].probes = 0;
 
   const uint32_t n_tiles = (uint32_t)(seg.tile_end - seg.tile_begin);
   // Records are decoded while they START before seg_limit.
@@ -764,14 +703,6 @@ __global__ void __launch_bounds__(kThreads, AGG == HBT_AGG_IP_HISTOGRAM ? HBT_HI
       if (!slow || attempt == 1) break;
       // the stride prediction did not hold: guess again by scanning
     }
-    if (AGG == HBT_AGG_IP_HISTOGRAM && !table_ready) {
-      // before the first insert: every CTA of this CPU has zeroed its slice
-      if (tid == 0) {
-        while (ld_acquire_u32(p.hist.arrive + seg.cpu) < ring.n_seg) __nanosleep(64);
-      }
-      __syncthreads();
-      table_ready = true;
-    }
     if (!stopped && !slow) {
       // ---- phase 3: aggregate my records ----------------------------------------
       uint64_t row_i = 0;
@@ -783,26 +714,11 @@ __global__ void __launch_bounds__(kThreads, AGG == HBT_AGG_IP_HISTOGRAM ? HBT_HI
       my_rec += __popc(mask);
       my_sample += __popc(smask);
       if (AGG == HBT_AGG_IP_HISTOGRAM) {
-        // answers of the CASes issued one tile ago; collisions move on one slot
-#pragma unroll
-        for (int i = 0; i < kPending; ++i) hist_advance(p.hist, seg.cpu, p.hist_inc, pd[i]);
         uint32_t m = smask;
         while (m) {
           const uint32_t pos = sb + 8u * (__ffs(m) - 1);
           m &= m - 1;
-          const uint64_t ip = tv.at(pos + 8);
-          const uint32_t pid = (uint32_t)tv.at(pos + 16);
-          bool placed = false;
-          if (!(ip == 0 && pid == 0)) {
-#pragma unroll
-            for (int i = 0; i < kPending; ++i) {
-              if (!placed && pd[i].probes == 0) {
-                hist_issue(p.hist, seg.cpu, ip, pid, p.hist_inc, pd[i]);
-                placed = true;
-              }
-            }
-          }
-          if (!placed) hist_insert_global(p.hist, seg.cpu, ip, pid, p.hist_inc);
+          hist_count(p.hist, cache, seg.cpu, tv.at(pos + 8), (uint32_t)tv.at(pos + 16));
         }
       }
       uint32_t m = AGG == HBT_AGG_COUNT_DELTAS ? (smask | omask) : omask;
@@ -891,8 +807,13 @@ __global__ void __launch_bounds__(kThreads, AGG == HBT_AGG_IP_HISTOGRAM ? HBT_HI
 
   // ---- segment epilogue --------------------------------------------------------
   if (AGG == HBT_AGG_IP_HISTOGRAM) {
-#pragma unroll
-    for (int i = 0; i < kPending; ++i) hist_drain(p.hist, seg.cpu, p.hist_inc, pd[i]);
+    for (int i = tid; i < kCacheSlots; i += kThreads) {
+      if (cache.state[i] == 2) {
+        const ulonglong2 e = cache.slots[i];
+        hist_append(p.hist, seg.cpu, e.x, (uint32_t)e.y, (uint32_t)(e.y >> 32),
+                    hist_hash(e.x, (uint32_t)e.y));
+      }
+    }
   }
   my_rec = __reduce_add_sync(0xffffffffu, my_rec);
   my_sample = __reduce_add_sync(0xffffffffu, my_sample);
@@ -1139,32 +1060,98 @@ __global__ void __launch_bounds__(64)
   clamp_head[c] = pos;
 }
 
-// Compact the occupied slots of the table into entries (cpu = cpu_base + local).
-__global__ void __launch_bounds__(256)
-    k_hist_compact(const HistTable t, uint32_t n_cpus, uint32_t cpu_base, hbt_hist_entry* out,
-                   unsigned long long* n_out, uint64_t cap) {
-  const uint64_t total = t.slots_per_cpu * n_cpus;
-  for (uint64_t g = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; g < total + n_cpus;
-       g += (uint64_t)gridDim.x * blockDim.x) {
-    hbt_hist_entry e;
-    if (g < total) {
-      const ulonglong2 s = t.slots[g];
-      const uint32_t cnt = (uint32_t)(s.y >> 32);
-      if (cnt == 0) continue;
-      e.ip = s.x;
-      e.pid = (uint32_t)s.y;
-      e.cpu = cpu_base + (uint32_t)(g / t.slots_per_cpu);
-      e.count = cnt;
-    } else {
-      const uint32_t c = (uint32_t)(g - total);
-      if (t.zero_key[c] == 0) continue;
-      e.ip = 0;
-      e.pid = 0;
-      e.cpu = cpu_base + c;
-      e.count = t.zero_key[c];
+// k_hist_aggregate: one CTA per (cpu, bucket) list.  Folds the list -- distinct
+// entries left by earlier decodes followed by the raw samples (count 1) the last
+// decode appended -- into distinct keys with a shared-memory hash table, writes
+// them back to the front of the same list and sets the cursor to their number.
+// cap <= kAggSlots / 2, so the table can never fill up.
+constexpr uint32_t kAggSlots = 4096;   // 64 KiB of 16-byte slots
+constexpr int kAggThreads = 256;
+constexpr int kAggBatch = 4;           // independent loads in flight per thread
+
+__global__ void __launch_bounds__(kAggThreads) k_hist_aggregate(const HistLists t, uint32_t n_lists) {
+  extern __shared__ __align__(16) uint8_t agg_smem[];
+  ulonglong2* slots = reinterpret_cast<ulonglong2*>(agg_smem);
+  __shared__ uint32_t s_out;
+  const uint32_t tid = threadIdx.x, lane = tid & 31;
+  const uint32_t s0 = smem_u32(slots);
+  for (uint32_t list = blockIdx.x; list < n_lists; list += gridDim.x) {
+    const uint32_t n = min(t.cursors[list], t.cap);
+    if (n <= 1) continue;  // nothing to fold (n is uniform over the CTA)
+    // table size: power of two >= 1.5 n (load <= 2/3; n <= cap = kAggSlots / 2)
+    uint32_t T = 64;
+    while (2 * T < 3 * n) T <<= 1;
+    for (uint32_t i = tid; i < T; i += kAggThreads) slots[i] = make_ulonglong2(0, 0);
+    if (tid == 0) s_out = 0;
+    __syncthreads();
+    ulonglong2* lst = t.entries + (uint64_t)list * t.cap;
+    for (uint32_t base = 0; base < n; base += kAggThreads * kAggBatch) {
+      ulonglong2 e[kAggBatch];
+#pragma unroll
+      for (int k = 0; k < kAggBatch; ++k) {
+        const uint32_t i = base + k * kAggThreads + tid;
+        e[k] = i < n ? ld_stream_v2u64(lst + i) : make_ulonglong2(0, 0);
+      }
+#pragma unroll
+      for (int k = 0; k < kAggBatch; ++k) {
+        const uint32_t pid = (uint32_t)e[k].y, w = (uint32_t)(e[k].y >> 32);
+        if (w == 0) continue;  // padding of the last batch (a real entry has weight >= 1)
+        // second hash: the bucket already consumed the top bits of hist_hash
+        uint32_t h = (uint32_t)mix64(e[k].x * 0xD6E8FEB86659FD93ull + pid) & (T - 1);
+        for (;;) {
+          uint64_t olo, ohi;
+          cas128_shared(s0 + h * 16, 0, 0, e[k].x, e[k].y, olo, ohi);
+          if (olo == 0 && ohi == 0) break;  // claimed with weight w
+          if (olo == e[k].x && (uint32_t)ohi == pid) {
+            atomicAdd(reinterpret_cast<uint32_t*>(slots + h) + 3, w);
+            break;
+          }
+          h = (h + 1) & (T - 1);
+        }
+      }
     }
-    const unsigned long long i = atomicAdd(n_out, 1ull);
-    if (out && i < cap) out[i] = e;
+    __syncthreads();
+    // write the distinct keys back to the front of the list (one cursor bump per warp)
+    for (uint32_t i0 = 0; i0 < T; i0 += kAggThreads) {
+      const bool in = i0 + tid < T;  // T can be smaller than the CTA
+      const ulonglong2 e = in ? slots[i0 + tid] : make_ulonglong2(0, 0);
+      const bool used = in && (e.y >> 32) != 0;
+      const uint32_t m = __ballot_sync(0xffffffffu, used);
+      uint32_t wbase = 0;
+      if (lane == 0 && m) wbase = atomicAdd(&s_out, (uint32_t)__popc(m));
+      wbase = __shfl_sync(0xffffffffu, wbase, 0);
+      if (used) lst[wbase + __popc(m & ((1u << lane) - 1))] = e;
+    }
+    __syncthreads();
+    if (tid == 0) t.cursors[list] = s_out;
+    __syncthreads();
+  }
+}
+
+// Gather every list into one array of entries (cpu = cpu_base + local index).
+__global__ void __launch_bounds__(128)
+    k_hist_gather(const HistLists t, uint32_t n_lists, uint32_t cpu_base, hbt_hist_entry* out,
+                  unsigned long long* n_out, uint64_t cap_out) {
+  __shared__ unsigned long long s_base;
+  for (uint32_t list = blockIdx.x; list < n_lists; list += gridDim.x) {
+    const uint32_t n = min(t.cursors[list], t.cap);
+    if (threadIdx.x == 0) s_base = atomicAdd(n_out, (unsigned long long)n);
+    __syncthreads();
+    const unsigned long long base = s_base;
+    if (out) {
+      const ulonglong2* lst = t.entries + (uint64_t)list * t.cap;
+      for (uint32_t i = threadIdx.x; i < n; i += blockDim.x) {
+        if (base + i >= cap_out) break;
+        const ulonglong2 e = lst[i];
+        hbt_hist_entry h;
+        h.ip = e.x;
+        h.pid = (uint32_t)e.y;
+        h.cpu = cpu_base + list / t.buckets;
+        h.count = e.y >> 32;
+        out[base + i] = h;
+      }
+    }
+    __syncthreads();
   }
 }
 

@@ -118,17 +118,17 @@ struct hbt_ctx {
   hbt_decode_desc desc{};
   uint32_t reruns = 0;
   cudaEvent_t ev_k0 = nullptr, ev_k1 = nullptr;  // around the decode kernel
+  cudaEvent_t ev_f0 = nullptr, ev_f1 = nullptr;  // around the histogram fold kernel
+  bool fold_timed = false;
 
-  // histogram
-  DevBuf<ulonglong2> hist_slots;
-  DevBuf<uint64_t> hist_zero;
+  // histogram: per-(cpu,bucket) lists (see HistLists)
+  DevBuf<ulonglong2> hist_entries;
+  DevBuf<uint32_t> hist_cursors, hist_cursors_snap;
   DevBuf<uint32_t> hist_overflow;
-  DevBuf<uint32_t> hist_arrive;
-  uint64_t hist_slots_per_cpu = 0;
-  bool hist_needs_zero = false;   // hbt_hist_clear is lazy: the next decode zeroes in-kernel
-  bool hist_zero_this_decode = false;
-  bool tiled_zero = true;
-  uint64_t hist_samples = 0;      // upper bound of samples added since the last clear
+  uint32_t hist_buckets = 0, hist_cap = 0;
+  bool hist_pending_fold = false;  // the last decode appended raw samples not yet folded
+  bool agg_attr_set = false;
+  uint64_t hist_samples = 0;       // upper bound of samples added since the last clear
   DevBuf<hbt_hist_entry> hist_out;
   DevBuf<unsigned long long> hist_n;
 
@@ -165,8 +165,9 @@ int cuda_fail(hbt_ctx* c, cudaError_t e, const char* what) {
 bool is_pow2(uint64_t x) { return x && !(x & (x - 1)); }
 
 size_t decode_smem_bytes(int agg) {
-  (void)agg;
-  return (size_t)kStages * kTile + ((sizeof(Smem) + 15) & ~size_t(15));
+  size_t s = (size_t)kStages * kTile + ((sizeof(Smem) + 15) & ~size_t(15));
+  if (agg == HBT_AGG_IP_HISTOGRAM) s += sizeof(HistCache);
+  return s;
 }
 
 int validate_desc(hbt_ctx* ctx, const hbt_decode_desc* d) {
@@ -184,7 +185,7 @@ int validate_desc(hbt_ctx* ctx, const hbt_decode_desc* d) {
   if (d->aggregate == HBT_AGG_IP_HISTOGRAM) {
     if (d->sample_layout != HBT_SAMPLE_IP || !(d->handled_mask & HBT_H_SAMPLE))
       return fail(ctx, -EINVAL, "IP_HISTOGRAM needs handled IP SAMPLE records");
-    if (ctx->hist_slots_per_cpu == 0) return fail(ctx, -EINVAL, "hbt_hist_configure first");
+    if (ctx->hist_buckets == 0) return fail(ctx, -EINVAL, "hbt_hist_configure first");
   }
   if (d->sample_layout == HBT_SAMPLE_IP &&
       (d->ip_sample_bytes < 40 || (d->ip_sample_bytes & 7) || d->ip_sample_bytes > 65528))
@@ -216,9 +217,8 @@ int build_tables(hbt_ctx* ctx, const uint64_t* clamp_head, const int64_t* clamp_
   // 8 tiles (128 KiB) per segment
   const uint64_t target_ctas = (uint64_t)ctx->sm_count * 8;
   uint32_t segs_per_cpu = active ? (uint32_t)((target_ctas + active - 1) / active) : 1;
-  // the histogram wants few CPUs in flight at a time (their sub-tables share L2):
-  // more, shorter segments per CPU, dispatched CPU-major
-  if (d.aggregate == HBT_AGG_IP_HISTOGRAM && segs_per_cpu < 64) segs_per_cpu = 64;
+  // the histogram's per-segment cache of hot keys wants short segments
+  if (d.aggregate == HBT_AGG_IP_HISTOGRAM && segs_per_cpu < 16) segs_per_cpu = 16;
   if (const char* e = getenv("HBT_SEGS_PER_CPU")) segs_per_cpu = (uint32_t)atoi(e);  // tuning aid
   if (segs_per_cpu > kMaxSegsPerCpu) segs_per_cpu = kMaxSegsPerCpu;
   if (segs_per_cpu < 1) segs_per_cpu = 1;
@@ -317,21 +317,18 @@ int build_tables(hbt_ctx* ctx, const uint64_t* clamp_head, const int64_t* clamp_
 }
 
 template <int AGG>
-int launch_decode_agg(hbt_ctx* ctx, uint32_t hist_inc) {
+int launch_decode_agg(hbt_ctx* ctx) {
   DecodeParams p{};
   p.rings = ctx->d_rings.p;
   p.segs = ctx->d_segs.p;
   p.results = ctx->d_results.p;
   p.state_in = ctx->state[ctx->cur].p;
   p.d = ctx->desc;
-  p.hist.slots = ctx->hist_slots.p;
-  p.hist.slots_per_cpu = ctx->hist_slots_per_cpu;
-  p.hist.zero_key = ctx->hist_zero.p;
+  p.hist.entries = ctx->hist_entries.p;
+  p.hist.cursors = ctx->hist_cursors.p;
+  p.hist.buckets = ctx->hist_buckets;
+  p.hist.cap = ctx->hist_cap;
   p.hist.overflow = ctx->hist_overflow.p;
-  p.hist.arrive = ctx->hist_arrive.p;
-  p.hist_inc = hist_inc;
-  p.hist_zero_first =
-      (AGG == HBT_AGG_IP_HISTOGRAM && ctx->hist_zero_this_decode && ctx->tiled && ctx->tiled_zero) ? 1 : 0;
   if (ctx->n_segs == 0) return 0;
   if (ctx->tiled) {
     const size_t smem = decode_smem_bytes(AGG);
@@ -340,9 +337,9 @@ int launch_decode_agg(hbt_ctx* ctx, uint32_t hist_inc) {
                               (int)smem));
       ctx->attr_set[AGG] = true;
     }
-    if (hist_inc == 1) CU(cudaEventRecord(ctx->ev_k0, ctx->stream));
+    CU(cudaEventRecord(ctx->ev_k0, ctx->stream));
     k_decode<AGG><<<ctx->n_segs, kThreads, smem, ctx->stream>>>(p);
-    if (hist_inc == 1) CU(cudaEventRecord(ctx->ev_k1, ctx->stream));
+    CU(cudaEventRecord(ctx->ev_k1, ctx->stream));
   } else {
     k_decode_small<AGG><<<(ctx->n_segs + 31) / 32, 32, 0, ctx->stream>>>(p, ctx->n_segs);
   }
@@ -351,11 +348,11 @@ int launch_decode_agg(hbt_ctx* ctx, uint32_t hist_inc) {
   return 0;
 }
 
-int launch_decode(hbt_ctx* ctx, uint32_t hist_inc) {
+int launch_decode(hbt_ctx* ctx) {
   switch (ctx->desc.aggregate) {
-    case HBT_AGG_NONE: return launch_decode_agg<HBT_AGG_NONE>(ctx, hist_inc);
-    case HBT_AGG_COUNT_DELTAS: return launch_decode_agg<HBT_AGG_COUNT_DELTAS>(ctx, hist_inc);
-    default: return launch_decode_agg<HBT_AGG_IP_HISTOGRAM>(ctx, hist_inc);
+    case HBT_AGG_NONE: return launch_decode_agg<HBT_AGG_NONE>(ctx);
+    case HBT_AGG_COUNT_DELTAS: return launch_decode_agg<HBT_AGG_COUNT_DELTAS>(ctx);
+    default: return launch_decode_agg<HBT_AGG_IP_HISTOGRAM>(ctx);
   }
 }
 
@@ -386,31 +383,42 @@ int launch_finalize(hbt_ctx* ctx) {
 }
 
 // Launch decode + finalize for the tables currently uploaded.
-int run_once(hbt_ctx* ctx, uint32_t hist_inc) {
+int run_once(hbt_ctx* ctx) {
   CU(cudaMemsetAsync(ctx->d_flags.p, 0, 4 * sizeof(uint32_t), ctx->stream));
   CU(cudaMemsetAsync(ctx->d_clamp_head.p, 0xFF, ctx->n_cpus * sizeof(uint64_t), ctx->stream));
   CU(cudaMemsetAsync(ctx->d_forced.p, 0xFF, (ctx->n_segs ? ctx->n_segs : 1) * sizeof(uint64_t),
                      ctx->stream));
-  if (ctx->desc.aggregate == HBT_AGG_IP_HISTOGRAM && ctx->hist_zero_this_decode) {
-    // lazy clear: tiled decodes zero each CPU's sub-table in-kernel; CPUs without a
-    // segment (and the untiled small-ring path) are cleared from here
-    const size_t per = ctx->hist_slots_per_cpu * sizeof(ulonglong2);
-    if (getenv("HBT_NO_ZERO_FIRST")) ctx->tiled_zero = false;  // tuning aid
-    if (!ctx->tiled || !ctx->tiled_zero) {
-      CU(cudaMemsetAsync(ctx->hist_slots.p, 0, per * ctx->n_cpus, ctx->stream));
-    } else {
-      CU(cudaMemsetAsync(ctx->hist_arrive.p, 0, ctx->n_cpus * sizeof(uint32_t), ctx->stream));
-      for (uint32_t c = 0; c < ctx->n_cpus; ++c)
-        if (ctx->h_rings.p[c].n_seg == 0)
-          CU(cudaMemsetAsync(ctx->hist_slots.p + (size_t)c * ctx->hist_slots_per_cpu, 0, per,
-                             ctx->stream));
-    }
-    CU(cudaMemsetAsync(ctx->hist_zero.p, 0, ctx->n_cpus * sizeof(uint64_t), ctx->stream));
-  }
-  int rc = launch_decode(ctx, hist_inc);
+  int rc = launch_decode(ctx);
   if (rc) return rc;
-  if (hist_inc != 1) return 0;  // taking a failed attempt back out: no finalize
   return launch_finalize(ctx);
+}
+
+size_t hist_lists(const hbt_ctx* ctx) { return (size_t)ctx->n_cpus * ctx->hist_buckets; }
+
+HistLists hist_view(hbt_ctx* ctx) {
+  return HistLists{ctx->hist_entries.p, ctx->hist_cursors.p, ctx->hist_buckets, ctx->hist_cap,
+                   ctx->hist_overflow.p};
+}
+
+// Fold the raw samples the last decode appended into distinct keys (k_hist_aggregate).
+int hist_fold(hbt_ctx* ctx) {
+  if (!ctx->hist_pending_fold) return 0;
+  const size_t smem = (size_t)kAggSlots * sizeof(ulonglong2);
+  if (!ctx->agg_attr_set) {
+    CU(cudaFuncSetAttribute(k_hist_aggregate, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    ctx->agg_attr_set = true;
+  }
+  const uint32_t n = (uint32_t)hist_lists(ctx);
+  uint32_t grid = (uint32_t)ctx->sm_count * 3 * 8;
+  if (grid > n) grid = n;
+  CU(cudaEventRecord(ctx->ev_f0, ctx->stream));
+  k_hist_aggregate<<<grid, kAggThreads, smem, ctx->stream>>>(hist_view(ctx), n);
+  CU(cudaEventRecord(ctx->ev_f1, ctx->stream));
+  ctx->fold_timed = true;
+  ++ctx->launches;
+  CU(cudaGetLastError());
+  ctx->hist_pending_fold = false;
+  return 0;
 }
 
 }  // namespace
@@ -447,6 +455,8 @@ int hbt_create(hbt_ctx** out, int device, uint32_t max_cpus, uint32_t max_events
   ctx->stream = ctx->own_stream;
   cudaEventCreate(&ctx->ev_k0);
   cudaEventCreate(&ctx->ev_k1);
+  cudaEventCreate(&ctx->ev_f0);
+  cudaEventCreate(&ctx->ev_f1);
   *out = ctx;
   return 0;
 }
@@ -478,10 +488,10 @@ void hbt_destroy(hbt_ctx* ctx) {
   ctx->h_clamp_head.release();
   ctx->h_clamp_ret.release();
   ctx->h_flags.release();
-  ctx->hist_slots.release();
-  ctx->hist_zero.release();
+  ctx->hist_entries.release();
+  ctx->hist_cursors.release();
+  ctx->hist_cursors_snap.release();
   ctx->hist_overflow.release();
-  ctx->hist_arrive.release();
   ctx->hist_out.release();
   ctx->hist_n.release();
   ctx->d_ratios.release();
@@ -493,6 +503,8 @@ void hbt_destroy(hbt_ctx* ctx) {
   ctx->c_ratio.release();
   if (ctx->ev_k0) cudaEventDestroy(ctx->ev_k0);
   if (ctx->ev_k1) cudaEventDestroy(ctx->ev_k1);
+  if (ctx->ev_f0) cudaEventDestroy(ctx->ev_f0);
+  if (ctx->ev_f1) cudaEventDestroy(ctx->ev_f1);
   if (ctx->own_stream) cudaStreamDestroy(ctx->own_stream);
   delete ctx;
 }
@@ -642,22 +654,21 @@ int hbt_decode(hbt_ctx* ctx, const hbt_decode_desc* desc) {
   if (rc) return rc;
   ctx->desc = *desc;
   if (ctx->desc.aggregate != HBT_AGG_COUNT_DELTAS) ctx->desc.n_events = 0;
-  ctx->hist_zero_this_decode = false;
   if (ctx->desc.aggregate == HBT_AGG_IP_HISTOGRAM) {
-    // 32-bit counts in the table: refuse anything that could wrap one
+    // 32-bit counts in the lists: refuse anything that could wrap one
     uint64_t bound = 0;
     for (const Window& w : ctx->win)
       if (w.active && w.head > w.tail) bound += (w.head - w.tail) / ctx->desc.ip_sample_bytes + 1;
-    if (ctx->hist_needs_zero) ctx->hist_samples = 0;
     if (ctx->hist_samples + bound > 0xFFFFFFFFull)
       return fail(ctx, -EOVERFLOW, "more than 2^32-1 samples since hbt_hist_clear");
     ctx->hist_samples += bound;
-    ctx->hist_zero_this_decode = ctx->hist_needs_zero;
-    ctx->hist_needs_zero = false;
+    // the lists as they are now: a re-run starts again from here
+    CU(cudaMemcpyAsync(ctx->hist_cursors_snap.p, ctx->hist_cursors.p,
+                       hist_lists(ctx) * sizeof(uint32_t), cudaMemcpyDeviceToDevice, ctx->stream));
   }
   rc = build_tables(ctx, nullptr, nullptr, nullptr);
   if (rc) return rc;
-  rc = run_once(ctx, 1);
+  rc = run_once(ctx);
   if (rc) return rc;
   ctx->pending = true;
   ctx->have_results = false;
@@ -682,12 +693,10 @@ static int complete_decode(hbt_ctx* ctx) {
     if (ctx->h_flags.p[0] == 0) break;
     if (iter > 4 * kMaxSegsPerCpu + 8) return fail(ctx, -EIO, "decode re-run did not converge");
     ++ctx->reruns;
-    // take the failed attempt back out of the shared table
-    if (ctx->desc.aggregate == HBT_AGG_IP_HISTOGRAM && !ctx->hist_zero_this_decode) {
-      // (a decode that clears the table first simply clears it again)
-      int rc = launch_decode(ctx, 0xFFFFFFFFu);
-      if (rc) return rc;
-    }
+    // forget what the failed attempt appended to the histogram lists
+    if (ctx->desc.aggregate == HBT_AGG_IP_HISTOGRAM)
+      CU(cudaMemcpyAsync(ctx->hist_cursors.p, ctx->hist_cursors_snap.p,
+                         hist_lists(ctx) * sizeof(uint32_t), cudaMemcpyDeviceToDevice, ctx->stream));
     // locate cuts for a finite max_num_records, then fetch clamps + forced entries
     k_locate<<<(C + 63) / 64, 64, 0, ctx->stream>>>(ctx->d_rings.p, C, ctx->d_clamp_head.p,
                                                    ctx->d_locate_from.p, ctx->d_locate_skip.p);
@@ -714,10 +723,14 @@ static int complete_decode(hbt_ctx* ctx) {
     }
     int rc = build_tables(ctx, have_clamp ? clamp_head.data() : nullptr, clamp_ret.data(), &forced);
     if (rc) return rc;
-    rc = run_once(ctx, 1);
+    rc = run_once(ctx);
     if (rc) return rc;
   }
-  // success: commit the generator state, fetch results
+  // success: fold the appended samples, commit the generator state, fetch results
+  if (ctx->desc.aggregate == HBT_AGG_IP_HISTOGRAM) {
+    ctx->hist_pending_fold = true;
+    if (int rc = hist_fold(ctx)) return rc;
+  }
   ctx->cur ^= 1;
   CU(cudaMemcpyAsync(ctx->h_out.p, ctx->d_out.p, C * sizeof(hbt_cpu_result),
                      cudaMemcpyDeviceToHost, ctx->stream));
@@ -750,8 +763,7 @@ int hbt_fetch_results(hbt_ctx* ctx, hbt_cpu_result* out, uint32_t cap) {
   if (ctx->desc.aggregate == HBT_AGG_IP_HISTOGRAM) {
     uint32_t ov = 0;
     CU(cudaMemcpy(&ov, ctx->hist_overflow.p, sizeof(ov), cudaMemcpyDeviceToHost));
-    if (ov == 1) return fail(ctx, -ENOSPC, "histogram table full: hbt_hist_configure a larger one");
-    if (ov == 2) return fail(ctx, -EOVERFLOW, "a histogram count exceeded 2^32-1");
+    if (ov) return fail(ctx, -ENOSPC, "a histogram list is full: hbt_hist_configure more capacity");
   }
   return (int)ctx->n_cpus;
 }
@@ -763,6 +775,17 @@ float hbt_decode_kernel_ms(hbt_ctx* ctx) {
   float ms = -1.0f;
   if (cudaEventSynchronize(ctx->ev_k1) != cudaSuccess) return -1.0f;
   if (cudaEventElapsedTime(&ms, ctx->ev_k0, ctx->ev_k1) != cudaSuccess) {
+    cudaGetLastError();
+    return -1.0f;
+  }
+  return ms;
+}
+
+float hbt_hist_fold_kernel_ms(hbt_ctx* ctx) {
+  if (!ctx || !ctx->fold_timed) return -1.0f;
+  float ms = -1.0f;
+  if (cudaEventSynchronize(ctx->ev_f1) != cudaSuccess) return -1.0f;
+  if (cudaEventElapsedTime(&ms, ctx->ev_f0, ctx->ev_f1) != cudaSuccess) {
     cudaGetLastError();
     return -1.0f;
   }
@@ -845,55 +868,47 @@ int hbt_fetch_carry(hbt_ctx* ctx, uint32_t cpu, uint64_t* last, uint32_t n_event
 // ---- histogram -----------------------------------------------------------------
 
 int hbt_hist_clear(hbt_ctx* ctx) {
-  if (!ctx || ctx->hist_slots_per_cpu == 0) return fail(ctx, -EINVAL, "no histogram configured");
+  if (!ctx || ctx->hist_buckets == 0) return fail(ctx, -EINVAL, "no histogram configured");
   if (int rc = complete_decode(ctx)) return rc;
-  // Lazy: the next IP_HISTOGRAM decode zeroes each CPU's sub-table in-kernel, right
-  // before filling it; hist_flush_clear() does it eagerly if something reads first.
-  ctx->hist_needs_zero = true;
-  ctx->hist_samples = 0;
+  // clearing = emptying the lists: only the cursors are touched
+  CU(cudaMemsetAsync(ctx->hist_cursors.p, 0, hist_lists(ctx) * sizeof(uint32_t), ctx->stream));
   CU(cudaMemsetAsync(ctx->hist_overflow.p, 0, sizeof(uint32_t), ctx->stream));
-  return 0;
-}
-
-static int hist_flush_clear(hbt_ctx* ctx) {
-  if (!ctx->hist_needs_zero) return 0;
-  CU(cudaMemsetAsync(ctx->hist_slots.p, 0,
-                     ctx->hist_slots_per_cpu * ctx->n_cpus * sizeof(ulonglong2), ctx->stream));
-  CU(cudaMemsetAsync(ctx->hist_zero.p, 0, ctx->n_cpus * sizeof(uint64_t), ctx->stream));
-  ctx->hist_needs_zero = false;
+  ctx->hist_samples = 0;
+  ctx->hist_pending_fold = false;
   return 0;
 }
 
 int hbt_hist_configure(hbt_ctx* ctx, uint64_t capacity_slots) {
   if (!ctx || ctx->n_cpus == 0) return fail(ctx, -EINVAL, "configure rings first");
   if (int rc = complete_decode(ctx)) return rc;
-  const uint64_t per = capacity_slots / ctx->n_cpus;
-  if (per < 64 || per >= (1ull << 32))
-    return fail(ctx, -EINVAL, "capacity %llu gives %llu slots per CPU (need 64..2^32-1)",
-                (unsigned long long)capacity_slots, (unsigned long long)per);
+  const uint64_t per_cpu = capacity_slots / ctx->n_cpus;
+  const uint32_t cap = kAggSlots / 2;  // a list always fits the fold's shared-memory table
+  const uint64_t buckets = (per_cpu + cap - 1) / cap;
+  if (per_cpu == 0 || buckets > (1u << 20))
+    return fail(ctx, -EINVAL, "capacity %llu gives %llu lists per CPU",
+                (unsigned long long)capacity_slots, (unsigned long long)buckets);
   CU(cudaSetDevice(ctx->device));
-  CU(ctx->hist_slots.reserve((size_t)per * ctx->n_cpus));
-  CU(ctx->hist_zero.reserve(ctx->n_cpus));
+  ctx->hist_buckets = (uint32_t)buckets;
+  ctx->hist_cap = cap;
+  CU(ctx->hist_entries.reserve(hist_lists(ctx) * cap));
+  CU(ctx->hist_cursors.reserve(hist_lists(ctx)));
+  CU(ctx->hist_cursors_snap.reserve(hist_lists(ctx)));
   CU(ctx->hist_overflow.reserve(1));
-  CU(ctx->hist_arrive.reserve(ctx->n_cpus));
   CU(ctx->hist_n.reserve(1));
-  ctx->hist_slots_per_cpu = per;
   return hbt_hist_clear(ctx);
 }
 
 static int64_t hist_collect(hbt_ctx* ctx, hbt_hist_entry* out, uint64_t cap) {
-  if (!ctx || ctx->hist_slots_per_cpu == 0) return fail(ctx, -EINVAL, "no histogram configured");
+  if (!ctx || ctx->hist_buckets == 0) return fail(ctx, -EINVAL, "no histogram configured");
   int rc = complete_decode(ctx);
-  if (rc) return rc;
-  rc = hist_flush_clear(ctx);
   if (rc) return rc;
   if (out) CU(ctx->hist_out.reserve(cap ? cap : 1));
   CU(cudaMemsetAsync(ctx->hist_n.p, 0, sizeof(unsigned long long), ctx->stream));
-  HistTable t{ctx->hist_slots.p, ctx->hist_slots_per_cpu, ctx->hist_zero.p, ctx->hist_overflow.p,
-              ctx->hist_arrive.p};
-  k_hist_compact<<<ctx->sm_count * 8, 256, 0, ctx->stream>>>(t, ctx->n_cpus, ctx->cpu_base,
-                                                            out ? ctx->hist_out.p : nullptr,
-                                                            ctx->hist_n.p, cap);
+  const uint32_t n_lists = (uint32_t)hist_lists(ctx);
+  uint32_t grid = (uint32_t)ctx->sm_count * 16;
+  if (grid > n_lists) grid = n_lists;
+  k_hist_gather<<<grid, 128, 0, ctx->stream>>>(hist_view(ctx), n_lists, ctx->cpu_base,
+                                               out ? ctx->hist_out.p : nullptr, ctx->hist_n.p, cap);
   ++ctx->launches;
   CU(cudaGetLastError());
   unsigned long long n = 0;
@@ -913,12 +928,15 @@ int64_t hbt_hist_fetch(hbt_ctx* ctx, hbt_hist_entry* out, uint64_t cap) {
   return hist_collect(ctx, out, cap);
 }
 
-int hbt_hist_table_dev(hbt_ctx* ctx, const void** slots, uint64_t* slots_per_cpu) {
-  if (!ctx || !slots || !slots_per_cpu || ctx->hist_slots_per_cpu == 0) return -EINVAL;
+int hbt_hist_lists_dev(hbt_ctx* ctx, const void** entries, const uint32_t** cursors,
+                       uint32_t* lists_per_cpu, uint32_t* list_capacity) {
+  if (!ctx || !entries || !cursors || !lists_per_cpu || !list_capacity || ctx->hist_buckets == 0)
+    return -EINVAL;
   if (int rc = complete_decode(ctx)) return rc;
-  if (int rc = hist_flush_clear(ctx)) return rc;
-  *slots = ctx->hist_slots.p;
-  *slots_per_cpu = ctx->hist_slots_per_cpu;
+  *entries = ctx->hist_entries.p;
+  *cursors = ctx->hist_cursors.p;
+  *lists_per_cpu = ctx->hist_buckets;
+  *list_capacity = ctx->hist_cap;
   return 0;
 }
 

@@ -141,6 +141,20 @@ __device__ __forceinline__ void red_add_u32_hint(uint32_t* p, uint32_t v, uint64
                : "memory");
 }
 
+__device__ __forceinline__ void cas128_shared(uint32_t saddr, uint64_t clo, uint64_t chi,
+                                              uint64_t nlo, uint64_t nhi, uint64_t& olo,
+                                              uint64_t& ohi) {
+  asm volatile(
+      "{\n\t.reg .b128 c, n, d;\n\t"
+      "mov.b128 c, {%3, %4};\n\t"
+      "mov.b128 n, {%5, %6};\n\t"
+      "atom.shared.relaxed.cta.cas.b128 d, [%2], c, n;\n\t"
+      "mov.b128 {%0, %1}, d;\n\t}"
+      : "=l"(olo), "=l"(ohi)
+      : "r"(saddr), "l"(clo), "l"(chi), "l"(nlo), "l"(nhi)
+      : "memory");
+}
+
 __device__ __forceinline__ ulonglong2 ld_relaxed_v2u64(const void* p) {
   ulonglong2 v;
   asm volatile("ld.relaxed.gpu.global.v2.u64 {%0, %1}, [%2];"

@@ -247,6 +247,8 @@ uint64_t hbt_decode_slow_tiles(hbt_ctx* ctx);
 /* Device time of the last decode kernel launch (CUDA events on the ctx stream
  * around that one launch; waits for it).  Negative when unavailable. */
 float hbt_decode_kernel_ms(hbt_ctx* ctx);
+/* Same for the last histogram fold kernel (k_hist_aggregate). */
+float hbt_hist_fold_kernel_ms(hbt_ctx* ctx);
 
 /* Rows {tstamp, duration, deltas[n_events]} of the last decode for `cpu`, in
  * stream order: the bytes CpuCountSampleGenerator writes to its output ring
@@ -264,22 +266,25 @@ uint32_t hbt_rows_max_slabs(const hbt_ctx* ctx);
 /* last_[] of `cpu` after the last decode (PerCpuCountSampleGenerator.h:228). */
 int hbt_fetch_carry(hbt_ctx* ctx, uint32_t cpu, uint64_t* last, uint32_t n_events);
 
-/* (cpu,pid,ip) table.  capacity_slots is split evenly between the configured
- * CPUs (each CPU owns a contiguous sub-table, so a CPU's keys stay in L2 while
- * that CPU's segments are decoded); a decode that overflows a CPU's share makes
- * hbt_fetch_results return -ENOSPC.  Counts are 32-bit in the table and
- * accumulate until hbt_hist_clear; hbt_decode returns -EOVERFLOW rather than let
- * more than 2^32-1 samples accumulate.  hbt_hist_clear is lazy: the next
- * HBT_AGG_IP_HISTOGRAM decode zeroes the table inside its kernel. */
+/* (cpu,pid,ip) histogram.  Every CPU owns a set of append-only lists of 16-byte
+ * entries {u64 ip; u32 pid; u32 count} (a key always goes to the list its hash
+ * selects): a decode appends one entry per sample, then a fold kernel reduces each
+ * list to distinct keys in shared memory, in place.  capacity_slots is the total
+ * number of entries the lists can hold, split evenly between the configured CPUs;
+ * per CPU it must cover the distinct keys accumulated so far PLUS the samples of
+ * one decode.  A decode that overflows a list makes hbt_fetch_results return
+ * -ENOSPC.  Counts are 32-bit and accumulate until hbt_hist_clear; hbt_decode
+ * returns -EOVERFLOW rather than let more than 2^32-1 samples accumulate.
+ * hbt_hist_clear only resets the list cursors. */
 int hbt_hist_configure(hbt_ctx* ctx, uint64_t capacity_slots);
 int hbt_hist_clear(hbt_ctx* ctx);
 /* Number of distinct keys, then the entries (unordered). */
 int64_t hbt_hist_size(hbt_ctx* ctx);
 int64_t hbt_hist_fetch(hbt_ctx* ctx, hbt_hist_entry* out, uint64_t cap);
-/* Device view: n_cpus consecutive sub-tables of *slots_per_cpu 16-byte slots
- * {u64 ip; u32 pid; u32 count}; an all-zero slot is empty; the key (ip=0,pid=0)
- * is kept outside the table and only appears in hbt_hist_fetch. */
-int hbt_hist_table_dev(hbt_ctx* ctx, const void** slots, uint64_t* slots_per_cpu);
+/* Device view for downstream kernels: list l = cpu * (*lists_per_cpu) + bucket
+ * holds cursors[l] distinct entries at entries + l * (*list_capacity) * 16 bytes. */
+int hbt_hist_lists_dev(hbt_ctx* ctx, const void** entries, const uint32_t** cursors,
+                       uint32_t* lists_per_cpu, uint32_t* list_capacity);
 
 /* ------------------------------------------------------------------------ */
 /* Counter groups: PerCpuBase<T>::read (PerCpuBase.h:104-119) over a recorded
