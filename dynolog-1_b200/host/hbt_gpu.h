@@ -1,0 +1,432 @@
+// Host-side mirror of the reference's interface for the perf_event decode/aggregate
+// path, written in the reference's language (C++17) on top of the C-ABI of
+// include/hbt_b200.h.  Same class names, argument meaning and error behaviour as
+//   hbt::perf_event::GroupReadValues      hbt/src/perf_event/CpuEventsGroup.h:368-535
+//   hbt::perf_event::PerCpuCountReader    hbt/src/perf_event/PerCpuCountReader.h:56-149
+//   hbt::perf_event::PerCpuBase::read     hbt/src/perf_event/PerCpuBase.h:104-119
+//   hbt::perf_event::RbDataSlices         hbt/src/perf_event/CpuEventsGroup.h:44-63
+//   hbt::mon::Monitor                     hbt/src/mon/Monitor.h:40-99,213-237,281-304,484-732
+// so that dynolog::PerfMonitor-shaped code (perf_monitor.h) compiles against it
+// unchanged in shape.  All arithmetic of the path runs on the GPU: there is no
+// host implementation behind these classes, and constructing a GpuContext
+// without a usable device throws.
+#pragma once
+#include <algorithm>
+#include <cerrno>
+#include <cstdint>
+#include <cstring>
+#include <deque>
+#include <map>
+#include <memory>
+#include <mutex>
+#include <optional>
+#include <set>
+#include <stdexcept>
+#include <string>
+#include <system_error>
+#include <vector>
+
+#include "../../include/hbt_b200.h"
+
+namespace hbt_gpu {
+
+using CpuId = unsigned;
+using TimeStamp = uint64_t;
+constexpr unsigned kMaxCpus = HBT_MAX_CPUS;                 // hbt/src/common/System.h:195
+constexpr TimeStamp kInvalidTimeStamp = ~TimeStamp(0);      // hbt/src/common/System.h:97
+
+// hbt::CpuSet (hbt/src/common/System.h:198-283), reduced to what the path uses.
+struct CpuSet {
+  std::set<CpuId> cpus;
+  CpuId max_cpu_id = 0;
+  template <class TCont>
+  static CpuSet makeFromCont(const TCont& c) {
+    CpuSet s;
+    for (auto cpu : c) {
+      if (cpu < 0 || static_cast<unsigned>(cpu) >= kMaxCpus)
+        throw std::invalid_argument("Invalid CPU ID: " + std::to_string(cpu));  // HBT_THROW_EINVAL
+      s.cpus.insert(static_cast<CpuId>(cpu));
+    }
+    if (!s.cpus.empty()) s.max_cpu_id = *s.cpus.rbegin();
+    return s;
+  }
+  static CpuSet makeRange(unsigned n) {
+    std::vector<int> v(n);
+    for (unsigned i = 0; i < n; ++i) v[i] = (int)i;
+    return makeFromCont(v);
+  }
+  bool hasCpu(CpuId c) const { return cpus.count(c) != 0; }
+  size_t numCpus() const { return cpus.size(); }
+};
+
+// RAII owner of one hbt_ctx.  Errors follow hbt's conventions: invalid arguments
+// -> std::invalid_argument (HBT_ARG_CHECK*), anything the system refuses ->
+// std::system_error (HBT_THROW_SYSTEM*), hbt/src/common/Defs.h:91-157.
+class GpuContext {
+ public:
+  explicit GpuContext(int device = 0, uint32_t max_cpus = kMaxCpus, uint32_t max_events = HBT_MAX_EVENTS) {
+    int rc = hbt_create(&ctx_, device, max_cpus, max_events);
+    if (rc == -EINVAL) throw std::invalid_argument("hbt_create: invalid limits");
+    if (rc < 0)
+      throw std::system_error(-rc, std::generic_category(),
+                              "hbt_create: no usable sm_100 CUDA device (there is no CPU fallback)");
+  }
+  ~GpuContext() { hbt_destroy(ctx_); }
+  GpuContext(const GpuContext&) = delete;
+  GpuContext& operator=(const GpuContext&) = delete;
+  hbt_ctx* get() const { return ctx_; }
+  void check(int64_t rc, const char* what) const {
+    if (rc >= 0) return;
+    const std::string msg = std::string(what) + ": " + hbt_last_error(ctx_);
+    if (rc == -EINVAL) throw std::invalid_argument(msg);
+    throw std::system_error((int)-rc, std::generic_category(), msg);
+  }
+
+ private:
+  hbt_ctx* ctx_ = nullptr;
+};
+
+namespace perf_event {
+
+struct DataSlice {
+  const void* from;
+  size_t size;
+};
+struct RbDataSlices {
+  RbDataSlices(const void* p1, size_t n1) : first{p1, n1} {}
+  RbDataSlices(const void* p1, size_t n1, const void* p2, size_t n2)
+      : first{p1, n1}, second{DataSlice{p2, n2}} {}
+  DataSlice first;
+  std::optional<DataSlice> second;
+};
+
+// GroupReadValues<TMode>: the kernel's read_format POD plus the accessors of the
+// reference.  getCount()'s multiplex scaling is what the GPU computed for this
+// read (scaled_), not a host re-computation.
+class GroupReadValues {
+ public:
+  explicit GroupReadValues(size_t n_events) : t_(3 + n_events, 0), scaled_(n_events, 0), rates_(n_events, 0.f) {
+    if (n_events == 0) throw std::invalid_argument("n_events must be > 0");  // HBT_ARG_CHECK_GT
+    t_[0] = n_events;
+  }
+  size_t getNumEvents() const { return (size_t)t_[0]; }
+  size_t getNumReadBytes() const { return 8 * t_.size(); }
+  uint64_t getTimeEnabled() const { return t_[1]; }
+  uint64_t getTimeRunning() const { return t_[2]; }
+  uint64_t getRawCount(size_t i) const { return t_.at(3 + checked(i)); }
+  uint64_t getCount(size_t i) const { return scaled_.at(checked(i)); }
+  std::vector<uint64_t> getRawCounts() const { return {t_.begin() + 3, t_.end()}; }
+  std::vector<uint64_t> getCounts() const { return scaled_; }
+  // float(double(getCount(i)) * 1e3 / double(getTimeRunning())): PerfMonitor.cpp:56-57
+  float getRatePerMs(size_t i) const { return rates_.at(checked(i)); }
+  bool hasMultiplexing() const { return t_[1] != 0 && t_[2] != t_[1]; }
+  uint64_t* raw() { return t_.data(); }
+  const uint64_t* raw() const { return t_.data(); }
+  uint64_t* scaled() { return scaled_.data(); }
+  float* rates() { return rates_.data(); }
+
+ private:
+  size_t checked(size_t i) const {
+    if (i >= getNumEvents()) throw std::invalid_argument("Index out of range");  // HBT_ARG_CHECK_LT
+    return i;
+  }
+  std::vector<uint64_t> t_;
+  std::vector<uint64_t> scaled_;
+  std::vector<float> rates_;
+};
+
+struct EventRef {
+  std::string nickname;
+};
+// MetricDesc reduced to the event order / nicknames the path needs
+// (hbt/src/perf_event/Metrics.h:122-179).
+struct MetricDesc {
+  std::string id;
+  std::vector<EventRef> event_refs;
+  std::optional<std::vector<EventRef>> getEventRefs() const {
+    if (event_refs.empty()) return std::nullopt;
+    return event_refs;
+  }
+  std::vector<std::string> eventNicknames() const {
+    std::vector<std::string> v;
+    for (auto& e : event_refs) v.push_back(e.nickname);
+    return v;
+  }
+  std::optional<size_t> getNumEvents() const {
+    if (event_refs.empty()) return std::nullopt;
+    return event_refs.size();
+  }
+};
+
+// Where the raw read_format bytes of each CPU's group leader come from: the
+// ::read(2) of CpuEventsGroupBase::read (CpuEventsGroup.h:596-615) in a live
+// daemon, a recorded trace in replay.  Returns false for a failed read.
+class CounterSource {
+ public:
+  virtual ~CounterSource() = default;
+  virtual bool readCpu(CpuId cpu, uint64_t* t, size_t n_events) = 0;
+  virtual void nextInterval() {}
+};
+
+class TraceReplaySource : public CounterSource {
+ public:
+  // reads[interval][cpu_index][3+E], cpu_index = rank of the CPU id in the set
+  TraceReplaySource(std::vector<uint64_t> reads, size_t n_cpus, size_t n_events)
+      : reads_(std::move(reads)), n_cpus_(n_cpus), W_(3 + n_events) {}
+  bool readCpu(CpuId cpu_index, uint64_t* t, size_t n_events) override {
+    if (interval_ * n_cpus_ * W_ + (cpu_index + 1) * W_ > reads_.size()) return false;
+    const uint64_t* src = &reads_[(interval_ * n_cpus_ + cpu_index) * W_];
+    if (src[0] != n_events) return false;
+    std::memcpy(t, src, 8 * W_);
+    return true;
+  }
+  void nextInterval() override { ++interval_; }
+
+ private:
+  std::vector<uint64_t> reads_;
+  size_t n_cpus_, W_, interval_ = 0;
+};
+
+// PerCpuCountReader: one counting-mode event group per CPU, read() = sum over CPUs
+// (PerCpuBase::read) then scaling -- both on the GPU through the C-ABI.
+class PerCpuCountReader {
+ public:
+  using ReadValues = GroupReadValues;
+
+  PerCpuCountReader(const CpuSet& mon_cpus, std::shared_ptr<const MetricDesc> metric_desc_in,
+                    std::shared_ptr<CounterSource> source, std::shared_ptr<GpuContext> gpu)
+      : metric_desc{std::move(metric_desc_in)}, mon_cpus_{mon_cpus}, source_{std::move(source)}, gpu_{std::move(gpu)} {
+    if (!metric_desc || !source_ || !gpu_) throw std::invalid_argument("null dependency");
+    if (mon_cpus_.numCpus() == 0) throw std::invalid_argument("empty CpuSet");
+    if (!metric_desc->getNumEvents()) throw std::invalid_argument("No events in metric_desc");
+    staging_.assign(mon_cpus_.numCpus() * (3 + getNumEvents()), 0);
+  }
+
+  void open(bool /*pinned*/ = false) { open_ = true; }
+  void close() {
+    if (!open_) return;
+    disable();
+    open_ = false;
+  }
+  void enable() {
+    if (!open_) throw std::invalid_argument("Cannot enable events that are not open");  // :1241
+    enabled_ = true;
+  }
+  void disable() {
+    if (!open_) throw std::invalid_argument("Cannot disable events that are not open");
+    enabled_ = false;
+  }
+  bool isOpen() const { return open_; }
+  bool isEnabled() const { return enabled_; }
+  size_t getNumEvents() const { return *metric_desc->getNumEvents(); }
+  ReadValues makeReadValues() const { return ReadValues{getNumEvents()}; }
+  CpuSet getMonCpus() const { return mon_cpus_; }
+
+  // PerCpuBase::read: false when not open or when any CPU's read fails.
+  bool read(ReadValues& rv) const {
+    if (!isOpen()) return false;
+    if (rv.getNumEvents() != getNumEvents())
+      throw std::invalid_argument("GroupReadValues of " + std::to_string(rv.getNumEvents()) + " but have " +
+                                  std::to_string(getNumEvents()));  // CpuEventsGroup.h:599-601
+    const size_t E = getNumEvents(), W = 3 + E, C = mon_cpus_.numCpus();
+    size_t k = 0;
+    for (CpuId cpu : mon_cpus_.cpus) {
+      (void)cpu;
+      uint64_t* t = &staging_[k * W];
+      if (!source_->readCpu((CpuId)k, t, E)) t[0] = 0;  // marks the failed read for the kernel
+      ++k;
+    }
+    source_->nextInterval();
+    std::vector<uint64_t> sums(W), scaled(E);
+    std::vector<float> rates(E);
+    gpu_->check(hbt_counts_pipeline_host(gpu_->get(), staging_.data(), 1, (uint32_t)C, (uint32_t)E, nullptr, 0,
+                                         sums.data(), scaled.data(), rates.data(), nullptr, nullptr),
+                "hbt_counts_pipeline_host");
+    if (sums[0] == 0) return false;  // some CPU's read failed -> std::nullopt upstream
+    std::memcpy(rv.raw(), sums.data(), 8 * W);
+    std::memcpy(rv.scaled(), scaled.data(), 8 * E);
+    std::memcpy(rv.rates(), rates.data(), 4 * E);
+    return true;
+  }
+
+  std::optional<ReadValues> read() const {
+    auto rv = makeReadValues();
+    if (read(rv)) return std::make_optional(rv);
+    return std::nullopt;
+  }
+
+  const std::shared_ptr<const MetricDesc> metric_desc;  // public, PerfMonitor::log reads it
+
+ private:
+  CpuSet mon_cpus_;
+  std::shared_ptr<CounterSource> source_;
+  std::shared_ptr<GpuContext> gpu_;
+  mutable std::vector<uint64_t> staging_;
+  bool open_ = false, enabled_ = false;
+};
+
+// Batch replacement of the per-CPU CpuCountSampleGenerator::consume() loop
+// (PerCpuSampleGeneratorBase::accumUntil, PerCpuSampleGeneratorBase.h:70-96): the
+// slices every CPU's onCpuDataBufferRead hands out are submitted, then one
+// consume() decodes all CPUs.
+class PerCpuCountSampleDecoder {
+ public:
+  PerCpuCountSampleDecoder(const CpuSet& mon_cpus, size_t n_events, size_t data_size,
+                           std::shared_ptr<GpuContext> gpu)
+      : mon_cpus_{mon_cpus}, n_events_{n_events}, gpu_{std::move(gpu)} {
+    if (n_events == 0 || n_events > HBT_MAX_EVENTS) throw std::invalid_argument("kNumEvents out of range");
+    gpu_->check(hbt_ring_configure(gpu_->get(), mon_cpus_.max_cpu_id + 1, data_size), "hbt_ring_configure");
+    results_.resize(mon_cpus_.max_cpu_id + 1);
+  }
+  // enable(): counters reset, count_.tstamp = now(), last_[] = 0 (enableImpl, :91-106)
+  void enable(TimeStamp now) { gpu_->check(hbt_ring_reset_state(gpu_->get(), now), "hbt_ring_reset_state"); }
+  // OnRbReadCallback body (CpuEventsGroup.h:63): tail = data_tail the slices start at
+  void onCpuDataBufferRead(CpuId cpu, const RbDataSlices& s, uint64_t tail, uint64_t head) {
+    if (!mon_cpus_.hasCpu(cpu)) throw std::invalid_argument("CPU " + std::to_string(cpu) + " not monitored");
+    size_t n2 = 0;
+    if (s.second) n2 = std::min(s.second->size, (size_t)(head - tail) - s.first.size);  // :1561 over-reports
+    gpu_->check(hbt_submit_ring(gpu_->get(), cpu, s.first.from, s.first.size, s.second ? s.second->from : nullptr,
+                                n2, tail),
+                "hbt_submit_ring");
+  }
+  // consume(max_num_records) for every CPU; returns what each CPU's consume() would.
+  std::map<CpuId, int64_t> consume(unsigned max_num_records) {
+    hbt_decode_desc d{};
+    d.handled_mask = HBT_MODE_SAMPLING;
+    d.sample_layout = HBT_SAMPLE_GROUP;
+    d.aggregate = HBT_AGG_COUNT_DELTAS;
+    d.n_events = (uint32_t)n_events_;
+    d.max_records = max_num_records;
+    d.tsc.time_mult = 1;
+    gpu_->check(hbt_decode(gpu_->get(), &d), "hbt_decode");
+    gpu_->check(hbt_fetch_results(gpu_->get(), results_.data(), (uint32_t)results_.size()), "hbt_fetch_results");
+    std::map<CpuId, int64_t> ret;
+    for (CpuId cpu : mon_cpus_.cpus) ret[cpu] = results_[cpu].ret;
+    return ret;
+  }
+  // rows {tstamp, duration, deltas[n]} of the last consume(), kWriteByteSize each (:69)
+  std::vector<uint64_t> rows(CpuId cpu) {
+    const auto& r = results_.at(cpu);
+    std::vector<uint64_t> out(r.n_rows * (2 + n_events_));
+    if (r.n_rows) gpu_->check(hbt_fetch_rows(gpu_->get(), cpu, out.data(), r.n_rows), "hbt_fetch_rows");
+    return out;
+  }
+  uint64_t getNumRecordLost(CpuId c) const { return results_.at(c).counters[HBT_CNT_LOST]; }
+  uint64_t getNumRecordSample(CpuId c) const { return results_.at(c).counters[HBT_CNT_SAMPLE]; }
+  uint64_t getNumUnknownCountInterval(CpuId c) const { return results_.at(c).num_unknown_count_interval; }
+  TimeStamp getLastTimeStamp(CpuId c) const { return results_.at(c).carry_tstamp; }
+  uint64_t dataTail(CpuId c) const { return results_.at(c).new_tail; }
+
+ private:
+  CpuSet mon_cpus_;
+  size_t n_events_;
+  std::shared_ptr<GpuContext> gpu_;
+  std::vector<hbt_cpu_result> results_;
+};
+
+}  // namespace perf_event
+
+namespace mon {
+
+// hbt::mon::Monitor: element map, mux queue, Closed/Open/Enabled state machine,
+// one mutex (hbt/src/mon/Monitor.h:40-99, 484-520, 681-732).
+template <class MuxGroupIdType = std::optional<std::string>, class ElemIdType = std::string>
+class Monitor {
+  enum class State { Closed, Open, Enabled };
+
+ public:
+  using TCountReader = perf_event::PerCpuCountReader;
+  using ElemId = ElemIdType;
+  using MuxGroupId = MuxGroupIdType;
+
+  bool open() { return lockedTo(State::Open); }
+  bool close() { return lockedTo(State::Closed); }
+  bool enable() { return lockedTo(State::Enabled); }
+  bool disable() { return lockedTo(State::Open); }
+  bool isOpen() const {
+    std::lock_guard<std::mutex> l{mutex_};
+    return state_ == State::Open;
+  }
+  bool isEnabled() const {
+    std::lock_guard<std::mutex> l{mutex_};
+    return state_ == State::Enabled;
+  }
+  void muxRotate() {
+    std::lock_guard<std::mutex> l{mutex_};
+    if (mux_queue_.empty()) return;
+    std::rotate(mux_queue_.rbegin(), mux_queue_.rbegin() + 1, mux_queue_.rend());
+    sync_();
+  }
+
+  std::shared_ptr<TCountReader> emplaceCountReader(const MuxGroupId& mux_group_id, const ElemId& elem_id,
+                                                   std::shared_ptr<const perf_event::MetricDesc> metric_desc,
+                                                   std::shared_ptr<perf_event::CounterSource> source,
+                                                   const CpuSet& mon_cpus, std::shared_ptr<GpuContext> gpu) {
+    std::lock_guard<std::mutex> l{mutex_};
+    if (count_readers_.count(elem_id) != 0)  // HBT_ARG_CHECK_EQ, Monitor.h:291-293
+      throw std::invalid_argument("There is already an interval source with key: \"" + elem_id + "\"");
+    auto& g = mux_groups_[mux_group_id];
+    if (g.empty()) mux_queue_.push_back(mux_group_id);
+    g.insert(elem_id);
+    auto [it, ok] = count_readers_.emplace(
+        elem_id, std::make_shared<TCountReader>(mon_cpus, std::move(metric_desc), std::move(source), std::move(gpu)));
+    (void)ok;
+    sync_();
+    return it->second;
+  }
+
+  std::map<ElemId, std::optional<typename TCountReader::ReadValues>> readAllCounts() const {
+    std::lock_guard<std::mutex> l{mutex_};
+    std::map<ElemId, std::optional<typename TCountReader::ReadValues>> rvs;
+    for (auto& [k, cr] : count_readers_) rvs.emplace(k, cr->read());
+    return rvs;
+  }
+  std::optional<typename TCountReader::ReadValues> readCounts(const ElemId& elem_id) const {
+    std::lock_guard<std::mutex> l{mutex_};
+    auto it = count_readers_.find(elem_id);
+    if (it == count_readers_.end()) return std::nullopt;
+    return it->second->read();
+  }
+
+ private:
+  bool lockedTo(State s) {
+    std::lock_guard<std::mutex> l{mutex_};
+    if (state_ == s) return false;
+    state_ = s;
+    sync_();
+    return true;
+  }
+  void sync_() {
+    if (mux_queue_.empty()) return;
+    for (auto& [k, p] : count_readers_) {
+      auto& e = *p;
+      switch (state_) {
+        case State::Closed:
+          if (e.isEnabled()) e.disable();
+          if (e.isOpen()) e.close();
+          break;
+        case State::Open:
+          if (e.isEnabled()) e.disable();
+          if (!e.isOpen()) e.open();
+          break;
+        case State::Enabled:
+          if (!e.isOpen()) e.open();
+          // only the group at the front of the multiplexing queue is enabled
+          if (mux_groups_.at(mux_queue_.front()).count(k) > 0) {
+            if (!e.isEnabled()) e.enable();
+          } else if (e.isEnabled()) {
+            e.disable();
+          }
+          break;
+      }
+    }
+  }
+  mutable std::mutex mutex_;
+  State state_ = State::Closed;
+  std::map<ElemId, std::shared_ptr<TCountReader>> count_readers_;
+  std::map<MuxGroupId, std::set<ElemId>> mux_groups_;
+  std::deque<MuxGroupId> mux_queue_;
+};
+
+}  // namespace mon
+}  // namespace hbt_gpu

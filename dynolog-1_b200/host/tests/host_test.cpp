@@ -1,0 +1,204 @@
+// Tests of the host-side mirror (hbt_gpu.h, perf_monitor.h).  `host_test cpu` needs no
+// GPU; `host_test gpu` drives the CUDA path through the mirrored reference API and
+// checks it against the reference's expressions restated here (test-side only).
+#include <cmath>
+#include <cstdio>
+#include <iostream>
+#include <sstream>
+
+#include "../perf_monitor.h"
+
+using namespace hbt_gpu;
+namespace pe = hbt_gpu::perf_event;
+
+static int g_fail = 0;
+#define CHECK(c)                                                          \
+  do {                                                                    \
+    if (!(c)) {                                                           \
+      std::printf("FAIL %s:%d: %s\n", __FILE__, __LINE__, #c);            \
+      ++g_fail;                                                           \
+    }                                                                     \
+  } while (0)
+template <class E, class F>
+bool throws(F f) {
+  try {
+    f();
+  } catch (const E&) {
+    return true;
+  } catch (...) {
+    return false;
+  }
+  return false;
+}
+
+static uint64_t sm64(uint64_t& s) {
+  uint64_t z = (s += 0x9E3779B97F4A7C15ull);
+  z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
+  z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
+  return z ^ (z >> 31);
+}
+
+// reads[I][C][3+E], cumulative, multiplexed
+static std::vector<uint64_t> make_trace(size_t I, size_t C, size_t E, uint64_t seed) {
+  std::vector<uint64_t> r(I * C * (3 + E));
+  std::vector<uint64_t> te(C, 0), tr(C, 0), cnt(C * E, 0);
+  for (size_t i = 0; i < I; ++i)
+    for (size_t c = 0; c < C; ++c) {
+      uint64_t d = 1000000000ull + sm64(seed) % 100000;
+      te[c] += d;
+      tr[c] += d / 4 + sm64(seed) % (d - d / 4);
+      uint64_t* t = &r[(i * C + c) * (3 + E)];
+      t[0] = E;
+      t[1] = te[c];
+      t[2] = tr[c];
+      for (size_t e = 0; e < E; ++e) {
+        cnt[c * E + e] += 100000 + sm64(seed) % 9900000;
+        t[3 + e] = cnt[c * E + e];
+      }
+    }
+  return r;
+}
+
+static void test_cpu() {
+  CHECK(throws<std::invalid_argument>([] { CpuSet::makeFromCont(std::vector<int>{1, 2, 600}); }));
+  CHECK(throws<std::invalid_argument>([] { pe::GroupReadValues rv(0); }));
+  pe::GroupReadValues rv(3);
+  CHECK(rv.getNumEvents() == 3 && rv.getNumReadBytes() == 48);
+  CHECK(throws<std::invalid_argument>([&] { rv.getRawCount(3); }));
+  CHECK(!rv.hasMultiplexing());
+  std::ostringstream os;
+  dynolog_gpu::JsonLogger lg(os);
+  lg.logFloat("mips", 691.4972f);
+  lg.logUint("cycles", 123456789012345ull);
+  lg.logInt("neg", -5);
+  lg.logStr("s", "x");
+  CHECK(lg.sample().at("mips") == "\"691.497\"");  // "{:.3f}" as a string, Logger.cpp:42-44
+  lg.finalize();
+  CHECK(os.str() == "{\"cycles\":123456789012345,\"mips\":\"691.497\",\"neg\":-5,\"s\":\"x\"}\n");
+  CHECK(lg.sample().empty());
+  pe::MetricDesc md{"ipc", {{"cycles"}, {"instructions"}}};
+  CHECK(*md.getNumEvents() == 2 && md.eventNicknames()[1] == "instructions");
+  pe::MetricDesc none{"none", {}};
+  CHECK(!none.getEventRefs().has_value());
+  // no GPU in this process -> constructing the context must fail loudly
+  int n = 0;
+  bool have_gpu = false;
+  {
+    hbt_ctx* c = nullptr;
+    int rc = hbt_create(&c, 0, 8, 8);
+    have_gpu = rc == 0;
+    if (c) hbt_destroy(c);
+    (void)n;
+  }
+  if (!have_gpu) CHECK(throws<std::system_error>([] { GpuContext g(0); }));
+  CHECK(throws<std::invalid_argument>([] { GpuContext g(0, HBT_MAX_CPUS + 1, 8); }));
+}
+
+static void test_gpu() {
+  auto gpu = std::make_shared<GpuContext>(0);
+  const size_t C = 16, I = 6;
+  auto cpus = CpuSet::makeRange(C);
+  auto metrics = std::make_shared<dynolog_gpu::Metrics>();
+  metrics->descs["instructions"] = std::make_shared<pe::MetricDesc>(pe::MetricDesc{"instructions", {{"instructions"}}});
+  metrics->descs["cycles"] = std::make_shared<pe::MetricDesc>(pe::MetricDesc{"cycles", {{"cycles"}}});
+  metrics->descs["ipc"] =
+      std::make_shared<pe::MetricDesc>(pe::MetricDesc{"ipc", {{"cycles"}, {"instructions"}}});
+  auto tr_i = make_trace(I, C, 1, 11), tr_c = make_trace(I, C, 1, 22), tr_ipc = make_trace(I, C, 2, 33);
+  tr_ipc[(3 * C + 5) * 5] = 0;  // interval 3, cpu 5: failed read -> nullopt for "ipc"
+  std::map<std::string, std::shared_ptr<pe::CounterSource>> src;
+  src["instructions"] = std::make_shared<pe::TraceReplaySource>(tr_i, C, 1);
+  src["cycles"] = std::make_shared<pe::TraceReplaySource>(tr_c, C, 1);
+  src["ipc"] = std::make_shared<pe::TraceReplaySource>(tr_ipc, C, 2);
+  dynolog_gpu::PerfMonitor pm(cpus, {"instructions", "cycles", "ipc"}, metrics, src, gpu);
+  for (size_t i = 0; i < I; ++i) {
+    pm.step();
+    std::ostringstream os;
+    dynolog_gpu::JsonLogger lg(os);
+    pm.log(lg);
+    // expectations: the reference's expressions (PerCpuBase.h:104-119, CpuEventsGroup.h:449-459,
+    // PerfMonitor.cpp:52-67) restated on the host
+    auto expect = [&](const std::vector<uint64_t>& tr, size_t E, size_t e, uint64_t& time) {
+      uint64_t te = 0, trn = 0, cnt = 0;
+      for (size_t c = 0; c < C; ++c) {
+        const uint64_t* t = &tr[(i * C + c) * (3 + E)];
+        te += t[1];
+        trn += t[2];
+        cnt += t[3 + e];
+      }
+      time = trn;
+      return te == 0 ? 0 : (uint64_t)((double)cnt * (double)te / (double)trn);
+    };
+    uint64_t time = 0;
+    char buf[64];
+    uint64_t ci = expect(tr_i, 1, 0, time);
+    std::snprintf(buf, sizeof buf, "\"%.3f\"", (float)((double)ci * 1e3 / (double)time));
+    CHECK(lg.sample().at("mips") == buf);
+    uint64_t cc = expect(tr_c, 1, 0, time);
+    std::snprintf(buf, sizeof buf, "\"%.3f\"", (float)((double)cc * 1e3 / (double)time));
+    CHECK(lg.sample().at("mega_cycles_per_second") == buf);
+    CHECK(pm.readValues().at("instructions")->getCount(0) == ci);
+    if (i == 3) {
+      CHECK(!pm.readValues().at("ipc").has_value());  // one CPU failed -> whole read fails
+      CHECK(lg.sample().count("cycles") == 0);
+    } else {
+      // metric "ipc": neither event matches the (id, nickname) special cases -> logUint(nickname)
+      uint64_t c0 = expect(tr_ipc, 2, 0, time), c1 = expect(tr_ipc, 2, 1, time);
+      CHECK(lg.sample().at("cycles") == std::to_string(c0));
+      CHECK(lg.sample().at("instructions") == std::to_string(c1));
+      CHECK(pm.readValues().at("ipc")->hasMultiplexing());
+    }
+  }
+  // Monitor: duplicate key, state machine, multiplexing queue
+  mon::Monitor<> m;
+  auto md = metrics->descs["cycles"];
+  auto s2 = std::make_shared<pe::TraceReplaySource>(tr_c, C, 1);
+  auto r1 = m.emplaceCountReader(std::string("g1"), "a", md, s2, cpus, gpu);
+  auto r2 = m.emplaceCountReader(std::string("g2"), "b", md, s2, cpus, gpu);
+  CHECK(throws<std::invalid_argument>([&] { m.emplaceCountReader(std::nullopt, "a", md, s2, cpus, gpu); }));
+  CHECK(!r1->isOpen() && !m.isOpen());
+  CHECK(m.open() && !m.open() && m.isOpen() && r1->isOpen() && r2->isOpen() && !r1->isEnabled());
+  CHECK(m.enable() && m.isEnabled() && !m.isOpen());
+  CHECK(r1->isEnabled() && !r2->isEnabled());  // only the front mux group runs
+  m.muxRotate();
+  CHECK(!r1->isEnabled() && r2->isEnabled());
+  CHECK(m.disable() && !r2->isEnabled() && r2->isOpen());
+  CHECK(m.close() && !r1->isOpen());
+  CHECK(!m.readCounts("a").has_value());  // closed reader: read() fails
+  CHECK(throws<std::invalid_argument>([&] { r1->enable(); }));
+
+  // ring decode through the mirrored generator API: LOST(num_lost=3) + 5 SAMPLEs of 2 events
+  const size_t ds = 1 << 16;
+  std::vector<uint64_t> ring(ds / 8, 0);
+  const uint64_t tail = 5 * ds + ds - 64;  // wraps the ring end
+  std::vector<uint64_t> s;
+  s.insert(s.end(), {2ull | (24ull << 48), 7, 3});
+  for (uint64_t k = 0; k < 5; ++k) s.insert(s.end(), {9ull | (56ull << 48), 1000 + 10 * k, 2, 5, 5, 100 * k, 200 * k});
+  for (size_t w = 0; w < s.size(); ++w) ring[((tail / 8) + w) & (ds / 8 - 1)] = s[w];
+  const uint64_t head = tail + 8 * s.size();
+  pe::PerCpuCountSampleDecoder dec(CpuSet::makeFromCont(std::vector<int>{0, 2}), 2, ds, gpu);
+  dec.enable(kInvalidTimeStamp);
+  const uint8_t* base = reinterpret_cast<const uint8_t*>(ring.data());
+  // the two slices onCpuDataBufferRead reports for a wrapped window; the second over-reports
+  pe::RbDataSlices slices(base + (tail & (ds - 1)), 64, base, ds - 64);
+  dec.onCpuDataBufferRead(2, slices, tail, head);
+  auto ret = dec.consume(0xFFFFFFFFu);
+  CHECK(ret.at(2) == -ENODATA && ret.at(0) == -ENODATA);
+  CHECK(dec.getNumRecordLost(2) == 3 && dec.getNumRecordSample(2) == 5);
+  CHECK(dec.getNumUnknownCountInterval(2) == 1 && dec.dataTail(2) == head);
+  auto rows = dec.rows(2);
+  CHECK(rows.size() == 4 * 4);
+  for (uint64_t k = 0; k < 4 && rows.size() == 16; ++k) {
+    CHECK(rows[4 * k] == 1000 + 10 * k && rows[4 * k + 1] == 10);
+    CHECK(rows[4 * k + 2] == 100 && rows[4 * k + 3] == 200);
+  }
+  CHECK(dec.getLastTimeStamp(2) == 1040);
+  CHECK(throws<std::invalid_argument>([&] { dec.onCpuDataBufferRead(1, slices, tail, head); }));
+}
+
+int main(int argc, char** argv) {
+  const std::string mode = argc > 1 ? argv[1] : "cpu";
+  test_cpu();
+  if (mode == "gpu") test_gpu();
+  std::printf("%s: %s (%d failures)\n", mode.c_str(), g_fail ? "FAILED" : "ok", g_fail);
+  return g_fail ? 1 : 0;
+}
