@@ -131,6 +131,154 @@ def make_c2(n_cpus: int, ring_bytes: int, cpu_base: int, device, sample_words=5)
     return imgs, tails, heads, n * n_cpus
 
 
+def make_group_rings(n_cpus: int, ring_bytes: int, cpu_base: int, device, n_events: int,
+                     lost_every: int = 5000):
+    """Rings of mode::Sampling SAMPLE records (40 + 8*n_events bytes) with a LOST now and then."""
+    imgs = torch.empty((n_cpus, ring_bytes // 8), dtype=torch.int64, device=device)
+    tails, heads = [], []
+    rec = 40 + 8 * n_events
+    n = (ring_bytes - 65536) // (rec + 1)
+    total = 0
+    for c in range(n_cpus):
+        seed = tg.stream_seed(3, cpu_base + c)
+        s = tg.group_sample_stream(seed, n, n_events, device=device, lost_every=lost_every)
+        tail = tg.random_tail(seed, ring_bytes)
+        ring, head = tg.place_in_ring(s, ring_bytes, tail, fill_seed=seed ^ 0xABCDEF)
+        imgs[c] = ring
+        tails.append(tail)
+        heads.append(head)
+        total += n + n // lost_every
+    return imgs, tails, heads, total
+
+
+def timed_steps(step, steps, dist, dev):
+    """CUDA-event timing of `steps` calls of step(), barrier + sync on both sides, max over ranks."""
+    if dist is not None:
+        dist.barrier()
+    torch.cuda.synchronize()
+    e0 = torch.cuda.Event(enable_timing=True)
+    e1 = torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(steps):
+        step()
+    e1.record()
+    torch.cuda.synchronize()
+    if dist is not None:
+        dist.barrier()
+    t = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=dev)
+    if dist is not None:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    return float(t.item()) / steps
+
+
+def bench_deltas(args, rank, world, local, dev, dist):
+    """Diagnostic workload (config 3 shape): group SAMPLE decode + per-interval deltas."""
+    E = args.events
+    ring_bytes = args.ring_mib << 20
+    imgs, tails, heads, n_rec = make_group_rings(args.cpus, ring_bytes, rank * args.cpus, dev, E)
+    window_bytes = sum(h - t for t, h in zip(tails, heads))
+    ctx = hbt.Context(local, max_cpus=args.cpus)
+    ctx.use_torch_stream()
+    ctx.ring_configure(args.cpus, 0)
+    desc = hbt.sampling_desc(E)
+    bases_a = np.array([imgs[c].data_ptr() for c in range(args.cpus)], dtype=np.uint64)
+    tails_a, heads_a = np.array(tails, dtype=np.uint64), np.array(heads, dtype=np.uint64)
+    kms = []
+
+    def step():
+        ctx.submit_rings_dev(bases_a, ring_bytes, tails_a, heads_a)
+        ctx.decode(desc)
+        step.res = ctx.fetch_results()
+        kms.append(ctx.decode_kernel_ms)
+
+    for _ in range(max(args.warmup, 3)):
+        step()
+    res = step.res
+    assert int(res["n_records"].sum()) == n_rec
+    n_rows = int(res["n_rows"].sum())
+    kms.clear()
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    l0 = ctx.launches
+    ms_step = timed_steps(step, args.steps, dist, dev)
+    launches = ctx.launches - l0
+    clocks = sampler.stop() if rank == 0 else None
+    if rank != 0:
+        return None
+    peak, peak_src = load_peaks()
+    k_ms = sum(kms) / len(kms)
+    algo = window_bytes + n_rows * 8 * (2 + E)
+    ach = algo / (k_ms * 1e-3) / 1e9
+    return {"metric": METRIC, "value": n_rec * world / (ms_step * 1e-3), "unit": UNIT, "n_gpus": world,
+            "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms_step,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u64",
+            "data": "synthetic",
+            "config": {"workload": f"c3_deltas: group SAMPLE ({40 + 8 * E} B, {E} events) decode + per-interval deltas",
+                       "cpus_per_gpu": args.cpus, "ring_mib": args.ring_mib, "records_per_gpu": n_rec,
+                       "rows_per_gpu": n_rows, "window_bytes_per_gpu": int(window_bytes),
+                       "l2": "inputs exceed L2; no flush needed", "slow_tiles": ctx.slow_tiles,
+                       "reruns": ctx.reruns},
+            "roofline": {"bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
+                         "traffic": load_traffic("k_decode<COUNT_DELTAS>"), "kernel": "k_decode<COUNT_DELTAS>",
+                         "kernel_ms": k_ms, "algorithmic_bytes": int(algo), "peak_source": peak_src},
+            "gpu_launches": int(launches), "clocks": clocks}
+
+
+def bench_counts(args, rank, world, local, dev, dist):
+    """Diagnostic workload (config 5 shape): counter-group reduce over CPUs, NCCL sum of the
+    integer triples across ranks, then scaling + rates + IPC ratio + interval deltas."""
+    from dynolog_1_b200 import sharding
+    E, C, I = args.events, args.cpus, args.intervals
+    reads = tg.counts_trace(tg.stream_seed(5, rank), I, C, E, device=dev, multiplexed=True)
+    ctx = hbt.Context(local, max_cpus=max(C, 1))
+    ctx.use_torch_stream()
+    W = 3 + E
+    sums = torch.zeros((I, W), dtype=torch.int64, device=dev)
+    scaled = torch.zeros((I, E), dtype=torch.int64, device=dev)
+    rates = torch.zeros((I, E), dtype=torch.float32, device=dev)
+    ratio = torch.zeros((I, 1), dtype=torch.float64, device=dev)
+    deltas = torch.zeros((I, E), dtype=torch.int64, device=dev)
+    ratios = [(min(1, E - 1), 0)]
+
+    def step():
+        if dist is None:
+            ctx.counts_pipeline_dev(reads, I, C, E, ratios, sums, scaled, rates, ratio, deltas)
+        else:
+            ctx.counts_reduce_dev(reads, I, C, E, sums)
+            sharding.allreduce_partial_sums(sums, E)
+            ctx.counts_scale_dev(sums, I, E, ratios, None, scaled, rates, ratio, deltas)
+
+    for _ in range(max(args.warmup, 3)):
+        step()
+    ctx.sync()
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    l0 = ctx.launches
+    ms_step = timed_steps(step, args.steps, dist, dev)
+    launches = ctx.launches - l0
+    clocks = sampler.stop() if rank == 0 else None
+    if rank != 0:
+        return None
+    peak, peak_src = load_peaks()
+    algo = I * C * W * 8 + I * (W * 8 + E * 8 + E * 4 + 8 + E * 8)
+    ach = algo / (ms_step * 1e-3) / 1e9
+    return {"metric": "counter-group reads decoded+aggregated/sec", "value": I * C * world / (ms_step * 1e-3),
+            "unit": "reads/s", "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
+            "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "u64/f64", "data": "synthetic",
+            "config": {"workload": f"c5_counts: {C} CPUs x {E} events x {I} intervals per GPU, "
+                                   "reduce -> [NCCL sum] -> scale/rates/ratio/deltas",
+                       "l2": f"input {I * C * W * 8 / 2**20:.0f} MiB per step exceeds L2" if I * C * W * 8 > 2**27
+                             else "input smaller than L2: not a valid HBM measurement"},
+            "roofline": {"bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
+                         "traffic": load_traffic("k_counts_reduce"), "kernel": "k_counts_reduce (+ scale, diff)",
+                         "kernel_ms": ms_step, "algorithmic_bytes": int(algo), "peak_source": peak_src,
+                         "note": "timed as the whole step (2-3 launches), not one kernel"},
+            "gpu_launches": int(launches), "clocks": clocks}
+
+
 def run_reference(args, rank, world):
     """The reference's consume() (reference headers, oracle/_ref) + the harness's
     (pid,ip) map, all host threads, on a bounded sample of the same workload."""
@@ -227,6 +375,10 @@ def main():
                     help="list capacity per CPU: distinct keys + the samples of one decode")
     ap.add_argument("--agg", default="hist", choices=["hist", "none"],
                     help="none: decode + counters only (diagnostic, not the headline workload)")
+    ap.add_argument("--workload", default="c2_ip_hist", choices=["c2_ip_hist", "c3_deltas", "c5_counts"],
+                    help="c2_ip_hist is the headline (BASELINE configs[1]); the others are diagnostics")
+    ap.add_argument("--events", type=int, default=8)
+    ap.add_argument("--intervals", type=int, default=100000)
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
@@ -247,6 +399,15 @@ def main():
         import torch.distributed as dist_
         dist = dist_
         dist.init_process_group("nccl", device_id=dev)
+
+    if args.workload != "c2_ip_hist":
+        fn = bench_deltas if args.workload == "c3_deltas" else bench_counts
+        line = fn(args, rank, world, local, dev, dist)
+        if rank == 0:
+            print(json.dumps(line))
+        if dist is not None:
+            dist.destroy_process_group()
+        return
 
     ring_bytes = args.ring_mib << 20
     cpu_base = rank * args.cpus
@@ -275,7 +436,8 @@ def main():
     def step_exchange():
         # metric-table merge across the GPUs of the box: per-type record counters
         if dist is not None:
-            dist.all_reduce(counters_dev)
+            from dynolog_1_b200 import sharding
+            sharding.allreduce_record_counters(counters_dev)
 
     # ---- warm-up + validation -------------------------------------------------
     for it in range(max(args.warmup, 3)):
