@@ -186,6 +186,9 @@ def bench_deltas(args, rank, world, local, dev, dist):
     kms = []
 
     def step():
+        # every step decodes the same trace again: start from the state after enable(),
+        # or the second pass would (correctly) report a timestamp regression
+        ctx.reset_state(hbt.INVALID_TS)
         ctx.submit_rings_dev(bases_a, ring_bytes, tails_a, heads_a)
         ctx.decode(desc)
         step.res = ctx.fetch_results()
@@ -394,6 +397,9 @@ def main():
     assert torch.cuda.is_available(), "bench.py needs a GPU (there is no CPU fallback)"
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
+    # everything (torch ops, the library's kernels, the timing events) runs on ONE
+    # non-default stream, so torch.cuda.Event sees the kernels it brackets
+    torch.cuda.set_stream(torch.cuda.Stream(dev))
     dist = None
     if world > 1:
         import torch.distributed as dist_

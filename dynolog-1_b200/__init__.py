@@ -202,8 +202,16 @@ class Context:
         self._ck(self.lib.hbt_set_stream(self.h, C.c_void_p(stream_ptr) if stream_ptr else None))
 
     def use_torch_stream(self):
+        """Queue this ctx's work on torch's current stream.  That must be a
+        non-default stream (`torch.cuda.set_stream(torch.cuda.Stream())`): the
+        default stream's handle is 0, which hbt_set_stream reads as "use the
+        ctx's own stream", and events recorded on the default stream would then
+        not see the ctx's kernels."""
         import torch
-        self.set_stream(torch.cuda.current_stream(self.device).cuda_stream)
+        h = torch.cuda.current_stream(self.device).cuda_stream
+        if not h:
+            raise RuntimeError("use_torch_stream() needs a non-default current torch stream")
+        self.set_stream(h)
 
     def sync(self):
         self._ck(self.lib.hbt_sync(self.h))

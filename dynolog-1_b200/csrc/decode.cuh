@@ -1047,6 +1047,18 @@ __global__ void __launch_bounds__(64) k_finalize(const FinalizeParams p) {
   out.carry_tstamp = cts;
 }
 
+// Generator state right after enable(): counters 0, last_[] = 0, count_.tstamp = seed.
+__global__ void __launch_bounds__(64) k_seed_state(CpuState* st, uint32_t n_cpus, uint64_t seed) {
+  const uint32_t c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= n_cpus) return;
+  CpuState s;
+  for (int i = 0; i < HBT_NUM_COUNTERS; ++i) s.counters[i] = 0;
+  s.num_unknown = 0;
+  s.carry_tstamp = seed;
+  for (int i = 0; i < HBT_MAX_EVENTS; ++i) s.carry_last[i] = 0;
+  st[c] = s;
+}
+
 // Position of the record `skip` records after `from` (header walk by one thread
 // per flagged CPU); used only for a finite max_num_records.
 __global__ void __launch_bounds__(64)

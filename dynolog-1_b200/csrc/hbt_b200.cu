@@ -535,14 +535,12 @@ int hbt_set_cpu_base(hbt_ctx* ctx, uint32_t cpu_base) {
 
 int hbt_ring_reset_state(hbt_ctx* ctx, uint64_t seed_tstamp) {
   if (!ctx || ctx->n_cpus == 0) return fail(ctx, -EINVAL, "no rings configured");
-  std::vector<CpuState> init(ctx->n_cpus);
-  memset(init.data(), 0, init.size() * sizeof(CpuState));
-  for (auto& s : init) s.carry_tstamp = seed_tstamp;
-  CU(cudaMemcpyAsync(ctx->state[ctx->cur].p, init.data(), init.size() * sizeof(CpuState),
-                     cudaMemcpyHostToDevice, ctx->stream));
-  CU(cudaStreamSynchronize(ctx->stream));
+  if (int rc = complete_decode(ctx)) return rc;
+  k_seed_state<<<(ctx->n_cpus + 63) / 64, 64, 0, ctx->stream>>>(ctx->state[ctx->cur].p, ctx->n_cpus,
+                                                               seed_tstamp);
+  ++ctx->launches;
+  CU(cudaGetLastError());
   for (auto& w : ctx->win) w.active = false;
-  ctx->pending = false;
   ctx->have_results = false;
   return 0;
 }

@@ -114,6 +114,9 @@ def test_counts_dev_split_equals_pipeline(ctx):
     rates = torch.zeros((I, E), dtype=torch.float32, device="cuda")
     ratio = torch.zeros((I, 1), dtype=torch.float64, device="cuda")
     deltas = torch.zeros((I, E), dtype=torch.int64, device="cuda")
+    torch.cuda.synchronize()
+    prev_stream = torch.cuda.current_stream()
+    torch.cuda.set_stream(torch.cuda.Stream())
     ctx.use_torch_stream()
     try:
         ctx.counts_reduce_dev(reads, I, C, E, sums)
@@ -136,6 +139,8 @@ def test_counts_dev_split_equals_pipeline(ctx):
         assert torch.equal(tot, sums)
     finally:
         ctx.set_stream(None)
+        torch.cuda.synchronize()
+        torch.cuda.set_stream(prev_stream)
 
 
 # ---------------------------------------------------------------------------
