@@ -302,9 +302,13 @@ class Context:
     def hist_size(self) -> int:
         return int(self._ck(self.lib.hbt_hist_size(self.h)))
 
-    def hist_fetch(self) -> np.ndarray:
-        n = self.hist_size()
-        out = np.zeros(max(1, n), dtype=HIST_DTYPE)
+    def hist_fetch(self, out: np.ndarray | None = None) -> np.ndarray:
+        """Entries of the histogram.  `out`: optional caller-owned HIST_DTYPE array
+        (e.g. a view of pinned memory, which makes the D2H copy several times
+        faster); it must be large enough or -ENOSPC is raised."""
+        if out is None:
+            n = self.hist_size()
+            out = np.zeros(max(1, n), dtype=HIST_DTYPE)
         m = self._ck(self.lib.hbt_hist_fetch(self.h, _ptr(out), out.shape[0]))
         return out[:m]
 

@@ -55,62 +55,101 @@ struct CountsArgs {
   int do_scale;        // 0: K4 only
 };
 
-// One CTA per interval at a time (grid-stride).  Thread t of the first
-// `active = floor(BLOCK/W)*W` threads reads words t, t+active, ... of the
-// interval's contiguous C*W words, so its column (t % W) is fixed and the
-// partial sum lives in a register; consecutive threads read consecutive u64s
-// (coalesced 256 B per warp request).
-template <int BLOCK>
-__global__ void __launch_bounds__(BLOCK) k_counts_reduce(const CountsArgs a) {
-  __shared__ uint64_t part[BLOCK];
-  __shared__ uint64_t tot[3 + HBT_MAX_EVENTS];
-  __shared__ uint64_t sc[HBT_MAX_EVENTS];
-
+// One WARP per interval at a time (grid-stride over intervals), no shared memory and
+// no block barrier: the 64 resident warps of an SM each stream their own interval.
+//  - W = 3+E <= 32: the first `active = floor(32/W)*W` lanes read words lane,
+//    lane+active, ... of the interval's contiguous C*W words, so a lane's column
+//    (lane % W) is fixed and its partial sum lives in one register; a warp request is
+//    `active` consecutive u64s.  Lanes with equal column are then combined by shuffles.
+//  - W > 32 (WIDE): lane l owns columns l, l+32, l+64 of every CPU's row.
+// The scale/derive epilogue runs in the same warp (FP64 on lanes that hold a count).
+template <bool WIDE>
+__global__ void __launch_bounds__(256) k_counts_reduce(const CountsArgs a) {
   const uint32_t E = a.n_events;
   const uint32_t W = 3 + E;
-  const uint32_t active = (BLOCK / W) * W;
-  const uint32_t per_col = active / W;
-  const uint32_t t = threadIdx.x;
-  const uint32_t col = t % W;
+  const uint32_t lane = threadIdx.x & 31;
+  const uint64_t warp0 = (blockIdx.x * (uint64_t)blockDim.x + threadIdx.x) >> 5;
+  const uint64_t n_warps = ((uint64_t)gridDim.x * blockDim.x) >> 5;
   const uint64_t N = (uint64_t)a.n_cpus * W;
+  constexpr unsigned FULL = 0xffffffffu;
 
-  for (uint64_t i = blockIdx.x; i < a.n_intervals; i += gridDim.x) {
+  for (uint64_t i = warp0; i < a.n_intervals; i += n_warps) {
     const uint64_t* base = a.reads + i * N;
-    uint64_t acc = 0;
-    if (t < active) {
-      if (col == 0) {
-        // word0 = n_events of each T; a mismatch marks a failed read
-        // (CpuEventsGroupBase::read, CpuEventsGroup.h:599-614).
+    // s0/s1/s2: the sums of columns lane, lane+32, lane+64 (column 0 counts failed reads)
+    uint64_t s0 = 0, s1 = 0, s2 = 0;
+    if (!WIDE) {
+      const uint32_t groups = 32 / W, active = groups * W;
+      const uint32_t col = lane % W;
+      uint64_t acc = 0;
+      if (lane < active) {
+        if (col == 0) {
+          // word0 = n_events of each T; a mismatch marks a failed read
+          // (CpuEventsGroupBase::read, CpuEventsGroup.h:599-614)
+#pragma unroll 8
+          for (uint64_t f = lane; f < N; f += active) acc += (ld_stream_u64(base + f) != E);
+        } else {
+#pragma unroll 8
+          for (uint64_t f = lane; f < N; f += active) acc += ld_stream_u64(base + f);
+        }
+      }
+      s0 = acc;
+      for (uint32_t k = 1; k < groups; ++k) {
+        const uint64_t o = __shfl_sync(FULL, acc, (lane + k * W) & 31);
+        if (lane < W) s0 += o;
+      }
+    } else {
+      const bool has1 = lane + 32 < W, has2 = lane + 64 < W;
 #pragma unroll 4
-        for (uint64_t f = t; f < N; f += active) acc += (ld_stream_u64(base + f) != E);
-      } else {
-#pragma unroll 4
-        for (uint64_t f = t; f < N; f += active) acc += ld_stream_u64(base + f);
+      for (uint32_t c = 0; c < a.n_cpus; ++c) {
+        const uint64_t* row = base + (uint64_t)c * W;
+        const uint64_t v0 = ld_stream_u64(row + lane);
+        const uint64_t v1 = has1 ? ld_stream_u64(row + lane + 32) : 0;
+        const uint64_t v2 = has2 ? ld_stream_u64(row + lane + 64) : 0;
+        s0 += lane == 0 ? (uint64_t)(v0 != E) : v0;
+        s1 += v1;
+        s2 += v2;
       }
     }
-    part[t] = acc;
-    __syncthreads();
-    if (t < W) {
-      uint64_t s = 0;
-      for (uint32_t k = 0; k < per_col; ++k) s += part[t + k * W];
-      if (t == 0) s = (s == 0) ? (uint64_t)E : 0;  // zero() keeps n_events (:508-512)
-      tot[t] = s;
-      if (a.sums) a.sums[i * W + t] = s;
+    if (lane == 0) s0 = (s0 == 0) ? (uint64_t)E : 0;  // zero() keeps n_events (:508-512)
+    if (a.sums) {
+      uint64_t* out = a.sums + i * W;
+      if (lane < W) out[lane] = s0;
+      if (WIDE && lane + 32 < W) out[lane + 32] = s1;
+      if (WIDE && lane + 64 < W) out[lane + 64] = s2;
     }
-    __syncthreads();
     if (a.do_scale) {
-      const bool ok = tot[0] != 0;
-      if (t < E) {
-        const uint64_t c = ok ? scaled_count(tot[3 + t], tot[1], tot[2]) : 0;
-        sc[t] = c;
-        if (a.scaled) a.scaled[i * E + t] = c;
-        if (a.rates) a.rates[i * E + t] = rate_per_ms(c, tot[2]);
+      const bool ok = __shfl_sync(FULL, s0, 0) != 0;
+      const uint64_t te = __shfl_sync(FULL, s0, 1), tr = __shfl_sync(FULL, s0, 2);
+      // the scaled count of column j = lane + 32k is event j - 3
+      uint64_t c0 = 0, c1 = 0, c2 = 0;
+      if (lane >= 3 && lane < W) {
+        c0 = ok ? scaled_count(s0, te, tr) : 0;
+        if (a.scaled) a.scaled[i * E + lane - 3] = c0;
+        if (a.rates) a.rates[i * E + lane - 3] = rate_per_ms(c0, tr);
       }
-      if (a.ratio_out && a.n_ratios) {
-        __syncthreads();
-        if (t < a.n_ratios) {
-          const hbt_ratio r = a.ratios[t];
-          a.ratio_out[i * a.n_ratios + t] = ratio_of(sc[r.num_event], sc[r.den_event]);
+      if (WIDE && lane + 32 < W) {
+        c1 = ok ? scaled_count(s1, te, tr) : 0;
+        if (a.scaled) a.scaled[i * E + lane + 29] = c1;
+        if (a.rates) a.rates[i * E + lane + 29] = rate_per_ms(c1, tr);
+      }
+      if (WIDE && lane + 64 < W) {
+        c2 = ok ? scaled_count(s2, te, tr) : 0;
+        if (a.scaled) a.scaled[i * E + lane + 61] = c2;
+        if (a.rates) a.rates[i * E + lane + 61] = rate_per_ms(c2, tr);
+      }
+      if (a.ratio_out) {
+        for (uint32_t r = 0; r < a.n_ratios; ++r) {
+          const hbt_ratio q = a.ratios[r];
+          const uint32_t jn = 3 + q.num_event, jd = 3 + q.den_event;
+          const uint64_t xn0 = __shfl_sync(FULL, c0, jn & 31), xd0 = __shfl_sync(FULL, c0, jd & 31);
+          uint64_t xn = xn0, xd = xd0;
+          if (WIDE) {
+            const uint64_t xn1 = __shfl_sync(FULL, c1, jn & 31), xd1 = __shfl_sync(FULL, c1, jd & 31);
+            const uint64_t xn2 = __shfl_sync(FULL, c2, jn & 31), xd2 = __shfl_sync(FULL, c2, jd & 31);
+            xn = jn < 32 ? xn0 : (jn < 64 ? xn1 : xn2);
+            xd = jd < 32 ? xd0 : (jd < 64 ? xd1 : xd2);
+          }
+          if (lane == 0) a.ratio_out[i * a.n_ratios + r] = ratio_of(xn, xd);
         }
       }
     }

@@ -42,11 +42,17 @@ constexpr uint64_t kNone = ~0ull;          // "no position"
 constexpr uint64_t kInvalidTs = ~0ull;     // kInvalidTimeStamp (System.h:97)
 constexpr uint64_t kPrevCarry = ~0ull - 1; // "previous sample" = carry from the last call
 
-constexpr int kTile = 16384;   // bytes per tile
-constexpr int kStages = 3;     // tiles resident per CTA
-constexpr int kThreads = 256;  // threads per CTA
-constexpr int kSubWords = kTile / 8 / kThreads;  // 8 words = 64 B per thread
-static_assert(kSubWords == 8, "skew formula below assumes 8-word sub-chunks");
+#ifndef HBT_TILE_BYTES
+#define HBT_TILE_BYTES 16384
+#endif
+#ifndef HBT_CTA_THREADS
+#define HBT_CTA_THREADS 256
+#endif
+constexpr int kTile = HBT_TILE_BYTES;      // bytes per tile
+constexpr int kStages = 3;                 // tiles resident per CTA
+constexpr int kThreads = HBT_CTA_THREADS;  // threads per CTA
+constexpr int kSubWords = kTile / 8 / kThreads;  // words (8 B) of the tile per thread
+static_assert(kSubWords == 8 || kSubWords == 16, "skew formula below covers 8- and 16-word sub-chunks");
 
 // Event kinds for the interval state machine of CpuCountSampleGenerator.
 constexpr uint32_t EV_NONE = 0, EV_SAMPLE = 1, EV_LOST = 2;
@@ -268,6 +274,14 @@ struct Smem {
   uint32_t warp_ls[kThreads / 32];  // last SAMPLE start in the tile, relative + 1
 };
 
+// COUNT_DELTAS: (current SAMPLE, previous SAMPLE) positions of every row of the tile
+// in row order, so that the rows can be written by consecutive threads.
+constexpr int kMaxRowsPerTile = kTile / 48 + 1;  // a SAMPLE is at least 40 + 8 bytes
+struct RowDescs {
+  uint64_t far_prev;            // absolute position of a previous SAMPLE outside the tile
+  uint2 d[kMaxRowsPerTile];     // {current, previous} tile-relative; previous = kNoRel -> far_prev
+};
+
 // Sequential consume() over [st.pos, limit) by ONE thread: the slow path for
 // tiles the fast path declines and the definition of what the fast path must
 // equal.  Reads the ring through global memory.  Stops at `limit` (first record
@@ -389,21 +403,24 @@ struct TileView {
 // First word (tile-relative, in 8-byte words) of sub-chunk j.  The skew spreads
 // the lock-step header scan of a warp over all shared-memory banks.
 __device__ __forceinline__ uint32_t sub_begin_word(uint32_t j) {
-  return kSubWords * j + ((j >> 1) & 7);
+  // a warp's 32 sub-chunk starts must cover the 16 eight-byte bank pairs twice
+  return kSubWords * j + (kSubWords == 8 ? ((j >> 1) & 7) : (j & 15));
 }
 // Sub-chunk that holds tile word w.
 __device__ __forceinline__ uint32_t sub_of_word(uint32_t w) {
-  const uint32_t j = w >> 3;
+  const uint32_t j = w / kSubWords;
   return w < sub_begin_word(j) ? j - 1 : j;
 }
 
 template <int AGG>
-__global__ void __launch_bounds__(kThreads, 4) k_decode(const DecodeParams p) {
+__global__ void __launch_bounds__(kThreads, kThreads == 256 ? (kTile <= 16384 ? 4 : 2) : 4) k_decode(const DecodeParams p) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   uint8_t* stages = smem_raw;  // kStages * kTile
   Smem& sm = *reinterpret_cast<Smem*>(smem_raw + kStages * kTile);
   HistCache& cache =
       *reinterpret_cast<HistCache*>(smem_raw + kStages * kTile + ((sizeof(Smem) + 15) & ~15ull));
+  RowDescs& rowd =
+      *reinterpret_cast<RowDescs*>(smem_raw + kStages * kTile + ((sizeof(Smem) + 15) & ~15ull));
 
   const SegDesc seg = p.segs[blockIdx.x];
   const RingDesc ring = p.rings[seg.cpu];
@@ -703,12 +720,14 @@ __global__ void __launch_bounds__(kThreads, 4) k_decode(const DecodeParams p) {
       if (!slow || attempt == 1) break;
       // the stride prediction did not hold: guess again by scanning
     }
+    uint64_t n_rows0 = 0;
     if (!stopped && !slow) {
       // ---- phase 3: aggregate my records ----------------------------------------
       uint64_t row_i = 0;
       uint64_t in_ev = in_ev0;
       if (AGG == HBT_AGG_COUNT_DELTAS) {
-        row_i = st.n_rows + (srow - rows_j);
+        n_rows0 = st.n_rows;
+        row_i = n_rows0 + (srow - rows_j);
         for (uint32_t w = 0; w < warp; ++w) row_i += sm.warp_rows[w];
       }
       my_rec += __popc(mask);
@@ -730,17 +749,12 @@ __global__ void __launch_bounds__(kThreads, 4) k_decode(const DecodeParams p) {
         const uint32_t type = hdr_type(h);
         if (AGG == HBT_AGG_COUNT_DELTAS && type == REC_SAMPLE && h_sample) {
           if (ev_kind(in_ev) == EV_SAMPLE) {
-            const uint64_t ppos = ev_pos(in_ev);
-            const uint64_t pts = tv.word_abs(ppos + 8);
-            const uint64_t ts = tv.at(pos + 8);
-            uint64_t* row = seg.rows + (1 + row_i) * (2 + (uint64_t)d.n_events);
-            row[0] = pts;
-            row[1] = ts - pts;
-            for (uint32_t i = 0; i < d.n_events; ++i) {
-              const uint64_t v = xform(d, i, tv.at(pos + 40 + 8 * i));
-              const uint64_t pv = xform(d, i, tv.word_abs(ppos + 40 + 8ull * i));
-              row[2 + i] = v - pv;
-            }
+            // row = {t_prev, t - t_prev, v_i - v_prev_i}: written cooperatively below
+            const uint64_t pp = ev_pos(in_ev);
+            uint32_t prel = kNoRel;
+            if (pp >= t_begin && pp - t_begin < 2ull * kTile) prel = (uint32_t)(pp - t_begin);
+            else rowd.far_prev = pp;  // only the tile's first row can reach back this far
+            rowd.d[row_i - n_rows0] = make_uint2(pos, prel);
             ++row_i;
           }
           in_ev = ev_make(t_begin + pos, EV_SAMPLE);
@@ -760,7 +774,34 @@ __global__ void __launch_bounds__(kThreads, 4) k_decode(const DecodeParams p) {
         if (pending_seam) st.first_ev = ev_make(t_begin + (first_ev >> 2) - 1, EV_SAMPLE);
       }
     }
-    if (AGG == HBT_AGG_COUNT_DELTAS) __syncthreads();  // row_i readers before n_rows moves
+    if (AGG == HBT_AGG_COUNT_DELTAS) {
+      __syncthreads();  // row descriptors are complete; nobody reads st.n_rows any more
+      if (!stopped && !slow) {
+        // ---- phase 3b: write the tile's rows, consecutive threads -> consecutive words
+        uint32_t trows = 0;
+        for (uint32_t w = 0; w < kThreads / 32; ++w) trows += sm.warp_rows[w];
+        const uint32_t wpr = 2 + d.n_events;
+        const float inv = __frcp_rn((float)wpr);
+        uint64_t* out = seg.rows + (1 + n_rows0) * (uint64_t)wpr;
+        const uint32_t total = trows * wpr;
+        for (uint32_t f = tid; f < total; f += kThreads) {
+          uint32_t r = (uint32_t)((float)f * inv);
+          if (r * wpr > f) --r;
+          else if ((r + 1) * wpr <= f) ++r;
+          const uint32_t w = f - r * wpr;
+          const uint2 rd = rowd.d[r];
+          const uint32_t off = w < 2 ? 8u : 40u + 8u * (w - 2);  // tstamp, or value[w-2]
+          const uint64_t cur = tv.at(rd.x + off);
+          const uint64_t prv = rd.y != kNoRel ? tv.at(rd.y + off)
+                                              : ring_word_g(ring, rowd.far_prev + off);
+          uint64_t v;
+          if (w == 0) v = prv;
+          else if (w == 1) v = cur - prv;
+          else v = xform(d, w - 2, cur) - xform(d, w - 2, prv);
+          out[f] = v;
+        }
+      }
+    }
     if (tid == 0) {
       if (!stopped) {
         const uint32_t a = attempt;  // the attempt whose scatter results were verified

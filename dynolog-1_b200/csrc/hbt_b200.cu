@@ -167,6 +167,7 @@ bool is_pow2(uint64_t x) { return x && !(x & (x - 1)); }
 size_t decode_smem_bytes(int agg) {
   size_t s = (size_t)kStages * kTile + ((sizeof(Smem) + 15) & ~size_t(15));
   if (agg == HBT_AGG_IP_HISTOGRAM) s += sizeof(HistCache);
+  if (agg == HBT_AGG_COUNT_DELTAS) s += sizeof(RowDescs);
   return s;
 }
 
@@ -962,8 +963,10 @@ static int upload_ratios(hbt_ctx* ctx, const hbt_ratio* ratios, uint32_t n_ratio
 }
 
 static int counts_grid(const hbt_ctx* ctx, uint64_t n_intervals) {
+  // one warp per interval, 8 warps per CTA, 8 CTAs per SM
   uint64_t g = (uint64_t)ctx->sm_count * 8;
-  if (g > n_intervals) g = n_intervals;
+  const uint64_t need = (n_intervals + 7) / 8;
+  if (g > need) g = need;
   return (int)(g ? g : 1);
 }
 
@@ -988,7 +991,10 @@ static int counts_launch(hbt_ctx* ctx, const uint64_t* reads, uint64_t n_interva
     CU(ctx->c_scaled.reserve(n_intervals * n_events));
     a.scaled = ctx->c_scaled.p;
   }
-  k_counts_reduce<256><<<counts_grid(ctx, n_intervals), 256, 0, ctx->stream>>>(a);
+  if (3 + n_events <= 32)
+    k_counts_reduce<false><<<counts_grid(ctx, n_intervals), 256, 0, ctx->stream>>>(a);
+  else
+    k_counts_reduce<true><<<counts_grid(ctx, n_intervals), 256, 0, ctx->stream>>>(a);
   ++ctx->launches;
   CU(cudaGetLastError());
   if (do_scale && deltas) {

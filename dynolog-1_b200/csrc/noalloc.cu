@@ -87,9 +87,12 @@ extern "C" int hbt_counts_deltas_static_dev(const uint64_t* reads, uint64_t n_in
   cudaGetDevice(&dev);
   if (cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || sms <= 0)
     sms = 148;
-  uint64_t grid = (uint64_t)sms * 8;
-  if (grid > n_intervals) grid = n_intervals;
-  k_counts_reduce<256><<<(unsigned)grid, 256, 0, stream>>>(a);
+  uint64_t grid = (uint64_t)sms * 8;  // one warp per interval, 8 warps per CTA
+  if (grid > (n_intervals + 7) / 8) grid = (n_intervals + 7) / 8;
+  if (3 + n_events <= 32)
+    k_counts_reduce<false><<<(unsigned)grid, 256, 0, stream>>>(a);
+  else
+    k_counts_reduce<true><<<(unsigned)grid, 256, 0, stream>>>(a);
   if (cudaGetLastError() != cudaSuccess) return -EIO;
   const uint64_t total = n_intervals * n_events;
   uint64_t g2 = (total + 255) / 256;
