@@ -82,14 +82,14 @@ __global__ void __launch_bounds__(256) k_counts_reduce(const CountsArgs a) {
       const uint32_t col = lane % W;
       uint64_t acc = 0;
       if (lane < active) {
-        if (col == 0) {
-          // word0 = n_events of each T; a mismatch marks a failed read
-          // (CpuEventsGroupBase::read, CpuEventsGroup.h:599-614)
+        // word0 = n_events of each T; a mismatch marks a failed read
+        // (CpuEventsGroupBase::read, CpuEventsGroup.h:599-614).  One loop for all
+        // columns (a select, not a branch: the lanes of a warp must not diverge here).
+        const bool is0 = col == 0;
 #pragma unroll 8
-          for (uint64_t f = lane; f < N; f += active) acc += (ld_stream_u64(base + f) != E);
-        } else {
-#pragma unroll 8
-          for (uint64_t f = lane; f < N; f += active) acc += ld_stream_u64(base + f);
+        for (uint64_t f = lane; f < N; f += active) {
+          const uint64_t v = ld_stream_u64(base + f);
+          acc += is0 ? (uint64_t)(v != E) : v;
         }
       }
       s0 = acc;
@@ -153,6 +153,126 @@ __global__ void __launch_bounds__(256) k_counts_reduce(const CountsArgs a) {
         }
       }
     }
+  }
+}
+
+// Per-warp epilogue: s0 holds the sum of column `lane` (column 0: number of failed
+// reads); writes sums / scaled / rates / ratios of interval i.
+__device__ __forceinline__ void counts_epilogue_narrow(const CountsArgs& a, uint64_t i, uint32_t lane,
+                                                       uint64_t s0) {
+  constexpr unsigned FULL = 0xffffffffu;
+  const uint32_t E = a.n_events, W = 3 + E;
+  if (lane == 0) s0 = (s0 == 0) ? (uint64_t)E : 0;  // zero() keeps n_events (:508-512)
+  if (a.sums && lane < W) a.sums[i * W + lane] = s0;
+  if (!a.do_scale) return;
+  const bool ok = __shfl_sync(FULL, s0, 0) != 0;
+  const uint64_t te = __shfl_sync(FULL, s0, 1), tr = __shfl_sync(FULL, s0, 2);
+  uint64_t c0 = 0;
+  if (lane >= 3 && lane < W) {
+    c0 = ok ? scaled_count(s0, te, tr) : 0;
+    if (a.scaled) a.scaled[i * E + lane - 3] = c0;
+    if (a.rates) a.rates[i * E + lane - 3] = rate_per_ms(c0, tr);
+  }
+  if (a.ratio_out) {
+    for (uint32_t r = 0; r < a.n_ratios; ++r) {
+      const hbt_ratio q = a.ratios[r];
+      const uint64_t xn = __shfl_sync(FULL, c0, (3 + q.num_event) & 31);
+      const uint64_t xd = __shfl_sync(FULL, c0, (3 + q.den_event) & 31);
+      if (lane == 0) a.ratio_out[i * a.n_ratios + r] = ratio_of(xn, xd);
+    }
+  }
+}
+
+// Streaming variant for W <= 32 and intervals that fit a stage: whole intervals are
+// staged in shared memory by 1-D bulk async copies (TMA unit), two stages deep, so
+// the bytes in flight do not depend on registers or on how many warps are resident.
+// The warps of the CTA reduce one staged interval each -- reading consecutive words
+// (conflict-free) with the fixed-column lane mapping of k_counts_reduce -- and run
+// the epilogue themselves.  When a stage holds fewer than 8 intervals each interval
+// is cut into row slices so that all 8 warps have work; the slices meet in a small
+// shared-memory table.  Needs C*W even (16-byte aligned interval starts).
+constexpr int kCountsStageBytes = 48 * 1024;
+constexpr int kCountsStages = 2;
+
+static __global__ void __launch_bounds__(256, 2)
+    k_counts_reduce_tma(const CountsArgs a, uint32_t per_stage) {
+  extern __shared__ __align__(128) uint8_t cs_smem[];
+  uint64_t* bar = reinterpret_cast<uint64_t*>(cs_smem + kCountsStages * kCountsStageBytes);
+  uint64_t* spart = bar + 8;  // [<= 8 items][32] partial column sums of row slices
+  const uint32_t E = a.n_events, W = 3 + E;
+  const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const uint64_t N = (uint64_t)a.n_cpus * W;
+  const uint32_t groups = 32 / W, active = groups * W;
+  const bool is0 = lane % W == 0;
+  constexpr unsigned FULL = 0xffffffffu;
+  // this CTA's contiguous range of intervals, walked in chunks of per_stage intervals
+  const uint64_t per_cta = (a.n_intervals + gridDim.x - 1) / gridDim.x;
+  const uint64_t i_begin = blockIdx.x * per_cta;
+  const uint64_t i_end = min(a.n_intervals, i_begin + per_cta);
+  if (i_begin >= i_end) return;
+  const uint64_t n_chunks = (i_end - i_begin + per_stage - 1) / per_stage;
+  if (tid == 0) {
+    for (int s = 0; s < kCountsStages; ++s) mbar_init(&bar[s], 1);
+    fence_mbar_init();
+  }
+  __syncthreads();
+  const uint64_t policy = l2_policy_evict_first();
+  auto issue = [&](uint64_t k) {
+    const int s = (int)(k % kCountsStages);
+    const uint64_t i0 = i_begin + k * per_stage;
+    const uint32_t n = (uint32_t)min((uint64_t)per_stage, i_end - i0);
+    const uint32_t bytes = (uint32_t)(n * N * 8);
+    mbar_arrive_expect_tx(&bar[s], bytes);
+    bulk_g2s_hint(cs_smem + s * kCountsStageBytes, a.reads + i0 * N, bytes, &bar[s], policy);
+  };
+  if (tid == 0) {
+    issue(0);
+    if (n_chunks > 1) issue(1);
+  }
+  uint32_t phase_bits = 0;
+  for (uint64_t k = 0; k < n_chunks; ++k) {
+    const int s = (int)(k % kCountsStages);
+    mbar_wait(&bar[s], (phase_bits >> s) & 1);
+    phase_bits ^= 1u << s;
+    const uint64_t i0 = i_begin + k * per_stage;
+    const uint32_t n = (uint32_t)min((uint64_t)per_stage, i_end - i0);
+    const uint32_t sbase = smem_u32(cs_smem + s * kCountsStageBytes);
+    uint32_t Q = 1;  // row slices per interval
+    while (Q * 2 * n <= 8 && Q * 2 <= a.n_cpus) Q *= 2;
+    const uint32_t rows_per = (a.n_cpus + Q - 1) / Q;
+    for (uint32_t item = warp; item < n * Q; item += 8) {
+      const uint32_t j = item / Q, q = item - j * Q;
+      const uint32_t r0 = q * rows_per, r1 = min(a.n_cpus, r0 + rows_per);
+      const uint32_t ibase = sbase + (uint32_t)((j * N + (uint64_t)r0 * W) * 8);
+      const uint32_t words = (r1 > r0 ? r1 - r0 : 0) * W;
+      uint64_t acc = 0;
+      if (lane < active) {
+#pragma unroll 4
+        for (uint32_t f = lane; f < words; f += active) {
+          const uint64_t v = lds_u64(ibase + 8 * f);
+          acc += is0 ? (uint64_t)(v != E) : v;
+        }
+      }
+      uint64_t s0 = acc;
+      for (uint32_t g = 1; g < groups; ++g) {
+        const uint64_t o = __shfl_sync(FULL, acc, (lane + g * W) & 31);
+        if (lane < W) s0 += o;
+      }
+      if (Q == 1) counts_epilogue_narrow(a, i0 + j, lane, s0);
+      else if (lane < W) spart[item * 32 + lane] = s0;
+    }
+    if (Q > 1) {
+      __syncthreads();
+      if (warp < n) {
+        uint64_t s0 = 0;
+        if (lane < W)
+          for (uint32_t q = 0; q < Q; ++q) s0 += spart[(warp * Q + q) * 32 + lane];
+        counts_epilogue_narrow(a, i0 + warp, lane, s0);
+      }
+    }
+    fence_proxy_async();
+    __syncthreads();  // the stage (and spart) are free again
+    if (tid == 0 && k + kCountsStages < n_chunks) issue(k + kCountsStages);
   }
 }
 

@@ -201,17 +201,16 @@ __device__ __forceinline__ void hist_append(const HistLists& t, uint32_t cpu, ui
 
 // Shared-memory privatised (pid,ip) cache of one segment.  Its job is the heavy
 // hitters: a key that occurs thousands of times in a CPU's window would otherwise
-// append thousands of entries to one list.  Two-way set associative, a state word
-// per slot (0 empty, 1 being written, 2 ready).  A sample whose two slots hold other
-// keys -- or one in the middle of being written -- bypasses the cache and is appended
-// to its list directly, so nothing ever spins and every sample is counted exactly once.
-// Frequent keys show up while the cache is still mostly empty and keep their slot
-// for the rest of the segment.  Flushed to the lists (weighted entries) at segment end.
+// append thousands of entries to one list.  Two-way set associative, 16-byte slots
+// {ip, pid | count << 32}; an all-zero slot is empty (a live slot has count >= 1).
+// A slot is claimed AND counted by one 128-bit shared-memory CAS, so there is never
+// a half-written slot to wait for; a sample whose two slots hold other keys is
+// appended to its list directly.  Every sample is counted exactly once.  Flushed
+// to the lists (weighted entries) at segment end.
 constexpr int kCacheSlots = 1024;
 
 struct HistCache {
-  ulonglong2 slots[kCacheSlots];  // {ip, pid | count << 32}
-  uint32_t state[kCacheSlots];
+  ulonglong2 slots[kCacheSlots];
 };
 
 __device__ __forceinline__ void hist_count(const HistLists& t, HistCache& c, uint32_t cpu,
@@ -220,22 +219,14 @@ __device__ __forceinline__ void hist_count(const HistLists& t, HistCache& c, uin
   uint32_t i = (hash ^ (hash >> 16)) & (kCacheSlots - 2);  // 2-way: slots i, i + 1
 #pragma unroll
   for (int way = 0; way < 2; ++way, ++i) {
-    uint32_t st = *reinterpret_cast<volatile uint32_t*>(c.state + i);
-    if (st == 0) {
-      st = atomicCAS(c.state + i, 0u, 1u);
-      if (st == 0) {  // claimed: publish the key, count it
-        c.slots[i].x = ip;
-        reinterpret_cast<uint32_t*>(&c.slots[i].y)[0] = pid;
-        atomicAdd(reinterpret_cast<uint32_t*>(&c.slots[i].y) + 1, 1u);
-        __threadfence_block();
-        *reinterpret_cast<volatile uint32_t*>(c.state + i) = 2;
-        return;
-      }
-    }
-    if (st != 2) break;  // being written by another thread: do not wait for it
     const volatile ulonglong2* vs = c.slots + i;
-    if (vs->x == ip && (uint32_t)vs->y == pid) {
-      atomicAdd(reinterpret_cast<uint32_t*>(&c.slots[i].y) + 1, 1u);
+    uint64_t lo = vs->x, hi = vs->y;
+    if (lo == 0 && hi == 0) {
+      cas128_shared(smem_u32(c.slots + i), 0, 0, ip, (uint64_t)pid | (1ull << 32), lo, hi);
+      if (lo == 0 && hi == 0) return;  // claimed with count 1
+    }
+    if (lo == ip && (uint32_t)hi == pid && (hi >> 32) != 0) {
+      atomicAdd(reinterpret_cast<uint32_t*>(c.slots + i) + 3, 1u);
       return;
     }
   }
@@ -453,10 +444,7 @@ __global__ void __launch_bounds__(kThreads, kThreads == 256 ? (kTile <= 16384 ? 
   }
   sm.expect[tid] = kNoRel;
   if (AGG == HBT_AGG_IP_HISTOGRAM) {
-    for (int i = tid; i < kCacheSlots; i += kThreads) {
-      cache.slots[i] = make_ulonglong2(0, 0);
-      cache.state[i] = 0;
-    }
+    for (int i = tid; i < kCacheSlots; i += kThreads) cache.slots[i] = make_ulonglong2(0, 0);
   }
   __syncthreads();
 
@@ -849,8 +837,8 @@ __global__ void __launch_bounds__(kThreads, kThreads == 256 ? (kTile <= 16384 ? 
   // ---- segment epilogue --------------------------------------------------------
   if (AGG == HBT_AGG_IP_HISTOGRAM) {
     for (int i = tid; i < kCacheSlots; i += kThreads) {
-      if (cache.state[i] == 2) {
-        const ulonglong2 e = cache.slots[i];
+      const ulonglong2 e = cache.slots[i];
+      if ((e.y >> 32) != 0) {
         hist_append(p.hist, seg.cpu, e.x, (uint32_t)e.y, (uint32_t)(e.y >> 32),
                     hist_hash(e.x, (uint32_t)e.y));
       }

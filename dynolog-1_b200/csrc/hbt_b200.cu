@@ -128,6 +128,7 @@ struct hbt_ctx {
   uint32_t hist_buckets = 0, hist_cap = 0;
   bool hist_pending_fold = false;  // the last decode appended raw samples not yet folded
   bool agg_attr_set = false;
+  bool counts_attr_set = false;
   uint64_t hist_samples = 0;       // upper bound of samples added since the last clear
   DevBuf<hbt_hist_entry> hist_out;
   DevBuf<unsigned long long> hist_n;
@@ -991,10 +992,27 @@ static int counts_launch(hbt_ctx* ctx, const uint64_t* reads, uint64_t n_interva
     CU(ctx->c_scaled.reserve(n_intervals * n_events));
     a.scaled = ctx->c_scaled.p;
   }
-  if (3 + n_events <= 32)
+  const uint64_t interval_bytes = (uint64_t)n_cpus * (3 + n_events) * 8;
+  const bool tma_ok = 3 + n_events <= 32 && interval_bytes <= (uint64_t)kCountsStageBytes &&
+                      (interval_bytes & 15) == 0 && ((uintptr_t)reads & 15) == 0 &&
+                      !getenv("HBT_COUNTS_NO_TMA");
+  if (tma_ok) {
+    // whole intervals staged in shared memory by bulk async copies
+    const size_t smem = (size_t)kCountsStages * kCountsStageBytes + 64 + 8 * 32 * 8;
+    if (!ctx->counts_attr_set) {
+      CU(cudaFuncSetAttribute(k_counts_reduce_tma, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+      ctx->counts_attr_set = true;
+    }
+    const uint32_t per_stage = (uint32_t)(kCountsStageBytes / interval_bytes);
+    uint64_t grid = (uint64_t)ctx->sm_count * 2;
+    const uint64_t chunks = (n_intervals + per_stage - 1) / per_stage;
+    if (grid > chunks) grid = chunks;
+    k_counts_reduce_tma<<<(unsigned)grid, 256, smem, ctx->stream>>>(a, per_stage);
+  } else if (3 + n_events <= 32) {
     k_counts_reduce<false><<<counts_grid(ctx, n_intervals), 256, 0, ctx->stream>>>(a);
-  else
+  } else {
     k_counts_reduce<true><<<counts_grid(ctx, n_intervals), 256, 0, ctx->stream>>>(a);
+  }
   ++ctx->launches;
   CU(cudaGetLastError());
   if (do_scale && deltas) {

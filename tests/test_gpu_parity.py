@@ -457,3 +457,86 @@ def test_device_resident_rings(ctx):
     host = imgs.cpu().numpy().view(np.uint64)
     for cpu, (tail, head) in enumerate(meta):
         check_cpu(ctx, cpu, res[cpu], orc.port_consume(host[cpu], tail, head, desc), desc)
+
+
+# ---------------------------------------------------------------------------
+# API behaviour around the kernels
+# ---------------------------------------------------------------------------
+def test_hist_capacity_overflow_is_loud(ctx):
+    """Lists too small for one decode: -ENOSPC from fetch_results, never a silent drop."""
+    import errno
+    ds = 1 << 20
+    n = (ds - 8192) // 40
+    s = tg.ip_sample_stream(9, n, cpu=0, n_pids=4096, n_ips=65536)
+    ring, head = ring_np(s, ds, 0)
+    ctx.ring_configure(1, ds)
+    ctx.reset_state(hbt.INVALID_TS)
+    ctx.hist_configure(4096)  # far fewer entries than samples
+    ctx.submit_ring_image(0, ring, 0, head)
+    ctx.decode(hbt.ip_desc(40))
+    with pytest.raises(hbt.HbtError) as e:
+        ctx.fetch_results()
+    assert e.value.code == -errno.ENOSPC
+    # a sufficient capacity works, and clear() empties the lists
+    ctx.hist_configure(1 << 18)
+    ctx.submit_ring_image(0, ring, 0, head)
+    ctx.decode(hbt.ip_desc(40))
+    ctx.fetch_results()
+    want = orc.port_consume(ring, 0, head, hbt.ip_desc(40))["hist"]
+    assert orc.hist_to_dict(ctx.hist_fetch()) == want
+    ctx.hist_clear()
+    assert ctx.hist_size() == 0
+
+
+def test_heavy_hitter_key(ctx):
+    """One key carries 90 % of the samples: the segment cache must absorb it (a list
+    holds 2048 entries) and the count must still be exact."""
+    ds = 1 << 22
+    n = (ds - 8192) // 40
+    s = tg.ip_sample_stream(10, n, cpu=0, n_pids=64, n_ips=4096).clone()
+    hot = tg.rand_uniform(77, n) < 0.9
+    s.view(n, 5)[hot, 1] = 0x401000
+    s.view(n, 5)[hot, 2] = 4242 | (4242 << 32)
+    tail = tg.random_tail(4, ds)
+    ring, head = ring_np(s, ds, tail)
+    desc = hbt.ip_desc(40)
+    res = gpu_decode(ctx, [(ring, tail, head)], desc, ds, hist_slots=1 << 18)
+    want = orc.port_consume(ring, tail, head, desc)
+    check_cpu(ctx, 0, res[0], want, desc)
+    got = orc.hist_to_dict(ctx.hist_fetch())
+    assert got == want["hist"]
+    assert got[(0, 4242, 0x401000)] > 0.85 * n
+
+
+def test_batch_submit_and_device_views(ctx):
+    import ctypes as C
+    import torch
+    ds, E, n_cpus = 1 << 20, 4, 3
+    desc = hbt.sampling_desc(E)
+    imgs = torch.zeros((n_cpus, ds // 8), dtype=torch.int64, device="cuda")
+    tails, heads = [], []
+    for cpu in range(n_cpus):
+        s = tg.group_sample_stream(500 + cpu, 9000, E, device="cuda", lost_every=777)
+        tail = tg.random_tail(cpu + 20, ds)
+        ring, head = tg.place_in_ring(s, ds, tail, fill_seed=5)
+        imgs[cpu] = ring
+        tails.append(tail)
+        heads.append(head)
+    torch.cuda.synchronize()
+    ctx.ring_configure(n_cpus, 0)
+    ctx.reset_state(hbt.INVALID_TS)
+    bases = np.array([imgs[c].data_ptr() for c in range(n_cpus)], dtype=np.uint64)
+    ctx.submit_rings_dev(bases, ds, np.array(tails, np.uint64), np.array(heads, np.uint64))
+    ctx.decode(desc)
+    res = ctx.fetch_results()
+    host = imgs.cpu().numpy().view(np.uint64)
+    for cpu in range(n_cpus):
+        want = orc.port_consume(host[cpu], tails[cpu], heads[cpu], desc)
+        check_cpu(ctx, cpu, res[cpu], want, desc)
+        # device view of the same rows: slabs in stream order
+        k = ctx.lib.hbt_rows_max_slabs(ctx.h)
+        ptrs = (C.c_void_p * k)()
+        ns = (C.c_uint64 * k)()
+        n_slabs = C.c_uint32()
+        assert ctx.lib.hbt_rows_slabs_dev(ctx.h, cpu, ptrs, ns, C.byref(n_slabs)) == 0
+        assert sum(ns[i] for i in range(n_slabs.value)) == want["n_rows"]
