@@ -510,14 +510,112 @@ __global__ void __launch_bounds__(kThreads, kThreads == 256 ? (kTile <= 16384 ? 
     const bool predict = S >= 8 && erel < (uint32_t)kTile;
     const float rcpS = predict ? __frcp_rn((float)S) : 0.f;
 
+    // ---- uniform fast path -------------------------------------------------------
+    // When the previous tile held records of one size S, try the same for this tile:
+    // record k would start at entry + k*S.  Every thread checks the headers of its
+    // records k = tid, tid + 256, ...; if ALL of them carry size S the record chain IS
+    // entry + k*S (induction from the exact entry) -- no guessing, no sub-chunks.  Any
+    // other record (other size, bad SAMPLE/READ layout, timestamp regression, a counted
+    // non-SAMPLE type) sends the tile to the general path below.
+    bool ufp_done = false;
+    if (predict && !stopped && S <= (uint32_t)kTile) {
+      const uint32_t n_t = lim > erel ? (lim - erel + S - 1) / S : 0u;  // records starting in the tile
+      const uint64_t in_ev = st.ev;         // interval state in front of the tile
+      const uint64_t n_rows_in = st.n_rows;
+      bool ok = true;
+      uint32_t my_n = 0;
+      for (uint32_t k = tid; k < n_t && ok; k += kThreads) {
+        const uint32_t pos = erel + k * S;
+        const uint64_t h = tv.at(pos);
+        const uint32_t type = hdr_type(h);
+        if (hdr_size(h) != S) {
+          ok = false;
+        } else if (type == REC_SAMPLE && h_sample) {
+          if (group_layout) {
+            const uint64_t nr = tv.at(pos + 16);
+            if ((uint64_t)S != 40 + 8 * nr || (AGG == HBT_AGG_COUNT_DELTAS && nr != d.n_events)) ok = false;
+            if (AGG == HBT_AGG_COUNT_DELTAS && ok) {
+              const uint64_t ts = tv.at(pos + 8);
+              if (k > 0) {
+                if (tv.at(pos - S + 8) > ts) ok = false;
+              } else if (ev_kind(in_ev) == EV_SAMPLE) {
+                if (tv.word_abs(ev_pos(in_ev) + 8) > ts) ok = false;
+              }
+            }
+          } else if (S != d.ip_sample_bytes) {
+            ok = false;
+          }
+          ++my_n;
+        } else if (AGG == HBT_AGG_COUNT_DELTAS || counter_of(type, d.handled_mask) >= 0) {
+          ok = false;  // LOST / READ / context-switch records: the general path counts them
+        }
+      }
+      if (__syncthreads_and(ok)) {
+        ufp_done = true;
+        my_rec += (n_t > tid) ? (n_t - tid + kThreads - 1) / kThreads : 0u;
+        my_sample += my_n;
+        if (AGG == HBT_AGG_IP_HISTOGRAM) {
+          for (uint32_t k = tid; k < n_t; k += kThreads) {
+            const uint32_t pos = erel + k * S;
+            if (hdr_type(tv.at(pos)) == REC_SAMPLE && h_sample)
+              hist_count(p.hist, cache, seg.cpu, tv.at(pos + 8), (uint32_t)tv.at(pos + 16));
+          }
+        }
+        uint32_t rows_tile = 0;
+        if (AGG == HBT_AGG_COUNT_DELTAS && n_t > 0) {
+          // every record is a SAMPLE: record k > 0 closes the interval opened by k-1;
+          // record 0 depends on what came before the tile
+          const uint32_t ik = ev_kind(in_ev);
+          const uint32_t first_row = ik == EV_SAMPLE ? 1u : 0u;
+          rows_tile = n_t - 1 + first_row;
+          const uint32_t wpr = 2 + d.n_events;
+          const float inv = __frcp_rn((float)wpr);
+          uint64_t* out = seg.rows + (1 + n_rows_in) * (uint64_t)wpr;
+          const uint32_t total = rows_tile * wpr;
+          const uint64_t far_prev = ev_pos(in_ev);
+          for (uint32_t f = tid; f < total; f += kThreads) {
+            uint32_t r = (uint32_t)((float)f * inv);
+            if (r * wpr > f) --r;
+            else if ((r + 1) * wpr <= f) ++r;
+            const uint32_t w = f - r * wpr;
+            const uint32_t k = r + 1 - first_row;  // the record that closes row r
+            const uint32_t cpos = erel + k * S;
+            const uint32_t off = w < 2 ? 8u : 40u + 8u * (w - 2);
+            const uint64_t cur = tv.at(cpos + off);
+            const uint64_t prv = k > 0 ? tv.at(cpos - S + off) : ring_word_g(ring, far_prev + off);
+            uint64_t v;
+            if (w == 0) v = prv;
+            else if (w == 1) v = cur - prv;
+            else v = xform(d, w - 2, cur) - xform(d, w - 2, prv);
+            out[f] = v;
+          }
+          if (tid == 0) {
+            if (ik == EV_LOST) ++st.n_unknown;  // record 0 re-seeds after a LOST
+            else if (ik == EV_NONE) st.first_ev = ev_make(t_begin + erel, EV_SAMPLE);  // seam
+          }
+        }
+        if (tid == 0 && n_t > 0) {
+          if (st.entry == kNone) st.entry = t_begin + erel;
+          st.pos = t_begin + erel + (uint64_t)n_t * S;
+          if (AGG == HBT_AGG_COUNT_DELTAS) {
+            const uint64_t last = t_begin + erel + (uint64_t)(n_t - 1) * S;
+            st.ev = ev_make(last, EV_SAMPLE);
+            st.last_sample = last;
+            st.n_rows += rows_tile;
+          }
+        }
+      }
+    }
+
     const uint32_t se = min(se_full, lim);
-    const bool live = !stopped && sb < se;
+    const bool live = !stopped && !ufp_done && sb < se;
 
     uint32_t my_entry, mask, smask, omask, my_x, first_ev, last_ev, my_ls, rows_local,
         unknown_local, sev, srow, rows_j, unknown_j;
     uint64_t in_ev0;
     bool owner, pending_seam, slow;
     uint32_t attempt = predict ? 0u : 1u;
+    if (!ufp_done) {
 #pragma unroll 1
     for (;; ++attempt) {
       // ---- phase 1: guess + walk over the own sub-chunk -------------------------
@@ -708,8 +806,10 @@ __global__ void __launch_bounds__(kThreads, kThreads == 256 ? (kTile <= 16384 ? 
       if (!slow || attempt == 1) break;
       // the stride prediction did not hold: guess again by scanning
     }
+    }  // !ufp_done
     uint64_t n_rows0 = 0;
-    if (!stopped && !slow) {
+    if (ufp_done) slow = false;
+    if (!stopped && !slow && !ufp_done) {
       // ---- phase 3: aggregate my records ----------------------------------------
       uint64_t row_i = 0;
       uint64_t in_ev = in_ev0;
@@ -762,7 +862,7 @@ __global__ void __launch_bounds__(kThreads, kThreads == 256 ? (kTile <= 16384 ? 
         if (pending_seam) st.first_ev = ev_make(t_begin + (first_ev >> 2) - 1, EV_SAMPLE);
       }
     }
-    if (AGG == HBT_AGG_COUNT_DELTAS) {
+    if (AGG == HBT_AGG_COUNT_DELTAS && !ufp_done) {
       __syncthreads();  // row descriptors are complete; nobody reads st.n_rows any more
       if (!stopped && !slow) {
         // ---- phase 3b: write the tile's rows, consecutive threads -> consecutive words
@@ -790,7 +890,7 @@ __global__ void __launch_bounds__(kThreads, kThreads == 256 ? (kTile <= 16384 ? 
         }
       }
     }
-    if (tid == 0) {
+    if (tid == 0 && !ufp_done) {
       if (!stopped) {
         const uint32_t a = attempt;  // the attempt whose scatter results were verified
         if (slow) {

@@ -1,6 +1,9 @@
 #!/bin/bash
 python -m pytest tests -m gpu -q -x > gpurun_out/pytest.log 2>&1; tail -2 gpurun_out/pytest.log
+show() { python -c "import json,sys; d=json.loads(sys.stdin.read().strip().splitlines()[-1]); r=d['roofline']; print('$1', 'ms/step %.3f kernel_ms %.3f (decode %.3f fold %.3f) frac %.3f slow %s reruns %s' % (d['ms_per_step'], r['kernel_ms'], r.get('decode_kernel_ms',0), r.get('fold_kernel_ms',0), r['frac'], d['config']['slow_tiles'], d['config']['reruns']))" || tail -5 gpurun_out/last.log; }
+run() { name=$1; shift; "$@" > gpurun_out/last.log 2>&1; cat gpurun_out/last.log | show $name; }
 B="python bench.py --steps 5 --warmup 3 --no-e2e --no-cpu-baseline"
-for w in "--workload c5_counts --cpus 64 --events 8 --intervals 400000" "--workload c5_counts --cpus 512 --events 1 --intervals 400000" "--workload c5_counts --cpus 256 --events 32 --intervals 50000" "--workload c5_counts --cpus 64 --events 2 --intervals 1000000" "--workload c5_counts --cpus 256 --events 8 --intervals 100000"; do
-  echo "== $w"; $B $w 2>&1 | tail -1 | python -c "import json,sys; d=json.loads(sys.stdin.read()); r=d['roofline']; print('value %.3e %s ms/step %.3f kernel_ms %.3f achieved %.0f GB/s frac %.3f' % (d['value'], d['unit'], d['ms_per_step'], r['kernel_ms'], r['achieved'], r['frac']), d['config'].get('slow_tiles'), d['config'].get('reruns'))"
-done
+run none $B --agg none
+run hist $B
+run deltas8 $B --workload c3_deltas --events 8
+run deltas32 $B --workload c3_deltas --events 32
