@@ -186,11 +186,14 @@ __device__ __forceinline__ uint32_t hist_hash(uint64_t ip, uint32_t pid) {
 // in L2 (the cursors of the CPUs in flight are a few KB) and one 16-byte store.
 // Neighbouring entries of a list are written close in time, so L2 merges them
 // into full sectors before they reach HBM.
-__device__ __forceinline__ void hist_append(const HistLists& t, uint32_t cpu, uint64_t ip,
-                                            uint32_t pid, uint32_t weight, uint32_t hash) {
+__device__ __forceinline__ uint32_t hist_reserve(const HistLists& t, uint32_t cpu, uint32_t hash,
+                                                 uint32_t& list) {
   const uint32_t b = (uint32_t)(((uint64_t)hash * t.buckets) >> 32);
-  const uint32_t list = cpu * t.buckets + b;
-  const uint32_t pos = atomicAdd(t.cursors + list, 1u);
+  list = cpu * t.buckets + b;
+  return atomicAdd(t.cursors + list, 1u);
+}
+__device__ __forceinline__ void hist_store(const HistLists& t, uint32_t list, uint32_t pos,
+                                           uint64_t ip, uint32_t pid, uint32_t weight) {
   if (pos < t.cap) {
     t.entries[(uint64_t)list * t.cap + pos] =
         make_ulonglong2(ip, (uint64_t)pid | ((uint64_t)weight << 32));
@@ -198,39 +201,68 @@ __device__ __forceinline__ void hist_append(const HistLists& t, uint32_t cpu, ui
     atomicExch(t.overflow, 1u);
   }
 }
+__device__ __forceinline__ void hist_append(const HistLists& t, uint32_t cpu, uint64_t ip,
+                                            uint32_t pid, uint32_t weight, uint32_t hash) {
+  uint32_t list;
+  const uint32_t pos = hist_reserve(t, cpu, hash, list);
+  hist_store(t, list, pos, ip, pid, weight);
+}
 
 // Shared-memory privatised (pid,ip) cache of one segment.  Its job is the heavy
 // hitters: a key that occurs thousands of times in a CPU's window would otherwise
 // append thousands of entries to one list.  Two-way set associative, 16-byte slots
 // {ip, pid | count << 32}; an all-zero slot is empty (a live slot has count >= 1).
 // A slot is claimed AND counted by one 128-bit shared-memory CAS, so there is never
-// a half-written slot to wait for; a sample whose two slots hold other keys is
-// appended to its list directly.  Every sample is counted exactly once.  Flushed
-// to the lists (weighted entries) at segment end.
+// a half-written slot to wait for.  A 32-bit tag per slot (0 = never claimed) is only
+// a filter: most samples are not in the cache, and one 8-byte load of the set's two
+// tags tells them so; a tag match is always confirmed against the full key.  A sample
+// whose set holds other keys is appended to its list directly.  Every sample is
+// counted exactly once.  Flushed to the lists (weighted entries) at segment end.
 constexpr int kCacheSlots = 1024;
 
 struct HistCache {
   ulonglong2 slots[kCacheSlots];
+  uint32_t tags[kCacheSlots];
 };
+
+// Count the sample in the segment cache; false = no room for this key (append it).
+__device__ __forceinline__ bool hist_cache_count(HistCache& c, uint64_t ip, uint32_t pid,
+                                                 uint32_t& hash) {
+  hash = hist_hash(ip, pid);
+  const uint32_t set = (hash ^ (hash >> 16)) & (kCacheSlots - 2);  // slots set, set + 1
+  const uint32_t tag = hash | 1u;
+  const uint64_t tg = *reinterpret_cast<const volatile uint64_t*>(c.tags + set);
+#pragma unroll
+  for (int way = 0; way < 2; ++way) {
+    const uint32_t t = way == 0 ? (uint32_t)tg : (uint32_t)(tg >> 32);
+    const uint32_t i = set + way;
+    if (t == tag) {
+      const volatile ulonglong2* vs = c.slots + i;
+      const uint64_t lo = vs->x, hi = vs->y;
+      if (lo == ip && (uint32_t)hi == pid && (hi >> 32) != 0) {
+        atomicAdd(reinterpret_cast<uint32_t*>(c.slots + i) + 3, 1u);
+        return true;
+      }
+    } else if (t == 0) {
+      uint64_t lo, hi;
+      cas128_shared(smem_u32(c.slots + i), 0, 0, ip, (uint64_t)pid | (1ull << 32), lo, hi);
+      if (lo == 0 && hi == 0) {  // claimed with count 1
+        *reinterpret_cast<volatile uint32_t*>(c.tags + i) = tag;
+        return true;
+      }
+      if (lo == ip && (uint32_t)hi == pid) {  // someone claimed it for the same key just now
+        atomicAdd(reinterpret_cast<uint32_t*>(c.slots + i) + 3, 1u);
+        return true;
+      }
+    }
+  }
+  return false;
+}
 
 __device__ __forceinline__ void hist_count(const HistLists& t, HistCache& c, uint32_t cpu,
                                            uint64_t ip, uint32_t pid) {
-  const uint32_t hash = hist_hash(ip, pid);
-  uint32_t i = (hash ^ (hash >> 16)) & (kCacheSlots - 2);  // 2-way: slots i, i + 1
-#pragma unroll
-  for (int way = 0; way < 2; ++way, ++i) {
-    const volatile ulonglong2* vs = c.slots + i;
-    uint64_t lo = vs->x, hi = vs->y;
-    if (lo == 0 && hi == 0) {
-      cas128_shared(smem_u32(c.slots + i), 0, 0, ip, (uint64_t)pid | (1ull << 32), lo, hi);
-      if (lo == 0 && hi == 0) return;  // claimed with count 1
-    }
-    if (lo == ip && (uint32_t)hi == pid && (hi >> 32) != 0) {
-      atomicAdd(reinterpret_cast<uint32_t*>(c.slots + i) + 3, 1u);
-      return;
-    }
-  }
-  hist_append(t, cpu, ip, pid, 1, hash);
+  uint32_t hash;
+  if (!hist_cache_count(c, ip, pid, hash)) hist_append(t, cpu, ip, pid, 1, hash);
 }
 
 // ---------------------------------------------------------------------------
@@ -444,7 +476,10 @@ __global__ void __launch_bounds__(kThreads, kThreads == 256 ? (kTile <= 16384 ? 
   }
   sm.expect[tid] = kNoRel;
   if (AGG == HBT_AGG_IP_HISTOGRAM) {
-    for (int i = tid; i < kCacheSlots; i += kThreads) cache.slots[i] = make_ulonglong2(0, 0);
+    for (int i = tid; i < kCacheSlots; i += kThreads) {
+      cache.slots[i] = make_ulonglong2(0, 0);
+      cache.tags[i] = 0;
+    }
   }
   __syncthreads();
 
@@ -555,10 +590,30 @@ __global__ void __launch_bounds__(kThreads, kThreads == 256 ? (kTile <= 16384 ? 
         my_rec += (n_t > tid) ? (n_t - tid + kThreads - 1) / kThreads : 0u;
         my_sample += my_n;
         if (AGG == HBT_AGG_IP_HISTOGRAM) {
-          for (uint32_t k = tid; k < n_t; k += kThreads) {
-            const uint32_t pos = erel + k * S;
-            if (hdr_type(tv.at(pos)) == REC_SAMPLE && h_sample)
-              hist_count(p.hist, cache, seg.cpu, tv.at(pos + 8), (uint32_t)tv.at(pos + 16));
+          for (uint32_t k = tid; k < n_t; k += 2 * kThreads) {
+            // two samples per thread per pass: their list appends (an atomic that has to
+            // return before the store can be placed) overlap
+            const uint32_t p0 = erel + k * S, p1 = p0 + kThreads * S;
+            const bool s0 = hdr_type(tv.at(p0)) == REC_SAMPLE && h_sample;
+            const bool s1 = k + kThreads < n_t && hdr_type(tv.at(p1)) == REC_SAMPLE && h_sample;
+            uint64_t ip0 = 0, ip1 = 0;
+            uint32_t pid0 = 0, pid1 = 0, hs0 = 0, hs1 = 0;
+            bool m0 = false, m1 = false;  // cache miss: append
+            if (s0) {
+              ip0 = tv.at(p0 + 8);
+              pid0 = (uint32_t)tv.at(p0 + 16);
+              m0 = !hist_cache_count(cache, ip0, pid0, hs0);
+            }
+            if (s1) {
+              ip1 = tv.at(p1 + 8);
+              pid1 = (uint32_t)tv.at(p1 + 16);
+              m1 = !hist_cache_count(cache, ip1, pid1, hs1);
+            }
+            uint32_t l0 = 0, l1 = 0, q0 = 0, q1 = 0;
+            if (m0) q0 = hist_reserve(p.hist, seg.cpu, hs0, l0);
+            if (m1) q1 = hist_reserve(p.hist, seg.cpu, hs1, l1);
+            if (m0) hist_store(p.hist, l0, q0, ip0, pid0, 1);
+            if (m1) hist_store(p.hist, l1, q1, ip1, pid1, 1);
           }
         }
         uint32_t rows_tile = 0;
@@ -569,10 +624,11 @@ __global__ void __launch_bounds__(kThreads, kThreads == 256 ? (kTile <= 16384 ? 
           const uint32_t first_row = ik == EV_SAMPLE ? 1u : 0u;
           rows_tile = n_t - 1 + first_row;
           const uint32_t wpr = 2 + d.n_events;
-          const float inv = __frcp_rn((float)wpr);
           uint64_t* out = seg.rows + (1 + n_rows_in) * (uint64_t)wpr;
-          const uint32_t total = rows_tile * wpr;
           const uint64_t far_prev = ev_pos(in_ev);
+          // consecutive threads write consecutive u64s of the tile's rows
+          const float inv = __frcp_rn((float)wpr);
+          const uint32_t total = rows_tile * wpr;
           for (uint32_t f = tid; f < total; f += kThreads) {
             uint32_t r = (uint32_t)((float)f * inv);
             if (r * wpr > f) --r;
@@ -580,7 +636,7 @@ __global__ void __launch_bounds__(kThreads, kThreads == 256 ? (kTile <= 16384 ? 
             const uint32_t w = f - r * wpr;
             const uint32_t k = r + 1 - first_row;  // the record that closes row r
             const uint32_t cpos = erel + k * S;
-            const uint32_t off = w < 2 ? 8u : 40u + 8u * (w - 2);
+            const uint32_t off = w < 2 ? 8u : 40u + 8u * (w - 2);  // tstamp, or value[w-2]
             const uint64_t cur = tv.at(cpos + off);
             const uint64_t prv = k > 0 ? tv.at(cpos - S + off) : ring_word_g(ring, far_prev + off);
             uint64_t v;
@@ -1206,19 +1262,29 @@ __global__ void __launch_bounds__(64)
 // decode appended -- into distinct keys with a shared-memory hash table, writes
 // them back to the front of the same list and sets the cursor to their number.
 // cap <= kAggSlots / 2, so the table can never fill up.
-constexpr uint32_t kAggSlots = 4096;   // 64 KiB of 16-byte slots
+#ifndef HBT_AGG_SLOTS
+#define HBT_AGG_SLOTS 4096
+#endif
+constexpr uint32_t kAggSlots = HBT_AGG_SLOTS;   // 16-byte slots of the fold's shared-memory table
 constexpr int kAggThreads = 256;
 constexpr int kAggBatch = 4;           // independent loads in flight per thread
 
-__global__ void __launch_bounds__(kAggThreads) k_hist_aggregate(const HistLists t, uint32_t n_lists) {
+// Lists with n_lo < n <= n_hi entries are folded by this launch: the host runs a
+// first pass with a small table (most lists, high occupancy) and a second one with
+// the full-size table for the few long lists.
+__global__ void __launch_bounds__(kAggThreads)
+    k_hist_aggregate(const HistLists t, uint32_t n_lists, uint32_t n_lo, uint32_t n_hi) {
   extern __shared__ __align__(16) uint8_t agg_smem[];
   ulonglong2* slots = reinterpret_cast<ulonglong2*>(agg_smem);
   __shared__ uint32_t s_out;
   const uint32_t tid = threadIdx.x, lane = tid & 31;
   const uint32_t s0 = smem_u32(slots);
+  uint32_t n_next = blockIdx.x < n_lists ? t.cursors[blockIdx.x] : 0;
   for (uint32_t list = blockIdx.x; list < n_lists; list += gridDim.x) {
-    const uint32_t n = min(t.cursors[list], t.cap);
-    if (n <= 1) continue;  // nothing to fold (n is uniform over the CTA)
+    const uint32_t n = min(n_next, t.cap);
+    // the next list's length is fetched while this one is folded
+    n_next = list + gridDim.x < n_lists ? t.cursors[list + gridDim.x] : 0;
+    if (n <= n_lo || n > n_hi) continue;  // not this pass (n is uniform over the CTA)
     // table size: power of two >= 1.5 n (load <= 2/3; n <= cap = kAggSlots / 2)
     uint32_t T = 64;
     while (2 * T < 3 * n) T <<= 1;

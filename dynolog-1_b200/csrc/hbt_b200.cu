@@ -405,19 +405,29 @@ HistLists hist_view(hbt_ctx* ctx) {
 // Fold the raw samples the last decode appended into distinct keys (k_hist_aggregate).
 int hist_fold(hbt_ctx* ctx) {
   if (!ctx->hist_pending_fold) return 0;
-  const size_t smem = (size_t)kAggSlots * sizeof(ulonglong2);
+  const size_t smem_full = (size_t)kAggSlots * sizeof(ulonglong2);
   if (!ctx->agg_attr_set) {
-    CU(cudaFuncSetAttribute(k_hist_aggregate, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    CU(cudaFuncSetAttribute(k_hist_aggregate, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                            (int)smem_full));
     ctx->agg_attr_set = true;
   }
   const uint32_t n = (uint32_t)hist_lists(ctx);
-  uint32_t grid = (uint32_t)ctx->sm_count * 3 * 8;
+  // pass 1: lists that fit a quarter-size table (table = pow2 >= 1.5 n): 7 CTAs per SM
+  const uint32_t small_slots = kAggSlots / 4;
+  const uint32_t small_n = small_slots * 2 / 3;
+  uint32_t grid = (uint32_t)ctx->sm_count * 7 * 4;
   if (grid > n) grid = n;
   CU(cudaEventRecord(ctx->ev_f0, ctx->stream));
-  k_hist_aggregate<<<grid, kAggThreads, smem, ctx->stream>>>(hist_view(ctx), n);
+  k_hist_aggregate<<<grid, kAggThreads, small_slots * sizeof(ulonglong2), ctx->stream>>>(
+      hist_view(ctx), n, 1, small_n);
+  // pass 2: the long lists, full-size table
+  grid = (uint32_t)ctx->sm_count * 3 * 4;
+  if (grid > n) grid = n;
+  k_hist_aggregate<<<grid, kAggThreads, smem_full, ctx->stream>>>(hist_view(ctx), n, small_n,
+                                                                 0xFFFFFFFFu);
   CU(cudaEventRecord(ctx->ev_f1, ctx->stream));
   ctx->fold_timed = true;
-  ++ctx->launches;
+  ctx->launches += 2;
   CU(cudaGetLastError());
   ctx->hist_pending_fold = false;
   return 0;
