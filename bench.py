@@ -151,6 +151,26 @@ def make_group_rings(n_cpus: int, ring_bytes: int, cpu_base: int, device, n_even
     return imgs, tails, heads, total
 
 
+def make_mixed_rings(n_cpus: int, ring_bytes: int, cpu_base: int, device, n_events: int):
+    """Rings of the mixed stream of config 4 (SAMPLE 70 % / SWITCH_CPU_WIDE 15 % / COMM / MMAP /
+    LOST / FORK / EXIT, 24-320 B records)."""
+    imgs = torch.empty((n_cpus, ring_bytes // 8), dtype=torch.int64, device=device)
+    tails, heads = [], []
+    avg = 0.70 * (40 + 8 * n_events) + 0.15 * 32 + 0.05 * 44 + 0.05 * 188 + 0.001 * 40 + 0.049 * 48
+    n = int((ring_bytes - (1 << 20)) / (avg * 1.02))
+    for c in range(n_cpus):
+        seed = tg.stream_seed(4, cpu_base + c)
+        s = tg.mixed_stream(seed, n, n_events, device=device)
+        assert s.numel() * 8 <= ring_bytes - 4096, "mixed stream does not fit the ring"
+        tail = tg.random_tail(seed, ring_bytes)
+        ring, head = tg.place_in_ring(s, ring_bytes, tail, fill_seed=seed ^ 0xABCDEF)
+        imgs[c] = ring
+        tails.append(tail)
+        heads.append(head)
+        del s, ring
+    return imgs, tails, heads, n * n_cpus
+
+
 def timed_steps(step, steps, dist, dev):
     """CUDA-event timing of `steps` calls of step(), barrier + sync on both sides, max over ranks."""
     if dist is not None:
@@ -175,12 +195,16 @@ def bench_deltas(args, rank, world, local, dev, dist):
     """Diagnostic workload (config 3 shape): group SAMPLE decode + per-interval deltas."""
     E = args.events
     ring_bytes = args.ring_mib << 20
-    imgs, tails, heads, n_rec = make_group_rings(args.cpus, ring_bytes, rank * args.cpus, dev, E)
+    mixed = args.workload == "c4_mixed"
+    if mixed:
+        imgs, tails, heads, n_rec = make_mixed_rings(args.cpus, ring_bytes, rank * args.cpus, dev, E)
+    else:
+        imgs, tails, heads, n_rec = make_group_rings(args.cpus, ring_bytes, rank * args.cpus, dev, E)
     window_bytes = sum(h - t for t, h in zip(tails, heads))
     ctx = hbt.Context(local, max_cpus=args.cpus)
     ctx.use_torch_stream()
     ctx.ring_configure(args.cpus, 0)
-    desc = hbt.sampling_desc(E)
+    desc = hbt.sampling_desc(E, handled=hbt.MODE_MIXED if mixed else hbt.MODE_SAMPLING)
     bases_a = np.array([imgs[c].data_ptr() for c in range(args.cpus)], dtype=np.uint64)
     tails_a, heads_a = np.array(tails, dtype=np.uint64), np.array(heads, dtype=np.uint64)
     kms = []
@@ -217,7 +241,9 @@ def bench_deltas(args, rank, world, local, dev, dist):
             "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms_step,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u64",
             "data": "synthetic",
-            "config": {"workload": f"c3_deltas: group SAMPLE ({40 + 8 * E} B, {E} events) decode + per-interval deltas",
+            "config": {"workload": (f"c4_mixed: SAMPLE/SWITCH/COMM/MMAP/LOST/FORK/EXIT stream, per-type counters "
+                                    f"+ per-interval deltas ({E} events)") if mixed else
+                                   f"c3_deltas: group SAMPLE ({40 + 8 * E} B, {E} events) decode + per-interval deltas",
                        "cpus_per_gpu": args.cpus, "ring_mib": args.ring_mib, "records_per_gpu": n_rec,
                        "rows_per_gpu": n_rows, "window_bytes_per_gpu": int(window_bytes),
                        "l2": "inputs exceed L2; no flush needed", "slow_tiles": ctx.slow_tiles,
@@ -374,11 +400,11 @@ def main():
     ap.add_argument("--cpus", type=int, default=256)
     ap.add_argument("--ring-mib", type=int, default=16)
     ap.add_argument("--ref-cpus", type=int, default=32, help="rings in the bounded CPU sample")
-    ap.add_argument("--hist-slots-per-cpu", type=int, default=1 << 20,
+    ap.add_argument("--hist-slots-per-cpu", type=int, default=1 << 21,
                     help="list capacity per CPU: distinct keys + the samples of one decode")
     ap.add_argument("--agg", default="hist", choices=["hist", "none"],
                     help="none: decode + counters only (diagnostic, not the headline workload)")
-    ap.add_argument("--workload", default="c2_ip_hist", choices=["c2_ip_hist", "c3_deltas", "c5_counts"],
+    ap.add_argument("--workload", default="c2_ip_hist", choices=["c2_ip_hist", "c3_deltas", "c4_mixed", "c5_counts"],
                     help="c2_ip_hist is the headline (BASELINE configs[1]); the others are diagnostics")
     ap.add_argument("--events", type=int, default=8)
     ap.add_argument("--intervals", type=int, default=100000)
@@ -407,7 +433,7 @@ def main():
         dist.init_process_group("nccl", device_id=dev)
 
     if args.workload != "c2_ip_hist":
-        fn = bench_deltas if args.workload == "c3_deltas" else bench_counts
+        fn = bench_counts if args.workload == "c5_counts" else bench_deltas
         line = fn(args, rank, world, local, dev, dist)
         if rank == 0:
             print(json.dumps(line))

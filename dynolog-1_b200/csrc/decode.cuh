@@ -1263,7 +1263,7 @@ __global__ void __launch_bounds__(64)
 // them back to the front of the same list and sets the cursor to their number.
 // cap <= kAggSlots / 2, so the table can never fill up.
 #ifndef HBT_AGG_SLOTS
-#define HBT_AGG_SLOTS 4096
+#define HBT_AGG_SLOTS 8192
 #endif
 constexpr uint32_t kAggSlots = HBT_AGG_SLOTS;   // 16-byte slots of the fold's shared-memory table
 constexpr int kAggThreads = 256;

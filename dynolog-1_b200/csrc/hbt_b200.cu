@@ -412,22 +412,24 @@ int hist_fold(hbt_ctx* ctx) {
     ctx->agg_attr_set = true;
   }
   const uint32_t n = (uint32_t)hist_lists(ctx);
-  // pass 1: lists that fit a quarter-size table (table = pow2 >= 1.5 n): 7 CTAs per SM
-  const uint32_t small_slots = kAggSlots / 4;
-  const uint32_t small_n = small_slots * 2 / 3;
-  uint32_t grid = (uint32_t)ctx->sm_count * 7 * 4;
-  if (grid > n) grid = n;
+  // Lists are folded by size class, smallest table first: most lists are short and
+  // a small table lets many CTAs share an SM; the few long ones (a warm key repeats in
+  // its list) get the full-size table.  A table is a power of two >= 1.5 n slots.
   CU(cudaEventRecord(ctx->ev_f0, ctx->stream));
-  k_hist_aggregate<<<grid, kAggThreads, small_slots * sizeof(ulonglong2), ctx->stream>>>(
-      hist_view(ctx), n, 1, small_n);
-  // pass 2: the long lists, full-size table
-  grid = (uint32_t)ctx->sm_count * 3 * 4;
-  if (grid > n) grid = n;
-  k_hist_aggregate<<<grid, kAggThreads, smem_full, ctx->stream>>>(hist_view(ctx), n, small_n,
-                                                                 0xFFFFFFFFu);
+  uint32_t lo = 1;
+  for (uint32_t slots = kAggSlots / 8; slots <= kAggSlots; slots *= 2) {
+    const uint32_t hi = slots == kAggSlots ? 0xFFFFFFFFu : slots * 2 / 3;
+    const size_t smem = (size_t)slots * sizeof(ulonglong2);
+    uint32_t per_sm = (uint32_t)((220 * 1024) / (smem + 1024));
+    if (per_sm > 8) per_sm = 8;
+    uint32_t grid = (uint32_t)ctx->sm_count * per_sm * 4;
+    if (grid > n) grid = n;
+    k_hist_aggregate<<<grid, kAggThreads, smem, ctx->stream>>>(hist_view(ctx), n, lo, hi);
+    ++ctx->launches;
+    lo = hi;
+  }
   CU(cudaEventRecord(ctx->ev_f1, ctx->stream));
   ctx->fold_timed = true;
-  ctx->launches += 2;
   CU(cudaGetLastError());
   ctx->hist_pending_fold = false;
   return 0;

@@ -272,8 +272,10 @@ int hbt_fetch_carry(hbt_ctx* ctx, uint32_t cpu, uint64_t* last, uint32_t n_event
  * list to distinct keys in shared memory, in place.  capacity_slots is the total
  * number of entries the lists can hold, split evenly between the configured CPUs;
  * per CPU it must cover the distinct keys accumulated so far PLUS the samples of
- * one decode.  A decode that overflows a list makes hbt_fetch_results return
- * -ENOSPC.  Counts are 32-bit and accumulate until hbt_hist_clear; hbt_decode
+ * one decode, with headroom: lists hold 4096 entries and a key that repeats a few
+ * hundred times within one decode fills its own list, so size for an average fill
+ * of a quarter or less (capacity >= 4 x (distinct + samples per decode)).  A decode
+ * that overflows a list makes hbt_fetch_results return -ENOSPC.  Counts are 32-bit and accumulate until hbt_hist_clear; hbt_decode
  * returns -EOVERFLOW rather than let more than 2^32-1 samples accumulate.
  * hbt_hist_clear only resets the list cursors. */
 int hbt_hist_configure(hbt_ctx* ctx, uint64_t capacity_slots);
