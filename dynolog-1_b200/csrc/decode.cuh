@@ -1279,12 +1279,31 @@ __global__ void __launch_bounds__(kAggThreads)
   __shared__ uint32_t s_out;
   const uint32_t tid = threadIdx.x, lane = tid & 31;
   const uint32_t s0 = smem_u32(slots);
-  uint32_t n_next = blockIdx.x < n_lists ? t.cursors[blockIdx.x] : 0;
-  for (uint32_t list = blockIdx.x; list < n_lists; list += gridDim.x) {
-    const uint32_t n = min(n_next, t.cap);
-    // the next list's length is fetched while this one is folded
-    n_next = list + gridDim.x < n_lists ? t.cursors[list + gridDim.x] : 0;
-    if (n <= n_lo || n > n_hi) continue;  // not this pass (n is uniform over the CTA)
+  // This CTA owns a contiguous range of lists.  Their lengths are read 256 at a time
+  // (coalesced) and the lists of this pass' size class are queued in shared memory,
+  // so that skipping the others costs no dependent loads.
+  __shared__ uint32_t s_q[kAggThreads], s_qlen[kAggThreads];
+  __shared__ uint32_t s_qn;
+  const uint32_t per_cta = (n_lists + gridDim.x - 1) / gridDim.x;
+  const uint32_t l_begin = blockIdx.x * per_cta;
+  const uint32_t l_end = min(n_lists, l_begin + per_cta);
+  for (uint32_t l0 = l_begin; l0 < l_end; l0 += kAggThreads) {
+    if (tid == 0) s_qn = 0;
+    __syncthreads();
+    {
+      const uint32_t l = l0 + tid;
+      const uint32_t len = l < l_end ? min(t.cursors[l], t.cap) : 0;
+      if (len > n_lo && len <= n_hi) {
+        const uint32_t q = atomicAdd(&s_qn, 1u);
+        s_q[q] = l;
+        s_qlen[q] = len;
+      }
+    }
+    __syncthreads();
+    const uint32_t qn = s_qn;
+  for (uint32_t qi = 0; qi < qn; ++qi) {
+    const uint32_t list = s_q[qi];
+    const uint32_t n = s_qlen[qi];
     // table size: power of two >= 1.5 n (load <= 2/3; n <= cap = kAggSlots / 2)
     uint32_t T = 64;
     while (2 * T < 3 * n) T <<= 1;
@@ -1332,6 +1351,7 @@ __global__ void __launch_bounds__(kAggThreads)
     __syncthreads();
     if (tid == 0) t.cursors[list] = s_out;
     __syncthreads();
+  }
   }
 }
 
