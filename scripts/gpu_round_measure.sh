@@ -9,5 +9,5 @@ for w in "c3_deltas --events 8" "c3_deltas --events 32" "c4_mixed --events 8" "c
 done
 CMD="python bench.py --steps 2 --warmup 3 --no-e2e --no-cpu-baseline"
 $CMD > gpurun_out/plain.log 2>&1 && ncu --metrics gpu__time_duration.sum --clock-control none -k regex:"k_decode|k_finalize|k_hist|k_seed|k_locate|k_counts|k_scaled" -c 400 --csv --log-file gpurun_out/launches.csv $CMD > gpurun_out/ncu_launches.log 2>&1
-$CMD > gpurun_out/plain.log 2>&1 && ncu --set full --clock-control none --import-source on -k regex:"k_decode|k_hist_aggregate" -s 9 -c 3 -o gpurun_out/prof_r1_top $CMD > gpurun_out/ncu_full.log 2>&1
+$CMD > gpurun_out/plain.log 2>&1 && ncu --set full --clock-control none --import-source on -k regex:"k_decode|k_hist_aggregate" -s 15 -c 5 -o gpurun_out/prof_r1_top $CMD > gpurun_out/ncu_full.log 2>&1
 tail -2 gpurun_out/ncu_full.log
