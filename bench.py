@@ -409,6 +409,8 @@ def main():
     ap.add_argument("--events", type=int, default=8)
     ap.add_argument("--intervals", type=int, default=100000)
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--e2e-groups", type=int, default=8,
+                    help="CPU groups (contexts) the end-to-end leg pipelines over PCIe")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
 
@@ -522,23 +524,59 @@ def main():
         host = torch.empty((args.cpus, ring_bytes // 8), dtype=torch.int64).pin_memory()
         host.copy_(imgs)
         host_np = host.numpy()
-        ctx.ring_configure(args.cpus, ring_bytes)
-        ctx.hist_configure(args.hist_slots_per_cpu * args.cpus)
+        ctx.close()
+        del imgs
+        torch.cuda.empty_cache()
+        # The CPUs are handled in G groups, one hbt_ctx (own stream) each — the reference's
+        # "one generator set per collecting thread" — so the H2D of group g+1 overlaps the
+        # decode, fold and D2H of group g (PCIe is full duplex; the copies dominate).
+        G = max(1, min(args.e2e_groups, args.cpus))
+        per = (args.cpus + G - 1) // G
+        groups = []
         ent_dt = hbt.HIST_DTYPE.itemsize
-        # result buffer in pinned host memory (a pageable destination makes the D2H
-        # copy of ~1 GB of entries the slowest part of the step)
-        ent_pinned = torch.empty(int(distinct * 1.05) * ent_dt + 4096, dtype=torch.uint8).pin_memory()
-        ent_buf = ent_pinned.numpy()[: int(distinct * 1.05) * ent_dt].view(hbt.HIST_DTYPE)
+        for g in range(G):
+            lo, hi = g * per, min(args.cpus, (g + 1) * per)
+            if lo >= hi:
+                break
+            cg = hbt.Context(local, max_cpus=hi - lo)
+            sg = torch.cuda.Stream(dev)
+            cg.set_stream(sg.cuda_stream)
+            cg.ring_configure(hi - lo, ring_bytes)
+            cg.set_cpu_base(cpu_base + lo)
+            cg.hist_configure(args.hist_slots_per_cpu * (hi - lo))
+            # result buffer in pinned host memory (a pageable destination makes the D2H
+            # copy of ~1 GB of entries the slowest part of the step)
+            cap = int(distinct * 1.25 * (hi - lo) / args.cpus) + 4096
+            pinned = torch.empty(cap * ent_dt, dtype=torch.uint8).pin_memory()
+            groups.append((cg, lo, hi, pinned.numpy().view(hbt.HIST_DTYPE), (pinned, sg)))
 
         def e2e_step():
-            ctx.hist_clear()
-            ctx.reset_state(hbt.INVALID_TS)
-            for c in range(args.cpus):
-                ctx.submit_ring_image(c, host_np[c], tails[c], heads[c])
-            ctx.decode(desc)
-            r = ctx.fetch_results()
-            ent = ctx.hist_fetch(out=ent_buf)
-            return r, ent
+            uploaded = None
+            for cg, lo, hi, _, (_, sg) in groups:
+                cg.hist_clear()
+                cg.reset_state(hbt.INVALID_TS)
+                # uploads of different streams would otherwise share the link round-robin and
+                # all finish together: chain them so group g is complete before g+1 starts
+                # (decode() itself issues no copy-engine work, so nothing of group g queues
+                # behind the next group's upload)
+                if uploaded is not None:
+                    sg.wait_event(uploaded)
+                for c in range(lo, hi):
+                    cg.submit_ring_image(c - lo, host_np[c], tails[c], heads[c])
+                uploaded = torch.cuda.Event()
+                uploaded.record(sg)
+                cg.decode(desc)
+            rs, n_ent = [], 0
+            trace = [time.perf_counter()]
+            for cg, lo, hi, buf, _ in groups:
+                rs.append(cg.fetch_results())
+                trace.append(time.perf_counter())
+                n_ent += len(cg.hist_fetch(out=buf))
+                trace.append(time.perf_counter())
+            if os.environ.get("HBT_BENCH_TRACE"):
+                print("e2e trace (ms since issue):",
+                      " ".join(f"{(x - trace[0]) * 1e3:.1f}" for x in trace[1:]), file=sys.stderr)
+            return np.concatenate(rs), n_ent
 
         e2e_step()
         if dist is not None:
@@ -546,7 +584,7 @@ def main():
         torch.cuda.synchronize()
         t0 = time.perf_counter()
         for _ in range(max(1, min(args.steps, 3))):
-            r, ent = e2e_step()
+            r, n_ent = e2e_step()
         torch.cuda.synchronize()
         dt = (time.perf_counter() - t0) / max(1, min(args.steps, 3))
         tt = torch.tensor([dt], dtype=torch.float64, device=dev)
@@ -554,8 +592,13 @@ def main():
             dist.all_reduce(tt, op=dist.ReduceOp.MAX)
         dt = float(tt.item())
         assert int(r["n_records"].sum()) == n_rec
+        assert n_ent == distinct, (n_ent, distinct)
         e2e = {"value": n_rec * world / dt, "unit": UNIT, "h2d_bytes_per_step": int(window_bytes),
-               "d2h_bytes_per_step": int(len(ent) * ent_dt + r.nbytes), "ms_per_step": dt * 1e3}
+               "d2h_bytes_per_step": int(n_ent * ent_dt + r.nbytes), "ms_per_step": dt * 1e3,
+               "pipeline": f"{len(groups)} CPU groups, one hbt_ctx + stream each: H2D of group g+1 "
+                           "overlaps decode + fold + D2H of group g"}
+        for cg, *_ in groups:
+            cg.close()
 
     if rank != 0:
         if dist is not None:

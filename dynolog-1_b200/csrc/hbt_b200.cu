@@ -310,12 +310,31 @@ int build_tables(hbt_ctx* ctx, const uint64_t* clamp_head, const int64_t* clamp_
   CU(ctx->d_forced.reserve(ns));
   CU(ctx->h_seam.reserve(ns));
   if (!segs.empty()) memcpy(ctx->h_segs.p, segs.data(), segs.size() * sizeof(SegDesc));
-  CU(cudaMemcpyAsync(ctx->d_rings.p, ctx->h_rings.p, C * sizeof(RingDesc),
-                     cudaMemcpyHostToDevice, ctx->stream));
-  if (!segs.empty())
-    CU(cudaMemcpyAsync(ctx->d_segs.p, ctx->h_segs.p, segs.size() * sizeof(SegDesc),
-                       cudaMemcpyHostToDevice, ctx->stream));
-  return 0;
+  return 0;  // k_prepare (run_once) moves the tables to the device
+}
+
+// Everything a decode needs set up on the device, in one launch and without the copy
+// engines (a context's small table uploads must not queue behind another context's ring
+// uploads): tables are read straight from the pinned host staging buffers, scratch words
+// are reset, and the histogram cursors are snapshotted for a possible re-run.
+struct PrepareParams {
+  const uint64_t* src_rings; uint64_t* dst_rings; uint32_t n_ring_words;
+  const uint64_t* src_segs;  uint64_t* dst_segs;  uint32_t n_seg_words;
+  uint32_t* flags;
+  uint64_t* clamp_head; uint32_t n_cpus;
+  uint64_t* forced; uint32_t n_forced;
+  const uint32_t* cursors; uint32_t* cursors_snap; uint32_t n_lists;  // n_lists = 0: no snapshot
+};
+
+static __global__ void k_prepare(PrepareParams p) {
+  const uint32_t stride = gridDim.x * blockDim.x;
+  const uint32_t t0 = blockIdx.x * blockDim.x + threadIdx.x;
+  for (uint32_t i = t0; i < p.n_seg_words; i += stride) p.dst_segs[i] = p.src_segs[i];
+  for (uint32_t i = t0; i < p.n_ring_words; i += stride) p.dst_rings[i] = p.src_rings[i];
+  for (uint32_t i = t0; i < p.n_cpus; i += stride) p.clamp_head[i] = ~0ull;
+  for (uint32_t i = t0; i < p.n_forced; i += stride) p.forced[i] = ~0ull;
+  for (uint32_t i = t0; i < p.n_lists; i += stride) p.cursors_snap[i] = p.cursors[i];
+  if (t0 < 4) p.flags[t0] = 0;
 }
 
 template <int AGG>
@@ -385,11 +404,35 @@ int launch_finalize(hbt_ctx* ctx) {
 }
 
 // Launch decode + finalize for the tables currently uploaded.
-int run_once(hbt_ctx* ctx) {
-  CU(cudaMemsetAsync(ctx->d_flags.p, 0, 4 * sizeof(uint32_t), ctx->stream));
-  CU(cudaMemsetAsync(ctx->d_clamp_head.p, 0xFF, ctx->n_cpus * sizeof(uint64_t), ctx->stream));
-  CU(cudaMemsetAsync(ctx->d_forced.p, 0xFF, (ctx->n_segs ? ctx->n_segs : 1) * sizeof(uint64_t),
-                     ctx->stream));
+int run_once(hbt_ctx* ctx, bool snapshot_cursors) {
+  static_assert(sizeof(RingDesc) % 8 == 0 && sizeof(SegDesc) % 8 == 0, "tables move as u64 words");
+  PrepareParams pp{};
+  void* dp = nullptr;
+  CU(cudaHostGetDevicePointer(&dp, ctx->h_rings.p, 0));
+  pp.src_rings = static_cast<const uint64_t*>(dp);
+  pp.dst_rings = reinterpret_cast<uint64_t*>(ctx->d_rings.p);
+  pp.n_ring_words = ctx->n_cpus * (uint32_t)(sizeof(RingDesc) / 8);
+  CU(cudaHostGetDevicePointer(&dp, ctx->h_segs.p, 0));
+  pp.src_segs = static_cast<const uint64_t*>(dp);
+  pp.dst_segs = reinterpret_cast<uint64_t*>(ctx->d_segs.p);
+  pp.n_seg_words = ctx->n_segs * (uint32_t)(sizeof(SegDesc) / 8);
+  pp.flags = ctx->d_flags.p;
+  pp.clamp_head = ctx->d_clamp_head.p;
+  pp.n_cpus = ctx->n_cpus;
+  pp.forced = ctx->d_forced.p;
+  pp.n_forced = ctx->n_segs ? ctx->n_segs : 1;
+  if (snapshot_cursors) {
+    pp.cursors = ctx->hist_cursors.p;
+    pp.cursors_snap = ctx->hist_cursors_snap.p;
+    pp.n_lists = (uint32_t)((size_t)ctx->n_cpus * ctx->hist_buckets);
+  }
+  const uint32_t work = pp.n_seg_words > pp.n_lists ? pp.n_seg_words : pp.n_lists;
+  uint32_t grid = (work + 1023) / 1024;
+  if (grid < 1) grid = 1;
+  if (grid > (uint32_t)ctx->sm_count * 2) grid = (uint32_t)ctx->sm_count * 2;
+  k_prepare<<<grid, 256, 0, ctx->stream>>>(pp);
+  ++ctx->launches;
+  CU(cudaGetLastError());
   int rc = launch_decode(ctx);
   if (rc) return rc;
   return launch_finalize(ctx);
@@ -573,7 +616,7 @@ static int configure_common(hbt_ctx* ctx, uint32_t n_cpus) {
   CU(ctx->h_clamp_head.reserve(n_cpus));
   CU(ctx->h_clamp_ret.reserve(n_cpus));
   CU(ctx->d_flags.reserve(4));
-  CU(ctx->h_flags.reserve(4));
+  CU(ctx->h_flags.reserve(8));
   ctx->cur = 0;
   return hbt_ring_reset_state(ctx, kInvalidTs);
 }
@@ -674,13 +717,11 @@ int hbt_decode(hbt_ctx* ctx, const hbt_decode_desc* desc) {
     if (ctx->hist_samples + bound > 0xFFFFFFFFull)
       return fail(ctx, -EOVERFLOW, "more than 2^32-1 samples since hbt_hist_clear");
     ctx->hist_samples += bound;
-    // the lists as they are now: a re-run starts again from here
-    CU(cudaMemcpyAsync(ctx->hist_cursors_snap.p, ctx->hist_cursors.p,
-                       hist_lists(ctx) * sizeof(uint32_t), cudaMemcpyDeviceToDevice, ctx->stream));
   }
   rc = build_tables(ctx, nullptr, nullptr, nullptr);
   if (rc) return rc;
-  rc = run_once(ctx);
+  // histogram: k_prepare also snapshots the lists' cursors, a re-run starts again from there
+  rc = run_once(ctx, ctx->desc.aggregate == HBT_AGG_IP_HISTOGRAM);
   if (rc) return rc;
   ctx->pending = true;
   ctx->have_results = false;
@@ -735,7 +776,7 @@ static int complete_decode(hbt_ctx* ctx) {
     }
     int rc = build_tables(ctx, have_clamp ? clamp_head.data() : nullptr, clamp_ret.data(), &forced);
     if (rc) return rc;
-    rc = run_once(ctx);
+    rc = run_once(ctx, false);
     if (rc) return rc;
   }
   // success: fold the appended samples, commit the generator state, fetch results
@@ -744,6 +785,10 @@ static int complete_decode(hbt_ctx* ctx) {
     if (int rc = hist_fold(ctx)) return rc;
   }
   ctx->cur ^= 1;
+  ctx->h_flags.p[4] = 0;
+  if (ctx->desc.aggregate == HBT_AGG_IP_HISTOGRAM)
+    CU(cudaMemcpyAsync(ctx->h_flags.p + 4, ctx->hist_overflow.p, sizeof(uint32_t),
+                       cudaMemcpyDeviceToHost, ctx->stream));
   CU(cudaMemcpyAsync(ctx->h_out.p, ctx->d_out.p, C * sizeof(hbt_cpu_result),
                      cudaMemcpyDeviceToHost, ctx->stream));
   if (ctx->n_segs) {
@@ -772,11 +817,10 @@ int hbt_fetch_results(hbt_ctx* ctx, hbt_cpu_result* out, uint32_t cap) {
   if (!ctx->have_results) return fail(ctx, -EINVAL, "no decode to fetch");
   if (cap < ctx->n_cpus) return fail(ctx, -ENOSPC, "cap %u < n_cpus %u", cap, ctx->n_cpus);
   memcpy(out, ctx->h_out.p, ctx->n_cpus * sizeof(hbt_cpu_result));
-  if (ctx->desc.aggregate == HBT_AGG_IP_HISTOGRAM) {
-    uint32_t ov = 0;
-    CU(cudaMemcpy(&ov, ctx->hist_overflow.p, sizeof(ov), cudaMemcpyDeviceToHost));
-    if (ov) return fail(ctx, -ENOSPC, "a histogram list is full: hbt_hist_configure more capacity");
-  }
+  // the overflow flag travelled with the results (everything stays on the context's stream:
+  // a copy on the legacy stream would queue behind other contexts' uploads)
+  if (ctx->desc.aggregate == HBT_AGG_IP_HISTOGRAM && ctx->h_flags.p[4])
+    return fail(ctx, -ENOSPC, "a histogram list is full: hbt_hist_configure more capacity");
   return (int)ctx->n_cpus;
 }
 
@@ -928,7 +972,9 @@ static int64_t hist_collect(hbt_ctx* ctx, hbt_hist_entry* out, uint64_t cap) {
   CU(cudaStreamSynchronize(ctx->stream));
   if (out) {
     if (n > cap) return fail(ctx, -ENOSPC, "cap %llu < %llu entries", (unsigned long long)cap, n);
-    CU(cudaMemcpy(out, ctx->hist_out.p, n * sizeof(hbt_hist_entry), cudaMemcpyDeviceToHost));
+    CU(cudaMemcpyAsync(out, ctx->hist_out.p, n * sizeof(hbt_hist_entry), cudaMemcpyDeviceToHost,
+                       ctx->stream));
+    CU(cudaStreamSynchronize(ctx->stream));
   }
   return (int64_t)n;
 }
