@@ -190,11 +190,18 @@ __device__ __forceinline__ uint32_t hist_reserve(const HistLists& t, uint32_t cp
                                                  uint32_t& list) {
   const uint32_t b = (uint32_t)(((uint64_t)hash * t.buckets) >> 32);
   list = cpu * t.buckets + b;
+#if HBT_EXP == 1 || HBT_EXP == 3  // timing experiment: no global atomic (results are wrong)
+  return (hash >> 7) & 1023u;
+#else
   return atomicAdd(t.cursors + list, 1u);
+#endif
 }
 __device__ __forceinline__ void hist_store(const HistLists& t, uint32_t list, uint32_t pos,
                                            uint64_t ip, uint32_t pid, uint32_t weight) {
   if (pos < t.cap) {
+#if HBT_EXP == 2 || HBT_EXP == 3  // timing experiment: no entry store
+    if (pos == 0xFFFFFFF0u)
+#endif
     t.entries[(uint64_t)list * t.cap + pos] =
         make_ulonglong2(ip, (uint64_t)pid | ((uint64_t)weight << 32));
   } else {
@@ -229,6 +236,9 @@ struct HistCache {
 __device__ __forceinline__ bool hist_cache_count(HistCache& c, uint64_t ip, uint32_t pid,
                                                  uint32_t& hash) {
   hash = hist_hash(ip, pid);
+#if HBT_EXP == 4  // timing experiment: no segment cache
+  return false;
+#endif
   const uint32_t set = (hash ^ (hash >> 16)) & (kCacheSlots - 2);  // slots set, set + 1
   const uint32_t tag = hash | 1u;
   const uint64_t tg = *reinterpret_cast<const volatile uint64_t*>(c.tags + set);
@@ -258,6 +268,19 @@ __device__ __forceinline__ bool hist_cache_count(HistCache& c, uint64_t ip, uint
   }
   return false;
 }
+
+// Up to two appends of one thread whose slot reservations (hist_reserve) have been issued
+// but whose entries are not stored yet.
+struct HistPending {
+  uint64_t ip0, ip1;
+  uint32_t pid0, pid1, l0, l1, q0, q1;
+  bool m0 = false, m1 = false;
+  __device__ __forceinline__ void flush(const HistLists& t) {
+    if (m0) hist_store(t, l0, q0, ip0, pid0, 1);
+    if (m1) hist_store(t, l1, q1, ip1, pid1, 1);
+    m0 = m1 = false;
+  }
+};
 
 __device__ __forceinline__ void hist_count(const HistLists& t, HistCache& c, uint32_t cpu,
                                            uint64_t ip, uint32_t pid) {
@@ -436,7 +459,7 @@ __device__ __forceinline__ uint32_t sub_of_word(uint32_t w) {
 }
 
 template <int AGG>
-__global__ void __launch_bounds__(kThreads, kThreads == 256 ? (kTile <= 16384 ? 4 : 2) : 4) k_decode(const DecodeParams p) {
+__global__ void __launch_bounds__(kThreads, AGG == HBT_AGG_IP_HISTOGRAM ? 3 : 4) k_decode(const DecodeParams p) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   uint8_t* stages = smem_raw;  // kStages * kTile
   Smem& sm = *reinterpret_cast<Smem*>(smem_raw + kStages * kTile);
@@ -504,6 +527,8 @@ __global__ void __launch_bounds__(kThreads, kThreads == 256 ? (kTile <= 16384 ? 
 
   // thread-local totals over the fast-path tiles (added to st in the epilogue)
   uint32_t my_rec = 0, my_sample = 0;
+
+  HistPending pend;  // IP_HISTOGRAM: appends whose cursor atomics are in flight
 
   // my sub-chunk, in tile-relative bytes
   const uint32_t sb = 8u * sub_begin_word(tid);
@@ -591,29 +616,26 @@ __global__ void __launch_bounds__(kThreads, kThreads == 256 ? (kTile <= 16384 ? 
         my_sample += my_n;
         if (AGG == HBT_AGG_IP_HISTOGRAM) {
           for (uint32_t k = tid; k < n_t; k += 2 * kThreads) {
-            // two samples per thread per pass: their list appends (an atomic that has to
-            // return before the store can be placed) overlap
+            // two samples per thread per pass.  A list append is an atomic on the list's
+            // cursor that has to return before the store can be placed: the stores are
+            // deferred to the next pass / tile (pend), so nobody waits for the round trip
+            pend.flush(p.hist);
             const uint32_t p0 = erel + k * S, p1 = p0 + kThreads * S;
             const bool s0 = hdr_type(tv.at(p0)) == REC_SAMPLE && h_sample;
             const bool s1 = k + kThreads < n_t && hdr_type(tv.at(p1)) == REC_SAMPLE && h_sample;
-            uint64_t ip0 = 0, ip1 = 0;
-            uint32_t pid0 = 0, pid1 = 0, hs0 = 0, hs1 = 0;
-            bool m0 = false, m1 = false;  // cache miss: append
+            uint32_t hs0 = 0, hs1 = 0;
             if (s0) {
-              ip0 = tv.at(p0 + 8);
-              pid0 = (uint32_t)tv.at(p0 + 16);
-              m0 = !hist_cache_count(cache, ip0, pid0, hs0);
+              pend.ip0 = tv.at(p0 + 8);
+              pend.pid0 = (uint32_t)tv.at(p0 + 16);
+              pend.m0 = !hist_cache_count(cache, pend.ip0, pend.pid0, hs0);
             }
             if (s1) {
-              ip1 = tv.at(p1 + 8);
-              pid1 = (uint32_t)tv.at(p1 + 16);
-              m1 = !hist_cache_count(cache, ip1, pid1, hs1);
+              pend.ip1 = tv.at(p1 + 8);
+              pend.pid1 = (uint32_t)tv.at(p1 + 16);
+              pend.m1 = !hist_cache_count(cache, pend.ip1, pend.pid1, hs1);
             }
-            uint32_t l0 = 0, l1 = 0, q0 = 0, q1 = 0;
-            if (m0) q0 = hist_reserve(p.hist, seg.cpu, hs0, l0);
-            if (m1) q1 = hist_reserve(p.hist, seg.cpu, hs1, l1);
-            if (m0) hist_store(p.hist, l0, q0, ip0, pid0, 1);
-            if (m1) hist_store(p.hist, l1, q1, ip1, pid1, 1);
+            if (pend.m0) pend.q0 = hist_reserve(p.hist, seg.cpu, hs0, pend.l0);
+            if (pend.m1) pend.q1 = hist_reserve(p.hist, seg.cpu, hs1, pend.l1);
           }
         }
         uint32_t rows_tile = 0;
@@ -992,6 +1014,7 @@ __global__ void __launch_bounds__(kThreads, kThreads == 256 ? (kTile <= 16384 ? 
 
   // ---- segment epilogue --------------------------------------------------------
   if (AGG == HBT_AGG_IP_HISTOGRAM) {
+    pend.flush(p.hist);
     for (int i = tid; i < kCacheSlots; i += kThreads) {
       const ulonglong2 e = cache.slots[i];
       if ((e.y >> 32) != 0) {
@@ -1257,28 +1280,49 @@ __global__ void __launch_bounds__(64)
   clamp_head[c] = pos;
 }
 
-// k_hist_aggregate: one CTA per (cpu, bucket) list.  Folds the list -- distinct
-// entries left by earlier decodes followed by the raw samples (count 1) the last
-// decode appended -- into distinct keys with a shared-memory hash table, writes
-// them back to the front of the same list and sets the cursor to their number.
-// cap <= kAggSlots / 2, so the table can never fill up.
+// k_hist_aggregate: folds (cpu, bucket) lists -- distinct entries left by earlier
+// decodes followed by the raw samples (count 1) and segment-cache flushes the last
+// decode appended -- into distinct keys, writes them back to the front of the same list
+// and sets the cursor to their number.
+//
+// The list is staged in shared memory; a table of 32-bit words {16-bit fingerprint,
+// entry index + 1} with T >= 2n slots finds duplicates: an entry claims a slot with a
+// 32-bit CAS (it becomes the key's representative) or meets a word with its fingerprint,
+// compares the full key against the staged representative and, if equal, adds its weight
+// to the representative's and zeroes its own.  Entries whose weight is still non-zero are
+// the distinct keys.  Only native 32-bit shared-memory atomics, 4-byte probes, load <= 1/2.
 #ifndef HBT_AGG_SLOTS
 #define HBT_AGG_SLOTS 8192
 #endif
-constexpr uint32_t kAggSlots = HBT_AGG_SLOTS;   // 16-byte slots of the fold's shared-memory table
+constexpr uint32_t kAggSlots = HBT_AGG_SLOTS;   // table words of the largest size class (= 2 * list capacity)
 constexpr int kAggThreads = 256;
 constexpr int kAggBatch = 4;           // independent loads in flight per thread
 
-// Lists with n_lo < n <= n_hi entries are folded by this launch: the host runs a
-// first pass with a small table (most lists, high occupancy) and a second one with
-// the full-size table for the few long lists.
+__host__ __device__ constexpr size_t agg_smem_bytes(uint32_t n_hi) {
+  return (size_t)n_hi * sizeof(ulonglong2) + (size_t)2 * n_hi * sizeof(uint32_t);
+}
+
+__device__ __forceinline__ uint32_t agg_hash(uint64_t ip, uint32_t pid) {
+  // independent of hist_hash (whose top bits chose the list)
+  uint32_t x = (uint32_t)ip * 0x9E3779B1u + (uint32_t)(ip >> 32) * 0x85EBCA77u + pid * 0xC2B2AE3Du;
+  x ^= x >> 16;
+  x *= 0x7FEB352Du;
+  x ^= x >> 15;
+  x *= 0x846CA68Bu;
+  x ^= x >> 16;
+  return x;
+}
+
+// Lists with n_lo < n <= n_hi entries are folded by this launch (shared memory is sized
+// for n_hi): the host runs the small size class first (most lists, high occupancy) and
+// larger ones for the few long lists.
 __global__ void __launch_bounds__(kAggThreads)
     k_hist_aggregate(const HistLists t, uint32_t n_lists, uint32_t n_lo, uint32_t n_hi) {
   extern __shared__ __align__(16) uint8_t agg_smem[];
-  ulonglong2* slots = reinterpret_cast<ulonglong2*>(agg_smem);
+  ulonglong2* ent = reinterpret_cast<ulonglong2*>(agg_smem);
+  uint32_t* tab = reinterpret_cast<uint32_t*>(agg_smem + (size_t)n_hi * sizeof(ulonglong2));
   __shared__ uint32_t s_out;
   const uint32_t tid = threadIdx.x, lane = tid & 31;
-  const uint32_t s0 = smem_u32(slots);
   // This CTA owns a contiguous range of lists.  Their lengths are read 256 at a time
   // (coalesced) and the lists of this pass' size class are queued in shared memory,
   // so that skipping the others costs no dependent loads.
@@ -1301,57 +1345,69 @@ __global__ void __launch_bounds__(kAggThreads)
     }
     __syncthreads();
     const uint32_t qn = s_qn;
-  for (uint32_t qi = 0; qi < qn; ++qi) {
-    const uint32_t list = s_q[qi];
-    const uint32_t n = s_qlen[qi];
-    // table size: power of two >= 1.5 n (load <= 2/3; n <= cap = kAggSlots / 2)
-    uint32_t T = 64;
-    while (2 * T < 3 * n) T <<= 1;
-    for (uint32_t i = tid; i < T; i += kAggThreads) slots[i] = make_ulonglong2(0, 0);
-    if (tid == 0) s_out = 0;
-    __syncthreads();
-    ulonglong2* lst = t.entries + (uint64_t)list * t.cap;
-    for (uint32_t base = 0; base < n; base += kAggThreads * kAggBatch) {
-      ulonglong2 e[kAggBatch];
+    for (uint32_t qi = 0; qi < qn; ++qi) {
+      const uint32_t list = s_q[qi];
+      const uint32_t n = s_qlen[qi];
+      uint32_t T = 64;  // power of two >= 2n (n <= n_hi, the table has 2 * n_hi words)
+      while (T < 2 * n) T <<= 1;
+      for (uint32_t i = tid * 4; i < T; i += kAggThreads * 4)
+        *reinterpret_cast<uint4*>(tab + i) = make_uint4(0, 0, 0, 0);
+      if (tid == 0) s_out = 0;
+      ulonglong2* lst = t.entries + (uint64_t)list * t.cap;
+      // stage the list
+      for (uint32_t base = 0; base < n; base += kAggThreads * kAggBatch) {
+        ulonglong2 e[kAggBatch];
 #pragma unroll
-      for (int k = 0; k < kAggBatch; ++k) {
-        const uint32_t i = base + k * kAggThreads + tid;
-        e[k] = i < n ? ld_stream_v2u64(lst + i) : make_ulonglong2(0, 0);
+        for (int k = 0; k < kAggBatch; ++k) {
+          const uint32_t i = base + k * kAggThreads + tid;
+          if (i < n) e[k] = ld_stream_v2u64(lst + i);
+        }
+#pragma unroll
+        for (int k = 0; k < kAggBatch; ++k) {
+          const uint32_t i = base + k * kAggThreads + tid;
+          if (i < n) ent[i] = e[k];
+        }
       }
-#pragma unroll
-      for (int k = 0; k < kAggBatch; ++k) {
-        const uint32_t pid = (uint32_t)e[k].y, w = (uint32_t)(e[k].y >> 32);
-        if (w == 0) continue;  // padding of the last batch (a real entry has weight >= 1)
-        // second hash: the bucket already consumed the top bits of hist_hash
-        uint32_t h = (uint32_t)mix64(e[k].x * 0xD6E8FEB86659FD93ull + pid) & (T - 1);
+      __syncthreads();
+      // find duplicates
+      for (uint32_t i = tid; i < n; i += kAggThreads) {
+        const ulonglong2 e = ent[i];
+        const uint32_t pid = (uint32_t)e.y, w = (uint32_t)(e.y >> 32);
+        if (w == 0) continue;  // never appended with weight 0; kept for robustness
+        const uint32_t x = agg_hash(e.x, pid);
+        const uint32_t word = (x & 0xFFFF0000u) | (i + 1);
+        uint32_t h = x & (T - 1);
         for (;;) {
-          uint64_t olo, ohi;
-          cas128_shared(s0 + h * 16, 0, 0, e[k].x, e[k].y, olo, ohi);
-          if (olo == 0 && ohi == 0) break;  // claimed with weight w
-          if (olo == e[k].x && (uint32_t)ohi == pid) {
-            atomicAdd(reinterpret_cast<uint32_t*>(slots + h) + 3, w);
-            break;
+          const uint32_t old = atomicCAS(tab + h, 0u, word);
+          if (old == 0) break;  // representative of its key
+          if (((old ^ word) & 0xFFFF0000u) == 0) {
+            const uint32_t j = (old & 0xFFFFu) - 1;
+            const volatile uint64_t* rj = reinterpret_cast<const volatile uint64_t*>(ent + j);
+            if (rj[0] == e.x && (uint32_t)rj[1] == pid) {
+              atomicAdd(reinterpret_cast<uint32_t*>(ent + j) + 3, w);
+              reinterpret_cast<uint32_t*>(ent + i)[3] = 0;  // merged: only this thread touches it
+              break;
+            }
           }
           h = (h + 1) & (T - 1);
         }
       }
+      __syncthreads();
+      // write the distinct keys back to the front of the list (one counter bump per warp)
+      for (uint32_t i0 = 0; i0 < n; i0 += kAggThreads) {
+        const bool in = i0 + tid < n;
+        const ulonglong2 e = in ? ent[i0 + tid] : make_ulonglong2(0, 0);
+        const bool used = in && (e.y >> 32) != 0;
+        const uint32_t m = __ballot_sync(0xffffffffu, used);
+        uint32_t wbase = 0;
+        if (lane == 0 && m) wbase = atomicAdd(&s_out, (uint32_t)__popc(m));
+        wbase = __shfl_sync(0xffffffffu, wbase, 0);
+        if (used) lst[wbase + __popc(m & ((1u << lane) - 1))] = e;
+      }
+      __syncthreads();
+      if (tid == 0) t.cursors[list] = s_out;
+      // the next list's staging must not start before everyone has read s_out / ent
     }
-    __syncthreads();
-    // write the distinct keys back to the front of the list (one cursor bump per warp)
-    for (uint32_t i0 = 0; i0 < T; i0 += kAggThreads) {
-      const bool in = i0 + tid < T;  // T can be smaller than the CTA
-      const ulonglong2 e = in ? slots[i0 + tid] : make_ulonglong2(0, 0);
-      const bool used = in && (e.y >> 32) != 0;
-      const uint32_t m = __ballot_sync(0xffffffffu, used);
-      uint32_t wbase = 0;
-      if (lane == 0 && m) wbase = atomicAdd(&s_out, (uint32_t)__popc(m));
-      wbase = __shfl_sync(0xffffffffu, wbase, 0);
-      if (used) lst[wbase + __popc(m & ((1u << lane) - 1))] = e;
-    }
-    __syncthreads();
-    if (tid == 0) t.cursors[list] = s_out;
-    __syncthreads();
-  }
   }
 }
 

@@ -448,21 +448,20 @@ HistLists hist_view(hbt_ctx* ctx) {
 // Fold the raw samples the last decode appended into distinct keys (k_hist_aggregate).
 int hist_fold(hbt_ctx* ctx) {
   if (!ctx->hist_pending_fold) return 0;
-  const size_t smem_full = (size_t)kAggSlots * sizeof(ulonglong2);
+  const size_t smem_full = agg_smem_bytes(kAggSlots / 2);
   if (!ctx->agg_attr_set) {
     CU(cudaFuncSetAttribute(k_hist_aggregate, cudaFuncAttributeMaxDynamicSharedMemorySize,
                             (int)smem_full));
     ctx->agg_attr_set = true;
   }
   const uint32_t n = (uint32_t)hist_lists(ctx);
-  // Lists are folded by size class, smallest table first: most lists are short and
-  // a small table lets many CTAs share an SM; the few long ones (a warm key repeats in
-  // its list) get the full-size table.  A table is a power of two >= 1.5 n slots.
+  // Lists are folded by size class, smallest first: most lists are short and a small
+  // staging area lets many CTAs share an SM; the few long ones (a warm key repeats in
+  // its list) get the full-size one.  Shared memory = 24 bytes per entry of the class.
   CU(cudaEventRecord(ctx->ev_f0, ctx->stream));
   uint32_t lo = 1;
-  for (uint32_t slots = kAggSlots / 8; slots <= kAggSlots; slots *= 2) {
-    const uint32_t hi = slots == kAggSlots ? 0xFFFFFFFFu : slots * 2 / 3;
-    const size_t smem = (size_t)slots * sizeof(ulonglong2);
+  for (uint32_t hi = kAggSlots / 8; hi <= kAggSlots / 2; hi *= 2) {
+    const size_t smem = agg_smem_bytes(hi);
     uint32_t per_sm = (uint32_t)((220 * 1024) / (smem + 1024));
     if (per_sm > 8) per_sm = 8;
     uint32_t grid = (uint32_t)ctx->sm_count * per_sm * 4;
