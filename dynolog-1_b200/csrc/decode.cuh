@@ -1298,8 +1298,9 @@ constexpr uint32_t kAggSlots = HBT_AGG_SLOTS;   // table words of the largest si
 constexpr int kAggThreads = 256;
 constexpr int kAggBatch = 4;           // independent loads in flight per thread
 
+// two staging buffers (the next list is copied in while the current one folds) + the table
 __host__ __device__ constexpr size_t agg_smem_bytes(uint32_t n_hi) {
-  return (size_t)n_hi * sizeof(ulonglong2) + (size_t)2 * n_hi * sizeof(uint32_t);
+  return (size_t)2 * n_hi * sizeof(ulonglong2) + (size_t)2 * n_hi * sizeof(uint32_t);
 }
 
 __device__ __forceinline__ uint32_t agg_hash(uint64_t ip, uint32_t pid) {
@@ -1318,19 +1319,26 @@ __device__ __forceinline__ uint32_t agg_hash(uint64_t ip, uint32_t pid) {
 // larger ones for the few long lists.
 __global__ void __launch_bounds__(kAggThreads)
     k_hist_aggregate(const HistLists t, uint32_t n_lists, uint32_t n_lo, uint32_t n_hi) {
-  extern __shared__ __align__(16) uint8_t agg_smem[];
-  ulonglong2* ent = reinterpret_cast<ulonglong2*>(agg_smem);
-  uint32_t* tab = reinterpret_cast<uint32_t*>(agg_smem + (size_t)n_hi * sizeof(ulonglong2));
+  extern __shared__ __align__(128) uint8_t agg_smem[];
+  ulonglong2* ent_buf = reinterpret_cast<ulonglong2*>(agg_smem);  // [2][n_hi]
+  uint32_t* tab = reinterpret_cast<uint32_t*>(agg_smem + (size_t)2 * n_hi * sizeof(ulonglong2));
   __shared__ uint32_t s_out;
+  __shared__ __align__(8) uint64_t s_bar[2];
   const uint32_t tid = threadIdx.x, lane = tid & 31;
   // This CTA owns a contiguous range of lists.  Their lengths are read 256 at a time
   // (coalesced) and the lists of this pass' size class are queued in shared memory,
   // so that skipping the others costs no dependent loads.
   __shared__ uint32_t s_q[kAggThreads], s_qlen[kAggThreads];
   __shared__ uint32_t s_qn;
+  if (tid == 0) {
+    mbar_init(&s_bar[0], 1);
+    mbar_init(&s_bar[1], 1);
+    fence_mbar_init();
+  }
   const uint32_t per_cta = (n_lists + gridDim.x - 1) / gridDim.x;
   const uint32_t l_begin = blockIdx.x * per_cta;
   const uint32_t l_end = min(n_lists, l_begin + per_cta);
+  uint32_t it = 0;  // lists folded so far: buffer = it & 1, mbarrier parity = (it >> 1) & 1
   for (uint32_t l0 = l_begin; l0 < l_end; l0 += kAggThreads) {
     if (tid == 0) s_qn = 0;
     __syncthreads();
@@ -1345,30 +1353,27 @@ __global__ void __launch_bounds__(kAggThreads)
     }
     __syncthreads();
     const uint32_t qn = s_qn;
-    for (uint32_t qi = 0; qi < qn; ++qi) {
+    // one bulk async copy stages a whole list; the copy of list qi+1 runs while qi folds
+    auto stage = [&](uint32_t q, uint32_t buf) {
+      const uint32_t bytes = s_qlen[q] * (uint32_t)sizeof(ulonglong2);
+      mbar_arrive_expect_tx(&s_bar[buf], bytes);
+      bulk_g2s(ent_buf + (size_t)buf * n_hi, t.entries + (uint64_t)s_q[q] * t.cap, bytes, &s_bar[buf]);
+    };
+    if (tid == 0 && qn) stage(0, it & 1);
+    for (uint32_t qi = 0; qi < qn; ++qi, ++it) {
       const uint32_t list = s_q[qi];
       const uint32_t n = s_qlen[qi];
+      const uint32_t buf = it & 1;
+      ulonglong2* ent = ent_buf + (size_t)buf * n_hi;
+      if (tid == 0 && qi + 1 < qn) stage(qi + 1, buf ^ 1);
       uint32_t T = 64;  // power of two >= 2n (n <= n_hi, the table has 2 * n_hi words)
       while (T < 2 * n) T <<= 1;
       for (uint32_t i = tid * 4; i < T; i += kAggThreads * 4)
         *reinterpret_cast<uint4*>(tab + i) = make_uint4(0, 0, 0, 0);
       if (tid == 0) s_out = 0;
-      ulonglong2* lst = t.entries + (uint64_t)list * t.cap;
-      // stage the list
-      for (uint32_t base = 0; base < n; base += kAggThreads * kAggBatch) {
-        ulonglong2 e[kAggBatch];
-#pragma unroll
-        for (int k = 0; k < kAggBatch; ++k) {
-          const uint32_t i = base + k * kAggThreads + tid;
-          if (i < n) e[k] = ld_stream_v2u64(lst + i);
-        }
-#pragma unroll
-        for (int k = 0; k < kAggBatch; ++k) {
-          const uint32_t i = base + k * kAggThreads + tid;
-          if (i < n) ent[i] = e[k];
-        }
-      }
+      mbar_wait(&s_bar[buf], (it >> 1) & 1);
       __syncthreads();
+      ulonglong2* lst = t.entries + (uint64_t)list * t.cap;
       // find duplicates
       for (uint32_t i = tid; i < n; i += kAggThreads) {
         const ulonglong2 e = ent[i];
@@ -1404,9 +1409,11 @@ __global__ void __launch_bounds__(kAggThreads)
         wbase = __shfl_sync(0xffffffffu, wbase, 0);
         if (used) lst[wbase + __popc(m & ((1u << lane) - 1))] = e;
       }
+      // this buffer is refilled by a bulk copy (async proxy) after the barrier: order the
+      // generic-proxy accesses above before it
+      fence_proxy_async();
       __syncthreads();
       if (tid == 0) t.cursors[list] = s_out;
-      // the next list's staging must not start before everyone has read s_out / ent
     }
   }
 }
