@@ -225,7 +225,10 @@ __device__ __forceinline__ void hist_append(const HistLists& t, uint32_t cpu, ui
 // tags tells them so; a tag match is always confirmed against the full key.  A sample
 // whose set holds other keys is appended to its list directly.  Every sample is
 // counted exactly once.  Flushed to the lists (weighted entries) at segment end.
-constexpr int kCacheSlots = 1024;
+#ifndef HBT_CACHE_SLOTS
+#define HBT_CACHE_SLOTS 1024
+#endif
+constexpr int kCacheSlots = HBT_CACHE_SLOTS;
 
 struct HistCache {
   ulonglong2 slots[kCacheSlots];
@@ -459,7 +462,7 @@ __device__ __forceinline__ uint32_t sub_of_word(uint32_t w) {
 }
 
 template <int AGG>
-__global__ void __launch_bounds__(kThreads, AGG == HBT_AGG_IP_HISTOGRAM ? 3 : 4) k_decode(const DecodeParams p) {
+__global__ void __launch_bounds__(kThreads, AGG == HBT_AGG_IP_HISTOGRAM && kCacheSlots > 256 ? 3 : 4) k_decode(const DecodeParams p) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   uint8_t* stages = smem_raw;  // kStages * kTile
   Smem& sm = *reinterpret_cast<Smem*>(smem_raw + kStages * kTile);

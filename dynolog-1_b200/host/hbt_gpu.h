@@ -6,6 +6,9 @@
 //   hbt::perf_event::PerCpuBase::read     hbt/src/perf_event/PerCpuBase.h:104-119
 //   hbt::perf_event::RbDataSlices         hbt/src/perf_event/CpuEventsGroup.h:44-63
 //   hbt::mon::Monitor                     hbt/src/mon/Monitor.h:40-99,213-237,281-304,484-732
+//   count-sample row sink + consumers     hbt/src/perf_event/PerCpuCountSampleGenerator.h:69,182-195,
+//                                         hbt/src/ringbuffer/Producer.h:137-197, hbt/src/mon/MonData.h:69-128,
+//                                         hbt/src/mon/TraceMonitor.h:34-109, TraceMonitor.cpp:25-100
 // so that dynolog::PerfMonitor-shaped code (perf_monitor.h) compiles against it
 // unchanged in shape.  All arithmetic of the path runs on the GPU: there is no
 // host implementation behind these classes, and constructing a GpuContext
@@ -324,9 +327,169 @@ class PerCpuCountSampleDecoder {
   std::vector<hbt_cpu_result> results_;
 };
 
+// What a CpuCountSampleGenerator's output ring is to its consumers: a byte FIFO of
+// nextPow2(rb_min_num_entries * kWriteByteSize) bytes (hbt/src/ringbuffer/RingBuffer.h:69)
+// holding rows {tstamp, duration, deltas[n]}.  write() follows handleRecordSample's
+// tail (PerCpuCountSampleGenerator.h:182-195): a row that does not fit is refused with
+// -ENOSPC unless num_counts_drop_if_full > 0, in which case that many of the OLDEST rows
+// are dropped first (Producer::dropN, Producer.h:181-197) and the write is retried.
+// The GPU decode produces a whole batch of rows at once, so unlike the reference a
+// refused row cannot stop consume() before its record: size the sink for a batch or
+// set the drop rule -- write() reports how many rows it had to refuse.
+class CountSampleSink {
+ public:
+  CountSampleSink(size_t n_events, size_t rb_min_num_entries, size_t num_counts_drop_if_full)
+      : kNumEvents{n_events}, kWriteByteSize{sizeof(uint64_t) * (2 + n_events)},
+        kNumBytesDropIfFull{num_counts_drop_if_full * kWriteByteSize},
+        kDataPoolByteSize{nextPow2(rb_min_num_entries * kWriteByteSize)} {
+    if (kNumBytesDropIfFull > kDataPoolByteSize) throw std::invalid_argument("drop size larger than the buffer");
+  }
+  const size_t kNumEvents, kWriteByteSize, kNumBytesDropIfFull, kDataPoolByteSize;
+
+  // One row; 0 or -ENOSPC.
+  int write(const uint64_t* row) {
+    if (usedBytes() + kWriteByteSize > kDataPoolByteSize) {
+      if (kNumBytesDropIfFull == 0) return -ENOSPC;
+      dropN(kNumBytesDropIfFull);
+      if (usedBytes() + kWriteByteSize > kDataPoolByteSize) return -ENOSPC;
+    }
+    data_.insert(data_.end(), row, row + 2 + kNumEvents);
+    return 0;
+  }
+  // n_rows rows in stream order; returns the number refused (0 when all were taken).
+  size_t write(const uint64_t* rows, size_t n_rows) {
+    size_t refused = 0;
+    for (size_t r = 0; r < n_rows; ++r)
+      if (write(rows + r * (2 + kNumEvents)) < 0) ++refused;
+    return refused;
+  }
+  // Header::dropN: forget the oldest bytes (all of them if fewer are stored)
+  void dropN(size_t n_bytes) {
+    head_ += std::min(n_bytes / sizeof(uint64_t), data_.size() - head_);
+    if (head_ * 2 > data_.size() && head_ >= 1024) {  // reclaim the consumed front now and then
+      data_.erase(data_.begin(), data_.begin() + (std::ptrdiff_t)head_);
+      head_ = 0;
+    }
+  }
+  size_t getNumEntries() const { return (data_.size() - head_) / (2 + kNumEvents); }
+  size_t usedBytes() const { return (data_.size() - head_) * sizeof(uint64_t); }
+  // Consumer side (ringbuffer::Consumer::readInTx / relSeekInTx / commitTx reduced to a cursor);
+  // the returned row is contiguous and stays valid until the next write/consume.
+  const uint64_t* peek(size_t i) const {
+    return i < getNumEntries() ? data_.data() + head_ + i * (2 + kNumEvents) : nullptr;
+  }
+  void consume(size_t n_rows) { dropN(n_rows * kWriteByteSize); }
+
+ private:
+  static size_t nextPow2(size_t v) {
+    size_t p = 1;
+    while (p < v) p <<= 1;
+    return p;
+  }
+  std::vector<uint64_t> data_;
+  size_t head_ = 0;  // first live word
+};
+
 }  // namespace perf_event
 
 namespace mon {
+
+// hbt::mon::CountData (hbt/src/mon/MonData.h:69-128): rows of one compute unit.
+struct CountData {
+  const std::vector<std::string> event_names;
+  const size_t kRowStride;  // in elements
+  explicit CountData(const std::vector<std::string>& names) : event_names{names}, kRowStride{names.size() + 2} {}
+  size_t numEvents() const noexcept { return event_names.size(); }
+  void write(const uint64_t* d) { data.insert(data.end(), d, d + (2 + numEvents())); }
+  size_t numIntervals() const { return data.size() / kRowStride; }
+  // {first row's start, last row's start + duration}
+  std::optional<std::pair<TimeStamp, TimeStamp>> getTimeStampRange() const {
+    if (data.size() % kRowStride != 0) throw std::runtime_error("CountData: partial row");  // HBT_THROW_ASSERT_IF
+    if (data.empty()) return std::nullopt;
+    const size_t last = data.size() - (2 + numEvents());
+    return std::make_pair(data[0], data[last] + data[last + 1]);
+  }
+  std::unique_ptr<CountData> filter(const std::vector<bool>& sel) const {
+    auto cd = std::make_unique<CountData>(event_names);
+    for (size_t r = 0, i = 0; r < data.size(); r += kRowStride, ++i)
+      if (sel[i]) {
+        std::vector<uint64_t> row(data.begin() + (std::ptrdiff_t)r, data.begin() + (std::ptrdiff_t)(r + kRowStride));
+        cd->write(row.data());
+      }
+    return cd;
+  }
+  std::optional<size_t> findCountAt(TimeStamp tstamp) const {
+    for (size_t r = 0, i = 0; r < data.size(); r += kRowStride, ++i)
+      if (data[r] <= tstamp && data[r] + data[r + 1] > tstamp) return i;
+    return std::nullopt;
+  }
+  std::deque<uint64_t> data;
+};
+
+// The count-generator half of hbt::mon::TraceMonitor (hbt/src/mon/TraceMonitor.h:34-109,
+// TraceMonitor.cpp:25-100): per-CPU sinks fed by the GPU decoder's rows, consumed either
+// through a callback or into CountData up to a stop timestamp.
+class TraceMonitor {
+ public:
+  TraceMonitor(const CpuSet& mon_cpus, std::vector<std::string> event_nicknames, size_t rb_min_num_entries,
+               size_t num_counts_drop_if_full)
+      : mon_cpus_{mon_cpus}, nicknames_{std::move(event_nicknames)} {
+    for (CpuId cpu : mon_cpus_.cpus)
+      sinks_.emplace(cpu, perf_event::CountSampleSink(nicknames_.size(), rb_min_num_entries, num_counts_drop_if_full));
+  }
+  perf_event::CountSampleSink& sink(CpuId cpu) {
+    auto it = sinks_.find(cpu);
+    if (it == sinks_.end()) throw std::invalid_argument("CPU " + std::to_string(cpu) + " not monitored");
+    return it->second;
+  }
+  // Move the rows of the decoder's last consume() into the sinks (the producer side:
+  // what handleRecordSample's output_producer_.write does row by row).  Returns rows refused.
+  size_t accum(perf_event::PerCpuCountSampleDecoder& dec) {
+    std::lock_guard<std::mutex> lock{counts_mutex_};
+    size_t refused = 0;
+    for (CpuId cpu : mon_cpus_.cpus) {
+      const std::vector<uint64_t> rows = dec.rows(cpu);
+      refused += sink(cpu).write(rows.data(), rows.size() / (2 + nicknames_.size()));
+    }
+    return refused;
+  }
+  // func(cpu, count_idx, event_nicknames, tstamp, duration, const uint64_t* counts, kNumEvents)
+  // for every stored row, CPUs in ascending order, then the rows are consumed (TraceMonitor.h:45-109).
+  template <class TFunc>
+  void applyToCountSamplesAndConsume(TFunc& func) {
+    std::lock_guard<std::mutex> lock{counts_mutex_};
+    for (CpuId cpu : mon_cpus_.cpus) {
+      auto& s = sink(cpu);
+      const size_t n = s.getNumEntries();
+      for (size_t i = 0; i < n; ++i) {
+        const uint64_t* p = s.peek(i);
+        func(cpu, (int)i, nicknames_, (TimeStamp)p[0], (TimeStamp)p[1], p + 2, nicknames_.size());
+      }
+      s.consume(n);
+    }
+  }
+  // releaseCountData_ (TraceMonitor.cpp:25-100) without slices: rows whose interval ends
+  // before stop_ts move into a CountData; the first row reaching stop_ts stays in the sink.
+  std::unique_ptr<CountData> releaseCountData(CpuId cpu, TimeStamp stop_ts) {
+    std::lock_guard<std::mutex> lock{counts_mutex_};
+    auto& s = sink(cpu);
+    auto cd = std::make_unique<CountData>(nicknames_);
+    size_t n = 0;
+    for (; n < s.getNumEntries(); ++n) {
+      const uint64_t* p = s.peek(n);
+      if (p[0] + p[1] >= stop_ts) break;
+      cd->write(p);
+    }
+    s.consume(n);
+    return cd;
+  }
+
+ private:
+  CpuSet mon_cpus_;
+  std::vector<std::string> nicknames_;
+  std::map<CpuId, perf_event::CountSampleSink> sinks_;
+  std::mutex counts_mutex_;
+};
 
 // hbt::mon::Monitor: element map, mux queue, Closed/Open/Enabled state machine,
 // one mutex (hbt/src/mon/Monitor.h:40-99, 484-520, 681-732).

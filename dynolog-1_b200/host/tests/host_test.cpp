@@ -1,6 +1,8 @@
 // Tests of the host-side mirror (hbt_gpu.h, perf_monitor.h).  `host_test cpu` needs no
 // GPU; `host_test gpu` drives the CUDA path through the mirrored reference API and
 // checks it against the reference's expressions restated here (test-side only).
+#include <dlfcn.h>
+
 #include <cmath>
 #include <cstdio>
 #include <iostream>
@@ -92,6 +94,88 @@ static void test_cpu() {
   }
   if (!have_gpu) CHECK(throws<std::system_error>([] { GpuContext g(0); }));
   CHECK(throws<std::invalid_argument>([] { GpuContext g(0, HBT_MAX_CPUS + 1, 8); }));
+}
+
+// Row sink, CountData and the TraceMonitor consumers (no GPU needed).  When the reference
+// harness (oracle/_ref/libhbt_ref.so, env HBT_REF_LIB) is present the sink is also checked
+// against the reference's own ringbuffer::Producer/Consumer on random row sequences.
+static void test_row_sink() {
+  const size_t E = 3;
+  auto row = [&](uint64_t k) { return std::vector<uint64_t>{1000 + 10 * k, 10, k, 2 * k, 3 * k}; };
+  // 40-byte rows, 6 requested -> 256-byte pool: 6 rows fit, the 7th does not
+  pe::CountSampleSink s0(E, 6, 0);
+  CHECK(s0.kWriteByteSize == 40 && s0.kDataPoolByteSize == 256);
+  for (uint64_t k = 0; k < 6; ++k) CHECK(s0.write(row(k).data()) == 0);
+  CHECK(s0.write(row(6).data()) == -ENOSPC && s0.getNumEntries() == 6);
+  // drop rule: the 2 oldest rows go, the new one enters
+  pe::CountSampleSink s1(E, 6, 2);
+  for (uint64_t k = 0; k < 7; ++k) CHECK(s1.write(row(k).data()) == 0);
+  CHECK(s1.getNumEntries() == 5 && s1.peek(0)[0] == 1020 && s1.peek(4)[0] == 1060);
+  CHECK(throws<std::invalid_argument>([] { pe::CountSampleSink bad(3, 2, 100); }));
+
+  mon::CountData cd({"a", "b", "c"});
+  CHECK(cd.kRowStride == 5 && !cd.getTimeStampRange().has_value());
+  for (uint64_t k = 0; k < 4; ++k) cd.write(row(k).data());
+  CHECK(cd.numIntervals() == 4);
+  CHECK(cd.getTimeStampRange()->first == 1000 && cd.getTimeStampRange()->second == 1040);
+  CHECK(*cd.findCountAt(1019) == 1 && *cd.findCountAt(1020) == 2 && !cd.findCountAt(1040).has_value());
+  auto f = cd.filter({true, false, false, true});
+  CHECK(f->numIntervals() == 2 && f->data[5] == 1030);
+
+  auto cpus = CpuSet::makeFromCont(std::vector<int>{1, 4});
+  mon::TraceMonitor tm(cpus, {"a", "b", "c"}, 64, 0);
+  for (uint64_t k = 0; k < 5; ++k) tm.sink(4).write(row(k).data());
+  for (uint64_t k = 0; k < 2; ++k) tm.sink(1).write(row(k + 10).data());
+  CHECK(throws<std::invalid_argument>([&] { tm.sink(2); }));
+  // rows ending before stop_ts are released, the one reaching it stays (TraceMonitor.cpp:62-70)
+  auto rel = tm.releaseCountData(4, 1030);
+  CHECK(rel->numIntervals() == 2 && tm.sink(4).getNumEntries() == 3);
+  std::vector<std::vector<uint64_t>> seen;
+  auto func = [&](CpuId cpu, int idx, const std::vector<std::string>& names, TimeStamp t, TimeStamp d,
+                  const uint64_t* c, size_t n) {
+    CHECK(names.size() == 3 && n == 3 && d == 10);
+    seen.push_back({cpu, (uint64_t)idx, t, c[0], c[2]});
+  };
+  tm.applyToCountSamplesAndConsume(func);
+  CHECK(seen.size() == 5);
+  if (seen.size() == 5) {
+    CHECK((seen[0] == std::vector<uint64_t>{1, 0, 1100, 10, 30}));  // CPUs ascending, idx per CPU
+    CHECK((seen[2] == std::vector<uint64_t>{4, 0, 1020, 2, 6}));
+    CHECK((seen[4] == std::vector<uint64_t>{4, 2, 1040, 4, 12}));
+  }
+  CHECK(tm.sink(1).getNumEntries() == 0 && tm.sink(4).getNumEntries() == 0);
+
+  const char* ref = std::getenv("HBT_REF_LIB");
+  void* h = ref ? dlopen(ref, RTLD_NOW | RTLD_LOCAL) : nullptr;
+  using Fn = int (*)(const uint64_t*, uint64_t, uint32_t, uint64_t, uint64_t, uint64_t*, uint64_t, uint64_t*, uint64_t*);
+  Fn fn = h ? (Fn)dlsym(h, "hbtref_row_sink") : nullptr;
+  if (!fn) {
+    std::printf("row sink vs reference ring buffer: skipped (HBT_REF_LIB not set or not loadable)\n");
+    return;
+  }
+  uint64_t seed = 42;
+  int cases = 0;
+  for (uint32_t ev : {1u, 3u, 8u, 32u})
+    for (uint64_t cap : {1ull, 5ull, 16ull, 100ull})
+      for (uint64_t drop : {0ull, 1ull, 3ull}) {
+        const uint64_t n = 1 + sm64(seed) % 300;
+        std::vector<uint64_t> rows(n * (2 + ev));
+        for (auto& w : rows) w = sm64(seed);
+        std::vector<uint64_t> out(rows.size());
+        uint64_t n_out = 0, refused = 0;
+        const size_t pool = [&] { size_t p = 1; while (p < cap * 8 * (2 + ev)) p <<= 1; return p; }();
+        if (drop * 8 * (2 + ev) > pool) continue;
+        CHECK(fn(rows.data(), n, ev, cap, drop, out.data(), n, &n_out, &refused) == 0);
+        pe::CountSampleSink sk(ev, cap, drop);
+        const size_t my_refused = sk.write(rows.data(), n);
+        CHECK(my_refused == refused && sk.getNumEntries() == n_out);
+        bool same = sk.getNumEntries() == n_out;
+        for (uint64_t r = 0; same && r < n_out; ++r)
+          same = std::memcmp(sk.peek(r), &out[r * (2 + ev)], 8 * (2 + ev)) == 0;
+        CHECK(same);
+        ++cases;
+      }
+  std::printf("row sink vs reference ring buffer: %d cases\n", cases);
 }
 
 static void test_gpu() {
@@ -193,11 +277,24 @@ static void test_gpu() {
   }
   CHECK(dec.getLastTimeStamp(2) == 1040);
   CHECK(throws<std::invalid_argument>([&] { dec.onCpuDataBufferRead(1, slices, tail, head); }));
+  // rows -> sinks -> applyToCountSamplesAndConsume callback (TraceMonitor.h:45-109)
+  mon::TraceMonitor tm(CpuSet::makeFromCont(std::vector<int>{0, 2}), {"cycles", "instructions"}, 16, 0);
+  CHECK(tm.accum(dec) == 0 && tm.sink(2).getNumEntries() == 4 && tm.sink(0).getNumEntries() == 0);
+  int calls = 0;
+  auto func = [&](CpuId cpu, int idx, const std::vector<std::string>& names, TimeStamp t, TimeStamp d,
+                  const uint64_t* c, size_t n) {
+    CHECK(cpu == 2 && idx == calls && names[1] == "instructions" && n == 2);
+    CHECK(t == 1000 + 10 * (uint64_t)idx && d == 10 && c[0] == 100 && c[1] == 200);
+    ++calls;
+  };
+  tm.applyToCountSamplesAndConsume(func);
+  CHECK(calls == 4 && tm.sink(2).getNumEntries() == 0);
 }
 
 int main(int argc, char** argv) {
   const std::string mode = argc > 1 ? argv[1] : "cpu";
   test_cpu();
+  test_row_sink();
   if (mode == "gpu") test_gpu();
   std::printf("%s: %s (%d failures)\n", mode.c_str(), g_fail ? "FAILED" : "ok", g_fail);
   return g_fail ? 1 : 0;

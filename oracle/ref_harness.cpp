@@ -606,6 +606,40 @@ double hbtref_sample_deltas_timed(const uint8_t* rings, uint64_t data_size, cons
   return std::chrono::duration<double>(t1 - t0).count();
 }
 
+// The generator's output ring as a row sink: n_rows rows {tstamp,duration,deltas[n]} go
+// through the REAL ringbuffer::Producer of a RingBuffer sized like the generator sizes its
+// own (rb_min_num_entries * kWriteByteSize, PerCpuCountSampleGenerator.h:69-71) with the
+// write / dropN / retry sequence of handleRecordSample (:182-195); what is left is drained
+// with the real ringbuffer::Consumer.  refused = rows whose write failed.
+int hbtref_row_sink(const uint64_t* rows, uint64_t n_rows, uint32_t n_events, uint64_t rb_min_num_entries,
+                    uint64_t num_counts_drop_if_full, uint64_t* out, uint64_t out_cap, uint64_t* n_out,
+                    uint64_t* refused) {
+  namespace rb = facebook::hbt::ringbuffer;
+  using Extra = hp::CpuCountSampleGenerator::RbExtraData;
+  const size_t row_bytes = sizeof(uint64_t) * (2 + n_events);
+  const size_t drop_bytes = num_counts_drop_if_full * row_bytes;
+  rb::Producer<Extra> prod(std::make_shared<rb::RingBuffer<Extra>>(rb_min_num_entries * row_bytes));
+  *refused = 0;
+  for (uint64_t r = 0; r < n_rows; ++r) {
+    auto ret = prod.write(rows + r * (2 + n_events), row_bytes);
+    if (drop_bytes > 0 && ret == -ENOSPC) {
+      if (prod.dropN(drop_bytes) < 0) return -EIO;
+      ret = prod.write(rows + r * (2 + n_events), row_bytes);
+    }
+    if (ret < 0) ++*refused;
+  }
+  rb::Consumer<Extra> cons(prod.getRingBuffer());
+  uint64_t n = 0;
+  std::vector<uint64_t> row(2 + n_events);
+  while (cons.copy(row_bytes, row.data()) >= 0) {
+    if (n >= out_cap) return -ENOSPC;
+    std::memcpy(out + n * (2 + n_events), row.data(), row_bytes);
+    ++n;
+  }
+  *n_out = n;
+  return 0;
+}
+
 // ---------------------------------------------------------------------------
 // Counter groups: the real PerCpuBase<T>::read (PerCpuBase.h:104-119) over a
 // fake per-CPU reader that replays a recorded trace, then the real
