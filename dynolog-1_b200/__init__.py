@@ -20,7 +20,7 @@ REPO_ROOT = os.path.dirname(_HERE)
 LIB_PATH = os.environ.get("HBT_B200_LIB") or os.path.join(_HERE, "libhbt_b200.so")  # env: tuning builds
 
 # ---- constants of include/hbt_b200.h -------------------------------------------
-ABI_VERSION = 1
+ABI_VERSION = 2
 MAX_CPUS = 512
 MAX_EVENTS = 64
 NUM_COUNTERS = 11
@@ -33,7 +33,14 @@ MODE_CONTEXT_SWITCH = H_LOST | H_COMM | H_EXIT | H_FORK | H_SWITCH_CPU_WIDE
 MODE_AUX_SPACE = H_AUX | H_ITRACE_START
 MODE_MIXED = MODE_CONTEXT_SWITCH | H_SAMPLE | H_READ
 SAMPLE_GROUP, SAMPLE_IP = 0, 1
-AGG_NONE, AGG_COUNT_DELTAS, AGG_IP_HISTOGRAM = 0, 1, 2
+AGG_NONE, AGG_COUNT_DELTAS, AGG_IP_HISTOGRAM, AGG_SWITCH_EVENTS = 0, 1, 2, 3
+# tagstack::Event::Type (Event.h:29-47) + the COMM pseudo-event of hbt_switch_event
+(SWEV_START, SWEV_END, SWEV_THREAD_CREATION, SWEV_THREAD_DESTRUCTION, SWEV_SWITCH_IN,
+ SWEV_SWITCH_OUT_PREEMPT, SWEV_SWITCH_OUT_YIELD, SWEV_WRITE_ERRORS_START,
+ SWEV_WRITE_ERRORS_END) = range(9)
+SWEV_COMM = 0x80
+TAG_NA = 0xFFFFFFFF
+LEVEL_INVALID = 0xFF
 DRAIN = 0xFFFFFFFF
 INVALID_TS = 0xFFFFFFFFFFFFFFFF
 
@@ -47,7 +54,8 @@ class DecodeDesc(C.Structure):
     _fields_ = [("handled_mask", C.c_uint32), ("sample_layout", C.c_uint32),
                 ("aggregate", C.c_uint32), ("n_events", C.c_uint32),
                 ("ip_sample_bytes", C.c_uint32), ("max_records", C.c_uint32),
-                ("tsc_transform_mask", C.c_uint64), ("tsc", TscParams)]
+                ("tsc_transform_mask", C.c_uint64), ("tsc", TscParams),
+                ("tid_level", C.c_uint32), ("reserved_", C.c_uint32)]
 
 
 class CpuResult(C.Structure):
@@ -69,6 +77,9 @@ HIST_DTYPE = np.dtype([("ip", "<u8"), ("pid", "<u4"), ("cpu", "<u4"), ("count", 
 RESULT_DTYPE = np.dtype([("ret", "<i8"), ("n_records", "<u8"), ("new_tail", "<u8"),
                          ("n_rows", "<u8"), ("counters", "<u8", (NUM_COUNTERS,)),
                          ("num_unknown_count_interval", "<u8"), ("carry_tstamp", "<u8")])
+SWITCH_EVENT_DTYPE = np.dtype([("tstamp", "<u8"), ("type", "u1"), ("level", "u1"),
+                               ("comp_unit_id", "<u2"), ("tag", "<u4")])
+assert SWITCH_EVENT_DTYPE.itemsize == 16
 assert HIST_DTYPE.itemsize == C.sizeof(HistEntry)
 assert RESULT_DTYPE.itemsize == C.sizeof(CpuResult)
 
@@ -96,6 +107,8 @@ EXPORTS = [
     ("hbt_decode_kernel_ms", C.c_float, [_P]),
     ("hbt_hist_fold_kernel_ms", C.c_float, [_P]),
     ("hbt_fetch_rows", C.c_int64, [_P, C.c_uint32, _P, C.c_uint64]),
+    ("hbt_fetch_switch_events", C.c_int64, [_P, C.c_uint32, _P, C.c_uint64]),
+    ("hbt_switch_events_dev", C.c_int, [_P, C.POINTER(_P), _U64P]),
     ("hbt_rows_slabs_dev", C.c_int, [_P, C.c_uint32, C.POINTER(_P), _U64P, C.POINTER(C.c_uint32)]),
     ("hbt_rows_max_slabs", C.c_uint32, [_P]),
     ("hbt_fetch_carry", C.c_int, [_P, C.c_uint32, _P, C.c_uint32]),
@@ -287,6 +300,19 @@ class Context:
         n = self._ck(self.lib.hbt_fetch_rows(self.h, cpu, _ptr(out), out.shape[0]))
         return out[:n]
 
+    def fetch_switch_events(self, cpu: int, n_events: int) -> np.ndarray:
+        """Events of the last AGG_SWITCH_EVENTS decode for `cpu` (SWITCH_EVENT_DTYPE)."""
+        out = np.zeros(max(1, n_events), dtype=SWITCH_EVENT_DTYPE)
+        m = self._ck(self.lib.hbt_fetch_switch_events(self.h, cpu, _ptr(out), out.shape[0]))
+        return out[:m]
+
+    def switch_events_dev(self):
+        """(device pointer, offsets[n_cpus + 1]) of all CPUs' events, back to back."""
+        base = C.c_void_p()
+        off = np.zeros(self.n_cpus + 1, dtype=np.uint64)
+        self._ck(self.lib.hbt_switch_events_dev(self.h, C.byref(base), off.ctypes.data_as(_U64P)))
+        return base.value or 0, off
+
     def fetch_carry(self, cpu: int, n_events: int) -> np.ndarray:
         out = np.zeros(n_events, dtype=np.uint64)
         self._ck(self.lib.hbt_fetch_carry(self.h, cpu, _ptr(out), n_events))
@@ -387,6 +413,19 @@ def ip_desc(ip_sample_bytes: int = 40, aggregate: int = AGG_IP_HISTOGRAM,
     d.ip_sample_bytes = ip_sample_bytes
     d.max_records = max_records
     d.tsc = TscParams(0, 1, 0, 0)
+    return d
+
+
+def switch_desc(tid_level: int = 0, max_records: int = DRAIN,
+                handled: int = MODE_CONTEXT_SWITCH) -> DecodeDesc:
+    """mode::ContextSwitch + CpuThreadSwitchGenerator's handlers -> tagstack::Event stream."""
+    d = DecodeDesc()
+    d.handled_mask = handled
+    d.sample_layout = SAMPLE_GROUP
+    d.aggregate = AGG_SWITCH_EVENTS
+    d.max_records = max_records
+    d.tsc.time_mult = 1
+    d.tid_level = tid_level
     return d
 
 

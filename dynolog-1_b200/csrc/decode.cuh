@@ -128,6 +128,7 @@ struct DecodeParams {
   const CpuState* state_in;
   hbt_decode_desc d;
   HistLists hist;
+  uint32_t cpu_base;  // SWITCH_EVENTS: comp_unit_id = cpu_base + cpu
 };
 
 // ---------------------------------------------------------------------------
@@ -175,6 +176,57 @@ __device__ __forceinline__ int counter_of(uint32_t type, uint32_t handled) {
     case REC_SWITCH_CPU_WIDE:
       return (handled & HBT_H_SWITCH_CPU_WIDE) ? HBT_CNT_SWITCH_CPU_WIDE : -1;
     default: return -1;
+  }
+}
+
+// ---- HBT_AGG_SWITCH_EVENTS ----------------------------------------------------------
+// Pass 1 (k_decode) writes one 16-byte "proto-event" per handled mode::ContextSwitch
+// record into the segment's row slab, in stream order: the tagstack::Event the record's
+// handler emits (PerCpuThreadSwitchGenerator.h:228-412) with the record's own timestamp.
+// What depends on the PREVIOUS record -- the WriteErrorsEnd in front of the first record
+// after a LOST (pendingRecordLost_, :441-453) and the WriteErrorsStart timestamp
+// last_tstamp_ + 1 (:243-245) -- is resolved by pass 2 (k_sw_count / k_sw_scan / k_sw_emit),
+// which is a prefix sum over "1 + previous is LOST".
+constexpr uint32_t kMiscSwitchOut = 1u << 13, kMiscSwitchOutPreempt = 1u << 14;
+
+// smallest well-formed size of a handled ContextSwitch record (CpuEventsGroup.h:105-184);
+// shorter ones are refused with -EPERM (the reference would read past the record)
+__device__ __forceinline__ uint32_t sw_min_size(uint32_t type) {
+  switch (type) {
+    case REC_LOST: return 40;
+    case REC_EXIT:
+    case REC_FORK: return 48;
+    default: return 32;  // COMM, SWITCH_CPU_WIDE
+  }
+}
+
+__device__ __forceinline__ uint64_t sw_word1(uint32_t type, uint32_t level, uint32_t cu, uint32_t tag) {
+  return (uint64_t)(type & 0xFF) | ((uint64_t)(level & 0xFF) << 8) | ((uint64_t)(cu & 0xFFFF) << 16) |
+         ((uint64_t)tag << 32);
+}
+
+// Proto-event of the handled record whose header is h; at(off) reads the record's word at
+// byte offset off.  cu = comp_unit_id.
+template <class At>
+__device__ __forceinline__ ulonglong2 sw_proto(uint64_t h, uint32_t level, uint32_t cu, At at) {
+  const uint32_t type = hdr_type(h), size = hdr_size(h);
+  switch (type) {
+    case REC_LOST:  // hdr id num_lost {pid tid tstamp}
+      return make_ulonglong2(at(32), sw_word1(HBT_SWEV_WRITE_ERRORS_START, HBT_LEVEL_INVALID, cu, HBT_TAG_NA));
+    case REC_COMM:  // hdr pid tid comm[] ... {pid tid tstamp}
+      return make_ulonglong2(at(size - 8), sw_word1(HBT_SWEV_COMM, level, cu, (uint32_t)(at(8) >> 32)));
+    case REC_EXIT:  // hdr pid ppid tid ptid time {..}
+      return make_ulonglong2(at(24), sw_word1(HBT_SWEV_THREAD_DESTRUCTION, level, cu, (uint32_t)at(16)));
+    case REC_FORK:
+      return make_ulonglong2(at(24), sw_word1(HBT_SWEV_THREAD_CREATION, level, cu, (uint32_t)at(16)));
+    default: {      // SWITCH_CPU_WIDE: hdr next_prev_pid next_prev_tid {pid tid tstamp}
+      const uint32_t misc = (uint32_t)(h >> 32) & 0xFFFF;
+      if (misc & kMiscSwitchOut)
+        return make_ulonglong2(at(24), sw_word1((misc & kMiscSwitchOutPreempt) ? HBT_SWEV_SWITCH_OUT_PREEMPT
+                                                                             : HBT_SWEV_SWITCH_OUT_YIELD,
+                                                level, cu, HBT_TAG_NA));
+      return make_ulonglong2(at(24), sw_word1(HBT_SWEV_SWITCH_IN, level, cu, (uint32_t)(at(16) >> 32)));
+    }
   }
 }
 
@@ -423,6 +475,22 @@ __device__ void consume_sequential(const DecodeParams& p, const RingDesc& ring,
       ++st.counters[HBT_CNT_READ];
     } else if (ci >= 0) {
       ++st.counters[ci];
+    }
+    if (AGG == HBT_AGG_SWITCH_EVENTS && ci >= 0) {
+      if (size < sw_min_size(type) || st.n_rows >= seg.rows_cap) {
+        // take the counter update back: the handler fails before consume() counts the record
+        if (type == REC_LOST) st.counters[HBT_CNT_LOST] -= ring_word_g(ring, pos + 16);
+        else --st.counters[ci];
+        st.err = size < sw_min_size(type) ? -1 : -28;  // -EPERM / -ENOSPC
+        st.err_pos = pos;
+        break;
+      }
+      const ulonglong2 e = sw_proto(h, d.tid_level, p.cpu_base + seg.cpu,
+                                    [&](uint32_t off) { return ring_word_g(ring, pos + off); });
+      uint64_t* row = seg.rows + (1 + st.n_rows) * 2;
+      row[0] = e.x;
+      row[1] = e.y;
+      ++st.n_rows;
     }
     ++st.n_rec;
     pos += size;
@@ -799,7 +867,13 @@ __global__ void __launch_bounds__(kThreads, AGG == HBT_AGG_IP_HISTOGRAM && kCach
               last_ev = ((pos + 1) << 2) | EV_LOST;
               if (first_ev == 0) first_ev = last_ev;
             }
-            if (counter_of(type, d.handled_mask) >= 0) omask |= bit;
+            if (counter_of(type, d.handled_mask) >= 0) {
+              if (AGG == HBT_AGG_SWITCH_EVENTS && size < sw_min_size(type)) {
+                bad = true;  // the sequential walk reports -EPERM
+                break;
+              }
+              omask |= bit;
+            }
           }
           mask |= bit;
           pos += size;
@@ -883,6 +957,17 @@ __global__ void __launch_bounds__(kThreads, AGG == HBT_AGG_IP_HISTOGRAM && kCach
         }
         if (lane == 31) sm.warp_rows[warp] = srow;
       }
+      if (AGG == HBT_AGG_SWITCH_EVENTS) {
+        // one proto-event per handled record: their index is a prefix sum over the threads
+        rows_j = __popc(omask);
+        srow = rows_j;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+          const uint32_t orow = __shfl_up_sync(0xffffffffu, srow, o);
+          if (lane >= o) srow += orow;
+        }
+        if (lane == 31) sm.warp_rows[warp] = srow;
+      }
       slow = __syncthreads_or(bad) != 0;  // B
       if (!slow || attempt == 1) break;
       // the stride prediction did not hold: guess again by scanning
@@ -894,7 +979,7 @@ __global__ void __launch_bounds__(kThreads, AGG == HBT_AGG_IP_HISTOGRAM && kCach
       // ---- phase 3: aggregate my records ----------------------------------------
       uint64_t row_i = 0;
       uint64_t in_ev = in_ev0;
-      if (AGG == HBT_AGG_COUNT_DELTAS) {
+      if (AGG == HBT_AGG_COUNT_DELTAS || AGG == HBT_AGG_SWITCH_EVENTS) {
         n_rows0 = st.n_rows;
         row_i = n_rows0 + (srow - rows_j);
         for (uint32_t w = 0; w < warp; ++w) row_i += sm.warp_rows[w];
@@ -935,6 +1020,12 @@ __global__ void __launch_bounds__(kThreads, AGG == HBT_AGG_IP_HISTOGRAM && kCach
           } else if (ci >= 0) {
             atomicAdd(&st.counters[ci], 1ull);
           }
+          if (AGG == HBT_AGG_SWITCH_EVENTS && ci >= 0) {
+            const ulonglong2 e = sw_proto(h, d.tid_level, p.cpu_base + seg.cpu,
+                                          [&](uint32_t off) { return tv.at(pos + off); });
+            *reinterpret_cast<ulonglong2*>(seg.rows + (1 + row_i) * 2) = e;
+            ++row_i;
+          }
         }
       }
       if (lost_sum) atomicAdd(&st.counters[HBT_CNT_LOST], lost_sum);
@@ -943,9 +1034,9 @@ __global__ void __launch_bounds__(kThreads, AGG == HBT_AGG_IP_HISTOGRAM && kCach
         if (pending_seam) st.first_ev = ev_make(t_begin + (first_ev >> 2) - 1, EV_SAMPLE);
       }
     }
-    if (AGG == HBT_AGG_COUNT_DELTAS && !ufp_done) {
+    if ((AGG == HBT_AGG_COUNT_DELTAS || AGG == HBT_AGG_SWITCH_EVENTS) && !ufp_done) {
       __syncthreads();  // row descriptors are complete; nobody reads st.n_rows any more
-      if (!stopped && !slow) {
+      if (AGG == HBT_AGG_COUNT_DELTAS && !stopped && !slow) {
         // ---- phase 3b: write the tile's rows, consecutive threads -> consecutive words
         uint32_t trows = 0;
         for (uint32_t w = 0; w < kThreads / 32; ++w) trows += sm.warp_rows[w];
@@ -998,6 +1089,11 @@ __global__ void __launch_bounds__(kThreads, AGG == HBT_AGG_IP_HISTOGRAM && kCach
             }
             if (tev) st.ev = ev_make(t_begin + (tev >> 2) - 1, tev & 3);
             if (tls) st.last_sample = t_begin + tls - 1;
+            st.n_rows += trows;
+          }
+          if (AGG == HBT_AGG_SWITCH_EVENTS) {
+            uint32_t trows = 0;
+            for (uint32_t w = 0; w < kThreads / 32; ++w) trows += sm.warp_rows[w];
             st.n_rows += trows;
           }
           st.stride = st.size_min == st.size_max ? st.size_min : 0;
@@ -1142,13 +1238,15 @@ __global__ void __launch_bounds__(64) k_finalize(const FinalizeParams p) {
                                   : xform(d, i, ring_word_g(ring, prev_pos + 40 + 8ull * i));
   };
 
+  // seam_valid: bit 0 = slot 0 of the slab holds a seam row, bit 1 = the segment's rows
+  // belong to this call's output (segments behind an error do not)
+  for (uint32_t s = 0; s < ring.n_seg; ++s) p.seam_valid[ring.seg_begin + s] = 0;
   for (uint32_t s = 0; s < ring.n_seg; ++s) {
     const uint32_t gi = ring.seg_begin + s;
     const SegResult& r = p.results[gi];
     const SegDesc& sd = p.segs[gi];
     const uint64_t seg_limit =
         p.seg_limit_tile ? min(sd.tile_end * p.seg_limit_tile, ring.head) : ring.head;
-    p.seam_valid[gi] = 0;
     if (pos >= seg_limit) {
       // the record chain jumps over this segment: nothing may start in it
       if (r.entry != kNone) {
@@ -1197,6 +1295,7 @@ __global__ void __launch_bounds__(64) k_finalize(const FinalizeParams p) {
         ++n_rows;
       }
     }
+    p.seam_valid[gi] |= 2;
     n_rec += r.n_records;
     n_rows += r.n_rows;
     unknown += r.n_unknown;
@@ -1444,6 +1543,156 @@ __global__ void __launch_bounds__(128)
         out[base + i] = h;
       }
     }
+    __syncthreads();
+  }
+}
+
+// ---------------------------------------------------------------------------
+// HBT_AGG_SWITCH_EVENTS, pass 2: proto-events -> tagstack::Event stream.
+// Event count of a proto = 1 + (the previous handled record of the CPU was a LOST).
+// k_sw_count: per segment, LOST protos that are not the slab's last (each one gives its
+//   successor a WriteErrorsEnd) and the slab's last proto.
+// k_sw_scan: one thread per CPU chains the segments from the generator state
+//   (last_tstamp_, in_write_errors_), gives every segment its output offset and the
+//   "previous record" of its first proto, then the CPUs' totals are prefix-summed.
+// k_sw_emit: per segment, block scan over 1 + prev_is_lost and the final events.
+// ---------------------------------------------------------------------------
+struct SwSeg {
+  uint64_t base;      // first event of the segment, relative to the CPU's first event
+  uint64_t prev_ts;   // tstamp of the handled record in front of the segment (last_tstamp_)
+  uint64_t last_ts;   // tstamp of the segment's last proto
+  uint32_t n;         // protos of the segment that belong to this call
+  uint32_t lost_inner;  // LOST protos among [0, n-1)
+  uint32_t prev_lost;   // the record in front of the segment was a LOST (in_write_errors_)
+  uint32_t last_lost;   // the segment's last proto is a LOST
+};
+
+struct SwParams {
+  const RingDesc* rings;
+  const SegDesc* segs;
+  const SegResult* results;
+  const uint8_t* seg_flags;  // k_finalize's seam_valid: bit 1 = segment belongs to the output
+  SwSeg* sw;
+  hbt_cpu_result* out;
+  uint64_t* state_ts;    // per CPU last_tstamp_
+  uint32_t* state_err;   // per CPU in_write_errors_
+  uint64_t* offsets;     // [n_cpus + 1] first event of each CPU
+  hbt_switch_event* events;
+  uint32_t n_cpus, n_segs, cpu_base;
+};
+
+__device__ __forceinline__ bool sw_is_lost(uint64_t w1) { return (uint32_t)(w1 & 0xFF) == HBT_SWEV_WRITE_ERRORS_START; }
+
+static __global__ void __launch_bounds__(256) k_sw_count(const SwParams p) {
+  const uint32_t gi = blockIdx.x;
+  const uint32_t n = (p.seg_flags[gi] & 2) ? (uint32_t)p.results[gi].n_rows : 0u;
+  const uint64_t* slab = p.segs[gi].rows + 2;  // slot 0 is the (unused) seam slot
+  uint32_t c = 0;
+  for (uint32_t i = threadIdx.x; i + 1 < n; i += blockDim.x) c += sw_is_lost(slab[2 * i + 1]);
+  c = __reduce_add_sync(0xffffffffu, c);
+  __shared__ uint32_t s_c;
+  if (threadIdx.x == 0) s_c = 0;
+  __syncthreads();
+  if ((threadIdx.x & 31) == 0 && c) atomicAdd(&s_c, c);
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    SwSeg& w = p.sw[gi];
+    w.n = n;
+    w.lost_inner = s_c;
+    w.last_ts = n ? slab[2 * (n - 1)] : 0;
+    w.last_lost = n ? sw_is_lost(slab[2 * (n - 1) + 1]) : 0;
+  }
+}
+
+// launched as one CTA of >= n_cpus threads (n_cpus <= HBT_MAX_CPUS = 512)
+static __global__ void __launch_bounds__(512) k_sw_scan(const SwParams p) {
+  const uint32_t c = threadIdx.x;
+  uint64_t total = 0;
+  if (c < p.n_cpus) {
+    const RingDesc ring = p.rings[c];
+    uint64_t prev_ts = p.state_ts[c];
+    uint32_t prev_lost = p.state_err[c];
+    for (uint32_t s = 0; s < ring.n_seg; ++s) {
+      SwSeg& w = p.sw[ring.seg_begin + s];
+      w.base = total;
+      w.prev_ts = prev_ts;
+      w.prev_lost = prev_lost;
+      if (w.n) {
+        total += w.n + w.lost_inner + prev_lost;
+        prev_ts = w.last_ts;
+        prev_lost = w.last_lost;
+      }
+    }
+    p.state_ts[c] = prev_ts;
+    p.state_err[c] = prev_lost;
+    hbt_cpu_result& o = p.out[c];
+    o.n_rows = total;
+    o.carry_tstamp = prev_ts;                 // last_tstamp_
+    o.num_unknown_count_interval = prev_lost; // in_write_errors_
+  }
+  // exclusive prefix sum of the totals over the CPUs
+  __shared__ uint64_t s_tot[512];
+  s_tot[threadIdx.x] = total;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    uint64_t run = 0;
+    for (uint32_t i = 0; i < p.n_cpus; ++i) {
+      p.offsets[i] = run;
+      run += s_tot[i];
+    }
+    p.offsets[p.n_cpus] = run;
+  }
+}
+
+static __global__ void __launch_bounds__(256) k_sw_emit(const SwParams p) {
+  const uint32_t gi = blockIdx.x;
+  const SwSeg w = p.sw[gi];
+  if (w.n == 0) return;
+  const SegDesc sd = p.segs[gi];
+  const ulonglong2* slab = reinterpret_cast<const ulonglong2*>(sd.rows + 2);
+  ulonglong2* out = reinterpret_cast<ulonglong2*>(p.events) + p.offsets[sd.cpu] + w.base;
+  const uint64_t end_w1 = sw_word1(HBT_SWEV_WRITE_ERRORS_END, HBT_LEVEL_INVALID, p.cpu_base + sd.cpu, HBT_TAG_NA);
+  __shared__ uint32_t s_warp[8];
+  __shared__ uint64_t s_run;
+  const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  if (tid == 0) s_run = 0;
+  __syncthreads();
+  for (uint32_t i0 = 0; i0 < w.n; i0 += 256) {
+    const uint32_t i = i0 + tid;
+    const bool in = i < w.n;
+    ulonglong2 e = make_ulonglong2(0, 0);
+    uint64_t prev_ts = 0;
+    uint32_t prev_lost = 0;
+    if (in) {
+      e = slab[i];
+      if (i == 0) {
+        prev_ts = w.prev_ts;
+        prev_lost = w.prev_lost;
+      } else {
+        const ulonglong2 pe = slab[i - 1];
+        prev_ts = pe.x;
+        prev_lost = sw_is_lost(pe.y);
+      }
+    }
+    const uint32_t cnt = in ? 1u + prev_lost : 0u;
+    uint32_t inc = cnt;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const uint32_t v = __shfl_up_sync(0xffffffffu, inc, o);
+      if (lane >= o) inc += v;
+    }
+    if (lane == 31) s_warp[warp] = inc;
+    __syncthreads();
+    uint32_t before = inc - cnt;
+    for (uint32_t k = 0; k < warp; ++k) before += s_warp[k];
+    uint64_t pos = s_run + before;
+    if (in) {
+      if (prev_lost) out[pos++] = make_ulonglong2(e.x, end_w1);       // pendingRecordLost_: End(tstamp)
+      if (sw_is_lost(e.y)) e.x = (prev_lost ? e.x : prev_ts) + 1;    // Start(last_tstamp_ + 1)
+      out[pos] = e;
+    }
+    __syncthreads();
+    if (tid == 255) s_run += before + cnt;  // thread 255 holds the chunk's total
     __syncthreads();
   }
 }

@@ -112,7 +112,7 @@ struct hbt_ctx {
   PinBuf<uint32_t> h_flags;
   uint32_t n_segs = 0;
   bool tiled = true;
-  bool attr_set[3] = {false, false, false};
+  bool attr_set[4] = {false, false, false, false};
   bool pending = false;  // a decode was launched and not yet fetched
   bool have_results = false;
   hbt_decode_desc desc{};
@@ -120,6 +120,15 @@ struct hbt_ctx {
   cudaEvent_t ev_k0 = nullptr, ev_k1 = nullptr;  // around the decode kernel
   cudaEvent_t ev_f0 = nullptr, ev_f1 = nullptr;  // around the histogram fold kernel
   bool fold_timed = false;
+
+  // HBT_AGG_SWITCH_EVENTS: generator state (last_tstamp_, in_write_errors_), pass-2 scratch, events
+  DevBuf<uint64_t> sw_state_ts;
+  DevBuf<uint32_t> sw_state_err;
+  DevBuf<SwSeg> d_sw;
+  DevBuf<uint64_t> d_sw_off;
+  PinBuf<uint64_t> h_sw_off;
+  DevBuf<hbt_switch_event> sw_events;
+  bool sw_valid = false;  // sw_events / h_sw_off describe the last fetched decode
 
   // histogram: per-(cpu,bucket) lists (see HistLists)
   DevBuf<ulonglong2> hist_entries;
@@ -175,7 +184,12 @@ size_t decode_smem_bytes(int agg) {
 int validate_desc(hbt_ctx* ctx, const hbt_decode_desc* d) {
   if (!d) return fail(ctx, -EINVAL, "desc is NULL");
   if (d->sample_layout > HBT_SAMPLE_IP) return fail(ctx, -EINVAL, "bad sample_layout");
-  if (d->aggregate > HBT_AGG_IP_HISTOGRAM) return fail(ctx, -EINVAL, "bad aggregate");
+  if (d->aggregate > HBT_AGG_SWITCH_EVENTS) return fail(ctx, -EINVAL, "bad aggregate");
+  if (d->aggregate == HBT_AGG_SWITCH_EVENTS) {
+    if (d->handled_mask == 0 || (d->handled_mask & ~(uint32_t)HBT_MODE_CONTEXT_SWITCH))
+      return fail(ctx, -EINVAL, "SWITCH_EVENTS handles mode::ContextSwitch records only");
+    if (d->tid_level > 0xFF) return fail(ctx, -EINVAL, "tid_level %u", d->tid_level);
+  }
   if (d->aggregate == HBT_AGG_COUNT_DELTAS) {
     if (d->sample_layout != HBT_SAMPLE_GROUP || !(d->handled_mask & HBT_H_SAMPLE))
       return fail(ctx, -EINVAL, "COUNT_DELTAS needs handled group SAMPLE records");
@@ -229,6 +243,8 @@ int build_tables(hbt_ctx* ctx, const uint64_t* clamp_head, const int64_t* clamp_
   segs.reserve((size_t)C * 4);
   const uint64_t row_words = 2 + (uint64_t)d.n_events;
   uint64_t rows_total_words = 0;
+  const bool sw = d.aggregate == HBT_AGG_SWITCH_EVENTS;  // 16-byte proto-events in the row slabs
+  const bool with_rows = sw || d.aggregate == HBT_AGG_COUNT_DELTAS;
   // first pass: segment geometry and row slab sizes
   for (uint32_t c = 0; c < C; ++c) {
     const Window& w = ctx->win[c];
@@ -254,7 +270,7 @@ int build_tables(hbt_ctx* ctx, const uint64_t* clamp_head, const int64_t* clamp_
       s.tile_begin = 0;
       s.tile_end = 0;
       s.forced_entry = kNone;
-      s.rows_cap = (r.head - r.tail) / (40 + 8ull * d.n_events) + 2;
+      s.rows_cap = (r.head - r.tail) / (sw ? 32 : 40 + 8ull * d.n_events) + 2;
       segs.push_back(s);
       r.n_seg = 1;
     } else {
@@ -275,19 +291,20 @@ int build_tables(hbt_ctx* ctx, const uint64_t* clamp_head, const int64_t* clamp_
         s.tile_begin = tb;
         s.tile_end = tb + per < t1 ? tb + per : t1;
         s.forced_entry = kNone;
-        s.rows_cap = ((s.tile_end - s.tile_begin) * kTile) / (40 + 8ull * d.n_events) + 2;
+        // rows per segment: a SAMPLE is at least 40 + 8n bytes, a handled ContextSwitch record 32
+        s.rows_cap = ((s.tile_end - s.tile_begin) * kTile) / (sw ? 32 : 40 + 8ull * d.n_events) + 2;
         segs.push_back(s);
       }
       r.n_seg = k;
     }
-    if (d.aggregate == HBT_AGG_COUNT_DELTAS)
+    if (with_rows)
       for (uint32_t k = 0; k < r.n_seg; ++k)
         rows_total_words += (1 + segs[r.seg_begin + k].rows_cap) * row_words;
   }
   if (keep_forced && keep_forced->size() == segs.size())
     for (size_t i = 0; i < segs.size(); ++i) segs[i].forced_entry = (*keep_forced)[i].forced_entry;
 
-  if (d.aggregate == HBT_AGG_COUNT_DELTAS) {
+  if (with_rows) {
     CU(ctx->d_rows.reserve(rows_total_words ? rows_total_words : 1));
     uint64_t off = 0;
     for (uint32_t c = 0; c < C; ++c) {
@@ -350,6 +367,7 @@ int launch_decode_agg(hbt_ctx* ctx) {
   p.hist.buckets = ctx->hist_buckets;
   p.hist.cap = ctx->hist_cap;
   p.hist.overflow = ctx->hist_overflow.p;
+  p.cpu_base = ctx->cpu_base;
   if (ctx->n_segs == 0) return 0;
   if (ctx->tiled) {
     const size_t smem = decode_smem_bytes(AGG);
@@ -373,6 +391,7 @@ int launch_decode(hbt_ctx* ctx) {
   switch (ctx->desc.aggregate) {
     case HBT_AGG_NONE: return launch_decode_agg<HBT_AGG_NONE>(ctx);
     case HBT_AGG_COUNT_DELTAS: return launch_decode_agg<HBT_AGG_COUNT_DELTAS>(ctx);
+    case HBT_AGG_SWITCH_EVENTS: return launch_decode_agg<HBT_AGG_SWITCH_EVENTS>(ctx);
     default: return launch_decode_agg<HBT_AGG_IP_HISTOGRAM>(ctx);
   }
 }
@@ -544,6 +563,12 @@ void hbt_destroy(hbt_ctx* ctx) {
   ctx->h_clamp_head.release();
   ctx->h_clamp_ret.release();
   ctx->h_flags.release();
+  ctx->sw_state_ts.release();
+  ctx->sw_state_err.release();
+  ctx->d_sw.release();
+  ctx->d_sw_off.release();
+  ctx->h_sw_off.release();
+  ctx->sw_events.release();
   ctx->hist_entries.release();
   ctx->hist_cursors.release();
   ctx->hist_cursors_snap.release();
@@ -596,8 +621,13 @@ int hbt_ring_reset_state(hbt_ctx* ctx, uint64_t seed_tstamp) {
                                                                seed_tstamp);
   ++ctx->launches;
   CU(cudaGetLastError());
+  // CpuThreadSwitchGenerator starts with last_tstamp_ = numeric_limits<TimeStamp>::min() and
+  // in_write_errors_ = false (PerCpuThreadSwitchGenerator.h:437-438)
+  CU(cudaMemsetAsync(ctx->sw_state_ts.p, 0, ctx->n_cpus * sizeof(uint64_t), ctx->stream));
+  CU(cudaMemsetAsync(ctx->sw_state_err.p, 0, ctx->n_cpus * sizeof(uint32_t), ctx->stream));
   for (auto& w : ctx->win) w.active = false;
   ctx->have_results = false;
+  ctx->sw_valid = false;
   return 0;
 }
 
@@ -608,6 +638,10 @@ static int configure_common(hbt_ctx* ctx, uint32_t n_cpus) {
   CU(ctx->state[1].reserve(n_cpus));
   CU(ctx->d_out.reserve(n_cpus));
   CU(ctx->h_out.reserve(n_cpus));
+  CU(ctx->sw_state_ts.reserve(n_cpus));
+  CU(ctx->sw_state_err.reserve(n_cpus));
+  CU(ctx->d_sw_off.reserve(n_cpus + 1));
+  CU(ctx->h_sw_off.reserve(n_cpus + 1));
   CU(ctx->d_clamp_head.reserve(n_cpus));
   CU(ctx->d_clamp_ret.reserve(n_cpus));
   CU(ctx->d_locate_from.reserve(n_cpus));
@@ -784,6 +818,33 @@ static int complete_decode(hbt_ctx* ctx) {
     if (int rc = hist_fold(ctx)) return rc;
   }
   ctx->cur ^= 1;
+  ctx->sw_valid = false;
+  SwParams sp{};
+  if (ctx->desc.aggregate == HBT_AGG_SWITCH_EVENTS) {
+    // pass 2 of the event stream: counts and offsets now, the events once their number is known
+    CU(ctx->d_sw.reserve(ctx->n_segs ? ctx->n_segs : 1));
+    sp.rings = ctx->d_rings.p;
+    sp.segs = ctx->d_segs.p;
+    sp.results = ctx->d_results.p;
+    sp.seg_flags = ctx->d_seam.p;
+    sp.sw = ctx->d_sw.p;
+    sp.out = ctx->d_out.p;
+    sp.state_ts = ctx->sw_state_ts.p;
+    sp.state_err = ctx->sw_state_err.p;
+    sp.offsets = ctx->d_sw_off.p;
+    sp.n_cpus = C;
+    sp.n_segs = ctx->n_segs;
+    sp.cpu_base = ctx->cpu_base;
+    if (ctx->n_segs) {
+      k_sw_count<<<ctx->n_segs, 256, 0, ctx->stream>>>(sp);
+      ++ctx->launches;
+    }
+    k_sw_scan<<<1, 512, 0, ctx->stream>>>(sp);
+    ++ctx->launches;
+    CU(cudaGetLastError());
+    CU(cudaMemcpyAsync(ctx->h_sw_off.p, ctx->d_sw_off.p, (C + 1) * sizeof(uint64_t),
+                       cudaMemcpyDeviceToHost, ctx->stream));
+  }
   ctx->h_flags.p[4] = 0;
   if (ctx->desc.aggregate == HBT_AGG_IP_HISTOGRAM)
     CU(cudaMemcpyAsync(ctx->h_flags.p + 4, ctx->hist_overflow.p, sizeof(uint32_t),
@@ -801,6 +862,17 @@ static int complete_decode(hbt_ctx* ctx) {
   for (uint32_t c = 0; c < C; ++c) {
     Window& w = ctx->win[c];
     if (w.active) w.tail = ctx->h_out.p[c].new_tail;
+  }
+  if (ctx->desc.aggregate == HBT_AGG_SWITCH_EVENTS) {
+    const uint64_t total = ctx->h_sw_off.p[C];
+    CU(ctx->sw_events.reserve(total ? total : 1));
+    sp.events = ctx->sw_events.p;
+    if (ctx->n_segs && total) {
+      k_sw_emit<<<ctx->n_segs, 256, 0, ctx->stream>>>(sp);
+      ++ctx->launches;
+      CU(cudaGetLastError());
+    }
+    ctx->sw_valid = true;
   }
   ctx->pending = false;
   ctx->have_results = true;
@@ -870,7 +942,7 @@ int hbt_rows_slabs_dev(hbt_ctx* ctx, uint32_t cpu, const uint64_t** ptr, uint64_
   for (uint32_t s = 0; s < r.n_seg && remaining; ++s) {
     const uint32_t gi = r.seg_begin + s;
     const SegDesc& sd = ctx->h_segs.p[gi];
-    if (ctx->h_seam.p[gi]) {
+    if (ctx->h_seam.p[gi] & 1) {
       ptr[k] = sd.rows;
       n_rows[k] = 1;
       ++k;
@@ -908,6 +980,28 @@ int64_t hbt_fetch_rows(hbt_ctx* ctx, uint32_t cpu, uint64_t* rows, uint64_t cap_
   }
   CU(cudaStreamSynchronize(ctx->stream));
   return (int64_t)off;
+}
+
+int64_t hbt_fetch_switch_events(hbt_ctx* ctx, uint32_t cpu, hbt_switch_event* out, uint64_t cap) {
+  if (!ctx || cpu >= ctx->n_cpus || !out) return -EINVAL;
+  if (int rc = complete_decode(ctx)) return rc;
+  if (!ctx->sw_valid) return fail(ctx, -EINVAL, "no SWITCH_EVENTS decode to read");
+  const uint64_t b = ctx->h_sw_off.p[cpu], n = ctx->h_sw_off.p[cpu + 1] - b;
+  if (n > cap) return fail(ctx, -ENOSPC, "cap %llu < %llu events", (unsigned long long)cap,
+                           (unsigned long long)n);
+  if (n) CU(cudaMemcpyAsync(out, ctx->sw_events.p + b, n * sizeof(hbt_switch_event),
+                            cudaMemcpyDeviceToHost, ctx->stream));
+  CU(cudaStreamSynchronize(ctx->stream));
+  return (int64_t)n;
+}
+
+int hbt_switch_events_dev(hbt_ctx* ctx, const hbt_switch_event** events, uint64_t* offsets) {
+  if (!ctx || !events || !offsets) return -EINVAL;
+  if (int rc = complete_decode(ctx)) return rc;
+  if (!ctx->sw_valid) return fail(ctx, -EINVAL, "no SWITCH_EVENTS decode to read");
+  *events = ctx->sw_events.p;
+  memcpy(offsets, ctx->h_sw_off.p, (ctx->n_cpus + 1) * sizeof(uint64_t));
+  return 0;
 }
 
 int hbt_fetch_carry(hbt_ctx* ctx, uint32_t cpu, uint64_t* last, uint32_t n_events) {

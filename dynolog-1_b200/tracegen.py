@@ -237,6 +237,109 @@ def mixed_stream(seed: int, n_records: int, n_events: int, device="cpu", mix=MIX
     return out
 
 
+MISC_SWITCH_OUT = 1 << 13          # PERF_RECORD_MISC_SWITCH_OUT
+MISC_SWITCH_OUT_PREEMPT = 1 << 14  # PERF_RECORD_MISC_SWITCH_OUT_PREEMPT
+
+CTX_MIX = (("switch", 0.86), ("comm", 0.04), ("fork", 0.04), ("exit", 0.04), ("lost", 0.02))
+
+
+def ctx_switch_stream(seed: int, n_records: int, device="cpu", mix=CTX_MIX, t0: int = 1_000_000,
+                      n_tids: int = 512) -> torch.Tensor:
+    """A mode::ContextSwitch stream (what CpuThreadSwitchGenerator's sw_dummy event
+    produces, CpuEventsGroup.h:105-184): SWITCH_CPU_WIDE in / out-yield / out-preempt,
+    COMM (8 or 16 byte names), FORK, EXIT and LOST records with {pid,tid,time} sample_id
+    trailers and increasing timestamps.  Vectorised; thread lifetimes are NOT consistent
+    (a tid may fork twice), which the GPU path and the C oracle do not care about -- use
+    ctx_switch_stream_consistent for streams the reference's own handlers accept."""
+    n = n_records
+    u = rand_uniform(seed, n, device, 41)
+    kinds = [k for k, _ in mix]
+    edges = torch.tensor([p for _, p in mix], dtype=torch.float64, device=device).cumsum(0)
+    edges = edges / edges[-1]
+    kind = torch.searchsorted(edges, u).clamp_(max=len(kinds) - 1)
+    name_w = 1 + rand_below(seed, n, 2, device, 42)
+    base_w = {"switch": 4, "lost": 5, "fork": 6, "exit": 6}
+    types = {"switch": REC_SWITCH_CPU_WIDE, "comm": REC_COMM, "lost": REC_LOST, "fork": REC_FORK,
+             "exit": REC_EXIT}
+    words = torch.zeros(n, dtype=torch.int64, device=device)
+    rtype = torch.zeros(n, dtype=torch.int64, device=device)
+    for i, k in enumerate(kinds):
+        sel = kind == i
+        w = 2 + name_w + 2 if k == "comm" else torch.full_like(words, base_w[k])
+        words = torch.where(sel, w, words)
+        rtype = torch.where(sel, torch.full_like(rtype, types[k]), rtype)
+    off = torch.cumsum(words, 0) - words
+    total = int(words.sum().item())
+    out = rand_u64(seed, total, device, 43) & _s64(0x0000FFFFFFFFFFFF)
+    dt = 1000 + rand_below(seed, n, 9000, device, 44)
+    ts = t0 + torch.cumsum(dt, 0)
+    tid = rand_below(seed, n, n_tids, device, 45)            # tid 0 (the idle task) occurs too
+    pid = tid - (tid % 4)
+    pidtid = pid | (tid << 32)
+    # SWITCH misc: in / out-yield / out-preempt
+    sw = rand_below(seed, n, 3, device, 46)
+    misc = torch.where(sw == 0, torch.zeros_like(sw),
+                       torch.where(sw == 1, torch.full_like(sw, MISC_SWITCH_OUT),
+                                   torch.full_like(sw, MISC_SWITCH_OUT | MISC_SWITCH_OUT_PREEMPT)))
+    misc = torch.where(rtype == REC_SWITCH_CPU_WIDE, misc, torch.zeros_like(misc))
+    out[off] = rtype | (misc << 32) | (words << 51)
+    out[off + words - 2] = pidtid      # sample_id {pid, tid}
+    out[off + words - 1] = ts          # sample_id.time
+    out[off + 1] = pidtid              # switch: next_prev ; comm: pid,tid ; lost: id
+    fe = (rtype == REC_FORK) | (rtype == REC_EXIT)
+    o = off[fe]
+    if o.numel():                      # Exit/Fork: pid ppid | tid ptid | time
+        out[o + 1] = pid[fe] | ((pid[fe] + 1) << 32)
+        out[o + 2] = tid[fe] | ((tid[fe] + 1) << 32)
+        out[o + 3] = ts[fe]
+    lo = off[rtype == REC_LOST]
+    if lo.numel():
+        out[lo + 1] = 7
+        out[lo + 2] = 1 + rand_below(seed, lo.numel(), 100, device, 47)
+    return out
+
+
+def ctx_switch_stream_consistent(seed: int, n_records: int, t0: int = 1_000_000, lost_every: int = 0,
+                                 first_tid: int = 1000) -> torch.Tensor:
+    """Small context-switch stream with consistent thread lifetimes, as the reference's
+    handlers require (they assert on a second FORK of a live thread or an EXIT before the
+    FORK): tids are forked once, switch in and out, get renamed, and exit once.  Pure
+    Python; for the reference-pinning tests."""
+    import random
+    rng = random.Random(seed)
+    live, next_tid, ts = [], first_tid, t0
+    words = []
+
+    def hdr(rtype, n_words, misc=0):
+        return rtype | (misc << 32) | ((8 * n_words) << 48)
+
+    for i in range(n_records):
+        ts += rng.randint(1000, 10000)
+        r = rng.random()
+        if lost_every and i % lost_every == lost_every - 1:
+            words += [hdr(REC_LOST, 5), 7, rng.randint(1, 100), 4 | (4 << 32), ts]
+        elif r < 0.12 or not live:
+            tid = next_tid
+            next_tid += 1
+            live.append(tid)
+            words += [hdr(REC_FORK, 6), (tid - tid % 4) | (1 << 32), tid | (1 << 32), ts,
+                      1 | (1 << 32), ts]
+        elif r < 0.20 and len(live) > 2:
+            tid = live.pop(rng.randrange(len(live)))
+            words += [hdr(REC_EXIT, 6), (tid - tid % 4) | (1 << 32), tid | (1 << 32), ts,
+                      (tid - tid % 4) | (tid << 32), ts]
+        elif r < 0.28:
+            tid = rng.choice(live)
+            nw = rng.randint(1, 2)
+            words += [hdr(REC_COMM, 2 + nw + 2), (tid - tid % 4) | (tid << 32)] + \
+                [0x0000616161616161] * nw + [(tid - tid % 4) | (tid << 32), ts]
+        else:
+            tid = rng.choice(live + [0])
+            misc = rng.choice([0, MISC_SWITCH_OUT, MISC_SWITCH_OUT | MISC_SWITCH_OUT_PREEMPT])
+            words += [hdr(REC_SWITCH_CPU_WIDE, 4, misc), 5 | (6 << 32), (tid - tid % 4) | (tid << 32), ts]
+    return torch.tensor([_s64(w) for w in words], dtype=torch.int64)
+
+
 # ---------------------------------------------------------------------------
 # Ring placement
 # ---------------------------------------------------------------------------

@@ -34,7 +34,7 @@
 extern "C" {
 #endif
 
-#define HBT_B200_ABI_VERSION 1
+#define HBT_B200_ABI_VERSION 2
 
 /* Limits taken from the reference: kMaxCpus (hbt/src/common/System.h:195),
  * CpuCountSampleGenerator::kMaxNumEvents (PerCpuCountSampleGenerator.h:44). */
@@ -108,8 +108,42 @@ enum {
    * (PerCpuCountSampleGenerator.h:110-202): rows {tstamp,duration,deltas[n]}. */
   HBT_AGG_COUNT_DELTAS = 1,
   /* (cpu,pid,ip) -> count table; needs HBT_SAMPLE_IP. */
-  HBT_AGG_IP_HISTOGRAM = 2
+  HBT_AGG_IP_HISTOGRAM = 2,
+  /* CpuThreadSwitchGenerator's handlers (PerCpuThreadSwitchGenerator.h:228-412):
+   * LOST / COMM / EXIT / FORK / SWITCH_CPU_WIDE records -> tagstack::Event stream
+   * (hbt_switch_event).  handled_mask must be a subset of HBT_MODE_CONTEXT_SWITCH. */
+  HBT_AGG_SWITCH_EVENTS = 3
 };
+
+/* tagstack::Event (hbt/src/tagstack/Event.h:28-227), same 16-byte layout.
+ * Difference to the reference, by design: `tag` of ThreadCreation / ThreadDestruction
+ * / SwitchIn events is the record's raw tid, not the virtual id PerThreadStats
+ * hands out (that map is sequential host state shared by all CPUs; the host side
+ * applies it: hbt_gpu::perf_event::ThreadSwitchVidMapper).  So that the host can do
+ * this, COMM records -- which change that map but emit no reference Event -- appear
+ * as pseudo-events of type HBT_SWEV_COMM (tag = tid), to be dropped after mapping. */
+typedef struct hbt_switch_event {
+  uint64_t tstamp;
+  uint8_t type;          /* HBT_SWEV_* */
+  uint8_t level;         /* desc->tid_level, or HBT_LEVEL_INVALID for WriteErrors* */
+  uint16_t comp_unit_id; /* cpu_base + ctx-local cpu index */
+  uint32_t tag;          /* tid, or HBT_TAG_NA */
+} hbt_switch_event;
+
+enum { /* Event::Type, Event.h:29-47 */
+  HBT_SWEV_START = 0,
+  HBT_SWEV_END = 1,
+  HBT_SWEV_THREAD_CREATION = 2,
+  HBT_SWEV_THREAD_DESTRUCTION = 3,
+  HBT_SWEV_SWITCH_IN = 4,
+  HBT_SWEV_SWITCH_OUT_PREEMPT = 5,
+  HBT_SWEV_SWITCH_OUT_YIELD = 6,
+  HBT_SWEV_WRITE_ERRORS_START = 7,
+  HBT_SWEV_WRITE_ERRORS_END = 8,
+  HBT_SWEV_COMM = 0x80 /* not a reference Event: see above */
+};
+#define HBT_TAG_NA 0xFFFFFFFFu    /* tagstack::kNA, TagStack.h:21 */
+#define HBT_LEVEL_INVALID 0xFFu   /* tagstack::kInvalidLevel, TagStack.h:26 */
 
 /* TSC -> kernel time parameters, TscConversionParams (System.h:175-179) and
  * CpuEventsGroup::kernelTimeFromTsc (CpuEventsGroup.h:1577-1591). */
@@ -131,7 +165,13 @@ typedef struct hbt_decode_desc {
    * (PmuEvent.h:218-226, PerCpuCountSampleGenerator.h:171-173) */
   uint64_t tsc_transform_mask;
   hbt_tsc_params tsc;
+  uint32_t tid_level;       /* HBT_AGG_SWITCH_EVENTS: tagstack level of thread tags (ctor arg tid_level) */
+  uint32_t reserved_;       /* 0 */
 } hbt_decode_desc;
+#ifdef __cplusplus
+static_assert(sizeof(hbt_decode_desc) == 56, "ABI 2 layout");
+static_assert(sizeof(hbt_switch_event) == 16, "tagstack::Event layout");
+#endif
 
 /* Result of one decode call for one CPU: what consume() returned plus the
  * object state it mutated.  counters[] and num_unknown_count_interval are the
@@ -142,10 +182,13 @@ typedef struct hbt_cpu_result {
                         (header.size < 8: the reference would never return) */
   uint64_t n_records;/* records consumed by this call (also when ret < 0) */
   uint64_t new_tail; /* value consume() wrote to data_tail (CpuEventsGroup.h:1520) */
-  uint64_t n_rows;   /* HBT_AGG_COUNT_DELTAS: rows emitted by this call */
+  uint64_t n_rows;   /* HBT_AGG_COUNT_DELTAS: rows emitted by this call;
+                        HBT_AGG_SWITCH_EVENTS: events emitted by this call */
   uint64_t counters[HBT_NUM_COUNTERS];
-  uint64_t num_unknown_count_interval; /* PerCpuCountSampleGenerator.h:152,230 */
-  uint64_t carry_tstamp; /* count_.tstamp after the call (UINT64_MAX = invalid) */
+  uint64_t num_unknown_count_interval; /* PerCpuCountSampleGenerator.h:152,230;
+                        HBT_AGG_SWITCH_EVENTS: in_write_errors_ (0/1) after the call */
+  uint64_t carry_tstamp; /* count_.tstamp after the call (UINT64_MAX = invalid);
+                        HBT_AGG_SWITCH_EVENTS: last_tstamp_ (PerCpuThreadSwitchGenerator.h:437) */
 } hbt_cpu_result;
 
 /* One entry of the (cpu,pid,ip) table. */
@@ -255,6 +298,15 @@ float hbt_hist_fold_kernel_ms(hbt_ctx* ctx);
  * (PerCpuCountSampleGenerator.h:69,182).  Returns the number of rows copied,
  * -ENOSPC if cap_rows is too small. */
 int64_t hbt_fetch_rows(hbt_ctx* ctx, uint32_t cpu, uint64_t* rows, uint64_t cap_rows);
+
+/* Events of the last HBT_AGG_SWITCH_EVENTS decode for `cpu`, in the order
+ * CpuThreadSwitchGenerator writes them to its output ring
+ * (PerCpuThreadSwitchGenerator.h:228-412; kWriteByteSize = sizeof(Event), :186).
+ * Returns the number copied, -ENOSPC if cap is too small. */
+int64_t hbt_fetch_switch_events(hbt_ctx* ctx, uint32_t cpu, hbt_switch_event* out, uint64_t cap);
+/* Device view: all CPUs' events back to back, CPU c at [offsets[c], offsets[c+1])
+ * (offsets: host array of n_cpus + 1 entries, filled by the call). */
+int hbt_switch_events_dev(hbt_ctx* ctx, const hbt_switch_event** events, uint64_t* offsets);
 
 /* Device view of the same rows for downstream kernels: rows of `cpu` live in
  * *n_slabs slabs; slab i has n_rows[i] rows at ptr[i].  Arrays must hold

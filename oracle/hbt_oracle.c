@@ -164,9 +164,39 @@ static inline uint64_t ring_word(const uint8_t* ring, uint64_t mask, uint64_t po
  * res->counters and res->num_unknown_count_interval are in/out running totals.
  * rows may be NULL unless COUNT_DELTAS; a full rows buffer behaves like the
  * reference's full output ring without drop-if-full (-ENOSPC, :191-194). */
-int hbt_oracle_consume(const uint8_t* ring, uint64_t data_size, uint64_t tail, uint64_t head,
-                       const hbt_decode_desc* d, hbt_oracle_carry* carry, uint64_t* rows,
-                       uint64_t rows_cap, hbt_oracle_hist* hist, hbt_cpu_result* res) {
+/* PERF_RECORD_MISC_SWITCH_OUT / _PREEMPT, /usr/include/linux/perf_event.h:779-790 */
+#define MISC_SWITCH_OUT (1u << 13)
+#define MISC_SWITCH_OUT_PREEMPT (1u << 14)
+
+/* One tagstack::Event (Event.h:28-60) as two words of the rows buffer. */
+static int sw_write(uint64_t* rows, uint64_t rows_cap, uint64_t* n_rows, uint64_t tstamp,
+                    uint32_t type, uint32_t level, uint32_t cu, uint32_t tag) {
+  if (*n_rows >= rows_cap) return -ENOSPC; /* output_producer_.write fails */
+  rows[2 * *n_rows] = tstamp;
+  rows[2 * *n_rows + 1] = (uint64_t)(type & 0xFF) | ((uint64_t)(level & 0xFF) << 8) |
+                          ((uint64_t)(cu & 0xFFFF) << 16) | ((uint64_t)tag << 32);
+  ++*n_rows;
+  return 0;
+}
+
+/* CpuThreadSwitchGenerator::pendingRecordLost_, PerCpuThreadSwitchGenerator.h:441-453.
+ * carry->tstamp = last_tstamp_, carry->last[0] = in_write_errors_. */
+static int sw_pending(hbt_oracle_carry* carry, uint64_t* rows, uint64_t rows_cap, uint64_t* n_rows,
+                      uint64_t tstamp, uint32_t cu) {
+  if (!carry->last[0]) return 0;
+  int ret = sw_write(rows, rows_cap, n_rows, tstamp, HBT_SWEV_WRITE_ERRORS_END, HBT_LEVEL_INVALID, cu,
+                     HBT_TAG_NA);
+  if (ret >= 0) {
+    carry->tstamp = tstamp;
+    carry->last[0] = 0;
+  }
+  return ret;
+}
+
+static int consume_core(const uint8_t* ring, uint64_t data_size, uint64_t tail, uint64_t head,
+                        const hbt_decode_desc* d, hbt_oracle_carry* carry, uint64_t* rows,
+                        uint64_t rows_cap, hbt_oracle_hist* hist, hbt_cpu_result* res, uint32_t cpu) {
+  const int sw = d->aggregate == HBT_AGG_SWITCH_EVENTS;
   int64_t err = 0;
   uint64_t n = 0;
   uint64_t n_rows = 0;
@@ -199,14 +229,56 @@ int hbt_oracle_consume(const uint8_t* ring, uint64_t data_size, uint64_t tail, u
         if (hm & HBT_H_LOST) {
           /* Lost: hdr, id, num_lost (CpuEventsGroup.h:112-120, :236-242) */
           if (d->aggregate == HBT_AGG_COUNT_DELTAS) carry->tstamp = INVALID_TS; /* gen :122 */
+          if (sw) {
+            /* handleRecordLost, PerCpuThreadSwitchGenerator.h:228-259; ContextSwitch::Lost
+             * = hdr id num_lost {pid tid tstamp} (CpuEventsGroup.h:112-120).  A record
+             * shorter than its struct: the reference reads past it; here -EPERM. */
+            if (size < 40) { err = -EPERM; goto exit; }
+            const uint64_t ts = ring_word(ring, mask, tail + 32);
+            int ret = sw_pending(carry, rows, rows_cap, &n_rows, ts, cpu);
+            if (ret >= 0)
+              ret = sw_write(rows, rows_cap, &n_rows, carry->tstamp + 1, HBT_SWEV_WRITE_ERRORS_START,
+                             HBT_LEVEL_INVALID, cpu, HBT_TAG_NA);
+            if (ret < 0) { err = ret; goto exit; } /* :1376-1379 */
+            carry->tstamp = ts;
+            carry->last[0] = 1;
+          }
           c[HBT_CNT_LOST] += ring_word(ring, mask, tail + 16);                  /* :1381 */
         }
         break;
       case REC_COMM:
-        if (hm & HBT_H_COMM) ++c[HBT_CNT_COMM]; /* :1394-1395 */
+        if (hm & HBT_H_COMM) {
+          if (sw) {
+            /* handleRecordComm, :261-297: no Event, but the thread map changes -> pseudo-event.
+             * Comm_Lower = hdr pid tid comm[]; sample_id closes the record (:1387-1393). */
+            if (size < 32) { err = -EPERM; goto exit; }
+            const uint64_t ts = ring_word(ring, mask, tail + size - 8);
+            const uint32_t tid = (uint32_t)(ring_word(ring, mask, tail + 8) >> 32);
+            int ret = sw_pending(carry, rows, rows_cap, &n_rows, ts, cpu);
+            if (ret >= 0)
+              ret = sw_write(rows, rows_cap, &n_rows, ts, HBT_SWEV_COMM, d->tid_level, cpu, tid);
+            if (ret < 0) { err = ret; goto exit; }
+            carry->tstamp = ts;
+          }
+          ++c[HBT_CNT_COMM]; /* :1394-1395 */
+        }
         break;
       case REC_EXIT:
-        if (hm & HBT_H_EXIT) ++c[HBT_CNT_EXIT];
+        if (hm & HBT_H_EXIT) {
+          if (sw) {
+            /* handleRecordExit, :299-331; Exit = hdr pid ppid tid ptid time sample_id (:139-146) */
+            if (size < 48) { err = -EPERM; goto exit; }
+            const uint64_t ts = ring_word(ring, mask, tail + 24);
+            const uint32_t tid = (uint32_t)ring_word(ring, mask, tail + 16);
+            int ret = sw_pending(carry, rows, rows_cap, &n_rows, ts, cpu);
+            if (ret >= 0)
+              ret = sw_write(rows, rows_cap, &n_rows, ts, HBT_SWEV_THREAD_DESTRUCTION, d->tid_level,
+                             cpu, tid);
+            if (ret < 0) { err = ret; goto exit; }
+            carry->tstamp = ts;
+          }
+          ++c[HBT_CNT_EXIT];
+        }
         break;
       case REC_THROTTLE:
         ++c[HBT_CNT_THROTTLE]; /* :1409-1414, unconditional */
@@ -215,7 +287,20 @@ int hbt_oracle_consume(const uint8_t* ring, uint64_t data_size, uint64_t tail, u
         ++c[HBT_CNT_UNTHROTTLE];
         break;
       case REC_FORK:
-        if (hm & HBT_H_FORK) ++c[HBT_CNT_FORK];
+        if (hm & HBT_H_FORK) {
+          if (sw) { /* handleRecordFork, :333-373; Fork = Exit layout */
+            if (size < 48) { err = -EPERM; goto exit; }
+            const uint64_t ts = ring_word(ring, mask, tail + 24);
+            const uint32_t tid = (uint32_t)ring_word(ring, mask, tail + 16);
+            int ret = sw_pending(carry, rows, rows_cap, &n_rows, ts, cpu);
+            if (ret >= 0)
+              ret = sw_write(rows, rows_cap, &n_rows, ts, HBT_SWEV_THREAD_CREATION, d->tid_level, cpu,
+                             tid);
+            if (ret < 0) { err = ret; goto exit; }
+            carry->tstamp = ts;
+          }
+          ++c[HBT_CNT_FORK];
+        }
         break;
       case REC_SAMPLE:
         if (hm & HBT_H_SAMPLE) {
@@ -297,7 +382,29 @@ int hbt_oracle_consume(const uint8_t* ring, uint64_t data_size, uint64_t tail, u
         if (hm & HBT_H_ITRACE_START) ++c[HBT_CNT_ITRACE_START];
         break;
       case REC_SWITCH_CPU_WIDE:
-        if (hm & HBT_H_SWITCH_CPU_WIDE) ++c[HBT_CNT_SWITCH_CPU_WIDE];
+        if (hm & HBT_H_SWITCH_CPU_WIDE) {
+          if (sw) {
+            /* handleRecordSwitchCpuWide, :375-412; SwitchCpuWide = hdr next_prev_pid
+             * next_prev_tid {pid tid tstamp} (:162-183) */
+            if (size < 32) { err = -EPERM; goto exit; }
+            const uint64_t ts = ring_word(ring, mask, tail + 24);
+            const uint32_t misc = (uint32_t)(hdr >> 32) & 0xFFFF;
+            int ret = sw_pending(carry, rows, rows_cap, &n_rows, ts, cpu);
+            if (ret >= 0) {
+              if (misc & MISC_SWITCH_OUT)
+                ret = sw_write(rows, rows_cap, &n_rows, ts,
+                               (misc & MISC_SWITCH_OUT_PREEMPT) ? HBT_SWEV_SWITCH_OUT_PREEMPT
+                                                                : HBT_SWEV_SWITCH_OUT_YIELD,
+                               d->tid_level, cpu, HBT_TAG_NA);
+              else
+                ret = sw_write(rows, rows_cap, &n_rows, ts, HBT_SWEV_SWITCH_IN, d->tid_level, cpu,
+                               (uint32_t)(ring_word(ring, mask, tail + 16) >> 32));
+            }
+            if (ret < 0) { err = ret; goto exit; }
+            carry->tstamp = ts;
+          }
+          ++c[HBT_CNT_SWITCH_CPU_WIDE];
+        }
         break;
       default: /* :1498-1500: logged, skipped by size */
         break;
@@ -312,7 +419,25 @@ exit:
   res->n_rows = n_rows;
   res->ret = err >= 0 ? (int64_t)n : err; /* :1521 */
   res->carry_tstamp = carry ? carry->tstamp : INVALID_TS;
+  if (sw) res->num_unknown_count_interval = carry->last[0];
   return 0;
+}
+
+int hbt_oracle_consume(const uint8_t* ring, uint64_t data_size, uint64_t tail, uint64_t head,
+                       const hbt_decode_desc* d, hbt_oracle_carry* carry, uint64_t* rows,
+                       uint64_t rows_cap, hbt_oracle_hist* hist, hbt_cpu_result* res) {
+  return consume_core(ring, data_size, tail, head, d, carry, rows, rows_cap, hist, res, 0);
+}
+
+/* Same with the CPU id that HBT_AGG_SWITCH_EVENTS writes into Event::comp_unit_id
+ * (comp_unit_id_ = cpu, PerCpuThreadSwitchGenerator.h:199).  rows then holds 16-byte
+ * hbt_switch_event records, rows_cap counts events; carry->tstamp is last_tstamp_
+ * (0 at start: numeric_limits<TimeStamp>::min(), :437) and carry->last[0] in_write_errors_. */
+int hbt_oracle_consume_cpu(const uint8_t* ring, uint64_t data_size, uint64_t tail, uint64_t head,
+                           const hbt_decode_desc* d, hbt_oracle_carry* carry, uint64_t* rows,
+                           uint64_t rows_cap, hbt_oracle_hist* hist, hbt_cpu_result* res,
+                           uint32_t cpu) {
+  return consume_core(ring, data_size, tail, head, d, carry, rows, rows_cap, hist, res, cpu);
 }
 
 /* ---- counter groups ------------------------------------------------------ */

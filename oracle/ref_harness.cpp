@@ -42,6 +42,7 @@
 #define protected public
 #include "hbt/src/perf_event/PerCpuCountReader.h"
 #include "hbt/src/perf_event/PerCpuCountSampleGenerator.h"
+#include "hbt/src/perf_event/PerCpuThreadSwitchGenerator.h"
 #include "hbt/src/ringbuffer/Consumer.h"
 #undef protected
 
@@ -637,6 +638,56 @@ int hbtref_row_sink(const uint64_t* rows, uint64_t n_rows, uint32_t n_events, ui
     ++n;
   }
   *n_out = n;
+  return 0;
+}
+
+// The REAL CpuThreadSwitchGenerator (PerCpuThreadSwitchGenerator.h:168-454) over n_cpus
+// ring images, CPUs in ascending order sharing one fresh PerThreadStats, exactly like
+// PerCpuThreadSwitchGenerator builds them (:466-481).  Events are drained from each
+// generator's own output ring; their tags are the reference's virtual ids.
+// last_tstamp / in_write_errors are last_tstamp_ / in_write_errors_ in and out.
+// The stream must be one the reference accepts: its handlers HBT_THROW_ASSERT inside
+// noexcept functions (std::terminate) on a second FORK of a live thread, for example.
+int hbtref_switch_events(const uint8_t* rings, uint64_t data_size, const uint64_t* tails,
+                         const uint64_t* heads, uint32_t n_cpus, uint32_t cpu_base, uint32_t tid_level,
+                         uint32_t max_records, uint64_t* last_tstamp, uint8_t* in_write_errors,
+                         hbt_switch_event* events, uint64_t events_cap, uint64_t* offsets,
+                         hbt_cpu_result* res) {
+  static_assert(sizeof(hbt_switch_event) == sizeof(facebook::hbt::tagstack::Event));
+  namespace rb = facebook::hbt::ringbuffer;
+  auto stats = std::make_shared<hp::PerThreadStats>();
+  hbt_tsc_params tsc{0, 1, 0, 0};
+  uint64_t n = 0;
+  for (uint32_t c = 0; c < n_cpus; ++c) {
+    offsets[c] = n;
+    const uint8_t* ring = rings + uint64_t(c) * data_size;
+    FakeMmapAlias mm;
+    mm.init(ring, data_size, tails[c], heads[c], tsc);
+    const uint64_t max_events = 2 * ((heads[c] - tails[c]) / 32 + 2);
+    hp::CpuThreadSwitchGenerator g(cpu_base + c, -1, static_cast<facebook::hbt::tagstack::Level>(tid_level),
+                                   stats, max_events + 1);
+    attach(g, mm.page, tsc);
+    load_counters(g, res[c].counters);
+    g.last_tstamp_ = last_tstamp[c];
+    g.in_write_errors_ = in_write_errors[c] != 0;
+    int64_t ret = run_consume(g, max_records);
+    finish_result(g, ring, data_size, tails[c], mm.hdr, ret, &res[c]);
+    rb::Consumer<hp::CpuThreadSwitchGenerator::RbExtraData> cons(g.getOutput());
+    facebook::hbt::tagstack::Event ev;
+    uint64_t k = 0;
+    while (cons.copy(sizeof(ev), &ev) >= 0) {
+      if (n >= events_cap) { detach(g); return -ENOSPC; }
+      std::memcpy(&events[n++], &ev, sizeof(ev));
+      ++k;
+    }
+    res[c].n_rows = k;
+    res[c].carry_tstamp = g.last_tstamp_;
+    res[c].num_unknown_count_interval = g.in_write_errors_ ? 1 : 0;
+    last_tstamp[c] = g.last_tstamp_;
+    in_write_errors[c] = g.in_write_errors_ ? 1 : 0;
+    detach(g);
+  }
+  offsets[n_cpus] = n;
   return 0;
 }
 

@@ -200,6 +200,102 @@ def ref_consume(ring: np.ndarray, tail: int, head: int, desc: hbt.DecodeDesc,
     return result_dict(resarr[0], hist=hist)
 
 
+def port_switch_events(ring: np.ndarray, tail: int, head: int, desc: hbt.DecodeDesc, cpu=0,
+                       last_tstamp=0, in_write_errors=0, counters=None):
+    """oracle/hbt_oracle.c with CpuThreadSwitchGenerator's handlers over one ring image:
+    tid-tagged events (SWITCH_EVENT_DTYPE, COMM pseudo-events included)."""
+    lib = port()
+    lib.hbt_oracle_consume_cpu.restype = C.c_int
+    lib.hbt_oracle_consume_cpu.argtypes = [_P, C.c_uint64, C.c_uint64, C.c_uint64,
+                                           C.POINTER(hbt.DecodeDesc), C.POINTER(Carry), _P, C.c_uint64,
+                                           _P, C.POINTER(hbt.CpuResult), C.c_uint32]
+    ring = np.ascontiguousarray(ring).view(np.uint8)
+    carry = Carry()
+    carry.tstamp = last_tstamp
+    carry.last[0] = in_write_errors
+    res = hbt.CpuResult()
+    if counters is not None:
+        for i, v in enumerate(counters):
+            res.counters[i] = int(v)
+    cap = 2 * ((head - tail) // 8 + 2)
+    ev = np.zeros(cap, dtype=hbt.SWITCH_EVENT_DTYPE)
+    rc = lib.hbt_oracle_consume_cpu(_np(ring), ring.nbytes, tail, head, C.byref(desc), C.byref(carry),
+                                    _np(ev), cap, None, C.byref(res), cpu)
+    assert rc == 0
+    d = result_dict(res)
+    d["events"] = ev[:res.n_rows].copy()
+    return d
+
+
+def ref_switch_events(rings: np.ndarray, tails, heads, tid_level=0, cpu_base=0, max_records=hbt.DRAIN,
+                      last_tstamp=None, in_write_errors=None):
+    """The reference's own CpuThreadSwitchGenerator over rings[n_cpus, data_size/8]: per CPU
+    result dict with vid-tagged events, CPUs processed in ascending order sharing one
+    PerThreadStats."""
+    lib = ref()
+    rings = np.ascontiguousarray(rings)
+    n_cpus = rings.shape[0]
+    ds = rings[0].nbytes
+    tails = np.asarray(tails, dtype=np.uint64)
+    heads = np.asarray(heads, dtype=np.uint64)
+    lt = np.zeros(n_cpus, dtype=np.uint64) if last_tstamp is None else np.asarray(last_tstamp, np.uint64).copy()
+    ie = np.zeros(n_cpus, dtype=np.uint8) if in_write_errors is None else np.asarray(in_write_errors, np.uint8).copy()
+    cap = int(sum(2 * ((int(h) - int(t)) // 32 + 2) for t, h in zip(tails, heads)))
+    ev = np.zeros(cap, dtype=hbt.SWITCH_EVENT_DTYPE)
+    off = np.zeros(n_cpus + 1, dtype=np.uint64)
+    res = (hbt.CpuResult * n_cpus)()
+    lib.hbtref_switch_events.restype = C.c_int
+    lib.hbtref_switch_events.argtypes = [_P, C.c_uint64, _P, _P, C.c_uint32, C.c_uint32, C.c_uint32,
+                                         C.c_uint32, _P, _P, _P, C.c_uint64, _P, _P]
+    rc = lib.hbtref_switch_events(_np(rings), ds, _np(tails), _np(heads), n_cpus, cpu_base, tid_level,
+                                  max_records, _np(lt), _np(ie), _np(ev), cap, _np(off), res)
+    assert rc == 0, rc
+    out = []
+    for c in range(n_cpus):
+        d = result_dict(res[c])
+        d["events"] = ev[int(off[c]):int(off[c + 1])].copy()
+        out.append(d)
+    return out
+
+
+def map_tids_to_vids(per_cpu_events):
+    """Test-side restatement of PerThreadStats' virtual-id bookkeeping as the handlers drive
+    it (PerCpuThreadSwitchGenerator.h:52-135, 228-412): turns tid-tagged event streams
+    (CPUs in ascending order, COMM pseudo-events included) into the reference's vid-tagged
+    ones (pseudo-events dropped)."""
+    next_vid = 1
+    active = {}
+    out = []
+    for ev in per_cpu_events:
+        keep = np.ones(len(ev), dtype=bool)
+        ev = ev.copy()
+        for i in range(len(ev)):
+            t, tid = int(ev["type"][i]), int(ev["tag"][i])
+            if t == hbt.SWEV_WRITE_ERRORS_START:
+                active.clear()                                  # :253-256
+                continue
+            if t not in (hbt.SWEV_COMM, hbt.SWEV_THREAD_CREATION, hbt.SWEV_THREAD_DESTRUCTION,
+                         hbt.SWEV_SWITCH_IN):
+                continue
+            if tid == 0:                                        # selectNextVid: tid 0 stays 0
+                vid, new = 0, False
+            elif tid in active:
+                vid, new = active[tid], False
+            else:
+                vid, new = next_vid, True
+            if new:                                             # createThreadInfo / registerFork
+                next_vid += 1
+                active[tid] = vid
+            if t == hbt.SWEV_THREAD_DESTRUCTION:
+                active.pop(tid, None)                           # registerExit
+            if t == hbt.SWEV_COMM:
+                keep[i] = False
+            else:
+                ev["tag"][i] = vid
+        out.append(ev[keep])
+    return out
+
+
 def counts_outputs(I, E, R):
     return dict(sums=np.zeros((I, 3 + E), np.uint64), scaled=np.zeros((I, E), np.uint64),
                 rates=np.zeros((I, E), np.float32), ratios=np.zeros((I, max(R, 1)), np.float64),

@@ -35,7 +35,8 @@ def test_library_exports_every_declared_symbol(built):
 
 def test_struct_layouts_match_header():
     # sizes the C side static-asserts through its own use; the binding must agree
-    assert C.sizeof(hbt.DecodeDesc) == 48
+    assert C.sizeof(hbt.DecodeDesc) == 56
+    assert hbt.SWITCH_EVENT_DTYPE.itemsize == 16  # sizeof(tagstack::Event), Event.h:222
     assert C.sizeof(hbt.CpuResult) == 8 * (4 + hbt.NUM_COUNTERS + 2)
     assert C.sizeof(hbt.HistEntry) == 24
     assert C.sizeof(hbt.TscParams) == 16
