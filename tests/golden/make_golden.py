@@ -138,6 +138,33 @@ def main():
                         deltas=o["deltas"])
     print("counts: ok")
 
+    # --- context switches: the real CpuThreadSwitchGenerator (vid-tagged tagstack::Events) ---
+    for name, seed, lost_every, n_rec in (("switch_events_lost", 5, 23, 500), ("switch_events_plain", 6, 0, 300)):
+        dsz = 1 << 15
+        rings, tails, heads = [], [], []
+        for c in range(3):
+            st = tg.ctx_switch_stream_consistent(seed * 100 + c, n_rec, lost_every=lost_every if c != 1 else 0,
+                                                 first_tid=1000 + 10000 * c)
+            tail = 3 * dsz + dsz - 1024 - 8 * c
+            ring, head = ring_np(st, dsz, tail)
+            rings.append(ring)
+            tails.append(tail)
+            heads.append(head)
+        rings = np.stack(rings)
+        ref = orc.ref_switch_events(rings, tails, heads, tid_level=2, cpu_base=8)
+        np.savez_compressed(
+            os.path.join(HERE, name + ".npz"), rings=rings, tails=np.array(tails, np.uint64),
+            heads=np.array(heads, np.uint64), tid_level=np.uint32(2), cpu_base=np.uint32(8),
+            events=np.concatenate([r["events"] for r in ref]),
+            n_events=np.array([len(r["events"]) for r in ref], np.uint64),
+            ret=np.array([r["ret"] for r in ref], np.int64),
+            n_records=np.array([r["n_records"] for r in ref], np.uint64),
+            new_tail=np.array([r["new_tail"] for r in ref], np.uint64),
+            counters=np.array([r["counters"] for r in ref], np.uint64),
+            last_tstamp=np.array([r["carry_tstamp"] for r in ref], np.uint64),
+            in_write_errors=np.array([r["num_unknown"] for r in ref], np.uint64))
+        print(f"{name}: events per cpu {[len(r['events']) for r in ref]}")
+
 
 if __name__ == "__main__":
     main()

@@ -12,8 +12,9 @@ import _oracle as orc
 
 GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
 DECODE_CASES = sorted(os.path.basename(p)[:-4] for p in glob.glob(os.path.join(GOLDEN, "*.npz"))
-                      if not os.path.basename(p).startswith("counts_"))
+                      if not os.path.basename(p).startswith(("counts_", "switch_")))
 COUNTS_CASES = ["counts_mux", "counts_c1_shape"]
+SWITCH_CASES = ["switch_events_lost", "switch_events_plain"]
 
 
 def load_desc(f):
@@ -136,3 +137,48 @@ def test_cuda_counts_match_reference_vectors(built, case):
     fin = np.isfinite(f["ratio_out"])
     # north star: f64 ratios within 1e-12 relative
     assert np.allclose(got["ratios"][fin], f["ratio_out"][fin], rtol=1e-12, atol=0.0)
+
+
+def check_switch(f, results, events):
+    """results/events: per CPU result dicts and tid-tagged events (oracle port or CUDA path);
+    mapped tid -> vid they must equal what the reference's own generator wrote."""
+    mapped = orc.map_tids_to_vids(events)
+    off = np.concatenate([[0], np.cumsum(f["n_events"])]).astype(int)
+    for c in range(len(events)):
+        r = results[c]
+        assert r["ret"] == int(f["ret"][c]) and r["n_records"] == int(f["n_records"][c]), c
+        assert r["new_tail"] == int(f["new_tail"][c]), c
+        assert r["counters"] == [int(x) for x in f["counters"][c]], c
+        assert r["carry_tstamp"] == int(f["last_tstamp"][c]), c
+        assert r["num_unknown"] == int(f["in_write_errors"][c]), c
+        want = f["events"][off[c]:off[c + 1]]
+        assert len(mapped[c]) == len(want) and (mapped[c] == want).all(), c
+
+
+@pytest.mark.parametrize("case", SWITCH_CASES)
+def test_oracle_switch_events_match_reference_vectors(built, case):
+    f = np.load(os.path.join(GOLDEN, case + ".npz"))
+    d = hbt.switch_desc(tid_level=int(f["tid_level"]))
+    res = [orc.port_switch_events(f["rings"][c], int(f["tails"][c]), int(f["heads"][c]), d,
+                                  cpu=int(f["cpu_base"]) + c) for c in range(len(f["tails"]))]
+    check_switch(f, res, [r["events"] for r in res])
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("case", SWITCH_CASES)
+def test_cuda_switch_events_match_reference_vectors(built, case):
+    f = np.load(os.path.join(GOLDEN, case + ".npz"))
+    n = len(f["tails"])
+    ctx = hbt.Context(0)
+    ctx.ring_configure(n, f["rings"][0].nbytes)
+    ctx.set_cpu_base(int(f["cpu_base"]))
+    for c in range(n):
+        ctx.submit_ring_image(c, f["rings"][c], int(f["tails"][c]), int(f["heads"][c]))
+    ctx.decode(hbt.switch_desc(tid_level=int(f["tid_level"])))
+    res = ctx.fetch_results()
+    results = [dict(ret=int(r["ret"]), n_records=int(r["n_records"]), new_tail=int(r["new_tail"]),
+                    counters=[int(x) for x in r["counters"]], carry_tstamp=int(r["carry_tstamp"]),
+                    num_unknown=int(r["num_unknown_count_interval"])) for r in res]
+    events = [ctx.fetch_switch_events(c, int(res[c]["n_rows"])) for c in range(n)]
+    ctx.close()
+    check_switch(f, results, events)
