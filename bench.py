@@ -171,6 +171,25 @@ def make_mixed_rings(n_cpus: int, ring_bytes: int, cpu_base: int, device, n_even
     return imgs, tails, heads, n * n_cpus
 
 
+def make_switch_rings(n_cpus: int, ring_bytes: int, cpu_base: int, device):
+    """Rings of mode::ContextSwitch records (what CpuThreadSwitchGenerator's sw_dummy event
+    fills its buffer with): SWITCH_CPU_WIDE 86 % / COMM / FORK / EXIT / LOST, 32-48 B records."""
+    imgs = torch.empty((n_cpus, ring_bytes // 8), dtype=torch.int64, device=device)
+    tails, heads = [], []
+    n = int((ring_bytes - (1 << 20)) / (34.4 * 1.02))
+    for c in range(n_cpus):
+        seed = tg.stream_seed(6, cpu_base + c)
+        s = tg.ctx_switch_stream(seed, n, device=device)
+        assert s.numel() * 8 <= ring_bytes - 4096, "switch stream does not fit the ring"
+        tail = tg.random_tail(seed, ring_bytes)
+        ring, head = tg.place_in_ring(s, ring_bytes, tail, fill_seed=seed ^ 0xABCDEF)
+        imgs[c] = ring
+        tails.append(tail)
+        heads.append(head)
+        del s, ring
+    return imgs, tails, heads, n * n_cpus
+
+
 def timed_steps(step, steps, dist, dev):
     """CUDA-event timing of `steps` calls of step(), barrier + sync on both sides, max over ranks."""
     if dist is not None:
@@ -196,7 +215,10 @@ def bench_deltas(args, rank, world, local, dev, dist):
     E = args.events
     ring_bytes = args.ring_mib << 20
     mixed = args.workload == "c4_mixed"
-    if mixed:
+    switch = args.workload == "c4_switch"
+    if switch:
+        imgs, tails, heads, n_rec = make_switch_rings(args.cpus, ring_bytes, rank * args.cpus, dev)
+    elif mixed:
         imgs, tails, heads, n_rec = make_mixed_rings(args.cpus, ring_bytes, rank * args.cpus, dev, E)
     else:
         imgs, tails, heads, n_rec = make_group_rings(args.cpus, ring_bytes, rank * args.cpus, dev, E)
@@ -205,6 +227,9 @@ def bench_deltas(args, rank, world, local, dev, dist):
     ctx.use_torch_stream()
     ctx.ring_configure(args.cpus, 0)
     desc = hbt.sampling_desc(E, handled=hbt.MODE_MIXED if mixed else hbt.MODE_SAMPLING)
+    if switch:
+        desc = hbt.switch_desc(tid_level=1)
+        ctx.set_cpu_base(rank * args.cpus)
     bases_a = np.array([imgs[c].data_ptr() for c in range(args.cpus)], dtype=np.uint64)
     tails_a, heads_a = np.array(tails, dtype=np.uint64), np.array(heads, dtype=np.uint64)
     kms = []
@@ -236,6 +261,25 @@ def bench_deltas(args, rank, world, local, dev, dist):
     peak, peak_src = load_peaks()
     k_ms = sum(kms) / len(kms)
     algo = window_bytes + n_rows * 8 * (2 + E)
+    if switch:
+        # two passes (proto-events, then the prefix sum that places WriteErrorsEnd events): the
+        # span is the whole device-timed step; n_rows counts 16-byte events
+        algo = window_bytes + n_rows * 16
+        ach = algo / (ms_step * 1e-3) / 1e9
+        return {"metric": METRIC, "value": n_rec * world / (ms_step * 1e-3), "unit": UNIT, "n_gpus": world,
+                "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms_step,
+                "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u64",
+                "data": "synthetic",
+                "config": {"workload": "c4_switch: mode::ContextSwitch records (32-48 B) -> tagstack::Event stream",
+                           "cpus_per_gpu": args.cpus, "ring_mib": args.ring_mib, "records_per_gpu": n_rec,
+                           "events_per_gpu": n_rows, "window_bytes_per_gpu": int(window_bytes),
+                           "l2": "inputs exceed L2; no flush needed", "slow_tiles": ctx.slow_tiles,
+                           "reruns": ctx.reruns},
+                "roofline": {"bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
+                             "traffic": None, "kernel": "k_decode<SWITCH_EVENTS> + k_sw_count/scan/emit",
+                             "kernel_ms": ms_step, "decode_kernel_ms": k_ms, "algorithmic_bytes": int(algo),
+                             "peak_source": peak_src},
+                "gpu_launches": int(launches), "clocks": clocks}
     ach = algo / (k_ms * 1e-3) / 1e9
     return {"metric": METRIC, "value": n_rec * world / (ms_step * 1e-3), "unit": UNIT, "n_gpus": world,
             "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms_step,
@@ -404,7 +448,7 @@ def main():
                     help="list capacity per CPU: distinct keys + the samples of one decode")
     ap.add_argument("--agg", default="hist", choices=["hist", "none"],
                     help="none: decode + counters only (diagnostic, not the headline workload)")
-    ap.add_argument("--workload", default="c2_ip_hist", choices=["c2_ip_hist", "c3_deltas", "c4_mixed", "c5_counts"],
+    ap.add_argument("--workload", default="c2_ip_hist", choices=["c2_ip_hist", "c3_deltas", "c4_mixed", "c4_switch", "c5_counts"],
                     help="c2_ip_hist is the headline (BASELINE configs[1]); the others are diagnostics")
     ap.add_argument("--events", type=int, default=8)
     ap.add_argument("--intervals", type=int, default=100000)

@@ -598,6 +598,11 @@ __global__ void __launch_bounds__(kThreads, AGG == HBT_AGG_IP_HISTOGRAM && kCach
 
   // thread-local totals over the fast-path tiles (added to st in the epilogue)
   uint32_t my_rec = 0, my_sample = 0;
+  // per-type counts of the other record types, 16 bits each (a thread sees at most 8 records
+  // per tile): counter ci lives in my_other[ci >> 2] at bit 16 * (ci & 3).  One shared-memory
+  // atomic per record would serialise the whole CTA on a stream of SWITCH records.
+  uint64_t my_other[3] = {0, 0, 0};
+  uint32_t my_other_n = 0;
 
   HistPending pend;  // IP_HISTOGRAM: appends whose cursor atomics are in flight
 
@@ -1018,7 +1023,15 @@ __global__ void __launch_bounds__(kThreads, AGG == HBT_AGG_IP_HISTOGRAM && kCach
             lost_sum += tv.at(pos + 16);
             if (AGG == HBT_AGG_COUNT_DELTAS) in_ev = ev_make(t_begin + pos, EV_LOST);
           } else if (ci >= 0) {
-            atomicAdd(&st.counters[ci], 1ull);
+            my_other[ci >> 2] += 1ull << (16 * (ci & 3));
+            if ((++my_other_n & 0x3FFF) == 0) {  // long before a 16-bit field can wrap: flush
+#pragma unroll
+              for (int c = 0; c < HBT_NUM_COUNTERS; ++c) {
+                const uint32_t v = (uint32_t)(my_other[c >> 2] >> (16 * (c & 3))) & 0xFFFFu;
+                if (v) atomicAdd(&st.counters[c], (unsigned long long)v);
+              }
+              my_other[0] = my_other[1] = my_other[2] = 0;
+            }
           }
           if (AGG == HBT_AGG_SWITCH_EVENTS && ci >= 0) {
             const ulonglong2 e = sw_proto(h, d.tid_level, p.cpu_base + seg.cpu,
@@ -1124,6 +1137,13 @@ __global__ void __launch_bounds__(kThreads, AGG == HBT_AGG_IP_HISTOGRAM && kCach
   }
   my_rec = __reduce_add_sync(0xffffffffu, my_rec);
   my_sample = __reduce_add_sync(0xffffffffu, my_sample);
+#pragma unroll
+  for (int c = 0; c < HBT_NUM_COUNTERS; ++c) {
+    if (c == HBT_CNT_LOST || c == HBT_CNT_SAMPLE) continue;
+    const uint32_t v =
+        __reduce_add_sync(0xffffffffu, (uint32_t)(my_other[c >> 2] >> (16 * (c & 3))) & 0xFFFFu);
+    if (lane == 0 && v) atomicAdd(&st.counters[c], (unsigned long long)v);
+  }
   if (lane == 0) {
     atomicAdd(&st.n_rec, (unsigned long long)my_rec);
     atomicAdd(&st.counters[HBT_CNT_SAMPLE], (unsigned long long)my_sample);

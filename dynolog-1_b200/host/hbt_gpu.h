@@ -6,6 +6,7 @@
 //   hbt::perf_event::PerCpuBase::read     hbt/src/perf_event/PerCpuBase.h:104-119
 //   hbt::perf_event::RbDataSlices         hbt/src/perf_event/CpuEventsGroup.h:44-63
 //   hbt::mon::Monitor                     hbt/src/mon/Monitor.h:40-99,213-237,281-304,484-732
+//   thread-switch generator               hbt/src/perf_event/PerCpuThreadSwitchGenerator.h:52-135,168-520
 //   count-sample row sink + consumers     hbt/src/perf_event/PerCpuCountSampleGenerator.h:69,182-195,
 //                                         hbt/src/ringbuffer/Producer.h:137-197, hbt/src/mon/MonData.h:69-128,
 //                                         hbt/src/mon/TraceMonitor.h:34-109, TraceMonitor.cpp:25-100
@@ -325,6 +326,107 @@ class PerCpuCountSampleDecoder {
   size_t n_events_;
   std::shared_ptr<GpuContext> gpu_;
   std::vector<hbt_cpu_result> results_;
+};
+
+// tagstack::Event (hbt/src/tagstack/Event.h:28-227) is hbt_switch_event byte for byte.
+using Event = hbt_switch_event;
+
+// The virtual-id half of PerThreadStats (PerCpuThreadSwitchGenerator.h:52-135) as the
+// generator's handlers drive it (:228-412).  The GPU tags thread events with the raw tid
+// and reports COMM records as pseudo-events; apply() replays the bookkeeping over one
+// CPU's events in stream order -- selectNextVid / createThreadInfo / registerExit, and
+// active_tids.clear() on WriteErrorsStart -- rewrites the tags to vids and drops the
+// pseudo-events.  Thread names, cmdlines and procfs reads stay with the caller.
+class ThreadSwitchVidMapper {
+ public:
+  uint32_t next_vid = 1;
+  std::map<uint32_t, uint32_t> active_tids;  // tid -> vid
+  size_t apply(std::vector<Event>& ev) {
+    size_t out = 0;
+    for (size_t i = 0; i < ev.size(); ++i) {
+      Event e = ev[i];
+      if (e.type == HBT_SWEV_WRITE_ERRORS_START) active_tids.clear();  // :253-256
+      const bool thread_ev = e.type == HBT_SWEV_COMM || e.type == HBT_SWEV_THREAD_CREATION ||
+                             e.type == HBT_SWEV_THREAD_DESTRUCTION || e.type == HBT_SWEV_SWITCH_IN;
+      if (thread_ev) {
+        const uint32_t tid = e.tag;
+        uint32_t vid = 0;
+        if (tid != 0) {  // tid 0 is not remapped (:91-97)
+          auto it = active_tids.find(tid);
+          if (it == active_tids.end()) {
+            vid = next_vid++;  // createThreadInfo / registerFork
+            active_tids[tid] = vid;
+          } else {
+            vid = it->second;
+          }
+        }
+        if (e.type == HBT_SWEV_THREAD_DESTRUCTION) active_tids.erase(tid);  // registerExit
+        if (e.type == HBT_SWEV_COMM) continue;
+        e.tag = vid;
+      }
+      ev[out++] = e;
+    }
+    ev.resize(out);
+    return out;
+  }
+};
+
+// Batch replacement of PerCpuThreadSwitchGenerator (PerCpuThreadSwitchGenerator.h:457-520):
+// every CPU's context-switch ring is decoded in one call; events(cpu) is what that CPU's
+// CpuThreadSwitchGenerator would have written to its output ring, vids included when the
+// CPUs are read in ascending order (the order accumUntil visits them).
+class PerCpuThreadSwitchDecoder {
+ public:
+  PerCpuThreadSwitchDecoder(const CpuSet& mon_cpus, uint8_t tid_level, size_t data_size,
+                            std::shared_ptr<GpuContext> gpu)
+      : mon_cpus_{mon_cpus}, tid_level_{tid_level}, gpu_{std::move(gpu)} {
+    gpu_->check(hbt_ring_configure(gpu_->get(), mon_cpus_.max_cpu_id + 1, data_size), "hbt_ring_configure");
+    results_.resize(mon_cpus_.max_cpu_id + 1);
+  }
+  void onCpuDataBufferRead(CpuId cpu, const RbDataSlices& s, uint64_t tail, uint64_t head) {
+    if (!mon_cpus_.hasCpu(cpu)) throw std::invalid_argument("CPU " + std::to_string(cpu) + " not monitored");
+    size_t n2 = 0;
+    if (s.second) n2 = std::min(s.second->size, (size_t)(head - tail) - s.first.size);
+    gpu_->check(hbt_submit_ring(gpu_->get(), cpu, s.first.from, s.first.size, s.second ? s.second->from : nullptr,
+                                n2, tail),
+                "hbt_submit_ring");
+  }
+  std::map<CpuId, int64_t> consume(unsigned max_num_records) {
+    hbt_decode_desc d{};
+    d.handled_mask = HBT_MODE_CONTEXT_SWITCH;
+    d.aggregate = HBT_AGG_SWITCH_EVENTS;
+    d.max_records = max_num_records;
+    d.tsc.time_mult = 1;
+    d.tid_level = tid_level_;
+    gpu_->check(hbt_decode(gpu_->get(), &d), "hbt_decode");
+    gpu_->check(hbt_fetch_results(gpu_->get(), results_.data(), (uint32_t)results_.size()), "hbt_fetch_results");
+    std::map<CpuId, int64_t> ret;
+    events_.clear();
+    for (CpuId cpu : mon_cpus_.cpus) {  // ascending: the vid map is shared by all CPUs
+      ret[cpu] = results_[cpu].ret;
+      std::vector<Event> ev(results_[cpu].n_rows);
+      if (!ev.empty())
+        gpu_->check(hbt_fetch_switch_events(gpu_->get(), cpu, ev.data(), ev.size()), "hbt_fetch_switch_events");
+      thread_stats_.apply(ev);
+      events_[cpu] = std::move(ev);
+    }
+    return ret;
+  }
+  const std::vector<Event>& events(CpuId cpu) const { return events_.at(cpu); }
+  size_t getNumEntries(CpuId cpu) const { return events_.at(cpu).size(); }
+  TimeStamp getLastTimeStamp(CpuId c) const { return results_.at(c).carry_tstamp; }
+  uint64_t getNumRecordLost(CpuId c) const { return results_.at(c).counters[HBT_CNT_LOST]; }
+  uint64_t getNumRecordSwitchCpuWide(CpuId c) const { return results_.at(c).counters[HBT_CNT_SWITCH_CPU_WIDE]; }
+  uint64_t dataTail(CpuId c) const { return results_.at(c).new_tail; }
+  const ThreadSwitchVidMapper& threadStats() const { return thread_stats_; }
+
+ private:
+  CpuSet mon_cpus_;
+  uint8_t tid_level_;
+  std::shared_ptr<GpuContext> gpu_;
+  std::vector<hbt_cpu_result> results_;
+  std::map<CpuId, std::vector<Event>> events_;
+  ThreadSwitchVidMapper thread_stats_;
 };
 
 // What a CpuCountSampleGenerator's output ring is to its consumers: a byte FIFO of

@@ -178,6 +178,42 @@ static void test_row_sink() {
   std::printf("row sink vs reference ring buffer: %d cases\n", cases);
 }
 
+// hand-written mode::ContextSwitch stream (CpuEventsGroup.h:105-184)
+static std::vector<uint64_t> switch_stream() {
+  auto hdr = [](uint64_t t, uint64_t words, uint64_t misc = 0) { return t | (misc << 32) | ((8 * words) << 48); };
+  const uint64_t OUT = 1u << 13, PRE = (1u << 13) | (1u << 14);
+  std::vector<uint64_t> w;
+  auto add = [&](std::initializer_list<uint64_t> l) { w.insert(w.end(), l); };
+  add({hdr(15, 4), 0, 40ull | (41ull << 32), 100});                       // switch in tid 41
+  add({hdr(15, 4, OUT), 0, 40ull | (41ull << 32), 110});                  // out, yield
+  add({hdr(7, 6), 50ull | (1ull << 32), 51ull | (1ull << 32), 120, 0, 121});  // FORK tid 51
+  add({hdr(3, 5), 50ull | (51ull << 32), 0x6161, 50ull | (51ull << 32), 130});  // COMM tid 51
+  add({hdr(15, 4), 0, 50ull | (51ull << 32), 140});                       // switch in tid 51
+  add({hdr(2, 5), 7, 3, 0, 150});                                         // LOST(3)
+  add({hdr(15, 4, PRE), 0, 50ull | (51ull << 32), 170});                  // out, preempt
+  add({hdr(15, 4), 0, 40ull | (41ull << 32), 180});                       // switch in tid 41 again
+  add({hdr(4, 6), 50ull | (1ull << 32), 51ull | (1ull << 32), 200, 0, 201});  // EXIT tid 51
+  return w;
+}
+
+static void test_vid_mapper() {
+  using E = pe::Event;
+  std::vector<E> ev = {
+      {100, HBT_SWEV_SWITCH_IN, 2, 0, 41},           {110, HBT_SWEV_SWITCH_OUT_YIELD, 2, 0, HBT_TAG_NA},
+      {120, HBT_SWEV_THREAD_CREATION, 2, 0, 51},     {130, HBT_SWEV_COMM, 2, 0, 51},
+      {135, HBT_SWEV_COMM, 2, 0, 77},                {140, HBT_SWEV_SWITCH_IN, 2, 0, 0},
+      {141, HBT_SWEV_WRITE_ERRORS_START, 0xFF, 0, HBT_TAG_NA}, {150, HBT_SWEV_WRITE_ERRORS_END, 0xFF, 0, HBT_TAG_NA},
+      {150, HBT_SWEV_SWITCH_IN, 2, 0, 41},           {160, HBT_SWEV_THREAD_DESTRUCTION, 2, 0, 41},
+      {170, HBT_SWEV_SWITCH_IN, 2, 0, 41}};
+  pe::ThreadSwitchVidMapper m;
+  CHECK(m.apply(ev) == 9);  // the two COMM pseudo-events are gone
+  const uint32_t want[9] = {1, HBT_TAG_NA, 2, 0, HBT_TAG_NA, HBT_TAG_NA, 4, 4, 5};
+  // tid 41 -> 1, tid 51 -> 2, COMM of unseen tid 77 takes vid 3, tid 0 stays 0,
+  // the LOST forgets everybody: 41 -> 4; after its EXIT the same tid is a new thread: 5
+  for (size_t i = 0; i < 9 && ev.size() == 9; ++i) CHECK(ev[i].tag == want[i]);
+  CHECK(m.next_vid == 6 && m.active_tids.size() == 1);
+}
+
 static void test_gpu() {
   auto gpu = std::make_shared<GpuContext>(0);
   const size_t C = 16, I = 6;
@@ -289,12 +325,43 @@ static void test_gpu() {
   };
   tm.applyToCountSamplesAndConsume(func);
   CHECK(calls == 4 && tm.sink(2).getNumEntries() == 0);
+
+  // context-switch ring through the thread-switch generator mirror: events with vids
+  {
+    const std::vector<uint64_t> sw = switch_stream();
+    std::vector<uint64_t> sring(ds / 8, 0);
+    const uint64_t stail = 3 * ds + 40;
+    for (size_t w = 0; w < sw.size(); ++w) sring[((stail / 8) + w) & (ds / 8 - 1)] = sw[w];
+    const uint64_t shead = stail + 8 * sw.size();
+    pe::PerCpuThreadSwitchDecoder sdec(CpuSet::makeFromCont(std::vector<int>{1, 3}), 2, ds, gpu);
+    const uint8_t* sbase = reinterpret_cast<const uint8_t*>(sring.data());
+    pe::RbDataSlices ss(sbase + (stail & (ds - 1)), 8 * sw.size());
+    sdec.onCpuDataBufferRead(3, ss, stail, shead);
+    auto sret = sdec.consume(0xFFFFFFFFu);
+    CHECK(sret.at(3) == -ENODATA && sret.at(1) == -ENODATA);
+    const auto& ev = sdec.events(3);
+    struct W { uint64_t ts; uint8_t type; uint32_t tag; };
+    const W want[] = {{100, HBT_SWEV_SWITCH_IN, 1},          {110, HBT_SWEV_SWITCH_OUT_YIELD, HBT_TAG_NA},
+                      {120, HBT_SWEV_THREAD_CREATION, 2},    {140, HBT_SWEV_SWITCH_IN, 2},
+                      {141, HBT_SWEV_WRITE_ERRORS_START, HBT_TAG_NA}, {170, HBT_SWEV_WRITE_ERRORS_END, HBT_TAG_NA},
+                      {170, HBT_SWEV_SWITCH_OUT_PREEMPT, HBT_TAG_NA}, {180, HBT_SWEV_SWITCH_IN, 3},
+                      {200, HBT_SWEV_THREAD_DESTRUCTION, 4}};
+    CHECK(ev.size() == 9);
+    for (size_t i = 0; i < 9 && ev.size() == 9; ++i) {
+      CHECK(ev[i].tstamp == want[i].ts && ev[i].type == want[i].type && ev[i].tag == want[i].tag);
+      CHECK(ev[i].comp_unit_id == 3);
+      CHECK(ev[i].level == (ev[i].type >= HBT_SWEV_WRITE_ERRORS_START ? HBT_LEVEL_INVALID : 2));
+    }
+    CHECK(sdec.getNumRecordLost(3) == 3 && sdec.getNumRecordSwitchCpuWide(3) == 5);
+    CHECK(sdec.getLastTimeStamp(3) == 200 && sdec.dataTail(3) == shead && sdec.events(1).empty());
+  }
 }
 
 int main(int argc, char** argv) {
   const std::string mode = argc > 1 ? argv[1] : "cpu";
   test_cpu();
   test_row_sink();
+  test_vid_mapper();
   if (mode == "gpu") test_gpu();
   std::printf("%s: %s (%d failures)\n", mode.c_str(), g_fail ? "FAILED" : "ok", g_fail);
   return g_fail ? 1 : 0;
