@@ -160,23 +160,33 @@ __device__ __forceinline__ uint64_t xform(const hbt_decode_desc& d, uint32_t i, 
   return ((d.tsc_transform_mask >> i) & 1) ? tsc_to_ktime(v, d.tsc) : v;
 }
 
-// Counter index of a record type, -1 for types consume() only skips.
-__device__ __forceinline__ int counter_of(uint32_t type, uint32_t handled) {
-  switch (type) {
-    case REC_LOST: return (handled & HBT_H_LOST) ? HBT_CNT_LOST : -1;
-    case REC_COMM: return (handled & HBT_H_COMM) ? HBT_CNT_COMM : -1;
-    case REC_EXIT: return (handled & HBT_H_EXIT) ? HBT_CNT_EXIT : -1;
-    case REC_THROTTLE: return HBT_CNT_THROTTLE;
-    case REC_UNTHROTTLE: return HBT_CNT_UNTHROTTLE;
-    case REC_FORK: return (handled & HBT_H_FORK) ? HBT_CNT_FORK : -1;
-    case REC_SAMPLE: return (handled & HBT_H_SAMPLE) ? HBT_CNT_SAMPLE : -1;
-    case REC_READ: return (handled & HBT_H_READ) ? HBT_CNT_READ : -1;
-    case REC_AUX: return (handled & HBT_H_AUX) ? HBT_CNT_AUX : -1;
-    case REC_ITRACE_START: return (handled & HBT_H_ITRACE_START) ? HBT_CNT_ITRACE_START : -1;
-    case REC_SWITCH_CPU_WIDE:
-      return (handled & HBT_H_SWITCH_CPU_WIDE) ? HBT_CNT_SWITCH_CPU_WIDE : -1;
-    default: return -1;
-  }
+// Counter index of a record type, -1 for types consume() only skips
+// (CpuEventsGroup.h:1372-1501).  Branch-free: a stream of mixed types would otherwise
+// serialise a warp over a 16-way switch for every record.  type_mask(handled) has bit t
+// set when records of PERF type t are counted; kCiNib holds the counter index of type t
+// in nibble t.
+__host__ __device__ constexpr uint32_t type_mask(uint32_t handled) {
+  return ((handled & HBT_H_LOST) ? 1u << REC_LOST : 0u) | ((handled & HBT_H_COMM) ? 1u << REC_COMM : 0u) |
+         ((handled & HBT_H_EXIT) ? 1u << REC_EXIT : 0u) | (1u << REC_THROTTLE) | (1u << REC_UNTHROTTLE) |
+         ((handled & HBT_H_FORK) ? 1u << REC_FORK : 0u) | ((handled & HBT_H_SAMPLE) ? 1u << REC_SAMPLE : 0u) |
+         ((handled & HBT_H_READ) ? 1u << REC_READ : 0u) | ((handled & HBT_H_AUX) ? 1u << REC_AUX : 0u) |
+         ((handled & HBT_H_ITRACE_START) ? 1u << REC_ITRACE_START : 0u) |
+         ((handled & HBT_H_SWITCH_CPU_WIDE) ? 1u << REC_SWITCH_CPU_WIDE : 0u);
+}
+constexpr uint64_t kCiNib =
+    ((uint64_t)HBT_CNT_LOST << (4 * REC_LOST)) | ((uint64_t)HBT_CNT_COMM << (4 * REC_COMM)) |
+    ((uint64_t)HBT_CNT_EXIT << (4 * REC_EXIT)) | ((uint64_t)HBT_CNT_THROTTLE << (4 * REC_THROTTLE)) |
+    ((uint64_t)HBT_CNT_UNTHROTTLE << (4 * REC_UNTHROTTLE)) | ((uint64_t)HBT_CNT_FORK << (4 * REC_FORK)) |
+    ((uint64_t)HBT_CNT_SAMPLE << (4 * REC_SAMPLE)) | ((uint64_t)HBT_CNT_READ << (4 * REC_READ)) |
+    ((uint64_t)HBT_CNT_AUX << (4 * REC_AUX)) | ((uint64_t)HBT_CNT_ITRACE_START << (4 * REC_ITRACE_START)) |
+    ((uint64_t)HBT_CNT_SWITCH_CPU_WIDE << (4 * REC_SWITCH_CPU_WIDE));
+static_assert(REC_SWITCH_CPU_WIDE == 15 && HBT_NUM_COUNTERS <= 16, "nibble table covers types 0..15");
+
+__device__ __forceinline__ bool counted(uint32_t type, uint32_t tmask) {
+  return type < 16 && ((tmask >> (type & 15)) & 1u);
+}
+__device__ __forceinline__ int counter_of(uint32_t type, uint32_t tmask) {
+  return counted(type, tmask) ? (int)((kCiNib >> (4 * (type & 15))) & 15) : -1;
 }
 
 // ---- HBT_AGG_SWITCH_EVENTS ----------------------------------------------------------
@@ -192,12 +202,8 @@ constexpr uint32_t kMiscSwitchOut = 1u << 13, kMiscSwitchOutPreempt = 1u << 14;
 // smallest well-formed size of a handled ContextSwitch record (CpuEventsGroup.h:105-184);
 // shorter ones are refused with -EPERM (the reference would read past the record)
 __device__ __forceinline__ uint32_t sw_min_size(uint32_t type) {
-  switch (type) {
-    case REC_LOST: return 40;
-    case REC_EXIT:
-    case REC_FORK: return 48;
-    default: return 32;  // COMM, SWITCH_CPU_WIDE
-  }
+  // LOST 40, EXIT / FORK 48, COMM / SWITCH_CPU_WIDE 32 (selects, no branches)
+  return 32u + (type == REC_LOST ? 8u : 0u) + ((type == REC_EXIT || type == REC_FORK) ? 16u : 0u);
 }
 
 __device__ __forceinline__ uint64_t sw_word1(uint32_t type, uint32_t level, uint32_t cu, uint32_t tag) {
@@ -401,7 +407,7 @@ __device__ void consume_sequential(const DecodeParams& p, const RingDesc& ring,
       break;
     }
     if (st.entry == kNone) st.entry = pos;
-    const int ci = counter_of(type, d.handled_mask);
+    const int ci = counter_of(type, type_mask(d.handled_mask));
     if (type == REC_LOST && ci >= 0) {
       st.counters[HBT_CNT_LOST] += ring_word_g(ring, pos + 16);
       if (AGG == HBT_AGG_COUNT_DELTAS) st.ev = ev_make(pos, EV_LOST);
@@ -548,6 +554,7 @@ __global__ void __launch_bounds__(kThreads, AGG == HBT_AGG_IP_HISTOGRAM && kCach
   const bool h_read = (d.handled_mask & HBT_H_READ) != 0;
   const bool h_lost = (d.handled_mask & HBT_H_LOST) != 0;
   const bool group_layout = d.sample_layout == HBT_SAMPLE_GROUP;
+  const uint32_t tmask = type_mask(d.handled_mask);
 
   if (tid == 0) {
     for (int s = 0; s < kStages; ++s) mbar_init(&sm.bar[s], 1);
@@ -682,7 +689,7 @@ __global__ void __launch_bounds__(kThreads, AGG == HBT_AGG_IP_HISTOGRAM && kCach
             ok = false;
           }
           ++my_n;
-        } else if (AGG == HBT_AGG_COUNT_DELTAS || counter_of(type, d.handled_mask) >= 0) {
+        } else if (AGG == HBT_AGG_COUNT_DELTAS || counted(type, tmask)) {
           ok = false;  // LOST / READ / context-switch records: the general path counts them
         }
       }
@@ -872,7 +879,7 @@ __global__ void __launch_bounds__(kThreads, AGG == HBT_AGG_IP_HISTOGRAM && kCach
               last_ev = ((pos + 1) << 2) | EV_LOST;
               if (first_ev == 0) first_ev = last_ev;
             }
-            if (counter_of(type, d.handled_mask) >= 0) {
+            if (counted(type, tmask)) {
               if (AGG == HBT_AGG_SWITCH_EVENTS && size < sw_min_size(type)) {
                 bad = true;  // the sequential walk reports -EPERM
                 break;
@@ -1018,7 +1025,7 @@ __global__ void __launch_bounds__(kThreads, AGG == HBT_AGG_IP_HISTOGRAM && kCach
           }
           in_ev = ev_make(t_begin + pos, EV_SAMPLE);
         } else {
-          const int ci = counter_of(type, d.handled_mask);
+          const int ci = counter_of(type, tmask);
           if (ci == HBT_CNT_LOST) {
             lost_sum += tv.at(pos + 16);
             if (AGG == HBT_AGG_COUNT_DELTAS) in_ev = ev_make(t_begin + pos, EV_LOST);
