@@ -536,7 +536,10 @@ __device__ __forceinline__ uint32_t sub_of_word(uint32_t w) {
 }
 
 template <int AGG>
-__global__ void __launch_bounds__(kThreads, AGG == HBT_AGG_IP_HISTOGRAM && kCacheSlots > 256 ? 3 : 4) k_decode(const DecodeParams p) {
+#ifndef HBT_MIN_BLOCKS
+#define HBT_MIN_BLOCKS 4
+#endif
+__global__ void __launch_bounds__(kThreads, AGG == HBT_AGG_IP_HISTOGRAM && kCacheSlots > 256 ? 3 : HBT_MIN_BLOCKS) k_decode(const DecodeParams p) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   uint8_t* stages = smem_raw;  // kStages * kTile
   Smem& sm = *reinterpret_cast<Smem*>(smem_raw + kStages * kTile);
@@ -612,6 +615,11 @@ __global__ void __launch_bounds__(kThreads, AGG == HBT_AGG_IP_HISTOGRAM && kCach
   uint32_t my_other_n = 0;
 
   HistPending pend;  // IP_HISTOGRAM: appends whose cursor atomics are in flight
+  // COUNT_DELTAS row writer (uniform fast path): this thread's fixed word column and first row
+  const uint32_t rw_wpr = 2 + d.n_events;
+  const uint32_t rw_rows = kThreads / rw_wpr;  // whole rows per pass (n_events <= 64: >= 3)
+  const uint32_t rw_r0 = tid / rw_wpr, rw_w = tid - rw_r0 * rw_wpr;
+  const bool rw_active = tid < rw_rows * rw_wpr;
 
   // my sub-chunk, in tile-relative bytes
   const uint32_t sb = 8u * sub_begin_word(tid);
@@ -731,24 +739,26 @@ __global__ void __launch_bounds__(kThreads, AGG == HBT_AGG_IP_HISTOGRAM && kCach
           const uint32_t wpr = 2 + d.n_events;
           uint64_t* out = seg.rows + (1 + n_rows_in) * (uint64_t)wpr;
           const uint64_t far_prev = ev_pos(in_ev);
-          // consecutive threads write consecutive u64s of the tile's rows
-          const float inv = __frcp_rn((float)wpr);
-          const uint32_t total = rows_tile * wpr;
-          for (uint32_t f = tid; f < total; f += kThreads) {
-            uint32_t r = (uint32_t)((float)f * inv);
-            if (r * wpr > f) --r;
-            else if ((r + 1) * wpr <= f) ++r;
-            const uint32_t w = f - r * wpr;
-            const uint32_t k = r + 1 - first_row;  // the record that closes row r
-            const uint32_t cpos = erel + k * S;
-            const uint32_t off = w < 2 ? 8u : 40u + 8u * (w - 2);  // tstamp, or value[w-2]
-            const uint64_t cur = tv.at(cpos + off);
-            const uint64_t prv = k > 0 ? tv.at(cpos - S + off) : ring_word_g(ring, far_prev + off);
-            uint64_t v;
-            if (w == 0) v = prv;
-            else if (w == 1) v = cur - prv;
-            else v = xform(d, w - 2, cur) - xform(d, w - 2, prv);
-            out[f] = v;
+          // Consecutive threads write consecutive u64s of the tile's rows.  A pass covers
+          // rw_rows whole rows with the first rw_rows * wpr threads, so a thread's word
+          // column rw_w (hence the field offset and the TSC transform flag) never changes
+          // and its row index just advances by rw_rows: no division in the loop.
+          if (rw_active) {
+            const uint32_t off = rw_w < 2 ? 8u : 24u + 8u * rw_w;  // tstamp, or value[rw_w - 2] at 40 + 8 (rw_w - 2)
+            const bool xf = rw_w >= 2 && ((d.tsc_transform_mask >> (rw_w - 2)) & 1);
+            uint32_t cpos = erel + (rw_r0 + 1 - first_row) * S + off;  // field of the record closing row r
+            const uint32_t step = rw_rows * S;
+            uint64_t* o = out + rw_r0 * wpr + rw_w;
+            const uint32_t ostep = rw_rows * wpr;
+            for (uint32_t r = rw_r0; r < rows_tile; r += rw_rows, cpos += step, o += ostep) {
+              const uint64_t cur = tv.at(cpos);
+              const uint64_t prv = r + 1 > first_row ? tv.at(cpos - S) : ring_word_g(ring, far_prev + off);
+              uint64_t v;
+              if (rw_w == 0) v = prv;
+              else if (!xf) v = cur - prv;   // duration, or a plain counter delta
+              else v = tsc_to_ktime(cur, d.tsc) - tsc_to_ktime(prv, d.tsc);
+              *o = v;
+            }
           }
           if (tid == 0) {
             if (ik == EV_LOST) ++st.n_unknown;  // record 0 re-seeds after a LOST
