@@ -1071,24 +1071,22 @@ __global__ void __launch_bounds__(kThreads, AGG == HBT_AGG_IP_HISTOGRAM && kCach
         uint32_t trows = 0;
         for (uint32_t w = 0; w < kThreads / 32; ++w) trows += sm.warp_rows[w];
         const uint32_t wpr = 2 + d.n_events;
-        const float inv = __frcp_rn((float)wpr);
         uint64_t* out = seg.rows + (1 + n_rows0) * (uint64_t)wpr;
-        const uint32_t total = trows * wpr;
-        for (uint32_t f = tid; f < total; f += kThreads) {
-          uint32_t r = (uint32_t)((float)f * inv);
-          if (r * wpr > f) --r;
-          else if ((r + 1) * wpr <= f) ++r;
-          const uint32_t w = f - r * wpr;
-          const uint2 rd = rowd.d[r];
-          const uint32_t off = w < 2 ? 8u : 40u + 8u * (w - 2);  // tstamp, or value[w-2]
-          const uint64_t cur = tv.at(rd.x + off);
-          const uint64_t prv = rd.y != kNoRel ? tv.at(rd.y + off)
-                                              : ring_word_g(ring, rowd.far_prev + off);
-          uint64_t v;
-          if (w == 0) v = prv;
-          else if (w == 1) v = cur - prv;
-          else v = xform(d, w - 2, cur) - xform(d, w - 2, prv);
-          out[f] = v;
+        if (rw_active) {  // same thread -> word column mapping as the uniform fast path
+          const uint32_t off = rw_w < 2 ? 8u : 24u + 8u * rw_w;
+          const bool xf = rw_w >= 2 && ((d.tsc_transform_mask >> (rw_w - 2)) & 1);
+          uint64_t* o = out + rw_r0 * wpr + rw_w;
+          for (uint32_t r = rw_r0; r < trows; r += rw_rows, o += rw_rows * wpr) {
+            const uint2 rd = rowd.d[r];
+            const uint64_t cur = tv.at(rd.x + off);
+            const uint64_t prv = rd.y != kNoRel ? tv.at(rd.y + off)
+                                                : ring_word_g(ring, rowd.far_prev + off);
+            uint64_t v;
+            if (rw_w == 0) v = prv;
+            else if (!xf) v = cur - prv;
+            else v = tsc_to_ktime(cur, d.tsc) - tsc_to_ktime(prv, d.tsc);
+            *o = v;
+          }
         }
       }
     }
