@@ -230,6 +230,9 @@ def bench_deltas(args, rank, world, local, dev, dist):
     if switch:
         desc = hbt.switch_desc(tid_level=1)
         ctx.set_cpu_base(rank * args.cpus)
+    if args.agg == "none":  # diagnostic: boundary discovery + per-type counters only
+        desc = hbt.count_desc(hbt.MODE_CONTEXT_SWITCH if switch else hbt.MODE_MIXED if mixed
+                              else hbt.MODE_SAMPLING)
     bases_a = np.array([imgs[c].data_ptr() for c in range(args.cpus)], dtype=np.uint64)
     tails_a, heads_a = np.array(tails, dtype=np.uint64), np.array(heads, dtype=np.uint64)
     kms = []

@@ -109,6 +109,8 @@ EXPORTS = [
     ("hbt_fetch_rows", C.c_int64, [_P, C.c_uint32, _P, C.c_uint64]),
     ("hbt_fetch_switch_events", C.c_int64, [_P, C.c_uint32, _P, C.c_uint64]),
     ("hbt_switch_events_dev", C.c_int, [_P, C.POINTER(_P), _U64P]),
+    ("hbt_switch_events_merged_dev", C.c_int, [_P, C.POINTER(_P), _U64P]),
+    ("hbt_fetch_switch_events_merged", C.c_int64, [_P, _P, C.c_uint64]),
     ("hbt_rows_slabs_dev", C.c_int, [_P, C.c_uint32, C.POINTER(_P), _U64P, C.POINTER(C.c_uint32)]),
     ("hbt_rows_max_slabs", C.c_uint32, [_P]),
     ("hbt_fetch_carry", C.c_int, [_P, C.c_uint32, _P, C.c_uint32]),
@@ -312,6 +314,14 @@ class Context:
         off = np.zeros(self.n_cpus + 1, dtype=np.uint64)
         self._ck(self.lib.hbt_switch_events_dev(self.h, C.byref(base), off.ctypes.data_as(_U64P)))
         return base.value or 0, off
+
+    def fetch_switch_events_merged(self) -> np.ndarray:
+        """All CPUs' events of the last AGG_SWITCH_EVENTS decode in Combinator order."""
+        base, n = C.c_void_p(), C.c_uint64()
+        self._ck(self.lib.hbt_switch_events_merged_dev(self.h, C.byref(base), C.byref(n)))
+        out = np.zeros(max(1, n.value), dtype=SWITCH_EVENT_DTYPE)
+        m = self._ck(self.lib.hbt_fetch_switch_events_merged(self.h, _ptr(out), out.shape[0]))
+        return out[:m]
 
     def fetch_carry(self, cpu: int, n_events: int) -> np.ndarray:
         out = np.zeros(n_events, dtype=np.uint64)

@@ -1732,4 +1732,67 @@ static __global__ void __launch_bounds__(256) k_sw_emit(const SwParams p) {
   }
 }
 
+// ---------------------------------------------------------------------------
+// k_sw_merge: one level of the binary Combinator tree (hbt/src/tagstack/Stream.h:114-248)
+// over the per-CPU event streams: runs of `run` CPUs are merged pairwise, (0,1), (2,3), ...
+// like makeBinaryTree pairs its nodes; an odd run at the end is copied.  The order is
+// Event::happenedBefore (Event.h:205-213): timestamp first, then comp_unit_id.  Every
+// thread produces kMergeK consecutive outputs: a merge-path binary search finds where its
+// diagonal cuts the two inputs, then it merges sequentially.  Exactly the Combinator's
+// output when each CPU's stream is timestamp-ordered, which the Combinator itself assumes
+// (its DCHECKs, Stream.h:139-141).
+// ---------------------------------------------------------------------------
+constexpr uint32_t kMergeK = 8;
+
+__device__ __forceinline__ bool ev_before(const ulonglong2& a, const ulonglong2& b) {
+  if (a.x != b.x) return a.x < b.x;
+  return (uint32_t)((a.y >> 16) & 0xFFFF) < (uint32_t)((b.y >> 16) & 0xFFFF);
+}
+
+static __global__ void __launch_bounds__(256)
+    k_sw_merge(const ulonglong2* __restrict__ in, ulonglong2* __restrict__ out,
+               const uint64_t* __restrict__ offsets, uint32_t n_cpus, uint32_t run) {
+  const uint64_t total = offsets[n_cpus];
+  uint64_t pos = ((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) * kMergeK;
+  const uint64_t end = min(pos + kMergeK, total);
+  const uint32_t n_pairs = (n_cpus + 2 * run - 1) / (2 * run);
+  while (pos < end) {
+    // the pair whose output range holds pos: largest p with offsets[2 p run] <= pos
+    uint32_t lo = 0, hi = n_pairs - 1;
+    while (lo < hi) {
+      const uint32_t mid = (lo + hi + 1) >> 1;
+      if (offsets[min(2 * mid * run, n_cpus)] <= pos) lo = mid;
+      else hi = mid - 1;
+    }
+    const uint64_t a0 = offsets[min(2 * lo * run, n_cpus)];
+    const uint64_t b0 = offsets[min((2 * lo + 1) * run, n_cpus)];
+    const uint64_t b1 = offsets[min((2 * lo + 2) * run, n_cpus)];
+    const uint64_t la = b0 - a0, lb = b1 - b0;
+    const ulonglong2* A = in + a0;
+    const ulonglong2* B = in + b0;
+    const uint64_t d = pos - a0;  // diagonal: d elements of this pair come before pos
+    // merge path: smallest i with !(A[i] before B[d-1-i])
+    uint64_t il = d > lb ? d - lb : 0, ih = min(d, la);
+    while (il < ih) {
+      const uint64_t mid = (il + ih) >> 1;
+      if (ev_before(A[mid], B[d - 1 - mid])) il = mid + 1;
+      else ih = mid;
+    }
+    uint64_t ai = il, bi = d - il;
+    const uint64_t stop = min(end, b1);
+    ulonglong2 ea = ai < la ? A[ai] : make_ulonglong2(0, 0);
+    ulonglong2 eb = bi < lb ? B[bi] : make_ulonglong2(0, 0);
+    for (; pos < stop; ++pos) {
+      const bool take_a = bi >= lb || (ai < la && ev_before(ea, eb));
+      if (take_a) {
+        out[pos] = ea;
+        if (++ai < la) ea = A[ai];
+      } else {
+        out[pos] = eb;
+        if (++bi < lb) eb = B[bi];
+      }
+    }
+  }
+}
+
 }  // namespace hbt

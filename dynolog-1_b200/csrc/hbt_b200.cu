@@ -128,6 +128,8 @@ struct hbt_ctx {
   DevBuf<uint64_t> d_sw_off;
   PinBuf<uint64_t> h_sw_off;
   DevBuf<hbt_switch_event> sw_events;
+  DevBuf<hbt_switch_event> sw_merge[2];       // ping-pong buffers of the Combinator tree levels
+  const hbt_switch_event* sw_merged = nullptr;  // result of the last merge, nullptr = not merged yet
   bool sw_valid = false;  // sw_events / h_sw_off describe the last fetched decode
 
   // histogram: per-(cpu,bucket) lists (see HistLists)
@@ -569,6 +571,8 @@ void hbt_destroy(hbt_ctx* ctx) {
   ctx->d_sw_off.release();
   ctx->h_sw_off.release();
   ctx->sw_events.release();
+  ctx->sw_merge[0].release();
+  ctx->sw_merge[1].release();
   ctx->hist_entries.release();
   ctx->hist_cursors.release();
   ctx->hist_cursors_snap.release();
@@ -819,6 +823,7 @@ static int complete_decode(hbt_ctx* ctx) {
   }
   ctx->cur ^= 1;
   ctx->sw_valid = false;
+  ctx->sw_merged = nullptr;
   SwParams sp{};
   if (ctx->desc.aggregate == HBT_AGG_SWITCH_EVENTS) {
     // pass 2 of the event stream: counts and offsets now, the events once their number is known
@@ -1002,6 +1007,46 @@ int hbt_switch_events_dev(hbt_ctx* ctx, const hbt_switch_event** events, uint64_
   *events = ctx->sw_events.p;
   memcpy(offsets, ctx->h_sw_off.p, (ctx->n_cpus + 1) * sizeof(uint64_t));
   return 0;
+}
+
+int hbt_switch_events_merged_dev(hbt_ctx* ctx, const hbt_switch_event** merged, uint64_t* n_events) {
+  if (!ctx || !merged || !n_events) return -EINVAL;
+  if (int rc = complete_decode(ctx)) return rc;
+  if (!ctx->sw_valid) return fail(ctx, -EINVAL, "no SWITCH_EVENTS decode to read");
+  const uint32_t C = ctx->n_cpus;
+  const uint64_t total = ctx->h_sw_off.p[C];
+  *n_events = total;
+  if (!ctx->sw_merged) {
+    const hbt_switch_event* cur = ctx->sw_events.p;
+    if (total) {
+      int which = 0;
+      for (uint32_t run = 1; run < C; run *= 2, which ^= 1) {
+        CU(ctx->sw_merge[which].reserve(total));
+        const uint64_t threads = (total + kMergeK - 1) / kMergeK;
+        k_sw_merge<<<(unsigned)((threads + 255) / 256), 256, 0, ctx->stream>>>(
+            reinterpret_cast<const ulonglong2*>(cur),
+            reinterpret_cast<ulonglong2*>(ctx->sw_merge[which].p), ctx->d_sw_off.p, C, run);
+        ++ctx->launches;
+        cur = ctx->sw_merge[which].p;
+      }
+      CU(cudaGetLastError());
+    }
+    ctx->sw_merged = cur;
+  }
+  *merged = ctx->sw_merged;
+  return 0;
+}
+
+int64_t hbt_fetch_switch_events_merged(hbt_ctx* ctx, hbt_switch_event* out, uint64_t cap) {
+  if (!out) return -EINVAL;
+  const hbt_switch_event* m = nullptr;
+  uint64_t n = 0;
+  if (int rc = hbt_switch_events_merged_dev(ctx, &m, &n)) return rc;
+  if (n > cap) return fail(ctx, -ENOSPC, "cap %llu < %llu events", (unsigned long long)cap,
+                           (unsigned long long)n);
+  if (n) CU(cudaMemcpyAsync(out, m, n * sizeof(hbt_switch_event), cudaMemcpyDeviceToHost, ctx->stream));
+  CU(cudaStreamSynchronize(ctx->stream));
+  return (int64_t)n;
 }
 
 int hbt_fetch_carry(hbt_ctx* ctx, uint32_t cpu, uint64_t* last, uint32_t n_events) {

@@ -307,6 +307,14 @@ int64_t hbt_fetch_switch_events(hbt_ctx* ctx, uint32_t cpu, hbt_switch_event* ou
 /* Device view: all CPUs' events back to back, CPU c at [offsets[c], offsets[c+1])
  * (offsets: host array of n_cpus + 1 entries, filled by the call). */
 int hbt_switch_events_dev(hbt_ctx* ctx, const hbt_switch_event** events, uint64_t* offsets);
+/* The per-CPU streams of that decode merged into one, in the order the reference's
+ * binary tree of stream::Combinator nodes delivers them (hbt/src/tagstack/Stream.h:114-248,
+ * makeBinaryTree :190-230): Event::happenedBefore = timestamp, then comp_unit_id
+ * (Event.h:205-213).  Requires what the Combinator itself assumes: each CPU's stream is
+ * timestamp-ordered.  The merge runs on the first call after a decode (log2(n_cpus)
+ * launches) and the result stays valid until the next decode. */
+int hbt_switch_events_merged_dev(hbt_ctx* ctx, const hbt_switch_event** merged, uint64_t* n_events);
+int64_t hbt_fetch_switch_events_merged(hbt_ctx* ctx, hbt_switch_event* out, uint64_t cap);
 
 /* Device view of the same rows for downstream kernels: rows of `cpu` live in
  * *n_slabs slabs; slab i has n_rows[i] rows at ptr[i].  Arrays must hold

@@ -296,6 +296,49 @@ def map_tids_to_vids(per_cpu_events):
     return out
 
 
+def combinator_merge(streams):
+    """Test-side restatement of the reference's binary tree of stream::Combinator nodes
+    (hbt/src/tagstack/Stream.h:114-248, makeBinaryTree :190-230) draining `streams` (one
+    SWITCH_EVENT_DTYPE array per compute unit) with stop_ts = infinity: every node caches one
+    event per input and hands out `a.happenedBefore(b) ? a : b` (Event.h:205-213); an
+    exhausted input counts as (kInvalidTimeStamp, max comp_unit_id)."""
+    INV = (0xFFFFFFFFFFFFFFFF, 0xFFFF)
+
+    def leaf(arr):
+        for i in range(len(arr)):
+            yield arr[i]
+
+    def before(a, b):
+        ka = (int(a["tstamp"]), int(a["comp_unit_id"])) if a is not None else INV
+        kb = (int(b["tstamp"]), int(b["comp_unit_id"])) if b is not None else INV
+        if ka[0] > kb[0]:
+            return False
+        return ka[0] < kb[0] or ka[1] < kb[1]
+
+    def node(ga, gb):
+        ea = next(ga, None)
+        eb = next(gb, None) if gb is not None else None
+        while ea is not None or eb is not None:
+            if before(ea, eb):
+                yield ea
+                ea = next(ga, None)
+            else:
+                yield eb
+                eb = next(gb, None)
+
+    level = [leaf(s) for s in streams]
+    while True:
+        nxt = [node(level[i], level[i + 1] if i + 1 < len(level) else None)
+               for i in range(0, len(level), 2)]
+        if len(nxt) == 1:
+            out = list(nxt[0])
+            res = np.zeros(len(out), dtype=hbt.SWITCH_EVENT_DTYPE)
+            for i, e in enumerate(out):
+                res[i] = e
+            return res
+        level = nxt
+
+
 def counts_outputs(I, E, R):
     return dict(sums=np.zeros((I, 3 + E), np.uint64), scaled=np.zeros((I, E), np.uint64),
                 rates=np.zeros((I, E), np.float32), ratios=np.zeros((I, max(R, 1)), np.float64),

@@ -118,6 +118,38 @@ def test_oracle_event_semantics(built):
     assert got["ret"] == -1 and got["n_records"] == 1 and len(got["events"]) == 1
 
 
+def test_combinator_restatement_known_answers(built):
+    """hbt/src/tagstack/tests/StreamTest.cpp:61-130 (BinaryCombinator): e1..e6 come out in
+    that order; equal timestamps are ordered by comp_unit_id."""
+    def ev(ts, t, lvl, tag, cu):
+        a = np.zeros(1, dtype=hbt.SWITCH_EVENT_DTYPE)
+        a[0] = (ts, t, lvl, cu, tag)
+        return a
+    NA = hbt.TAG_NA
+    e1 = ev(20, hbt.SWEV_SWITCH_IN, 0, 2, 2)
+    e2 = ev(21, hbt.SWEV_SWITCH_OUT_PREEMPT, 0, NA, 2)
+    e3 = ev(24, hbt.SWEV_SWITCH_IN, 1, 2, 1)
+    e4 = ev(30, hbt.SWEV_SWITCH_OUT_PREEMPT, 1, NA, 1)
+    e5 = ev(30, hbt.SWEV_SWITCH_IN, 1, 5, 2)
+    e6 = ev(31, hbt.SWEV_SWITCH_OUT_PREEMPT, 1, NA, 1)
+    got = orc.combinator_merge([np.concatenate([e3, e4, e6]), np.concatenate([e1, e2, e5])])
+    assert same_events(got, np.concatenate([e1, e2, e3, e4, e5, e6]))
+    # five streams (odd node at two levels) against a stable sort by (tstamp, comp_unit_id)
+    rng = np.random.default_rng(5)
+    streams = []
+    for cu in range(5):
+        n = int(rng.integers(0, 40))
+        a = np.zeros(n, dtype=hbt.SWITCH_EVENT_DTYPE)
+        a["tstamp"] = np.sort(rng.integers(0, 50, n))
+        a["comp_unit_id"] = cu
+        a["tag"] = np.arange(n)
+        streams.append(a)
+    got = orc.combinator_merge(streams)
+    allev = np.concatenate(streams)
+    want = allev[np.lexsort((allev["comp_unit_id"], allev["tstamp"]))]
+    assert same_events(got, want)
+
+
 # ---------------------------------------------------------------------------
 # CUDA path vs oracle
 # ---------------------------------------------------------------------------
@@ -244,3 +276,32 @@ def test_gpu_switch_events_short_record_and_foreign_types(ctx):
     want = orc.port_switch_events(ring, 0, head, d)
     assert want["ret"] == -1 and want["n_records"] == 1234
     check(res, ev, want, 0)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("n_cpus,n_records", [(1, 500), (2, 800), (5, 700), (8, 3000), (13, 1500), (64, 400)])
+def test_gpu_switch_events_merged(ctx, n_cpus, n_records):
+    """k-way merge of the per-CPU streams = the Combinator tree's order."""
+    ds = 1 << 18
+    d = hbt.switch_desc(tid_level=1)
+    rings = []
+    for c in range(n_cpus):
+        # no LOST: a WriteErrorsEnd carries the LOST record's own (later) timestamp, all
+        # other events are in timestamp order; CPUs share the time base so streams interleave
+        n = n_records if c != 1 else 0
+        s = tg.ctx_switch_stream(5000 + c, max(n, 1), mix=(("switch", 0.8), ("fork", 0.1), ("exit", 0.1)),
+                                 t0=1_000_000 + 37 * c)
+        if n == 0:
+            s = s[:0]
+        tail = tg.random_tail(300 + c, ds)
+        ring, head = ring_np(s, ds, tail, fill=3)
+        rings.append((ring, tail, head))
+    res, ev = gpu_switch(ctx, rings, d, ds, cpu_base=3)
+    merged = ctx.fetch_switch_events_merged()
+    assert len(merged) == sum(len(e) for e in ev)
+    if n_cpus <= 13:
+        assert same_events(merged, orc.combinator_merge(ev))
+    allev = np.concatenate(ev)
+    assert same_events(merged, allev[np.lexsort((allev["comp_unit_id"], allev["tstamp"]))])
+    # asking again returns the cached result
+    assert same_events(ctx.fetch_switch_events_merged(), merged)
