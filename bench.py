@@ -18,6 +18,7 @@ inside the timed region.  `--impl reference` times the reference's own consume()
 from __future__ import annotations
 
 import argparse
+import ctypes as C
 import json
 import os
 import statistics
@@ -269,6 +270,14 @@ def bench_deltas(args, rank, world, local, dev, dist):
         # span is the whole device-timed step; n_rows counts 16-byte events
         algo = window_bytes + n_rows * 16
         ach = algo / (ms_step * 1e-3) / 1e9
+        # the Combinator-tree merge of the per-CPU streams, timed once on its own
+        m0, m1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        base, n_ev = C.c_void_p(), C.c_uint64()
+        m0.record()
+        ctx._ck(ctx.lib.hbt_switch_events_merged_dev(ctx.h, C.byref(base), C.byref(n_ev)))
+        m1.record()
+        torch.cuda.synchronize()
+        merge_ms = m0.elapsed_time(m1)
         return {"metric": METRIC, "value": n_rec * world / (ms_step * 1e-3), "unit": UNIT, "n_gpus": world,
                 "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms_step,
                 "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u64",
@@ -276,6 +285,7 @@ def bench_deltas(args, rank, world, local, dev, dist):
                 "config": {"workload": "c4_switch: mode::ContextSwitch records (32-48 B) -> tagstack::Event stream",
                            "cpus_per_gpu": args.cpus, "ring_mib": args.ring_mib, "records_per_gpu": n_rec,
                            "events_per_gpu": n_rows, "window_bytes_per_gpu": int(window_bytes),
+                           "merge_ms": merge_ms, "merge_levels": max(0, (args.cpus - 1).bit_length()),
                            "l2": "inputs exceed L2; no flush needed", "slow_tiles": ctx.slow_tiles,
                            "reruns": ctx.reruns},
                 "roofline": {"bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
