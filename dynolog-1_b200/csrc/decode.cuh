@@ -237,7 +237,16 @@ __device__ __forceinline__ ulonglong2 sw_proto(uint64_t h, uint32_t level, uint3
 }
 
 __device__ __forceinline__ uint32_t hist_hash(uint64_t ip, uint32_t pid) {
-  return (uint32_t)(mix64(ip ^ ((uint64_t)pid * 0x9E3779B97F4A7C15ull)) >> 32);
+  // 32-bit multiply-mix (murmur3 finaliser): the top bits choose the list, the low bits
+  // the cache set, all of it the cache tag.  64-bit multiplies would cost three times
+  // as many instructions on the per-sample path.
+  uint32_t x = (uint32_t)ip * 0xCC9E2D51u + (uint32_t)(ip >> 32) * 0x1B873593u + pid * 0xE6546B64u;
+  x ^= x >> 16;
+  x *= 0x85EBCA6Bu;
+  x ^= x >> 13;
+  x *= 0xC2B2AE35u;
+  x ^= x >> 16;
+  return x;
 }
 
 // Append one sample to the list of its bucket: one atomic on a cursor that lives
