@@ -191,6 +191,30 @@ def make_switch_rings(n_cpus: int, ring_bytes: int, cpu_base: int, device):
     return imgs, tails, heads, n * n_cpus
 
 
+def bind_to_gpu_cpus(local: int):
+    """Run this rank (and first-touch its pinned host buffers) on the CPUs next to its GPU:
+    with several ranks uploading at once, host buffers on the far socket halve the PCIe rate.
+    Returns the CPU list used, or None when NVML has nothing to say."""
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        try:  # CUDA ordinal -> NVML handle through the PCI address (CUDA_VISIBLE_DEVICES may reorder)
+            pr = torch.cuda.get_device_properties(local)
+            h = pynvml.nvmlDeviceGetHandleByPciBusId(
+                f"{pr.pci_domain_id:08x}:{pr.pci_bus_id:02x}:{pr.pci_device_id:02x}.0")
+        except Exception:
+            h = pynvml.nvmlDeviceGetHandleByIndex(local)
+        words = pynvml.nvmlDeviceGetCpuAffinity(h, (os.cpu_count() + 63) // 64)
+        near = {64 * i + b for i, w in enumerate(words) for b in range(64) if (int(w) >> b) & 1}
+        cpus = sorted(near & os.sched_getaffinity(0))
+        if cpus:
+            os.sched_setaffinity(0, cpus)
+            return cpus
+    except Exception:
+        pass
+    return None
+
+
 def timed_steps(step, steps, dist, dev):
     """CUDA-event timing of `steps` calls of step(), barrier + sync on both sides, max over ranks."""
     if dist is not None:
@@ -481,6 +505,8 @@ def main():
 
     assert torch.cuda.is_available(), "bench.py needs a GPU (there is no CPU fallback)"
     torch.cuda.set_device(local)
+    all_cpus = os.sched_getaffinity(0)
+    numa = bind_to_gpu_cpus(local)
     dev = torch.device("cuda", local)
     # everything (torch ops, the library's kernels, the timing events) runs on ONE
     # non-default stream, so torch.cuda.Event sees the kernels it brackets
@@ -653,7 +679,8 @@ def main():
         e2e = {"value": n_rec * world / dt, "unit": UNIT, "h2d_bytes_per_step": int(window_bytes),
                "d2h_bytes_per_step": int(n_ent * ent_dt + r.nbytes), "ms_per_step": dt * 1e3,
                "pipeline": f"{len(groups)} CPU groups, one hbt_ctx + stream each: H2D of group g+1 "
-                           "overlaps decode + fold + D2H of group g"}
+                           "overlaps decode + fold + D2H of group g",
+               "host_cpus_bound": len(numa) if numa else None}
         for cg, *_ in groups:
             cg.close()
 
@@ -692,6 +719,7 @@ def main():
     if e2e:
         line["e2e"] = e2e
     if world == 1 and not args.no_cpu_baseline:
+        os.sched_setaffinity(0, all_cpus)  # the CPU baseline gets every host core again
         cb = cpu_baseline_leg(args)
         if cb:
             line["cpu_baseline"] = cb
