@@ -297,6 +297,9 @@ def bench_deltas(args, rank, world, local, dev, dist):
         # the Combinator-tree merge of the per-CPU streams, timed once on its own
         m0, m1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         base, n_ev = C.c_void_p(), C.c_uint64()
+        ctx._ck(ctx.lib.hbt_switch_events_merged_dev(ctx.h, C.byref(base), C.byref(n_ev)))  # allocates
+        step()
+        torch.cuda.synchronize()
         m0.record()
         ctx._ck(ctx.lib.hbt_switch_events_merged_dev(ctx.h, C.byref(base), C.byref(n_ev)))
         m1.record()

@@ -1751,56 +1751,68 @@ static __global__ void __launch_bounds__(256) k_sw_emit(const SwParams p) {
 // output when each CPU's stream is timestamp-ordered, which the Combinator itself assumes
 // (its DCHECKs, Stream.h:139-141).
 // ---------------------------------------------------------------------------
-constexpr uint32_t kMergeK = 8;
+constexpr uint32_t kMergeK = 8;                 // outputs per thread
+constexpr uint32_t kMergeTile = 256 * kMergeK;  // outputs per CTA
 
 __device__ __forceinline__ bool ev_before(const ulonglong2& a, const ulonglong2& b) {
   if (a.x != b.x) return a.x < b.x;
   return (uint32_t)((a.y >> 16) & 0xFFFF) < (uint32_t)((b.y >> 16) & 0xFFFF);
 }
 
+// merge path: how many of the first d outputs of merge(A[0..la), B[0..lb)) come from A
+template <class TA, class TB>
+__device__ __forceinline__ uint64_t merge_path(TA A, uint64_t la, TB B, uint64_t lb, uint64_t d) {
+  uint64_t il = d > lb ? d - lb : 0, ih = min(d, la);
+  while (il < ih) {
+    const uint64_t mid = (il + ih) >> 1;
+    if (ev_before(A[mid], B[d - 1 - mid])) il = mid + 1;
+    else ih = mid;
+  }
+  return il;
+}
+
+// tile_prefix[p] = first CTA of pair p (host-computed from the offsets), [n_pairs] = grid size.
+// A CTA merges kMergeTile consecutive outputs of its pair: two binary searches in global
+// memory cut the pair's inputs at the tile's diagonals, the two input pieces (together
+// exactly one tile) are staged in shared memory with coalesced loads, and every thread
+// merges its kMergeK outputs from there.
 static __global__ void __launch_bounds__(256)
     k_sw_merge(const ulonglong2* __restrict__ in, ulonglong2* __restrict__ out,
-               const uint64_t* __restrict__ offsets, uint32_t n_cpus, uint32_t run) {
-  const uint64_t total = offsets[n_cpus];
-  uint64_t pos = ((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) * kMergeK;
-  const uint64_t end = min(pos + kMergeK, total);
-  const uint32_t n_pairs = (n_cpus + 2 * run - 1) / (2 * run);
-  while (pos < end) {
-    // the pair whose output range holds pos: largest p with offsets[2 p run] <= pos
-    uint32_t lo = 0, hi = n_pairs - 1;
-    while (lo < hi) {
-      const uint32_t mid = (lo + hi + 1) >> 1;
-      if (offsets[min(2 * mid * run, n_cpus)] <= pos) lo = mid;
-      else hi = mid - 1;
-    }
-    const uint64_t a0 = offsets[min(2 * lo * run, n_cpus)];
-    const uint64_t b0 = offsets[min((2 * lo + 1) * run, n_cpus)];
-    const uint64_t b1 = offsets[min((2 * lo + 2) * run, n_cpus)];
-    const uint64_t la = b0 - a0, lb = b1 - b0;
-    const ulonglong2* A = in + a0;
-    const ulonglong2* B = in + b0;
-    const uint64_t d = pos - a0;  // diagonal: d elements of this pair come before pos
-    // merge path: smallest i with !(A[i] before B[d-1-i])
-    uint64_t il = d > lb ? d - lb : 0, ih = min(d, la);
-    while (il < ih) {
-      const uint64_t mid = (il + ih) >> 1;
-      if (ev_before(A[mid], B[d - 1 - mid])) il = mid + 1;
-      else ih = mid;
-    }
-    uint64_t ai = il, bi = d - il;
-    const uint64_t stop = min(end, b1);
-    ulonglong2 ea = ai < la ? A[ai] : make_ulonglong2(0, 0);
-    ulonglong2 eb = bi < lb ? B[bi] : make_ulonglong2(0, 0);
-    for (; pos < stop; ++pos) {
-      const bool take_a = bi >= lb || (ai < la && ev_before(ea, eb));
-      if (take_a) {
-        out[pos] = ea;
-        if (++ai < la) ea = A[ai];
-      } else {
-        out[pos] = eb;
-        if (++bi < lb) eb = B[bi];
-      }
-    }
+               const uint64_t* __restrict__ offsets, uint32_t n_cpus, uint32_t run,
+               const uint32_t* __restrict__ tile_prefix, uint32_t n_pairs) {
+  __shared__ ulonglong2 s_ev[kMergeTile];
+  __shared__ uint64_t s_cut[2];
+  const uint32_t tid = threadIdx.x;
+  uint32_t lo = 0, hi = n_pairs - 1;
+  while (lo < hi) {  // largest p with tile_prefix[p] <= blockIdx.x
+    const uint32_t mid = (lo + hi + 1) >> 1;
+    if (tile_prefix[mid] <= blockIdx.x) lo = mid;
+    else hi = mid - 1;
+  }
+  const uint64_t a0 = offsets[min(2 * lo * run, n_cpus)];
+  const uint64_t b0 = offsets[min((2 * lo + 1) * run, n_cpus)];
+  const uint64_t b1 = offsets[min((2 * lo + 2) * run, n_cpus)];
+  const uint64_t la = b0 - a0, lb = b1 - b0;
+  const ulonglong2* A = in + a0;
+  const ulonglong2* B = in + b0;
+  const uint64_t d0 = (uint64_t)(blockIdx.x - tile_prefix[lo]) * kMergeTile;
+  const uint64_t d1 = min(d0 + kMergeTile, la + lb);
+  if (tid < 2) s_cut[tid] = merge_path(A, la, B, lb, tid == 0 ? d0 : d1);
+  __syncthreads();
+  const uint64_t i0 = s_cut[0], i1 = s_cut[1];
+  const uint32_t na = (uint32_t)(i1 - i0), n = (uint32_t)(d1 - d0), nb = n - na;
+  for (uint32_t i = tid; i < n; i += 256) s_ev[i] = i < na ? A[i0 + i] : B[(d0 - i0) + (i - na)];
+  __syncthreads();
+  const ulonglong2* sA = s_ev;
+  const ulonglong2* sB = s_ev + na;
+  const uint32_t dd = min(tid * kMergeK, n);
+  uint32_t ai = (uint32_t)merge_path(sA, (uint64_t)na, sB, (uint64_t)nb, (uint64_t)dd);
+  uint32_t bi = dd - ai;
+  ulonglong2* o = out + a0 + d0 + dd;
+  const uint32_t cnt = min(kMergeK, n - dd);
+  for (uint32_t j = 0; j < cnt; ++j) {
+    const bool take_a = bi >= nb || (ai < na && ev_before(sA[ai], sB[bi]));
+    o[j] = take_a ? sA[ai++] : sB[bi++];
   }
 }
 

@@ -129,6 +129,8 @@ struct hbt_ctx {
   PinBuf<uint64_t> h_sw_off;
   DevBuf<hbt_switch_event> sw_events;
   DevBuf<hbt_switch_event> sw_merge[2];       // ping-pong buffers of the Combinator tree levels
+  DevBuf<uint32_t> d_merge_prefix;
+  PinBuf<uint32_t> h_merge_prefix;
   const hbt_switch_event* sw_merged = nullptr;  // result of the last merge, nullptr = not merged yet
   bool sw_valid = false;  // sw_events / h_sw_off describe the last fetched decode
 
@@ -573,6 +575,8 @@ void hbt_destroy(hbt_ctx* ctx) {
   ctx->sw_events.release();
   ctx->sw_merge[0].release();
   ctx->sw_merge[1].release();
+  ctx->d_merge_prefix.release();
+  ctx->h_merge_prefix.release();
   ctx->hist_entries.release();
   ctx->hist_cursors.release();
   ctx->hist_cursors_snap.release();
@@ -1020,12 +1024,36 @@ int hbt_switch_events_merged_dev(hbt_ctx* ctx, const hbt_switch_event** merged, 
     const hbt_switch_event* cur = ctx->sw_events.p;
     if (total) {
       int which = 0;
-      for (uint32_t run = 1; run < C; run *= 2, which ^= 1) {
+      // per level: first CTA of every pair of runs (one CTA per kMergeTile outputs)
+      std::vector<uint32_t> prefix;
+      std::vector<uint32_t> level_at;
+      for (uint32_t run = 1; run < C; run *= 2) {
+        level_at.push_back((uint32_t)prefix.size());
+        const uint32_t n_pairs = (C + 2 * run - 1) / (2 * run);
+        uint32_t acc = 0;
+        for (uint32_t p = 0; p < n_pairs; ++p) {
+          prefix.push_back(acc);
+          const uint32_t lo = std::min(2 * p * run, C), hi = std::min((2 * p + 2) * run, C);
+          const uint64_t len = ctx->h_sw_off.p[hi] - ctx->h_sw_off.p[lo];
+          acc += (uint32_t)((len + kMergeTile - 1) / kMergeTile);
+        }
+        prefix.push_back(acc);
+      }
+      CU(ctx->d_merge_prefix.reserve(prefix.size() ? prefix.size() : 1));
+      CU(ctx->h_merge_prefix.reserve(prefix.size() ? prefix.size() : 1));
+      memcpy(ctx->h_merge_prefix.p, prefix.data(), prefix.size() * sizeof(uint32_t));
+      CU(cudaMemcpyAsync(ctx->d_merge_prefix.p, ctx->h_merge_prefix.p, prefix.size() * sizeof(uint32_t),
+                         cudaMemcpyHostToDevice, ctx->stream));
+      uint32_t level = 0;
+      for (uint32_t run = 1; run < C; run *= 2, which ^= 1, ++level) {
         CU(ctx->sw_merge[which].reserve(total));
-        const uint64_t threads = (total + kMergeK - 1) / kMergeK;
-        k_sw_merge<<<(unsigned)((threads + 255) / 256), 256, 0, ctx->stream>>>(
-            reinterpret_cast<const ulonglong2*>(cur),
-            reinterpret_cast<ulonglong2*>(ctx->sw_merge[which].p), ctx->d_sw_off.p, C, run);
+        const uint32_t n_pairs = (C + 2 * run - 1) / (2 * run);
+        const uint32_t* pre = ctx->d_merge_prefix.p + level_at[level];
+        const uint32_t grid = prefix[level_at[level] + n_pairs];
+        if (grid)
+          k_sw_merge<<<grid, 256, 0, ctx->stream>>>(
+              reinterpret_cast<const ulonglong2*>(cur),
+              reinterpret_cast<ulonglong2*>(ctx->sw_merge[which].p), ctx->d_sw_off.p, C, run, pre, n_pairs);
         ++ctx->launches;
         cur = ctx->sw_merge[which].p;
       }
