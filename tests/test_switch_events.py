@@ -305,3 +305,50 @@ def test_gpu_switch_events_merged(ctx, n_cpus, n_records):
     assert same_events(merged, allev[np.lexsort((allev["comp_unit_id"], allev["tstamp"]))])
     # asking again returns the cached result
     assert same_events(ctx.fetch_switch_events_merged(), merged)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("ds", [4096, 16384, 32768])
+def test_gpu_switch_events_small_rings_and_empty_windows(ctx, ds):
+    """Rings too small to tile take the one-thread path (k_decode_small); empty windows
+    produce no events and leave the generator state alone."""
+    d = hbt.switch_desc(tid_level=3)
+    rings = []
+    for c in range(4):
+        n = 0 if c == 2 else (ds // 40) - 8
+        s = tg.ctx_switch_stream(600 + c, max(n, 1), mix=(("switch", 0.6), ("lost", 0.2), ("comm", 0.2)))
+        s = s[:0] if n == 0 else s[: (ds // 8) - 8]
+        # cut at a record boundary: walk the headers
+        w = s.numpy().view(np.uint64)
+        pos = 0
+        while pos < len(w) and pos + int(w[pos] >> np.uint64(51)) <= len(w):
+            pos += int(w[pos] >> np.uint64(51))
+        s = s[:pos]
+        tail = 8 * (ds // 16 + c)
+        ring, head = ring_np(s, ds, tail, fill=2)
+        rings.append((ring, tail, head))
+    res, ev = gpu_switch(ctx, rings, d, ds)
+    for c, (ring, tail, head) in enumerate(rings):
+        check(res, ev, orc.port_switch_events(ring, tail, head, d, cpu=c), c)
+    assert int(res[2]["n_rows"]) == 0 and int(res[2]["ret"]) == -61
+
+
+@pytest.mark.gpu
+def test_gpu_switch_events_payload_like_headers(ctx):
+    """COMM names filled with bytes that look like record headers: segment-entry guesses go
+    wrong and the batch is re-run with forced entries; the events must not change."""
+    ds = 1 << 20
+    d = hbt.switch_desc(tid_level=0)
+    s = tg.ctx_switch_stream(4242, 20000, mix=(("comm", 0.5), ("switch", 0.5))).numpy().view(np.uint64).copy()
+    pos = 0
+    fake = np.uint64(15 | (32 << 48))  # a plausible SWITCH_CPU_WIDE header of 32 bytes
+    while pos < len(s):
+        words = int(s[pos] >> np.uint64(51))
+        if int(s[pos] & np.uint64(0xFFFFFFFF)) == 3:  # COMM: hdr, pid/tid, name..., sample_id(2)
+            for k in range(2, words - 2):
+                s[pos + k] = fake
+        pos += words
+    import torch
+    ring, head = ring_np(torch.from_numpy(s.view(np.int64)), ds, 8 * 5)
+    res, ev = gpu_switch(ctx, [(ring, 8 * 5, head)], d, ds)
+    check(res, ev, orc.port_switch_events(ring, 8 * 5, head, d), 0)
