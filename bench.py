@@ -470,9 +470,16 @@ def cpu_baseline_leg(args):
                                heads_a.ctypes.data, sample_cpus, 40, hbt.DRAIN, cores, res)
         best = t if best is None else min(best, t)
     lib.hbtref_hist_free(h)
+    # one thread, as the reference runs it (one collecting thread), on 4 of the rings
+    one = min(4, sample_cpus)
+    h1 = lib.hbtref_hist_new()
+    t1 = lib.hbtref_ip_hist(h1, rings.ctypes.data, ring_bytes, tails_a.ctypes.data, heads_a.ctypes.data,
+                            one, 40, hbt.DRAIN, 1, res)
+    lib.hbtref_hist_free(h1)
     return {"value": n_rec / best, "unit": UNIT, "cores": cores, "kind": "reference",
             "sample": f"{sample_cpus} of {args.cpus} rings x {args.ring_mib} MiB, best of 2; "
-                      "reference consume() + std::unordered_map handler"}
+                      "reference consume() + std::unordered_map handler",
+            "single_thread_value": (n_rec // sample_cpus) * one / t1 if t1 > 0 else None}
 
 
 def main():
