@@ -601,11 +601,15 @@ __global__ void __launch_bounds__(kThreads, AGG == HBT_AGG_IP_HISTOGRAM && kCach
   const uint64_t seg_limit = min(seg.tile_end * (uint64_t)kTile, ring.head);
   const uint64_t policy = l2_policy_evict_first();
 
+  // shared-space addresses, computed once and kept (see pin_u32)
+  uint32_t stages_u32 = smem_u32(stages), bar_u32 = smem_u32(&sm.bar[0]);
+  pin_u32(stages_u32);
+  pin_u32(bar_u32);
   auto issue = [&](uint32_t k, uint32_t stage) {  // tile k of this segment (k == n_tiles: lookahead)
     const uint64_t t = seg.tile_begin + k;
-    mbar_arrive_expect_tx(&sm.bar[stage], kTile);
-    bulk_g2s_hint(stages + stage * kTile, ring.base + ((t * (uint64_t)kTile) & ring.mask), kTile,
-                  &sm.bar[stage], policy);
+    mbar_arrive_expect_tx_u32(bar_u32 + 8 * stage, kTile);
+    bulk_g2s_hint_u32(stages_u32 + stage * kTile, ring.base + ((t * (uint64_t)kTile) & ring.mask), kTile,
+                      bar_u32 + 8 * stage, policy);
   };
   // stage of tile k is k % kStages (tile numbering local to the segment)
   if (tid == 0) {
@@ -626,9 +630,17 @@ __global__ void __launch_bounds__(kThreads, AGG == HBT_AGG_IP_HISTOGRAM && kCach
   HistPending pend;  // IP_HISTOGRAM: appends whose cursor atomics are in flight
   // COUNT_DELTAS row writer (uniform fast path): this thread's fixed word column and first row
   const uint32_t rw_wpr = 2 + d.n_events;
-  const uint32_t rw_rows = kThreads / rw_wpr;  // whole rows per pass (n_events <= 64: >= 3)
-  const uint32_t rw_r0 = tid / rw_wpr, rw_w = tid - rw_r0 * rw_wpr;
-  const bool rw_active = tid < rw_rows * rw_wpr;
+  // {first row, word column, rows per pass, active}: packed and pinned, or the compiler
+  // re-derives them with two integer divisions in every tile
+  uint32_t rw_pack;
+  {
+    const uint32_t rows = kThreads / rw_wpr;  // whole rows per pass (n_events <= 64: >= 3)
+    const uint32_t r0 = tid / rw_wpr;
+    rw_pack = r0 | ((tid - r0 * rw_wpr) << 8) | (rows << 16) | ((tid < rows * rw_wpr ? 1u : 0u) << 24);
+    pin_u32(rw_pack);
+  }
+  const uint32_t rw_r0 = rw_pack & 0xFF, rw_w = (rw_pack >> 8) & 0xFF, rw_rows = (rw_pack >> 16) & 0xFF;
+  const bool rw_active = (rw_pack >> 24) != 0;
 
   // my sub-chunk, in tile-relative bytes
   const uint32_t sb = 8u * sub_begin_word(tid);
@@ -642,14 +654,14 @@ __global__ void __launch_bounds__(kThreads, AGG == HBT_AGG_IP_HISTOGRAM && kCach
     // round ordered every read of it before this copy
     if (tid == 0 && k + 2 <= n_tiles) issue(k + 2, sc_i);
     if (k == 0) {
-      mbar_wait(&sm.bar[sa_i], (phase_bits >> sa_i) & 1);
+      mbar_wait_u32(bar_u32 + 8 * sa_i, (phase_bits >> sa_i) & 1);
       phase_bits ^= 1u << sa_i;
     }
-    mbar_wait(&sm.bar[sb_i], (phase_bits >> sb_i) & 1);
+    mbar_wait_u32(bar_u32 + 8 * sb_i, (phase_bits >> sb_i) & 1);
     phase_bits ^= 1u << sb_i;
 
     const uint64_t t_begin = (seg.tile_begin + k) * (uint64_t)kTile;
-    TileView tv{smem_u32(stages + sa_i * kTile), smem_u32(stages + sb_i * kTile) - (uint32_t)kTile,
+    TileView tv{stages_u32 + sa_i * (uint32_t)kTile, stages_u32 + sb_i * (uint32_t)kTile - (uint32_t)kTile,
                 t_begin, &ring};
     // tile-uniform limits, tile-relative: record starts must be < lim; bytes up to
     // look (<= 2*kTile) are resident and inside the window

@@ -79,6 +79,35 @@ __device__ __forceinline__ void bulk_g2s_hint(void* smem_dst, const void* gmem_s
       : "memory");
 }
 
+// Variants taking shared-space addresses computed once (smem_u32 is a generic->shared
+// conversion the compiler otherwise re-emits at every use when registers are tight), and
+// pin_u32: an empty volatile asm that makes a value opaque, so that it is kept in its
+// register instead of being recomputed (an integer division, a cvta) inside the hot loop.
+__device__ __forceinline__ void pin_u32(uint32_t& v) { asm volatile("" : "+r"(v)); }
+__device__ __forceinline__ void mbar_arrive_expect_tx_u32(uint32_t bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait_u32(uint32_t bar, uint32_t parity) {
+  uint32_t ok;
+  do {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(ok)
+        : "r"(bar), "r"(parity)
+        : "memory");
+  } while (!ok);
+}
+__device__ __forceinline__ void bulk_g2s_hint_u32(uint32_t smem_dst, const void* gmem_src, uint32_t bytes,
+                                                  uint32_t bar, uint64_t policy) {
+  asm volatile(
+      "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint "
+      "[%0], [%1], %2, [%3], %4;" ::"r"(smem_dst),
+      "l"(gmem_src), "r"(bytes), "r"(bar), "l"(policy)
+      : "memory");
+}
+
 __device__ __forceinline__ uint64_t lds_u64(uint32_t saddr) {
   uint64_t v;
   asm volatile("ld.shared.u64 %0, [%1];" : "=l"(v) : "r"(saddr) : "memory");
