@@ -546,9 +546,12 @@ __device__ __forceinline__ uint32_t sub_of_word(uint32_t w) {
 
 template <int AGG>
 #ifndef HBT_MIN_BLOCKS
-#define HBT_MIN_BLOCKS 4
+#define HBT_MIN_BLOCKS 4       // CTAs per SM the register budget must allow
 #endif
-__global__ void __launch_bounds__(kThreads, AGG == HBT_AGG_IP_HISTOGRAM && kCacheSlots > 256 ? 3 : HBT_MIN_BLOCKS) k_decode(const DecodeParams p) {
+#ifndef HBT_HIST_MIN_BLOCKS
+#define HBT_HIST_MIN_BLOCKS 3  // IP_HISTOGRAM: the segment cache leaves room for three
+#endif
+__global__ void __launch_bounds__(kThreads, AGG == HBT_AGG_IP_HISTOGRAM ? HBT_HIST_MIN_BLOCKS : HBT_MIN_BLOCKS) k_decode(const DecodeParams p) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   uint8_t* stages = smem_raw;  // kStages * kTile
   Smem& sm = *reinterpret_cast<Smem*>(smem_raw + kStages * kTile);
