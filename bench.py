@@ -289,7 +289,7 @@ def bench_deltas(args, rank, world, local, dev, dist):
     peak, peak_src = load_peaks()
     k_ms = sum(kms) / len(kms)
     algo = window_bytes + n_rows * 8 * (2 + E)
-    if switch:
+    if switch and args.agg != "none":
         # two passes (proto-events, then the prefix sum that places WriteErrorsEnd events): the
         # span is the whole device-timed step; n_rows counts 16-byte events
         algo = window_bytes + n_rows * 16

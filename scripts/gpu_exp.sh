@@ -1,6 +1,6 @@
 #!/bin/bash
-for w in c4_mixed c4_switch; do
-timeout 600 python bench.py --steps 3 --warmup 3 --no-e2e --no-cpu-baseline --workload $w --cpus 32 --ring-mib 1024 > gpurun_out/last.log 2>&1; python -c "
-import json; d=json.loads(open('gpurun_out/last.log').read().strip().splitlines()[-1]); r=d['roofline']; print('1GiB x32 $w', round(d['ms_per_step'],3), round(r['kernel_ms'],3), round(r['frac'],4), d['config'])" || tail -5 gpurun_out/last.log
+timeout 900 python -m pytest tests -m gpu -q -x > gpurun_out/pytest.log 2>&1; tail -3 gpurun_out/pytest.log
+for w in c2_ip_hist "c3_deltas --events 8" c4_mixed c4_switch "c4_switch --agg none"; do
+python bench.py --steps 5 --warmup 3 --no-e2e --no-cpu-baseline --workload $w > gpurun_out/last.log 2>&1; python -c "
+import json; d=json.loads(open('gpurun_out/last.log').read().strip().splitlines()[-1]); r=d['roofline']; print('$w', round(d['ms_per_step'],3), r.get('decode_kernel_ms'), round(r['kernel_ms'],3), round(r['frac'],4), d['config']['slow_tiles'])" || tail -3 gpurun_out/last.log
 done
-nvidia-smi --query-gpu=memory.used --format=csv
