@@ -1479,7 +1479,11 @@ __device__ __forceinline__ uint32_t agg_hash(uint64_t ip, uint32_t pid) {
 // for n_hi): the host runs the small size class first (most lists, high occupancy) and
 // larger ones for the few long lists.
 __global__ void __launch_bounds__(kAggThreads)
-    k_hist_aggregate(const HistLists t, uint32_t n_lists, uint32_t n_lo, uint32_t n_hi) {
+    k_hist_aggregate(const HistLists t, uint32_t n_lists, uint32_t n_lo, uint32_t n_hi,
+                     const uint32_t* __restrict__ skip_if_set) {
+  // queued right behind k_finalize without a host round trip: when that asked for a re-run
+  // of the batch (flag set) the lists are left alone, the host restores them and decodes again
+  if (skip_if_set && *skip_if_set) return;
   extern __shared__ __align__(128) uint8_t agg_smem[];
   ulonglong2* ent_buf = reinterpret_cast<ulonglong2*>(agg_smem);  // [2][n_hi]
   uint32_t* tab = reinterpret_cast<uint32_t*>(agg_smem + (size_t)2 * n_hi * sizeof(ulonglong2));

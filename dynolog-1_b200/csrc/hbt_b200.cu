@@ -426,7 +426,9 @@ int launch_finalize(hbt_ctx* ctx) {
   return 0;
 }
 
-// Launch decode + finalize for the tables currently uploaded.
+int hist_fold(hbt_ctx* ctx);
+
+// Launch decode + finalize (+ the histogram fold) for the tables currently uploaded.
 int run_once(hbt_ctx* ctx, bool snapshot_cursors) {
   static_assert(sizeof(RingDesc) % 8 == 0 && sizeof(SegDesc) % 8 == 0, "tables move as u64 words");
   PrepareParams pp{};
@@ -458,7 +460,14 @@ int run_once(hbt_ctx* ctx, bool snapshot_cursors) {
   CU(cudaGetLastError());
   int rc = launch_decode(ctx);
   if (rc) return rc;
-  return launch_finalize(ctx);
+  rc = launch_finalize(ctx);
+  if (rc) return rc;
+  if (ctx->desc.aggregate == HBT_AGG_IP_HISTOGRAM) {
+    // the fold follows at once; it skips itself if k_finalize asks for a re-run
+    ctx->hist_pending_fold = true;
+    rc = hist_fold(ctx);
+  }
+  return rc;
 }
 
 size_t hist_lists(const hbt_ctx* ctx) { return (size_t)ctx->n_cpus * ctx->hist_buckets; }
@@ -489,7 +498,7 @@ int hist_fold(hbt_ctx* ctx) {
     if (per_sm > 8) per_sm = 8;
     uint32_t grid = (uint32_t)ctx->sm_count * per_sm * 4;
     if (grid > n) grid = n;
-    k_hist_aggregate<<<grid, kAggThreads, smem, ctx->stream>>>(hist_view(ctx), n, lo, hi);
+    k_hist_aggregate<<<grid, kAggThreads, smem, ctx->stream>>>(hist_view(ctx), n, lo, hi, ctx->d_flags.p);
     ++ctx->launches;
     lo = hi;
   }
@@ -821,10 +830,7 @@ static int complete_decode(hbt_ctx* ctx) {
     if (rc) return rc;
   }
   // success: fold the appended samples, commit the generator state, fetch results
-  if (ctx->desc.aggregate == HBT_AGG_IP_HISTOGRAM) {
-    ctx->hist_pending_fold = true;
-    if (int rc = hist_fold(ctx)) return rc;
-  }
+  // (histogram: the fold of the successful run was queued by run_once)
   ctx->cur ^= 1;
   ctx->sw_valid = false;
   ctx->sw_merged = nullptr;
