@@ -1269,9 +1269,14 @@ struct FinalizeParams {
   uint64_t seg_limit_tile;  // kTile, or 0 for the untiled small-ring path
 };
 
-__global__ void __launch_bounds__(64) k_finalize(const FinalizeParams p) {
-  const uint32_t c = blockIdx.x * blockDim.x + threadIdx.x;
+// One warp per CPU: the segment results are staged in shared memory 32 at a time by the
+// whole warp (coalesced), lane 0 walks them -- the chain is sequential, but it no longer pays
+// a global-memory round trip per field.
+__global__ void __launch_bounds__(32) k_finalize(const FinalizeParams p) {
+  const uint32_t c = blockIdx.x, lane = threadIdx.x;
   if (c >= p.n_cpus) return;
+  __shared__ SegResult s_res[32];
+  __shared__ SegDesc s_seg[32];
   const RingDesc ring = p.rings[c];
   const hbt_decode_desc& d = p.d;
   const CpuState& sin = p.state_in[c];
@@ -1299,11 +1304,26 @@ __global__ void __launch_bounds__(64) k_finalize(const FinalizeParams p) {
 
   // seam_valid: bit 0 = slot 0 of the slab holds a seam row, bit 1 = the segment's rows
   // belong to this call's output (segments behind an error do not)
-  for (uint32_t s = 0; s < ring.n_seg; ++s) p.seam_valid[ring.seg_begin + s] = 0;
-  for (uint32_t s = 0; s < ring.n_seg; ++s) {
+  for (uint32_t s = lane; s < ring.n_seg; s += 32) p.seam_valid[ring.seg_begin + s] = 0;
+  __syncwarp();
+  bool stop = false;  // lane 0 left the segment loop early
+  for (uint32_t s0 = 0; s0 < ring.n_seg && !stop; s0 += 32) {
+    const uint32_t n_chunk = min(32u, ring.n_seg - s0);
+    {
+      const uint64_t* src = reinterpret_cast<const uint64_t*>(p.results + ring.seg_begin + s0);
+      uint64_t* dst = reinterpret_cast<uint64_t*>(s_res);
+      for (uint32_t w = lane; w < n_chunk * (uint32_t)(sizeof(SegResult) / 8); w += 32) dst[w] = src[w];
+      src = reinterpret_cast<const uint64_t*>(p.segs + ring.seg_begin + s0);
+      dst = reinterpret_cast<uint64_t*>(s_seg);
+      for (uint32_t w = lane; w < n_chunk * (uint32_t)(sizeof(SegDesc) / 8); w += 32) dst[w] = src[w];
+    }
+    __syncwarp();
+    if (lane == 0) {
+  for (uint32_t j = 0; j < n_chunk; ++j) {
+    const uint32_t s = s0 + j;
     const uint32_t gi = ring.seg_begin + s;
-    const SegResult& r = p.results[gi];
-    const SegDesc& sd = p.segs[gi];
+    const SegResult& r = s_res[j];
+    const SegDesc& sd = s_seg[j];
     const uint64_t seg_limit =
         p.seg_limit_tile ? min(sd.tile_end * p.seg_limit_tile, ring.head) : ring.head;
     if (pos >= seg_limit) {
@@ -1311,14 +1331,14 @@ __global__ void __launch_bounds__(64) k_finalize(const FinalizeParams p) {
       if (r.entry != kNone) {
         p.forced_out[gi] = pos;
         redo = true;
-        break;
+        { stop = true; break; }
       }
       continue;
     }
     if (r.entry != pos) {
       p.forced_out[gi] = pos;
       redo = true;
-      break;
+      { stop = true; break; }
     }
     if (n_rec + r.n_records > (uint64_t)d.max_records) {
       // consume(max_num_records) stops inside this segment: the host locates the
@@ -1328,7 +1348,7 @@ __global__ void __launch_bounds__(64) k_finalize(const FinalizeParams p) {
       p.locate_from[c] = pos;
       p.locate_skip[c] = (uint64_t)d.max_records - n_rec;
       redo = true;
-      break;
+      { stop = true; break; }
     }
     // seam: the segment's first SAMPLE had no SAMPLE/LOST before it in the segment
     if (p.agg == HBT_AGG_COUNT_DELTAS && ev_kind(r.first_ev) == EV_SAMPLE) {
@@ -1343,7 +1363,7 @@ __global__ void __launch_bounds__(64) k_finalize(const FinalizeParams p) {
           p.clamp_head[c] = sp;
           p.clamp_ret[c] = -1;  // -EPERM
           redo = true;
-          break;
+          { stop = true; break; }
         }
         uint64_t* row = sd.rows;  // slot 0 of the slab
         row[0] = pts;
@@ -1371,9 +1391,14 @@ __global__ void __launch_bounds__(64) k_finalize(const FinalizeParams p) {
         p.clamp_ret[c] = r.err;
         redo = true;
       }
-      break;
+      { stop = true; break; }
     }
   }
+    }
+    stop = __shfl_sync(0xffffffffu, stop ? 1 : 0, 0) != 0;
+    __syncwarp();  // the staging buffers are reused by the next chunk
+  }
+  if (lane != 0) return;
   if (redo) {
     atomicExch(&p.flags[0], 1u);
     return;

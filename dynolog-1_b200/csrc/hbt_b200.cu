@@ -420,7 +420,7 @@ int launch_finalize(hbt_ctx* ctx) {
   f.d = ctx->desc;
   f.agg = (int)ctx->desc.aggregate;
   f.seg_limit_tile = ctx->tiled ? kTile : 0;
-  k_finalize<<<(C + 63) / 64, 64, 0, ctx->stream>>>(f);
+  k_finalize<<<C, 32, 0, ctx->stream>>>(f);
   ++ctx->launches;
   CU(cudaGetLastError());
   return 0;
