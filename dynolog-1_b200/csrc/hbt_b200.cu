@@ -789,9 +789,30 @@ static int complete_decode(hbt_ctx* ctx) {
   std::vector<uint64_t> clamp_head(C, kNone);
   std::vector<int64_t> clamp_ret(C, 0);
   bool have_clamp = false;
+  // Results travel with the re-run flag (one synchronisation in the common case); they only
+  // count when the flag is clear.  The event-stream aggregate still has its second pass to run
+  // on them, so it copies them afterwards.
+  const bool early_results = ctx->desc.aggregate != HBT_AGG_SWITCH_EVENTS;
+  auto copy_results = [&]() -> int {
+    ctx->h_flags.p[4] = 0;
+    if (ctx->desc.aggregate == HBT_AGG_IP_HISTOGRAM)
+      CU(cudaMemcpyAsync(ctx->h_flags.p + 4, ctx->hist_overflow.p, sizeof(uint32_t),
+                         cudaMemcpyDeviceToHost, ctx->stream));
+    CU(cudaMemcpyAsync(ctx->h_out.p, ctx->d_out.p, C * sizeof(hbt_cpu_result),
+                       cudaMemcpyDeviceToHost, ctx->stream));
+    if (ctx->n_segs) {
+      CU(cudaMemcpyAsync(ctx->h_results.p, ctx->d_results.p, ctx->n_segs * sizeof(SegResult),
+                         cudaMemcpyDeviceToHost, ctx->stream));
+      CU(cudaMemcpyAsync(ctx->h_seam.p, ctx->d_seam.p, ctx->n_segs, cudaMemcpyDeviceToHost,
+                         ctx->stream));
+    }
+    return 0;
+  };
   for (int iter = 0;; ++iter) {
     CU(cudaMemcpyAsync(ctx->h_flags.p, ctx->d_flags.p, 4 * sizeof(uint32_t),
                        cudaMemcpyDeviceToHost, ctx->stream));
+    if (early_results)
+      if (int rc = copy_results()) return rc;
     CU(cudaStreamSynchronize(ctx->stream));
     if (ctx->h_flags.p[0] == 0) break;
     if (iter > 4 * kMaxSegsPerCpu + 8) return fail(ctx, -EIO, "decode re-run did not converge");
@@ -860,19 +881,10 @@ static int complete_decode(hbt_ctx* ctx) {
     CU(cudaMemcpyAsync(ctx->h_sw_off.p, ctx->d_sw_off.p, (C + 1) * sizeof(uint64_t),
                        cudaMemcpyDeviceToHost, ctx->stream));
   }
-  ctx->h_flags.p[4] = 0;
-  if (ctx->desc.aggregate == HBT_AGG_IP_HISTOGRAM)
-    CU(cudaMemcpyAsync(ctx->h_flags.p + 4, ctx->hist_overflow.p, sizeof(uint32_t),
-                       cudaMemcpyDeviceToHost, ctx->stream));
-  CU(cudaMemcpyAsync(ctx->h_out.p, ctx->d_out.p, C * sizeof(hbt_cpu_result),
-                     cudaMemcpyDeviceToHost, ctx->stream));
-  if (ctx->n_segs) {
-    CU(cudaMemcpyAsync(ctx->h_results.p, ctx->d_results.p, ctx->n_segs * sizeof(SegResult),
-                       cudaMemcpyDeviceToHost, ctx->stream));
-    CU(cudaMemcpyAsync(ctx->h_seam.p, ctx->d_seam.p, ctx->n_segs, cudaMemcpyDeviceToHost,
-                       ctx->stream));
+  if (!early_results) {
+    if (int rc = copy_results()) return rc;
+    CU(cudaStreamSynchronize(ctx->stream));
   }
-  CU(cudaStreamSynchronize(ctx->stream));
   // consumed windows: tail advances like writeDataTail (CpuEventsGroup.h:1520)
   for (uint32_t c = 0; c < C; ++c) {
     Window& w = ctx->win[c];
