@@ -834,14 +834,37 @@ __global__ void __launch_bounds__(kThreads, AGG == HBT_AGG_IP_HISTOGRAM ? HBT_HI
             else if (q < se) q = sb;  // prediction failed here: scan
             else q = se;              // predicted: nothing starts in my sub-chunk
           }
-          if (my_entry == kNoRel) {
-#pragma unroll 1
-            for (; q < se; q += 8) {
-              const uint64_t h = tv.at(q);
-              if (!plausible(h)) continue;
-              const uint32_t q2 = q + hdr_size(h);
+          if (my_entry == kNoRel && q < se) {
+            // Scan: the first plausible header at or after q whose successor is plausible
+            // too.  All words of the sub-chunk (it lies inside tile k) are loaded at once
+            // -- independent loads, no divergent trip count -- and reduced to a bit mask
+            // plus their 16-bit sizes; only the candidates' successors are looked up.
+            // (the skew makes a sub-chunk kSubWords + 1 words long at most; loading a few words
+            // past a short one stays inside the staging area and is masked out below)
+            constexpr int kScanWords = kSubWords + 1;
+            constexpr int kScanGroups = (kScanWords + 3) / 4;
+            uint32_t pm = 0;
+            uint64_t szp[kScanGroups];
+#pragma unroll
+            for (int w = 0; w < kScanWords; ++w) {
+              const uint64_t h = lds_u64(tv.sa + sb + 8u * w);
+              if (plausible(h)) pm |= 1u << w;
+              if ((w & 3) == 0) szp[w >> 2] = 0;
+              szp[w >> 2] |= (uint64_t)hdr_size(h) << (16 * (w & 3));
+            }
+            const uint32_t w0 = (q - sb) >> 3, w1 = (se - sb) >> 3;  // words [w0, w1)
+            pm &= ((1u << w1) - 1u) & ~((1u << w0) - 1u);
+            while (pm) {
+              const uint32_t w = __ffs(pm) - 1;
+              pm &= pm - 1;
+              uint64_t sz4 = 0;
+#pragma unroll
+              for (int g = 0; g < kScanGroups; ++g)
+                if ((w >> 2) == (uint32_t)g) sz4 = szp[g];
+              const uint32_t qq = sb + 8u * w;
+              const uint32_t q2 = qq + (uint32_t)((sz4 >> (16 * (w & 3))) & 0xFFFFu);
               if (q2 < look && !plausible(tv.at(q2))) continue;
-              my_entry = q;
+              my_entry = qq;
               break;
             }
           }
