@@ -843,24 +843,27 @@ __global__ void __launch_bounds__(kThreads, AGG == HBT_AGG_IP_HISTOGRAM ? HBT_HI
             // past a short one stays inside the staging area and is masked out below)
             constexpr int kScanWords = kSubWords + 1;
             constexpr int kScanGroups = (kScanWords + 3) / 4;
+            static_assert(kScanGroups <= 5, "size registers below");
             uint32_t pm = 0;
-            uint64_t szp[kScanGroups];
+            uint64_t sz0 = 0, sz1 = 0, sz2 = 0, sz3 = 0, sz4r = 0;  // 16-bit sizes, 4 per register
 #pragma unroll
             for (int w = 0; w < kScanWords; ++w) {
               const uint64_t h = lds_u64(tv.sa + sb + 8u * w);
               if (plausible(h)) pm |= 1u << w;
-              if ((w & 3) == 0) szp[w >> 2] = 0;
-              szp[w >> 2] |= (uint64_t)hdr_size(h) << (16 * (w & 3));
+              const uint64_t sz = (uint64_t)hdr_size(h) << (16 * (w & 3));
+              if ((w >> 2) == 0) sz0 |= sz;
+              else if ((w >> 2) == 1) sz1 |= sz;
+              else if ((w >> 2) == 2) sz2 |= sz;
+              else if ((w >> 2) == 3) sz3 |= sz;
+              else sz4r |= sz;
             }
             const uint32_t w0 = (q - sb) >> 3, w1 = (se - sb) >> 3;  // words [w0, w1)
             pm &= ((1u << w1) - 1u) & ~((1u << w0) - 1u);
             while (pm) {
               const uint32_t w = __ffs(pm) - 1;
               pm &= pm - 1;
-              uint64_t sz4 = 0;
-#pragma unroll
-              for (int g = 0; g < kScanGroups; ++g)
-                if ((w >> 2) == (uint32_t)g) sz4 = szp[g];
+              const uint32_t g = w >> 2;
+              const uint64_t sz4 = g == 0 ? sz0 : g == 1 ? sz1 : g == 2 ? sz2 : g == 3 ? sz3 : sz4r;
               const uint32_t qq = sb + 8u * w;
               const uint32_t q2 = qq + (uint32_t)((sz4 >> (16 * (w & 3))) & 0xFFFFu);
               if (q2 < look && !plausible(tv.at(q2))) continue;
