@@ -98,7 +98,7 @@ struct SegResult {
   int32_t err;        // 0 or negative errno: decoding stopped before err_pos
   uint32_t slow_tiles;
   uint32_t hist_overflow;
-  uint32_t pad_;
+  uint32_t n_lost_recs;  // handled LOST records of the segment (SWITCH_EVENTS: LOST proto-events)
 };
 
 struct CpuState {  // generator state across calls
@@ -195,7 +195,7 @@ __device__ __forceinline__ int counter_of(uint32_t type, uint32_t tmask) {
 // handler emits (PerCpuThreadSwitchGenerator.h:228-412) with the record's own timestamp.
 // What depends on the PREVIOUS record -- the WriteErrorsEnd in front of the first record
 // after a LOST (pendingRecordLost_, :441-453) and the WriteErrorsStart timestamp
-// last_tstamp_ + 1 (:243-245) -- is resolved by pass 2 (k_sw_count / k_sw_scan / k_sw_emit),
+// last_tstamp_ + 1 (:243-245) -- is resolved by pass 2 (k_sw_scan / k_sw_emit),
 // which is a prefix sum over "1 + previous is LOST".
 constexpr uint32_t kMiscSwitchOut = 1u << 13, kMiscSwitchOutPreempt = 1u << 14;
 
@@ -372,6 +372,7 @@ struct SegState {
   uint64_t err_pos;
   int32_t err;
   uint32_t slow_tiles;
+  uint32_t n_lost_recs;  // handled LOST records so far
   // per-tile scratch, one copy per guessing attempt (0: stride-predicted, 1: scanned)
   uint32_t guess_min[2];  // smallest guessed entry (tile-relative), segment start only
   uint32_t tile_x[2];     // where the record chain left the tile (tile-relative)
@@ -418,6 +419,7 @@ __device__ void consume_sequential(const DecodeParams& p, const RingDesc& ring,
     if (st.entry == kNone) st.entry = pos;
     const int ci = counter_of(type, type_mask(d.handled_mask));
     if (type == REC_LOST && ci >= 0) {
+      ++st.n_lost_recs;
       st.counters[HBT_CNT_LOST] += ring_word_g(ring, pos + 16);
       if (AGG == HBT_AGG_COUNT_DELTAS) st.ev = ev_make(pos, EV_LOST);
     } else if (type == REC_SAMPLE && ci >= 0) {
@@ -494,8 +496,12 @@ __device__ void consume_sequential(const DecodeParams& p, const RingDesc& ring,
     if (AGG == HBT_AGG_SWITCH_EVENTS && ci >= 0) {
       if (size < sw_min_size(type) || st.n_rows >= seg.rows_cap) {
         // take the counter update back: the handler fails before consume() counts the record
-        if (type == REC_LOST) st.counters[HBT_CNT_LOST] -= ring_word_g(ring, pos + 16);
-        else --st.counters[ci];
+        if (type == REC_LOST) {
+          st.counters[HBT_CNT_LOST] -= ring_word_g(ring, pos + 16);
+          --st.n_lost_recs;
+        } else {
+          --st.counters[ci];
+        }
         st.err = size < sw_min_size(type) ? -1 : -28;  // -EPERM / -ENOSPC
         st.err_pos = pos;
         break;
@@ -584,6 +590,7 @@ __global__ void __launch_bounds__(kThreads, AGG == HBT_AGG_IP_HISTOGRAM ? HBT_HI
     st.err = 0;
     st.err_pos = 0;
     st.slow_tiles = 0;
+    st.n_lost_recs = 0;
     st.guess_min[0] = st.guess_min[1] = kNoRel;
     st.tile_x[0] = st.tile_x[1] = kNoRel;
     st.stride = 0;
@@ -1068,6 +1075,7 @@ __global__ void __launch_bounds__(kThreads, AGG == HBT_AGG_IP_HISTOGRAM ? HBT_HI
       }
       uint32_t m = AGG == HBT_AGG_COUNT_DELTAS ? (smask | omask) : omask;
       unsigned long long lost_sum = 0;
+      uint32_t lost_n = 0;
       while (m) {
         const uint32_t pos = sb + 8u * (__ffs(m) - 1);
         m &= m - 1;
@@ -1088,6 +1096,7 @@ __global__ void __launch_bounds__(kThreads, AGG == HBT_AGG_IP_HISTOGRAM ? HBT_HI
           const int ci = counter_of(type, tmask);
           if (ci == HBT_CNT_LOST) {
             lost_sum += tv.at(pos + 16);
+            ++lost_n;
             if (AGG == HBT_AGG_COUNT_DELTAS) in_ev = ev_make(t_begin + pos, EV_LOST);
           } else if (ci >= 0) {
             my_other[ci >> 2] += 1ull << (16 * (ci & 3));
@@ -1109,6 +1118,7 @@ __global__ void __launch_bounds__(kThreads, AGG == HBT_AGG_IP_HISTOGRAM ? HBT_HI
         }
       }
       if (lost_sum) atomicAdd(&st.counters[HBT_CNT_LOST], lost_sum);
+      if (lost_n) atomicAdd(&st.n_lost_recs, lost_n);
       if (AGG == HBT_AGG_COUNT_DELTAS) {
         if (unknown_j) atomicAdd(&st.n_unknown, (unsigned long long)unknown_j);
         if (pending_seam) st.first_ev = ev_make(t_begin + (first_ev >> 2) - 1, EV_SAMPLE);
@@ -1229,6 +1239,7 @@ __global__ void __launch_bounds__(kThreads, AGG == HBT_AGG_IP_HISTOGRAM ? HBT_HI
     r.err_pos = st.err_pos;
     r.slow_tiles = st.slow_tiles;
     r.hist_overflow = 0;
+    r.n_lost_recs = st.n_lost_recs;
   }
 }
 
@@ -1251,6 +1262,7 @@ __global__ void __launch_bounds__(32) k_decode_small(const DecodeParams p, uint3
   st.err = 0;
   st.err_pos = 0;
   st.slow_tiles = 1;
+  st.n_lost_recs = 0;
   consume_sequential<AGG>(p, ring, seg, st, ring.head);
   SegResult& r = p.results[g];
   r.entry = st.entry;
@@ -1266,6 +1278,7 @@ __global__ void __launch_bounds__(32) k_decode_small(const DecodeParams p, uint3
   r.err_pos = st.err_pos;
   r.slow_tiles = 1;
   r.hist_overflow = 0;
+  r.n_lost_recs = st.n_lost_recs;
 }
 
 // ---------------------------------------------------------------------------
@@ -1664,9 +1677,9 @@ __global__ void __launch_bounds__(128)
 // ---------------------------------------------------------------------------
 // HBT_AGG_SWITCH_EVENTS, pass 2: proto-events -> tagstack::Event stream.
 // Event count of a proto = 1 + (the previous handled record of the CPU was a LOST).
-// k_sw_count: per segment, LOST protos that are not the slab's last (each one gives its
-//   successor a WriteErrorsEnd) and the slab's last proto.
-// k_sw_scan: one thread per CPU chains the segments from the generator state
+// k_sw_scan: one thread per CPU chains the segments (k_decode counted each segment's LOST
+//   protos; the ones that are not the slab's last give their successor a WriteErrorsEnd)
+//   from the generator state
 //   (last_tstamp_, in_write_errors_), gives every segment its output offset and the
 //   "previous record" of its first proto, then the CPUs' totals are prefix-summed.
 // k_sw_emit: per segment, block scan over 1 + prev_is_lost and the final events.
@@ -1697,27 +1710,6 @@ struct SwParams {
 
 __device__ __forceinline__ bool sw_is_lost(uint64_t w1) { return (uint32_t)(w1 & 0xFF) == HBT_SWEV_WRITE_ERRORS_START; }
 
-static __global__ void __launch_bounds__(256) k_sw_count(const SwParams p) {
-  const uint32_t gi = blockIdx.x;
-  const uint32_t n = (p.seg_flags[gi] & 2) ? (uint32_t)p.results[gi].n_rows : 0u;
-  const uint64_t* slab = p.segs[gi].rows + 2;  // slot 0 is the (unused) seam slot
-  uint32_t c = 0;
-  for (uint32_t i = threadIdx.x; i + 1 < n; i += blockDim.x) c += sw_is_lost(slab[2 * i + 1]);
-  c = __reduce_add_sync(0xffffffffu, c);
-  __shared__ uint32_t s_c;
-  if (threadIdx.x == 0) s_c = 0;
-  __syncthreads();
-  if ((threadIdx.x & 31) == 0 && c) atomicAdd(&s_c, c);
-  __syncthreads();
-  if (threadIdx.x == 0) {
-    SwSeg& w = p.sw[gi];
-    w.n = n;
-    w.lost_inner = s_c;
-    w.last_ts = n ? slab[2 * (n - 1)] : 0;
-    w.last_lost = n ? sw_is_lost(slab[2 * (n - 1) + 1]) : 0;
-  }
-}
-
 // launched as one CTA of >= n_cpus threads (n_cpus <= HBT_MAX_CPUS = 512)
 static __global__ void __launch_bounds__(512) k_sw_scan(const SwParams p) {
   const uint32_t c = threadIdx.x;
@@ -1727,7 +1719,17 @@ static __global__ void __launch_bounds__(512) k_sw_scan(const SwParams p) {
     uint64_t prev_ts = p.state_ts[c];
     uint32_t prev_lost = p.state_err[c];
     for (uint32_t s = 0; s < ring.n_seg; ++s) {
-      SwSeg& w = p.sw[ring.seg_begin + s];
+      const uint32_t gi = ring.seg_begin + s;
+      SwSeg& w = p.sw[gi];
+      // the segment's protos that belong to this call, its last proto, and the LOST protos in
+      // front of that one (each gives its successor a WriteErrorsEnd)
+      w.n = (p.seg_flags[gi] & 2) ? (uint32_t)p.results[gi].n_rows : 0u;
+      if (w.n) {
+        const uint64_t* last = p.segs[gi].rows + 2 + 2 * (uint64_t)(w.n - 1);  // slot 0 = unused seam slot
+        w.last_ts = last[0];
+        w.last_lost = sw_is_lost(last[1]);
+        w.lost_inner = p.results[gi].n_lost_recs - w.last_lost;
+      }
       w.base = total;
       w.prev_ts = prev_ts;
       w.prev_lost = prev_lost;

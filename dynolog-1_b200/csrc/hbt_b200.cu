@@ -871,10 +871,6 @@ static int complete_decode(hbt_ctx* ctx) {
     sp.n_cpus = C;
     sp.n_segs = ctx->n_segs;
     sp.cpu_base = ctx->cpu_base;
-    if (ctx->n_segs) {
-      k_sw_count<<<ctx->n_segs, 256, 0, ctx->stream>>>(sp);
-      ++ctx->launches;
-    }
     k_sw_scan<<<1, 512, 0, ctx->stream>>>(sp);
     ++ctx->launches;
     CU(cudaGetLastError());
