@@ -140,8 +140,10 @@ __device__ __forceinline__ uint32_t hdr_size(uint64_t h) { return (uint32_t)(h >
 // Guess filter only (never decides results): a header the kernel could have
 // written -- small type id, u64-padded size.
 __device__ __forceinline__ bool plausible(uint64_t h) {
-  const uint32_t type = hdr_type(h), size = hdr_size(h);
-  return type >= 1 && type < 64 && size >= 8 && (size & 7) == 0;
+  // type in [1, 64), size >= 8 and a multiple of 8 -- on the two halves of the header word
+  // (size is the top 16 bits): three compares
+  const uint32_t lo = (uint32_t)h, hi = (uint32_t)(h >> 32);
+  return (lo - 1u) < 63u && (hi & 0x00070000u) == 0 && hi >= 0x00080000u;
 }
 
 __device__ __forceinline__ uint64_t ring_word_g(const RingDesc& r, uint64_t pos) {
@@ -631,11 +633,26 @@ __global__ void __launch_bounds__(kThreads, AGG == HBT_AGG_IP_HISTOGRAM ? HBT_HI
 
   // thread-local totals over the fast-path tiles (added to st in the epilogue)
   uint32_t my_rec = 0, my_sample = 0;
-  // per-type counts of the other record types, 16 bits each (a thread sees at most 8 records
-  // per tile): counter ci lives in my_other[ci >> 2] at bit 16 * (ci & 3).  One shared-memory
-  // atomic per record would serialise the whole CTA on a stream of SWITCH records.
-  uint64_t my_other[3] = {0, 0, 0};
+  // per-type counts of the other record types (all but LOST and SAMPLE: nine counters), 7 bits
+  // each in ONE register: counter ci lives at bit 7 * other_field(ci); flushed to shared memory
+  // every 127 records.  One shared-memory atomic per record would serialise the whole CTA on a
+  // stream of SWITCH records, and an indexed array of registers would live in local memory.
+  uint64_t my_other = 0;
   uint32_t my_other_n = 0;
+  auto other_field = [](int ci) { return ci - 1 - (ci > HBT_CNT_SAMPLE ? 1 : 0); };
+  auto flush_other = [&](bool warp_wide) {
+#pragma unroll
+    for (int c = 0; c < HBT_NUM_COUNTERS; ++c) {
+      if (c == HBT_CNT_LOST || c == HBT_CNT_SAMPLE) continue;
+      uint32_t v = (uint32_t)(my_other >> (7 * other_field(c))) & 0x7Fu;
+      if (warp_wide) {
+        v = __reduce_add_sync(0xffffffffu, v);
+        if (lane != 0) v = 0;
+      }
+      if (v) atomicAdd(&st.counters[c], (unsigned long long)v);
+    }
+    my_other = 0;
+  };
 
   HistPending pend;  // IP_HISTOGRAM: appends whose cursor atomics are in flight
   // COUNT_DELTAS row writer (uniform fast path): this thread's fixed word column and first row
@@ -1099,14 +1116,10 @@ __global__ void __launch_bounds__(kThreads, AGG == HBT_AGG_IP_HISTOGRAM ? HBT_HI
             ++lost_n;
             if (AGG == HBT_AGG_COUNT_DELTAS) in_ev = ev_make(t_begin + pos, EV_LOST);
           } else if (ci >= 0) {
-            my_other[ci >> 2] += 1ull << (16 * (ci & 3));
-            if ((++my_other_n & 0x3FFF) == 0) {  // long before a 16-bit field can wrap: flush
-#pragma unroll
-              for (int c = 0; c < HBT_NUM_COUNTERS; ++c) {
-                const uint32_t v = (uint32_t)(my_other[c >> 2] >> (16 * (c & 3))) & 0xFFFFu;
-                if (v) atomicAdd(&st.counters[c], (unsigned long long)v);
-              }
-              my_other[0] = my_other[1] = my_other[2] = 0;
+            my_other += 1ull << (7 * other_field(ci));
+            if (++my_other_n == 127) {  // before a 7-bit field can wrap
+              flush_other(false);
+              my_other_n = 0;
             }
           }
           if (AGG == HBT_AGG_SWITCH_EVENTS && ci >= 0) {
@@ -1212,13 +1225,7 @@ __global__ void __launch_bounds__(kThreads, AGG == HBT_AGG_IP_HISTOGRAM ? HBT_HI
   }
   my_rec = __reduce_add_sync(0xffffffffu, my_rec);
   my_sample = __reduce_add_sync(0xffffffffu, my_sample);
-#pragma unroll
-  for (int c = 0; c < HBT_NUM_COUNTERS; ++c) {
-    if (c == HBT_CNT_LOST || c == HBT_CNT_SAMPLE) continue;
-    const uint32_t v =
-        __reduce_add_sync(0xffffffffu, (uint32_t)(my_other[c >> 2] >> (16 * (c & 3))) & 0xFFFFu);
-    if (lane == 0 && v) atomicAdd(&st.counters[c], (unsigned long long)v);
-  }
+  flush_other(true);
   if (lane == 0) {
     atomicAdd(&st.n_rec, (unsigned long long)my_rec);
     atomicAdd(&st.counters[HBT_CNT_SAMPLE], (unsigned long long)my_sample);
