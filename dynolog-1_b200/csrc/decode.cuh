@@ -639,6 +639,9 @@ __global__ void __launch_bounds__(kThreads, AGG == HBT_AGG_IP_HISTOGRAM ? HBT_HI
   // stream of SWITCH records, and an indexed array of registers would live in local memory.
   uint64_t my_other = 0;
   uint32_t my_other_n = 0;
+  // LOST: sum of num_lost and number of records, added to st in the epilogue
+  uint64_t my_lost_sum = 0;
+  uint32_t my_lost_n = 0;
   auto other_field = [](int ci) { return ci - 1 - (ci > HBT_CNT_SAMPLE ? 1 : 0); };
   auto flush_other = [&](bool warp_wide) {
 #pragma unroll
@@ -1091,8 +1094,6 @@ __global__ void __launch_bounds__(kThreads, AGG == HBT_AGG_IP_HISTOGRAM ? HBT_HI
         }
       }
       uint32_t m = AGG == HBT_AGG_COUNT_DELTAS ? (smask | omask) : omask;
-      unsigned long long lost_sum = 0;
-      uint32_t lost_n = 0;
       while (m) {
         const uint32_t pos = sb + 8u * (__ffs(m) - 1);
         m &= m - 1;
@@ -1112,8 +1113,8 @@ __global__ void __launch_bounds__(kThreads, AGG == HBT_AGG_IP_HISTOGRAM ? HBT_HI
         } else {
           const int ci = counter_of(type, tmask);
           if (ci == HBT_CNT_LOST) {
-            lost_sum += tv.at(pos + 16);
-            ++lost_n;
+            my_lost_sum += tv.at(pos + 16);
+            ++my_lost_n;
             if (AGG == HBT_AGG_COUNT_DELTAS) in_ev = ev_make(t_begin + pos, EV_LOST);
           } else if (ci >= 0) {
             my_other += 1ull << (7 * other_field(ci));
@@ -1130,8 +1131,6 @@ __global__ void __launch_bounds__(kThreads, AGG == HBT_AGG_IP_HISTOGRAM ? HBT_HI
           }
         }
       }
-      if (lost_sum) atomicAdd(&st.counters[HBT_CNT_LOST], lost_sum);
-      if (lost_n) atomicAdd(&st.n_lost_recs, lost_n);
       if (AGG == HBT_AGG_COUNT_DELTAS) {
         if (unknown_j) atomicAdd(&st.n_unknown, (unsigned long long)unknown_j);
         if (pending_seam) st.first_ev = ev_make(t_begin + (first_ev >> 2) - 1, EV_SAMPLE);
@@ -1226,6 +1225,13 @@ __global__ void __launch_bounds__(kThreads, AGG == HBT_AGG_IP_HISTOGRAM ? HBT_HI
   my_rec = __reduce_add_sync(0xffffffffu, my_rec);
   my_sample = __reduce_add_sync(0xffffffffu, my_sample);
   flush_other(true);
+  my_lost_n = __reduce_add_sync(0xffffffffu, my_lost_n);
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) my_lost_sum += __shfl_xor_sync(0xffffffffu, my_lost_sum, o);
+  if (lane == 0 && my_lost_n) {
+    atomicAdd(&st.counters[HBT_CNT_LOST], (unsigned long long)my_lost_sum);
+    atomicAdd(&st.n_lost_recs, my_lost_n);
+  }
   if (lane == 0) {
     atomicAdd(&st.n_rec, (unsigned long long)my_rec);
     atomicAdd(&st.counters[HBT_CNT_SAMPLE], (unsigned long long)my_sample);
