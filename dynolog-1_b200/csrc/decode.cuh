@@ -399,6 +399,11 @@ constexpr int kMaxRowsPerTile = kTile / 48 + 1;  // a SAMPLE is at least 40 + 8 
 struct RowDescs {
   uint64_t far_prev;            // absolute position of a previous SAMPLE outside the tile
   uint2 d[kMaxRowsPerTile];     // {current, previous} tile-relative; previous = kNoRel -> far_prev
+  // The last SAMPLE of a uniform tile, kept for the first row of the next tile (its bytes have
+  // left the staging area by then; without this copy that row waits for global memory).
+  // Two slots by tile parity: tile k writes slot k & 1 while its own first row reads the other.
+  uint64_t prev_pos[2];                          // absolute position of the saved SAMPLE, kNone = none
+  uint64_t prev_words[2][5 + HBT_MAX_EVENTS];    // its header, tstamp, nr, times and values
 };
 
 // Sequential consume() over [st.pos, limit) by ONE thread: the slow path for
@@ -600,6 +605,7 @@ __global__ void __launch_bounds__(kThreads, AGG == HBT_AGG_IP_HISTOGRAM ? HBT_HI
     st.size_max = 0;
   }
   sm.expect[tid] = kNoRel;
+  if (AGG == HBT_AGG_COUNT_DELTAS && tid < 2) rowd.prev_pos[tid] = kNone;
   if (AGG == HBT_AGG_IP_HISTOGRAM) {
     for (int i = tid; i < kCacheSlots; i += kThreads) {
       cache.slots[i] = make_ulonglong2(0, 0);
@@ -678,6 +684,7 @@ __global__ void __launch_bounds__(kThreads, AGG == HBT_AGG_IP_HISTOGRAM ? HBT_HI
 
 #pragma unroll 1
   for (uint32_t k = 0; k < n_tiles; ++k) {
+    const uint32_t tile_k = k;  // (inner loops reuse the name k)
     const uint32_t sb_i = sa_i + 1 == kStages ? 0 : sa_i + 1;
     const uint32_t sc_i = sb_i + 1 == kStages ? 0 : sb_i + 1;
     // refill the stage tile k-1 lived in; the trailing barrier of the previous
@@ -803,13 +810,22 @@ __global__ void __launch_bounds__(kThreads, AGG == HBT_AGG_IP_HISTOGRAM ? HBT_HI
             const uint32_t ostep = rw_rows * wpr;
             for (uint32_t r = rw_r0; r < rows_tile; r += rw_rows, cpos += step, o += ostep) {
               const uint64_t cur = tv.at(cpos);
-              const uint64_t prv = r + 1 > first_row ? tv.at(cpos - S) : ring_word_g(ring, far_prev + off);
+              uint64_t prv;
+              if (r + 1 > first_row) prv = tv.at(cpos - S);
+              else if (rowd.prev_pos[(tile_k & 1) ^ 1] == far_prev) prv = rowd.prev_words[(tile_k & 1) ^ 1][off >> 3];
+              else prv = ring_word_g(ring, far_prev + off);
               uint64_t v;
               if (rw_w == 0) v = prv;
               else if (!xf) v = cur - prv;   // duration, or a plain counter delta
               else v = tsc_to_ktime(cur, d.tsc) - tsc_to_ktime(prv, d.tsc);
               *o = v;
             }
+          }
+          // keep the tile's last SAMPLE for the next tile's first row
+          {
+            const uint32_t last = erel + (n_t - 1) * S;
+            if (tid < S / 8) rowd.prev_words[tile_k & 1][tid] = tv.at(last + 8 * tid);
+            if (tid == 0) rowd.prev_pos[tile_k & 1] = t_begin + last;
           }
           if (tid == 0) {
             if (ik == EV_LOST) ++st.n_unknown;  // record 0 re-seeds after a LOST
@@ -1151,8 +1167,10 @@ __global__ void __launch_bounds__(kThreads, AGG == HBT_AGG_IP_HISTOGRAM ? HBT_HI
           for (uint32_t r = rw_r0; r < trows; r += rw_rows, o += rw_rows * wpr) {
             const uint2 rd = rowd.d[r];
             const uint64_t cur = tv.at(rd.x + off);
-            const uint64_t prv = rd.y != kNoRel ? tv.at(rd.y + off)
-                                                : ring_word_g(ring, rowd.far_prev + off);
+            uint64_t prv;
+            if (rd.y != kNoRel) prv = tv.at(rd.y + off);
+            else if (rowd.prev_pos[(tile_k & 1) ^ 1] == rowd.far_prev) prv = rowd.prev_words[(tile_k & 1) ^ 1][off >> 3];
+            else prv = ring_word_g(ring, rowd.far_prev + off);
             uint64_t v;
             if (rw_w == 0) v = prv;
             else if (!xf) v = cur - prv;
