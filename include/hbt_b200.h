@@ -265,7 +265,10 @@ int hbt_submit_rings_dev(hbt_ctx* ctx, uint32_t n, const void* const* ring_bases
 /* Forget counters, carry (count_.tstamp, last_[]) and windows of all CPUs:
  * the state after enable() (CpuEventsGroup.h:1240-1280, enableImpl
  * PerCpuCountSampleGenerator.h:91-106).  seed_tstamp is the value enableImpl
- * takes from now(); UINT64_MAX seeds an invalid (re-seeding) interval. */
+ * takes from now(); UINT64_MAX seeds an invalid (re-seeding) interval.
+ * The thread-switch generator's state goes back to its constructor values too:
+ * last_tstamp_ = 0 (numeric_limits<TimeStamp>::min()), in_write_errors_ = false
+ * (PerCpuThreadSwitchGenerator.h:437-438). */
 int hbt_ring_reset_state(hbt_ctx* ctx, uint64_t seed_tstamp);
 
 /* ------------------------------------------------------------------------ */
