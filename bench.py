@@ -321,7 +321,10 @@ def bench_deltas(args, rank, world, local, dev, dist):
                              "peak_source": peak_src},
                 "gpu_launches": int(launches), "clocks": clocks}
     ach = algo / (k_ms * 1e-3) / 1e9
-    return {"metric": METRIC, "value": n_rec * world / (ms_step * 1e-3), "unit": UNIT, "n_gpus": world,
+    cb = None
+    if world == 1 and not args.no_cpu_baseline and not mixed and not switch and args.agg != "none":
+        cb = cpu_baseline_deltas(args, E)
+    line = {"metric": METRIC, "value": n_rec * world / (ms_step * 1e-3), "unit": UNIT, "n_gpus": world,
             "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms_step,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u64",
             "data": "synthetic",
@@ -336,6 +339,9 @@ def bench_deltas(args, rank, world, local, dev, dist):
                          "traffic": load_traffic("k_decode<COUNT_DELTAS>"), "kernel": "k_decode<COUNT_DELTAS>",
                          "kernel_ms": k_ms, "algorithmic_bytes": int(algo), "peak_source": peak_src},
             "gpu_launches": int(launches), "clocks": clocks}
+    if cb:
+        line["cpu_baseline"] = cb
+    return line
 
 
 def bench_counts(args, rank, world, local, dev, dist):
@@ -443,6 +449,50 @@ def run_reference(args, rank, world):
                              "sample": sample},
             "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     print(json.dumps(line))
+
+
+def cpu_baseline_deltas(args, n_events: int):
+    """The reference's own CpuCountSampleGenerator (oracle/_ref) over a bounded sample of the
+    c3_deltas rings, one generator per ring, all host cores."""
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    try:
+        import _oracle as orc
+        if not orc.have_ref():
+            return None
+        lib = orc.ref()
+    except Exception:
+        return None
+    cores = os.cpu_count() or 1
+    ring_bytes = args.ring_mib << 20
+    sample_cpus = min(args.cpus, args.ref_cpus)
+    imgs, tails, heads, n_rec = make_group_rings(sample_cpus, ring_bytes, 0, "cpu", n_events)
+    rings = imgs.numpy().view(np.uint8)
+    tails_a, heads_a = np.array(tails, dtype=np.uint64), np.array(heads, dtype=np.uint64)
+    lib.hbtref_sample_deltas_timed.restype = C.c_double
+    lib.hbtref_sample_deltas_timed.argtypes = [C.c_void_p, C.c_uint64, C.c_void_p, C.c_void_p, C.c_uint32,
+                                               C.c_uint32, C.c_uint32, C.POINTER(C.c_uint64),
+                                               C.POINTER(C.c_uint64)]
+    best = None
+    recs, rows = C.c_uint64(), C.c_uint64()
+    # the reference logs a warning per LOST record (PerCpuCountSampleGenerator.h:111): keep it
+    # (it is part of what the reference does) but not on this process's stderr
+    sys.stderr.flush()
+    saved, devnull = os.dup(2), os.open(os.devnull, os.O_WRONLY)
+    os.dup2(devnull, 2)
+    try:
+        for _ in range(2):
+            t = lib.hbtref_sample_deltas_timed(rings.ctypes.data, ring_bytes, tails_a.ctypes.data,
+                                               heads_a.ctypes.data, sample_cpus, n_events, cores,
+                                               C.byref(recs), C.byref(rows))
+            best = t if best is None else min(best, t)
+    finally:
+        os.dup2(saved, 2)
+        os.close(saved)
+        os.close(devnull)
+    return {"value": n_rec / best, "unit": UNIT, "cores": cores, "kind": "reference",
+            "sample": f"{sample_cpus} of {args.cpus} rings x {args.ring_mib} MiB, best of 2; the reference's "
+                      "CpuCountSampleGenerator::consume() with its own output ring",
+            "rows": int(rows.value)}
 
 
 def cpu_baseline_leg(args):
