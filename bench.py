@@ -180,7 +180,7 @@ def make_switch_rings(n_cpus: int, ring_bytes: int, cpu_base: int, device):
     n = int((ring_bytes - (1 << 20)) / (34.4 * 1.02))
     for c in range(n_cpus):
         seed = tg.stream_seed(6, cpu_base + c)
-        s = tg.ctx_switch_stream(seed, n, device=device)
+        s = tg.ctx_switch_stream(seed, n, device=device, fork_tid_base=(cpu_base + c) << 22)
         assert s.numel() * 8 <= ring_bytes - 4096, "switch stream does not fit the ring"
         tail = tg.random_tail(seed, ring_bytes)
         ring, head = tg.place_in_ring(s, ring_bytes, tail, fill_seed=seed ^ 0xABCDEF)
@@ -294,6 +294,7 @@ def bench_deltas(args, rank, world, local, dev, dist):
         # span is the whole device-timed step; n_rows counts 16-byte events
         algo = window_bytes + n_rows * 16
         ach = algo / (ms_step * 1e-3) / 1e9
+        sw_cb = cpu_baseline_switch(args) if world == 1 and not args.no_cpu_baseline else None
         # the Combinator-tree merge of the per-CPU streams, timed once on its own
         m0, m1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         base, n_ev = C.c_void_p(), C.c_uint64()
@@ -319,7 +320,8 @@ def bench_deltas(args, rank, world, local, dev, dist):
                              "traffic": None, "kernel": "k_decode<SWITCH_EVENTS> + k_sw_count/scan/emit",
                              "kernel_ms": ms_step, "decode_kernel_ms": k_ms, "algorithmic_bytes": int(algo),
                              "peak_source": peak_src},
-                "gpu_launches": int(launches), "clocks": clocks}
+                "gpu_launches": int(launches), "clocks": clocks,
+                **({"cpu_baseline": sw_cb} if sw_cb else {})}
     ach = algo / (k_ms * 1e-3) / 1e9
     cb = None
     if world == 1 and not args.no_cpu_baseline and not mixed and not switch and args.agg != "none":
@@ -493,6 +495,33 @@ def cpu_baseline_deltas(args, n_events: int):
             "sample": f"{sample_cpus} of {args.cpus} rings x {args.ring_mib} MiB, best of 2; the reference's "
                       "CpuCountSampleGenerator::consume() with its own output ring",
             "rows": int(rows.value)}
+
+
+def cpu_baseline_switch(args):
+    """The reference's own CpuThreadSwitchGenerator (oracle/_ref) over a bounded sample of the
+    c4_switch rings.  One thread: its generators share one unsynchronised PerThreadStats map
+    (thread ids -> virtual ids, with a /proc lookup per new thread), as in the reference."""
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    try:
+        import _oracle as orc
+        if not orc.have_ref():
+            return None
+    except Exception:
+        return None
+    ring_bytes = args.ring_mib << 20
+    sample_cpus = min(args.cpus, 4)  # ~4 us per record (a /proc lookup per new thread): keep it short
+    imgs, tails, heads, n_rec = make_switch_rings(sample_cpus, ring_bytes, 0, "cpu")
+    rings = imgs.numpy().view(np.uint64)
+    best = None
+    for _ in range(2):
+        t0 = time.perf_counter()
+        ref = orc.ref_switch_events(rings, tails, heads, tid_level=1)
+        dt = time.perf_counter() - t0
+        best = dt if best is None else min(best, dt)
+    return {"value": n_rec / best, "unit": UNIT, "cores": 1, "kind": "reference",
+            "sample": f"{sample_cpus} of {args.cpus} rings x {args.ring_mib} MiB, best of 2; the reference's "
+                      "CpuThreadSwitchGenerator::consume() with its own output ring and thread map",
+            "events": int(sum(len(r["events"]) for r in ref))}
 
 
 def cpu_baseline_leg(args):

@@ -244,13 +244,14 @@ CTX_MIX = (("switch", 0.86), ("comm", 0.04), ("fork", 0.04), ("exit", 0.04), ("l
 
 
 def ctx_switch_stream(seed: int, n_records: int, device="cpu", mix=CTX_MIX, t0: int = 1_000_000,
-                      n_tids: int = 512) -> torch.Tensor:
+                      n_tids: int = 512, fork_tid_base: int = 0) -> torch.Tensor:
     """A mode::ContextSwitch stream (what CpuThreadSwitchGenerator's sw_dummy event
     produces, CpuEventsGroup.h:105-184): SWITCH_CPU_WIDE in / out-yield / out-preempt,
     COMM (8 or 16 byte names), FORK, EXIT and LOST records with {pid,tid,time} sample_id
-    trailers and increasing timestamps.  Vectorised; thread lifetimes are NOT consistent
-    (a tid may fork twice), which the GPU path and the C oracle do not care about -- use
-    ctx_switch_stream_consistent for streams the reference's own handlers accept."""
+    trailers and increasing timestamps.  Vectorised.  Switch / COMM / EXIT records draw their
+    tid from a pool of n_tids; every FORK creates a fresh tid above the pool (the reference's
+    handlers assert on a second FORK of a live thread), so the reference's own generator
+    accepts the stream, although threads "exit" without having forked."""
     n = n_records
     u = rand_uniform(seed, n, device, 41)
     kinds = [k for k, _ in mix]
@@ -273,7 +274,10 @@ def ctx_switch_stream(seed: int, n_records: int, device="cpu", mix=CTX_MIX, t0: 
     out = rand_u64(seed, total, device, 43) & _s64(0x0000FFFFFFFFFFFF)
     dt = 1000 + rand_below(seed, n, 9000, device, 44)
     ts = t0 + torch.cumsum(dt, 0)
-    tid = rand_below(seed, n, n_tids, device, 45)            # tid 0 (the idle task) occurs too
+    tid = rand_below(seed, n, n_tids, device, 45)            # tid 0 (the idle task) occurs too ...
+    # ... but only in SWITCH records: the reference's COMM / EXIT handlers look tid 0 up in a map
+    # that never holds it (PerCpuThreadSwitchGenerator.h:92-97, 279, 128) and abort
+    tid = torch.where((rtype != REC_SWITCH_CPU_WIDE) & (tid == 0), torch.ones_like(tid), tid)
     pid = tid - (tid % 4)
     pidtid = pid | (tid << 32)
     # SWITCH misc: in / out-yield / out-preempt
@@ -286,7 +290,11 @@ def ctx_switch_stream(seed: int, n_records: int, device="cpu", mix=CTX_MIX, t0: 
     out[off + words - 2] = pidtid      # sample_id {pid, tid}
     out[off + words - 1] = ts          # sample_id.time
     out[off + 1] = pidtid              # switch: next_prev ; comm: pid,tid ; lost: id
-    fe = (rtype == REC_FORK) | (rtype == REC_EXIT)
+    is_fork = rtype == REC_FORK
+    # (fork_tid_base keeps the fresh tids of different CPUs' streams apart: they share one thread map)
+    tid = torch.where(is_fork, n_tids + fork_tid_base + torch.cumsum(is_fork.to(torch.int64), 0), tid)
+    pid = torch.where(is_fork, tid, pid)
+    fe = is_fork | (rtype == REC_EXIT)
     o = off[fe]
     if o.numel():                      # Exit/Fork: pid ppid | tid ptid | time
         out[o + 1] = pid[fe] | ((pid[fe] + 1) << 32)

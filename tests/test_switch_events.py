@@ -57,6 +57,34 @@ def test_oracle_vs_reference_generator(built, seed, lost_every):
         assert len(port[c]["events"]) - len(mapped[c]) == port[c]["counters"][hbt.CNT_COMM]
 
 
+@pytest.mark.parametrize("seed,mix", [(11, tg.CTX_MIX), (12, (("switch", 0.5), ("lost", 0.2), ("exit", 0.15), ("fork", 0.15))),
+                                      (13, (("comm", 0.5), ("exit", 0.3), ("fork", 0.2)))])
+def test_oracle_vs_reference_generator_random_tids(built, seed, mix):
+    """The vectorised stream (random tids from a small pool, tid 0 included, exits of threads
+    never seen before, COMM of unknown threads): the reference's generator accepts it, and its
+    vid-tagged events equal the restatement's mapped ones."""
+    if not orc.have_ref():
+        pytest.skip("oracle/_ref not built (reference tree absent)")
+    ds = 1 << 17
+    rings, tails, heads = [], [], []
+    for c in range(2):
+        s = tg.ctx_switch_stream(seed * 10 + c, 2500, mix=mix, n_tids=48, fork_tid_base=100000 * c)
+        tail = tg.random_tail(seed + c, ds)
+        ring, head = ring_np(s, ds, tail)
+        rings.append(ring)
+        tails.append(tail)
+        heads.append(head)
+    rings = np.stack(rings)
+    d = hbt.switch_desc(tid_level=1)
+    ref = orc.ref_switch_events(rings, tails, heads, tid_level=1)
+    port = [orc.port_switch_events(rings[c], tails[c], heads[c], d, cpu=c) for c in range(2)]
+    mapped = orc.map_tids_to_vids([p["events"] for p in port])
+    for c in range(2):
+        for k in ("ret", "n_records", "new_tail", "counters", "carry_tstamp", "num_unknown"):
+            assert ref[c][k] == port[c][k], (c, k)
+        assert same_events(ref[c]["events"], mapped[c]), c
+
+
 def test_oracle_vs_reference_carry_and_max_records(built):
     if not orc.have_ref():
         pytest.skip("oracle/_ref not built (reference tree absent)")
