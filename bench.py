@@ -338,7 +338,8 @@ def bench_deltas(args, rank, world, local, dev, dist):
                        "l2": "inputs exceed L2; no flush needed", "slow_tiles": ctx.slow_tiles,
                        "reruns": ctx.reruns},
             "roofline": {"bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
-                         "traffic": load_traffic("k_decode<COUNT_DELTAS>"), "kernel": "k_decode<COUNT_DELTAS>",
+                         "traffic": (load_traffic(f"k_decode<COUNT_DELTAS>@{E}ev") if not mixed else None),
+                         "kernel": "k_decode<COUNT_DELTAS>",
                          "kernel_ms": k_ms, "algorithmic_bytes": int(algo), "peak_source": peak_src},
             "gpu_launches": int(launches), "clocks": clocks}
     if cb:
