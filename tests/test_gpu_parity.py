@@ -540,3 +540,47 @@ def test_batch_submit_and_device_views(ctx):
         n_slabs = C.c_uint32()
         assert ctx.lib.hbt_rows_slabs_dev(ctx.h, cpu, ptrs, ns, C.byref(n_slabs)) == 0
         assert sum(ns[i] for i in range(n_slabs.value)) == want["n_rows"]
+
+
+def test_two_contexts_interleaved(built):
+    """Two contexts (own streams) with decodes in flight at the same time, the way bench.py's
+    end-to-end leg pipelines CPU groups over PCIe: results are those of separate decodes."""
+    ds, E = 1 << 19, 4
+    a, b = hbt.Context(0), hbt.Context(0)
+    try:
+        jobs = []
+        for ctx, seed, desc, base in ((a, 71, hbt.sampling_desc(E), 0), (b, 72, hbt.ip_desc(40), 8)):
+            rings = []
+            for c in range(3):
+                if desc.aggregate == hbt.AGG_COUNT_DELTAS:
+                    s = tg.group_sample_stream(seed * 10 + c, 3000, E, lost_every=301)
+                else:
+                    s = tg.ip_sample_stream(seed * 10 + c, 9000, cpu=base + c, n_pids=32, n_ips=128)
+                tail = tg.random_tail(seed + c, ds)
+                ring, head = ring_np(s, ds, tail)
+                rings.append((ring, tail, head))
+            ctx.ring_configure(3, ds)
+            ctx.set_cpu_base(base)
+            ctx.reset_state(hbt.INVALID_TS)
+            if desc.aggregate == hbt.AGG_IP_HISTOGRAM:
+                ctx.hist_configure(3 << 16)
+            jobs.append((ctx, rings, desc, base))
+        # everything queued before anything is fetched
+        for ctx, rings, desc, _ in jobs:
+            for cpu, (ring, tail, head) in enumerate(rings):
+                ctx.submit_ring_image(cpu, ring, tail, head)
+            ctx.decode(desc)
+        for ctx, rings, desc, base in reversed(jobs):
+            res = ctx.fetch_results()
+            hist = orc.hist_to_dict(ctx.hist_fetch()) if desc.aggregate == hbt.AGG_IP_HISTOGRAM else None
+            want_hist = {}
+            for cpu, (ring, tail, head) in enumerate(rings):
+                want = orc.port_consume(ring, tail, head, desc, cpu=base + cpu)
+                check_cpu(ctx, cpu, res[cpu], want, desc)
+                if want.get("hist"):
+                    want_hist.update(want["hist"])
+            if hist is not None:
+                assert hist == want_hist
+    finally:
+        a.close()
+        b.close()
