@@ -124,6 +124,11 @@ class GroupReadValues {
   // float(double(getCount(i)) * 1e3 / double(getTimeRunning())): PerfMonitor.cpp:56-57
   float getRatePerMs(size_t i) const { return rates_.at(checked(i)); }
   bool hasMultiplexing() const { return t_[1] != 0 && t_[2] != t_[1]; }
+  // Accessors on the summed triple, formulas as written in the reference
+  // (CpuEventsGroup.h:481-501; note that getRunningRatio divides enabled by running)
+  float getRunningRatio() const { return t_[1] == 0 ? 1.0f : (float)t_[1] / (float)t_[2]; }
+  template <size_t scale = 100>
+  uint64_t getRunningRatioInteger() const { return t_[1] == 0 ? scale : (scale * t_[2]) / t_[1]; }
   uint64_t* raw() { return t_.data(); }
   const uint64_t* raw() const { return t_.data(); }
   uint64_t* scaled() { return scaled_.data(); }

@@ -68,6 +68,10 @@ static void test_cpu() {
   CHECK(rv.getNumEvents() == 3 && rv.getNumReadBytes() == 48);
   CHECK(throws<std::invalid_argument>([&] { rv.getRawCount(3); }));
   CHECK(!rv.hasMultiplexing());
+  CHECK(rv.getRunningRatio() == 1.0f && rv.getRunningRatioInteger<>() == 100);  // time_enabled == 0
+  rv.raw()[1] = 4000;
+  rv.raw()[2] = 1000;
+  CHECK(rv.hasMultiplexing() && rv.getRunningRatio() == 4.0f && rv.getRunningRatioInteger<1000>() == 250);
   std::ostringstream os;
   dynolog_gpu::JsonLogger lg(os);
   lg.logFloat("mips", 691.4972f);
