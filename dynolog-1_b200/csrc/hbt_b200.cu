@@ -378,6 +378,9 @@ int launch_decode_agg(hbt_ctx* ctx) {
     if (!ctx->attr_set[AGG]) {
       CU(cudaFuncSetAttribute(k_decode<AGG>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                               (int)smem));
+      // the staging area decides how many CTAs share an SM: ask for all the shared memory
+      CU(cudaFuncSetAttribute(k_decode<AGG>, cudaFuncAttributePreferredSharedMemoryCarveout,
+                              (int)cudaSharedmemCarveoutMaxShared));
       ctx->attr_set[AGG] = true;
     }
     CU(cudaEventRecord(ctx->ev_k0, ctx->stream));
