@@ -243,8 +243,10 @@ int build_tables(hbt_ctx* ctx, const uint64_t* clamp_head, const int64_t* clamp_
   if (segs_per_cpu > kMaxSegsPerCpu) segs_per_cpu = kMaxSegsPerCpu;
   if (segs_per_cpu < 1) segs_per_cpu = 1;
 
+  uint64_t min_tiles_per_seg = 8;
+  if (const char* e = getenv("HBT_MIN_TILES_PER_SEG")) min_tiles_per_seg = (uint64_t)atoi(e);  // tuning aid
   std::vector<SegDesc> segs;
-  segs.reserve((size_t)C * 4);
+  segs.reserve((size_t)active * segs_per_cpu + 1);  // no regrowth while the tables are built
   const uint64_t row_words = 2 + (uint64_t)d.n_events;
   uint64_t rows_total_words = 0;
   const bool sw = d.aggregate == HBT_AGG_SWITCH_EVENTS;  // 16-byte proto-events in the row slabs
@@ -284,9 +286,7 @@ int build_tables(hbt_ctx* ctx, const uint64_t* clamp_head, const int64_t* clamp_
       const uint64_t t1 = (w.head + kTile - 1) / kTile;
       const uint64_t nt = t1 - t0;
       uint64_t per = (nt + segs_per_cpu - 1) / segs_per_cpu;
-      uint64_t min_per = 8;
-      if (const char* e = getenv("HBT_MIN_TILES_PER_SEG")) min_per = (uint64_t)atoi(e);  // tuning aid
-      if (per < min_per) per = min_per;
+      if (per < min_tiles_per_seg) per = min_tiles_per_seg;
       uint32_t k = 0;
       for (uint64_t tb = t0; tb < t1; tb += per, ++k) {
         SegDesc s{};
