@@ -259,18 +259,11 @@ __device__ __forceinline__ uint32_t hist_reserve(const HistLists& t, uint32_t cp
                                                  uint32_t& list) {
   const uint32_t b = (uint32_t)(((uint64_t)hash * t.buckets) >> 32);
   list = cpu * t.buckets + b;
-#if HBT_EXP == 1 || HBT_EXP == 3  // timing experiment: no global atomic (results are wrong)
-  return (hash >> 7) & 1023u;
-#else
   return atomicAdd(t.cursors + list, 1u);
-#endif
 }
 __device__ __forceinline__ void hist_store(const HistLists& t, uint32_t list, uint32_t pos,
                                            uint64_t ip, uint32_t pid, uint32_t weight) {
   if (pos < t.cap) {
-#if HBT_EXP == 2 || HBT_EXP == 3  // timing experiment: no entry store
-    if (pos == 0xFFFFFFF0u)
-#endif
     t.entries[(uint64_t)list * t.cap + pos] =
         make_ulonglong2(ip, (uint64_t)pid | ((uint64_t)weight << 32));
   } else {
@@ -308,9 +301,6 @@ struct HistCache {
 __device__ __forceinline__ bool hist_cache_count(HistCache& c, uint64_t ip, uint32_t pid,
                                                  uint32_t& hash) {
   hash = hist_hash(ip, pid);
-#if HBT_EXP == 4  // timing experiment: no segment cache
-  return false;
-#endif
   const uint32_t set = (hash ^ (hash >> 16)) & (kCacheSlots - 2);  // slots set, set + 1
   const uint32_t tag = hash | 1u;
   const uint64_t tg = *reinterpret_cast<const volatile uint64_t*>(c.tags + set);
