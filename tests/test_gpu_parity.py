@@ -584,3 +584,25 @@ def test_two_contexts_interleaved(built):
     finally:
         a.close()
         b.close()
+
+
+def test_max_cpus_decode(built):
+    """HBT_MAX_CPUS rings in one decode (the reference's kMaxCpus, System.h:195): every CPU's
+    counters, rows and carry against the oracle."""
+    ds, E, n_cpus = 1 << 16, 3, hbt.MAX_CPUS
+    ctx = hbt.Context(0)
+    try:
+        rings = []
+        for c in range(n_cpus):
+            s = tg.group_sample_stream(9000 + c, 200 + (c % 7) * 40, E, lost_every=53 if c % 3 else 0)
+            tail = tg.random_tail(c, ds)
+            ring, head = ring_np(s, ds, tail)
+            rings.append((ring, tail, head))
+        desc = hbt.sampling_desc(E)
+        res = gpu_decode(ctx, rings, desc, ds)
+        for c in (0, 1, 2, 255, 256, 300, 510, 511):
+            check_cpu(ctx, c, res[c], orc.port_consume(*rings[c], desc), desc)
+        want_rec = [orc.port_consume(*rings[c], desc)["n_records"] for c in range(n_cpus)]
+        assert [int(r) for r in res["n_records"]] == want_rec
+    finally:
+        ctx.close()
