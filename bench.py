@@ -59,7 +59,10 @@ def load_peaks():
 
 
 class ClockSampler:
-    """nvidia-smi clocks + throttle reasons during the timed region."""
+    """nvidia-smi clocks + throttle reasons during the timed region.  The process is started
+    ahead of the region (its start-up takes the driver's locks for a moment and would otherwise
+    stall the first timed step of every rank on the box); stop(t0, t1) keeps the samples that
+    were read inside [t0, t1]."""
     Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,"
          "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
          "clocks_event_reasons.sw_power_cap")
@@ -73,7 +76,7 @@ class ClockSampler:
         try:
             self.proc = subprocess.Popen(
                 ["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}",
-                 "--format=csv,noheader,nounits", "-lms", "100"],
+                 "--format=csv,noheader,nounits", "-lms", "20"],
                 stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             self.thread = threading.Thread(target=self._read, daemon=True)
             self.thread.start()
@@ -82,9 +85,9 @@ class ClockSampler:
 
     def _read(self):
         for line in self.proc.stdout:
-            self.samples.append(line.strip())
+            self.samples.append((time.time(), line.strip()))
 
-    def stop(self):
+    def stop(self, t0=None, t1=None):
         if not self.proc:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
         self.proc.terminate()
@@ -94,7 +97,10 @@ class ClockSampler:
             self.proc.kill()
         sm, mx, reasons = [], [], set()
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        for s in self.samples:
+        lines = [l for ts, l in self.samples if t0 is None or t0 <= ts <= t1 + 0.02]
+        if not lines:  # a region shorter than the sampling period: the samples closest to it
+            lines = [l for _, l in sorted(self.samples, key=lambda x: abs(x[0] - t1))[:3]]
+        for s in lines:
             parts = [x.strip() for x in s.split(",")]
             if len(parts) < 6:
                 continue
@@ -271,19 +277,20 @@ def bench_deltas(args, rank, world, local, dev, dist):
         step.res = ctx.fetch_results()
         kms.append(ctx.decode_kernel_ms)
 
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()  # ahead of the warm-up: see ClockSampler
     for _ in range(max(args.warmup, 3)):
         step()
     res = step.res
     assert int(res["n_records"].sum()) == n_rec
     n_rows = int(res["n_rows"].sum())
     kms.clear()
-    sampler = ClockSampler(local)
-    if rank == 0:
-        sampler.start()
     l0 = ctx.launches
+    wall0 = time.time()
     ms_step = timed_steps(step, args.steps, dist, dev)
     launches = ctx.launches - l0
-    clocks = sampler.stop() if rank == 0 else None
+    clocks = sampler.stop(wall0, time.time()) if rank == 0 else None
     if rank != 0:
         return None
     peak, peak_src = load_peaks()
@@ -371,16 +378,17 @@ def bench_counts(args, rank, world, local, dev, dist):
             sharding.allreduce_partial_sums(sums, E)
             ctx.counts_scale_dev(sums, I, E, ratios, None, scaled, rates, ratio, deltas)
 
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()  # ahead of the warm-up: see ClockSampler
     for _ in range(max(args.warmup, 3)):
         step()
     ctx.sync()
-    sampler = ClockSampler(local)
-    if rank == 0:
-        sampler.start()
     l0 = ctx.launches
+    wall0 = time.time()
     ms_step = timed_steps(step, args.steps, dist, dev)
     launches = ctx.launches - l0
-    clocks = sampler.stop() if rank == 0 else None
+    clocks = sampler.stop(wall0, time.time()) if rank == 0 else None
     if rank != 0:
         return None
     peak, peak_src = load_peaks()
@@ -616,6 +624,9 @@ def main():
             dist.destroy_process_group()
         return
 
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()  # long before the timed region: see ClockSampler
     ring_bytes = args.ring_mib << 20
     cpu_base = rank * args.cpus
     imgs, tails, heads, n_rec = make_c2(args.cpus, ring_bytes, cpu_base, dev)
@@ -658,9 +669,6 @@ def main():
     slow, reruns = ctx.slow_tiles, ctx.reruns
 
     # ---- timed region: device-resident ----------------------------------------
-    sampler = ClockSampler(local)
-    if rank == 0:
-        sampler.start()
     launches0 = ctx.launches
     kernel_ms, fold_ms = [], []
     if dist is not None:
@@ -669,9 +677,13 @@ def main():
     e0 = torch.cuda.Event(enable_timing=True)
     e1 = torch.cuda.Event(enable_timing=True)
     e0.record()
+    wall0 = time.time()
+    host_us = []
     for _ in range(args.steps):
         # the decode path shards by CPU with no exchange step: no collective in here
+        h0 = time.perf_counter()
         step()
+        host_us.append((time.perf_counter() - h0) * 1e6)  # host time to queue one step
         # completing the decode (re-run check) is part of the step; it syncs the stream
         last_res = ctx.fetch_results()
         kernel_ms.append(ctx.decode_kernel_ms)
@@ -683,7 +695,7 @@ def main():
         dist.barrier()
     ms_total = e0.elapsed_time(e1)
     launches = ctx.launches - launches0
-    clocks = sampler.stop() if rank == 0 else None
+    clocks = sampler.stop(wall0, time.time()) if rank == 0 else None
     # the metric-table merge across the GPUs of the box, once, outside the timed steps: the
     # per-type record counters of every rank's CPUs summed over NCCL (and checked)
     counters_dev.zero_()
@@ -694,8 +706,12 @@ def main():
     assert merged_samples == n_rec * world * (max(args.warmup, 3) + args.steps), merged_samples
 
     t = torch.tensor([ms_total], dtype=torch.float64, device=dev)
+    # per-rank spread (diagnostic): slowest rank's kernel span and host queueing time per step
+    spread = torch.tensor([(sum(kernel_ms) + sum(fold_ms)) / len(kernel_ms), sum(host_us) / len(host_us)],
+                          dtype=torch.float64, device=dev)
     if dist is not None:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        dist.all_reduce(spread, op=dist.ReduceOp.MAX)
     ms_step = float(t.item()) / args.steps
     value = n_rec * world / (ms_step * 1e-3)
 
@@ -804,7 +820,9 @@ def main():
                    "l2": "inputs (4 GiB/GPU) exceed L2; no flush needed",
                    "sharding": "by CPU id, 256 CPUs per rank, no collective in the decode path; per-type counters "
                                "merged over NCCL once after the timed steps",
-                   "slow_tiles": slow, "reruns": reruns},
+                   "slow_tiles": slow, "reruns": reruns,
+                   "max_over_ranks": {"kernel_ms": float(spread[0].item()),
+                                      "host_queue_us_per_step": float(spread[1].item())}},
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
                      "frac": achieved / peak,
                      "traffic": load_traffic("k_decode<IP_HISTOGRAM>") if args.agg == "hist" else None,
