@@ -94,12 +94,15 @@ EXPORTS = [
     ("hbt_set_stream", C.c_int, [_P, _P]),
     ("hbt_sync", C.c_int, [_P]),
     ("hbt_launch_count", C.c_uint64, [_P]),
+    ("hbt_set_geometry", C.c_int, [_P, C.c_uint32, C.c_uint32]),
     ("hbt_set_cpu_base", C.c_int, [_P, C.c_uint32]),
     ("hbt_ring_configure", C.c_int, [_P, C.c_uint32, C.c_uint64]),
     ("hbt_submit_ring", C.c_int, [_P, C.c_uint32, _P, C.c_size_t, _P, C.c_size_t, C.c_uint64]),
     ("hbt_submit_ring_dev", C.c_int, [_P, C.c_uint32, _P, C.c_uint64, C.c_uint64, C.c_uint64]),
     ("hbt_submit_rings_dev", C.c_int, [_P, C.c_uint32, _P, C.c_uint64, _P, _P]),
     ("hbt_ring_reset_state", C.c_int, [_P, C.c_uint64]),
+    ("hbt_ring_set_carry", C.c_int, [_P, C.c_uint32, C.c_uint64, _P, C.c_uint32, _P, C.c_uint64]),
+    ("hbt_ring_set_switch_state", C.c_int, [_P, C.c_uint32, C.c_uint64, C.c_uint32]),
     ("hbt_decode", C.c_int, [_P, C.POINTER(DecodeDesc)]),
     ("hbt_fetch_results", C.c_int, [_P, _P, C.c_uint32]),
     ("hbt_decode_reruns", C.c_uint32, [_P]),
@@ -235,6 +238,10 @@ class Context:
     def launches(self) -> int:
         return int(self.lib.hbt_launch_count(self.h))
 
+    def set_geometry(self, segs_per_cpu: int = 0, min_tiles_per_seg: int = 0):
+        """Segments per CPU / tiles per segment of the decode (0 = automatic)."""
+        self._ck(self.lib.hbt_set_geometry(self.h, segs_per_cpu, min_tiles_per_seg))
+
     def set_cpu_base(self, base: int):
         self._ck(self.lib.hbt_set_cpu_base(self.h, base))
 
@@ -271,6 +278,17 @@ class Context:
 
     def reset_state(self, seed_tstamp: int = INVALID_TS):
         self._ck(self.lib.hbt_ring_reset_state(self.h, seed_tstamp))
+
+    def set_carry(self, cpu: int, carry_tstamp: int, last=None, counters=None, num_unknown: int = 0):
+        """Restore count_.tstamp / last_[] / num_record_*_ of one CPU (hbt_ring_set_carry)."""
+        la = None if last is None else np.ascontiguousarray(last, dtype=np.uint64)
+        ca = None if counters is None else np.ascontiguousarray(counters, dtype=np.uint64)
+        assert ca is None or ca.shape[0] == NUM_COUNTERS
+        self._ck(self.lib.hbt_ring_set_carry(self.h, cpu, carry_tstamp, _ptr(la),
+                                             0 if la is None else la.shape[0], _ptr(ca), num_unknown))
+
+    def set_switch_state(self, cpu: int, last_tstamp: int, in_write_errors: int):
+        self._ck(self.lib.hbt_ring_set_switch_state(self.h, cpu, last_tstamp, in_write_errors))
 
     # ---- decode
     def decode(self, desc: DecodeDesc):

@@ -5,6 +5,7 @@
 #include <cuda_runtime.h>
 #include <cerrno>
 #include <cstdarg>
+#include <cstddef>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -111,6 +112,7 @@ struct hbt_ctx {
   PinBuf<int64_t> h_clamp_ret;
   PinBuf<uint32_t> h_flags;
   uint32_t n_segs = 0;
+  uint32_t geo_segs_per_cpu = 0, geo_min_tiles = 0;  // hbt_set_geometry; 0 = automatic
   bool tiled = true;
   bool attr_set[4] = {false, false, false, false};
   bool pending = false;  // a decode was launched and not yet fetched
@@ -139,6 +141,7 @@ struct hbt_ctx {
   DevBuf<uint32_t> hist_cursors, hist_cursors_snap;
   DevBuf<uint32_t> hist_overflow;
   uint32_t hist_buckets = 0, hist_cap = 0;
+  uint32_t hist_n_cpus = 0;        // the n_cpus the lists were sized for
   bool hist_pending_fold = false;  // the last decode appended raw samples not yet folded
   bool agg_attr_set = false;
   bool counts_attr_set = false;
@@ -205,7 +208,8 @@ int validate_desc(hbt_ctx* ctx, const hbt_decode_desc* d) {
   if (d->aggregate == HBT_AGG_IP_HISTOGRAM) {
     if (d->sample_layout != HBT_SAMPLE_IP || !(d->handled_mask & HBT_H_SAMPLE))
       return fail(ctx, -EINVAL, "IP_HISTOGRAM needs handled IP SAMPLE records");
-    if (ctx->hist_buckets == 0) return fail(ctx, -EINVAL, "hbt_hist_configure first");
+    if (ctx->hist_buckets == 0 || ctx->hist_n_cpus != ctx->n_cpus)
+      return fail(ctx, -EINVAL, "hbt_hist_configure first (after the rings are configured)");
   }
   if (d->sample_layout == HBT_SAMPLE_IP &&
       (d->ip_sample_bytes < 40 || (d->ip_sample_bytes & 7) || d->ip_sample_bytes > 65528))
@@ -239,12 +243,12 @@ int build_tables(hbt_ctx* ctx, const uint64_t* clamp_head, const int64_t* clamp_
   uint32_t segs_per_cpu = active ? (uint32_t)((target_ctas + active - 1) / active) : 1;
   // the histogram's per-segment cache of hot keys wants short segments
   if (d.aggregate == HBT_AGG_IP_HISTOGRAM && segs_per_cpu < 16) segs_per_cpu = 16;
-  if (const char* e = getenv("HBT_SEGS_PER_CPU")) segs_per_cpu = (uint32_t)atoi(e);  // tuning aid
+  if (ctx->geo_segs_per_cpu) segs_per_cpu = ctx->geo_segs_per_cpu;  // hbt_set_geometry
   if (segs_per_cpu > kMaxSegsPerCpu) segs_per_cpu = kMaxSegsPerCpu;
   if (segs_per_cpu < 1) segs_per_cpu = 1;
 
   uint64_t min_tiles_per_seg = 8;
-  if (const char* e = getenv("HBT_MIN_TILES_PER_SEG")) min_tiles_per_seg = (uint64_t)atoi(e);  // tuning aid
+  if (ctx->geo_min_tiles) min_tiles_per_seg = ctx->geo_min_tiles;
   std::vector<SegDesc> segs;
   segs.reserve((size_t)active * segs_per_cpu + 1);  // no regrowth while the tables are built
   const uint64_t row_words = 2 + (uint64_t)d.n_events;
@@ -614,6 +618,9 @@ const char* hbt_last_error(const hbt_ctx* ctx) { return ctx ? ctx->err.c_str() :
 
 int hbt_set_stream(hbt_ctx* ctx, void* cuda_stream) {
   if (!ctx) return -EINVAL;
+  // a pending decode finishes on the stream it was queued on (its completion reads results
+  // back and may launch re-runs there)
+  if (int rc = complete_decode(ctx)) return rc;
   ctx->stream = cuda_stream ? static_cast<cudaStream_t>(cuda_stream) : ctx->own_stream;
   return 0;
 }
@@ -625,6 +632,14 @@ int hbt_sync(hbt_ctx* ctx) {
 }
 
 uint64_t hbt_launch_count(const hbt_ctx* ctx) { return ctx ? ctx->launches : 0; }
+
+int hbt_set_geometry(hbt_ctx* ctx, uint32_t segs_per_cpu, uint32_t min_tiles_per_seg) {
+  if (!ctx) return -EINVAL;
+  if (segs_per_cpu > (uint32_t)kMaxSegsPerCpu) return fail(ctx, -EINVAL, "segs_per_cpu > %d", kMaxSegsPerCpu);
+  ctx->geo_segs_per_cpu = segs_per_cpu;
+  ctx->geo_min_tiles = min_tiles_per_seg;
+  return 0;
+}
 
 int hbt_set_cpu_base(hbt_ctx* ctx, uint32_t cpu_base) {
   if (!ctx) return -EINVAL;
@@ -651,7 +666,48 @@ int hbt_ring_reset_state(hbt_ctx* ctx, uint64_t seed_tstamp) {
   return 0;
 }
 
+int hbt_ring_set_carry(hbt_ctx* ctx, uint32_t cpu, uint64_t carry_tstamp, const uint64_t* last,
+                       uint32_t n_events, const uint64_t* counters, uint64_t num_unknown) {
+  if (!ctx || cpu >= ctx->n_cpus) return fail(ctx, -EINVAL, "cpu out of range");
+  if (n_events > HBT_MAX_EVENTS || (n_events && !last)) return fail(ctx, -EINVAL, "bad last_[]");
+  CU(cudaSetDevice(ctx->device));
+  if (int rc = complete_decode(ctx)) return rc;
+  // the committed generator state of this CPU; the copies below are ordered on the ctx stream
+  // behind everything queued so far and read their (pageable or pinned) sources before returning
+  uint8_t* st = reinterpret_cast<uint8_t*>(ctx->state[ctx->cur].p + cpu);
+  CU(cudaMemcpyAsync(st + offsetof(CpuState, carry_tstamp), &carry_tstamp, 8, cudaMemcpyHostToDevice,
+                     ctx->stream));
+  CU(cudaMemcpyAsync(st + offsetof(CpuState, num_unknown), &num_unknown, 8, cudaMemcpyHostToDevice,
+                     ctx->stream));
+  if (n_events)
+    CU(cudaMemcpyAsync(st + offsetof(CpuState, carry_last), last, 8ull * n_events,
+                       cudaMemcpyHostToDevice, ctx->stream));
+  if (counters)
+    CU(cudaMemcpyAsync(st + offsetof(CpuState, counters), counters, 8ull * HBT_NUM_COUNTERS,
+                       cudaMemcpyHostToDevice, ctx->stream));
+  CU(cudaStreamSynchronize(ctx->stream));
+  return 0;
+}
+
+int hbt_ring_set_switch_state(hbt_ctx* ctx, uint32_t cpu, uint64_t last_tstamp, uint32_t in_write_errors) {
+  if (!ctx || cpu >= ctx->n_cpus) return fail(ctx, -EINVAL, "cpu out of range");
+  CU(cudaSetDevice(ctx->device));
+  if (int rc = complete_decode(ctx)) return rc;
+  const uint32_t e = in_write_errors ? 1u : 0u;
+  CU(cudaMemcpyAsync(ctx->sw_state_ts.p + cpu, &last_tstamp, 8, cudaMemcpyHostToDevice, ctx->stream));
+  CU(cudaMemcpyAsync(ctx->sw_state_err.p + cpu, &e, 4, cudaMemcpyHostToDevice, ctx->stream));
+  CU(cudaStreamSynchronize(ctx->stream));
+  return 0;
+}
+
 static int configure_common(hbt_ctx* ctx, uint32_t n_cpus) {
+  if (int rc = complete_decode(ctx)) return rc;
+  if (n_cpus != ctx->hist_n_cpus) {
+    // the histogram lists are laid out [n_cpus][lists][cap]: a different CPU count needs
+    // hbt_hist_configure again (validate_desc refuses an IP_HISTOGRAM decode until then)
+    ctx->hist_buckets = 0;
+    ctx->hist_n_cpus = 0;
+  }
   ctx->n_cpus = n_cpus;
   ctx->win.assign(n_cpus, Window());
   CU(ctx->state[0].reserve(n_cpus));
@@ -1129,6 +1185,7 @@ int hbt_hist_configure(hbt_ctx* ctx, uint64_t capacity_slots) {
   CU(cudaSetDevice(ctx->device));
   ctx->hist_buckets = (uint32_t)buckets;
   ctx->hist_cap = cap;
+  ctx->hist_n_cpus = ctx->n_cpus;
   CU(ctx->hist_entries.reserve(hist_lists(ctx) * cap));
   CU(ctx->hist_cursors.reserve(hist_lists(ctx)));
   CU(ctx->hist_cursors_snap.reserve(hist_lists(ctx)));
@@ -1235,8 +1292,7 @@ static int counts_launch(hbt_ctx* ctx, const uint64_t* reads, uint64_t n_interva
   }
   const uint64_t interval_bytes = (uint64_t)n_cpus * (3 + n_events) * 8;
   const bool tma_ok = 3 + n_events <= 32 && interval_bytes <= (uint64_t)kCountsStageBytes &&
-                      (interval_bytes & 15) == 0 && ((uintptr_t)reads & 15) == 0 &&
-                      !getenv("HBT_COUNTS_NO_TMA");
+                      (interval_bytes & 15) == 0 && ((uintptr_t)reads & 15) == 0;
   if (tma_ok) {
     // whole intervals staged in shared memory by bulk async copies
     const size_t smem = (size_t)kCountsStages * kCountsStageBytes + 64 + 8 * 32 * 8;

@@ -1,5 +1,5 @@
 // Small sm_100a PTX wrappers used by the decode / counts kernels: streaming
-// loads, mbarrier, 1-D bulk async copy (TMA unit, SASS UBLKCP) and 128-bit CAS.
+// loads, mbarrier, 1-D bulk async copy (TMA unit, SASS UBLKCP) and the shared-memory 128-bit CAS.
 #pragma once
 #include <cstdint>
 
@@ -9,20 +9,12 @@ __device__ __forceinline__ uint32_t smem_u32(const void* p) {
   return static_cast<uint32_t>(__cvta_generic_to_shared(p));
 }
 
-// Streaming 8/16-byte global loads that do not allocate in L1 (data is touched once).
+// Streaming 8-byte global loads that do not allocate in L1 (data is touched once).
 __device__ __forceinline__ uint64_t ld_stream_u64(const uint64_t* p) {
   uint64_t v;
   asm volatile("ld.global.nc.L1::no_allocate.u64 %0, [%1];" : "=l"(v) : "l"(p));
   return v;
 }
-__device__ __forceinline__ ulonglong2 ld_stream_v2u64(const void* p) {
-  ulonglong2 v;
-  asm volatile("ld.global.nc.L1::no_allocate.v2.u64 {%0, %1}, [%2];"
-               : "=l"(v.x), "=l"(v.y)
-               : "l"(p));
-  return v;
-}
-
 // ---- mbarrier --------------------------------------------------------------
 __device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
   asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
@@ -114,62 +106,12 @@ __device__ __forceinline__ uint64_t lds_u64(uint32_t saddr) {
   return v;
 }
 
-__device__ __forceinline__ uint32_t ld_acquire_u32(const uint32_t* p) {
-  uint32_t v;
-  asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
-  return v;
-}
-
-// Fire-and-forget global add (SASS RED): no return value, no round-trip wait.
-__device__ __forceinline__ void red_add_u32(uint32_t* p, uint32_t v) {
-  asm volatile("red.global.add.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
-}
-
 // Order generic-proxy reads of a stage before the async proxy overwrites it.
 __device__ __forceinline__ void fence_proxy_async() {
   asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
 }
 
-// ---- 128-bit compare-and-swap (SASS ATOMG.E.CAS.128) --------------------------
-__device__ __forceinline__ void cas128_global(void* addr, uint64_t clo, uint64_t chi,
-                                              uint64_t nlo, uint64_t nhi, uint64_t& olo,
-                                              uint64_t& ohi) {
-  asm volatile(
-      "{\n\t.reg .b128 c, n, d;\n\t"
-      "mov.b128 c, {%3, %4};\n\t"
-      "mov.b128 n, {%5, %6};\n\t"
-      "atom.global.relaxed.gpu.cas.b128 d, [%2], c, n;\n\t"
-      "mov.b128 {%0, %1}, d;\n\t}"
-      : "=l"(olo), "=l"(ohi)
-      : "l"(addr), "l"(clo), "l"(chi), "l"(nlo), "l"(nhi)
-      : "memory");
-}
-
-// The same with an L2 eviction-priority hint (the histogram table is re-used,
-// the ring bytes streaming past it are not).
-__device__ __forceinline__ uint64_t l2_policy_evict_last() {
-  uint64_t pol;
-  asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(pol));
-  return pol;
-}
-__device__ __forceinline__ void cas128_global_hint(void* addr, uint64_t clo, uint64_t chi,
-                                                   uint64_t nlo, uint64_t nhi, uint64_t& olo,
-                                                   uint64_t& ohi, uint64_t policy) {
-  asm volatile(
-      "{\n\t.reg .b128 c, n, d;\n\t"
-      "mov.b128 c, {%3, %4};\n\t"
-      "mov.b128 n, {%5, %6};\n\t"
-      "atom.global.relaxed.gpu.cas.L2::cache_hint.b128 d, [%2], c, n, %7;\n\t"
-      "mov.b128 {%0, %1}, d;\n\t}"
-      : "=l"(olo), "=l"(ohi)
-      : "l"(addr), "l"(clo), "l"(chi), "l"(nlo), "l"(nhi), "l"(policy)
-      : "memory");
-}
-__device__ __forceinline__ void red_add_u32_hint(uint32_t* p, uint32_t v, uint64_t policy) {
-  asm volatile("red.global.add.L2::cache_hint.u32 [%0], %1, %2;" ::"l"(p), "r"(v), "l"(policy)
-               : "memory");
-}
-
+// 128-bit compare-and-swap on shared memory (claims a 16-byte cache slot in one step).
 __device__ __forceinline__ void cas128_shared(uint32_t saddr, uint64_t clo, uint64_t chi,
                                               uint64_t nlo, uint64_t nhi, uint64_t& olo,
                                               uint64_t& ohi) {
@@ -182,24 +124,6 @@ __device__ __forceinline__ void cas128_shared(uint32_t saddr, uint64_t clo, uint
       : "=l"(olo), "=l"(ohi)
       : "r"(saddr), "l"(clo), "l"(chi), "l"(nlo), "l"(nhi)
       : "memory");
-}
-
-__device__ __forceinline__ ulonglong2 ld_relaxed_v2u64(const void* p) {
-  ulonglong2 v;
-  asm volatile("ld.relaxed.gpu.global.v2.u64 {%0, %1}, [%2];"
-               : "=l"(v.x), "=l"(v.y)
-               : "l"(p)
-               : "memory");
-  return v;
-}
-
-__device__ __forceinline__ uint64_t mix64(uint64_t x) {
-  x ^= x >> 33;
-  x *= 0xff51afd7ed558ccdull;
-  x ^= x >> 33;
-  x *= 0xc4ceb9fe1a85ec53ull;
-  x ^= x >> 33;
-  return x;
 }
 
 }  // namespace hbt

@@ -164,6 +164,15 @@ MIXED_MIX = (("sample", 0.70), ("switch", 0.15), ("comm", 0.05), ("mmap", 0.05),
              ("fork", 0.0245), ("exit", 0.0245))
 
 
+# Every record type consume() dispatches on (CpuEventsGroup.h:1372-1501): the config-4 mix plus
+# THROTTLE / UNTHROTTLE (hdr time id stream_id), READ (mode::Sampling::Read, :247-259), AUX and
+# ITRACE_START (mode::AUXSpace, :205-227).
+FULL_MIX = (("sample", 0.55), ("switch", 0.15), ("comm", 0.05), ("mmap", 0.05), ("lost", 0.01),
+            ("fork", 0.03), ("exit", 0.03), ("throttle", 0.02), ("unthrottle", 0.02), ("read", 0.04),
+            ("aux", 0.03), ("itrace", 0.02))
+_TRAILER_KINDS = ("switch", "comm", "mmap", "lost", "fork", "exit")
+
+
 def mixed_stream(seed: int, n_records: int, n_events: int, device="cpu", mix=MIXED_MIX,
                  t0: int = 1_000_000, unknown_types: bool = True) -> torch.Tensor:
     """Mixed stream (config 4) in the harness-local Mixed mode: ContextSwitch
@@ -181,7 +190,8 @@ def mixed_stream(seed: int, n_records: int, n_events: int, device="cpu", mix=MIX
     name_w = 1 + rand_below(seed, n, 2, device, 22)     # comm: 1..16 B name, padded to 8
     file_w = 1 + rand_below(seed, n, 32, device, 23)    # mmap: 8..256 B filename
     words = torch.zeros(n, dtype=torch.int64, device=device)
-    sizes = {"sample": 5 + E, "switch": 4, "lost": 5, "fork": 6, "exit": 6}
+    sizes = {"sample": 5 + E, "switch": 4, "lost": 5, "fork": 6, "exit": 6, "throttle": 4,
+             "unthrottle": 4, "read": 5 + E, "aux": 4, "itrace": 2}
     for i, k in enumerate(kinds):
         sel = kind == i
         if k == "comm":
@@ -198,7 +208,9 @@ def mixed_stream(seed: int, n_records: int, n_events: int, device="cpu", mix=MIX
     pid = 100 + rand_below(seed, n, 4096, device, 26)
     pidtid = pid | ((pid + 1) << 32)
     types = {"sample": REC_SAMPLE, "switch": REC_SWITCH_CPU_WIDE, "comm": REC_COMM,
-             "mmap": REC_MMAP, "lost": REC_LOST, "fork": REC_FORK, "exit": REC_EXIT}
+             "mmap": REC_MMAP, "lost": REC_LOST, "fork": REC_FORK, "exit": REC_EXIT,
+             "throttle": REC_THROTTLE, "unthrottle": REC_UNTHROTTLE, "read": REC_READ,
+             "aux": REC_AUX, "itrace": REC_ITRACE_START}
     hdr = torch.zeros(n, dtype=torch.int64, device=device)
     for i, k in enumerate(kinds):
         hdr = torch.where(kind == i, types[k] | (words << 51), hdr)  # size = 8*words -> << 48+3
@@ -209,8 +221,11 @@ def mixed_stream(seed: int, n_records: int, n_events: int, device="cpu", mix=MIX
         hdr = torch.where(is_mmap & (alt == 0), (hdr & ~0xFFFFFFFF) | 10, hdr)
         hdr = torch.where(is_mmap & (alt == 1), (hdr & ~0xFFFFFFFF) | 19, hdr)
     out[off] = hdr
-    # sample_id trailer {pid,tid ; time} on every non-SAMPLE record
-    non_sample = kind != kinds.index("sample")
+    # sample_id trailer {pid,tid ; time} on the context-switch style records
+    non_sample = torch.zeros(n, dtype=torch.bool, device=device)
+    for i, k in enumerate(kinds):
+        if k in _TRAILER_KINDS:
+            non_sample |= kind == i
     o = off[non_sample]
     w = words[non_sample]
     out[o + w - 2] = pidtid[non_sample]
@@ -233,7 +248,21 @@ def mixed_stream(seed: int, n_records: int, n_events: int, device="cpu", mix=MIX
     if lo.numel():
         out[lo + 1] = 5
         out[lo + 2] = 1 + rand_below(seed, lo.numel(), 100, device, 29)
-    # SWITCH_CPU_WIDE misc: half are switch-out
+    if "read" in kinds:   # hdr {pid,tid} nr time_enabled time_running value[nr]
+        sel = kind == kinds.index("read")
+        ro = off[sel]
+        if ro.numel():
+            out[ro + 1] = pidtid[sel]
+            out[ro + 2] = E
+            out[ro + 3] = ts[sel] - t0
+            out[ro + 4] = ts[sel] - t0
+    for k in ("throttle", "unthrottle"):   # hdr time id stream_id
+        if k in kinds:
+            sel = kind == kinds.index(k)
+            out[off[sel] + 1] = ts[sel]
+    if "itrace" in kinds:  # hdr {pid,tid}
+        sel = kind == kinds.index("itrace")
+        out[off[sel] + 1] = pidtid[sel]
     return out
 
 

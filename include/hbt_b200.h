@@ -217,7 +217,8 @@ void hbt_destroy(hbt_ctx* ctx);
 const char* hbt_last_error(const hbt_ctx* ctx);
 
 /* Run every later call of this ctx on `cuda_stream` (a cudaStream_t); NULL
- * restores the ctx's own stream. */
+ * restores the ctx's own stream.  A decode that is still pending is completed on
+ * the stream it was queued on first (this call then blocks until it is done). */
 int hbt_set_stream(hbt_ctx* ctx, void* cuda_stream);
 
 /* Block until all work queued by this ctx is complete. */
@@ -225,6 +226,14 @@ int hbt_sync(hbt_ctx* ctx);
 
 /* Number of kernels this ctx launched since creation (bench.py's gpu_launches). */
 uint64_t hbt_launch_count(const hbt_ctx* ctx);
+
+/* How a CPU's unread window is cut into segments (one CTA each): at most
+ * segs_per_cpu segments of at least min_tiles_per_seg 16-KiB tiles.  0 = let the
+ * library choose from the number of active CPUs and the SM count (the default).
+ * Results never depend on it; it exists for benchmarks and tests that want to
+ * exercise many segment seams.  No counterpart in the reference (one thread
+ * walks a whole ring, CpuEventsGroup.h:1348). */
+int hbt_set_geometry(hbt_ctx* ctx, uint32_t segs_per_cpu, uint32_t min_tiles_per_seg);
 
 /* CPU ids reported in hbt_hist_entry are cpu_base + the ctx-local index: a rank
  * that holds the shard [cpu_base, cpu_base + n_cpus) of a larger machine sets it
@@ -238,7 +247,8 @@ int hbt_set_cpu_base(hbt_ctx* ctx, uint32_t cpu_base);
 
 /* Library-owned device image of n_cpus rings of data_size bytes (power of two,
  * >= 4096: CpuEventsGroup.h:1065-1068,1077-1078).  Re-configuring frees the
- * previous images and resets all per-CPU state. */
+ * previous images and resets all per-CPU state; with a different n_cpus it also
+ * drops the histogram configuration (call hbt_hist_configure again). */
 int hbt_ring_configure(hbt_ctx* ctx, uint32_t n_cpus, uint64_t data_size);
 
 /* Copy the two slices of one OnRbReadCallback invocation into the device image
@@ -270,6 +280,23 @@ int hbt_submit_rings_dev(hbt_ctx* ctx, uint32_t n, const void* const* ring_bases
  * last_tstamp_ = 0 (numeric_limits<TimeStamp>::min()), in_write_errors_ = false
  * (PerCpuThreadSwitchGenerator.h:437-438). */
 int hbt_ring_reset_state(hbt_ctx* ctx, uint64_t seed_tstamp);
+
+/* Restore the generator state of one CPU, e.g. after a daemon restart (the
+ * reference has no checkpoint: this is the state its objects would have to carry,
+ * SURVEY section 5): count_.tstamp and last_[n_events] of CpuCountSampleGenerator
+ * (PerCpuCountSampleGenerator.h:222-230; UINT64_MAX = invalid, the next SAMPLE
+ * re-seeds), the running per-type counters num_record_*_ (CpuEventsGroup.h:822-832,
+ * HBT_NUM_COUNTERS words, NULL = keep) and num_unknown_count_interval_.  What
+ * hbt_fetch_results (counters, carry_tstamp, num_unknown_count_interval) and
+ * hbt_fetch_carry (last_[]) returned after the last decode can be fed back here.
+ * Synchronous.  Completes a pending decode first. */
+int hbt_ring_set_carry(hbt_ctx* ctx, uint32_t cpu, uint64_t carry_tstamp, const uint64_t* last,
+                       uint32_t n_events, const uint64_t* counters, uint64_t num_unknown);
+/* The same for CpuThreadSwitchGenerator's state: last_tstamp_ and in_write_errors_
+ * (PerCpuThreadSwitchGenerator.h:437-438), as reported in hbt_cpu_result.carry_tstamp /
+ * num_unknown_count_interval after an HBT_AGG_SWITCH_EVENTS decode. */
+int hbt_ring_set_switch_state(hbt_ctx* ctx, uint32_t cpu, uint64_t last_tstamp,
+                              uint32_t in_write_errors);
 
 /* ------------------------------------------------------------------------ */
 /* Decode: CpuEventsGroup::consume (CpuEventsGroup.h:1326-1522) for every CPU

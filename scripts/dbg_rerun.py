@@ -16,8 +16,7 @@ for ncpu, lost in ((8, 5000), (8, 0), (40, 5000)):
         imgs[c] = ring; tails.append(tail); heads.append(head)
     torch.cuda.synchronize()
     for segs in ("5", "16"):
-        os.environ["HBT_SEGS_PER_CPU"] = segs
-        ctx = hbt.Context(0); ctx.ring_configure(ncpu, 0)
+        ctx = hbt.Context(0); ctx.ring_configure(ncpu, 0); ctx.set_geometry(int(segs))
         for c in range(ncpu): ctx.submit_ring_dev(c, imgs[c], ring_bytes, tails[c], heads[c])
         ctx.decode(hbt.sampling_desc(E)); res = ctx.fetch_results()
         print("ncpu", ncpu, "lost", lost, "segs", segs, "reruns", ctx.reruns, "slow", ctx.slow_tiles, "rets", set(int(x) for x in res["ret"]))

@@ -95,7 +95,9 @@ def main():
                 orc.ref_consume(ring, 5 * ds + 3000 * 8, head, d))
 
     # --- consume() counters per mode over a mixed stream --------------------------------
-    s = tg.mixed_stream(201, 330, 8)
+    # every record type consume() dispatches on, THROTTLE / UNTHROTTLE / READ / AUX / ITRACE_START
+    # included (CpuEventsGroup.h:1409-1420, 1446-1496)
+    s = tg.mixed_stream(201, 330, 8, mix=tg.FULL_MIX)
     tail = 7 * ds + ds - 2048
     ring, head = ring_np(s, ds, tail)
     for name, mode in (("sampling", hbt.MODE_SAMPLING), ("ctxswitch", hbt.MODE_CONTEXT_SWITCH),
@@ -104,8 +106,26 @@ def main():
         save_decode(f"count_{name}", ring, tail, head, d, orc.ref_consume(ring, tail, head, d))
     d = hbt.count_desc(hbt.MODE_CONTEXT_SWITCH, max_records=100)
     save_decode("count_ctxswitch_max100", ring, tail, head, d, orc.ref_consume(ring, tail, head, d))
+    # a READ whose size disagrees with its nr: -EPERM in front of it (CpuEventsGroup.h:1446-1456)
+    w = s.clone()
+    pos, k = 0, 0
+    while pos < w.numel():
+        h = int(w[pos].item()) & ((1 << 64) - 1)
+        if (h & 0xFFFFFFFF) == tg.REC_READ:
+            k += 1
+            if k == 5:
+                w[pos + 2] = 9
+                break
+        pos += (h >> 48) // 8
+    assert k == 5
+    ring, head = ring_np(w, ds, tail)
+    for name, mode in (("sampling", hbt.MODE_SAMPLING), ("ctxswitch", hbt.MODE_CONTEXT_SWITCH)):
+        d = hbt.count_desc(mode)
+        save_decode(f"count_{name}_bad_read", ring, tail, head, d, orc.ref_consume(ring, tail, head, d))
+    ring, head = ring_np(s, ds, tail)
     mix = (("sample", 0.6), ("switch", 0.2), ("comm", 0.05), ("mmap", 0.05), ("lost", 0.03),
-           ("fork", 0.035), ("exit", 0.035))
+           ("fork", 0.035), ("exit", 0.035), ("read", 0.03), ("throttle", 0.01), ("unthrottle", 0.01),
+           ("aux", 0.01))
     s = tg.mixed_stream(202, 330, 8, mix=mix)
     ring, head = ring_np(s, ds, tail)
     d = hbt.sampling_desc(8, handled=hbt.MODE_MIXED)
