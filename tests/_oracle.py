@@ -200,6 +200,92 @@ def ref_consume(ring: np.ndarray, tail: int, head: int, desc: hbt.DecodeDesc,
     return result_dict(resarr[0], hist=hist)
 
 
+def _ref_covers(desc: hbt.DecodeDesc) -> bool:
+    """Decodes ref_consume can run through the reference's own classes."""
+    if desc.aggregate == hbt.AGG_NONE and desc.sample_layout == hbt.SAMPLE_GROUP:
+        return desc.handled_mask in MODE_INDEX
+    if desc.aggregate == hbt.AGG_COUNT_DELTAS:
+        return desc.handled_mask in (hbt.MODE_SAMPLING, hbt.MODE_MIXED)
+    if desc.sample_layout == hbt.SAMPLE_IP and desc.aggregate in (hbt.AGG_NONE, hbt.AGG_IP_HISTOGRAM):
+        return desc.handled_mask == (hbt.H_LOST | hbt.H_SAMPLE) and desc.ip_sample_bytes in IP_REF_SIZES
+    return False
+
+
+# hbtref_ip_hist instantiates its IP sample mode for these record sizes only
+IP_REF_SIZES = (40, 48, 64, 104, 128)
+
+
+def consume(ring: np.ndarray, tail: int, head: int, desc: hbt.DecodeDesc, carry_tstamp=hbt.INVALID_TS,
+            carry_last=None, counters=None, num_unknown=0, cpu=0):
+    """What the GPU tests compare the CUDA path with: the REFERENCE's own consume() (oracle/_ref)
+    whenever that library is present and covers the decode -- the C restatement is then only
+    cross-checked against it here -- else the C restatement alone."""
+    p = port_consume(ring, tail, head, desc, carry_tstamp, carry_last, counters, num_unknown, cpu)
+    if not (have_ref() and _ref_covers(desc)):
+        return p
+    with quiet_stderr():
+        r = ref_consume(ring, tail, head, desc, carry_tstamp, carry_last, counters, num_unknown, cpu)
+    for k in ("ret", "n_records", "new_tail", "counters"):
+        assert r[k] == p[k], ("oracle port != reference", k, r[k], p[k])
+    if desc.aggregate == hbt.AGG_COUNT_DELTAS:
+        for k in ("n_rows", "num_unknown", "carry_tstamp"):
+            assert r[k] == p[k], ("oracle port != reference", k, r[k], p[k])
+        assert np.array_equal(r["rows"], p["rows"]) and np.array_equal(r["carry_last"], p["carry_last"])
+    else:
+        r["carry_tstamp"] = p["carry_tstamp"]
+    if desc.aggregate == hbt.AGG_IP_HISTOGRAM:
+        assert r["hist"] == p["hist"]
+    r["checked_against"] = "reference"
+    return r
+
+
+class quiet_stderr:
+    """The reference logs a line per LOST / THROTTLE / unknown record (CpuEventsGroup.h:1409-1420,
+    1498-1500; PerCpuCountSampleGenerator.h:111): keep that out of the test log."""
+
+    def __enter__(self):
+        import sys
+        sys.stderr.flush()
+        self.saved, self.null = os.dup(2), os.open(os.devnull, os.O_WRONLY)
+        os.dup2(self.null, 2)
+
+    def __exit__(self, *a):
+        os.dup2(self.saved, 2)
+        os.close(self.saved)
+        os.close(self.null)
+
+
+def switch_events(rings, tails, heads, desc: hbt.DecodeDesc, cpu_base=0, last_tstamp=None,
+                  in_write_errors=None, counters=None):
+    """Per-CPU oracle answer for an AGG_SWITCH_EVENTS decode (tid-tagged events of the C
+    restatement).  With oracle/_ref present the REAL CpuThreadSwitchGenerator runs over the same
+    rings (CPUs in ascending order, one shared thread map) and every field -- and the events after
+    the tid -> vid mapping -- must equal its output; "ref_events" then holds its vid-tagged events
+    for a direct comparison with the GPU's mapped stream.  Streams must be ones the reference's
+    handlers accept (see tracegen.ctx_switch_stream)."""
+    n = len(tails)
+    out = []
+    for c in range(n):
+        out.append(port_switch_events(
+            rings[c], int(tails[c]), int(heads[c]), desc, cpu=cpu_base + c,
+            last_tstamp=0 if last_tstamp is None else int(last_tstamp[c]),
+            in_write_errors=0 if in_write_errors is None else int(in_write_errors[c]),
+            counters=None if counters is None else counters[c]))
+    if have_ref() and desc.handled_mask == hbt.MODE_CONTEXT_SWITCH and counters is None:
+        with quiet_stderr():
+            ref_out = ref_switch_events(np.stack([np.asarray(r) for r in rings]), tails, heads,
+                                        tid_level=desc.tid_level, cpu_base=cpu_base,
+                                        max_records=desc.max_records, last_tstamp=last_tstamp,
+                                        in_write_errors=in_write_errors)
+        mapped = map_tids_to_vids([o["events"] for o in out])
+        for c in range(n):
+            for k in ("ret", "n_records", "new_tail", "counters", "carry_tstamp", "num_unknown"):
+                assert ref_out[c][k] == out[c][k], ("oracle port != reference", c, k)
+            assert len(ref_out[c]["events"]) == len(mapped[c]) and (ref_out[c]["events"] == mapped[c]).all()
+            out[c]["ref_events"] = ref_out[c]["events"]
+    return out
+
+
 def port_switch_events(ring: np.ndarray, tail: int, head: int, desc: hbt.DecodeDesc, cpu=0,
                        last_tstamp=0, in_write_errors=0, counters=None):
     """oracle/hbt_oracle.c with CpuThreadSwitchGenerator's handlers over one ring image:
@@ -357,6 +443,23 @@ def port_counts(reads: np.ndarray, ratios=()):
     assert rc == 0
     o["ratios"] = o["ratios"][:, :R]
     return o
+
+
+def counts(reads: np.ndarray, ratios=()):
+    """Counter-group oracle for the GPU tests: the C restatement's outputs, cross-checked here
+    against the reference's own PerCpuBase::read / GroupReadValues::getCount (oracle/_ref) when
+    that library is present (words of a failed-read interval other than word0 are unspecified)."""
+    p = port_counts(reads, ratios)
+    if have_ref():
+        r = ref_counts(reads, ratios)
+        ok = r["sums"][:, 0] != 0
+        assert np.array_equal(r["sums"][:, 0], p["sums"][:, 0])
+        assert np.array_equal(r["sums"][ok], p["sums"][ok])
+        for k in ("scaled", "deltas"):
+            assert np.array_equal(r[k], p[k]), ("oracle port != reference", k)
+        assert np.array_equal(r["rates"], p["rates"], equal_nan=True)
+        assert np.array_equal(r["ratios"], p["ratios"], equal_nan=True)
+    return p
 
 
 def ref_counts(reads: np.ndarray, ratios=(), threads=1):

@@ -93,7 +93,7 @@ def test_cuda_matches_reference_vectors(built, case):
         # seed the generator state the vector was produced with
         ctx.reset_state(int(f["carry_in_tstamp"]))
         if "carry_in_last" in f:
-            pytest.skip("non-zero last_[] seed is covered by test_gpu_parity.test_carry_across_calls")
+            ctx.set_carry(0, int(f["carry_in_tstamp"]), f["carry_in_last"])
         if d.aggregate == hbt.AGG_IP_HISTOGRAM:
             ctx.hist_configure(1 << 12)
         img = torch.from_numpy(ring.view(np.int64)).cuda()

@@ -1,6 +1,8 @@
-"""Parity of the CUDA path (through the C-ABI, libhbt_b200.so) with the oracle
-(oracle/hbt_oracle.c, itself pinned to the reference by
-test_oracle_vs_reference.py / test_golden.py) on the same seeded inputs.
+"""Parity of the CUDA path (through the C-ABI, libhbt_b200.so) with the oracle on the same
+seeded inputs.  orc.consume() runs the REFERENCE's own consume() / generators (oracle/_ref, which
+travels to the GPU box) wherever they cover the decode and cross-checks the C restatement
+(oracle/hbt_oracle.c) against them; without oracle/_ref the restatement (pinned by
+test_oracle_vs_reference.py / test_golden.py) is the checker.
 Bit-exact for every integer output; f64 ratios within 1e-12 relative."""
 import numpy as np
 import pytest
@@ -77,7 +79,7 @@ def check_cpu(ctx, cpu, got, want, desc):
 def test_counts_pipeline(ctx, I, C, E, mux):
     reads = tg.counts_trace(61 + E, I, C, E, multiplexed=mux).numpy().view(np.uint64)
     ratios = [(min(1, E - 1), 0), (E - 1, min(1, E - 1))]
-    got, want = ctx.counts_pipeline_host(reads, ratios), orc.port_counts(reads, ratios)
+    got, want = ctx.counts_pipeline_host(reads, ratios), orc.counts(reads, ratios)
     for k in ("sums", "scaled", "deltas"):
         assert np.array_equal(got[k], want[k]), k
     assert np.array_equal(got["rates"], want["rates"])
@@ -94,7 +96,7 @@ def test_counts_edge_values(ctx):
     reads[3, :, 1] = 0
     reads[3, :, 2] = 0
     reads[4, 2, 0] = 0
-    got, want = ctx.counts_pipeline_host(reads), orc.port_counts(reads)
+    got, want = ctx.counts_pipeline_host(reads), orc.counts(reads)
     assert np.array_equal(got["sums"], want["sums"])
     assert got["sums"][4, 0] == 0
     assert np.array_equal(got["scaled"], want["scaled"])
@@ -122,7 +124,7 @@ def test_counts_dev_split_equals_pipeline(ctx):
         ctx.counts_reduce_dev(reads, I, C, E, sums)
         ctx.counts_scale_dev(sums, I, E, [(1, 0)], None, scaled, rates, ratio, deltas)
         ctx.sync()
-        want = orc.port_counts(reads.cpu().numpy().view(np.uint64), [(1, 0)])
+        want = orc.counts(reads.cpu().numpy().view(np.uint64), [(1, 0)])
         assert np.array_equal(sums.cpu().numpy().view(np.uint64), want["sums"])
         assert np.array_equal(scaled.cpu().numpy().view(np.uint64), want["scaled"])
         assert np.array_equal(deltas.cpu().numpy().view(np.uint64), want["deltas"])
@@ -161,7 +163,7 @@ def test_sample_deltas(ctx, n_events, lost_every, ds, n_cpus):
         rings.append((ring, tail, head))
     res = gpu_decode(ctx, rings, desc, ds)
     for cpu, (ring, tail, head) in enumerate(rings):
-        check_cpu(ctx, cpu, res[cpu], orc.port_consume(ring, tail, head, desc), desc)
+        check_cpu(ctx, cpu, res[cpu], orc.consume(ring, tail, head, desc), desc)
     assert ctx.reruns == 0 and ctx.slow_tiles == 0, "well-formed streams must stay on the fast path"
 
 
@@ -183,7 +185,7 @@ def test_carry_across_calls(ctx):
         # and the next window starts where it left the tail
         if b <= a:
             continue
-        want = orc.port_consume(ring, a, b, desc, st["carry_tstamp"], st["carry_last"],
+        want = orc.consume(ring, a, b, desc, st["carry_tstamp"], st["carry_last"],
                                 st["counters"], st["num_unknown"])
         got = gpu_decode_full_images(ctx, [(ring, a, b)], desc, ds, reset=False)[0]
         check_cpu(ctx, 0, got, want, desc)
@@ -204,7 +206,7 @@ def test_max_records(ctx, max_records):
     desc = hbt.sampling_desc(E, max_records=max_records)
     res = gpu_decode(ctx, rings, desc, ds)
     for cpu, (ring, tail, head) in enumerate(rings):
-        check_cpu(ctx, cpu, res[cpu], orc.port_consume(ring, tail, head, desc), desc)
+        check_cpu(ctx, cpu, res[cpu], orc.consume(ring, tail, head, desc), desc)
 
 
 def test_timestamp_regression_and_bad_size(ctx):
@@ -223,7 +225,7 @@ def test_timestamp_regression_and_bad_size(ctx):
         rings.append((ring, tail, head))
     res = gpu_decode(ctx, rings, desc, ds)
     for cpu, (ring, tail, head) in enumerate(rings):
-        want = orc.port_consume(ring, tail, head, desc)
+        want = orc.consume(ring, tail, head, desc)
         assert want["ret"] == -1
         check_cpu(ctx, cpu, res[cpu], want, desc)
 
@@ -238,7 +240,7 @@ def test_regression_at_every_position_small(ctx):
         tail = 48 * 7
         ring, head = ring_np(s, ds, tail)
         res = gpu_decode(ctx, [(ring, tail, head)], desc, ds)
-        check_cpu(ctx, 0, res[0], orc.port_consume(ring, tail, head, desc), desc)
+        check_cpu(ctx, 0, res[0], orc.consume(ring, tail, head, desc), desc)
 
 
 def test_tsc_transform(ctx):
@@ -248,24 +250,90 @@ def test_tsc_transform(ctx):
     ring, head = ring_np(s, ds, tail)
     desc = hbt.sampling_desc(E, tsc_mask=0b100101, tsc=(987654321, 1234567, 21))
     res = gpu_decode(ctx, [(ring, tail, head)], desc, ds)
-    check_cpu(ctx, 0, res[0], orc.port_consume(ring, tail, head, desc), desc)
+    check_cpu(ctx, 0, res[0], orc.consume(ring, tail, head, desc), desc)
 
 
 @pytest.mark.parametrize("mode", [hbt.MODE_SAMPLING, hbt.MODE_CONTEXT_SWITCH, hbt.MODE_AUX_SPACE,
                                   hbt.MODE_MIXED])
 @pytest.mark.parametrize("max_records", [hbt.DRAIN, 7777])
-def test_mixed_stream_counters(ctx, mode, max_records):
+@pytest.mark.parametrize("mix", [tg.MIXED_MIX, tg.FULL_MIX], ids=["config4", "all_types"])
+def test_mixed_stream_counters(ctx, mode, max_records, mix):
+    """Every record type consume() dispatches on (the all_types mix adds THROTTLE / UNTHROTTLE /
+    READ / AUX / ITRACE_START, CpuEventsGroup.h:1409-1420, 1446-1496) under every handler set."""
     ds, E = 1 << 21, 8
     rings = []
     for cpu in range(4):
-        s = tg.mixed_stream(41 + cpu, 18000, E)
+        s = tg.mixed_stream(41 + cpu, 18000, E, mix=mix)
         tail = tg.random_tail(9 + cpu, ds)
         ring, head = ring_np(s, ds, tail)
         rings.append((ring, tail, head))
     desc = hbt.count_desc(mode, max_records=max_records)
     res = gpu_decode(ctx, rings, desc, ds)
     for cpu, (ring, tail, head) in enumerate(rings):
-        check_cpu(ctx, cpu, res[cpu], orc.port_consume(ring, tail, head, desc), desc)
+        check_cpu(ctx, cpu, res[cpu], orc.consume(ring, tail, head, desc), desc)
+
+
+def first_record_of_type(s, rtype, nth):
+    """Word index of the nth record of PERF type `rtype` in a stream of u64 words."""
+    w = s.numpy().view(np.uint64)
+    pos, k = 0, 0
+    while pos < len(w):
+        h = int(w[pos])
+        if (h & 0xFFFFFFFF) == rtype:
+            k += 1
+            if k == nth:
+                return pos
+        pos += (h >> 48) // 8
+    raise AssertionError("not enough records of that type")
+
+
+@pytest.mark.parametrize("mode", [hbt.MODE_SAMPLING, hbt.MODE_MIXED, hbt.MODE_CONTEXT_SWITCH])
+def test_read_record_with_bad_size(ctx, mode):
+    """A PERF_RECORD_READ whose header.size disagrees with its nr: -EPERM in front of it where
+    READ has a handler (CpuEventsGroup.h:1446-1456), skipped by size where it has none."""
+    ds, E = 1 << 20, 8
+    rings = []
+    for cpu, nth in enumerate((1, 40, 333)):     # first tile, a later tile, another segment
+        s = tg.mixed_stream(141 + cpu, 9000, E, mix=tg.FULL_MIX).clone()
+        s[first_record_of_type(s, tg.REC_READ, nth) + 2] = E + 3
+        tail = tg.random_tail(19 + cpu, ds)
+        ring, head = ring_np(s, ds, tail)
+        rings.append((ring, tail, head))
+    desc = hbt.count_desc(mode)
+    res = gpu_decode(ctx, rings, desc, ds)
+    for cpu, (ring, tail, head) in enumerate(rings):
+        want = orc.consume(ring, tail, head, desc)
+        assert (want["ret"] == -1) == bool(mode & hbt.H_READ)
+        check_cpu(ctx, cpu, res[cpu], want, desc)
+
+
+def test_resume_from_saved_state(built):
+    """Checkpoint / resume: the state a decode leaves (counters, count_.tstamp, last_[],
+    num_unknown) read out of one context and restored into a fresh one with hbt_ring_set_carry;
+    the second half decoded there equals the oracle chained across the cut."""
+    ds, E = 1 << 19, 6
+    s = tg.group_sample_stream(77, 5000, E, lost_every=211)
+    tail = tg.random_tail(6, ds)
+    ring, head = ring_np(s, ds, tail)
+    desc1 = hbt.sampling_desc(E, max_records=2600)
+    desc2 = hbt.sampling_desc(E)
+    a, b = hbt.Context(0), hbt.Context(0)
+    try:
+        r1 = gpu_decode(a, [(ring, tail, head)], desc1, ds, seed_ts=4242)[0]
+        w1 = orc.consume(ring, tail, head, desc1, carry_tstamp=4242, carry_last=np.zeros(E, np.uint64))
+        check_cpu(a, 0, r1, w1, desc1)
+        last = a.fetch_carry(0, E)
+        b.ring_configure(1, ds)
+        b.set_carry(0, int(r1["carry_tstamp"]), last, r1["counters"], int(r1["num_unknown_count_interval"]))
+        b.submit_ring_image(0, ring, int(r1["new_tail"]), head)
+        b.decode(desc2)
+        r2 = b.fetch_results()[0]
+        w2 = orc.consume(ring, w1["new_tail"], head, desc2, w1["carry_tstamp"], w1["carry_last"],
+                         w1["counters"], w1["num_unknown"])
+        check_cpu(b, 0, r2, w2, desc2)
+    finally:
+        a.close()
+        b.close()
 
 
 def test_mixed_stream_deltas(ctx):
@@ -281,7 +349,7 @@ def test_mixed_stream_deltas(ctx):
     desc = hbt.sampling_desc(E, handled=hbt.MODE_MIXED)
     res = gpu_decode(ctx, rings, desc, ds)
     for cpu, (ring, tail, head) in enumerate(rings):
-        check_cpu(ctx, cpu, res[cpu], orc.port_consume(ring, tail, head, desc), desc)
+        check_cpu(ctx, cpu, res[cpu], orc.consume(ring, tail, head, desc), desc)
 
 
 # ---------------------------------------------------------------------------
@@ -300,7 +368,7 @@ def test_ip_histogram(ctx, words, ds, n_cpus, n_pids, n_ips):
         tail = tg.random_tail(12 + cpu, ds)
         ring, head = ring_np(s, ds, tail)
         rings.append((ring, tail, head))
-        w = orc.port_consume(ring, tail, head, desc, cpu=cpu)
+        w = orc.consume(ring, tail, head, desc, cpu=cpu)
         want_hist.update(w["hist"])
         wants.append(w)
     res = gpu_decode(ctx, rings, desc, ds, hist_slots=1 << 22)
@@ -332,7 +400,7 @@ def test_ip_histogram_zero_key_and_error(ctx):
     tail = tg.random_tail(3, ds)
     ring, head = ring_np(s, ds, tail)
     desc = hbt.ip_desc(40)
-    want = orc.port_consume(ring, tail, head, desc)
+    want = orc.consume(ring, tail, head, desc)
     assert want["ret"] == -1 and want["n_records"] == bad_at
     res = gpu_decode(ctx, [(ring, tail, head)], desc, ds, hist_slots=1 << 16)
     check_cpu(ctx, 0, res[0], want, desc)
@@ -356,7 +424,7 @@ def test_payload_that_looks_like_headers(ctx):
     ring, head = ring_np(s, ds, tail, fill=0)
     desc = hbt.sampling_desc(E)
     res = gpu_decode(ctx, [(ring, tail, head)] * 2, desc, ds)
-    want = orc.port_consume(ring, tail, head, desc)
+    want = orc.consume(ring, tail, head, desc)
     check_cpu(ctx, 0, res[0], want, desc)
     check_cpu(ctx, 1, res[1], want, desc)
 
@@ -386,7 +454,7 @@ def test_unknown_types_and_giant_records(ctx):
     ring, head = ring_np(s, ds, tail)
     desc = hbt.sampling_desc(2)
     res = gpu_decode(ctx, [(ring, tail, head)], desc, ds)
-    check_cpu(ctx, 0, res[0], orc.port_consume(ring, tail, head, desc), desc)
+    check_cpu(ctx, 0, res[0], orc.consume(ring, tail, head, desc), desc)
 
 
 def test_zero_size_record_stops(ctx):
@@ -396,6 +464,8 @@ def test_zero_size_record_stops(ctx):
     ring, head = ring_np(s, ds, 0)
     desc = hbt.sampling_desc(E)
     res = gpu_decode(ctx, [(ring, 0, head)], desc, ds)
+    # (the reference itself would never return from this stream: documented deviation,
+    # so the restatement alone is the checker here)
     want = orc.port_consume(ring, 0, head, desc)
     assert want["ret"] == -74 and want["n_records"] == 600
     check_cpu(ctx, 0, res[0], want, desc)
@@ -416,7 +486,7 @@ def test_small_rings_and_empty_windows(ctx, ds):
         rings.append((ring, tail, head))
     res = gpu_decode(ctx, rings, desc, ds)
     for cpu, (ring, tail, head) in enumerate(rings):
-        check_cpu(ctx, cpu, res[cpu], orc.port_consume(ring, tail, head, desc), desc)
+        check_cpu(ctx, cpu, res[cpu], orc.consume(ring, tail, head, desc), desc)
     assert int(res[1]["ret"]) == -61 and int(res[1]["n_records"]) == 0
 
 
@@ -429,7 +499,7 @@ def test_window_overrunning_head(ctx):
     desc = hbt.sampling_desc(E)
     for cut in (8, 16, 96):
         res = gpu_decode_full_images(ctx, [(ring, 64, head - cut)], desc, ds)
-        want = orc.port_consume(ring, 64, head - cut, desc)
+        want = orc.consume(ring, 64, head - cut, desc)
         assert want["new_tail"] > head - cut or cut % 104 == 0
         check_cpu(ctx, 0, res[0], want, desc)
 
@@ -456,7 +526,7 @@ def test_device_resident_rings(ctx):
     res = ctx.fetch_results()
     host = imgs.cpu().numpy().view(np.uint64)
     for cpu, (tail, head) in enumerate(meta):
-        check_cpu(ctx, cpu, res[cpu], orc.port_consume(host[cpu], tail, head, desc), desc)
+        check_cpu(ctx, cpu, res[cpu], orc.consume(host[cpu], tail, head, desc), desc)
 
 
 # ---------------------------------------------------------------------------
@@ -482,10 +552,42 @@ def test_hist_capacity_overflow_is_loud(ctx):
     ctx.submit_ring_image(0, ring, 0, head)
     ctx.decode(hbt.ip_desc(40))
     ctx.fetch_results()
-    want = orc.port_consume(ring, 0, head, hbt.ip_desc(40))["hist"]
+    want = orc.consume(ring, 0, head, hbt.ip_desc(40))["hist"]
     assert orc.hist_to_dict(ctx.hist_fetch()) == want
     ctx.hist_clear()
     assert ctx.hist_size() == 0
+
+
+def test_hist_must_be_reconfigured_after_cpu_count_change(built):
+    """ring_configure(8) -> hist_configure -> ring_configure(64): the lists were laid out for 8
+    CPUs; a histogram decode is refused (-EINVAL) until hbt_hist_configure is called again."""
+    import errno
+    ds = 1 << 16
+    ctx = hbt.Context(0)
+    try:
+        ctx.ring_configure(8, ds)
+        ctx.hist_configure(8 << 13)
+        ctx.ring_configure(64, ds)
+        rings = []
+        for cpu in range(64):
+            s = tg.ip_sample_stream(600 + cpu, 1200, cpu=cpu, n_pids=8, n_ips=32)
+            ring, head = ring_np(s, ds, 0)
+            rings.append((ring, 0, head))
+            ctx.submit_ring_image(cpu, ring, 0, head)
+        with pytest.raises(hbt.HbtError) as e:
+            ctx.decode(hbt.ip_desc(40))
+        assert e.value.code == -errno.EINVAL
+        ctx.hist_configure(64 << 13)
+        for cpu, (ring, tail, head) in enumerate(rings):
+            ctx.submit_ring_image(cpu, ring, tail, head)
+        ctx.decode(hbt.ip_desc(40))
+        ctx.fetch_results()
+        want = {}
+        for cpu, (ring, tail, head) in enumerate(rings):
+            want.update(orc.consume(ring, tail, head, hbt.ip_desc(40), cpu=cpu)["hist"])
+        assert orc.hist_to_dict(ctx.hist_fetch()) == want
+    finally:
+        ctx.close()
 
 
 def test_heavy_hitter_key(ctx):
@@ -501,7 +603,7 @@ def test_heavy_hitter_key(ctx):
     ring, head = ring_np(s, ds, tail)
     desc = hbt.ip_desc(40)
     res = gpu_decode(ctx, [(ring, tail, head)], desc, ds, hist_slots=1 << 18)
-    want = orc.port_consume(ring, tail, head, desc)
+    want = orc.consume(ring, tail, head, desc)
     check_cpu(ctx, 0, res[0], want, desc)
     got = orc.hist_to_dict(ctx.hist_fetch())
     assert got == want["hist"]
@@ -531,7 +633,7 @@ def test_batch_submit_and_device_views(ctx):
     res = ctx.fetch_results()
     host = imgs.cpu().numpy().view(np.uint64)
     for cpu in range(n_cpus):
-        want = orc.port_consume(host[cpu], tails[cpu], heads[cpu], desc)
+        want = orc.consume(host[cpu], tails[cpu], heads[cpu], desc)
         check_cpu(ctx, cpu, res[cpu], want, desc)
         # device view of the same rows: slabs in stream order
         k = ctx.lib.hbt_rows_max_slabs(ctx.h)
@@ -575,7 +677,7 @@ def test_two_contexts_interleaved(built):
             hist = orc.hist_to_dict(ctx.hist_fetch()) if desc.aggregate == hbt.AGG_IP_HISTOGRAM else None
             want_hist = {}
             for cpu, (ring, tail, head) in enumerate(rings):
-                want = orc.port_consume(ring, tail, head, desc, cpu=base + cpu)
+                want = orc.consume(ring, tail, head, desc, cpu=base + cpu)
                 check_cpu(ctx, cpu, res[cpu], want, desc)
                 if want.get("hist"):
                     want_hist.update(want["hist"])
@@ -601,8 +703,8 @@ def test_max_cpus_decode(built):
         desc = hbt.sampling_desc(E)
         res = gpu_decode(ctx, rings, desc, ds)
         for c in (0, 1, 2, 255, 256, 300, 510, 511):
-            check_cpu(ctx, c, res[c], orc.port_consume(*rings[c], desc), desc)
-        want_rec = [orc.port_consume(*rings[c], desc)["n_records"] for c in range(n_cpus)]
+            check_cpu(ctx, c, res[c], orc.consume(*rings[c], desc), desc)
+        want_rec = [orc.consume(*rings[c], desc)["n_records"] for c in range(n_cpus)]
         assert [int(r) for r in res["n_records"]] == want_rec
     finally:
         ctx.close()

@@ -224,14 +224,23 @@ def test_gpu_switch_events(ctx, n_records, ds, n_cpus, mix):
     d = hbt.switch_desc(tid_level=4)
     rings = []
     for c in range(n_cpus):
-        s = tg.ctx_switch_stream(tg.stream_seed(40, c) + n_records, n_records, mix=mix)
+        # (fresh FORK tids per CPU: the reference's generators share one thread map)
+        s = tg.ctx_switch_stream(tg.stream_seed(40, c) + n_records, n_records, mix=mix,
+                                 fork_tid_base=c << 22)
         assert s.numel() * 8 < ds
         tail = tg.random_tail(900 + c, ds)
         ring, head = ring_np(s, ds, tail, fill=5)
         rings.append((ring, tail, head))
     res, ev = gpu_switch(ctx, rings, d, ds, cpu_base=16)
-    for c, (ring, tail, head) in enumerate(rings):
-        check(res, ev, orc.port_switch_events(ring, tail, head, d, cpu=16 + c), c)
+    # with oracle/_ref on the box this runs the REAL CpuThreadSwitchGenerator over the rings
+    want = orc.switch_events([r for r, _, _ in rings], [t for _, t, _ in rings],
+                             [h for _, _, h in rings], d, cpu_base=16)
+    for c in range(n_cpus):
+        check(res, ev, want[c], c)
+    if "ref_events" in want[0]:
+        mapped = orc.map_tids_to_vids(ev)   # the host-side tid -> vid step, applied to the GPU stream
+        for c in range(n_cpus):
+            assert same_events(mapped[c], want[c]["ref_events"]), f"cpu {c}: GPU events != reference's"
     assert ctx.reruns == 0
     # device view: all CPUs back to back
     base, off = ctx.switch_events_dev()
