@@ -73,6 +73,13 @@ class Ratio(C.Structure):
     _fields_ = [("num_event", C.c_uint32), ("den_event", C.c_uint32)]
 
 
+class MetricDesc(C.Structure):
+    _fields_ = [("id", C.c_char_p), ("arch", C.c_char_p), ("n_events", C.c_uint32),
+                ("nicknames", C.POINTER(C.c_char_p)), ("n_ratios", C.c_uint32),
+                ("ratios", C.POINTER(Ratio)), ("ratio_names", C.POINTER(C.c_char_p)),
+                ("builtin", C.c_uint32), ("index", C.c_uint32), ("tsc_transform_mask", C.c_uint64)]
+
+
 HIST_DTYPE = np.dtype([("ip", "<u8"), ("pid", "<u4"), ("cpu", "<u4"), ("count", "<u8")])
 RESULT_DTYPE = np.dtype([("ret", "<i8"), ("n_records", "<u8"), ("new_tail", "<u8"),
                          ("n_rows", "<u8"), ("counters", "<u8", (NUM_COUNTERS,)),
@@ -123,6 +130,12 @@ EXPORTS = [
     ("hbt_hist_fetch", C.c_int64, [_P, _P, C.c_uint64]),
     ("hbt_hist_lists_dev", C.c_int,
      [_P, C.POINTER(_P), C.POINTER(_P), C.POINTER(C.c_uint32), C.POINTER(C.c_uint32)]),
+    ("hbt_metric_count", C.c_uint32, []),
+    ("hbt_metric_at", C.POINTER(MetricDesc), [C.c_uint32]),
+    ("hbt_metric_find", C.POINTER(MetricDesc), [C.c_char_p, C.c_char_p]),
+    ("hbt_metric_event_index", C.c_int, [C.POINTER(MetricDesc), C.c_char_p]),
+    ("hbt_counts_pipeline_metric_dev", C.c_int,
+     [_P, C.POINTER(MetricDesc), _P, C.c_uint64, C.c_uint32, _P, _P, _P, _P, _P]),
     ("hbt_counts_reduce_dev", C.c_int, [_P, _P, C.c_uint64, C.c_uint32, C.c_uint32, _P]),
     ("hbt_counts_scale_dev", C.c_int,
      [_P, _P, C.c_uint64, C.c_uint32, _P, C.c_uint32, _P, _P, _P, _P, _P]),
@@ -387,6 +400,13 @@ class Context:
                                                   _ptr(sums), _ptr(scaled), _ptr(rates),
                                                   _ptr(ratio_out), _ptr(deltas)))
 
+    def counts_pipeline_metric_dev(self, desc, reads, n_intervals, n_cpus, sums=None, scaled=None,
+                                   rates=None, ratio_out=None, deltas=None):
+        """K4+K5 for the metric descriptor `desc` (metric_find): events and named ratios are its."""
+        self._ck(self.lib.hbt_counts_pipeline_metric_dev(self.h, desc, _ptr(reads), n_intervals, n_cpus,
+                                                         _ptr(sums), _ptr(scaled), _ptr(rates),
+                                                         _ptr(ratio_out), _ptr(deltas)))
+
     def counts_pipeline_host(self, reads: np.ndarray, ratios=()):
         """reads: [I][C][3+E] u64 on the host -> dict of host arrays."""
         I, Cc, W = reads.shape
@@ -402,6 +422,27 @@ class Context:
             _ptr(out["ratios"]) if R else None, _ptr(out["deltas"])))
         out["ratios"] = out["ratios"][:, :R]
         return out
+
+
+def metric_table():
+    """The library's metric descriptors as dicts (id, arch, nicknames, ratios as
+    (name, num, den) triples, builtin, tsc_transform_mask); no GPU needed."""
+    lib = load_library()
+    out = []
+    for i in range(lib.hbt_metric_count()):
+        d = lib.hbt_metric_at(i).contents
+        out.append(dict(id=d.id.decode(), arch=d.arch.decode(),
+                        nicknames=[d.nicknames[k].decode() for k in range(d.n_events)],
+                        ratios=[(d.ratio_names[k].decode(), d.ratios[k].num_event, d.ratios[k].den_event)
+                                for k in range(d.n_ratios)],
+                        builtin=int(d.builtin), index=int(d.index), tsc_transform_mask=int(d.tsc_transform_mask)))
+    return out
+
+
+def metric_find(metric_id: str, arch: str | None = None):
+    """hbt_metric_find: a pointer to the descriptor (pass it to counts_pipeline_metric_dev) or None."""
+    p = load_library().hbt_metric_find(metric_id.encode(), arch.encode() if arch else None)
+    return p if p else None
 
 
 STATIC_SCRATCH_WORDS = 512 * 1024

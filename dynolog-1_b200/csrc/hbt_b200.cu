@@ -15,6 +15,7 @@
 #include "../../include/hbt_b200.h"
 #include "counts.cuh"
 #include "decode.cuh"
+#include "metric_table.h"
 
 using namespace hbt;
 
@@ -150,6 +151,7 @@ struct hbt_ctx {
   DevBuf<unsigned long long> hist_n;
 
   // counts scratch
+  const hbt_ratio* metric_ratios_dev = nullptr;  // c_metric_ratios on this device
   DevBuf<hbt_ratio> d_ratios;
   DevBuf<uint64_t> c_reads, c_sums, c_scaled, c_deltas;
   DevBuf<float> c_rates;
@@ -1253,6 +1255,33 @@ static int counts_check(hbt_ctx* ctx, uint64_t n_intervals, uint32_t n_cpus, uin
   return 0;
 }
 
+// ---- metric descriptors ---------------------------------------------------------------
+
+uint32_t hbt_metric_count(void) { return kNumMetrics; }
+
+const hbt_metric_desc* hbt_metric_at(uint32_t index) {
+  return index < kNumMetrics ? &kMetricTable[index] : nullptr;
+}
+
+const hbt_metric_desc* hbt_metric_find(const char* id, const char* arch) {
+  if (!id) return nullptr;
+  const hbt_metric_desc* any = nullptr;
+  for (uint32_t i = 0; i < kNumMetrics; ++i) {
+    const hbt_metric_desc& d = kMetricTable[i];
+    if (strcmp(d.id, id) != 0) continue;
+    if (arch && strcmp(d.arch, arch) == 0) return &d;   // architecture-specific list first
+    if (strcmp(d.arch, "any") == 0) any = &d;
+  }
+  return any;
+}
+
+int hbt_metric_event_index(const hbt_metric_desc* desc, const char* nickname) {
+  if (!desc || !nickname) return -EINVAL;
+  for (uint32_t i = 0; i < desc->n_events; ++i)
+    if (strcmp(desc->nicknames[i], nickname) == 0) return (int)i;
+  return -ENOENT;
+}
+
 static int upload_ratios(hbt_ctx* ctx, const hbt_ratio* ratios, uint32_t n_ratios) {
   CU(ctx->d_ratios.reserve(kMaxRatios));
   if (n_ratios)
@@ -1272,14 +1301,14 @@ static int counts_grid(const hbt_ctx* ctx, uint64_t n_intervals) {
 static int counts_launch(hbt_ctx* ctx, const uint64_t* reads, uint64_t n_intervals,
                          uint32_t n_cpus, uint32_t n_events, uint32_t n_ratios, uint64_t* sums,
                          uint64_t* scaled, float* rates, double* ratio_out, uint64_t* deltas,
-                         int do_scale) {
+                         int do_scale, const hbt_ratio* dev_ratios = nullptr) {
   if (n_intervals == 0) return 0;
   CountsArgs a{};
   a.reads = reads;
   a.n_intervals = n_intervals;
   a.n_cpus = n_cpus;
   a.n_events = n_events;
-  a.ratios = ctx->d_ratios.p;
+  a.ratios = dev_ratios ? dev_ratios : ctx->d_ratios.p;
   a.n_ratios = n_ratios;
   a.sums = sums;
   a.rates = rates;
@@ -1383,6 +1412,27 @@ int hbt_counts_pipeline_dev(hbt_ctx* ctx, const uint64_t* reads, uint64_t n_inte
   if (rc) return rc;
   return counts_launch(ctx, reads, n_intervals, n_cpus, n_events, ratio_out ? n_ratios : 0, sums,
                        scaled, rates, ratio_out, deltas, 1);
+}
+
+int hbt_counts_pipeline_metric_dev(hbt_ctx* ctx, const hbt_metric_desc* desc, const uint64_t* reads,
+                                   uint64_t n_intervals, uint32_t n_cpus, uint64_t* sums,
+                                   uint64_t* scaled, float* rates, double* ratio_out,
+                                   uint64_t* deltas) {
+  if (!ctx) return -EINVAL;
+  if (!desc || desc < kMetricTable || desc >= kMetricTable + kNumMetrics)
+    return fail(ctx, -EINVAL, "desc is not an entry of the library's metric table");
+  int rc = counts_check(ctx, n_intervals, n_cpus, desc->n_events, 0, nullptr);
+  if (rc) return rc;
+  if (!reads) return fail(ctx, -EINVAL, "NULL buffer");
+  CU(cudaSetDevice(ctx->device));
+  if (!ctx->metric_ratios_dev) {
+    void* sym = nullptr;  // device address of the constant table on this ctx's device
+    CU(cudaGetSymbolAddress(&sym, c_metric_ratios));
+    ctx->metric_ratios_dev = static_cast<const hbt_ratio*>(sym);
+  }
+  return counts_launch(ctx, reads, n_intervals, n_cpus, desc->n_events,
+                       ratio_out ? desc->n_ratios : 0, sums, scaled, rates, ratio_out, deltas, 1,
+                       ctx->metric_ratios_dev + (size_t)desc->index * kMaxMetricRatios);
 }
 
 int hbt_counts_pipeline_host(hbt_ctx* ctx, const uint64_t* reads, uint64_t n_intervals,

@@ -392,6 +392,43 @@ typedef struct hbt_ratio {
   uint32_t den_event;
 } hbt_ratio;
 
+/* Metric descriptors: which events make up a metric and in which order their values
+ * appear in a group read (MetricDesc::event_refs_by_arch, hbt/src/perf_event/Metrics.h:45-179;
+ * the registry is makeAvailableMetrics, BuiltinMetrics.cpp:470-1175).  The table inside the
+ * library restates that registry (builtin = 1, pinned against it by
+ * tests/golden/builtin_metrics.json) and adds two build-defined miss-rate groups over the
+ * reference's generic hardware-cache events (builtin = 0).  ratios[] are NAMED derived
+ * values over the descriptor's own event order; the reference defines none (no code divides
+ * events), so they are build-defined in the convention of PerfMonitor.cpp:56-57. */
+typedef struct hbt_metric_desc {
+  const char* id;                 /* MetricDesc::id, e.g. "ipc" */
+  const char* arch;               /* "any", or the CpuArch the event list is registered for */
+  uint32_t n_events;
+  const char* const* nicknames;   /* [n_events], index = position of the value (EventRef::nickname) */
+  uint32_t n_ratios;
+  const hbt_ratio* ratios;        /* [n_ratios] indices into nicknames */
+  const char* const* ratio_names; /* [n_ratios] */
+  uint32_t builtin;
+  uint32_t index;                 /* position in the table */
+  uint64_t tsc_transform_mask;    /* bit i: event i carries EventValueTransforms::TscToKernelTime */
+} hbt_metric_desc;
+
+uint32_t hbt_metric_count(void);
+const hbt_metric_desc* hbt_metric_at(uint32_t index);
+/* MetricDesc::getEventRefs(cpu_arch) (Metrics.h:162-180): the list registered for `arch` if
+ * there is one, else the one registered for any architecture, else NULL.  arch may be NULL. */
+const hbt_metric_desc* hbt_metric_find(const char* id, const char* arch);
+/* MetricDesc::eventIdxFromNicknames (Metrics.h:136-151): -ENOENT if there is none. */
+int hbt_metric_event_index(const hbt_metric_desc* desc, const char* nickname);
+
+/* K4+K5 for one metric selected by descriptor: n_events and the ratio table are the
+ * descriptor's (the index pairs live in constant memory on the device; nothing is uploaded).
+ * ratio_out: [n_intervals][desc->n_ratios]. */
+int hbt_counts_pipeline_metric_dev(hbt_ctx* ctx, const hbt_metric_desc* desc, const uint64_t* reads,
+                                   uint64_t n_intervals, uint32_t n_cpus, uint64_t* sums,
+                                   uint64_t* scaled, float* rates, double* ratio_out,
+                                   uint64_t* deltas);
+
 /* K4.  reads: [n_intervals][n_cpus][3+n_events] u64, one T per (interval,cpu).
  * sums:  [n_intervals][3+n_events] u64 = zero() then accum() over the CPUs
  * (CpuEventsGroup.h:508-522): word0 = n_events, time_enabled, time_running,
