@@ -2,13 +2,9 @@
 // log keys as dynolog/src/Logger.h:24-45, dynolog/src/Logger.cpp:38-58 and
 // dynolog/src/PerfMonitor.{h,cpp}.
 #pragma once
-#include <algorithm>
 #include <chrono>
-#include <cmath>
 #include <cstdio>
 #include <map>
-#include <numeric>
-#include <type_traits>
 #include <ostream>
 #include <string>
 
@@ -92,24 +88,29 @@ class PerfMonitor {
 
   void step() { readValues_ = hbtMon_.readAllCounts(); }
 
-  // PerfMonitor::log (PerfMonitor.cpp:38-73): cumulative values; `instructions` and
-  // `cycles` become mips / mega_cycles_per_second, everything else logUint(nickname).
+  // What dynolog logs per metric (PerfMonitor.cpp:38-73): the cumulative scaled count of every
+  // event under its nickname, except the two metrics whose single event is reported as a rate
+  // per millisecond of running time.  Those rates were computed on the GPU with the read
+  // (GroupReadValues::getRatePerMs); nothing is divided here.
+  struct RateKey {
+    const char* metric_and_event;  // the metric id, whose only event carries the same nickname
+    const char* log_key;
+  };
+  static constexpr RateKey kRateKeys[2] = {{"instructions", "mips"}, {"cycles", "mega_cycles_per_second"}};
+
   void log(Logger& logger) {
-    for (auto& [id, countReader] : countReaders_) {
-      if (countReader == nullptr) continue;
-      auto eventRefsOpt = countReader->metric_desc->getEventRefs();
-      auto readValueOpt = readValues_[id];
-      if (!eventRefsOpt.has_value() || !readValueOpt.has_value()) continue;  // LOG(ERROR) + continue
-      for (size_t i = 0; i < eventRefsOpt->size(); i++) {
-        const std::string nickname = (*eventRefsOpt)[i].nickname;
-        const uint64_t count = readValueOpt->getCount(i);
-        if (id == "instructions" && nickname == "instructions") {
-          logger.logFloat("mips", readValueOpt->getRatePerMs(i));
-        } else if (id == "cycles" && nickname == "cycles") {
-          logger.logFloat("mega_cycles_per_second", readValueOpt->getRatePerMs(i));
-        } else {
-          logger.logUint(nickname, count);
-        }
+    for (const auto& [metric, reader] : countReaders_) {
+      if (!reader) continue;
+      const auto refs = reader->metric_desc->getEventRefs();
+      const auto& values = readValues_[metric];
+      if (!refs || !values) continue;  // the reference logs an error and moves on (:46-51)
+      const char* rate_key = nullptr;
+      for (const RateKey& k : kRateKeys)
+        if (metric == k.metric_and_event) rate_key = k.log_key;
+      for (size_t e = 0; e < refs->size(); ++e) {
+        const std::string& nick = (*refs)[e].nickname;
+        if (rate_key && nick == metric) logger.logFloat(rate_key, values->getRatePerMs(e));
+        else logger.logUint(nick, values->getCount(e));
       }
     }
   }
@@ -122,70 +123,6 @@ class PerfMonitor {
   const MuxGroupId defaultMuxGroupId_;
   std::map<ElemId, std::optional<TCountReader::ReadValues>> readValues_;
   std::map<ElemId, std::shared_ptr<TCountReader>> countReaders_;
-};
-
-// dynolog::MetricSeries<T> (dynolog/src/metric_frame/MetricSeries.h:18-260): a ring of the
-// last bufferLen samples with diff / rate / avg / percentile over [begin, end) given as
-// distances from the oldest sample (the reference's Iterator is exactly such a distance).
-// This is where the per-interval scaled counts (GroupReadValues::getCount) and the deltas
-// k_scaled_diff produces end up when dynolog keeps metric tables.
-template <typename T>
-class MetricSeries final {
- public:
-  MetricSeries(size_t bufferLen, std::string name, std::string description)
-      : data_(bufferLen), name_{std::move(name)}, description_{std::move(description)} {}
-  const std::string& name() const { return name_; }
-  const std::string& description() const { return description_; }
-  void addSample(const T& sample) {  // :148-158: overwrite the oldest when full
-    data_[tail_] = sample;
-    tail_ = (tail_ + 1) % data_.size();
-    if (size_ == data_.size()) head_ = (head_ + 1) % data_.size();
-    else ++size_;
-  }
-  size_t size() const { return size_; }
-  size_t maxLength() const { return data_.size(); }
-  const T& at(size_t idx) const { return data_[(head_ + idx) % data_.size()]; }
-  const T& operator[](size_t idx) const { return at(idx); }
-  size_t begin() const { return 0; }
-  size_t end() const { return size_; }
-
-  T diff(std::optional<size_t> b = std::nullopt, std::optional<size_t> e = std::nullopt) const {
-    return at(e.value_or(end()) - 1) - at(b.value_or(begin()));  // :221-227
-  }
-  template <typename R>
-  R rate(std::chrono::steady_clock::duration period, std::chrono::steady_clock::duration duration,
-         std::optional<size_t> b = std::nullopt, std::optional<size_t> e = std::nullopt) const {
-    const T value = diff(b, e);
-    if constexpr (std::is_integral_v<R>) {  // :235-240
-      if (period > duration) return value * (period / duration);
-      return value / (duration / period);
-    } else {                                  // :241-249
-      return static_cast<R>(value) *
-             static_cast<double>(std::chrono::duration_cast<std::chrono::microseconds>(period).count()) /
-             std::chrono::duration_cast<std::chrono::microseconds>(duration).count();
-    }
-  }
-  template <typename R>
-  R avg(std::optional<size_t> b = std::nullopt, std::optional<size_t> e = std::nullopt) const {
-    const size_t b_ = b.value_or(begin()), e_ = e.value_or(end());
-    R acc{0};
-    for (size_t i = b_; i < e_; ++i) acc += at(i);  // std::accumulate(begin_, end_, R{0})
-    return acc / static_cast<int>(e_ - b_);        // Iterator::difference_type is int (:22)
-  }
-  T percentile(float percentage, std::optional<size_t> b = std::nullopt,
-               std::optional<size_t> e = std::nullopt) const {
-    const size_t b_ = b.value_or(begin()), e_ = e.value_or(end());
-    std::vector<T> copy;
-    for (size_t i = b_; i < e_; ++i) copy.push_back(at(i));
-    const long nth = lround(percentage * (copy.size() - 1));  // :214
-    std::nth_element(copy.begin(), copy.begin() + nth, copy.end());
-    return copy[nth];
-  }
-
- private:
-  std::vector<T> data_;
-  size_t head_ = 0, tail_ = 0, size_ = 0;
-  const std::string name_, description_;
 };
 
 }  // namespace dynolog_gpu

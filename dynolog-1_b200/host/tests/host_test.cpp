@@ -200,33 +200,6 @@ static std::vector<uint64_t> switch_stream() {
   return w;
 }
 
-// the reference's own expectations: dynolog/tests/metric_frame/MetricSeriesTest.cpp:17-119
-static void test_metric_series() {
-  using namespace std::chrono;
-  dynolog_gpu::MetricSeries<int> w(3, "test_metric", "wraps");
-  for (int i = 0; i < 5; ++i) w.addSample(i);  // keeps 2,3,4
-  CHECK(w.size() == 3 && w.maxLength() == 3 && w[0] == 2 && w.at(2) == 4);
-  dynolog_gpu::MetricSeries<int> t(3, "test_metric", "this is a test metric in unittest");
-  t.addSample(0);
-  t.addSample(5);
-  t.addSample(12);
-  CHECK(t.rate<int>(seconds(1), seconds(2), t.begin(), t.end()) == 6);
-  CHECK(t.rate<int>(seconds(1), seconds(2)) == 6);
-  CHECK(t.rate<int>(minutes(1), seconds(2), t.begin(), t.end() - 1) == 150);
-  CHECK(std::fabs(t.rate<float>(seconds(1), seconds(2), t.begin(), t.end() - 1) - 2.5f) < 1e-3f);
-  dynolog_gpu::MetricSeries<int> a(3, "m", "d");
-  a.addSample(0);
-  a.addSample(12);
-  a.addSample(8);
-  CHECK(a.avg<int>(a.begin(), a.end() - 1) == 6 && a.avg<int>() == 6);
-  CHECK(std::fabs(a.avg<float>() - 20.0f / 3) < 1e-3f);
-  CHECK(a.diff() == 8 && a.diff(a.begin(), a.end() - 1) == 12 && a.diff(a.begin() + 1, a.end()) == -4);
-  dynolog_gpu::MetricSeries<int> p(101, "m", "d");
-  for (int i = 0; i <= 100; ++i) p.addSample((i * 37) % 101);  // a permutation of 0..100
-  CHECK(p.percentile(0.57f) == 57 && p.percentile(0.0f) == 0 && p.percentile(1.0f) == 100);
-  CHECK(p.percentile(0.124f) == 12 && p.percentile(0.125f) == 13);
-}
-
 static void test_vid_mapper() {
   using E = pe::Event;
   std::vector<E> ev = {
@@ -393,7 +366,6 @@ int main(int argc, char** argv) {
   test_cpu();
   test_row_sink();
   test_vid_mapper();
-  test_metric_series();
   if (mode == "gpu") test_gpu();
   std::printf("%s: %s (%d failures)\n", mode.c_str(), g_fail ? "FAILED" : "ok", g_fail);
   return g_fail ? 1 : 0;
