@@ -143,6 +143,15 @@ EXPORTS = [
      [_P, _P, C.c_uint64, C.c_uint32, C.c_uint32, _P, C.c_uint32, _P, _P, _P, _P, _P]),
     ("hbt_counts_pipeline_host", C.c_int,
      [_P, _P, C.c_uint64, C.c_uint32, C.c_uint32, _P, C.c_uint32, _P, _P, _P, _P, _P]),
+    ("hbt_comm_unique_id", C.c_int, [_P]),
+    ("hbt_comm_init", C.c_int, [_P, _P, C.c_int, C.c_int]),
+    ("hbt_comm_attach", C.c_int, [_P, _P, C.c_int, C.c_int]),
+    ("hbt_comm_n_ranks", C.c_int, [_P]),
+    ("hbt_counts_allreduce_dev", C.c_int, [_P, _P, C.c_uint64, C.c_uint32]),
+    ("hbt_counts_pipeline_sharded_dev", C.c_int,
+     [_P, _P, C.c_uint64, C.c_uint32, C.c_uint32, _P, C.c_uint32, _P, _P, _P, _P, _P]),
+    ("hbt_fetch_results_all", C.c_int, [_P, _P, C.c_uint32]),
+    ("hbt_hist_gather", C.c_int64, [_P, C.c_int, _P, C.c_uint64, _U64P]),
     ("hbt_counts_deltas_static_dev", C.c_int,
      [_P, C.c_uint64, C.c_uint32, C.c_uint32, _P, _P]),
 ]
@@ -406,6 +415,59 @@ class Context:
         self._ck(self.lib.hbt_counts_pipeline_metric_dev(self.h, desc, _ptr(reads), n_intervals, n_cpus,
                                                          _ptr(sums), _ptr(scaled), _ptr(rates),
                                                          _ptr(ratio_out), _ptr(deltas)))
+
+    # ---- multi-GPU merge (NCCL)
+    def comm_init(self, dist=None, group=None):
+        """Give this ctx an NCCL communicator over the ranks of torch.distributed's (default)
+        group: rank 0 draws the unique id, it travels as a broadcast, every rank joins."""
+        if dist is None:
+            import torch.distributed as dist
+        import torch
+        rank, world = dist.get_rank(group), dist.get_world_size(group)
+        ident = (C.c_ubyte * 128)()
+        if rank == 0:
+            rc = self.lib.hbt_comm_unique_id(ident)
+            if rc < 0:
+                raise HbtError(rc, "hbt_comm_unique_id (libnccl.so.2 not loadable?)")
+        box = [bytes(ident)]
+        dist.broadcast_object_list(box, src=dist.get_global_rank(group, 0) if group is not None else 0, group=group)
+        buf = (C.c_ubyte * 128).from_buffer_copy(box[0])
+        self._ck(self.lib.hbt_comm_init(self.h, buf, world, rank))
+        self.n_ranks, self.rank = world, rank
+
+    def comm_init_single(self):
+        """A one-rank communicator (the collectives become local copies): single-GPU tests."""
+        ident = (C.c_ubyte * 128)()
+        rc = self.lib.hbt_comm_unique_id(ident)
+        if rc < 0:
+            raise HbtError(rc, "hbt_comm_unique_id (libnccl.so.2 not loadable?)")
+        self._ck(self.lib.hbt_comm_init(self.h, ident, 1, 0))
+        self.n_ranks, self.rank = 1, 0
+
+    def counts_allreduce_dev(self, sums, n_intervals, n_events):
+        self._ck(self.lib.hbt_counts_allreduce_dev(self.h, _ptr(sums), n_intervals, n_events))
+
+    def counts_pipeline_sharded_dev(self, reads, n_intervals, n_cpus_local, n_events, ratios, sums,
+                                    scaled=None, rates=None, ratio_out=None, deltas=None):
+        r = make_ratios(ratios)
+        self._ck(self.lib.hbt_counts_pipeline_sharded_dev(
+            self.h, _ptr(reads), n_intervals, n_cpus_local, n_events, C.cast(r, C.c_void_p), len(ratios),
+            _ptr(sums), _ptr(scaled), _ptr(rates), _ptr(ratio_out), _ptr(deltas)))
+
+    def fetch_results_all(self) -> np.ndarray:
+        """Per-CPU results of every rank: [n_ranks * n_cpus] (rank-major)."""
+        out = np.zeros(self.n_cpus * self.n_ranks, dtype=RESULT_DTYPE)
+        self._ck(self.lib.hbt_fetch_results_all(self.h, _ptr(out), out.shape[0]))
+        return out
+
+    def hist_gather(self, root: int = 0, out: np.ndarray | None = None, cap: int = 0):
+        """(entries on root / None elsewhere, counts per rank)."""
+        counts = np.zeros(self.n_ranks, dtype=np.uint64)
+        if self.rank == root and out is None:
+            out = np.zeros(max(1, cap), dtype=HIST_DTYPE)
+        n = self._ck(self.lib.hbt_hist_gather(self.h, root, _ptr(out) if out is not None else None,
+                                              0 if out is None else out.shape[0], counts.ctypes.data_as(_U64P)))
+        return (out[:n] if self.rank == root else None), counts
 
     def counts_pipeline_host(self, reads: np.ndarray, ratios=()):
         """reads: [I][C][3+E] u64 on the host -> dict of host arrays."""

@@ -3,6 +3,7 @@
 // launches, and the (rare) exact re-run loop.  There is no CPU implementation of
 // any entry point: without a CUDA device hbt_create fails and nothing else runs.
 #include <cuda_runtime.h>
+#include <dlfcn.h>
 #include <cerrno>
 #include <cstdarg>
 #include <cstddef>
@@ -23,6 +24,7 @@ namespace {
 
 constexpr int kMaxSegsPerCpu = 256;
 constexpr int kMaxRatios = 64;
+constexpr int kMaxCommChunks = 8;  // interval chunks of hbt_counts_pipeline_sharded_dev
 
 template <class T>
 struct DevBuf {
@@ -63,6 +65,8 @@ struct PinBuf {
     n = 0;
   }
 };
+
+void comm_release(hbt_ctx* ctx);  // destroys an owned NCCL communicator (end of this file)
 
 struct Window {
   const uint8_t* base = nullptr;
@@ -149,6 +153,17 @@ struct hbt_ctx {
   uint64_t hist_samples = 0;       // upper bound of samples added since the last clear
   DevBuf<hbt_hist_entry> hist_out;
   DevBuf<unsigned long long> hist_n;
+
+  // multi-GPU merge (NCCL communicator over the ranks of the box)
+  void* comm = nullptr;       // ncclComm_t
+  bool comm_owned = false;
+  int n_ranks = 1, rank = 0;
+  cudaStream_t comm_stream = nullptr;
+  cudaEvent_t ev_chunk_reduced[kMaxCommChunks] = {}, ev_chunk_merged[kMaxCommChunks] = {};
+  DevBuf<hbt_cpu_result> d_out_all;
+  PinBuf<hbt_cpu_result> h_out_all;
+  DevBuf<unsigned long long> d_hist_counts;
+  PinBuf<unsigned long long> h_hist_counts;
 
   // counts scratch
   const hbt_ratio* metric_ratios_dev = nullptr;  // c_metric_ratios on this device
@@ -601,6 +616,18 @@ void hbt_destroy(hbt_ctx* ctx) {
   ctx->hist_overflow.release();
   ctx->hist_out.release();
   ctx->hist_n.release();
+  comm_release(ctx);
+  if (ctx->comm_stream) {
+    cudaStreamDestroy(ctx->comm_stream);
+    for (int k = 0; k < kMaxCommChunks; ++k) {
+      cudaEventDestroy(ctx->ev_chunk_reduced[k]);
+      cudaEventDestroy(ctx->ev_chunk_merged[k]);
+    }
+  }
+  ctx->d_out_all.release();
+  ctx->h_out_all.release();
+  ctx->d_hist_counts.release();
+  ctx->h_hist_counts.release();
   ctx->d_ratios.release();
   ctx->c_reads.release();
   ctx->c_sums.release();
@@ -1479,3 +1506,309 @@ int hbt_counts_pipeline_host(hbt_ctx* ctx, const uint64_t* reads, uint64_t n_int
 }
 
 }  // extern "C"
+
+// ---- multi-GPU merge over NCCL ---------------------------------------------
+//
+// One process per GPU; the ranks of a box shard the CPUs.  The decode path needs no exchange
+// (per-CPU outputs are disjoint by key); what IS exchanged: (i) the partial group sums of
+// counter groups -- an integer SUM all-reduce BEFORE the scaling (PerCpuBase.h:104-119 sums,
+// CpuEventsGroup.h:449-459 scales the sum) -- and (ii) gathers of per-CPU-keyed outputs.
+// libnccl is bound at run time (dlopen; the copy the process already holds, e.g. torch's, is
+// preferred), so the library has no link-time dependency on it and a single-GPU daemon never
+// loads it.
+
+namespace {
+
+struct NcclUniqueId {  // ncclUniqueId: passed by value
+  char b[HBT_COMM_ID_BYTES];
+};
+
+struct NcclApi {
+  // prototypes of nccl.h (NCCL 2.x ABI): results are ints (0 = ncclSuccess), comms opaque
+  int (*GetUniqueId)(void* id) = nullptr;
+  int (*CommInitRank)(void** comm, int nranks, NcclUniqueId id, int rank) = nullptr;
+  int (*CommDestroy)(void* comm) = nullptr;
+  int (*AllReduce)(const void* send, void* recv, size_t count, int dtype, int op, void* comm,
+                   cudaStream_t stream) = nullptr;
+  int (*AllGather)(const void* send, void* recv, size_t sendcount, int dtype, void* comm,
+                   cudaStream_t stream) = nullptr;
+  int (*Send)(const void* send, size_t count, int dtype, int peer, void* comm, cudaStream_t stream) = nullptr;
+  int (*Recv)(void* recv, size_t count, int dtype, int peer, void* comm, cudaStream_t stream) = nullptr;
+  int (*GroupStart)() = nullptr;
+  int (*GroupEnd)() = nullptr;
+  const char* (*GetErrorString)(int) = nullptr;
+  bool ok = false;
+};
+constexpr int kNcclSum = 0, kNcclUint8 = 1, kNcclUint64 = 5;  // ncclRedOp_t / ncclDataType_t values
+
+NcclApi* nccl_api() {
+  static NcclApi api;
+  static bool tried = false;
+  if (tried) return api.ok ? &api : nullptr;
+  tried = true;
+  void* h = dlopen("libnccl.so.2", RTLD_NOW | RTLD_NOLOAD);  // the copy already in the process
+  if (!h) h = dlopen("libnccl.so.2", RTLD_NOW | RTLD_GLOBAL);
+  if (!h) return nullptr;
+  auto sym = [&](const char* n) { return dlsym(h, n); };
+  api.GetUniqueId = reinterpret_cast<decltype(api.GetUniqueId)>(sym("ncclGetUniqueId"));
+  api.CommInitRank = reinterpret_cast<decltype(api.CommInitRank)>(sym("ncclCommInitRank"));
+  api.CommDestroy = reinterpret_cast<decltype(api.CommDestroy)>(sym("ncclCommDestroy"));
+  api.AllReduce = reinterpret_cast<decltype(api.AllReduce)>(sym("ncclAllReduce"));
+  api.AllGather = reinterpret_cast<decltype(api.AllGather)>(sym("ncclAllGather"));
+  api.Send = reinterpret_cast<decltype(api.Send)>(sym("ncclSend"));
+  api.Recv = reinterpret_cast<decltype(api.Recv)>(sym("ncclRecv"));
+  api.GroupStart = reinterpret_cast<decltype(api.GroupStart)>(sym("ncclGroupStart"));
+  api.GroupEnd = reinterpret_cast<decltype(api.GroupEnd)>(sym("ncclGroupEnd"));
+  api.GetErrorString = reinterpret_cast<decltype(api.GetErrorString)>(sym("ncclGetErrorString"));
+  api.ok = api.GetUniqueId && api.CommInitRank && api.CommDestroy && api.AllReduce && api.AllGather &&
+           api.Send && api.Recv && api.GroupStart && api.GroupEnd && api.GetErrorString;
+  return api.ok ? &api : nullptr;
+}
+
+int nccl_fail(hbt_ctx* ctx, int rc, const char* what) {
+  NcclApi* a = nccl_api();
+  return fail(ctx, -EIO, "%s: %s", what, a ? a->GetErrorString(rc) : "libnccl.so.2 not loadable");
+}
+#define NC(call)                                      \
+  do {                                                \
+    int r__ = (call);                                 \
+    if (r__ != 0) return nccl_fail(ctx, r__, #call);  \
+  } while (0)
+
+// word0 of a merged group sum: n_events if every rank's shard read fine (each contributed
+// n_events), else 0 -- a failed read anywhere fails the interval (PerCpuBase.h:111-113)
+__global__ void k_fix_word0(uint64_t* sums, uint64_t n_intervals, uint32_t W, uint64_t n_events,
+                            uint64_t n_ranks) {
+  for (uint64_t i = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; i < n_intervals;
+       i += (uint64_t)gridDim.x * blockDim.x)
+    sums[i * W] = sums[i * W] == n_ranks * n_events ? n_events : 0;
+}
+
+void comm_release(hbt_ctx* ctx) {
+  if (ctx->comm && ctx->comm_owned)
+    if (NcclApi* a = nccl_api()) a->CommDestroy(ctx->comm);
+  ctx->comm = nullptr;
+}
+
+int comm_ready(hbt_ctx* ctx) {
+  if (!ctx) return -EINVAL;
+  if (!ctx->comm) return fail(ctx, -ENOTCONN, "no communicator: hbt_comm_init or hbt_comm_attach first");
+  return 0;
+}
+
+int comm_streams(hbt_ctx* ctx) {
+  if (!ctx->comm_stream) {
+    CU(cudaStreamCreateWithFlags(&ctx->comm_stream, cudaStreamNonBlocking));
+    for (int k = 0; k < kMaxCommChunks; ++k) {
+      CU(cudaEventCreateWithFlags(&ctx->ev_chunk_reduced[k], cudaEventDisableTiming));
+      CU(cudaEventCreateWithFlags(&ctx->ev_chunk_merged[k], cudaEventDisableTiming));
+    }
+  }
+  return 0;
+}
+
+int allreduce_sums(hbt_ctx* ctx, uint64_t* sums, uint64_t n_intervals, uint32_t n_events, cudaStream_t st) {
+  NcclApi* a = nccl_api();
+  const uint32_t W = 3 + n_events;
+  NC(a->AllReduce(sums, sums, n_intervals * W, kNcclUint64, kNcclSum, ctx->comm, st));
+  int g = (int)((n_intervals + 255) / 256);
+  if (g > ctx->sm_count * 8) g = ctx->sm_count * 8;
+  k_fix_word0<<<g, 256, 0, st>>>(sums, n_intervals, W, n_events, (uint64_t)ctx->n_ranks);
+  ++ctx->launches;
+  CU(cudaGetLastError());
+  return 0;
+}
+
+}  // namespace
+
+extern "C" {
+
+int hbt_comm_unique_id(void* id_out) {
+  NcclApi* a = nccl_api();
+  if (!a || !id_out) return a ? -EINVAL : -ENOSYS;
+  return a->GetUniqueId(id_out) == 0 ? 0 : -EIO;
+}
+
+int hbt_comm_init(hbt_ctx* ctx, const void* id, int n_ranks, int rank) {
+  if (!ctx || !id || n_ranks < 1 || rank < 0 || rank >= n_ranks) return fail(ctx, -EINVAL, "bad rank / n_ranks");
+  NcclApi* a = nccl_api();
+  if (!a) return fail(ctx, -ENOSYS, "libnccl.so.2 could not be loaded");
+  if (ctx->comm) return fail(ctx, -EALREADY, "this context already has a communicator");
+  CU(cudaSetDevice(ctx->device));
+  NcclUniqueId uid;
+  memcpy(uid.b, id, HBT_COMM_ID_BYTES);
+  NC(a->CommInitRank(&ctx->comm, n_ranks, uid, rank));
+  ctx->comm_owned = true;
+  ctx->n_ranks = n_ranks;
+  ctx->rank = rank;
+  return 0;
+}
+
+int hbt_comm_attach(hbt_ctx* ctx, void* nccl_comm, int n_ranks, int rank) {
+  if (!ctx || !nccl_comm || n_ranks < 1 || rank < 0 || rank >= n_ranks) return fail(ctx, -EINVAL, "bad arguments");
+  if (!nccl_api()) return fail(ctx, -ENOSYS, "libnccl.so.2 could not be loaded");
+  if (ctx->comm) return fail(ctx, -EALREADY, "this context already has a communicator");
+  ctx->comm = nccl_comm;
+  ctx->comm_owned = false;
+  ctx->n_ranks = n_ranks;
+  ctx->rank = rank;
+  return 0;
+}
+
+int hbt_comm_n_ranks(const hbt_ctx* ctx) { return ctx && ctx->comm ? ctx->n_ranks : 0; }
+
+int hbt_counts_allreduce_dev(hbt_ctx* ctx, uint64_t* sums, uint64_t n_intervals, uint32_t n_events) {
+  if (int rc = comm_ready(ctx)) return rc;
+  if (!sums || n_events == 0 || n_events > HBT_MAX_EVENTS) return fail(ctx, -EINVAL, "bad arguments");
+  if (n_intervals == 0) return 0;
+  CU(cudaSetDevice(ctx->device));
+  return allreduce_sums(ctx, sums, n_intervals, n_events, ctx->stream);
+}
+
+int hbt_counts_pipeline_sharded_dev(hbt_ctx* ctx, const uint64_t* reads, uint64_t n_intervals,
+                                    uint32_t n_cpus_local, uint32_t n_events, const hbt_ratio* ratios,
+                                    uint32_t n_ratios, uint64_t* sums, uint64_t* scaled, float* rates,
+                                    double* ratio_out, uint64_t* deltas) {
+  if (int rc = comm_ready(ctx)) return rc;
+  int rc = counts_check(ctx, n_intervals, n_cpus_local, n_events, n_ratios, ratios);
+  if (rc) return rc;
+  if (!reads || !sums) return fail(ctx, -EINVAL, "NULL buffer (sums is needed: it is what the ranks exchange)");
+  if (n_intervals == 0) return 0;
+  CU(cudaSetDevice(ctx->device));
+  if ((rc = comm_streams(ctx))) return rc;
+  if ((rc = upload_ratios(ctx, ratios, n_ratios))) return rc;
+  const uint64_t W = 3 + (uint64_t)n_events;
+  if (deltas && !scaled) {
+    CU(ctx->c_scaled.reserve(n_intervals * n_events));
+    scaled = ctx->c_scaled.p;
+  }
+  // Interval chunks: the collective of chunk k (own stream) runs while chunk k+1 is reduced.
+  // Chunks of >= 4 MiB of sums keep the all-reduce out of its latency-bound regime.
+  uint64_t n_chunks = n_intervals * W * 8 / (4u << 20);
+  if (n_chunks < 1) n_chunks = 1;
+  if (n_chunks > (uint64_t)kMaxCommChunks) n_chunks = kMaxCommChunks;
+  const uint64_t per = (n_intervals + n_chunks - 1) / n_chunks;
+  auto scale_chunk = [&](uint64_t k) -> int {
+    const uint64_t i0 = k * per, n = std::min(per, n_intervals - i0);
+    CU(cudaStreamWaitEvent(ctx->stream, ctx->ev_chunk_merged[k], 0));
+    ScaleArgs a{};
+    a.sums = sums + i0 * W;
+    a.n_intervals = n;
+    a.n_events = n_events;
+    a.ratios = ctx->d_ratios.p;
+    a.n_ratios = ratio_out ? n_ratios : 0;
+    a.scaled = scaled ? scaled + i0 * n_events : nullptr;
+    a.rates = rates ? rates + i0 * n_events : nullptr;
+    a.ratio_out = ratio_out ? ratio_out + i0 * n_ratios : nullptr;
+    const uint64_t total = n * (n_events + a.n_ratios);
+    int g = (int)((total + 255) / 256);
+    if (g > ctx->sm_count * 16) g = ctx->sm_count * 16;
+    k_counts_scale<<<g, 256, 0, ctx->stream>>>(a);
+    ++ctx->launches;
+    CU(cudaGetLastError());
+    if (deltas) {
+      // interval i0's delta reaches back into the previous chunk, scaled one step earlier on this stream
+      k_scaled_diff<<<g, 256, 0, ctx->stream>>>(a.scaled, i0 ? a.scaled - n_events : nullptr, n, n_events,
+                                                deltas + i0 * n_events);
+      ++ctx->launches;
+      CU(cudaGetLastError());
+    }
+    return 0;
+  };
+  for (uint64_t k = 0; k < n_chunks; ++k) {
+    const uint64_t i0 = k * per;
+    if (i0 >= n_intervals) { n_chunks = k; break; }
+    const uint64_t n = std::min(per, n_intervals - i0);
+    rc = counts_launch(ctx, reads + i0 * n_cpus_local * W, n, n_cpus_local, n_events, 0, sums + i0 * W,
+                       nullptr, nullptr, nullptr, nullptr, 0);
+    if (rc) return rc;
+    CU(cudaEventRecord(ctx->ev_chunk_reduced[k], ctx->stream));
+    CU(cudaStreamWaitEvent(ctx->comm_stream, ctx->ev_chunk_reduced[k], 0));
+    if ((rc = allreduce_sums(ctx, sums + i0 * W, n, n_events, ctx->comm_stream))) return rc;
+    CU(cudaEventRecord(ctx->ev_chunk_merged[k], ctx->comm_stream));
+    if (k > 0 && (rc = scale_chunk(k - 1))) return rc;  // behind reduce k: overlaps all-reduce k
+  }
+  return scale_chunk(n_chunks - 1);
+}
+
+int hbt_fetch_results_all(hbt_ctx* ctx, hbt_cpu_result* out_all, uint32_t cap) {
+  if (int rc = comm_ready(ctx)) return rc;
+  if (!out_all) return -EINVAL;
+  if (int rc = complete_decode(ctx)) return rc;
+  if (!ctx->have_results) return fail(ctx, -EINVAL, "no decode to fetch");
+  const uint32_t C = ctx->n_cpus, total = C * (uint32_t)ctx->n_ranks;
+  if (cap < total) return fail(ctx, -ENOSPC, "cap %u < %u results", cap, total);
+  CU(cudaSetDevice(ctx->device));
+  CU(ctx->d_out_all.reserve(total));
+  CU(ctx->h_out_all.reserve(total));
+  NcclApi* a = nccl_api();
+  // every rank's per-CPU results (disjoint by CPU id) -> all ranks; ranks hold equal CPU counts
+  NC(a->AllGather(ctx->d_out.p, ctx->d_out_all.p, C * sizeof(hbt_cpu_result), kNcclUint8, ctx->comm, ctx->stream));
+  CU(cudaMemcpyAsync(ctx->h_out_all.p, ctx->d_out_all.p, total * sizeof(hbt_cpu_result), cudaMemcpyDeviceToHost,
+                     ctx->stream));
+  CU(cudaStreamSynchronize(ctx->stream));
+  memcpy(out_all, ctx->h_out_all.p, total * sizeof(hbt_cpu_result));
+  if (ctx->desc.aggregate == HBT_AGG_IP_HISTOGRAM && ctx->h_flags.p[4])
+    return fail(ctx, -ENOSPC, "a histogram list is full: hbt_hist_configure more capacity");
+  return (int)total;
+}
+
+int64_t hbt_hist_gather(hbt_ctx* ctx, int root, hbt_hist_entry* out, uint64_t cap, uint64_t* counts_per_rank) {
+  if (int rc = comm_ready(ctx)) return rc;
+  if (root < 0 || root >= ctx->n_ranks) return fail(ctx, -EINVAL, "root %d", root);
+  if (ctx->hist_buckets == 0) return fail(ctx, -EINVAL, "no histogram configured");
+  if (int rc = complete_decode(ctx)) return rc;
+  CU(cudaSetDevice(ctx->device));
+  NcclApi* a = nccl_api();
+  const int R = ctx->n_ranks;
+  // local entries into one array (device), their number to everybody
+  CU(ctx->d_hist_counts.reserve(R + 1));
+  CU(ctx->h_hist_counts.reserve(R + 1));
+  const uint32_t n_lists = (uint32_t)hist_lists(ctx);
+  CU(cudaMemsetAsync(ctx->hist_n.p, 0, sizeof(unsigned long long), ctx->stream));
+  uint32_t grid = (uint32_t)ctx->sm_count * 16;
+  if (grid > n_lists) grid = n_lists;
+  k_hist_gather<<<grid, 128, 0, ctx->stream>>>(hist_view(ctx), n_lists, ctx->cpu_base, nullptr, ctx->hist_n.p, 0);
+  ++ctx->launches;
+  CU(cudaGetLastError());
+  NC(a->AllGather(ctx->hist_n.p, ctx->d_hist_counts.p, 1, kNcclUint64, ctx->comm, ctx->stream));
+  CU(cudaMemcpyAsync(ctx->h_hist_counts.p, ctx->d_hist_counts.p, R * sizeof(unsigned long long),
+                     cudaMemcpyDeviceToHost, ctx->stream));
+  CU(cudaStreamSynchronize(ctx->stream));
+  uint64_t total = 0, mine_off = 0;
+  for (int r = 0; r < R; ++r) {
+    if (r == ctx->rank) mine_off = total;
+    if (counts_per_rank) counts_per_rank[r] = ctx->h_hist_counts.p[r];
+    total += ctx->h_hist_counts.p[r];
+  }
+  const uint64_t mine = ctx->h_hist_counts.p[ctx->rank];
+  const bool is_root = ctx->rank == root;
+  if (is_root && (!out || total > cap)) return fail(ctx, -ENOSPC, "cap %llu < %llu entries", (unsigned long long)cap,
+                                                   (unsigned long long)total);
+  CU(ctx->hist_out.reserve(is_root ? (total ? total : 1) : (mine ? mine : 1)));
+  CU(cudaMemsetAsync(ctx->hist_n.p, 0, sizeof(unsigned long long), ctx->stream));
+  k_hist_gather<<<grid, 128, 0, ctx->stream>>>(hist_view(ctx), n_lists, ctx->cpu_base,
+                                               ctx->hist_out.p + (is_root ? mine_off : 0), ctx->hist_n.p, mine);
+  ++ctx->launches;
+  CU(cudaGetLastError());
+  NC(a->GroupStart());
+  if (is_root) {
+    uint64_t off = 0;
+    for (int r = 0; r < R; ++r) {
+      const uint64_t n = ctx->h_hist_counts.p[r];
+      if (r != root && n)
+        NC(a->Recv(ctx->hist_out.p + off, n * sizeof(hbt_hist_entry), kNcclUint8, r, ctx->comm, ctx->stream));
+      off += n;
+    }
+  } else if (mine) {
+    NC(a->Send(ctx->hist_out.p, mine * sizeof(hbt_hist_entry), kNcclUint8, root, ctx->comm, ctx->stream));
+  }
+  NC(a->GroupEnd());
+  if (is_root && total)
+    CU(cudaMemcpyAsync(out, ctx->hist_out.p, total * sizeof(hbt_hist_entry), cudaMemcpyDeviceToHost, ctx->stream));
+  CU(cudaStreamSynchronize(ctx->stream));
+  return is_root ? (int64_t)total : (int64_t)mine;
+}
+
+}  // extern "C"
+

@@ -461,6 +461,61 @@ int hbt_counts_pipeline_host(hbt_ctx* ctx, const uint64_t* reads, uint64_t n_int
                              float* rates, double* ratio_out, uint64_t* deltas);
 
 /* ------------------------------------------------------------------------ */
+/* Multi-GPU merge (one process per GPU; the ranks of a box shard the CPUs).
+ * The reference has no counterpart: it is a single host process.  What the
+ * ranks exchange follows from its order of operations: PerCpuBase::read sums the
+ * raw triples over the CPUs as u64 (PerCpuBase.h:104-119, CpuEventsGroup.h:514-522)
+ * and getCount scales the SUM (:449-459), so partial sums are merged by an integer
+ * all-reduce BEFORE the scaling; per-CPU outputs (results, rows, (cpu,..)-keyed
+ * histogram) are disjoint by key and are only gathered.  The collectives are
+ * NCCL's; libnccl.so.2 is bound at run time (the copy the process already holds,
+ * e.g. torch's, else the system's), a single-GPU caller never loads it.       */
+/* ------------------------------------------------------------------------ */
+#define HBT_COMM_ID_BYTES 128   /* sizeof(ncclUniqueId) */
+
+/* Rank 0 fills id_out (ncclGetUniqueId) and passes the bytes to the other ranks
+ * over any host channel; then EVERY rank calls hbt_comm_init with them
+ * (ncclCommInitRank, collective).  The communicator belongs to the ctx.
+ * -ENOSYS when libnccl.so.2 cannot be loaded. */
+int hbt_comm_unique_id(void* id_out);
+int hbt_comm_init(hbt_ctx* ctx, const void* id, int n_ranks, int rank);
+/* Or use a communicator the caller already has (an ncclComm_t made by the same
+ * libnccl the process holds); it is not destroyed with the ctx. */
+int hbt_comm_attach(hbt_ctx* ctx, void* nccl_comm, int n_ranks, int rank);
+int hbt_comm_n_ranks(const hbt_ctx* ctx);   /* 0 = no communicator */
+
+/* (i) sums [n_intervals][3+n_events] of this rank's CPU shard (hbt_counts_reduce_dev)
+ * -> the sums over all ranks' CPUs, in place, on the ctx stream: ncclAllReduce(u64,
+ * sum), then word0 = n_events if every shard read fine, else 0.  Feed the result to
+ * hbt_counts_scale_dev. */
+int hbt_counts_allreduce_dev(hbt_ctx* ctx, uint64_t* sums, uint64_t n_intervals, uint32_t n_events);
+
+/* reduce -> all-reduce -> scale for a trace sharded by CPU: reads holds this rank's
+ * n_cpus_local CPUs, every rank ends up with the outputs over ALL CPUs (same
+ * outputs as hbt_counts_pipeline_dev over the unsharded trace; sums is required).
+ * Works in interval chunks: the all-reduce of chunk k runs on the ctx's second
+ * stream while chunk k+1 is reduced.  Collective: every rank calls it with the same
+ * n_intervals / n_events. */
+int hbt_counts_pipeline_sharded_dev(hbt_ctx* ctx, const uint64_t* reads, uint64_t n_intervals,
+                                    uint32_t n_cpus_local, uint32_t n_events,
+                                    const hbt_ratio* ratios, uint32_t n_ratios, uint64_t* sums,
+                                    uint64_t* scaled, float* rates, double* ratio_out,
+                                    uint64_t* deltas);
+
+/* (ii) hbt_fetch_results on every rank at once: out_all[r * n_cpus + c] is CPU c of
+ * rank r (ncclAllGather of the per-CPU results; all ranks configure the same
+ * n_cpus).  Returns n_ranks * n_cpus. */
+int hbt_fetch_results_all(hbt_ctx* ctx, hbt_cpu_result* out_all, uint32_t cap);
+
+/* (ii) the (cpu,pid,ip) tables of all ranks on rank `root` (keys are disjoint by
+ * cpu): root's `out` receives every rank's entries back to back, rank r's at
+ * [sum(counts[0..r)), ...); counts_per_rank (n_ranks entries, may be NULL) is filled
+ * on every rank.  Returns the number of entries in `out` on root, the rank's own
+ * number elsewhere (out may be NULL there). */
+int64_t hbt_hist_gather(hbt_ctx* ctx, int root, hbt_hist_entry* out, uint64_t cap,
+                        uint64_t* counts_per_rank);
+
+/* ------------------------------------------------------------------------ */
 /* Allocation-free variant                                                  */
 /* ------------------------------------------------------------------------ */
 
