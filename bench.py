@@ -7,8 +7,13 @@ Default workload = BASELINE.json configs[1]: PERF_RECORD_SAMPLE ring-buffer deco
 + (cpu,pid,ip) histogram, 256 CPUs x 16 MiB rings per GPU (IP|TID|TIME|CPU samples
 of 40 B, pid ~ Zipf(1.1) over 4096, ip ~ Zipf(1.1) over 65536 addresses per pid).
 One "step" = one pass of decode+aggregate over that batch.  Under torchrun every
-rank holds its own 256-CPU shard (weak scaling, sharded by CPU id) and the
-per-type record counters are summed with one NCCL all-reduce per step.
+rank holds its own 256-CPU shard (weak scaling, sharded by CPU id); the decode needs
+no exchange, and each timed step ends with the gather of every rank's per-CPU results
+on every rank (hbt_fetch_results_all: one NCCL all-gather inside the timed region).
+
+The line also carries a "diagnostics" block: the other BASELINE configs (C1 on the host
+cores, C3 deltas, C4 mixed stream / switch events, C5 counter groups -- at N > 1 sharded by
+CPU with the integer all-reduce inside the timed step), each with its own clock sample.
 
 Prints ONE JSON line (rank 0).  `value` is measured with the traces resident in
 HBM; `e2e` goes through the host-buffer C-ABI calls with the H2D / D2H copies
@@ -59,13 +64,15 @@ def load_peaks():
 
 
 class ClockSampler:
-    """nvidia-smi clocks + throttle reasons during the timed region.  The process is started
-    ahead of the region (its start-up takes the driver's locks for a moment and would otherwise
-    stall the first timed step of every rank on the box); stop(t0, t1) keeps the samples that
-    were read inside [t0, t1]."""
+    """nvidia-smi clocks + throttle reasons, sampled every 20 ms for the whole life of the bench
+    process (started once, long before the first timed region: its start-up takes the driver's
+    locks for a moment and would otherwise stall the first timed step of every rank on the box).
+    window(t0, t1) reports the samples read inside [t0, t1]; a region shorter than the sampling
+    period gets the samples closest to it."""
     Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,"
          "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
          "clocks_event_reasons.sw_power_cap")
+    NAMES = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
 
     def __init__(self, index: int):
         self.index = index
@@ -73,6 +80,8 @@ class ClockSampler:
         self.proc = None
 
     def start(self):
+        if self.proc is not None:
+            return self
         try:
             self.proc = subprocess.Popen(
                 ["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}",
@@ -82,26 +91,27 @@ class ClockSampler:
             self.thread.start()
         except Exception:
             self.proc = None
+        return self
 
     def _read(self):
         for line in self.proc.stdout:
             self.samples.append((time.time(), line.strip()))
 
-    def stop(self, t0=None, t1=None):
+    def window(self, t0, t1):
         if not self.proc:
-            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
-        self.proc.terminate()
-        try:
-            self.proc.wait(timeout=2)
-        except Exception:
-            self.proc.kill()
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"], "samples": 0}
+        deadline = time.time() + 0.5
+        while not self.samples and time.time() < deadline:   # never return empty-handed
+            time.sleep(0.02)
+        snap = list(self.samples)
+        lines = [l for ts, l in snap if t0 <= ts <= t1 + 0.02]
+        nearest = False
+        if not lines:
+            lines = [l for _, l in sorted(snap, key=lambda x: abs(x[0] - 0.5 * (t0 + t1)))[:3]]
+            nearest = True
         sm, mx, reasons = [], [], set()
-        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        lines = [l for ts, l in self.samples if t0 is None or t0 <= ts <= t1 + 0.02]
-        if not lines:  # a region shorter than the sampling period: the samples closest to it
-            lines = [l for _, l in sorted(self.samples, key=lambda x: abs(x[0] - t1))[:3]]
-        for s in lines:
-            parts = [x.strip() for x in s.split(",")]
+        for s_ in lines:
+            parts = [x.strip() for x in s_.split(",")]
             if len(parts) < 6:
                 continue
             try:
@@ -109,12 +119,40 @@ class ClockSampler:
                 mx.append(float(parts[1]))
             except ValueError:
                 continue
-            for n, v in zip(names, parts[2:6]):
+            for n, v in zip(self.NAMES, parts[2:6]):
                 if v.lower().startswith("active"):
                     reasons.add(n)
-        return {"sm_mhz": statistics.median(sm) if sm else None,
-                "sm_max_mhz": max(mx) if mx else None, "reasons": sorted(reasons),
-                "samples": len(sm)}
+        out = {"sm_mhz": statistics.median(sm) if sm else None,
+               "sm_max_mhz": max(mx) if mx else None, "reasons": sorted(reasons), "samples": len(sm)}
+        if nearest:
+            out["note"] = "region shorter than the 20 ms sampling period: nearest samples"
+        return out
+
+    def stop(self, t0=None, t1=None):
+        """Last use: report [t0, t1] and end the sampling process."""
+        out = self.window(t0 if t0 is not None else 0.0, t1 if t1 is not None else time.time())
+        self.close()
+        return out
+
+    def close(self):
+        if self.proc:
+            self.proc.terminate()
+            try:
+                self.proc.wait(timeout=2)
+            except Exception:
+                self.proc.kill()
+            self.proc = None
+
+
+_SAMPLER = None
+
+
+def sampler_for(local: int) -> ClockSampler:
+    """The process-wide clock sampler (rank 0 only ever asks for it)."""
+    global _SAMPLER
+    if _SAMPLER is None:
+        _SAMPLER = ClockSampler(local).start()
+    return _SAMPLER
 
 
 # ---------------------------------------------------------------------------
@@ -197,6 +235,27 @@ def make_switch_rings(n_cpus: int, ring_bytes: int, cpu_base: int, device):
     return imgs, tails, heads, n * n_cpus
 
 
+class _DevArray:
+    """A device buffer of the library seen as a torch tensor (__cuda_array_interface__)."""
+
+    def __init__(self, ptr, shape, typestr):
+        self.__cuda_array_interface__ = {"shape": shape, "typestr": typestr, "data": (ptr, False), "version": 2}
+
+
+def hist_weight_per_cpu(ctx, n_cpus: int, dev) -> np.ndarray:
+    """Sum of the entry weights of every CPU's lists, computed on the device straight from the
+    list storage (hbt_hist_lists_dev): [n_cpus] int64."""
+    ent_p, cur_p, lpc, cap = ctx.hist_lists_dev()
+    out = np.zeros(n_cpus, dtype=np.int64)
+    cursors = torch.as_tensor(_DevArray(cur_p, (n_cpus, lpc), "<u4"), device=dev).to(torch.int64)
+    pos = torch.arange(cap, device=dev)[None, :]
+    for c in range(n_cpus):   # one CPU at a time: [lists][cap] weights = 8 MiB
+        words = torch.as_tensor(_DevArray(ent_p + c * lpc * cap * 16, (lpc, cap, 4), "<u4"), device=dev)
+        w = words[:, :, 3].to(torch.int64)
+        out[c] = int((w * (pos < cursors[c][:, None])).sum().item())
+    return out
+
+
 def bind_to_gpu_cpus(local: int):
     """Run this rank (and first-touch its pinned host buffers) on the CPUs next to its GPU:
     with several ranks uploading at once, host buffers on the far socket halve the PCIe rate.
@@ -247,24 +306,33 @@ def bench_deltas(args, rank, world, local, dev, dist):
     ring_bytes = args.ring_mib << 20
     mixed = args.workload == "c4_mixed"
     switch = args.workload == "c4_switch"
+    # --shard: args.cpus is the whole machine, sharded by CPU id over the ranks (config 4:
+    # "sharded by CPU across 8 B200"); else every rank holds args.cpus rings of its own
+    shard = bool(getattr(args, "shard", False)) and world > 1
+    cpus = args.cpus // world if shard else args.cpus
+    assert cpus > 0
     if switch:
-        imgs, tails, heads, n_rec = make_switch_rings(args.cpus, ring_bytes, rank * args.cpus, dev)
+        imgs, tails, heads, n_rec = make_switch_rings(cpus, ring_bytes, rank * cpus, dev)
     elif mixed:
-        imgs, tails, heads, n_rec = make_mixed_rings(args.cpus, ring_bytes, rank * args.cpus, dev, E)
+        imgs, tails, heads, n_rec = make_mixed_rings(cpus, ring_bytes, rank * cpus, dev, E)
     else:
-        imgs, tails, heads, n_rec = make_group_rings(args.cpus, ring_bytes, rank * args.cpus, dev, E)
+        imgs, tails, heads, n_rec = make_group_rings(cpus, ring_bytes, rank * cpus, dev, E)
     window_bytes = sum(h - t for t, h in zip(tails, heads))
-    ctx = hbt.Context(local, max_cpus=args.cpus)
+    ctx = hbt.Context(local, max_cpus=cpus)
     ctx.use_torch_stream()
-    ctx.ring_configure(args.cpus, 0)
+    ctx.ring_configure(cpus, 0)
+    if args.segs_per_cpu:
+        ctx.set_geometry(args.segs_per_cpu)
+    if dist is not None:
+        ctx.comm_init(dist)
     desc = hbt.sampling_desc(E, handled=hbt.MODE_MIXED if mixed else hbt.MODE_SAMPLING)
     if switch:
         desc = hbt.switch_desc(tid_level=1)
-        ctx.set_cpu_base(rank * args.cpus)
+        ctx.set_cpu_base(rank * cpus)
     if args.agg == "none":  # diagnostic: boundary discovery + per-type counters only
         desc = hbt.count_desc(hbt.MODE_CONTEXT_SWITCH if switch else hbt.MODE_MIXED if mixed
                               else hbt.MODE_SAMPLING)
-    bases_a = np.array([imgs[c].data_ptr() for c in range(args.cpus)], dtype=np.uint64)
+    bases_a = np.array([imgs[c].data_ptr() for c in range(cpus)], dtype=np.uint64)
     tails_a, heads_a = np.array(tails, dtype=np.uint64), np.array(heads, dtype=np.uint64)
     kms = []
 
@@ -274,12 +342,15 @@ def bench_deltas(args, rank, world, local, dev, dist):
         ctx.reset_state(hbt.INVALID_TS)
         ctx.submit_rings_dev(bases_a, ring_bytes, tails_a, heads_a)
         ctx.decode(desc)
-        step.res = ctx.fetch_results()
+        if dist is not None:
+            # per-CPU results of the whole machine on every rank: one NCCL all-gather per step
+            step.res_all = ctx.fetch_results_all()
+            step.res = step.res_all[rank * cpus:(rank + 1) * cpus]
+        else:
+            step.res = ctx.fetch_results()
         kms.append(ctx.decode_kernel_ms)
 
-    sampler = ClockSampler(local)
-    if rank == 0:
-        sampler.start()  # ahead of the warm-up: see ClockSampler
+    sampler = sampler_for(local) if rank == 0 else None
     for _ in range(max(args.warmup, 3)):
         step()
     res = step.res
@@ -290,8 +361,9 @@ def bench_deltas(args, rank, world, local, dev, dist):
     wall0 = time.time()
     ms_step = timed_steps(step, args.steps, dist, dev)
     launches = ctx.launches - l0
-    clocks = sampler.stop(wall0, time.time()) if rank == 0 else None
+    clocks = sampler.window(wall0, time.time()) if rank == 0 else None
     if rank != 0:
+        ctx.close()
         return None
     peak, peak_src = load_peaks()
     k_ms = sum(kms) / len(kms)
@@ -306,7 +378,11 @@ def bench_deltas(args, rank, world, local, dev, dist):
         m0, m1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         base, n_ev = C.c_void_p(), C.c_uint64()
         ctx._ck(ctx.lib.hbt_switch_events_merged_dev(ctx.h, C.byref(base), C.byref(n_ev)))  # allocates
-        step()
+        # (a local re-decode: the other ranks have left, so no collective in here)
+        ctx.reset_state(hbt.INVALID_TS)
+        ctx.submit_rings_dev(bases_a, ring_bytes, tails_a, heads_a)
+        ctx.decode(desc)
+        ctx.fetch_results()
         torch.cuda.synchronize()
         m0.record()
         ctx._ck(ctx.lib.hbt_switch_events_merged_dev(ctx.h, C.byref(base), C.byref(n_ev)))
@@ -315,10 +391,10 @@ def bench_deltas(args, rank, world, local, dev, dist):
         merge_ms = m0.elapsed_time(m1)
         return {"metric": METRIC, "value": n_rec * world / (ms_step * 1e-3), "unit": UNIT, "n_gpus": world,
                 "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms_step,
-                "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u64",
+                "higher_is_better": True, "scaling": "strong" if shard else "weak", "vs_baseline": None, "dtype": "u64",
                 "data": "synthetic",
                 "config": {"workload": "c4_switch: mode::ContextSwitch records (32-48 B) -> tagstack::Event stream",
-                           "cpus_per_gpu": args.cpus, "ring_mib": args.ring_mib, "records_per_gpu": n_rec,
+                           "cpus_per_gpu": cpus, "ring_mib": args.ring_mib, "records_per_gpu": n_rec,
                            "events_per_gpu": n_rows, "window_bytes_per_gpu": int(window_bytes),
                            "merge_ms": merge_ms, "merge_levels": max(0, (args.cpus - 1).bit_length()),
                            "l2": "inputs exceed L2; no flush needed", "slow_tiles": ctx.slow_tiles,
@@ -335,12 +411,12 @@ def bench_deltas(args, rank, world, local, dev, dist):
         cb = cpu_baseline_deltas(args, E)
     line = {"metric": METRIC, "value": n_rec * world / (ms_step * 1e-3), "unit": UNIT, "n_gpus": world,
             "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms_step,
-            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u64",
+            "higher_is_better": True, "scaling": "strong" if shard else "weak", "vs_baseline": None, "dtype": "u64",
             "data": "synthetic",
             "config": {"workload": (f"c4_mixed: SAMPLE/SWITCH/COMM/MMAP/LOST/FORK/EXIT stream, per-type counters "
                                     f"+ per-interval deltas ({E} events)") if mixed else
                                    f"c3_deltas: group SAMPLE ({40 + 8 * E} B, {E} events) decode + per-interval deltas",
-                       "cpus_per_gpu": args.cpus, "ring_mib": args.ring_mib, "records_per_gpu": n_rec,
+                       "cpus_per_gpu": cpus, "ring_mib": args.ring_mib, "records_per_gpu": n_rec,
                        "rows_per_gpu": n_rows, "window_bytes_per_gpu": int(window_bytes),
                        "l2": "inputs exceed L2; no flush needed", "slow_tiles": ctx.slow_tiles,
                        "reruns": ctx.reruns},
@@ -355,13 +431,22 @@ def bench_deltas(args, rank, world, local, dev, dist):
 
 
 def bench_counts(args, rank, world, local, dev, dist):
-    """Diagnostic workload (config 5 shape): counter-group reduce over CPUs, NCCL sum of the
-    integer triples across ranks, then scaling + rates + IPC ratio + interval deltas."""
+    """Config 5 shape: counter-group reduce over CPUs, scaling + rates + IPC ratio + interval
+    deltas.  At N > 1 the args.cpus CPUs are SHARDED over the ranks (strong scaling over CPUs, the
+    north star's "512-CPU trace ... merged via NCCL reduce"): every timed step is
+    hbt_counts_pipeline_sharded_dev = local reduce -> ncclAllReduce(u64 sum) of the [I][3+E]
+    partial sums -> scale, in interval chunks with the collective on a second stream."""
     from dynolog_1_b200 import sharding
-    E, C, I = args.events, args.cpus, args.intervals
+    E, C_total, I = args.events, args.cpus, args.intervals
+    mine = sharding.shard_cpus(C_total, world, rank)
+    C = len(mine)
+    assert C > 0, "more ranks than CPUs"
+    # (seeded per CPU block so that a rank's shard does not depend on the world size)
     reads = tg.counts_trace(tg.stream_seed(5, rank), I, C, E, device=dev, multiplexed=True)
     ctx = hbt.Context(local, max_cpus=max(C, 1))
     ctx.use_torch_stream()
+    if dist is not None:
+        ctx.comm_init(dist)
     W = 3 + E
     sums = torch.zeros((I, W), dtype=torch.int64, device=dev)
     scaled = torch.zeros((I, E), dtype=torch.int64, device=dev)
@@ -374,13 +459,13 @@ def bench_counts(args, rank, world, local, dev, dist):
         if dist is None:
             ctx.counts_pipeline_dev(reads, I, C, E, ratios, sums, scaled, rates, ratio, deltas)
         else:
-            ctx.counts_reduce_dev(reads, I, C, E, sums)
-            sharding.allreduce_partial_sums(sums, E)
-            ctx.counts_scale_dev(sums, I, E, ratios, None, scaled, rates, ratio, deltas)
+            ctx.counts_pipeline_sharded_dev(reads, I, C, E, ratios, sums, scaled, rates, ratio, deltas)
 
-    sampler = ClockSampler(local)
-    if rank == 0:
-        sampler.start()  # ahead of the warm-up: see ClockSampler
+    def step_local():  # the same work without the exchange: what the collective costs on top
+        ctx.counts_reduce_dev(reads, I, C, E, sums)
+        ctx.counts_scale_dev(sums, I, E, ratios, None, scaled, rates, ratio, deltas)
+
+    sampler = sampler_for(local) if rank == 0 else None
     for _ in range(max(args.warmup, 3)):
         step()
     ctx.sync()
@@ -388,25 +473,46 @@ def bench_counts(args, rank, world, local, dev, dist):
     wall0 = time.time()
     ms_step = timed_steps(step, args.steps, dist, dev)
     launches = ctx.launches - l0
-    clocks = sampler.stop(wall0, time.time()) if rank == 0 else None
+    clocks = sampler.window(wall0, time.time()) if rank == 0 else None
+    ms_local = None
+    if dist is not None:
+        step_local()
+        ms_local = timed_steps(step_local, args.steps, dist, dev)
+    # cross-check (outside the timed region): the merged sums' time_enabled column is the sum
+    # over ALL CPUs -- every rank must hold the same table
+    if dist is not None:
+        chk = sums[:, 1].sum().reshape(1).clone()
+        lo, hi = chk.clone(), chk.clone()
+        dist.all_reduce(lo, op=dist.ReduceOp.MIN)
+        dist.all_reduce(hi, op=dist.ReduceOp.MAX)
+        assert int(lo.item()) == int(hi.item()), "ranks disagree on the merged sums"
+    ctx.close()
     if rank != 0:
         return None
     peak, peak_src = load_peaks()
-    algo = I * C * W * 8 + I * (W * 8 + E * 8 + E * 4 + 8 + E * 8)
-    ach = algo / (ms_step * 1e-3) / 1e9
-    return {"metric": "counter-group reads decoded+aggregated/sec", "value": I * C * world / (ms_step * 1e-3),
+    # algorithmic bytes of the whole job: every rank reads its shard once, the outputs are written once
+    algo = I * C_total * W * 8 + I * (W * 8 + E * 8 + E * 4 + 8 + E * 8)
+    ach = algo / world / (ms_step * 1e-3) / 1e9   # per GPU: the roofline is a per-GPU peak
+    line = {"metric": "counter-group reads decoded+aggregated/sec", "value": I * C_total / (ms_step * 1e-3),
             "unit": "reads/s", "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
-            "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-            "dtype": "u64/f64", "data": "synthetic",
-            "config": {"workload": f"c5_counts: {C} CPUs x {E} events x {I} intervals per GPU, "
-                                   "reduce -> [NCCL sum] -> scale/rates/ratio/deltas",
-                       "l2": f"input {I * C * W * 8 / 2**20:.0f} MiB per step exceeds L2" if I * C * W * 8 > 2**27
+            "ms_per_step": ms_step, "higher_is_better": True, "scaling": "strong" if world > 1 else "weak",
+            "vs_baseline": None, "dtype": "u64/f64", "data": "synthetic",
+            "config": {"workload": f"c5_counts: {C_total} CPUs x {E} events x {I} intervals"
+                                   + (f", sharded {C} CPUs per GPU: reduce -> ncclAllReduce(u64) -> scale/rates/ratio/deltas"
+                                      if world > 1 else ": reduce -> scale/rates/ratio/deltas"),
+                       "cpus_per_gpu": C,
+                       "l2": f"input {I * C * W * 8 / 2**20:.0f} MiB per GPU per step exceeds L2" if I * C * W * 8 > 2**27
                              else "input smaller than L2: not a valid HBM measurement"},
             "roofline": {"bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
                          "traffic": load_traffic("k_counts_reduce"), "kernel": "k_counts_reduce (+ scale, diff)",
-                         "kernel_ms": ms_step, "algorithmic_bytes": int(algo), "peak_source": peak_src,
-                         "note": "timed as the whole step (2-3 launches), not one kernel"},
+                         "kernel_ms": ms_step, "algorithmic_bytes": int(algo // world), "peak_source": peak_src,
+                         "note": "per GPU, timed as the whole step (reduce, [all-reduce], scale, diff), not one kernel"},
             "gpu_launches": int(launches), "clocks": clocks}
+    if ms_local is not None:
+        line["collective"] = {"op": "ncclAllReduce(u64, sum) of [I][3+E] partial sums, chunked, on a second stream",
+                              "bytes_per_step": int(I * W * 8), "ms_step_without_exchange": ms_local,
+                              "share_of_step": max(0.0, 1.0 - ms_local / ms_step)}
+    return line
 
 
 def run_reference(args, rank, world):
@@ -518,7 +624,7 @@ def cpu_baseline_switch(args):
     except Exception:
         return None
     ring_bytes = args.ring_mib << 20
-    sample_cpus = min(args.cpus, 4)  # ~4 us per record (a /proc lookup per new thread): keep it short
+    sample_cpus = min(args.cpus, 2)  # ~4 us per record (a /proc lookup per new thread): keep it short
     imgs, tails, heads, n_rec = make_switch_rings(sample_cpus, ring_bytes, 0, "cpu")
     rings = imgs.numpy().view(np.uint64)
     best = None
@@ -533,8 +639,12 @@ def cpu_baseline_switch(args):
             "events": int(sum(len(r["events"]) for r in ref))}
 
 
-def cpu_baseline_leg(args):
-    """Bounded CPU baseline beside the GPU number (rank 0, N=1 only)."""
+def cpu_baseline_leg(args, gpu_sample=None):
+    """Bounded CPU baseline beside the GPU number (rank 0, N=1 only): the reference's consume()
+    (oracle/_ref) + the harness's (pid,ip) map over the first ref_cpus rings.  gpu_sample =
+    (GPU histogram entries of those CPUs, per-CPU GPU results): when given, the reference's
+    histogram and per-CPU counters of the sample are compared with them entry by entry and the
+    outcome is reported as "parity_check"."""
     sys.path.insert(0, os.path.join(ROOT, "tests"))
     try:
         import _oracle as orc
@@ -554,9 +664,32 @@ def cpu_baseline_leg(args):
     h = lib.hbtref_hist_new()
     best = None
     for _ in range(2):
+        for r in res:
+            for i in range(hbt.NUM_COUNTERS):
+                r.counters[i] = 0
         t = lib.hbtref_ip_hist(h, rings.ctypes.data, ring_bytes, tails_a.ctypes.data,
                                heads_a.ctypes.data, sample_cpus, 40, hbt.DRAIN, cores, res)
         best = t if best is None else min(best, t)
+    parity = None
+    if gpu_sample is not None:
+        got_ent, got_res = gpu_sample
+        m = int(lib.hbtref_hist_size(h))
+        ref_ent = np.zeros(max(1, m), dtype=hbt.HIST_DTYPE)
+        k = int(lib.hbtref_hist_fetch(h, ref_ent.ctypes.data, ref_ent.shape[0]))
+        ref_ent = ref_ent[:k]
+
+        def canon(e):
+            o = np.lexsort((e["ip"], e["pid"], e["cpu"]))
+            return e[o]
+        a, b = canon(got_ent), canon(ref_ent)
+        same_hist = len(a) == len(b) and bool((a == b).all())
+        same_res = all(int(got_res[c]["ret"]) == int(res[c].ret) and int(got_res[c]["n_records"]) == int(res[c].n_records)
+                       and int(got_res[c]["new_tail"]) == int(res[c].new_tail)
+                       and int(res[c].counters[hbt.CNT_SAMPLE]) == int(got_res[c]["n_records"])
+                       for c in range(sample_cpus))
+        parity = {"result": "ok" if (same_hist and same_res) else "MISMATCH",
+                  "checked": f"(cpu,pid,ip) histogram of CPUs 0-{sample_cpus - 1} ({len(b)} keys, "
+                             f"{int(b['count'].sum())} samples) and their consume() results, GPU vs reference, bit-exact"}
     lib.hbtref_hist_free(h)
     # one thread, as the reference runs it (one collecting thread), on 4 of the rings
     one = min(4, sample_cpus)
@@ -564,10 +697,135 @@ def cpu_baseline_leg(args):
     t1 = lib.hbtref_ip_hist(h1, rings.ctypes.data, ring_bytes, tails_a.ctypes.data, heads_a.ctypes.data,
                             one, 40, hbt.DRAIN, 1, res)
     lib.hbtref_hist_free(h1)
-    return {"value": n_rec / best, "unit": UNIT, "cores": cores, "kind": "reference",
-            "sample": f"{sample_cpus} of {args.cpus} rings x {args.ring_mib} MiB, best of 2; "
-                      "reference consume() + std::unordered_map handler",
-            "single_thread_value": (n_rec // sample_cpus) * one / t1 if t1 > 0 else None}
+    out = {"value": n_rec / best, "unit": UNIT, "cores": cores, "kind": "reference",
+           "sample": f"{sample_cpus} of {args.cpus} rings x {args.ring_mib} MiB, best of 2; "
+                     "reference consume() + std::unordered_map handler",
+           "single_thread_value": (n_rec // sample_cpus) * one / t1 if t1 > 0 else None}
+    return out, parity
+
+
+def c1_reference_leg(args):
+    """BASELINE configs[0], the reference's own CPU-runnable case: PerCpuCountReader-style group
+    reads + getCount + PerfMonitor's rates over a 64-CPU x 8-event x 10k-interval trace, through
+    the reference's PerCpuBase::read / GroupReadValues (oracle/_ref), all host cores."""
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    try:
+        import _oracle as orc
+        if not orc.have_ref():
+            return None
+    except Exception:
+        return None
+    I, Cc, E = 10000, 64, 8
+    reads = tg.counts_trace(tg.stream_seed(1, 0), I, Cc, E, multiplexed=False).numpy().view(np.uint64)
+    cores = os.cpu_count() or 1
+    best = None
+    for _ in range(3):
+        o = orc.ref_counts(reads, [(1, 0)], threads=cores)
+        best = o["seconds"] if best is None else min(best, o["seconds"])
+    one = orc.ref_counts(reads, [(1, 0)], threads=1)["seconds"]
+    return {"workload": "c1: 64 CPUs x 8 events x 10k intervals, PerCpuBase::read + getCount + rates + IPC (CPU reference, no GPU)",
+            "value": I * Cc / best, "unit": "reads/s", "cores": cores, "kind": "reference", "seconds": best,
+            "single_thread_value": I * Cc / one, "sample": "the whole config, best of 3"}
+
+
+def run_diagnostics(args, rank, world, local, dev, dist):
+    """The other BASELINE configs beside the headline, a few steps each, every one with its own
+    clock sample.  N = 1: C3 deltas (32 events), C4 mixed stream, C4 switch events, C5 counter
+    groups (512 CPUs x 1 event x 1M intervals, and the 64 x 8 shape), C1 on the host cores.
+    N > 1: the configs the north star shards -- C5 over 512 CPUs and C4's mixed stream over 256
+    CPUs, split over the ranks, with the NCCL exchange inside every timed step."""
+    import copy
+    import gc
+
+    def variant(**kw):
+        a = copy.copy(args)
+        for k, v in kw.items():
+            setattr(a, k, v)
+        return a
+
+    if world == 1:
+        specs = [("c3_deltas_32ev", bench_deltas, variant(workload="c3_deltas", events=32, agg="hist")),
+                 ("c3_deltas_8ev", bench_deltas, variant(workload="c3_deltas", events=8, agg="hist", no_cpu_baseline=True)),
+                 ("c4_mixed", bench_deltas, variant(workload="c4_mixed", events=8, agg="hist")),
+                 ("c4_switch", bench_deltas, variant(workload="c4_switch", agg="hist")),
+                 ("c2_count_only", bench_deltas_c2none, variant()),
+                 ("c5_counts_512x1", bench_counts, variant(workload="c5_counts", cpus=512, events=1, intervals=1_000_000)),
+                 ("c5_counts_64x8", bench_counts, variant(workload="c5_counts", cpus=64, events=8, intervals=400_000))]
+    else:
+        specs = [("c5_counts_512x1_sharded", bench_counts,
+                  variant(workload="c5_counts", cpus=512, events=1, intervals=1_000_000)),
+                 ("c4_mixed_256cpus_sharded", bench_deltas,
+                  variant(workload="c4_mixed", events=8, cpus=256, shard=True, agg="hist", no_cpu_baseline=True))]
+    out = {}
+    for name, fn, a in specs:
+        a.steps = max(args.diag_steps, 3)
+        gc.collect()
+        torch.cuda.empty_cache()
+        try:
+            line = fn(a, rank, world, local, dev, dist)
+        except Exception as e:  # a diagnostic must not take the headline down with it
+            line = {"error": f"{type(e).__name__}: {e}"}
+            if dist is not None:
+                raise
+        if rank != 0 or line is None:
+            continue
+        keep = {k: line[k] for k in ("value", "unit", "ms_per_step", "steps", "scaling", "clocks", "cpu_baseline",
+                                     "collective", "gpu_launches", "error") if k in line}
+        if "config" in line:
+            keep["workload"] = line["config"].get("workload")
+            for k in ("cpus_per_gpu", "slow_tiles", "reruns", "merge_ms", "l2"):
+                if k in line["config"]:
+                    keep[k] = line["config"][k]
+        if "roofline" in line:
+            keep["roofline"] = {k: line["roofline"][k] for k in ("achieved", "peak", "frac", "kernel", "kernel_ms",
+                                                                 "algorithmic_bytes") if k in line["roofline"]}
+        out[name] = keep
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        c1 = c1_reference_leg(args)
+        if c1:
+            out["c1_cpu_reference"] = c1
+    return out
+
+
+def bench_deltas_c2none(args, rank, world, local, dev, dist):
+    """The headline's rings decoded with per-type counters only (no histogram): how fast the
+    boundary discovery alone streams the 4 GiB."""
+    ring_bytes = args.ring_mib << 20
+    imgs, tails, heads, n_rec = make_c2(args.cpus, ring_bytes, rank * args.cpus, dev)
+    window_bytes = sum(h - t for t, h in zip(tails, heads))
+    ctx = hbt.Context(local, max_cpus=args.cpus)
+    ctx.use_torch_stream()
+    ctx.ring_configure(args.cpus, 0)
+    desc = hbt.ip_desc(40, aggregate=hbt.AGG_NONE)
+    bases_a = np.array([imgs[c].data_ptr() for c in range(args.cpus)], dtype=np.uint64)
+    tails_a, heads_a = np.array(tails, dtype=np.uint64), np.array(heads, dtype=np.uint64)
+    kms = []
+
+    def step():
+        ctx.submit_rings_dev(bases_a, ring_bytes, tails_a, heads_a)
+        ctx.decode(desc)
+        step.res = ctx.fetch_results()
+        kms.append(ctx.decode_kernel_ms)
+
+    sampler = sampler_for(local) if rank == 0 else None
+    for _ in range(3):
+        step()
+    assert int(step.res["n_records"].sum()) == n_rec
+    kms.clear()
+    wall0 = time.time()
+    ms_step = timed_steps(step, args.steps, dist, dev)
+    clocks = sampler.window(wall0, time.time()) if rank == 0 else None
+    ctx.close()
+    if rank != 0:
+        return None
+    peak, _ = load_peaks()
+    k_ms = sum(kms) / len(kms)
+    ach = window_bytes / (k_ms * 1e-3) / 1e9
+    return {"value": n_rec * world / (ms_step * 1e-3), "unit": UNIT, "ms_per_step": ms_step, "steps": args.steps,
+            "scaling": "weak", "clocks": clocks,
+            "config": {"workload": "c2 rings, decode + per-type counters only (HBT_AGG_NONE)", "cpus_per_gpu": args.cpus},
+            "roofline": {"achieved": ach, "peak": peak, "frac": ach / peak, "kernel": "k_decode<NONE>", "kernel_ms": k_ms,
+                         "algorithmic_bytes": int(window_bytes)}}
 
 
 def main():
@@ -591,6 +849,12 @@ def main():
     ap.add_argument("--e2e-groups", type=int, default=8,
                     help="CPU groups (contexts) the end-to-end leg pipelines over PCIe")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-diagnostics", action="store_true",
+                    help="skip the diagnostics block (the other BASELINE configs)")
+    ap.add_argument("--diag-steps", type=int, default=20, help="timed steps of each diagnostic workload")
+    ap.add_argument("--segs-per-cpu", type=int, default=0, help="hbt_set_geometry (0 = automatic)")
+    ap.add_argument("--shard", action="store_true",
+                    help="ring workloads at N > 1: --cpus is the whole machine, sharded over the ranks")
     args = ap.parse_args()
 
     rank = int(os.environ.get("RANK", "0"))
@@ -624,9 +888,7 @@ def main():
             dist.destroy_process_group()
         return
 
-    sampler = ClockSampler(local)
-    if rank == 0:
-        sampler.start()  # long before the timed region: see ClockSampler
+    sampler = sampler_for(local) if rank == 0 else None  # started long before the timed region
     ring_bytes = args.ring_mib << 20
     cpu_base = rank * args.cpus
     imgs, tails, heads, n_rec = make_c2(args.cpus, ring_bytes, cpu_base, dev)
@@ -638,8 +900,11 @@ def main():
     ctx.ring_configure(args.cpus, 0)
     ctx.set_cpu_base(cpu_base)
     ctx.hist_configure(args.hist_slots_per_cpu * args.cpus)
+    if args.segs_per_cpu:
+        ctx.set_geometry(args.segs_per_cpu)
+    if dist is not None:
+        ctx.comm_init(dist)   # NCCL communicator of the library itself (hbt_comm_init)
     desc = hbt.ip_desc(40, aggregate=hbt.AGG_IP_HISTOGRAM if args.agg == "hist" else hbt.AGG_NONE)
-    counters_dev = torch.zeros(hbt.NUM_COUNTERS + 1, dtype=torch.int64, device=dev)
 
     bases_a = np.array([imgs[c].data_ptr() for c in range(args.cpus)], dtype=np.uint64)
     tails_a = np.array(tails, dtype=np.uint64)
@@ -651,12 +916,6 @@ def main():
         ctx.submit_rings_dev(bases_a, ring_bytes, tails_a, heads_a)
         ctx.decode(desc)
 
-    def step_exchange():
-        # metric-table merge across the GPUs of the box: per-type record counters
-        if dist is not None:
-            from dynolog_1_b200 import sharding
-            sharding.allreduce_record_counters(counters_dev)
-
     # ---- warm-up + validation -------------------------------------------------
     for it in range(max(args.warmup, 3)):
         step()
@@ -667,6 +926,15 @@ def main():
     assert total == n_rec, (total, n_rec)
     distinct = ctx.hist_size() if args.agg == "hist" else 0
     slow, reruns = ctx.slow_tiles, ctx.reruns
+    gpu_sample = None
+    if args.agg == "hist":
+        # every sample must be in the table exactly once: weights summed over each CPU's lists on
+        # the device == that CPU's record count (all records are samples)
+        per_cpu = hist_weight_per_cpu(ctx, args.cpus, dev)
+        assert np.array_equal(per_cpu, res["n_records"].astype(np.int64)), "histogram weights != samples per CPU"
+        if rank == 0 and world == 1 and not args.no_cpu_baseline:
+            # kept for the parity check against the reference's histogram of the same CPUs
+            gpu_sample = (ctx.hist_fetch_cpus(0, min(args.cpus, args.ref_cpus)), res.copy())
 
     # ---- timed region: device-resident ----------------------------------------
     launches0 = ctx.launches
@@ -680,12 +948,13 @@ def main():
     wall0 = time.time()
     host_us = []
     for _ in range(args.steps):
-        # the decode path shards by CPU with no exchange step: no collective in here
         h0 = time.perf_counter()
         step()
         host_us.append((time.perf_counter() - h0) * 1e6)  # host time to queue one step
-        # completing the decode (re-run check) is part of the step; it syncs the stream
-        last_res = ctx.fetch_results()
+        # completing the decode (re-run check) is part of the step; it syncs the stream.  The
+        # decode itself shards by CPU with no exchange; at N > 1 the step ends with every rank's
+        # per-CPU results gathered on every rank (one NCCL all-gather, hbt_fetch_results_all)
+        last_res = ctx.fetch_results_all() if dist is not None else ctx.fetch_results()
         kernel_ms.append(ctx.decode_kernel_ms)
         if args.agg == "hist":
             fold_ms.append(ctx.hist_fold_kernel_ms)
@@ -695,14 +964,10 @@ def main():
         dist.barrier()
     ms_total = e0.elapsed_time(e1)
     launches = ctx.launches - launches0
-    clocks = sampler.stop(wall0, time.time()) if rank == 0 else None
-    # the metric-table merge across the GPUs of the box, once, outside the timed steps: the
-    # per-type record counters of every rank's CPUs summed over NCCL (and checked)
-    counters_dev.zero_()
-    counters_dev[:hbt.NUM_COUNTERS] = torch.from_numpy(
-        last_res["counters"].sum(axis=0).astype(np.int64)).to(dev)
-    step_exchange()
-    merged_samples = int(counters_dev[hbt.CNT_SAMPLE].item())
+    clocks = sampler.window(wall0, time.time()) if rank == 0 else None
+    # the gathered table holds every rank's CPUs: running SAMPLE counters of the whole machine
+    merged_samples = int(last_res["counters"][:, hbt.CNT_SAMPLE].sum())
+    assert len(last_res) == args.cpus * world
     assert merged_samples == n_rec * world * (max(args.warmup, 3) + args.steps), merged_samples
 
     t = torch.tensor([ms_total], dtype=torch.float64, device=dev)
@@ -779,24 +1044,62 @@ def main():
         if dist is not None:
             dist.barrier()
         torch.cuda.synchronize()
+        e2e_steps = max(1, args.steps)   # the requested number of steps, like the device-resident leg
         t0 = time.perf_counter()
-        for _ in range(max(1, min(args.steps, 3))):
+        for _ in range(e2e_steps):
             r, n_ent = e2e_step()
         torch.cuda.synchronize()
-        dt = (time.perf_counter() - t0) / max(1, min(args.steps, 3))
+        dt = (time.perf_counter() - t0) / e2e_steps
         tt = torch.tensor([dt], dtype=torch.float64, device=dev)
         if dist is not None:
             dist.all_reduce(tt, op=dist.ReduceOp.MAX)
         dt = float(tt.item())
         assert int(r["n_records"].sum()) == n_rec
         assert n_ent == distinct, (n_ent, distinct)
+
+        # The floor of that step on this host: the same uploads with nothing else (no decode, no
+        # download), all ranks at once -- what the PCIe links and the host's memory system give
+        # when every GPU of the box pulls its rings at the same time.
+        def upload_only():
+            for cg, lo, hi, _, (_, sg) in groups:
+                for c in range(lo, hi):
+                    cg.submit_ring_image(c - lo, host_np[c], tails[c], heads[c])
+            for cg, *_ in groups:
+                cg.sync()
+        upload_only()
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        for _ in range(3):
+            upload_only()
+        up = (time.perf_counter() - t0) / 3
+        tu = torch.tensor([up], dtype=torch.float64, device=dev)
+        if dist is not None:
+            dist.all_reduce(tu, op=dist.ReduceOp.MAX)
+        up = float(tu.item())
         e2e = {"value": n_rec * world / dt, "unit": UNIT, "h2d_bytes_per_step": int(window_bytes),
                "d2h_bytes_per_step": int(n_ent * ent_dt + r.nbytes), "ms_per_step": dt * 1e3,
+               "steps": e2e_steps,
+               "upload_only_ms_per_step": up * 1e3,
+               "upload_only_gbs_per_gpu": window_bytes / up / 1e9,
+               "frac_of_upload_floor": up / dt,
                "pipeline": f"{len(groups)} CPU groups, one hbt_ctx + stream each: H2D of group g+1 "
                            "overlaps decode + fold + D2H of group g",
                "host_cpus_bound": len(numa) if numa else None}
         for cg, *_ in groups:
             cg.close()
+        del host, host_np, groups
+
+    # ---- the other BASELINE configs (all ranks take part: the sharded ones hold collectives) ----
+    diagnostics = None
+    if not args.no_diagnostics:
+        try:
+            ctx.close()
+        except Exception:
+            pass
+        imgs = None
+        diagnostics = run_diagnostics(args, rank, world, local, dev, dist)
 
     if rank != 0:
         if dist is not None:
@@ -818,8 +1121,9 @@ def main():
                    "records_per_gpu": n_rec, "distinct_keys_per_gpu": distinct,
                    "window_bytes_per_gpu": int(window_bytes),
                    "l2": "inputs (4 GiB/GPU) exceed L2; no flush needed",
-                   "sharding": "by CPU id, 256 CPUs per rank, no collective in the decode path; per-type counters "
-                               "merged over NCCL once after the timed steps",
+                   "sharding": "by CPU id, 256 CPUs per rank; the decode needs no exchange (per-CPU outputs are "
+                               "disjoint by key); at N > 1 every timed step ends with hbt_fetch_results_all, one "
+                               "NCCL all-gather of every rank's per-CPU results",
                    "slow_tiles": slow, "reruns": reruns,
                    "max_over_ranks": {"kernel_ms": float(spread[0].item()),
                                       "host_queue_us_per_step": float(spread[1].item())}},
@@ -835,11 +1139,17 @@ def main():
     }
     if e2e:
         line["e2e"] = e2e
+    if diagnostics:
+        line["diagnostics"] = diagnostics
     if world == 1 and not args.no_cpu_baseline:
         os.sched_setaffinity(0, all_cpus)  # the CPU baseline gets every host core again
-        cb = cpu_baseline_leg(args)
+        cb = cpu_baseline_leg(args, gpu_sample)
         if cb:
-            line["cpu_baseline"] = cb
+            line["cpu_baseline"] = cb[0]
+            if cb[1]:
+                line["parity_check"] = cb[1]["result"]
+                line["config"]["parity_check"] = cb[1]["checked"]
+                assert cb[1]["result"] == "ok", "GPU histogram differs from the reference's on the sampled CPUs"
     print(json.dumps(line))
     if dist is not None:
         dist.destroy_process_group()

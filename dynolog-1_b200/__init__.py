@@ -128,6 +128,7 @@ EXPORTS = [
     ("hbt_hist_clear", C.c_int, [_P]),
     ("hbt_hist_size", C.c_int64, [_P]),
     ("hbt_hist_fetch", C.c_int64, [_P, _P, C.c_uint64]),
+    ("hbt_hist_fetch_cpus", C.c_int64, [_P, C.c_uint32, C.c_uint32, _P, C.c_uint64]),
     ("hbt_hist_lists_dev", C.c_int,
      [_P, C.POINTER(_P), C.POINTER(_P), C.POINTER(C.c_uint32), C.POINTER(C.c_uint32)]),
     ("hbt_metric_count", C.c_uint32, []),
@@ -387,6 +388,20 @@ class Context:
             out = np.zeros(max(1, n), dtype=HIST_DTYPE)
         m = self._ck(self.lib.hbt_hist_fetch(self.h, _ptr(out), out.shape[0]))
         return out[:m]
+
+    def hist_fetch_cpus(self, first_cpu: int, n_cpus: int) -> np.ndarray:
+        """Entries of the ctx-local CPUs [first_cpu, first_cpu + n_cpus)."""
+        n = self._ck(self.lib.hbt_hist_fetch_cpus(self.h, first_cpu, n_cpus, None, 0))
+        out = np.zeros(max(1, n), dtype=HIST_DTYPE)
+        m = self._ck(self.lib.hbt_hist_fetch_cpus(self.h, first_cpu, n_cpus, _ptr(out), out.shape[0]))
+        return out[:m]
+
+    def hist_lists_dev(self):
+        """(entries pointer, cursors pointer, lists per CPU, list capacity) of the device lists."""
+        ent, cur = C.c_void_p(), C.c_void_p()
+        lpc, cap = C.c_uint32(), C.c_uint32()
+        self._ck(self.lib.hbt_hist_lists_dev(self.h, C.byref(ent), C.byref(cur), C.byref(lpc), C.byref(cap)))
+        return ent.value, cur.value, lpc.value, cap.value
 
     # ---- counter groups
     def counts_reduce_dev(self, reads, n_intervals, n_cpus, n_events, sums):

@@ -1223,21 +1223,30 @@ int hbt_hist_configure(hbt_ctx* ctx, uint64_t capacity_slots) {
   return hbt_hist_clear(ctx);
 }
 
-static int64_t hist_collect(hbt_ctx* ctx, hbt_hist_entry* out, uint64_t cap) {
+static int64_t hist_collect(hbt_ctx* ctx, hbt_hist_entry* out, uint64_t cap, uint32_t first_cpu = 0,
+                            uint32_t n_cpus = 0xFFFFFFFFu) {
   if (!ctx || ctx->hist_buckets == 0) return fail(ctx, -EINVAL, "no histogram configured");
   int rc = complete_decode(ctx);
   if (rc) return rc;
+  if (n_cpus == 0xFFFFFFFFu) n_cpus = ctx->n_cpus - (first_cpu < ctx->n_cpus ? first_cpu : ctx->n_cpus);
+  if (first_cpu + (uint64_t)n_cpus > ctx->n_cpus) return fail(ctx, -EINVAL, "CPU range outside the configured CPUs");
   if (out) CU(ctx->hist_out.reserve(cap ? cap : 1));
   CU(cudaMemsetAsync(ctx->hist_n.p, 0, sizeof(unsigned long long), ctx->stream));
-  const uint32_t n_lists = (uint32_t)hist_lists(ctx);
-  uint32_t grid = (uint32_t)ctx->sm_count * 16;
-  if (grid > n_lists) grid = n_lists;
-  k_hist_gather<<<grid, 128, 0, ctx->stream>>>(hist_view(ctx), n_lists, ctx->cpu_base,
-                                               out ? ctx->hist_out.p : nullptr, ctx->hist_n.p, cap);
-  ++ctx->launches;
-  CU(cudaGetLastError());
+  // the lists of CPUs [first_cpu, first_cpu + n_cpus) are contiguous
+  HistLists v = hist_view(ctx);
+  v.entries += (uint64_t)first_cpu * ctx->hist_buckets * ctx->hist_cap;
+  v.cursors += (uint64_t)first_cpu * ctx->hist_buckets;
+  const uint32_t n_lists = n_cpus * ctx->hist_buckets;
   unsigned long long n = 0;
-  CU(cudaMemcpyAsync(&n, ctx->hist_n.p, sizeof(n), cudaMemcpyDeviceToHost, ctx->stream));
+  if (n_lists) {
+    uint32_t grid = (uint32_t)ctx->sm_count * 16;
+    if (grid > n_lists) grid = n_lists;
+    k_hist_gather<<<grid, 128, 0, ctx->stream>>>(v, n_lists, ctx->cpu_base + first_cpu,
+                                                 out ? ctx->hist_out.p : nullptr, ctx->hist_n.p, cap);
+    ++ctx->launches;
+    CU(cudaGetLastError());
+    CU(cudaMemcpyAsync(&n, ctx->hist_n.p, sizeof(n), cudaMemcpyDeviceToHost, ctx->stream));
+  }
   CU(cudaStreamSynchronize(ctx->stream));
   if (out) {
     if (n > cap) return fail(ctx, -ENOSPC, "cap %llu < %llu entries", (unsigned long long)cap, n);
@@ -1253,6 +1262,11 @@ int64_t hbt_hist_size(hbt_ctx* ctx) { return hist_collect(ctx, nullptr, 0); }
 int64_t hbt_hist_fetch(hbt_ctx* ctx, hbt_hist_entry* out, uint64_t cap) {
   if (!out) return -EINVAL;
   return hist_collect(ctx, out, cap);
+}
+
+int64_t hbt_hist_fetch_cpus(hbt_ctx* ctx, uint32_t first_cpu, uint32_t n_cpus, hbt_hist_entry* out,
+                            uint64_t cap) {
+  return hist_collect(ctx, out, out ? cap : 0, first_cpu, n_cpus);
 }
 
 int hbt_hist_lists_dev(hbt_ctx* ctx, const void** entries, const uint32_t** cursors,

@@ -373,6 +373,10 @@ int hbt_hist_clear(hbt_ctx* ctx);
 /* Number of distinct keys, then the entries (unordered). */
 int64_t hbt_hist_size(hbt_ctx* ctx);
 int64_t hbt_hist_fetch(hbt_ctx* ctx, hbt_hist_entry* out, uint64_t cap);
+/* The entries of the ctx-local CPUs [first_cpu, first_cpu + n_cpus) only; out = NULL
+ * returns their number. */
+int64_t hbt_hist_fetch_cpus(hbt_ctx* ctx, uint32_t first_cpu, uint32_t n_cpus, hbt_hist_entry* out,
+                            uint64_t cap);
 /* Device view for downstream kernels: list l = cpu * (*lists_per_cpu) + bucket
  * holds cursors[l] distinct entries at entries + l * (*list_capacity) * 16 bytes. */
 int hbt_hist_lists_dev(hbt_ctx* ctx, const void** entries, const uint32_t** cursors,
