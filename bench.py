@@ -475,9 +475,6 @@ def bench_counts(args, rank, world, local, dev, dist):
     launches = ctx.launches - l0
     clocks = sampler.window(wall0, time.time()) if rank == 0 else None
     ms_local = None
-    if dist is not None:
-        step_local()
-        ms_local = timed_steps(step_local, args.steps, dist, dev)
     # cross-check (outside the timed region): the merged sums' time_enabled column is the sum
     # over ALL CPUs -- every rank must hold the same table
     if dist is not None:
@@ -486,6 +483,9 @@ def bench_counts(args, rank, world, local, dev, dist):
         dist.all_reduce(lo, op=dist.ReduceOp.MIN)
         dist.all_reduce(hi, op=dist.ReduceOp.MAX)
         assert int(lo.item()) == int(hi.item()), "ranks disagree on the merged sums"
+    if dist is not None:
+        step_local()
+        ms_local = timed_steps(step_local, args.steps, dist, dev)
     ctx.close()
     if rank != 0:
         return None
@@ -919,7 +919,10 @@ def main():
     # ---- warm-up + validation -------------------------------------------------
     for it in range(max(args.warmup, 3)):
         step()
-        res = ctx.fetch_results()
+        if dist is not None:   # the same calls as the timed steps (the first gather sets NCCL up)
+            res = ctx.fetch_results_all()[rank * args.cpus:(rank + 1) * args.cpus]
+        else:
+            res = ctx.fetch_results()
         # counters are running totals since reset_state, like the reference's members
         assert int(res["counters"][:, hbt.CNT_SAMPLE].sum()) == n_rec * (it + 1)
     total = int(res["n_records"].sum())
