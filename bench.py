@@ -748,7 +748,8 @@ def run_diagnostics(args, rank, world, local, dev, dist):
                  ("c3_deltas_8ev", bench_deltas, variant(workload="c3_deltas", events=8, agg="hist", no_cpu_baseline=True)),
                  ("c4_mixed", bench_deltas, variant(workload="c4_mixed", events=8, agg="hist")),
                  ("c4_switch", bench_deltas, variant(workload="c4_switch", agg="hist")),
-                 ("c2_count_only", bench_deltas_c2none, variant()),
+                 ("c2_count_only", bench_c2_variant, variant(c2_agg="none", c2_words=5)),
+                 ("c2_ip_hist_128B_samples", bench_c2_variant, variant(c2_agg="hist", c2_words=16)),
                  ("c5_counts_512x1", bench_counts, variant(workload="c5_counts", cpus=512, events=1, intervals=1_000_000)),
                  ("c5_counts_64x8", bench_counts, variant(workload="c5_counts", cpus=64, events=8, intervals=400_000))]
     else:
@@ -787,30 +788,39 @@ def run_diagnostics(args, rank, world, local, dev, dist):
     return out
 
 
-def bench_deltas_c2none(args, rank, world, local, dev, dist):
-    """The headline's rings decoded with per-type counters only (no histogram): how fast the
-    boundary discovery alone streams the 4 GiB."""
+def bench_c2_variant(args, rank, world, local, dev, dist):
+    """The headline's rings, device-resident only, in a variant: args.c2_agg = "none" decodes
+    with per-type counters only (how fast the boundary discovery alone streams the 4 GiB);
+    args.c2_words = 16 uses 128-byte samples (sample_type IP|TID|TIME|CPU|READ with an 8-event
+    read group: SURVEY 8d allows "40 B + optional read group") with the histogram."""
     ring_bytes = args.ring_mib << 20
-    imgs, tails, heads, n_rec = make_c2(args.cpus, ring_bytes, rank * args.cpus, dev)
+    words = getattr(args, "c2_words", 5)
+    hist = getattr(args, "c2_agg", "hist") == "hist"
+    imgs, tails, heads, n_rec = make_c2(args.cpus, ring_bytes, rank * args.cpus, dev, sample_words=words)
     window_bytes = sum(h - t for t, h in zip(tails, heads))
     ctx = hbt.Context(local, max_cpus=args.cpus)
     ctx.use_torch_stream()
     ctx.ring_configure(args.cpus, 0)
-    desc = hbt.ip_desc(40, aggregate=hbt.AGG_NONE)
+    if hist:
+        ctx.hist_configure(args.hist_slots_per_cpu * args.cpus)
+    desc = hbt.ip_desc(8 * words, aggregate=hbt.AGG_IP_HISTOGRAM if hist else hbt.AGG_NONE)
     bases_a = np.array([imgs[c].data_ptr() for c in range(args.cpus)], dtype=np.uint64)
     tails_a, heads_a = np.array(tails, dtype=np.uint64), np.array(heads, dtype=np.uint64)
     kms = []
 
     def step():
+        if hist:
+            ctx.hist_clear()
         ctx.submit_rings_dev(bases_a, ring_bytes, tails_a, heads_a)
         ctx.decode(desc)
         step.res = ctx.fetch_results()
-        kms.append(ctx.decode_kernel_ms)
+        kms.append(ctx.decode_kernel_ms + (ctx.hist_fold_kernel_ms if hist else 0.0))
 
     sampler = sampler_for(local) if rank == 0 else None
     for _ in range(3):
         step()
     assert int(step.res["n_records"].sum()) == n_rec
+    distinct = ctx.hist_size() if hist else 0
     kms.clear()
     wall0 = time.time()
     ms_step = timed_steps(step, args.steps, dist, dev)
@@ -820,12 +830,16 @@ def bench_deltas_c2none(args, rank, world, local, dev, dist):
         return None
     peak, _ = load_peaks()
     k_ms = sum(kms) / len(kms)
-    ach = window_bytes / (k_ms * 1e-3) / 1e9
+    algo = window_bytes + 16 * distinct
+    ach = algo / (k_ms * 1e-3) / 1e9
+    what = (f"c2 rings with {8 * words}-byte samples, decode + (cpu,pid,ip) histogram" if hist
+            else "c2 rings, decode + per-type counters only (HBT_AGG_NONE)")
     return {"value": n_rec * world / (ms_step * 1e-3), "unit": UNIT, "ms_per_step": ms_step, "steps": args.steps,
             "scaling": "weak", "clocks": clocks,
-            "config": {"workload": "c2 rings, decode + per-type counters only (HBT_AGG_NONE)", "cpus_per_gpu": args.cpus},
-            "roofline": {"achieved": ach, "peak": peak, "frac": ach / peak, "kernel": "k_decode<NONE>", "kernel_ms": k_ms,
-                         "algorithmic_bytes": int(window_bytes)}}
+            "config": {"workload": what, "cpus_per_gpu": args.cpus},
+            "roofline": {"achieved": ach, "peak": peak, "frac": ach / peak,
+                         "kernel": "k_decode<IP_HISTOGRAM> + k_hist_aggregate" if hist else "k_decode<NONE>",
+                         "kernel_ms": k_ms, "algorithmic_bytes": int(algo)}}
 
 
 def main():
