@@ -409,6 +409,9 @@ def bench_deltas(args, rank, world, local, dev, dist):
     cb = None
     if world == 1 and not args.no_cpu_baseline and not mixed and not switch and args.agg != "none":
         cb = cpu_baseline_deltas(args, E)
+    e2e = None
+    if world == 1 and not args.no_e2e and not switch and args.agg != "none":
+        e2e = e2e_deltas(args, local, dev, imgs, tails, heads, desc, E, n_rec, n_rows, window_bytes)
     line = {"metric": METRIC, "value": n_rec * world / (ms_step * 1e-3), "unit": UNIT, "n_gpus": world,
             "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms_step,
             "higher_is_better": True, "scaling": "strong" if shard else "weak", "vs_baseline": None, "dtype": "u64",
@@ -427,7 +430,67 @@ def bench_deltas(args, rank, world, local, dev, dist):
             "gpu_launches": int(launches), "clocks": clocks}
     if cb:
         line["cpu_baseline"] = cb
+    if e2e:
+        line["e2e"] = e2e
     return line
+
+
+def e2e_deltas(args, local, dev, imgs, tails, heads, desc, E, n_rec, n_rows, window_bytes):
+    """End to end for the deltas path: ring images in pinned HOST memory through hbt_submit_ring,
+    decode, per-CPU results and ALL delta rows back to pinned host memory (hbt_fetch_rows_all: the
+    slabs are packed on the device and leave in one copy per context).  CPU groups are pipelined
+    over PCIe like the headline's e2e leg: one hbt_ctx + stream per group."""
+    cpus, ring_bytes = len(tails), args.ring_mib << 20
+    host = torch.empty((cpus, ring_bytes // 8), dtype=torch.int64).pin_memory()
+    host.copy_(imgs)
+    host_np = host.numpy()
+    G = max(1, min(args.e2e_groups, cpus))
+    per = (cpus + G - 1) // G
+    groups = []
+    for g in range(G):
+        lo, hi = g * per, min(cpus, (g + 1) * per)
+        if lo >= hi:
+            break
+        cg = hbt.Context(local, max_cpus=hi - lo)
+        sg = torch.cuda.Stream(dev)
+        cg.set_stream(sg.cuda_stream)
+        cg.ring_configure(hi - lo, ring_bytes)
+        cap_rows = int(n_rows * 1.1 * (hi - lo) / cpus) + 1024
+        pinned = torch.empty((cap_rows, 2 + E), dtype=torch.int64).pin_memory()
+        groups.append((cg, lo, hi, pinned.numpy().view(np.uint64), sg, pinned))
+
+    def step():
+        uploaded = None
+        for cg, lo, hi, _, sg, _ in groups:
+            cg.reset_state(hbt.INVALID_TS)
+            if uploaded is not None:
+                sg.wait_event(uploaded)
+            for c in range(lo, hi):
+                cg.submit_ring_image(c - lo, host_np[c], tails[c], heads[c])
+            uploaded = torch.cuda.Event()
+            uploaded.record(sg)
+            cg.decode(desc)
+        recs = rows = 0
+        for cg, lo, hi, buf, _, _ in groups:
+            recs += int(cg.fetch_results()["n_records"].sum())
+            rows += len(cg.fetch_rows_all(E, out=buf)[0])
+        return recs, rows
+
+    step()
+    torch.cuda.synchronize()
+    steps = max(1, min(args.steps, 5))
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        recs, rows = step()
+    torch.cuda.synchronize()
+    dt = (time.perf_counter() - t0) / steps
+    assert recs == n_rec and rows == n_rows, (recs, n_rec, rows, n_rows)
+    for cg, *_ in groups:
+        cg.close()
+    return {"value": n_rec / dt, "unit": UNIT, "h2d_bytes_per_step": int(window_bytes),
+            "d2h_bytes_per_step": int(n_rows * 8 * (2 + E)), "ms_per_step": dt * 1e3, "steps": steps,
+            "pipeline": f"{len(groups)} CPU groups, one hbt_ctx + stream each; rows packed on the device, "
+                        "one device-to-host copy per group"}
 
 
 def bench_counts(args, rank, world, local, dev, dist):
@@ -745,8 +808,8 @@ def run_diagnostics(args, rank, world, local, dev, dist):
 
     if world == 1:
         specs = [("c3_deltas_32ev", bench_deltas, variant(workload="c3_deltas", events=32, agg="hist")),
-                 ("c3_deltas_8ev", bench_deltas, variant(workload="c3_deltas", events=8, agg="hist", no_cpu_baseline=True)),
-                 ("c4_mixed", bench_deltas, variant(workload="c4_mixed", events=8, agg="hist")),
+                 ("c3_deltas_8ev", bench_deltas, variant(workload="c3_deltas", events=8, agg="hist", no_cpu_baseline=True, no_e2e=True)),
+                 ("c4_mixed", bench_deltas, variant(workload="c4_mixed", events=8, agg="hist", no_e2e=True)),
                  ("c4_switch", bench_deltas, variant(workload="c4_switch", agg="hist")),
                  ("c2_count_only", bench_c2_variant, variant(c2_agg="none", c2_words=5)),
                  ("c2_ip_hist_128B_samples", bench_c2_variant, variant(c2_agg="hist", c2_words=16)),
@@ -771,7 +834,7 @@ def run_diagnostics(args, rank, world, local, dev, dist):
         if rank != 0 or line is None:
             continue
         keep = {k: line[k] for k in ("value", "unit", "ms_per_step", "steps", "scaling", "clocks", "cpu_baseline",
-                                     "collective", "gpu_launches", "error") if k in line}
+                                     "collective", "gpu_launches", "error", "e2e") if k in line}
         if "config" in line:
             keep["workload"] = line["config"].get("workload")
             for k in ("cpus_per_gpu", "slow_tiles", "reruns", "merge_ms", "l2"):

@@ -117,6 +117,8 @@ EXPORTS = [
     ("hbt_decode_kernel_ms", C.c_float, [_P]),
     ("hbt_hist_fold_kernel_ms", C.c_float, [_P]),
     ("hbt_fetch_rows", C.c_int64, [_P, C.c_uint32, _P, C.c_uint64]),
+    ("hbt_rows_packed_dev", C.c_int, [_P, C.POINTER(_P), _U64P]),
+    ("hbt_fetch_rows_all", C.c_int64, [_P, _P, C.c_uint64, _U64P]),
     ("hbt_fetch_switch_events", C.c_int64, [_P, C.c_uint32, _P, C.c_uint64]),
     ("hbt_switch_events_dev", C.c_int, [_P, C.POINTER(_P), _U64P]),
     ("hbt_switch_events_merged_dev", C.c_int, [_P, C.POINTER(_P), _U64P]),
@@ -342,6 +344,19 @@ class Context:
         out = np.zeros((max(1, n_rows), 2 + n_events), dtype=np.uint64)
         n = self._ck(self.lib.hbt_fetch_rows(self.h, cpu, _ptr(out), out.shape[0]))
         return out[:n]
+
+    def fetch_rows_all(self, n_events: int, out: np.ndarray | None = None, total_rows: int | None = None):
+        """All CPUs' rows of the last decode with one device-to-host copy: (rows [total][2+n],
+        offsets [n_cpus + 1]).  `out`: optional caller-owned (e.g. pinned) uint64 array."""
+        off = np.zeros(self.n_cpus + 1, dtype=np.uint64)
+        if out is None:
+            if total_rows is None:
+                base = C.c_void_p()
+                self._ck(self.lib.hbt_rows_packed_dev(self.h, C.byref(base), off.ctypes.data_as(_U64P)))
+                total_rows = int(off[self.n_cpus])
+            out = np.zeros((max(1, total_rows), 2 + n_events), dtype=np.uint64)
+        n = self._ck(self.lib.hbt_fetch_rows_all(self.h, _ptr(out), out.shape[0], off.ctypes.data_as(_U64P)))
+        return out[:n], off
 
     def fetch_switch_events(self, cpu: int, n_events: int) -> np.ndarray:
         """Events of the last AGG_SWITCH_EVENTS decode for `cpu` (SWITCH_EVENT_DTYPE)."""

@@ -68,6 +68,12 @@ struct PinBuf {
 
 void comm_release(hbt_ctx* ctx);  // destroys an owned NCCL communicator (end of this file)
 
+struct RowSlab {  // one run of rows of the last COUNT_DELTAS decode
+  const uint64_t* src;
+  uint64_t dst_row;  // first row in the packed array
+  uint64_t n_rows;
+};
+
 struct Window {
   const uint8_t* base = nullptr;
   uint64_t data_size = 0;
@@ -108,6 +114,11 @@ struct hbt_ctx {
   DevBuf<int64_t> d_clamp_ret;
   DevBuf<uint32_t> d_flags;
   DevBuf<uint64_t> d_rows;
+  // hbt_rows_compact_dev: the slabs of the last decode packed into one array
+  DevBuf<uint64_t> d_rows_packed;
+  PinBuf<RowSlab> h_slabs;
+  std::vector<uint64_t> rows_offsets;  // [n_cpus + 1], rows
+  bool rows_packed_valid = false;
   PinBuf<RingDesc> h_rings;
   PinBuf<SegDesc> h_segs;
   PinBuf<SegResult> h_results;
@@ -592,6 +603,8 @@ void hbt_destroy(hbt_ctx* ctx) {
   ctx->d_clamp_ret.release();
   ctx->d_flags.release();
   ctx->d_rows.release();
+  ctx->d_rows_packed.release();
+  ctx->h_slabs.release();
   ctx->h_rings.release();
   ctx->h_segs.release();
   ctx->h_results.release();
@@ -863,6 +876,7 @@ int hbt_decode(hbt_ctx* ctx, const hbt_decode_desc* desc) {
   if (rc) return rc;
   ctx->pending = true;
   ctx->have_results = false;
+  ctx->rows_packed_valid = false;
   ctx->reruns = 0;
   return 0;
 }
@@ -1091,6 +1105,91 @@ int64_t hbt_fetch_rows(hbt_ctx* ctx, uint32_t cpu, uint64_t* rows, uint64_t cap_
   }
   CU(cudaStreamSynchronize(ctx->stream));
   return (int64_t)off;
+}
+
+}  // extern "C"
+
+// Packs the row slabs of a decode (one or two runs per segment: the seam row, the segment's
+// rows) into one array, CPU after CPU in stream order: one CTA per run, consecutive threads copy
+// consecutive u64 words.  The run table lives in pinned host memory (read over PCIe once).
+static __global__ void __launch_bounds__(256)
+    k_rows_pack(const RowSlab* __restrict__ slabs, uint32_t n_slabs, uint32_t row_words,
+                uint64_t* __restrict__ dst) {
+  for (uint32_t s = blockIdx.x; s < n_slabs; s += gridDim.x) {
+    const RowSlab sl = slabs[s];
+    const uint64_t n = sl.n_rows * row_words;
+    uint64_t* out = dst + sl.dst_row * row_words;
+    for (uint64_t w = threadIdx.x; w < n; w += blockDim.x) out[w] = sl.src[w];
+  }
+}
+
+extern "C" {
+
+int hbt_rows_packed_dev(hbt_ctx* ctx, const uint64_t** rows, uint64_t* offsets) {
+  if (!ctx || !rows || !offsets) return -EINVAL;
+  int rc = complete_decode(ctx);
+  if (rc) return rc;
+  if (!ctx->have_results || ctx->desc.aggregate != HBT_AGG_COUNT_DELTAS)
+    return fail(ctx, -EINVAL, "no COUNT_DELTAS decode to read");
+  const uint32_t C = ctx->n_cpus;
+  const uint32_t row_words = 2 + ctx->desc.n_events;
+  if (!ctx->rows_packed_valid) {
+    CU(cudaSetDevice(ctx->device));
+    CU(ctx->h_slabs.reserve((size_t)2 * ctx->n_segs + 1));
+    ctx->rows_offsets.assign(C + 1, 0);
+    uint32_t k = 0;
+    uint64_t total = 0;
+    for (uint32_t c = 0; c < C; ++c) {  // the same walk as hbt_rows_slabs_dev, for every CPU
+      ctx->rows_offsets[c] = total;
+      const RingDesc& r = ctx->h_rings.p[c];
+      uint64_t remaining = ctx->h_out.p[c].n_rows;
+      for (uint32_t sgm = 0; sgm < r.n_seg && remaining; ++sgm) {
+        const uint32_t gi = r.seg_begin + sgm;
+        const SegDesc& sd = ctx->h_segs.p[gi];
+        if (ctx->h_seam.p[gi] & 1) {
+          ctx->h_slabs.p[k++] = RowSlab{sd.rows, total, 1};
+          ++total;
+          --remaining;
+        }
+        uint64_t n = ctx->h_results.p[gi].n_rows;
+        if (n > remaining) n = remaining;
+        if (n) {
+          ctx->h_slabs.p[k++] = RowSlab{sd.rows + row_words, total, n};
+          total += n;
+          remaining -= n;
+        }
+      }
+    }
+    ctx->rows_offsets[C] = total;
+    CU(ctx->d_rows_packed.reserve(total ? total * row_words : 1));
+    if (k) {
+      void* dp = nullptr;
+      CU(cudaHostGetDevicePointer(&dp, ctx->h_slabs.p, 0));
+      uint32_t grid = k < (uint32_t)ctx->sm_count * 16 ? k : (uint32_t)ctx->sm_count * 16;
+      k_rows_pack<<<grid, 256, 0, ctx->stream>>>(static_cast<const RowSlab*>(dp), k, row_words,
+                                                 ctx->d_rows_packed.p);
+      ++ctx->launches;
+      CU(cudaGetLastError());
+    }
+    ctx->rows_packed_valid = true;
+  }
+  *rows = ctx->d_rows_packed.p;
+  memcpy(offsets, ctx->rows_offsets.data(), (C + 1) * sizeof(uint64_t));
+  return 0;
+}
+
+int64_t hbt_fetch_rows_all(hbt_ctx* ctx, uint64_t* rows, uint64_t cap_rows, uint64_t* offsets) {
+  if (!ctx || !rows || !offsets) return -EINVAL;
+  const uint64_t* dev = nullptr;
+  if (int rc = hbt_rows_packed_dev(ctx, &dev, offsets)) return rc;
+  const uint64_t total = offsets[ctx->n_cpus];
+  if (total > cap_rows)
+    return fail(ctx, -ENOSPC, "cap_rows %llu < %llu", (unsigned long long)cap_rows, (unsigned long long)total);
+  if (total)
+    CU(cudaMemcpyAsync(rows, dev, total * (2 + (uint64_t)ctx->desc.n_events) * 8, cudaMemcpyDeviceToHost,
+                       ctx->stream));
+  CU(cudaStreamSynchronize(ctx->stream));  // also orders the pack kernel's reads of the pinned table
+  return (int64_t)total;
 }
 
 int64_t hbt_fetch_switch_events(hbt_ctx* ctx, uint32_t cpu, hbt_switch_event* out, uint64_t cap) {

@@ -329,6 +329,15 @@ float hbt_hist_fold_kernel_ms(hbt_ctx* ctx);
  * -ENOSPC if cap_rows is too small. */
 int64_t hbt_fetch_rows(hbt_ctx* ctx, uint32_t cpu, uint64_t* rows, uint64_t cap_rows);
 
+/* The rows of ALL CPUs of the last decode in one array: the per-segment slabs are packed on the
+ * device (one launch) into [total rows][2 + n_events], CPU c at rows [offsets[c], offsets[c+1])
+ * (offsets: host array of n_cpus + 1 entries, filled by the call), each CPU's rows in the order
+ * its generator writes them to its output ring.  hbt_fetch_rows_all then needs ONE device-to-host
+ * copy for the whole decode (hbt_fetch_rows issues one per slab); the packed array stays valid
+ * until the next decode.  Returns the total number of rows, -ENOSPC if cap_rows is too small. */
+int hbt_rows_packed_dev(hbt_ctx* ctx, const uint64_t** rows, uint64_t* offsets);
+int64_t hbt_fetch_rows_all(hbt_ctx* ctx, uint64_t* rows, uint64_t cap_rows, uint64_t* offsets);
+
 /* Events of the last HBT_AGG_SWITCH_EVENTS decode for `cpu`, in the order
  * CpuThreadSwitchGenerator writes them to its output ring
  * (PerCpuThreadSwitchGenerator.h:228-412; kWriteByteSize = sizeof(Event), :186).

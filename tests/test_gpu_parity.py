@@ -162,9 +162,19 @@ def test_sample_deltas(ctx, n_events, lost_every, ds, n_cpus):
         ring, head = ring_np(s, ds, tail)
         rings.append((ring, tail, head))
     res = gpu_decode(ctx, rings, desc, ds)
-    for cpu, (ring, tail, head) in enumerate(rings):
-        check_cpu(ctx, cpu, res[cpu], orc.consume(ring, tail, head, desc), desc)
+    wants = [orc.consume(ring, tail, head, desc) for ring, tail, head in rings]
+    for cpu in range(n_cpus):
+        check_cpu(ctx, cpu, res[cpu], wants[cpu], desc)
     assert ctx.reruns == 0 and ctx.slow_tiles == 0, "well-formed streams must stay on the fast path"
+    check_rows_all(ctx, wants, n_events)
+
+
+def check_rows_all(ctx, wants, n_events):
+    """hbt_fetch_rows_all: every CPU's rows packed on the device, one copy for the whole decode."""
+    rows, off = ctx.fetch_rows_all(n_events)
+    assert int(off[-1]) == sum(w["n_rows"] for w in wants) == len(rows)
+    for cpu, w in enumerate(wants):
+        assert np.array_equal(rows[int(off[cpu]):int(off[cpu + 1])], w["rows"]), f"packed rows of cpu {cpu}"
 
 
 def test_carry_across_calls(ctx):
@@ -205,8 +215,10 @@ def test_max_records(ctx, max_records):
         rings.append((ring, tail, head))
     desc = hbt.sampling_desc(E, max_records=max_records)
     res = gpu_decode(ctx, rings, desc, ds)
-    for cpu, (ring, tail, head) in enumerate(rings):
-        check_cpu(ctx, cpu, res[cpu], orc.consume(ring, tail, head, desc), desc)
+    wants = [orc.consume(ring, tail, head, desc) for ring, tail, head in rings]
+    for cpu in range(len(rings)):
+        check_cpu(ctx, cpu, res[cpu], wants[cpu], desc)
+    check_rows_all(ctx, wants, E)   # rows of a window cut by max_num_records
 
 
 def test_timestamp_regression_and_bad_size(ctx):
@@ -485,9 +497,11 @@ def test_small_rings_and_empty_windows(ctx, ds):
         ring, head = ring_np(s, ds, tail)
         rings.append((ring, tail, head))
     res = gpu_decode(ctx, rings, desc, ds)
-    for cpu, (ring, tail, head) in enumerate(rings):
-        check_cpu(ctx, cpu, res[cpu], orc.consume(ring, tail, head, desc), desc)
+    wants = [orc.consume(ring, tail, head, desc) for ring, tail, head in rings]
+    for cpu in range(len(rings)):
+        check_cpu(ctx, cpu, res[cpu], wants[cpu], desc)
     assert int(res[1]["ret"]) == -61 and int(res[1]["n_records"]) == 0
+    check_rows_all(ctx, wants, E)   # an empty CPU in the middle
 
 
 def test_window_overrunning_head(ctx):
