@@ -73,6 +73,17 @@ class Ratio(C.Structure):
     _fields_ = [("num_event", C.c_uint32), ("den_event", C.c_uint32)]
 
 
+class FrameRange(C.Structure):
+    _fields_ = [("start_offset", C.c_uint64), ("end_offset", C.c_uint64),
+                ("start_time_ns", C.c_int64), ("end_time_ns", C.c_int64)]
+
+
+FRAME_RANGE_DTYPE = np.dtype([("start_offset", "<u8"), ("end_offset", "<u8"),
+                              ("start_time_ns", "<i8"), ("end_time_ns", "<i8")])
+MATCH_CLOSEST, MATCH_PREV_CLOSEST, MATCH_NEXT_CLOSEST = 0, 1, 2
+FRAME_MAX_LEN = 8192
+
+
 class MetricDesc(C.Structure):
     _fields_ = [("id", C.c_char_p), ("arch", C.c_char_p), ("n_events", C.c_uint32),
                 ("nicknames", C.POINTER(C.c_char_p)), ("n_ratios", C.c_uint32),
@@ -146,6 +157,14 @@ EXPORTS = [
      [_P, _P, C.c_uint64, C.c_uint32, C.c_uint32, _P, C.c_uint32, _P, _P, _P, _P, _P]),
     ("hbt_counts_pipeline_host", C.c_int,
      [_P, _P, C.c_uint64, C.c_uint32, C.c_uint32, _P, C.c_uint32, _P, _P, _P, _P, _P]),
+    ("hbt_frame_create", C.c_int, [_P, C.POINTER(_P), C.c_uint32, C.c_uint32, _P, C.c_int64]),
+    ("hbt_frame_destroy", None, [_P]),
+    ("hbt_frame_length", C.c_uint64, [_P]),
+    ("hbt_frame_add_samples_dev", C.c_int, [_P, _P, C.c_uint64, C.c_uint32, C.c_int64]),
+    ("hbt_frame_add_samples", C.c_int, [_P, _P, C.c_uint64, C.c_int64]),
+    ("hbt_frame_get_range", C.c_int, [_P, C.c_int64, C.c_int64, C.c_int, C.c_int, C.POINTER(FrameRange)]),
+    ("hbt_frame_query", C.c_int,
+     [_P, _P, C.c_uint32, C.c_int64, C.c_float, _P, _P, _P, _P, _P, _P]),
     ("hbt_comm_unique_id", C.c_int, [_P]),
     ("hbt_comm_init", C.c_int, [_P, _P, C.c_int, C.c_int]),
     ("hbt_comm_attach", C.c_int, [_P, _P, C.c_int, C.c_int]),
@@ -513,6 +532,58 @@ class Context:
             _ptr(out["sums"]), _ptr(out["scaled"]), _ptr(out["rates"]),
             _ptr(out["ratios"]) if R else None, _ptr(out["deltas"])))
         out["ratios"] = out["ratios"][:, :R]
+        return out
+
+
+class Frame:
+    """hbt_frame: a MetricFrameVector kept on the device of `ctx` (dynolog/src/metric_frame)."""
+
+    def __init__(self, ctx: "Context", is_double, frame_len: int, interval_us: int):
+        self.ctx = ctx
+        self.is_double = np.ascontiguousarray(is_double, dtype=np.uint8)
+        self.n_series = len(self.is_double)
+        h = C.c_void_p()
+        ctx._ck(ctx.lib.hbt_frame_create(ctx.h, C.byref(h), self.n_series, frame_len, _ptr(self.is_double),
+                                         interval_us))
+        self.h = h
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.ctx.lib.hbt_frame_destroy(self.h)
+            self.h = None
+
+    def __len__(self):
+        return int(self.ctx.lib.hbt_frame_length(self.h))
+
+    def add_samples(self, rows: np.ndarray, last_time_ns: int):
+        rows = np.ascontiguousarray(rows)
+        assert rows.ndim == 2 and rows.shape[1] == self.n_series and rows.itemsize == 8
+        self.ctx._ck(self.ctx.lib.hbt_frame_add_samples(self.h, _ptr(rows), rows.shape[0], last_time_ns))
+
+    def add_samples_dev(self, rows, n_rows: int, row_stride_words: int, last_time_ns: int):
+        self.ctx._ck(self.ctx.lib.hbt_frame_add_samples_dev(self.h, _ptr(rows), n_rows, row_stride_words,
+                                                            last_time_ns))
+
+    def get_range(self, start_ns: int, end_ns: int, start_policy=MATCH_CLOSEST, end_policy=MATCH_CLOSEST):
+        """MetricFrameBase::slice's range, or None where the reference returns std::nullopt."""
+        r = FrameRange()
+        rc = self.ctx.lib.hbt_frame_get_range(self.h, start_ns, end_ns, start_policy, end_policy, C.byref(r))
+        if rc < 0:
+            return None
+        return (int(r.start_offset), int(r.end_offset), int(r.start_time_ns), int(r.end_time_ns))
+
+    def query(self, ranges, period_ns: int, percentage: float):
+        """ranges: list of get_range() tuples -> dict of [n_windows][n_series] arrays."""
+        ra = np.zeros(len(ranges), dtype=FRAME_RANGE_DTYPE)
+        for i, r in enumerate(ranges):
+            ra[i] = r
+        W, S = len(ranges), self.n_series
+        out = dict(diff=np.zeros((W, S), np.uint64), rate_f64=np.zeros((W, S), np.float64),
+                   rate_i64=np.zeros((W, S), np.int64), avg_f64=np.zeros((W, S), np.float64),
+                   avg_i64=np.zeros((W, S), np.int64), pct=np.zeros((W, S), np.uint64))
+        self.ctx._ck(self.ctx.lib.hbt_frame_query(self.h, _ptr(ra), W, period_ns, percentage, _ptr(out["diff"]),
+                                                  _ptr(out["rate_f64"]), _ptr(out["rate_i64"]),
+                                                  _ptr(out["avg_f64"]), _ptr(out["avg_i64"]), _ptr(out["pct"])))
         return out
 
 

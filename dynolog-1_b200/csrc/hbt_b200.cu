@@ -15,6 +15,7 @@
 
 #include "../../include/hbt_b200.h"
 #include "counts.cuh"
+#include "ctx_internal.h"
 #include "decode.cuh"
 #include "metric_table.h"
 
@@ -547,6 +548,21 @@ int hist_fold(hbt_ctx* ctx) {
 }  // namespace
 
 static int complete_decode(hbt_ctx* ctx);
+
+// ctx_internal.h
+int hbt_ctx_device(const hbt_ctx* ctx) { return ctx->device; }
+cudaStream_t hbt_ctx_stream(const hbt_ctx* ctx) { return ctx->stream; }
+int hbt_ctx_sm_count(const hbt_ctx* ctx) { return ctx->sm_count; }
+void hbt_ctx_count_launches(hbt_ctx* ctx, unsigned n) { ctx->launches += n; }
+int hbt_ctx_fail(hbt_ctx* ctx, int code, const char* fmt, ...) {
+  char buf[512];
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(buf, sizeof(buf), fmt, ap);
+  va_end(ap);
+  if (ctx) ctx->err = buf;
+  return code;
+}
 
 extern "C" {
 

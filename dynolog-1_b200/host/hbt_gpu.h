@@ -309,16 +309,27 @@ class PerCpuCountSampleDecoder {
     d.tsc.time_mult = 1;
     gpu_->check(hbt_decode(gpu_->get(), &d), "hbt_decode");
     gpu_->check(hbt_fetch_results(gpu_->get(), results_.data(), (uint32_t)results_.size()), "hbt_fetch_results");
+    rows_valid_ = false;
     std::map<CpuId, int64_t> ret;
     for (CpuId cpu : mon_cpus_.cpus) ret[cpu] = results_[cpu].ret;
     return ret;
   }
-  // rows {tstamp, duration, deltas[n]} of the last consume(), kWriteByteSize each (:69)
+  // rows {tstamp, duration, deltas[n]} of the last consume(), kWriteByteSize each (:69).  The
+  // first call after a consume() brings the rows of ALL CPUs back with one copy (the library
+  // packs them on the device, hbt_fetch_rows_all); later calls slice that.
   std::vector<uint64_t> rows(CpuId cpu) {
     const auto& r = results_.at(cpu);
-    std::vector<uint64_t> out(r.n_rows * (2 + n_events_));
-    if (r.n_rows) gpu_->check(hbt_fetch_rows(gpu_->get(), cpu, out.data(), r.n_rows), "hbt_fetch_rows");
-    return out;
+    const size_t w = 2 + n_events_;
+    if (!rows_valid_) {
+      uint64_t total = 0;
+      for (const auto& x : results_) total += x.n_rows;
+      rows_all_.resize(total * w + 1);
+      rows_off_.assign(results_.size() + 1, 0);
+      gpu_->check(hbt_fetch_rows_all(gpu_->get(), rows_all_.data(), total, rows_off_.data()), "hbt_fetch_rows_all");
+      rows_valid_ = true;
+    }
+    const uint64_t* b = rows_all_.data() + rows_off_[cpu] * w;
+    return std::vector<uint64_t>(b, b + r.n_rows * w);
   }
   uint64_t getNumRecordLost(CpuId c) const { return results_.at(c).counters[HBT_CNT_LOST]; }
   uint64_t getNumRecordSample(CpuId c) const { return results_.at(c).counters[HBT_CNT_SAMPLE]; }
@@ -331,6 +342,8 @@ class PerCpuCountSampleDecoder {
   size_t n_events_;
   std::shared_ptr<GpuContext> gpu_;
   std::vector<hbt_cpu_result> results_;
+  std::vector<uint64_t> rows_all_, rows_off_;
+  bool rows_valid_ = false;
 };
 
 // tagstack::Event (hbt/src/tagstack/Event.h:28-227) is hbt_switch_event byte for byte.

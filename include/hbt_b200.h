@@ -474,6 +474,73 @@ int hbt_counts_pipeline_host(hbt_ctx* ctx, const uint64_t* reads, uint64_t n_int
                              float* rates, double* ratio_out, uint64_t* deltas);
 
 /* ------------------------------------------------------------------------ */
+/* Metric tables: dynolog's MetricFrame (a set of MetricSeries rings sharing one
+ * fixed-interval time axis, dynolog/src/metric_frame/MetricFrame.h:37-55,
+ * MetricFrameTsUnit.cpp:14-132) kept in HBM, fed with the per-interval tables
+ * the counter-group kernels produce, and the window statistics of
+ * MetricSeriesSlice (MetricFrameBase.h:66-91 over MetricSeries.h:189-251).   */
+/* ------------------------------------------------------------------------ */
+typedef struct hbt_frame hbt_frame;
+#define HBT_FRAME_MAX_LEN 8192u   /* samples a frame can hold (a window is staged in shared memory) */
+
+enum {  /* MATCH_POLICY, MetricFrameTsUnitInterface.h:15-19 */
+  HBT_MATCH_CLOSEST = 0,
+  HBT_MATCH_PREV_CLOSEST = 1,
+  HBT_MATCH_NEXT_CLOSEST = 2
+};
+
+/* MetricFrameRange (MetricFrameTsUnitInterface.h:21-29): offsets count from the
+ * oldest sample held; times are steady_clock ticks (nanoseconds). */
+typedef struct hbt_frame_range {
+  uint64_t start_offset;
+  uint64_t end_offset;      /* inclusive, like MetricFrameOffset */
+  int64_t start_time_ns;
+  int64_t end_time_ns;
+} hbt_frame_range;
+
+/* A MetricFrameVector of n_series rings of frame_len samples on ctx's device.
+ * series_is_double[s] != 0 makes series s a MetricSeries<double>, else
+ * MetricSeries<int64_t> (NULL: all int64).  interval_us is the fixed sampling
+ * interval of the time axis (MetricFrameTsUnitFixInterval); 0 is refused like
+ * the reference's constructor refuses it.  Destroy frames before their ctx. */
+int hbt_frame_create(hbt_ctx* ctx, hbt_frame** out, uint32_t n_series, uint32_t frame_len,
+                     const uint8_t* series_is_double, int64_t interval_us);
+void hbt_frame_destroy(hbt_frame* frame);
+uint64_t hbt_frame_length(const hbt_frame* frame);   /* MetricFrameBase::length() */
+
+/* MetricFrameVector::addSamples for n_rows consecutive samples (oldest first):
+ * row r holds one 8-byte value per series (int64 or the bits of a double);
+ * last_time_ns is the time of the LAST row (with a fixed interval the axis keeps
+ * nothing else).  _dev: rows is a DEVICE array with row_stride_words >= n_series
+ * words per row -- e.g. the `scaled` / `deltas` / `ratio_out` table of
+ * hbt_counts_pipeline_dev, appended without leaving the GPU; asynchronous on the
+ * ctx stream.  The host variant copies the rows up and returns when done. */
+int hbt_frame_add_samples_dev(hbt_frame* frame, const void* rows, uint64_t n_rows,
+                              uint32_t row_stride_words, int64_t last_time_ns);
+int hbt_frame_add_samples(hbt_frame* frame, const void* rows, uint64_t n_rows, int64_t last_time_ns);
+
+/* MetricFrameBase::slice / MetricFrameTsUnitFixInterval::getRange
+ * (MetricFrameTsUnit.cpp:49-99): the samples matching [start, end] under the two
+ * policies.  -ENOENT where the reference returns std::nullopt. */
+int hbt_frame_get_range(const hbt_frame* frame, int64_t start_ns, int64_t end_ns, int start_policy,
+                        int end_policy, hbt_frame_range* out);
+
+/* The statistics of MetricSeriesSlice for n_windows ranges x every series in one
+ * pass; outputs are HOST arrays [n_windows][n_series], any may be NULL:
+ *   diff      last - first of the window, raw 8 bytes (int64, or the bits of a double)
+ *   rate_f64  rate<double>(period): double(diff) * us(period) / us(window duration)
+ *   rate_i64  rate<int64_t>(period): diff * (period / duration) if period > duration
+ *             else diff / (duration / period), on steady_clock ticks (MetricSeries.h:229-249)
+ *   avg_f64   avg<double>(): left fold in sample order, divided by the sample count
+ *   avg_i64   avg<int64_t>() (int64 series; 0 for double series)
+ *   pct       percentile(percentage): the lround(percentage * (n - 1))-th order statistic, raw 8 bytes
+ * A one-sample window has duration 0: the reference divides by zero there; here
+ * rate_i64 is 0 and rate_f64 follows IEEE. */
+int hbt_frame_query(hbt_frame* frame, const hbt_frame_range* ranges, uint32_t n_windows,
+                    int64_t period_ns, float percentage, uint64_t* diff, double* rate_f64,
+                    int64_t* rate_i64, double* avg_f64, int64_t* avg_i64, uint64_t* pct);
+
+/* ------------------------------------------------------------------------ */
 /* Multi-GPU merge (one process per GPU; the ranks of a box shard the CPUs).
  * The reference has no counterpart: it is a single host process.  What the
  * ranks exchange follows from its order of operations: PerCpuBase::read sums the

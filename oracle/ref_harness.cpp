@@ -821,3 +821,86 @@ uint64_t hbtref_kernel_time_from_tsc(uint64_t tsc_cycles, const hbt_tsc_params* 
 }
 
 }  // extern "C"
+
+// ---------------------------------------------------------------------------
+// Metric tables: the REAL dynolog::MetricFrameVector / MetricSeries / MetricFrameTsUnitFixInterval
+// (dynolog/src/metric_frame/*, compiled from the reference's own .cpp files by oracle/Makefile).
+// rows [n_rows][S] are added oldest first, row r at t_last - (n_rows-1-r) * interval; each query
+// slices the frame like MetricFrameBase::slice and evaluates MetricSeriesSlice's statistics.
+// ---------------------------------------------------------------------------
+#include "dynolog/src/metric_frame/MetricFrame.h"
+#include "dynolog/src/metric_frame/MetricFrameTsUnit.h"
+
+extern "C" int hbtref_frame_query(const uint64_t* rows, uint64_t n_rows, uint32_t S, const uint8_t* is_double,
+                                  uint32_t frame_len, int64_t interval_us, int64_t t_last_ns,
+                                  const int64_t* q_start, const int64_t* q_end, const int32_t* pol_s,
+                                  const int32_t* pol_e, uint32_t Q, int64_t period_ns, float percentage,
+                                  hbt_frame_range* ranges_out, uint8_t* ok, uint64_t* diff, double* rate_f64,
+                                  int64_t* rate_i64, double* avg_f64, int64_t* avg_i64, uint64_t* pct,
+                                  uint64_t* length_out) {
+  namespace dl = facebook::dynolog;
+  using ns = std::chrono::nanoseconds;
+  auto ts = std::make_shared<dl::MetricFrameTsUnitFixInterval>(std::chrono::microseconds(interval_us), frame_len);
+  dl::VectorSeriesDefList defs;
+  for (uint32_t s = 0; s < S; ++s) {
+    if (is_double[s])
+      defs.push_back(std::make_shared<dl::MetricSeries<double>>(frame_len, "s" + std::to_string(s), ""));
+    else
+      defs.push_back(std::make_shared<dl::MetricSeries<int64_t>>(frame_len, "s" + std::to_string(s), ""));
+  }
+  dl::MetricFrameVector frame(defs, "frame", "", ts);
+  for (uint64_t r = 0; r < n_rows; ++r) {
+    dl::VectorSamplesT samples;
+    for (uint32_t s = 0; s < S; ++s) {
+      const uint64_t raw = rows[r * S + s];
+      if (is_double[s]) {
+        double d;
+        std::memcpy(&d, &raw, 8);
+        samples.emplace_back(d);
+      } else {
+        samples.emplace_back(static_cast<int64_t>(raw));
+      }
+    }
+    const int64_t t = t_last_ns - static_cast<int64_t>(n_rows - 1 - r) * interval_us * 1000;
+    if (!frame.addSamples(samples, dl::TimePoint(ns(t)))) return -EINVAL;
+  }
+  *length_out = frame.length();
+  const auto period = std::chrono::steady_clock::duration(ns(period_ns));
+  for (uint32_t q = 0; q < Q; ++q) {
+    const auto a = dl::TimePoint(ns(q_start[q])), b = dl::TimePoint(ns(q_end[q]));
+    const auto ps = static_cast<dl::MATCH_POLICY>(pol_s[q]), pe = static_cast<dl::MATCH_POLICY>(pol_e[q]);
+    auto range = ts->getRange(a, b, ps, pe);
+    auto slice = frame.slice(a, b, ps, pe);
+    ok[q] = range.has_value() && slice.has_value() && range->end.offset >= range->start.offset;
+    if (!ok[q]) continue;
+    ranges_out[q].start_offset = range->start.offset;
+    ranges_out[q].end_offset = range->end.offset;
+    ranges_out[q].start_time_ns = std::chrono::duration_cast<ns>(range->start.time.time_since_epoch()).count();
+    ranges_out[q].end_time_ns = std::chrono::duration_cast<ns>(range->end.time.time_since_epoch()).count();
+    const bool zero_duration = range->start.time == range->end.time;  // integral rate would divide by zero
+    for (uint32_t s = 0; s < S; ++s) {
+      const size_t g = static_cast<size_t>(q) * S + s;
+      if (is_double[s]) {
+        auto sl = slice->series<double>(static_cast<int>(s));
+        if (!sl) return -EIO;
+        const double d = sl->diff(), p = sl->percentile(percentage);
+        std::memcpy(&diff[g], &d, 8);
+        std::memcpy(&pct[g], &p, 8);
+        rate_f64[g] = sl->rate<double>(period);
+        rate_i64[g] = zero_duration ? 0 : sl->rate<int64_t>(period);
+        avg_f64[g] = sl->avg<double>();
+        avg_i64[g] = 0;
+      } else {
+        auto sl = slice->series<int64_t>(static_cast<int>(s));
+        if (!sl) return -EIO;
+        diff[g] = static_cast<uint64_t>(sl->diff());
+        pct[g] = static_cast<uint64_t>(sl->percentile(percentage));
+        rate_f64[g] = sl->rate<double>(period);
+        rate_i64[g] = zero_duration ? 0 : sl->rate<int64_t>(period);
+        avg_f64[g] = sl->avg<double>();
+        avg_i64[g] = sl->avg<int64_t>();
+      }
+    }
+  }
+  return 0;
+}

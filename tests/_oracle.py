@@ -474,3 +474,161 @@ def ref_counts(reads: np.ndarray, ratios=(), threads=1):
     o["ratios"] = o["ratios"][:, :R]
     o["seconds"] = t
     return o
+
+
+# ---------------------------------------------------------------------------
+# Metric tables (dynolog/src/metric_frame): the reference's own classes through oracle/_ref, and a
+# numpy / plain-Python restatement for machines without it.
+# ---------------------------------------------------------------------------
+def ref_frame_query(rows, is_double, frame_len, interval_us, t_last_ns, queries, period_ns, percentage):
+    """The REAL MetricFrameVector / MetricFrameTsUnitFixInterval / MetricSeriesSlice.  rows [n][S]
+    raw 8-byte values, queries = [(start_ns, end_ns, start_policy, end_policy)].  Returns (length,
+    ranges (None where slice() is nullopt), dict of [Q][S] arrays)."""
+    lib = ref()
+    rows = np.ascontiguousarray(rows).view(np.uint64)
+    n, S = rows.shape
+    isd = np.ascontiguousarray(is_double, dtype=np.uint8)
+    Q = len(queries)
+    qs = np.array([q[0] for q in queries], np.int64)
+    qe = np.array([q[1] for q in queries], np.int64)
+    ps = np.array([q[2] for q in queries], np.int32)
+    pe = np.array([q[3] for q in queries], np.int32)
+    ranges = np.zeros(Q, dtype=hbt.FRAME_RANGE_DTYPE)
+    ok = np.zeros(Q, np.uint8)
+    out = dict(diff=np.zeros((Q, S), np.uint64), rate_f64=np.zeros((Q, S), np.float64),
+               rate_i64=np.zeros((Q, S), np.int64), avg_f64=np.zeros((Q, S), np.float64),
+               avg_i64=np.zeros((Q, S), np.int64), pct=np.zeros((Q, S), np.uint64))
+    length = C.c_uint64()
+    lib.hbtref_frame_query.restype = C.c_int
+    lib.hbtref_frame_query.argtypes = [_P, C.c_uint64, C.c_uint32, _P, C.c_uint32, C.c_int64, C.c_int64, _P, _P, _P,
+                                       _P, C.c_uint32, C.c_int64, C.c_float] + [_P] * 8 + [C.POINTER(C.c_uint64)]
+    rc = lib.hbtref_frame_query(_np(rows), n, S, _np(isd), frame_len, interval_us, t_last_ns, _np(qs), _np(qe),
+                                _np(ps), _np(pe), Q, period_ns, percentage, _np(ranges), _np(ok),
+                                _np(out["diff"]), _np(out["rate_f64"]), _np(out["rate_i64"]), _np(out["avg_f64"]),
+                                _np(out["avg_i64"]), _np(out["pct"]), C.byref(length))
+    assert rc == 0, rc
+    rl = [tuple(int(x) for x in ranges[i]) if ok[i] else None for i in range(Q)]
+    return int(length.value), rl, out
+
+
+def _trunc_div(a: int, b: int) -> int:
+    """C++ integer division (truncates toward zero)."""
+    q = abs(a) // abs(b)
+    return q if (a < 0) == (b < 0) else -q
+
+
+def _wrap64(x: int) -> int:
+    x &= (1 << 64) - 1
+    return x - (1 << 64) if x >= (1 << 63) else x
+
+
+def port_frame_range(n_samples, last_time_ns, interval_us, t_start, t_end, pol_s, pol_e):
+    """MetricFrameTsUnitFixInterval::getRange / findMatchingOffset (MetricFrameTsUnit.cpp:49-132)."""
+    import math
+
+    def match(t, pol):
+        if n_samples == 0:
+            return None
+        off = (n_samples - 1) + float(_trunc_div(t - last_time_ns, 1000)) / float(interval_us)
+        top = n_samples - 1
+        if pol == hbt.MATCH_CLOSEST:
+            o = 0 if off < 0 else top if off > top else int(math.floor(abs(off) + 0.5) * (1 if off >= 0 else -1))
+        elif pol == hbt.MATCH_PREV_CLOSEST:
+            if off < 0:
+                return None
+            o = top if off > top else int(math.floor(off))
+        else:
+            if off > top:
+                return None
+            o = 0 if off < 0 else int(math.ceil(off))
+        return o, last_time_ns - (n_samples - o - 1) * interval_us * 1000
+    a, b = match(t_start, pol_s), match(t_end, pol_e)
+    if a is None or b is None:
+        return None
+    return (a[0], b[0], a[1], b[1])
+
+
+def port_frame_query(rows, is_double, frame_len, interval_us, t_last_ns, queries, period_ns, percentage):
+    """Restatement of MetricFrameVector::addSamples (MetricFrame.cpp:82-95), MetricSeries::addSample
+    (MetricSeries.h:148-158: the ring keeps the last frame_len samples) and MetricSeriesSlice's
+    diff / rate / avg / percentile (MetricFrameBase.h:66-91, MetricSeries.h:189-249)."""
+    import struct
+    rows = np.ascontiguousarray(rows).view(np.uint64)
+    n, S = rows.shape
+    held = rows[max(0, n - frame_len):]
+    length = len(held)
+    Q = len(queries)
+    out = dict(diff=np.zeros((Q, S), np.uint64), rate_f64=np.zeros((Q, S), np.float64),
+               rate_i64=np.zeros((Q, S), np.int64), avg_f64=np.zeros((Q, S), np.float64),
+               avg_i64=np.zeros((Q, S), np.int64), pct=np.zeros((Q, S), np.uint64))
+    ranges = []
+    f32 = np.float32
+    for q, (t0, t1, p0, p1) in enumerate(queries):
+        r = port_frame_range(length, t_last_ns, interval_us, t0, t1, p0, p1)
+        if r is not None and r[1] < r[0]:
+            r = None
+        ranges.append(r)
+        if r is None:
+            continue
+        b, e = r[0], r[1] + 1
+        duration = r[3] - r[2]
+        cnt = e - b
+        # lround(float(percentage) * float(n - 1)): round half away from zero, in float
+        prod = float(f32(percentage) * f32(cnt - 1))
+        nth = int(np.floor(prod + 0.5))
+        for s in range(S):
+            col = held[b:e, s]
+            if is_double[s]:
+                v = col.view(np.float64)
+                d = float(v[-1] - v[0])
+                out["diff"][q, s] = struct.unpack("<Q", struct.pack("<d", d))[0]
+                with np.errstate(divide="ignore", invalid="ignore"):
+                    out["rate_f64"][q, s] = np.float64(d) * np.float64(period_ns // 1000) / np.float64(_trunc_div(duration, 1000))
+                if duration == 0:
+                    ri = 0
+                elif period_ns > duration:
+                    ri = int(d * float(period_ns // duration))
+                else:
+                    ri = int(d / float(duration // period_ns))
+                out["rate_i64"][q, s] = ri
+                acc = 0.0
+                for x in v:
+                    acc = acc + float(x)
+                out["avg_f64"][q, s] = acc / cnt
+                out["pct"][q, s] = np.sort(v)[nth].view(np.uint64)
+            else:
+                v = col.view(np.int64)
+                d = _wrap64(int(v[-1]) - int(v[0]))
+                out["diff"][q, s] = np.uint64(d & ((1 << 64) - 1))
+                with np.errstate(divide="ignore", invalid="ignore"):
+                    out["rate_f64"][q, s] = np.float64(d) * np.float64(period_ns // 1000) / np.float64(_trunc_div(duration, 1000))
+                if duration == 0:
+                    ri = 0
+                elif period_ns > duration:
+                    ri = _wrap64(d * (period_ns // duration))
+                else:
+                    ri = _trunc_div(d, duration // period_ns)
+                out["rate_i64"][q, s] = ri
+                acc, acci = 0.0, 0
+                for x in v:
+                    acc = acc + float(int(x))
+                    acci = _wrap64(acci + int(x))
+                out["avg_f64"][q, s] = acc / cnt
+                out["avg_i64"][q, s] = _trunc_div(acci, cnt)
+                out["pct"][q, s] = np.sort(v)[nth].view(np.uint64)
+    return length, ranges, out
+
+
+def frame_query(rows, is_double, frame_len, interval_us, t_last_ns, queries, period_ns, percentage):
+    """Oracle for the metric-table tests: the reference's own classes when oracle/_ref is present
+    (the restatement is then cross-checked against them), else the restatement."""
+    p = port_frame_query(rows, is_double, frame_len, interval_us, t_last_ns, queries, period_ns, percentage)
+    if not have_ref():
+        return p
+    r = ref_frame_query(rows, is_double, frame_len, interval_us, t_last_ns, queries, period_ns, percentage)
+    assert r[0] == p[0] and r[1] == p[1], ("oracle port != reference (length / ranges)", r[:2], p[:2])
+    live = np.array([x is not None for x in r[1]], dtype=bool)
+    for k in r[2]:
+        a, b = r[2][k][live], p[2][k][live]
+        assert np.array_equal(a.view(np.uint64), b.view(np.uint64)), ("oracle port != reference", k)
+    return r
