@@ -81,6 +81,12 @@ class FrameRange(C.Structure):
 FRAME_RANGE_DTYPE = np.dtype([("start_offset", "<u8"), ("end_offset", "<u8"),
                               ("start_time_ns", "<i8"), ("end_time_ns", "<i8")])
 MATCH_CLOSEST, MATCH_PREV_CLOSEST, MATCH_NEXT_CLOSEST = 0, 1, 2
+# tagstack::slice::Slice (Slicer.h:30-84) and mon::SliceFreq (MonData.h:30-48)
+SLICE_DTYPE = np.dtype([("tstamp", "<u8"), ("duration", "<u8"), ("stack_id", "<u8"), ("swin_type", "u1"),
+                        ("swout_type", "u1"), ("pad_", "u1", (6,))])
+SLICE_FREQ_DTYPE = np.dtype([("stack_id", "<u8"), ("duration", "<u8"), ("num_obs", "<u8"), ("num_intervals", "<u8")])
+assert SLICE_DTYPE.itemsize == 32
+TT_NA, TT_ANALYSIS, TT_THREAD_PREEMPTED, TT_THREAD_YIELD, TT_PHASE_CHANGE = range(5)
 FRAME_MAX_LEN = 8192
 
 
@@ -165,6 +171,16 @@ EXPORTS = [
     ("hbt_frame_get_range", C.c_int, [_P, C.c_int64, C.c_int64, C.c_int, C.c_int, C.POINTER(FrameRange)]),
     ("hbt_frame_query", C.c_int,
      [_P, _P, C.c_uint32, C.c_int64, C.c_float, _P, _P, _P, _P, _P, _P]),
+    ("hbt_slice_stats_create", C.c_int, [_P, C.POINTER(_P), C.c_uint64]),
+    ("hbt_slice_stats_destroy", None, [_P]),
+    ("hbt_slice_stats_clear", C.c_int, [_P]),
+    ("hbt_slices_join_dev", C.c_int64,
+     [_P, _P, C.c_uint64, C.c_uint64, _P, C.c_uint32, C.c_uint64, C.c_int, C.c_int, _P, C.c_uint64, _P, _U64P]),
+    ("hbt_slice_stats_add_unit_dev", C.c_int, [_P, _P, _P, C.c_uint64, C.c_uint64]),
+    ("hbt_slice_stats_fetch", C.c_int64, [_P, _P, C.c_uint64]),
+    ("hbt_slice_bins_prepare", C.c_int64, [_P, C.c_uint64, C.c_uint64, C.c_uint64, _P, _P, C.c_uint64]),
+    ("hbt_slice_bins_add_unit_dev", C.c_int, [_P, _P, _P, C.c_uint64]),
+    ("hbt_slice_bins_fetch", C.c_int, [_P, _P, C.c_uint64]),
     ("hbt_comm_unique_id", C.c_int, [_P]),
     ("hbt_comm_init", C.c_int, [_P, _P, C.c_int, C.c_int]),
     ("hbt_comm_attach", C.c_int, [_P, _P, C.c_int, C.c_int]),
@@ -585,6 +601,61 @@ class Frame:
                                                   _ptr(out["rate_f64"]), _ptr(out["rate_i64"]),
                                                   _ptr(out["avg_f64"]), _ptr(out["avg_i64"]), _ptr(out["pct"])))
         return out
+
+
+class SliceStats:
+    """hbt_slice_stats: the interval join, slice frequencies and bin matrix on the device of `ctx`."""
+
+    def __init__(self, ctx: "Context", max_stack_ids: int):
+        self.ctx = ctx
+        h = C.c_void_p()
+        ctx._ck(ctx.lib.hbt_slice_stats_create(ctx.h, C.byref(h), max_stack_ids))
+        self.h = h
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.ctx.lib.hbt_slice_stats_destroy(self.h)
+            self.h = None
+
+    def clear(self):
+        self.ctx._ck(self.ctx.lib.hbt_slice_stats_clear(self.h))
+
+    def join_dev(self, slices, n_slices, offset, intervals, stride_words, n_intervals, trim, abort_on_missing,
+                 out, cap, out_offsets):
+        """All device tensors/pointers; returns (slices written, new consumer mark)."""
+        mark = C.c_uint64()
+        n = self.ctx._ck(self.ctx.lib.hbt_slices_join_dev(self.h, _ptr(slices), n_slices, offset, _ptr(intervals),
+                                                          stride_words, n_intervals, int(trim), int(abort_on_missing),
+                                                          _ptr(out), cap, _ptr(out_offsets), C.byref(mark)))
+        return int(n), int(mark.value)
+
+    def add_unit_dev(self, pi_slices, offsets, n_intervals, n_slices):
+        self.ctx._ck(self.ctx.lib.hbt_slice_stats_add_unit_dev(self.h, _ptr(pi_slices), _ptr(offsets), n_intervals,
+                                                               n_slices))
+
+    def fetch(self) -> np.ndarray:
+        n = self.ctx._ck(self.ctx.lib.hbt_slice_stats_fetch(self.h, None, 0))
+        out = np.zeros(max(1, n), dtype=SLICE_FREQ_DTYPE)
+        m = self.ctx._ck(self.ctx.lib.hbt_slice_stats_fetch(self.h, _ptr(out), out.shape[0]))
+        return out[:m]
+
+    def bins_prepare(self, min_distinct_intervals, min_duration, n_rows):
+        """-> (n_bins, stack ids ascending, their bins)."""
+        n = self.ctx._ck(self.ctx.lib.hbt_slice_stats_fetch(self.h, None, 0))
+        sids = np.zeros(max(1, n), dtype=np.uint64)
+        bids = np.zeros(max(1, n), dtype=np.uint32)
+        nb = self.ctx._ck(self.ctx.lib.hbt_slice_bins_prepare(self.h, min_distinct_intervals, min_duration, n_rows,
+                                                              _ptr(sids), _ptr(bids), sids.shape[0]))
+        self.n_rows, self.n_bins = n_rows, int(nb)
+        return int(nb), sids[:n], bids[:n]
+
+    def bins_add_unit_dev(self, pi_slices, offsets, n_intervals):
+        self.ctx._ck(self.ctx.lib.hbt_slice_bins_add_unit_dev(self.h, _ptr(pi_slices), _ptr(offsets), n_intervals))
+
+    def bins_fetch(self) -> np.ndarray:
+        m = np.zeros((self.n_rows, self.n_bins), dtype=np.uint64)
+        self.ctx._ck(self.ctx.lib.hbt_slice_bins_fetch(self.h, _ptr(m), m.size))
+        return m
 
 
 def metric_table():

@@ -541,6 +541,88 @@ int hbt_frame_query(hbt_frame* frame, const hbt_frame_range* ranges, uint32_t n_
                     int64_t* rate_i64, double* avg_f64, int64_t* avg_i64, uint64_t* pct);
 
 /* ------------------------------------------------------------------------ */
+/* Slices: the interval join, per-stack-id frequencies and the interval x bin
+ * duration matrix downstream of the decode (tagstack::IntervalSlicer,
+ * hbt/src/tagstack/IntervalSlicer.cpp:52-216; mon::CuMonData::stackIdFreqs,
+ * MonData::stackIdFreqs, hbt/src/mon/MonData.h:30-48,243-268,386-403;
+ * binmap::TagStackIdBinner, :425-612).                                       */
+/* ------------------------------------------------------------------------ */
+
+/* tagstack::slice::Slice (hbt/src/tagstack/Slicer.h:30-84), same 32-byte layout. */
+typedef struct hbt_slice {
+  uint64_t tstamp;
+  uint64_t duration;
+  uint64_t stack_id;     /* TagStackId; UINT64_MAX = kInvalidTagStackId */
+  uint8_t swin_type;     /* Slice::TransitionType: 0 NA, 1 Analysis, 2 ThreadPreempted, 3 ThreadYield, 4 PhaseChange */
+  uint8_t swout_type;
+  uint8_t pad_[6];
+} hbt_slice;
+
+/* mon::SliceFreq of one stack id (MonData.h:30-48). */
+typedef struct hbt_slice_freq {
+  uint64_t stack_id;
+  uint64_t duration;       /* total duration */
+  uint64_t num_obs;        /* times the slice appears */
+  uint64_t num_intervals;  /* distinct intervals it appears in */
+} hbt_slice_freq;
+
+typedef struct hbt_slice_stats hbt_slice_stats;
+
+/* Frequency table for up to max_stack_ids distinct stack ids on ctx's device
+ * (-ENOSPC later if there are more).  Destroy it before its ctx. */
+int hbt_slice_stats_create(hbt_ctx* ctx, hbt_slice_stats** out, uint64_t max_stack_ids);
+void hbt_slice_stats_destroy(hbt_slice_stats* st);
+int hbt_slice_stats_clear(hbt_slice_stats* st);
+
+/* IntervalSlicer::consumeSlices for n_intervals intervals in one pass: for every
+ * interval [tstamp, tstamp + duration) the slices makeIntervalIntersectingSlices
+ * returns (trimmed copies of the boundary slices with TransitionType::Analysis when
+ * `trim`; an empty list where the reference returns nullptr: nothing intersects,
+ * or, with abort_on_missing_slices, the slices do not cover the interval without a
+ * hole).  slices: DEVICE array of one compute unit's slices in time order (as a
+ * Slicer writes them); offset = the consumer mark (slices already consumed).
+ * intervals: DEVICE words, interval k = {tstamp, duration} at
+ * intervals + k * interval_stride_words -- the packed delta rows of
+ * hbt_rows_packed_dev qualify as they are (stride 2 + n_events), which is how the
+ * reference's TraceCollector pairs count intervals with slices.  Intervals must be
+ * in increasing time order.  out: DEVICE array of cap slices; out_offsets: DEVICE
+ * array of n_intervals + 1 entries (interval k's slices are out[offsets[k] ..
+ * offsets[k+1])).  *new_offset: the mark after the last interval that consumed
+ * slices.  Returns the number of slices written, -ENOSPC if cap is too small,
+ * -EINVAL for an interval of zero duration (HBT_ARG_CHECK_GT, :64) and -EDOM where
+ * the reference throws because an interval's slices are longer than the interval
+ * (:179-181; only possible without trimming). */
+int64_t hbt_slices_join_dev(hbt_slice_stats* st, const hbt_slice* slices, uint64_t n_slices,
+                            uint64_t offset, const uint64_t* intervals,
+                            uint32_t interval_stride_words, uint64_t n_intervals, int trim,
+                            int abort_on_missing_slices, hbt_slice* out, uint64_t cap,
+                            uint64_t* out_offsets, uint64_t* new_offset);
+
+/* CuMonData::stackIdFreqs of one compute unit's per-interval slices (the output of
+ * the join), accumulated into the table like MonData::stackIdFreqs accumulates the
+ * units (SliceFreq::accum): call once per compute unit. */
+int hbt_slice_stats_add_unit_dev(hbt_slice_stats* st, const hbt_slice* pi_slices,
+                                 const uint64_t* offsets, uint64_t n_intervals, uint64_t n_slices);
+/* The accumulated frequencies in ascending stack-id order; out = NULL returns the count. */
+int64_t hbt_slice_stats_fetch(hbt_slice_stats* st, hbt_slice_freq* out, uint64_t cap);
+
+/* TagStackIdBinner (MonData.h:517-612).  prepare: every stack id of the table that
+ * appears in >= min_distinct_intervals intervals with >= min_duration total gets a
+ * bin of its own, the others share bin 0 (ignored_bid), and a zeroed n_rows x n_bins
+ * matrix is made; returns n_bins and, if given, the stack ids (ascending) with their
+ * bins.  Bins are numbered in ascending stack-id order (the reference numbers them
+ * in the iteration order of an unordered_map, which is unspecified).  add_unit: one
+ * compute unit's per-interval slices add their durations to matrix[row][bin], row =
+ * rank of the interval among that unit's intervals with a non-zero total duration
+ * (:563-606).  fetch: the matrix, row-major. */
+int64_t hbt_slice_bins_prepare(hbt_slice_stats* st, uint64_t min_distinct_intervals,
+                               uint64_t min_duration, uint64_t n_rows, uint64_t* stack_ids,
+                               uint32_t* bids, uint64_t cap);
+int hbt_slice_bins_add_unit_dev(hbt_slice_stats* st, const hbt_slice* pi_slices,
+                                const uint64_t* offsets, uint64_t n_intervals);
+int hbt_slice_bins_fetch(hbt_slice_stats* st, uint64_t* matrix, uint64_t cap_cells);
+
+/* ------------------------------------------------------------------------ */
 /* Multi-GPU merge (one process per GPU; the ranks of a box shard the CPUs).
  * The reference has no counterpart: it is a single host process.  What the
  * ranks exchange follows from its order of operations: PerCpuBase::read sums the

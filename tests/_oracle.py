@@ -632,3 +632,127 @@ def frame_query(rows, is_double, frame_len, interval_us, t_last_ns, queries, per
         a, b = r[2][k][live], p[2][k][live]
         assert np.array_equal(a.view(np.uint64), b.view(np.uint64)), ("oracle port != reference", k)
     return r
+
+
+# ---------------------------------------------------------------------------
+# Slices.  hbt/src/tagstack needs Boost.Intrusive and hbt/src/mon/MonData.h
+# the absent hbt/src/phase, so the reference's own code does not compile here: the checker is a
+# plain-Python restatement, pinned to the reference's IntervalSlicerTest.cpp known answers
+# (tests/test_slices.py) for the join; the frequencies and the bin matrix have no reference test.
+# ---------------------------------------------------------------------------
+class ReferenceThrows(Exception):
+    """The reference throws on this input (HBT_THROW_ASSERT*)."""
+
+
+def port_interval_slices(slices, offset, tstamp, duration, trim, abort_on_missing):
+    """IntervalSlicer::makeIntervalIntersectingSlices (IntervalSlicer.cpp:52-188) over a list of
+    (tstamp, duration, stack_id, swin, swout) tuples; returns (slices or None, num_consumed)."""
+    assert duration > 0
+    t_end = tstamp + duration
+    it = iter(range(offset, len(slices)))
+    i = next(it, None)
+    consumed = 0
+    while i is not None and slices[i][0] + slices[i][1] < tstamp:   # :79-84
+        i = next(it, None)
+        consumed += 1
+    if i is None:
+        return None, 0
+    if abort_on_missing and slices[i][0] > tstamp:
+        return None, 0
+    total = 0
+    last_end = slices[i][0]
+    part = []
+    while i is not None and slices[i][0] < t_end:                    # :104-123
+        s = slices[i]
+        if abort_on_missing and last_end != s[0]:
+            return None, 0
+        if not trim and s[0] + s[1] > t_end:
+            break
+        total += s[1]
+        part.append(list(s))
+        last_end = s[0] + s[1]
+        i = next(it, None)
+        consumed += 1
+    if not part:
+        return None, 0
+    last_slice_end = part[-1][0] + part[-1][1]
+    if abort_on_missing and last_slice_end < t_end:
+        return None, 0
+    if trim:                                                         # :147-161
+        f = part[0]
+        if f[0] < tstamp:
+            overlap = f[0] + f[1] - tstamp
+            total -= f[1] - overlap
+            f[1] = overlap
+            f[0] = tstamp
+            f[3] = hbt.TT_ANALYSIS
+    if last_slice_end > t_end:
+        consumed -= 1
+    if trim and last_slice_end > t_end:
+        delta = last_slice_end - t_end
+        part[-1][1] -= delta
+        part[-1][4] = hbt.TT_ANALYSIS
+        total -= delta
+    if total > duration:   # HBT_THROW_ASSERT_IF(slices_duration > duration) (:179-181)
+        raise ReferenceThrows("slices_duration > duration")
+    return [tuple(x) for x in part], consumed
+
+
+def port_consume_slices(slices, intervals, trim, abort_on_missing, offset=0):
+    """consumeSlices (:196-216) once per interval with the consumer mark carried along."""
+    out = []
+    for (t, d) in intervals:
+        part, n = port_interval_slices(slices, offset, t, d, trim, abort_on_missing)
+        out.append(part or [])
+        offset += n
+    return out, offset
+
+
+def port_stack_id_freqs(per_interval_slices):
+    """CuMonData::stackIdFreqs (MonData.h:245-266): {stack_id: [duration, num_obs, num_intervals]}."""
+    freqs = {}
+    for sl in per_interval_slices:
+        seen = set()
+        for s in sl:
+            f = freqs.setdefault(s[2], [0, 0, 0])
+            f[1] += 1
+            f[0] = (f[0] + s[1]) & ((1 << 64) - 1)
+            if s[2] not in seen:
+                f[2] += 1
+                seen.add(s[2])
+    return freqs
+
+
+def port_accum_freqs(per_unit_freqs):
+    """MonData::stackIdFreqs (:386-403) with SliceFreq::accum (:41-45)."""
+    tot = {}
+    for fs in per_unit_freqs:
+        for sid, f in fs.items():
+            t = tot.setdefault(sid, [0, 0, 0])
+            for i in range(3):
+                t[i] = (t[i] + f[i]) & ((1 << 64) - 1)
+    return tot
+
+
+def port_bin_matrix(per_unit_pis, freqs, min_distinct_intervals, min_duration, n_rows):
+    """TagStackIdBinner (MonData.h:517-606) -> {stack_id: column of durations per row}; ignored stack
+    ids share the column keyed None.  (Columns are keyed by stack id because the reference's bin
+    numbering follows an unordered_map's iteration order.)"""
+    keep = {sid for sid, f in freqs.items() if f[2] >= min_distinct_intervals and f[0] >= min_duration}
+    cols = {sid: [0] * n_rows for sid in keep}
+    cols[None] = [0] * n_rows
+    for pis in per_unit_pis:
+        i = 0
+        for sl in pis:
+            if not sl:
+                continue
+            row_dur = 0
+            for s in sl:
+                if s[1] == 0:
+                    continue
+                row_dur += s[1]
+                col = cols[s[2]] if s[2] in keep else cols[None]
+                col[i] = (col[i] + s[1]) & ((1 << 64) - 1)
+            if row_dur:
+                i += 1
+    return cols
