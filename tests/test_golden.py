@@ -12,7 +12,7 @@ import _oracle as orc
 
 GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
 DECODE_CASES = sorted(os.path.basename(p)[:-4] for p in glob.glob(os.path.join(GOLDEN, "*.npz"))
-                      if not os.path.basename(p).startswith(("counts_", "switch_")))
+                      if not os.path.basename(p).startswith(("counts_", "switch_", "metric_")))
 COUNTS_CASES = ["counts_mux", "counts_c1_shape"]
 SWITCH_CASES = ["switch_events_lost", "switch_events_plain"]
 
