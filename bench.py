@@ -196,6 +196,27 @@ def make_group_rings(n_cpus: int, ring_bytes: int, cpu_base: int, device, n_even
     return imgs, tails, heads, total
 
 
+def make_hostile_rings(n_cpus: int, ring_bytes: int, cpu_base: int, device, n_events: int):
+    """Group SAMPLE rings whose counter VALUES are valid-looking perf_event_headers (a SAMPLE header
+    of the stream's own size in value[2], a LOST header in value[4]): chains of fake records that even
+    validate, so segment-entry guesses that land on them go wrong and have to be caught and re-run."""
+    imgs = torch.empty((n_cpus, ring_bytes // 8), dtype=torch.int64, device=device)
+    tails, heads = [], []
+    W = 5 + n_events
+    n = (ring_bytes - 65536) // (8 * W)
+    for c in range(n_cpus):
+        seed = tg.stream_seed(7, cpu_base + c)
+        s = tg.group_sample_stream(seed, n, n_events, device=device)
+        s[7::W] = tg.header(tg.REC_SAMPLE, 8 * W)
+        s[9::W] = tg.header(tg.REC_LOST, 24)
+        tail = tg.random_tail(seed, ring_bytes)
+        ring, head = tg.place_in_ring(s, ring_bytes, tail, fill_seed=0)
+        imgs[c] = ring
+        tails.append(tail)
+        heads.append(head)
+    return imgs, tails, heads, n * n_cpus
+
+
 def make_mixed_rings(n_cpus: int, ring_bytes: int, cpu_base: int, device, n_events: int):
     """Rings of the mixed stream of config 4 (SAMPLE 70 % / SWITCH_CPU_WIDE 15 % / COMM / MMAP /
     LOST / FORK / EXIT, 24-320 B records)."""
@@ -306,6 +327,7 @@ def bench_deltas(args, rank, world, local, dev, dist):
     ring_bytes = args.ring_mib << 20
     mixed = args.workload == "c4_mixed"
     switch = args.workload == "c4_switch"
+    hostile = args.workload == "c3_hostile"
     # --shard: args.cpus is the whole machine, sharded by CPU id over the ranks (config 4:
     # "sharded by CPU across 8 B200"); else every rank holds args.cpus rings of its own
     shard = bool(getattr(args, "shard", False)) and world > 1
@@ -315,6 +337,8 @@ def bench_deltas(args, rank, world, local, dev, dist):
         imgs, tails, heads, n_rec = make_switch_rings(cpus, ring_bytes, rank * cpus, dev)
     elif mixed:
         imgs, tails, heads, n_rec = make_mixed_rings(cpus, ring_bytes, rank * cpus, dev, E)
+    elif hostile:
+        imgs, tails, heads, n_rec = make_hostile_rings(cpus, ring_bytes, rank * cpus, dev, E)
     else:
         imgs, tails, heads, n_rec = make_group_rings(cpus, ring_bytes, rank * cpus, dev, E)
     window_bytes = sum(h - t for t, h in zip(tails, heads))
@@ -405,6 +429,10 @@ def bench_deltas(args, rank, world, local, dev, dist):
                              "peak_source": peak_src},
                 "gpu_launches": int(launches), "clocks": clocks,
                 **({"cpu_baseline": sw_cb} if sw_cb else {})}
+    if ctx.reruns:
+        # the kernel timer brackets the LAST decode launch only; with re-runs the step is several
+        # launches and host round trips: the whole device-timed step is the span
+        k_ms = ms_step
     ach = algo / (k_ms * 1e-3) / 1e9
     cb = None
     if world == 1 and not args.no_cpu_baseline and not mixed and not switch and args.agg != "none":
@@ -418,11 +446,13 @@ def bench_deltas(args, rank, world, local, dev, dist):
             "data": "synthetic",
             "config": {"workload": (f"c4_mixed: SAMPLE/SWITCH/COMM/MMAP/LOST/FORK/EXIT stream, per-type counters "
                                     f"+ per-interval deltas ({E} events)") if mixed else
+                                   (f"c3_hostile: group SAMPLE ({40 + 8 * E} B) whose counter values are valid-looking record "
+                                    "headers (wrong entry guesses are caught and re-run), per-interval deltas") if hostile else
                                    f"c3_deltas: group SAMPLE ({40 + 8 * E} B, {E} events) decode + per-interval deltas",
                        "cpus_per_gpu": cpus, "ring_mib": args.ring_mib, "records_per_gpu": n_rec,
                        "rows_per_gpu": n_rows, "window_bytes_per_gpu": int(window_bytes),
                        "l2": "inputs exceed L2; no flush needed", "slow_tiles": ctx.slow_tiles,
-                       "reruns": ctx.reruns},
+                       "reruns": ctx.reruns, "rerun_segments": ctx.rerun_segments},
             "roofline": {"bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
                          "traffic": (load_traffic(f"k_decode<COUNT_DELTAS>@{E}ev") if not mixed else None),
                          "kernel": "k_decode<COUNT_DELTAS>",
@@ -811,6 +841,8 @@ def run_diagnostics(args, rank, world, local, dev, dist):
                  ("c3_deltas_8ev", bench_deltas, variant(workload="c3_deltas", events=8, agg="hist", no_cpu_baseline=True, no_e2e=True)),
                  ("c4_mixed", bench_deltas, variant(workload="c4_mixed", events=8, agg="hist", no_e2e=True)),
                  ("c4_switch", bench_deltas, variant(workload="c4_switch", agg="hist")),
+                 ("c3_hostile_payload", bench_deltas, variant(workload="c3_hostile", events=8, agg="hist",
+                                                              no_cpu_baseline=True, no_e2e=True)),
                  ("c2_count_only", bench_c2_variant, variant(c2_agg="none", c2_words=5)),
                  ("c2_ip_hist_128B_samples", bench_c2_variant, variant(c2_agg="hist", c2_words=16)),
                  ("c5_counts_512x1", bench_counts, variant(workload="c5_counts", cpus=512, events=1, intervals=1_000_000)),
@@ -837,7 +869,7 @@ def run_diagnostics(args, rank, world, local, dev, dist):
                                      "collective", "gpu_launches", "error", "e2e") if k in line}
         if "config" in line:
             keep["workload"] = line["config"].get("workload")
-            for k in ("cpus_per_gpu", "slow_tiles", "reruns", "merge_ms", "l2"):
+            for k in ("cpus_per_gpu", "slow_tiles", "reruns", "rerun_segments", "merge_ms", "l2"):
                 if k in line["config"]:
                     keep[k] = line["config"][k]
         if "roofline" in line:
@@ -918,7 +950,7 @@ def main():
                     help="list capacity per CPU: distinct keys + the samples of one decode")
     ap.add_argument("--agg", default="hist", choices=["hist", "none"],
                     help="none: decode + counters only (diagnostic, not the headline workload)")
-    ap.add_argument("--workload", default="c2_ip_hist", choices=["c2_ip_hist", "c3_deltas", "c4_mixed", "c4_switch", "c5_counts"],
+    ap.add_argument("--workload", default="c2_ip_hist", choices=["c2_ip_hist", "c3_deltas", "c3_hostile", "c4_mixed", "c4_switch", "c5_counts"],
                     help="c2_ip_hist is the headline (BASELINE configs[1]); the others are diagnostics")
     ap.add_argument("--events", type=int, default=8)
     ap.add_argument("--intervals", type=int, default=100000)

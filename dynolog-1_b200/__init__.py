@@ -130,6 +130,7 @@ EXPORTS = [
     ("hbt_decode", C.c_int, [_P, C.POINTER(DecodeDesc)]),
     ("hbt_fetch_results", C.c_int, [_P, _P, C.c_uint32]),
     ("hbt_decode_reruns", C.c_uint32, [_P]),
+    ("hbt_decode_rerun_segments", C.c_uint64, [_P]),
     ("hbt_decode_slow_tiles", C.c_uint64, [_P]),
     ("hbt_decode_kernel_ms", C.c_float, [_P]),
     ("hbt_hist_fold_kernel_ms", C.c_float, [_P]),
@@ -362,6 +363,10 @@ class Context:
     @property
     def reruns(self) -> int:
         return int(self.lib.hbt_decode_reruns(self.h))
+
+    @property
+    def rerun_segments(self) -> int:
+        return int(self.lib.hbt_decode_rerun_segments(self.h))
 
     @property
     def decode_kernel_ms(self) -> float:

@@ -129,6 +129,8 @@ struct DecodeParams {
   hbt_decode_desc d;
   HistLists hist;
   uint32_t cpu_base;  // SWITCH_EVENTS: comp_unit_id = cpu_base + cpu
+  // a re-run decodes only the segments listed here (null: CTA i decodes segment i)
+  const uint32_t* run_list;
 };
 
 // ---------------------------------------------------------------------------
@@ -405,6 +407,10 @@ __device__ void consume_sequential(const DecodeParams& p, const RingDesc& ring,
                                    const SegDesc& seg, SegState& st, uint64_t limit) {
   const hbt_decode_desc& d = p.d;
   uint64_t pos = st.pos;
+  // record sizes seen by this walk: a tile of one record size re-arms the stride prediction, so one
+  // tile the guesses could not handle does not send the rest of its segment down this path as well
+  st.size_min = kNoRel;
+  st.size_max = 0;
   while (pos < limit) {
     const uint64_t h = ring_word_g(ring, pos);
     const uint32_t type = hdr_type(h), size = hdr_size(h);
@@ -413,6 +419,8 @@ __device__ void consume_sequential(const DecodeParams& p, const RingDesc& ring,
       st.err_pos = pos;
       break;
     }
+    st.size_min = min(st.size_min, size);
+    st.size_max = max(st.size_max, size);
     if (st.entry == kNone) st.entry = pos;
     const int ci = counter_of(type, type_mask(d.handled_mask));
     if (type == REC_LOST && ci >= 0) {
@@ -563,7 +571,8 @@ __global__ void __launch_bounds__(kThreads, AGG == HBT_AGG_IP_HISTOGRAM ? HBT_HI
   RowDescs& rowd =
       *reinterpret_cast<RowDescs*>(smem_raw + kStages * kTile + ((sizeof(Smem) + 15) & ~15ull));
 
-  const SegDesc seg = p.segs[blockIdx.x];
+  const uint32_t seg_index = p.run_list ? p.run_list[blockIdx.x] : blockIdx.x;
+  const SegDesc seg = p.segs[seg_index];
   const RingDesc ring = p.rings[seg.cpu];
   const hbt_decode_desc& d = p.d;
   const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -1178,8 +1187,11 @@ __global__ void __launch_bounds__(kThreads, AGG == HBT_AGG_IP_HISTOGRAM ? HBT_HI
           ++st.slow_tiles;
           const uint32_t g = min(st.guess_min[0], st.guess_min[1]);
           if (st.pos == kNone && g != kNoRel) st.pos = t_begin + g;
-          if (st.pos != kNone) consume_sequential<AGG>(p, ring, seg, st, t_begin + lim);
           st.stride = 0;
+          if (st.pos != kNone) {
+            consume_sequential<AGG>(p, ring, seg, st, t_begin + lim);
+            if (st.err == 0 && st.size_min == st.size_max) st.stride = st.size_min;  // exact entry + one size
+          }
         } else {
           // chain bookkeeping for the next tile
           const uint32_t e = erel != kNoRel ? erel : st.guess_min[a];
@@ -1246,7 +1258,7 @@ __global__ void __launch_bounds__(kThreads, AGG == HBT_AGG_IP_HISTOGRAM ? HBT_HI
   }
   __syncthreads();
   if (tid == 0) {
-    SegResult& r = p.results[blockIdx.x];
+    SegResult& r = p.results[seg_index];
     r.entry = st.entry;
     r.exit = st.pos;
     r.n_records = st.n_rec;
@@ -1268,8 +1280,9 @@ __global__ void __launch_bounds__(kThreads, AGG == HBT_AGG_IP_HISTOGRAM ? HBT_HI
 // literal consume() over the whole window.  Same outputs as k_decode.
 template <int AGG>
 __global__ void __launch_bounds__(32) k_decode_small(const DecodeParams p, uint32_t n_segs) {
-  const uint32_t g = blockIdx.x * blockDim.x + threadIdx.x;
-  if (g >= n_segs) return;
+  const uint32_t gt = blockIdx.x * blockDim.x + threadIdx.x;
+  if (gt >= n_segs) return;
+  const uint32_t g = p.run_list ? p.run_list[gt] : gt;
   const SegDesc seg = p.segs[g];
   const RingDesc ring = p.rings[seg.cpu];
   SegState st;
@@ -1323,6 +1336,7 @@ struct FinalizeParams {
   uint64_t* locate_from; // per CPU: record start to count from ...
   uint64_t* locate_skip; // ... and how many records to skip to find the cut
   uint32_t* flags;       // [0] re-run needed
+  uint8_t* cpu_done;     // per CPU: 1 = this decode's results for the CPU are final (a re-run skips it)
   uint32_t n_cpus;
   hbt_decode_desc d;
   int agg;
@@ -1335,6 +1349,7 @@ struct FinalizeParams {
 __global__ void __launch_bounds__(32) k_finalize(const FinalizeParams p) {
   const uint32_t c = blockIdx.x, lane = threadIdx.x;
   if (c >= p.n_cpus) return;
+  if (p.cpu_done[c]) return;  // settled by an earlier attempt of this decode
   __shared__ SegResult s_res[32];
   __shared__ SegDesc s_seg[32];
   const RingDesc ring = p.rings[c];
@@ -1499,6 +1514,7 @@ __global__ void __launch_bounds__(32) k_finalize(const FinalizeParams p) {
   }
   sout.carry_tstamp = cts;
   out.carry_tstamp = cts;
+  p.cpu_done[c] = 1;
 }
 
 // Generator state right after enable(): counters 0, last_[] = 0, count_.tstamp = seed.

@@ -129,6 +129,14 @@ struct hbt_ctx {
   PinBuf<int64_t> h_clamp_ret;
   PinBuf<uint32_t> h_flags;
   uint32_t n_segs = 0;
+  // a re-run decodes only the segments of h_run_list (n_run = 0: every segment) and finalises
+  // only the CPUs that are not settled yet (d_cpu_done)
+  DevBuf<uint32_t> d_run_list;
+  PinBuf<uint32_t> h_run_list;
+  uint32_t n_run = 0;
+  DevBuf<uint8_t> d_cpu_done;
+  PinBuf<uint8_t> h_cpu_done;
+  uint64_t rerun_segments = 0;  // segments decoded again by the re-runs of the last decode
   uint32_t geo_segs_per_cpu = 0, geo_min_tiles = 0;  // hbt_set_geometry; 0 = automatic
   bool tiled = true;
   bool attr_set[4] = {false, false, false, false};
@@ -309,7 +317,8 @@ int build_tables(hbt_ctx* ctx, const uint64_t* clamp_head, const int64_t* clamp_
       s.tile_begin = 0;
       s.tile_end = 0;
       s.forced_entry = kNone;
-      s.rows_cap = (r.head - r.tail) / (sw ? 32 : 40 + 8ull * d.n_events) + 2;
+      // (from the TRUE window, like the tiled geometry: a clamped re-run keeps every slab in place)
+      s.rows_cap = (w.head - r.tail) / (sw ? 32 : 40 + 8ull * d.n_events) + 2;
       segs.push_back(s);
       r.n_seg = 1;
     } else {
@@ -363,6 +372,8 @@ int build_tables(hbt_ctx* ctx, const uint64_t* clamp_head, const int64_t* clamp_
   CU(ctx->d_seam.reserve(ns));
   CU(ctx->d_forced.reserve(ns));
   CU(ctx->h_seam.reserve(ns));
+  CU(ctx->d_run_list.reserve(ns));
+  CU(ctx->h_run_list.reserve(ns));
   if (!segs.empty()) memcpy(ctx->h_segs.p, segs.data(), segs.size() * sizeof(SegDesc));
   return 0;  // k_prepare (run_once) moves the tables to the device
 }
@@ -378,6 +389,8 @@ struct PrepareParams {
   uint64_t* clamp_head; uint32_t n_cpus;
   uint64_t* forced; uint32_t n_forced;
   const uint32_t* cursors; uint32_t* cursors_snap; uint32_t n_lists;  // n_lists = 0: no snapshot
+  const uint32_t* src_run; uint32_t* dst_run; uint32_t n_run;
+  uint8_t* cpu_done; uint32_t n_done_reset;  // first attempt: every CPU is open again
 };
 
 static __global__ void k_prepare(PrepareParams p) {
@@ -388,6 +401,8 @@ static __global__ void k_prepare(PrepareParams p) {
   for (uint32_t i = t0; i < p.n_cpus; i += stride) p.clamp_head[i] = ~0ull;
   for (uint32_t i = t0; i < p.n_forced; i += stride) p.forced[i] = ~0ull;
   for (uint32_t i = t0; i < p.n_lists; i += stride) p.cursors_snap[i] = p.cursors[i];
+  for (uint32_t i = t0; i < p.n_run; i += stride) p.dst_run[i] = p.src_run[i];
+  for (uint32_t i = t0; i < p.n_done_reset; i += stride) p.cpu_done[i] = 0;
   if (t0 < 4) p.flags[t0] = 0;
 }
 
@@ -405,7 +420,9 @@ int launch_decode_agg(hbt_ctx* ctx) {
   p.hist.cap = ctx->hist_cap;
   p.hist.overflow = ctx->hist_overflow.p;
   p.cpu_base = ctx->cpu_base;
+  p.run_list = ctx->n_run ? ctx->d_run_list.p : nullptr;
   if (ctx->n_segs == 0) return 0;
+  const uint32_t n_launch = ctx->n_run ? ctx->n_run : ctx->n_segs;
   if (ctx->tiled) {
     const size_t smem = decode_smem_bytes(AGG);
     if (!ctx->attr_set[AGG]) {
@@ -417,10 +434,10 @@ int launch_decode_agg(hbt_ctx* ctx) {
       ctx->attr_set[AGG] = true;
     }
     CU(cudaEventRecord(ctx->ev_k0, ctx->stream));
-    k_decode<AGG><<<ctx->n_segs, kThreads, smem, ctx->stream>>>(p);
+    k_decode<AGG><<<n_launch, kThreads, smem, ctx->stream>>>(p);
     CU(cudaEventRecord(ctx->ev_k1, ctx->stream));
   } else {
-    k_decode_small<AGG><<<(ctx->n_segs + 31) / 32, 32, 0, ctx->stream>>>(p, ctx->n_segs);
+    k_decode_small<AGG><<<(n_launch + 31) / 32, 32, 0, ctx->stream>>>(p, n_launch);
   }
   ++ctx->launches;
   CU(cudaGetLastError());
@@ -452,6 +469,7 @@ int launch_finalize(hbt_ctx* ctx) {
   f.locate_from = ctx->d_locate_from.p;
   f.locate_skip = ctx->d_locate_skip.p;
   f.flags = ctx->d_flags.p;
+  f.cpu_done = ctx->d_cpu_done.p;
   f.n_cpus = C;
   f.d = ctx->desc;
   f.agg = (int)ctx->desc.aggregate;
@@ -486,6 +504,14 @@ int run_once(hbt_ctx* ctx, bool snapshot_cursors) {
     pp.cursors = ctx->hist_cursors.p;
     pp.cursors_snap = ctx->hist_cursors_snap.p;
     pp.n_lists = (uint32_t)((size_t)ctx->n_cpus * ctx->hist_buckets);
+  }
+  pp.cpu_done = ctx->d_cpu_done.p;
+  pp.n_done_reset = ctx->n_run ? 0 : ctx->n_cpus;  // the first attempt of a decode opens every CPU
+  if (ctx->n_run) {
+    CU(cudaHostGetDevicePointer(&dp, ctx->h_run_list.p, 0));
+    pp.src_run = static_cast<const uint32_t*>(dp);
+    pp.dst_run = ctx->d_run_list.p;
+    pp.n_run = ctx->n_run;
   }
   const uint32_t work = pp.n_seg_words > pp.n_lists ? pp.n_seg_words : pp.n_lists;
   uint32_t grid = (work + 1023) / 1024;
@@ -620,6 +646,10 @@ void hbt_destroy(hbt_ctx* ctx) {
   ctx->d_flags.release();
   ctx->d_rows.release();
   ctx->d_rows_packed.release();
+  ctx->d_run_list.release();
+  ctx->h_run_list.release();
+  ctx->d_cpu_done.release();
+  ctx->h_cpu_done.release();
   ctx->h_slabs.release();
   ctx->h_rings.release();
   ctx->h_segs.release();
@@ -784,6 +814,8 @@ static int configure_common(hbt_ctx* ctx, uint32_t n_cpus) {
   CU(ctx->h_clamp_ret.reserve(n_cpus));
   CU(ctx->d_flags.reserve(4));
   CU(ctx->h_flags.reserve(8));
+  CU(ctx->d_cpu_done.reserve(n_cpus));
+  CU(ctx->h_cpu_done.reserve(n_cpus));
   ctx->cur = 0;
   return hbt_ring_reset_state(ctx, kInvalidTs);
 }
@@ -887,6 +919,8 @@ int hbt_decode(hbt_ctx* ctx, const hbt_decode_desc* desc) {
   }
   rc = build_tables(ctx, nullptr, nullptr, nullptr);
   if (rc) return rc;
+  ctx->n_run = 0;
+  ctx->rerun_segments = 0;
   // histogram: k_prepare also snapshots the lists' cursors, a re-run starts again from there
   rc = run_once(ctx, ctx->desc.aggregate == HBT_AGG_IP_HISTOGRAM);
   if (rc) return rc;
@@ -935,11 +969,7 @@ static int complete_decode(hbt_ctx* ctx) {
     if (ctx->h_flags.p[0] == 0) break;
     if (iter > 4 * kMaxSegsPerCpu + 8) return fail(ctx, -EIO, "decode re-run did not converge");
     ++ctx->reruns;
-    // forget what the failed attempt appended to the histogram lists
-    if (ctx->desc.aggregate == HBT_AGG_IP_HISTOGRAM)
-      CU(cudaMemcpyAsync(ctx->hist_cursors.p, ctx->hist_cursors_snap.p,
-                         hist_lists(ctx) * sizeof(uint32_t), cudaMemcpyDeviceToDevice, ctx->stream));
-    // locate cuts for a finite max_num_records, then fetch clamps + forced entries
+    // locate cuts for a finite max_num_records, then fetch clamps, forced entries and which CPUs are settled
     k_locate<<<(C + 63) / 64, 64, 0, ctx->stream>>>(ctx->d_rings.p, C, ctx->d_clamp_head.p,
                                                    ctx->d_locate_from.p, ctx->d_locate_skip.p);
     ++ctx->launches;
@@ -948,23 +978,48 @@ static int complete_decode(hbt_ctx* ctx) {
                        cudaMemcpyDeviceToHost, ctx->stream));
     CU(cudaMemcpyAsync(ctx->h_clamp_ret.p, ctx->d_clamp_ret.p, C * sizeof(int64_t),
                        cudaMemcpyDeviceToHost, ctx->stream));
+    CU(cudaMemcpyAsync(ctx->h_cpu_done.p, ctx->d_cpu_done.p, C, cudaMemcpyDeviceToHost, ctx->stream));
     std::vector<SegDesc> forced(ctx->h_segs.p, ctx->h_segs.p + ctx->n_segs);
     std::vector<uint64_t> forced_new(ctx->n_segs, kNone);
     if (ctx->n_segs)
       CU(cudaMemcpyAsync(forced_new.data(), ctx->d_forced.p, ctx->n_segs * sizeof(uint64_t),
                          cudaMemcpyDeviceToHost, ctx->stream));
     CU(cudaStreamSynchronize(ctx->stream));
-    for (uint32_t i = 0; i < ctx->n_segs; ++i)
-      if (forced_new[i] != kNone) forced[i].forced_entry = forced_new[i];
+    // Only what the failed attempt got wrong is decoded again.  A CPU whose chain held is settled
+    // (its results stay).  Of an open CPU: a clamped window (max_num_records, a regression at a
+    // seam, an error under the histogram) changes where every segment stops -> all its segments;
+    // the histogram cannot take single segments back out of the shared lists -> all its segments,
+    // after its cursors are put back; otherwise only the segment whose entry guess was wrong --
+    // the other segments' results stand and are chained again.
+    const bool hist = ctx->desc.aggregate == HBT_AGG_IP_HISTOGRAM;
+    uint32_t n_run = 0;
     for (uint32_t c = 0; c < C; ++c) {
+      if (ctx->h_cpu_done.p[c]) continue;
+      const RingDesc& r = ctx->h_rings.p[c];
+      bool whole = hist;
       if (ctx->h_clamp_head.p[c] != kNone) {
         clamp_head[c] = ctx->h_clamp_head.p[c];
         clamp_ret[c] = ctx->h_clamp_ret.p[c];
         have_clamp = true;
+        whole = true;
+      }
+      for (uint32_t k = 0; k < r.n_seg; ++k) {
+        const uint32_t gi = r.seg_begin + k;
+        if (forced_new[gi] != kNone) forced[gi].forced_entry = forced_new[gi];
+        if (whole || forced_new[gi] != kNone) ctx->h_run_list.p[n_run++] = gi;
+      }
+      if (hist && r.n_seg) {
+        // forget what the failed attempt appended to this CPU's lists
+        const size_t l0 = (size_t)c * ctx->hist_buckets;
+        CU(cudaMemcpyAsync(ctx->hist_cursors.p + l0, ctx->hist_cursors_snap.p + l0,
+                           ctx->hist_buckets * sizeof(uint32_t), cudaMemcpyDeviceToDevice, ctx->stream));
       }
     }
+    if (n_run == 0) return fail(ctx, -EIO, "decode asked for a re-run without naming a segment");
     int rc = build_tables(ctx, have_clamp ? clamp_head.data() : nullptr, clamp_ret.data(), &forced);
     if (rc) return rc;
+    ctx->n_run = n_run;
+    ctx->rerun_segments += n_run;
     rc = run_once(ctx, false);
     if (rc) return rc;
   }
@@ -1037,6 +1092,7 @@ int hbt_fetch_results(hbt_ctx* ctx, hbt_cpu_result* out, uint32_t cap) {
 }
 
 uint32_t hbt_decode_reruns(const hbt_ctx* ctx) { return ctx ? ctx->reruns : 0; }
+uint64_t hbt_decode_rerun_segments(const hbt_ctx* ctx) { return ctx ? ctx->rerun_segments : 0; }
 
 float hbt_decode_kernel_ms(hbt_ctx* ctx) {
   if (!ctx || !ctx->tiled) return -1.0f;

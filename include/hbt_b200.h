@@ -316,6 +316,11 @@ int hbt_fetch_results(hbt_ctx* ctx, hbt_cpu_result* out, uint32_t cap);
  * re-run with corrected segment entries / clamped windows, and how many tiles
  * fell back to the one-thread sequential walk.  Both are 0 on well-formed streams. */
 uint32_t hbt_decode_reruns(const hbt_ctx* ctx);
+/* Segments decoded again by those re-runs.  A re-run is restricted to what the first
+ * attempt got wrong: the one segment whose entry guess did not chain (every segment of
+ * the CPU when its window has to be clamped, or under HBT_AGG_IP_HISTOGRAM); the other
+ * CPUs' and segments' results stand. */
+uint64_t hbt_decode_rerun_segments(const hbt_ctx* ctx);
 uint64_t hbt_decode_slow_tiles(hbt_ctx* ctx);
 /* Device time of the last decode kernel launch (CUDA events on the ctx stream
  * around that one launch; waits for it).  Negative when unavailable. */

@@ -435,10 +435,22 @@ def test_payload_that_looks_like_headers(ctx):
     tail = tg.random_tail(77, ds)
     ring, head = ring_np(s, ds, tail, fill=0)
     desc = hbt.sampling_desc(E)
-    res = gpu_decode(ctx, [(ring, tail, head)] * 2, desc, ds)
+    clean = tg.group_sample_stream(6, 4000, E)
+    ring_c, head_c = ring_np(clean, ds, tail)
+    ctx.ring_configure(3, ds)
+    ctx.set_geometry(16, 1)          # many short segments: many entry guesses to get wrong
+    try:
+        res = gpu_decode(ctx, [(ring, tail, head), (ring_c, tail, head_c), (ring, tail, head)], desc, ds, reset=False)
+    finally:
+        ctx.set_geometry(0, 0)
     want = orc.consume(ring, tail, head, desc)
     check_cpu(ctx, 0, res[0], want, desc)
-    check_cpu(ctx, 1, res[1], want, desc)
+    check_cpu(ctx, 1, res[1], orc.consume(ring_c, tail, head_c, desc), desc)
+    check_cpu(ctx, 2, res[2], want, desc)
+    # wrong guesses cost re-runs, but only of the segments that were wrong: never the clean CPU's
+    # (an attempt re-decodes at most one segment per hostile CPU)
+    assert ctx.reruns > 0
+    assert ctx.rerun_segments <= 2 * ctx.reruns
 
 
 def test_unknown_types_and_giant_records(ctx):
