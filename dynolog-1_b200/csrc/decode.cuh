@@ -80,6 +80,12 @@ struct SegDesc {  // one per CTA
   uint64_t tile_begin;   // first tile index (absolute)
   uint64_t tile_end;     // one past the last tile index
   uint64_t forced_entry; // kNone = guess
+  // Where the segment's first record starts IF the stream is one run of equal-sized records from
+  // the window's tail (host arithmetic: tail + k * size); kNone = no such expectation.  Only a
+  // first guess: the tile's headers must agree, and k_finalize still chains entry to exit.
+  uint64_t entry_hint;
+  uint32_t hint_size;    // that record size
+  uint32_t pad_;
   uint64_t* rows;        // slab: slot 0 is the seam row, rows follow
   uint64_t rows_cap;     // rows after the seam slot
 };
@@ -714,8 +720,17 @@ __global__ void __launch_bounds__(kThreads, AGG == HBT_AGG_IP_HISTOGRAM ? HBT_HI
     // Stride prediction: when every record of the previous tile had the same size S
     // the starts of this tile are guessed as entry + k*S (one header check each)
     // instead of scanning for plausible headers.  Still only a guess.
-    const uint32_t S = st.stride;
-    const bool predict = S >= 8 && erel < (uint32_t)kTile;
+    uint32_t S = st.stride;
+    // A segment that has to guess its entry tries the host's expectation first (equal-sized records
+    // all the way from the tail): if every header of the tile agrees, the uniform fast path below
+    // takes it from the first tile on; if not, the scan guesses as before.
+    const bool hinted = entry_abs == kNone && tile_k == 0 && seg.entry_hint != kNone &&
+                        seg.entry_hint >= t_begin && seg.entry_hint - t_begin < (uint64_t)kTile;
+    if (hinted) {
+      erel = (uint32_t)(seg.entry_hint - t_begin);
+      S = seg.hint_size;
+    }
+    bool predict = S >= 8 && erel < (uint32_t)kTile;
     const float rcpS = predict ? __frcp_rn((float)S) : 0.f;
 
     // ---- uniform fast path -------------------------------------------------------
@@ -833,6 +848,7 @@ __global__ void __launch_bounds__(kThreads, AGG == HBT_AGG_IP_HISTOGRAM ? HBT_HI
         }
         if (tid == 0 && n_t > 0) {
           if (st.entry == kNone) st.entry = t_begin + erel;
+          if (hinted) st.stride = S;
           st.pos = t_begin + erel + (uint64_t)n_t * S;
           if (AGG == HBT_AGG_COUNT_DELTAS) {
             const uint64_t last = t_begin + erel + (uint64_t)(n_t - 1) * S;
@@ -844,6 +860,11 @@ __global__ void __launch_bounds__(kThreads, AGG == HBT_AGG_IP_HISTOGRAM ? HBT_HI
       }
     }
 
+    if (hinted && !ufp_done) {  // the expectation did not hold here: guess by scanning
+      erel = kNoRel;
+      S = 0;
+      predict = false;
+    }
     const uint32_t se = min(se_full, lim);
     const bool live = !stopped && !ufp_done && sb < se;
 

@@ -284,6 +284,11 @@ int build_tables(hbt_ctx* ctx, const uint64_t* clamp_head, const int64_t* clamp_
   if (segs_per_cpu > kMaxSegsPerCpu) segs_per_cpu = kMaxSegsPerCpu;
   if (segs_per_cpu < 1) segs_per_cpu = 1;
 
+  // record size when the stream is expected to be one run of equal-sized SAMPLE records (0: none)
+  uint32_t hint_size = 0;
+  if (d.sample_layout == HBT_SAMPLE_IP && (d.handled_mask & HBT_H_SAMPLE)) hint_size = d.ip_sample_bytes;
+  else if (d.aggregate == HBT_AGG_COUNT_DELTAS) hint_size = 40 + 8 * d.n_events;
+  if (hint_size > (uint32_t)kTile / 2) hint_size = 0;
   uint64_t min_tiles_per_seg = 8;
   if (ctx->geo_min_tiles) min_tiles_per_seg = ctx->geo_min_tiles;
   std::vector<SegDesc> segs;
@@ -317,6 +322,7 @@ int build_tables(hbt_ctx* ctx, const uint64_t* clamp_head, const int64_t* clamp_
       s.tile_begin = 0;
       s.tile_end = 0;
       s.forced_entry = kNone;
+      s.entry_hint = kNone;
       // (from the TRUE window, like the tiled geometry: a clamped re-run keeps every slab in place)
       s.rows_cap = (w.head - r.tail) / (sw ? 32 : 40 + 8ull * d.n_events) + 2;
       segs.push_back(s);
@@ -337,6 +343,12 @@ int build_tables(hbt_ctx* ctx, const uint64_t* clamp_head, const int64_t* clamp_
         s.tile_begin = tb;
         s.tile_end = tb + per < t1 ? tb + per : t1;
         s.forced_entry = kNone;
+        s.entry_hint = kNone;
+        if (hint_size && k > 0) {  // first record start at or after the segment's first byte, counted from the tail
+          const uint64_t seg_pos = tb * kTile;
+          s.entry_hint = r.tail + (seg_pos - r.tail + hint_size - 1) / hint_size * hint_size;
+          s.hint_size = hint_size;
+        }
         // rows per segment: a SAMPLE is at least 40 + 8n bytes, a handled ContextSwitch record 32
         s.rows_cap = ((s.tile_end - s.tile_begin) * kTile) / (sw ? 32 : 40 + 8ull * d.n_events) + 2;
         segs.push_back(s);

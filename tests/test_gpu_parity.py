@@ -432,6 +432,10 @@ def test_payload_that_looks_like_headers(ctx):
     fake = tg.header(tg.REC_SAMPLE, 8 * W)  # a value equal to a real SAMPLE header
     s[7::W] = fake                           # value[2] of every sample
     s[9::W] = tg.header(tg.REC_LOST, 24)
+    # a LOST record in front shifts every SAMPLE off the positions an equal-sized-records stream
+    # would have them at, so the segments cannot lean on the host's entry expectation: they scan
+    import torch
+    s = torch.cat([torch.tensor([tg.header(tg.REC_LOST, 24), 7, 3], dtype=torch.int64), s])
     tail = tg.random_tail(77, ds)
     ring, head = ring_np(s, ds, tail, fill=0)
     desc = hbt.sampling_desc(E)
