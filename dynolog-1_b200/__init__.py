@@ -127,6 +127,7 @@ EXPORTS = [
     ("hbt_ring_reset_state", C.c_int, [_P, C.c_uint64]),
     ("hbt_ring_set_carry", C.c_int, [_P, C.c_uint32, C.c_uint64, _P, C.c_uint32, _P, C.c_uint64]),
     ("hbt_ring_set_switch_state", C.c_int, [_P, C.c_uint32, C.c_uint64, C.c_uint32]),
+    ("hbt_set_rows_budget", C.c_int, [_P, _P, C.c_uint32]),
     ("hbt_decode", C.c_int, [_P, C.POINTER(DecodeDesc)]),
     ("hbt_fetch_results", C.c_int, [_P, _P, C.c_uint32]),
     ("hbt_decode_reruns", C.c_uint32, [_P]),
@@ -347,6 +348,14 @@ class Context:
         assert ca is None or ca.shape[0] == NUM_COUNTERS
         self._ck(self.lib.hbt_ring_set_carry(self.h, cpu, carry_tstamp, _ptr(la),
                                              0 if la is None else la.shape[0], _ptr(ca), num_unknown))
+
+    def set_rows_budget(self, rows_per_cpu=None):
+        """Rows every CPU's sink can still take (hbt_set_rows_budget); None removes the budgets."""
+        if rows_per_cpu is None:
+            self._ck(self.lib.hbt_set_rows_budget(self.h, None, 0))
+            return
+        a = np.ascontiguousarray(rows_per_cpu, dtype=np.uint64)
+        self._ck(self.lib.hbt_set_rows_budget(self.h, _ptr(a), a.shape[0]))
 
     def set_switch_state(self, cpu: int, last_tstamp: int, in_write_errors: int):
         self._ck(self.lib.hbt_ring_set_switch_state(self.h, cpu, last_tstamp, in_write_errors))

@@ -1355,7 +1355,10 @@ struct FinalizeParams {
   uint64_t* clamp_head;  // per CPU: kNone, kClampLocate, or where a re-run must stop
   int64_t* clamp_ret;    // per CPU: return value to report after such a re-run
   uint64_t* locate_from; // per CPU: record start to count from ...
-  uint64_t* locate_skip; // ... and how many records to skip to find the cut
+  uint64_t* locate_skip; // ... and how many records (or rows) to skip to find the cut
+  uint32_t* locate_mode; // per CPU: 0 = count records; 1 / 2 = count delta rows, the interval in front
+                         //          of locate_from being invalid / valid
+  const uint64_t* rows_budget;  // per CPU: rows the caller's sink can take (null: no limit)
   uint32_t* flags;       // [0] re-run needed
   uint8_t* cpu_done;     // per CPU: 1 = this decode's results for the CPU are final (a re-run skips it)
   uint32_t n_cpus;
@@ -1443,8 +1446,30 @@ __global__ void __launch_bounds__(32) k_finalize(const FinalizeParams p) {
       p.clamp_ret[c] = (int64_t)d.max_records;
       p.locate_from[c] = pos;
       p.locate_skip[c] = (uint64_t)d.max_records - n_rec;
+      p.locate_mode[c] = 0;
       redo = true;
       { stop = true; break; }
+    }
+    if (p.agg == HBT_AGG_COUNT_DELTAS && p.rows_budget && ring.override_ret != -28) {
+      // Back-pressure: the generator's output ring takes rows_budget more rows; the SAMPLE whose row
+      // does not fit makes handleRecordSample return -ENOSPC and consume() stop in FRONT of it
+      // (PerCpuCountSampleGenerator.h:182-195, CpuEventsGroup.h:1441-1444).  When that row belongs
+      // to this segment the host locates the record and re-runs with the window clamped there.
+      // (a regression at the segment's seam sample is found first, below, like in the reference,
+      // whose timestamp check precedes the write: the seam row is only counted when it would be written)
+      uint64_t seg_rows = r.n_rows;
+      if (ev_kind(r.first_ev) == EV_SAMPLE && valid &&
+          !(prev_ts() > ring_word_g(ring, ev_pos(r.first_ev) + 8)))
+        ++seg_rows;
+      if (n_rows + seg_rows > p.rows_budget[c]) {
+        p.clamp_head[c] = kClampLocate;
+        p.clamp_ret[c] = -28;  // -ENOSPC
+        p.locate_from[c] = pos;
+        p.locate_skip[c] = p.rows_budget[c] - n_rows;
+        p.locate_mode[c] = valid ? 2 : 1;
+        redo = true;
+        { stop = true; break; }
+      }
     }
     // seam: the segment's first SAMPLE had no SAMPLE/LOST before it in the segment
     if (p.agg == HBT_AGG_COUNT_DELTAS && ev_kind(r.first_ev) == EV_SAMPLE) {
@@ -1529,6 +1554,13 @@ __global__ void __launch_bounds__(32) k_finalize(const FinalizeParams p) {
     // a regression found at a seam arrives here as the override of a clamped re-run
     if (ring.override_ret == -1) cts = kInvalidTs;
     for (uint32_t i = 0; i < d.n_events; ++i) sout.carry_last[i] = prev_val(i);
+    if (ring.override_ret == -28) {
+      // the refused SAMPLE (it starts where the clamped window ends) had already been folded into
+      // last_[] when its write failed, and the failure invalidates the interval (:165-179, :191-194)
+      cts = kInvalidTs;
+      for (uint32_t i = 0; i < d.n_events; ++i)
+        sout.carry_last[i] = xform(d, i, ring_word_g(ring, ring.head + 40 + 8ull * i));
+    }
     for (uint32_t i = d.n_events; i < HBT_MAX_EVENTS; ++i) sout.carry_last[i] = sin.carry_last[i];
   } else {
     for (uint32_t i = 0; i < HBT_MAX_EVENTS; ++i) sout.carry_last[i] = sin.carry_last[i];
@@ -1550,16 +1582,38 @@ __global__ void __launch_bounds__(64) k_seed_state(CpuState* st, uint32_t n_cpus
   st[c] = s;
 }
 
-// Position of the record `skip` records after `from` (header walk by one thread
-// per flagged CPU); used only for a finite max_num_records.
+// Where a clamped re-run must stop (header walk by one thread per flagged CPU): the record `skip`
+// records after `from` (a finite max_num_records), or the SAMPLE that would write delta row number
+// `skip` + 1 counted from `from` (a full output ring).  Rows follow the generator's interval state:
+// a SAMPLE closes an interval (a row) when the interval is valid, a LOST invalidates it, the next
+// SAMPLE only re-seeds.
 __global__ void __launch_bounds__(64)
-    k_locate(const RingDesc* rings, uint32_t n_cpus, uint64_t* clamp_head,
-             const uint64_t* locate_from, const uint64_t* locate_skip) {
+    k_locate(const RingDesc* rings, uint32_t n_cpus, uint64_t* clamp_head, const uint64_t* locate_from,
+             const uint64_t* locate_skip, const uint32_t* locate_mode, uint32_t handled_mask) {
   const uint32_t c = blockIdx.x * blockDim.x + threadIdx.x;
   if (c >= n_cpus || clamp_head[c] != kClampLocate) return;
   const RingDesc ring = rings[c];
   uint64_t pos = locate_from[c];
-  for (uint64_t k = 0; k < locate_skip[c]; ++k) pos += hdr_size(ring_word_g(ring, pos));
+  if (locate_mode[c] == 0) {
+    for (uint64_t k = 0; k < locate_skip[c]; ++k) pos += hdr_size(ring_word_g(ring, pos));
+  } else {
+    bool valid = locate_mode[c] == 2;
+    uint64_t left = locate_skip[c];
+    for (; pos < ring.head;) {
+      const uint64_t h = ring_word_g(ring, pos);
+      const uint32_t type = hdr_type(h);
+      if (type == REC_SAMPLE && (handled_mask & HBT_H_SAMPLE)) {
+        if (valid) {
+          if (left == 0) break;  // this SAMPLE's row is the one that does not fit
+          --left;
+        }
+        valid = true;
+      } else if (type == REC_LOST && (handled_mask & HBT_H_LOST)) {
+        valid = false;
+      }
+      pos += hdr_size(h);
+    }
+  }
   clamp_head[c] = pos;
 }
 

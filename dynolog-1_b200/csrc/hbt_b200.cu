@@ -112,6 +112,9 @@ struct hbt_ctx {
   DevBuf<uint8_t> d_seam;
   DevBuf<uint64_t> d_forced;
   DevBuf<uint64_t> d_clamp_head, d_locate_from, d_locate_skip;
+  DevBuf<uint32_t> d_locate_mode;
+  DevBuf<uint64_t> d_rows_budget;  // hbt_set_rows_budget
+  bool has_rows_budget = false;
   DevBuf<int64_t> d_clamp_ret;
   DevBuf<uint32_t> d_flags;
   DevBuf<uint64_t> d_rows;
@@ -480,6 +483,8 @@ int launch_finalize(hbt_ctx* ctx) {
   f.clamp_ret = ctx->d_clamp_ret.p;
   f.locate_from = ctx->d_locate_from.p;
   f.locate_skip = ctx->d_locate_skip.p;
+  f.locate_mode = ctx->d_locate_mode.p;
+  f.rows_budget = ctx->has_rows_budget ? ctx->d_rows_budget.p : nullptr;
   f.flags = ctx->d_flags.p;
   f.cpu_done = ctx->d_cpu_done.p;
   f.n_cpus = C;
@@ -654,6 +659,8 @@ void hbt_destroy(hbt_ctx* ctx) {
   ctx->d_clamp_head.release();
   ctx->d_locate_from.release();
   ctx->d_locate_skip.release();
+  ctx->d_locate_mode.release();
+  ctx->d_rows_budget.release();
   ctx->d_clamp_ret.release();
   ctx->d_flags.release();
   ctx->d_rows.release();
@@ -789,6 +796,22 @@ int hbt_ring_set_carry(hbt_ctx* ctx, uint32_t cpu, uint64_t carry_tstamp, const 
   return 0;
 }
 
+int hbt_set_rows_budget(hbt_ctx* ctx, const uint64_t* rows_per_cpu, uint32_t n_cpus) {
+  if (!ctx || ctx->n_cpus == 0) return fail(ctx, -EINVAL, "no rings configured");
+  if (int rc = complete_decode(ctx)) return rc;
+  if (!rows_per_cpu) {
+    ctx->has_rows_budget = false;
+    return 0;
+  }
+  if (n_cpus != ctx->n_cpus) return fail(ctx, -EINVAL, "one budget per configured CPU (%u), got %u", ctx->n_cpus, n_cpus);
+  CU(cudaSetDevice(ctx->device));
+  CU(cudaMemcpyAsync(ctx->d_rows_budget.p, rows_per_cpu, n_cpus * sizeof(uint64_t), cudaMemcpyHostToDevice,
+                     ctx->stream));
+  CU(cudaStreamSynchronize(ctx->stream));
+  ctx->has_rows_budget = true;
+  return 0;
+}
+
 int hbt_ring_set_switch_state(hbt_ctx* ctx, uint32_t cpu, uint64_t last_tstamp, uint32_t in_write_errors) {
   if (!ctx || cpu >= ctx->n_cpus) return fail(ctx, -EINVAL, "cpu out of range");
   CU(cudaSetDevice(ctx->device));
@@ -822,6 +845,9 @@ static int configure_common(hbt_ctx* ctx, uint32_t n_cpus) {
   CU(ctx->d_clamp_ret.reserve(n_cpus));
   CU(ctx->d_locate_from.reserve(n_cpus));
   CU(ctx->d_locate_skip.reserve(n_cpus));
+  CU(ctx->d_locate_mode.reserve(n_cpus));
+  CU(ctx->d_rows_budget.reserve(n_cpus));
+  ctx->has_rows_budget = false;
   CU(ctx->h_clamp_head.reserve(n_cpus));
   CU(ctx->h_clamp_ret.reserve(n_cpus));
   CU(ctx->d_flags.reserve(4));
@@ -983,7 +1009,8 @@ static int complete_decode(hbt_ctx* ctx) {
     ++ctx->reruns;
     // locate cuts for a finite max_num_records, then fetch clamps, forced entries and which CPUs are settled
     k_locate<<<(C + 63) / 64, 64, 0, ctx->stream>>>(ctx->d_rings.p, C, ctx->d_clamp_head.p,
-                                                   ctx->d_locate_from.p, ctx->d_locate_skip.p);
+                                                   ctx->d_locate_from.p, ctx->d_locate_skip.p,
+                                                   ctx->d_locate_mode.p, ctx->desc.handled_mask);
     ++ctx->launches;
     CU(cudaGetLastError());
     CU(cudaMemcpyAsync(ctx->h_clamp_head.p, ctx->d_clamp_head.p, C * sizeof(uint64_t),

@@ -298,6 +298,19 @@ int hbt_ring_set_carry(hbt_ctx* ctx, uint32_t cpu, uint64_t carry_tstamp, const 
 int hbt_ring_set_switch_state(hbt_ctx* ctx, uint32_t cpu, uint64_t last_tstamp,
                               uint32_t in_write_errors);
 
+/* Back-pressure of the generators' output rings.  rows_per_cpu[c] = the rows CPU c's
+ * sink can still take (its ring's free space / kWriteByteSize).  An
+ * HBT_AGG_COUNT_DELTAS decode then behaves like the reference with a full ring and
+ * no drop-if-full (PerCpuCountSampleGenerator.h:182-195; a handler returning < 0
+ * leaves data_tail in FRONT of that record, CpuEventsGroup.h:1318-1322,1441-1444):
+ * the SAMPLE whose row would not fit ends the CPU's consume() with ret = -ENOSPC,
+ * new_tail at that SAMPLE, the record not counted, count_.tstamp invalid and
+ * last_[] already holding its values -- submit the rest of the window again once
+ * the sink has room and the SAMPLE re-seeds, exactly as it does in the reference.
+ * The budgets stay in force until changed; NULL removes them.  n_cpus must equal
+ * the configured CPU count. */
+int hbt_set_rows_budget(hbt_ctx* ctx, const uint64_t* rows_per_cpu, uint32_t n_cpus);
+
 /* ------------------------------------------------------------------------ */
 /* Decode: CpuEventsGroup::consume (CpuEventsGroup.h:1326-1522) for every CPU
  * with a submitted window, plus the SAMPLE/LOST handlers selected by

@@ -330,6 +330,13 @@ static int consume_core(const uint8_t* ring, uint64_t data_size, uint64_t tail, 
                 goto exit;
               } else {
                 if (n_rows >= rows_cap) { /* write fails: gen :191-194 */
+                  /* the deltas loop has already folded this sample into last_[] (:165-179) */
+                  for (uint32_t i = 0; i < ne; ++i) {
+                    uint64_t v = ring_word(ring, mask, tail + 40 + 8ull * i);
+                    if ((d->tsc_transform_mask >> i) & 1)
+                      v = hbt_oracle_kernel_time_from_tsc(v, &d->tsc);
+                    carry->last[i] = v;
+                  }
                   carry->tstamp = INVALID_TS;
                   err = -ENOSPC;
                   goto exit;

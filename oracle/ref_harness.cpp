@@ -904,3 +904,56 @@ extern "C" int hbtref_frame_query(const uint64_t* rows, uint64_t n_rows, uint32_
   }
   return 0;
 }
+
+// Back-pressure: the REAL CpuCountSampleGenerator with an output ring that has room for exactly
+// `rows_budget` more rows (the ring is filled with dummy rows to the brim, then rows_budget of
+// them are consumed) and no drop-if-full: the SAMPLE whose row does not fit makes
+// handleRecordSample return -ENOSPC (PerCpuCountSampleGenerator.h:182-195) and consume() stop in
+// front of it (CpuEventsGroup.h:1441-1444).  Outputs as hbtref_sample_deltas.
+extern "C" int hbtref_sample_deltas_budget(const uint8_t* ring, uint64_t data_size, uint64_t tail, uint64_t head,
+                                           uint32_t n_events, uint32_t max_records, uint64_t rows_budget,
+                                           uint64_t* carry_tstamp, uint64_t* carry_last, uint64_t* rows,
+                                           uint64_t rows_cap, hbt_cpu_result* res) {
+  if (n_events == 0 || n_events > HBT_MAX_EVENTS) return -EINVAL;
+  hbt_tsc_params tsc{0, 1, 0, 0};
+  FakeMmapAlias mm;
+  mm.init(ring, data_size, tail, head, tsc);
+  auto confs = make_confs(n_events, 0);
+  std::vector<std::string> names;
+  for (auto& c : confs) names.push_back(c.id);
+  hp::CpuCountSampleGenerator g(names, 0, -1, confs, rows_budget + 8, 0);
+  attach(g, mm.page, tsc);
+  load_counters(g, res->counters);
+  g.count_.tstamp = *carry_tstamp;
+  for (uint32_t i = 0; i < n_events; ++i) g.last_[i] = carry_last[i];
+  g.num_unknown_count_interval_ = static_cast<uint32_t>(res->num_unknown_count_interval);
+  const size_t row_bytes = g.kWriteByteSize;
+  using Extra = hp::CpuCountSampleGenerator::RbExtraData;
+  facebook::hbt::ringbuffer::Producer<Extra> filler(g.getOutput());
+  facebook::hbt::ringbuffer::Consumer<Extra> cons(g.getOutput());
+  std::vector<uint64_t> row(2 + n_events, 0xD0D0D0D0D0D0D0D0ull);
+  uint64_t dummies = 0;
+  while (filler.write(row.data(), row_bytes) >= 0) ++dummies;
+  if (dummies < rows_budget) { detach(g); return -ERANGE; }
+  for (uint64_t k = 0; k < rows_budget; ++k)
+    if (cons.copy(row_bytes, row.data()) < 0) { detach(g); return -EIO; }
+  dummies -= rows_budget;
+
+  int64_t ret = run_consume(g, max_records);
+  finish_result(g, ring, data_size, tail, mm.hdr, ret, res);
+  uint64_t n = 0, seen = 0;
+  int rc = 0;
+  while (cons.copy(row_bytes, row.data()) >= 0) {
+    if (seen++ < dummies) continue;
+    if (n >= rows_cap) { rc = -ENOSPC; break; }
+    std::memcpy(rows + n * (2 + n_events), row.data(), row_bytes);
+    ++n;
+  }
+  res->n_rows = n;
+  res->num_unknown_count_interval = g.num_unknown_count_interval_;
+  res->carry_tstamp = g.count_.tstamp;
+  *carry_tstamp = g.count_.tstamp;
+  for (uint32_t i = 0; i < n_events; ++i) carry_last[i] = g.last_[i];
+  detach(g);
+  return rc;
+}

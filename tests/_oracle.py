@@ -113,8 +113,9 @@ def hist_to_dict(entries: np.ndarray):
 
 def port_consume(ring: np.ndarray, tail: int, head: int, desc: hbt.DecodeDesc,
                  carry_tstamp=hbt.INVALID_TS, carry_last=None, counters=None, num_unknown=0,
-                 cpu=0):
-    """oracle/hbt_oracle.c over one ring image (uint8/uint64 numpy array)."""
+                 cpu=0, rows_budget=None):
+    """oracle/hbt_oracle.c over one ring image (uint8/uint64 numpy array).  rows_budget: rows the
+    generator's output ring still takes (None: unlimited)."""
     lib = port()
     ring = np.ascontiguousarray(ring).view(np.uint8)
     n = max(1, desc.n_events)
@@ -130,6 +131,8 @@ def port_consume(ring: np.ndarray, tail: int, head: int, desc: hbt.DecodeDesc,
     res.num_unknown_count_interval = num_unknown
     cap = (head - tail) // (40 + 8 * n) + 2
     rows = np.zeros((cap, 2 + n), dtype=np.uint64)
+    if rows_budget is not None:
+        cap = min(cap, rows_budget)
     h = lib.hbt_oracle_hist_new() if desc.aggregate == hbt.AGG_IP_HISTOGRAM else None
     rc = lib.hbt_oracle_consume(_np(ring), ring.nbytes, tail, head, C.byref(desc), C.byref(carry),
                                 _np(rows), cap, h, C.byref(res))
@@ -200,6 +203,35 @@ def ref_consume(ring: np.ndarray, tail: int, head: int, desc: hbt.DecodeDesc,
     return result_dict(resarr[0], hist=hist)
 
 
+def ref_consume_budget(ring, tail, head, desc, rows_budget, carry_tstamp=hbt.INVALID_TS, carry_last=None,
+                       counters=None, num_unknown=0):
+    """The reference's own CpuCountSampleGenerator with an output ring that has room for exactly
+    rows_budget more rows (oracle/_ref, hbtref_sample_deltas_budget)."""
+    lib = ref()
+    ring = np.ascontiguousarray(ring).view(np.uint8)
+    n = desc.n_events
+    res = hbt.CpuResult()
+    if counters is not None:
+        for i, v in enumerate(counters):
+            res.counters[i] = int(v)
+    res.num_unknown_count_interval = num_unknown
+    ts = C.c_uint64(carry_tstamp)
+    last = np.zeros(hbt.MAX_EVENTS, dtype=np.uint64)
+    if carry_last is not None:
+        last[:len(carry_last)] = carry_last
+    cap = (head - tail) // (40 + 8 * n) + 2
+    rows = np.zeros((cap, 2 + n), dtype=np.uint64)
+    lib.hbtref_sample_deltas_budget.restype = C.c_int
+    lib.hbtref_sample_deltas_budget.argtypes = [_P, C.c_uint64, C.c_uint64, C.c_uint64, C.c_uint32, C.c_uint32,
+                                                C.c_uint64, C.POINTER(C.c_uint64), _P, _P, C.c_uint64,
+                                                C.POINTER(hbt.CpuResult)]
+    with quiet_stderr():
+        rc = lib.hbtref_sample_deltas_budget(_np(ring), ring.nbytes, tail, head, n, desc.max_records, rows_budget,
+                                             C.byref(ts), _np(last), _np(rows), cap, C.byref(res))
+    assert rc == 0, rc
+    return result_dict(res, rows[:res.n_rows].copy(), last[:n].copy())
+
+
 def _ref_covers(desc: hbt.DecodeDesc) -> bool:
     """Decodes ref_consume can run through the reference's own classes."""
     if desc.aggregate == hbt.AGG_NONE and desc.sample_layout == hbt.SAMPLE_GROUP:
@@ -216,15 +248,19 @@ IP_REF_SIZES = (40, 48, 64, 104, 128)
 
 
 def consume(ring: np.ndarray, tail: int, head: int, desc: hbt.DecodeDesc, carry_tstamp=hbt.INVALID_TS,
-            carry_last=None, counters=None, num_unknown=0, cpu=0):
+            carry_last=None, counters=None, num_unknown=0, cpu=0, rows_budget=None):
     """What the GPU tests compare the CUDA path with: the REFERENCE's own consume() (oracle/_ref)
     whenever that library is present and covers the decode -- the C restatement is then only
     cross-checked against it here -- else the C restatement alone."""
-    p = port_consume(ring, tail, head, desc, carry_tstamp, carry_last, counters, num_unknown, cpu)
+    p = port_consume(ring, tail, head, desc, carry_tstamp, carry_last, counters, num_unknown, cpu, rows_budget)
     if not (have_ref() and _ref_covers(desc)):
         return p
-    with quiet_stderr():
-        r = ref_consume(ring, tail, head, desc, carry_tstamp, carry_last, counters, num_unknown, cpu)
+    if rows_budget is not None:
+        assert desc.aggregate == hbt.AGG_COUNT_DELTAS and desc.handled_mask == hbt.MODE_SAMPLING and not desc.tsc_transform_mask
+        r = ref_consume_budget(ring, tail, head, desc, rows_budget, carry_tstamp, carry_last, counters, num_unknown)
+    else:
+        with quiet_stderr():
+            r = ref_consume(ring, tail, head, desc, carry_tstamp, carry_last, counters, num_unknown, cpu)
     for k in ("ret", "n_records", "new_tail", "counters"):
         assert r[k] == p[k], ("oracle port != reference", k, r[k], p[k])
     if desc.aggregate == hbt.AGG_COUNT_DELTAS:

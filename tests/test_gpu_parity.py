@@ -348,6 +348,45 @@ def test_resume_from_saved_state(built):
         b.close()
 
 
+@pytest.mark.parametrize("budgets", [(0, 1, 5000), (137, 10**5, 2), (3000, 3001, 2999)])
+def test_rows_budget_back_pressure(ctx, budgets):
+    """hbt_set_rows_budget: the SAMPLE whose row the sink cannot take ends that CPU's consume() with
+    -ENOSPC in front of it (the reference with a full output ring); the rest of the window, decoded
+    after the sink was drained, starts by re-seeding on that SAMPLE.  Cuts land in first tiles,
+    at segment seams and deep inside windows."""
+    ds, E = 1 << 20, 6
+    desc = hbt.sampling_desc(E)
+    rings = []
+    for cpu in range(3):
+        s = tg.group_sample_stream(700 + cpu, 9000, E, lost_every=(0, 97, 1500)[cpu])
+        tail = tg.random_tail(50 + cpu, ds)
+        ring, head = ring_np(s, ds, tail)
+        rings.append((ring, tail, head))
+    ctx.ring_configure(3, ds)
+    ctx.reset_state(123)
+    ctx.set_rows_budget(budgets)
+    try:
+        res = gpu_decode(ctx, rings, desc, ds, reset=False)
+        wants = []
+        for cpu, (ring, tail, head) in enumerate(rings):
+            w = orc.consume(ring, tail, head, desc, 123, np.zeros(E, np.uint64), rows_budget=budgets[cpu])
+            check_cpu(ctx, cpu, res[cpu], w, desc)
+            assert (w["ret"] == -28) == (budgets[cpu] < 8000)
+            wants.append(w)
+        check_rows_all(ctx, wants, E)
+        # the sinks were drained: the rest of every window
+        ctx.set_rows_budget(None)
+        rest = [(ring, wants[c]["new_tail"], head) for c, (ring, tail, head) in enumerate(rings)]
+        res2 = gpu_decode(ctx, rest, desc, ds, reset=False)
+        for cpu, (ring, tail, head) in enumerate(rest):
+            w0 = wants[cpu]
+            w = orc.consume(ring, tail, head, desc, w0["carry_tstamp"], w0["carry_last"], w0["counters"],
+                            w0["num_unknown"])
+            check_cpu(ctx, cpu, res2[cpu], w, desc)
+    finally:
+        ctx.set_rows_budget(None)
+
+
 def test_mixed_stream_deltas(ctx):
     ds, E = 1 << 21, 8
     mix = (("sample", 0.6), ("switch", 0.2), ("comm", 0.05), ("mmap", 0.05), ("lost", 0.02),

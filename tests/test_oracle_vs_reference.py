@@ -173,3 +173,34 @@ def test_counts_edge_values(built):
     threads = orc.ref_counts(reads, threads=3)
     assert np.array_equal(threads["scaled"], a["scaled"])
     assert np.array_equal(threads["deltas"], a["deltas"])
+
+
+@pytest.mark.parametrize("budget", [0, 1, 7, 150, 10**6])
+def test_full_output_ring_stops_consume_in_front_of_the_sample(built, budget):
+    """Back-pressure (PerCpuCountSampleGenerator.h:182-195, CpuEventsGroup.h:1441-1444): the real
+    generator with room for `budget` rows against the restatement's rows_cap, then the rest of the
+    window once the ring was drained (the refused SAMPLE re-seeds)."""
+    if not orc.have_ref():
+        pytest.skip("oracle/_ref not built (reference tree absent)")
+    ds, E = 1 << 17, 4
+    s = tg.group_sample_stream(505, 900, E, lost_every=61)
+    tail = 3 * ds + ds - 4096
+    ring, head = tg.place_in_ring(s, ds, tail, fill_seed=3)
+    ring = ring.numpy().view(np.uint64)
+    d = hbt.sampling_desc(E)
+    r = orc.ref_consume_budget(ring, tail, head, d, budget, carry_tstamp=1000, carry_last=np.zeros(E, np.uint64))
+    p = orc.port_consume(ring, tail, head, d, 1000, np.zeros(E, np.uint64), rows_budget=budget)
+    for k in ("ret", "n_records", "new_tail", "counters", "n_rows", "num_unknown", "carry_tstamp"):
+        assert r[k] == p[k], k
+    assert np.array_equal(r["rows"], p["rows"]) and np.array_equal(r["carry_last"], p["carry_last"])
+    if budget < 800:
+        assert r["ret"] == -28 and r["n_rows"] == budget and r["carry_tstamp"] == hbt.INVALID_TS
+        # drained: the rest of the window
+        r2 = orc.ref_consume_budget(ring, r["new_tail"], head, d, 10**6, r["carry_tstamp"], r["carry_last"],
+                                    r["counters"], r["num_unknown"])
+        p2 = orc.port_consume(ring, p["new_tail"], head, d, p["carry_tstamp"], p["carry_last"], p["counters"],
+                              p["num_unknown"])
+        for k in ("ret", "n_records", "new_tail", "counters", "n_rows", "num_unknown", "carry_tstamp"):
+            assert r2[k] == p2[k], k
+        assert np.array_equal(r2["rows"], p2["rows"])
+        assert r2["num_unknown"] >= r["num_unknown"] + 1   # the refused SAMPLE only re-seeds
