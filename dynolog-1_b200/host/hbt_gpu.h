@@ -298,6 +298,15 @@ class PerCpuCountSampleDecoder {
                                 n2, tail),
                 "hbt_submit_ring");
   }
+  // Back-pressure: rows every CPU's output ring still takes.  consume() then stops a CPU with
+  // -ENOSPC in front of the SAMPLE whose row would not fit, as the generator does when its ring is
+  // full and nothing may be dropped (PerCpuCountSampleGenerator.h:182-195).
+  void setRowsBudget(const std::map<CpuId, uint64_t>& free_rows) {
+    std::vector<uint64_t> b(results_.size(), ~0ull);
+    for (const auto& [cpu, n] : free_rows) b.at(cpu) = n;
+    gpu_->check(hbt_set_rows_budget(gpu_->get(), b.data(), (uint32_t)b.size()), "hbt_set_rows_budget");
+  }
+  void clearRowsBudget() { gpu_->check(hbt_set_rows_budget(gpu_->get(), nullptr, 0), "hbt_set_rows_budget"); }
   // consume(max_num_records) for every CPU; returns what each CPU's consume() would.
   std::map<CpuId, int64_t> consume(unsigned max_num_records) {
     hbt_decode_desc d{};
@@ -492,6 +501,8 @@ class CountSampleSink {
     }
   }
   size_t getNumEntries() const { return (data_.size() - head_) / (2 + kNumEvents); }
+  // rows write() still takes before it answers -ENOSPC (no drop-if-full)
+  size_t freeRows() const { return (kDataPoolByteSize - usedBytes()) / kWriteByteSize; }
   size_t usedBytes() const { return (data_.size() - head_) * sizeof(uint64_t); }
   // Consumer side (ringbuffer::Consumer::readInTx / relSeekInTx / commitTx reduced to a cursor);
   // the returned row is contiguous and stays valid until the next write/consume.
@@ -562,8 +573,18 @@ class TraceMonitor {
     if (it == sinks_.end()) throw std::invalid_argument("CPU " + std::to_string(cpu) + " not monitored");
     return it->second;
   }
+  // Tell the decoder how many rows every sink still takes, so that its next consume() stops where
+  // the reference's would (sinks that drop their oldest rows when full never push back).
+  void applyBackPressure(perf_event::PerCpuCountSampleDecoder& dec) {
+    std::lock_guard<std::mutex> lock{counts_mutex_};
+    std::map<CpuId, uint64_t> free_rows;
+    for (CpuId cpu : mon_cpus_.cpus)
+      if (sink(cpu).kNumBytesDropIfFull == 0) free_rows[cpu] = sink(cpu).freeRows();
+    dec.setRowsBudget(free_rows);
+  }
   // Move the rows of the decoder's last consume() into the sinks (the producer side:
-  // what handleRecordSample's output_producer_.write does row by row).  Returns rows refused.
+  // what handleRecordSample's output_producer_.write does row by row).  Returns rows refused
+  // (none after applyBackPressure).
   size_t accum(perf_event::PerCpuCountSampleDecoder& dec) {
     std::lock_guard<std::mutex> lock{counts_mutex_};
     size_t refused = 0;

@@ -330,6 +330,35 @@ static void test_gpu() {
   tm.applyToCountSamplesAndConsume(func);
   CHECK(calls == 4 && tm.sink(2).getNumEntries() == 0);
 
+  // back-pressure: a sink with room for 2 rows stops consume() in front of the SAMPLE whose row
+  // would be the third (-ENOSPC, tail before it); once drained, the rest follows and that SAMPLE re-seeds
+  {
+    mon::TraceMonitor small(CpuSet::makeFromCont(std::vector<int>{0, 2}), {"cycles", "instructions"}, 2, 0);
+    const size_t room = small.sink(2).freeRows();
+    dec.enable(kInvalidTimeStamp);
+    dec.onCpuDataBufferRead(2, slices, tail, head);
+    small.applyBackPressure(dec);
+    auto r1 = dec.consume(0xFFFFFFFFu);
+    CHECK(r1.at(2) == -ENOSPC && dec.rows(2).size() == room * 4);
+    CHECK(small.accum(dec) == 0 && small.sink(2).getNumEntries() == room && small.sink(2).freeRows() == 0);
+    // LOST + re-seeding SAMPLE + `room` row-writing SAMPLEs were consumed; the tail stands in front of the next
+    CHECK(dec.dataTail(2) == tail + 24 + 56 * (1 + room));
+    CHECK(dec.getLastTimeStamp(2) == kInvalidTimeStamp);
+    int seen = 0;
+    auto drain = [&](CpuId, int, const std::vector<std::string>&, TimeStamp, TimeStamp, const uint64_t*, size_t) { ++seen; };
+    small.applyToCountSamplesAndConsume(drain);
+    CHECK(seen == (int)room);
+    // the rest of the window (what onCpuDataBufferRead hands out from the new tail; it no longer wraps)
+    const uint64_t t2 = dec.dataTail(2);
+    pe::RbDataSlices rest(base + (t2 & (ds - 1)), head - t2);
+    dec.onCpuDataBufferRead(2, rest, t2, head);
+    small.applyBackPressure(dec);
+    auto r2 = dec.consume(0xFFFFFFFFu);
+    CHECK(r2.at(2) == -ENODATA && dec.dataTail(2) == head);
+    CHECK(dec.rows(2).size() == (4 - room - 1) * 4);   // the refused SAMPLE only re-seeds
+    dec.clearRowsBudget();
+  }
+
   // context-switch ring through the thread-switch generator mirror: events with vids
   {
     const std::vector<uint64_t> sw = switch_stream();
