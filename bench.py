@@ -347,6 +347,8 @@ def bench_deltas(args, rank, world, local, dev, dist):
     ctx.ring_configure(cpus, 0)
     if args.segs_per_cpu:
         ctx.set_geometry(args.segs_per_cpu)
+    if args.kernel:
+        ctx.set_decode_kernel({"tiles": hbt.KERNEL_TILES, "walk": hbt.KERNEL_WALK}[args.kernel])
     if dist is not None:
         ctx.comm_init(dist)
     desc = hbt.sampling_desc(E, handled=hbt.MODE_MIXED if mixed else hbt.MODE_SAMPLING)
@@ -962,6 +964,7 @@ def main():
                     help="skip the diagnostics block (the other BASELINE configs)")
     ap.add_argument("--diag-steps", type=int, default=20, help="timed steps of each diagnostic workload")
     ap.add_argument("--segs-per-cpu", type=int, default=0, help="hbt_set_geometry (0 = automatic)")
+    ap.add_argument("--kernel", default="", choices=["", "tiles", "walk"], help="hbt_set_decode_kernel (default: automatic)")
     ap.add_argument("--shard", action="store_true",
                     help="ring workloads at N > 1: --cpus is the whole machine, sharded over the ranks")
     args = ap.parse_args()
@@ -1011,6 +1014,8 @@ def main():
     ctx.hist_configure(args.hist_slots_per_cpu * args.cpus)
     if args.segs_per_cpu:
         ctx.set_geometry(args.segs_per_cpu)
+    if args.kernel:
+        ctx.set_decode_kernel({"tiles": hbt.KERNEL_TILES, "walk": hbt.KERNEL_WALK}[args.kernel])
     if dist is not None:
         ctx.comm_init(dist)   # NCCL communicator of the library itself (hbt_comm_init)
     desc = hbt.ip_desc(40, aggregate=hbt.AGG_IP_HISTOGRAM if args.agg == "hist" else hbt.AGG_NONE)

@@ -34,6 +34,7 @@ MODE_AUX_SPACE = H_AUX | H_ITRACE_START
 MODE_MIXED = MODE_CONTEXT_SWITCH | H_SAMPLE | H_READ
 SAMPLE_GROUP, SAMPLE_IP = 0, 1
 AGG_NONE, AGG_COUNT_DELTAS, AGG_IP_HISTOGRAM, AGG_SWITCH_EVENTS = 0, 1, 2, 3
+KERNEL_AUTO, KERNEL_TILES, KERNEL_WALK = 0, 1, 2
 # tagstack::Event::Type (Event.h:29-47) + the COMM pseudo-event of hbt_switch_event
 (SWEV_START, SWEV_END, SWEV_THREAD_CREATION, SWEV_THREAD_DESTRUCTION, SWEV_SWITCH_IN,
  SWEV_SWITCH_OUT_PREEMPT, SWEV_SWITCH_OUT_YIELD, SWEV_WRITE_ERRORS_START,
@@ -119,6 +120,7 @@ EXPORTS = [
     ("hbt_sync", C.c_int, [_P]),
     ("hbt_launch_count", C.c_uint64, [_P]),
     ("hbt_set_geometry", C.c_int, [_P, C.c_uint32, C.c_uint32]),
+    ("hbt_set_decode_kernel", C.c_int, [_P, C.c_int]),
     ("hbt_set_cpu_base", C.c_int, [_P, C.c_uint32]),
     ("hbt_ring_configure", C.c_int, [_P, C.c_uint32, C.c_uint64]),
     ("hbt_submit_ring", C.c_int, [_P, C.c_uint32, _P, C.c_size_t, _P, C.c_size_t, C.c_uint64]),
@@ -299,6 +301,10 @@ class Context:
     @property
     def launches(self) -> int:
         return int(self.lib.hbt_launch_count(self.h))
+
+    def set_decode_kernel(self, which: int = 0):
+        """KERNEL_AUTO / KERNEL_TILES (k_decode) / KERNEL_WALK (k_walk)."""
+        self._ck(self.lib.hbt_set_decode_kernel(self.h, which))
 
     def set_geometry(self, segs_per_cpu: int = 0, min_tiles_per_seg: int = 0):
         """Segments per CPU / tiles per segment of the decode (0 = automatic)."""

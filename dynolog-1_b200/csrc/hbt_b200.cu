@@ -17,6 +17,7 @@
 #include "counts.cuh"
 #include "ctx_internal.h"
 #include "decode.cuh"
+#include "walk.cuh"
 #include "metric_table.h"
 
 using namespace hbt;
@@ -141,6 +142,9 @@ struct hbt_ctx {
   PinBuf<uint8_t> h_cpu_done;
   uint64_t rerun_segments = 0;  // segments decoded again by the re-runs of the last decode
   uint32_t geo_segs_per_cpu = 0, geo_min_tiles = 0;  // hbt_set_geometry; 0 = automatic
+  int kernel_choice = HBT_KERNEL_AUTO;                // hbt_set_decode_kernel
+  bool walk = false;                                  // this decode runs k_walk (set by build_tables)
+  bool walk_attr_set[4] = {false, false, false, false};
   bool tiled = true;
   bool attr_set[4] = {false, false, false, false};
   bool pending = false;  // a decode was launched and not yet fetched
@@ -257,6 +261,15 @@ int validate_desc(hbt_ctx* ctx, const hbt_decode_desc* d) {
   return 0;
 }
 
+// Which kernel decodes: k_walk for streams of mixed record types (anything but a sampling-only
+// handler set), where k_decode's uniform fast path has nothing to hold on to; k_decode otherwise.
+static bool use_walk(const hbt_ctx* ctx) {
+  const hbt_decode_desc& d = ctx->desc;
+  if (d.aggregate == HBT_AGG_IP_HISTOGRAM) return false;
+  if (ctx->kernel_choice != HBT_KERNEL_AUTO) return ctx->kernel_choice == HBT_KERNEL_WALK;
+  return d.aggregate == HBT_AGG_SWITCH_EVENTS;  // (measured: k_walk wins there, k_decode elsewhere)
+}
+
 // Build ring / segment tables for the current windows (+ clamps) into pinned
 // memory and upload them.
 int build_tables(hbt_ctx* ctx, const uint64_t* clamp_head, const int64_t* clamp_ret,
@@ -276,10 +289,11 @@ int build_tables(hbt_ctx* ctx, const uint64_t* clamp_head, const int64_t* clamp_
     }
   }
   ctx->tiled = !any_small;
+  ctx->walk = ctx->tiled && use_walk(ctx);
 
   // segments per CPU: enough CTAs to fill the machine a few times, at least
-  // 8 tiles (128 KiB) per segment
-  const uint64_t target_ctas = (uint64_t)ctx->sm_count * 8;
+  // 8 tiles (128 KiB) per segment.  k_walk gives a segment to a WARP: many more, shorter segments.
+  const uint64_t target_ctas = (uint64_t)ctx->sm_count * (ctx->walk ? 96 : 8);
   uint32_t segs_per_cpu = active ? (uint32_t)((target_ctas + active - 1) / active) : 1;
   // the histogram's per-segment cache of hot keys wants short segments
   if (d.aggregate == HBT_AGG_IP_HISTOGRAM && segs_per_cpu < 16) segs_per_cpu = 16;
@@ -292,7 +306,7 @@ int build_tables(hbt_ctx* ctx, const uint64_t* clamp_head, const int64_t* clamp_
   if (d.sample_layout == HBT_SAMPLE_IP && (d.handled_mask & HBT_H_SAMPLE)) hint_size = d.ip_sample_bytes;
   else if (d.aggregate == HBT_AGG_COUNT_DELTAS) hint_size = 40 + 8 * d.n_events;
   if (hint_size > (uint32_t)kTile / 2) hint_size = 0;
-  uint64_t min_tiles_per_seg = 8;
+  uint64_t min_tiles_per_seg = ctx->walk ? 2 : 8;
   if (ctx->geo_min_tiles) min_tiles_per_seg = ctx->geo_min_tiles;
   std::vector<SegDesc> segs;
   segs.reserve((size_t)active * segs_per_cpu + 1);  // no regrowth while the tables are built
@@ -422,6 +436,20 @@ static __global__ void k_prepare(PrepareParams p) {
 }
 
 template <int AGG>
+static int launch_walk(hbt_ctx* ctx, const DecodeParams& p, uint32_t n_launch) {
+  if constexpr (AGG != HBT_AGG_IP_HISTOGRAM) {
+    if (!ctx->walk_attr_set[AGG]) {  // six CTAs' staging slices per SM
+      CU(cudaFuncSetAttribute(k_walk<AGG>, cudaFuncAttributePreferredSharedMemoryCarveout,
+                              (int)cudaSharedmemCarveoutMaxShared));
+      ctx->walk_attr_set[AGG] = true;
+    }
+    k_walk<AGG><<<(n_launch + kWalkWarps - 1) / kWalkWarps, 32 * kWalkWarps, kWalkWarps * kWalkSmemPerWarp,
+                  ctx->stream>>>(p, n_launch);
+  }
+  return 0;
+}
+
+template <int AGG>
 int launch_decode_agg(hbt_ctx* ctx) {
   DecodeParams p{};
   p.rings = ctx->d_rings.p;
@@ -438,7 +466,11 @@ int launch_decode_agg(hbt_ctx* ctx) {
   p.run_list = ctx->n_run ? ctx->d_run_list.p : nullptr;
   if (ctx->n_segs == 0) return 0;
   const uint32_t n_launch = ctx->n_run ? ctx->n_run : ctx->n_segs;
-  if (ctx->tiled) {
+  if (ctx->walk) {
+    CU(cudaEventRecord(ctx->ev_k0, ctx->stream));
+    if (int rc = launch_walk<AGG>(ctx, p, n_launch)) return rc;
+    CU(cudaEventRecord(ctx->ev_k1, ctx->stream));
+  } else if (ctx->tiled) {
     const size_t smem = decode_smem_bytes(AGG);
     if (!ctx->attr_set[AGG]) {
       CU(cudaFuncSetAttribute(k_decode<AGG>, cudaFuncAttributeMaxDynamicSharedMemorySize,
@@ -745,6 +777,14 @@ int hbt_set_geometry(hbt_ctx* ctx, uint32_t segs_per_cpu, uint32_t min_tiles_per
   if (segs_per_cpu > (uint32_t)kMaxSegsPerCpu) return fail(ctx, -EINVAL, "segs_per_cpu > %d", kMaxSegsPerCpu);
   ctx->geo_segs_per_cpu = segs_per_cpu;
   ctx->geo_min_tiles = min_tiles_per_seg;
+  return 0;
+}
+
+int hbt_set_decode_kernel(hbt_ctx* ctx, int which) {
+  if (!ctx) return -EINVAL;
+  if (which != HBT_KERNEL_AUTO && which != HBT_KERNEL_TILES && which != HBT_KERNEL_WALK)
+    return fail(ctx, -EINVAL, "unknown decode kernel %d", which);
+  ctx->kernel_choice = which;
   return 0;
 }
 

@@ -235,6 +235,17 @@ uint64_t hbt_launch_count(const hbt_ctx* ctx);
  * walks a whole ring, CpuEventsGroup.h:1348). */
 int hbt_set_geometry(hbt_ctx* ctx, uint32_t segs_per_cpu, uint32_t min_tiles_per_seg);
 
+/* Which of the two decode kernels runs.  HBT_KERNEL_TILES (k_decode): a CTA per segment, tiles staged
+ * in shared memory by TMA, a fast path for runs of equal-sized records -- the sampling streams.
+ * HBT_KERNEL_WALK (k_walk): a warp per segment, every lane follows header.size through its own
+ * kilobyte and the warp settles the seams -- streams of mixed record types (context-switch rings).
+ * HBT_KERNEL_AUTO (the default) picks by the handled record types.  Results never depend on it (the
+ * tests run both on the same input).  No counterpart in the reference. */
+#define HBT_KERNEL_AUTO 0
+#define HBT_KERNEL_TILES 1
+#define HBT_KERNEL_WALK 2
+int hbt_set_decode_kernel(hbt_ctx* ctx, int which);
+
 /* CPU ids reported in hbt_hist_entry are cpu_base + the ctx-local index: a rank
  * that holds the shard [cpu_base, cpu_base + n_cpus) of a larger machine sets it
  * (sharding by CPU id, PerCpuBase.h:26 keeps one generator per CPU). */

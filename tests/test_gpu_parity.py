@@ -14,9 +14,12 @@ import _oracle as orc
 pytestmark = pytest.mark.gpu
 
 
-@pytest.fixture(scope="module")
-def ctx(built):
+@pytest.fixture(scope="module", params=[hbt.KERNEL_TILES, hbt.KERNEL_WALK], ids=["tiles", "walk"])
+def ctx(built, request):
+    """Every test runs under both decode kernels (the choice only matters where k_walk covers the
+    aggregation; results must never depend on it)."""
     c = hbt.Context(0)
+    c.set_decode_kernel(request.param)
     yield c
     c.close()
 
