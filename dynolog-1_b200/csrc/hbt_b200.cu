@@ -443,7 +443,7 @@ static int launch_walk(hbt_ctx* ctx, const DecodeParams& p, uint32_t n_launch) {
                               (int)cudaSharedmemCarveoutMaxShared));
       ctx->walk_attr_set[AGG] = true;
     }
-    k_walk<AGG><<<(n_launch + kWalkWarps - 1) / kWalkWarps, 32 * kWalkWarps, kWalkWarps * kWalkSmemPerWarp,
+    k_walk<AGG><<<(n_launch + kWalkWarps - 1) / kWalkWarps, 32 * kWalkWarps, kWalkWarps * walk_smem_per_warp(AGG),
                   ctx->stream>>>(p, n_launch);
   }
   return 0;
