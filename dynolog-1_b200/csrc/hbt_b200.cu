@@ -267,7 +267,10 @@ static bool use_walk(const hbt_ctx* ctx) {
   const hbt_decode_desc& d = ctx->desc;
   if (d.aggregate == HBT_AGG_IP_HISTOGRAM) return false;
   if (ctx->kernel_choice != HBT_KERNEL_AUTO) return ctx->kernel_choice == HBT_KERNEL_WALK;
-  return d.aggregate == HBT_AGG_SWITCH_EVENTS;  // (measured: k_walk wins there, k_decode elsewhere)
+  // measured (profiles/r2_notes.md): k_walk wins on streams of mixed record types, k_decode's uniform fast
+  // path on runs of equal-sized samples
+  return (d.handled_mask & (HBT_H_COMM | HBT_H_EXIT | HBT_H_FORK | HBT_H_SWITCH_CPU_WIDE | HBT_H_AUX |
+                            HBT_H_ITRACE_START)) != 0;
 }
 
 // Build ring / segment tables for the current windows (+ clamps) into pinned

@@ -18,9 +18,12 @@
 // the next round, so only a segment's very first record remains a guess that k_finalize has to
 // confirm (as for k_decode).  No block barriers: warps of a CTA share nothing.
 //
-// Round = stage, pass A (guess + walk, counting record types on the way), seam resolution, pass B
-// (a second walk over the now exact records for the outputs that need stream-order indices:
-// proto-events, delta rows).
+// Round = stage; guess + walk (each lane marks the record starts of its chunk in a 32-bit mask, one
+// bit per word); seam resolution; then the record starts of the whole round are written to one list
+// in stream order and every per-record step -- type counters, size checks, proto-events, the
+// SAMPLE / LOST interval state and the delta rows -- runs over that list 32 records at a time, one
+// record per lane whatever its type or size, with ballots giving the stream-order indices.  The
+// walk, whose trip count differs from lane to lane, is only a header load and an add per record.
 //
 // Shared-memory layout: chunk j of the round lives at j * (256 + 8) bytes, so that lanes reading the
 // same offset of their own chunks (the common case: every lane starts at its chunk's first header)
@@ -39,15 +42,14 @@ constexpr int kWalkStaged = 34;                 // chunks staged per round (the 
 constexpr uint32_t kWalkStagedBytes = kWalkStaged * kWalkChunk;
 constexpr int kWalkWarps = 4;                   // warps (= segments) per CTA
 constexpr int kWalkStageSmem = kWalkStaged * kWalkPitch;
-// COUNT_DELTAS: {current, previous} SAMPLE of every row of the round, in row order (a SAMPLE is at
-// least 40 bytes even with nr = 0)
-constexpr int kWalkMaxRows = kWalkRound / 40 + 3;
+constexpr int kWalkList = 512;                  // record starts listed at a time (16-bit offsets)
 constexpr uint32_t kFarPrev = 0xFFFFFFFEu;      // "previous SAMPLE lies before this round"
-static_assert(kWalkChunk == 256, "WalkView shifts by 8");
-static_assert(kWalkStageSmem % 8 == 0, "row descriptors follow the staging slice");
+static_assert(kWalkChunk == 256, "WalkView shifts by 8; a chunk's record starts fit a 32-bit mask");
+static_assert(kWalkStageSmem % 8 == 0, "the lists follow the staging slice");
 
+// per warp: staging slice, record-start list, COUNT_DELTAS: {current, previous} SAMPLE of up to 32 rows
 __host__ __device__ constexpr int walk_smem_per_warp(int agg) {
-  return kWalkStageSmem + (agg == HBT_AGG_COUNT_DELTAS ? kWalkMaxRows * 8 : 0);
+  return kWalkStageSmem + kWalkList * 2 + (agg == HBT_AGG_COUNT_DELTAS ? 32 * 8 : 0);
 }
 
 struct WalkView {
@@ -59,131 +61,52 @@ struct WalkView {
   __device__ __forceinline__ uint64_t near(uint32_t r) const { return lds_u64(s + r + ((r >> 8) << 3)); }
   // any offset
   __device__ __forceinline__ uint64_t far(uint32_t r) const {
-    return r < kWalkStagedBytes ? near(r) : ring_word_g(*ring, base + r);
+    if (r < kWalkStagedBytes) return near(r);
+    return slow(base + r);
   }
+  __device__ __noinline__ uint64_t slow(uint64_t pos) const { return ring_word_g(*ring, pos); }
   // any ring position
   __device__ __forceinline__ uint64_t at(uint64_t pos) const {
     const uint64_t rel = pos - base;  // (positions before the round wrap to huge values)
-    return rel < (uint64_t)kWalkStagedBytes ? near((uint32_t)rel) : ring_word_g(*ring, pos);
+    if (rel < (uint64_t)kWalkStagedBytes) return near((uint32_t)rel);
+    return slow(pos);
   }
 };
-
-// events of a chunk, round-relative: (offset + 1) << 2 | kind, 0 = none
-__device__ __forceinline__ uint32_t rev_make(uint32_t r, uint32_t kind) { return ((r + 1) << 2) | kind; }
-__device__ __forceinline__ uint32_t rev_off(uint32_t e) { return (e >> 2) - 1; }
 
 struct WalkLane {
   uint32_t entry;    // first record start in my chunk (kNoRel: none)
   uint32_t exit;     // where my walk left the chunk
-  uint32_t err_r;
-  int32_t err;       // error met by the walk (only meaningful once the entry is confirmed)
-  uint32_t n_rec;
-  uint32_t n_handled;      // SWITCH_EVENTS: records that emit a proto-event
-  uint32_t n_lost;         // handled LOST records
-  uint64_t lost_sum;       // their num_lost
-  uint64_t cnt_lo, cnt_hi; // per-type counts, 8 bits each: counter index 0..7 / 8..10
-  // COUNT_DELTAS: the SAMPLE / LOST events of my chunk
-  uint32_t first_ev, last_ev;  // rev_make, 0 = none
-  uint32_t last_sample;        // offset + 1, 0 = none
-  uint32_t n_rows;             // SAMPLEs whose previous event (in my chunk) is a SAMPLE
-  uint32_t n_unknown;          // SAMPLEs whose previous event (in my chunk) is a LOST
+  uint32_t mask;     // bit k: a record starts at word k of my chunk
+  uint32_t bad;      // kNoRel, or the offset of a header that cannot be one (size < 8 or not a multiple of 8)
 };
 
-__device__ __forceinline__ void walk_clear(WalkLane& w) {
-  w.err = 0;
-  w.err_r = 0;
-  w.n_rec = w.n_handled = w.n_lost = 0;
-  w.lost_sum = 0;
-  w.cnt_lo = w.cnt_hi = 0;
-  w.first_ev = w.last_ev = 0;
-  w.last_sample = 0;
-  w.n_rows = w.n_unknown = 0;
-}
-
-// Follow header.size from offset `from` while records start before `end`, counting per type.  The
-// walk must be harmless on garbage (a guess may be wrong): it stops at the first header that cannot
-// be one, or that the decode mode refuses, and remembers why.
-template <int AGG>
-__device__ __forceinline__ void walk_chunk(const hbt_decode_desc& d, const WalkView& v, uint32_t from, uint32_t end,
-                                           uint32_t tmask, WalkLane& w) {
-  walk_clear(w);
-  const bool group_layout = d.sample_layout == HBT_SAMPLE_GROUP;
-  uint32_t k = EV_NONE;  // kind of the last SAMPLE / LOST event of this walk
+// Follow header.size from offset `from` while records start before `end` (both in the chunk that
+// begins at `chunk`), marking the starts.  Harmless on garbage (a guess may be wrong).
+__device__ __forceinline__ void walk_chunk(const WalkView& v, uint32_t chunk, uint32_t from, uint32_t end, WalkLane& w) {
+  w.mask = 0;
+  w.bad = kNoRel;
   uint32_t r = from;
   while (r < end) {
-    const uint64_t h = v.near(r);
-    const uint32_t type = hdr_type(h), size = hdr_size(h);
-    if (size < 8 || (size & 7)) {
-      w.err = -74;  // -EBADMSG
-      w.err_r = r;
+    const uint32_t size = (uint32_t)(v.near(r) >> 48);
+    if (((size - 8u) & 0xFFFF0007u) != 0) {  // size < 8 or not a multiple of 8
+      w.bad = r;
       break;
     }
-    if (counted(type, tmask)) {
-      const uint32_t ci = (uint32_t)(kCiNib >> (4 * type)) & 15u;
-      if (type == REC_SAMPLE || type == REC_READ) {
-        // hard size checks of consume() (CpuEventsGroup.h:1435-1440, 1451-1456)
-        const bool group = type == REC_READ || group_layout;
-        const uint64_t want = group ? 40 + 8 * v.near(r + 16) : d.ip_sample_bytes;
-        if ((uint64_t)size != want) {
-          w.err = -1;  // -EPERM
-          w.err_r = r;
-          break;
-        }
-      }
-      if (AGG == HBT_AGG_SWITCH_EVENTS) {
-        if (size < sw_min_size(type)) {  // the handler would read past the record
-          w.err = -1;
-          w.err_r = r;
-          break;
-        }
-        ++w.n_handled;
-      }
-      if (AGG == HBT_AGG_COUNT_DELTAS && type == REC_SAMPLE && group_layout) {
-        if (k == EV_NONE) w.first_ev = rev_make(r, EV_SAMPLE);
-        else if (k == EV_LOST) ++w.n_unknown;
-        else ++w.n_rows;
-        k = EV_SAMPLE;
-        w.last_ev = rev_make(r, EV_SAMPLE);
-        w.last_sample = r + 1;
-      }
-      if (type == REC_LOST) {
-        w.lost_sum += v.near(r + 16);
-        ++w.n_lost;
-        if (AGG == HBT_AGG_COUNT_DELTAS) {
-          if (k == EV_NONE) w.first_ev = rev_make(r, EV_LOST);
-          k = EV_LOST;
-          w.last_ev = rev_make(r, EV_LOST);
-        }
-      } else if (ci < 8) {
-        w.cnt_lo += 1ull << (8 * ci);
-      } else {
-        w.cnt_hi += 1ull << (8 * (ci - 8));
-      }
-    }
-    ++w.n_rec;
+    w.mask |= 1u << ((r - chunk) >> 3);
     r += size;
   }
   w.exit = r;
 }
 
 // First record start at or after offset `from` (below `end`) judged by looks: a plausible header
-// whose next three successors are plausible too (or lie beyond the window).  kNoRel if there is none.
+// whose successor is plausible too (or lies beyond the staged bytes / the window).  kNoRel if there
+// is none.  Only a guess: the seams decide.
 __device__ __forceinline__ uint32_t guess_entry(const WalkView& v, uint32_t from, uint32_t end, uint32_t head_r) {
   for (uint32_t q = from; q < end; q += 8) {
-    uint64_t h = v.near(q);
+    const uint64_t h = v.near(q);
     if (!plausible(h)) continue;
-    uint32_t nx = q + hdr_size(h);
-    bool ok = true;
-#pragma unroll 1
-    for (int k = 0; k < 3 && nx < head_r; ++k) {
-      h = v.far(nx);
-      if (!plausible(h)) {
-        ok = false;
-        break;
-      }
-      nx += hdr_size(h);
-    }
-    if (ok) return q;
+    const uint32_t nx = q + hdr_size(h);
+    if (nx >= head_r || nx >= kWalkStagedBytes || plausible(v.near(nx))) return q;
   }
   return kNoRel;
 }
@@ -248,9 +171,20 @@ __device__ __forceinline__ ulonglong2 sw_proto_flat(const WalkView& v, uint32_t 
   return make_ulonglong2(ts, sw_word1(et, lost ? (uint32_t)HBT_LEVEL_INVALID : level, cu, tag));
 }
 
+__device__ __forceinline__ void prefetch_l2(const void* p) {
+  asm volatile("prefetch.global.L2 [%0];" ::"l"(p));
+}
+__device__ __forceinline__ void sts_u16(uint32_t saddr, uint32_t v) {
+  asm volatile("st.shared.u16 [%0], %1;" ::"r"(saddr), "h"((unsigned short)v) : "memory");
+}
+__device__ __forceinline__ uint32_t lds_u16(uint32_t saddr) {
+  unsigned short r;
+  asm volatile("ld.shared.u16 %0, [%1];" : "=h"(r) : "r"(saddr));
+  return r;
+}
+
 template <int AGG>
-__global__ void __launch_bounds__(32 * kWalkWarps, AGG == HBT_AGG_COUNT_DELTAS ? 5 : 6)
-    k_walk(const DecodeParams p, uint32_t n_launch) {
+__global__ void __launch_bounds__(32 * kWalkWarps, 5) k_walk(const DecodeParams p, uint32_t n_launch) {
   extern __shared__ __align__(16) uint8_t walk_smem[];
   const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const uint32_t gw = blockIdx.x * kWalkWarps + warp;
@@ -261,18 +195,27 @@ __global__ void __launch_bounds__(32 * kWalkWarps, AGG == HBT_AGG_COUNT_DELTAS ?
   const hbt_decode_desc& d = p.d;
   const uint32_t tmask = type_mask(d.handled_mask);
   constexpr unsigned FULL = 0xffffffffu;
-  const bool ev_samples = AGG == HBT_AGG_COUNT_DELTAS && d.sample_layout == HBT_SAMPLE_GROUP;
+  const uint32_t lt = (1u << lane) - 1u;
+  const bool group_layout = d.sample_layout == HBT_SAMPLE_GROUP;
+  const bool ev_samples = AGG == HBT_AGG_COUNT_DELTAS && group_layout;
   const uint32_t row_words = 2 + d.n_events;
   // cooperative row writer: lane -> (row of the batch, word of the row)
   const uint32_t rows_per_iter = row_words <= 32 ? 32 / row_words : 0;
   const uint32_t sub_row = rows_per_iter ? lane / row_words : 0;
   const uint32_t sub_col = rows_per_iter ? lane - sub_row * row_words : lane;
+  // word `col` of a row: column 0 = previous tstamp, 1 = tstamp - previous, 2 + i = value i - previous
+  // value i (both through the TSC transform when bit i of the mask asks for it)
+  auto col_off = [](uint32_t col) { return col < 2 ? 8u : 40u + 8u * (col - 2); };
+  const uint32_t sub_off = col_off(sub_col);
+  const bool sub_xf = sub_col >= 2 && ((d.tsc_transform_mask >> (sub_col - 2)) & 1);
 
   WalkView v;
   v.s = smem_u32(walk_smem) + warp * walk_smem_per_warp(AGG);
   v.ring = &ring;
-  const uint32_t s_desc = v.s + kWalkStageSmem;  // COUNT_DELTAS: row descriptors
+  const uint32_t s_list = v.s + kWalkStageSmem;    // record starts of the round (16-bit offsets)
+  const uint32_t s_desc = s_list + kWalkList * 2;  // COUNT_DELTAS: {current, previous} of up to 32 rows
   const bool src16 = (reinterpret_cast<uintptr_t>(ring.base) & 15) == 0;
+  const uint32_t chunk = lane * kWalkChunk;
 
   // records are decoded while they START in [seg_lo, seg_limit)
   const uint64_t seg_lo = max(seg.tile_begin * (uint64_t)kTile, ring.tail);
@@ -284,12 +227,12 @@ __global__ void __launch_bounds__(32 * kWalkWarps, AGG == HBT_AGG_COUNT_DELTAS ?
   int32_t err = 0;
   uint64_t err_pos = 0;
   // warp-uniform running state
-  uint64_t n_rows = 0;           // rows / proto-events written so far
+  uint64_t n_rec = 0, n_rows = 0, n_unknown = 0;
+  uint32_t n_lost = 0;
   uint64_t ev = 0;               // last SAMPLE / LOST event so far (ev_make)
   uint64_t last_sample = kNone;
   uint64_t seg_first_ev = 0;     // the segment's first SAMPLE when no event precedes it (the seam)
   // per-lane accumulators, reduced when the segment is done
-  uint32_t acc_rec = 0, acc_lost_n = 0, acc_unknown = 0;
   uint64_t acc_lost = 0;
   uint64_t acc_lo = 0, acc_hi = 0;  // packed 8-bit counts of the rounds since the last flush
   uint32_t acc_rounds = 0;
@@ -329,32 +272,40 @@ __global__ void __launch_bounds__(32 * kWalkWarps, AGG == HBT_AGG_COUNT_DELTAS ?
       }
     }
     __syncwarp();
+    // the next round's lines on their way into L2 while this one is decoded
+    if (base + kWalkRound < seg_limit) {
+#pragma unroll
+      for (uint32_t ln = lane; ln < kWalkStagedBytes / 128; ln += 32)
+        prefetch_l2(ring.base + ((base + kWalkRound + ln * 128) & ring.mask));
+    }
 
     // round-relative geometry: the segment's part of the round, my chunk's part of that
     const uint32_t lo_r = seg_lo > base ? (uint32_t)(seg_lo - base) : 0u;
     const uint32_t lim_r = (uint32_t)min(seg_limit - base, (uint64_t)kWalkRound);
     const uint32_t head_r = (uint32_t)min(ring.head - base, (uint64_t)0xFFFF0000u);
-    const uint32_t cs = max(lane * kWalkChunk, lo_r);
-    const uint32_t ce = min((lane + 1) * kWalkChunk, lim_r);
+    const uint32_t cs = max(chunk, lo_r);
+    const uint32_t ce = min(chunk + kWalkChunk, lim_r);
     const bool have = cs < ce;
     // where the chain enters the round (kNoRel: the segment still guesses)
     const uint32_t pos_r = pos == kNone ? kNoRel : (uint32_t)min(pos - base, (uint64_t)0xFFFF0000u);
 
-    // ---- pass A: guess and walk -------------------------------------------------------------
+    // ---- guess and walk -------------------------------------------------------------------------
     WalkLane w;
-    walk_clear(w);
     w.entry = kNoRel;
     w.exit = 0;
+    w.mask = 0;
+    w.bad = kNoRel;
     if (have) {
       if (pos_r != kNoRel && pos_r >= cs && pos_r < ce) w.entry = pos_r;  // the exact entry lies in my chunk
       else if (pos_r != kNoRel && pos_r >= ce) w.entry = kNoRel;          // a record spans my whole chunk
       else w.entry = guess_entry(v, cs, ce, head_r);  // (the host's entry_hint is of no use here: it may
                                                       //  name a record that is not the FIRST one)
-      if (w.entry != kNoRel) walk_chunk<AGG>(d, v, w.entry, ce, tmask, w);
+      if (w.entry != kNoRel) walk_chunk(v, chunk, w.entry, ce, w);
     }
 
     // ---- seams: lane l must start where the records before it end --------------------------------
-    uint32_t cur;  // where the chain leaves the round (kNoRel: still nothing found)
+    uint32_t cur;              // where the chain leaves the round (kNoRel: still nothing found)
+    uint32_t bad_r = kNoRel;   // a header on the confirmed chain that cannot be one
     {
       // if every guess is right: the chain position in front of my chunk is the exit of the nearest
       // walk before me (exits grow with the lane), else what the round inherited
@@ -366,12 +317,12 @@ __global__ void __launch_bounds__(32 * kWalkWarps, AGG == HBT_AGG_COUNT_DELTAS ?
       if (before == kNoRel) ok = true;  // nothing known in front of me
       else if (!have || before >= ce) ok = w.entry == kNoRel;
       else ok = w.entry == before;
-      ok = ok && w.err == 0;
+      ok = ok && w.bad == kNoRel;
       if (__all_sync(FULL, ok)) {
         const uint32_t last = __shfl_sync(FULL, incl, 31);
         cur = last ? last - 1 : pos_r;
       } else {
-        // some guess was wrong (or a walk met an error): settle the lanes one after the other
+        // some guess was wrong (or a walk met a bad header): settle the lanes one after the other
         cur = pos_r;
         for (int l = 0; l < 32; ++l) {
           const uint32_t l_cs = max((uint32_t)l * kWalkChunk, lo_r);
@@ -390,14 +341,12 @@ __global__ void __launch_bounds__(32 * kWalkWarps, AGG == HBT_AGG_COUNT_DELTAS ?
           }
           if (lane == l && w.entry != cur) {  // wrong (or no) guess: walk again from the right place
             w.entry = cur;
-            walk_chunk<AGG>(d, v, cur, ce, tmask, w);
+            walk_chunk(v, chunk, cur, ce, w);
           }
-          const int32_t e_l = __shfl_sync(FULL, w.err, l);
           cur = __shfl_sync(FULL, w.exit, l);
-          if (e_l != 0) {  // a real error on the confirmed chain: consume() stops in front of that record
-            err = e_l;
-            err_pos = base + __shfl_sync(FULL, w.err_r, l);
-            if ((int)lane > l) w.entry = kNoRel;  // records consume() never reaches
+          bad_r = __shfl_sync(FULL, w.bad, l);
+          if (bad_r != kNoRel) {  // consume() stops in front of that header (-EBADMSG) ...
+            if ((int)lane > l) w.entry = kNoRel;  // ... and never reaches what lies behind it
             break;
           }
         }
@@ -407,176 +356,182 @@ __global__ void __launch_bounds__(32 * kWalkWarps, AGG == HBT_AGG_COUNT_DELTAS ?
       const uint32_t m = __reduce_min_sync(FULL, w.entry);
       if (m != kNoRel) entry = base + m;
     }
-    if (w.entry == kNoRel) walk_clear(w);
-    const uint32_t stop = w.err ? w.err_r : ce;  // my records start in [w.entry, stop)
+    if (w.entry == kNoRel) w.mask = 0;
 
-    // ---- pass B: outputs that need stream-order indices ------------------------------------------
-    if (AGG == HBT_AGG_SWITCH_EVENTS) {
-      const uint32_t incl = warp_sum_scan_incl(w.n_handled, lane);
-      uint64_t row_i = n_rows + (incl - w.n_handled);
-      if (w.n_handled) {
-        uint32_t q = w.entry;
-        while (q < stop) {
-          const uint64_t h = v.near(q);
-          if (counted(hdr_type(h), tmask)) {
-            const ulonglong2 e = sw_proto_flat(v, q, h, d.tid_level, p.cpu_base + seg.cpu);
-            if (row_i < seg.rows_cap) *reinterpret_cast<ulonglong2*>(seg.rows + (1 + row_i) * 2) = e;
-            ++row_i;
-          }
-          q += hdr_size(h);
+    // ---- the round's records in stream order, 32 at a time -----------------------------------------
+    const uint32_t my_n = __popc(w.mask);
+    const uint32_t incl_n = warp_sum_scan_incl(my_n, lane);
+    const uint32_t my_first = incl_n - my_n;
+    const uint32_t n_round = __shfl_sync(FULL, incl_n, 31);
+    for (uint32_t b0 = 0; b0 < n_round && err == 0; b0 += kWalkList) {
+      __syncwarp();  // the readers of the previous list are done
+      {
+        uint32_t m = w.mask, k = my_first;
+        while (m) {
+          const uint32_t bit = __ffs(m) - 1;
+          m &= m - 1;
+          if (k - b0 < (uint32_t)kWalkList) sts_u16(s_list + (k - b0) * 2, chunk + bit * 8);
+          ++k;
         }
       }
-      n_rows += __shfl_sync(FULL, incl, 31);
-    }
-    if (AGG == HBT_AGG_COUNT_DELTAS) {
-      // the event in front of my chunk: last event of the nearest lane before me that has one, else
-      // what the segment has seen so far
-      const uint32_t incl_ev = warp_max_scan_incl(w.last_ev, lane);
-      uint32_t in_rev = __shfl_up_sync(FULL, incl_ev, 1);
-      if (lane == 0) in_rev = 0;
-      const uint32_t in_kind = in_rev ? (in_rev & 3u) : ev_kind(ev);
-      uint32_t my_rows, my_unknown;
-      uint64_t my_seam;
-      auto derive = [&]() {
-        my_rows = w.n_rows;
-        my_unknown = w.n_unknown;
-        my_seam = 0;
-        if ((w.first_ev & 3u) == EV_SAMPLE) {
-          if (in_kind == EV_SAMPLE) ++my_rows;            // interval from the previous SAMPLE
-          else if (in_kind == EV_LOST) ++my_unknown;      // re-seed, PerCpuCountSampleGenerator.h:135-154
-          else my_seam = ev_make(base + rev_off(w.first_ev), EV_SAMPLE);  // nothing before it in this
-        }                                                                  // segment: k_finalize's seam
-      };
-      derive();
-      const uint32_t incl_r = warp_sum_scan_incl(my_rows, lane);
-      const uint32_t row0 = incl_r - my_rows;  // my first row of the round
-      int32_t late_err = 0;
-      uint32_t late_r = 0;
-      if (w.last_ev != 0) {
-        // second walk: {current, previous} of each of my rows, checked like the generator checks them
-        bool valid = in_kind == EV_SAMPLE;
-        uint32_t prev = in_rev ? rev_off(in_rev) : kFarPrev;  // (kFarPrev: the SAMPLE ev names)
-        uint32_t row_i = row0;
-        uint32_t q = w.entry;
-        while (q < stop) {
-          const uint64_t h = v.near(q);
-          const uint32_t type = hdr_type(h);
-          if (counted(type, tmask)) {
-            if (type == REC_SAMPLE && ev_samples) {
-              if (valid) {
-                const uint64_t ts = v.near(q + 8);
-                const uint64_t pts = prev == kFarPrev ? ring_word_g(ring, ev_pos(ev) + 8) : v.near(prev + 8);
-                if (pts > ts) {  // :156-163: the interval is refused, consume() stops in front of the record
-                  late_err = -1;
-                  late_r = q;
-                  break;
-                }
-                if (n_rows + row_i >= seg.rows_cap) {  // (only with nr != n_events) a full output ring, :191-194
-                  late_err = -28;
-                  late_r = q;
-                  break;
-                }
-                if (row_i < (uint32_t)kWalkMaxRows) sts_u32x2(s_desc + row_i * 8, q, prev);
-                ++row_i;
+      __syncwarp();
+      const uint32_t n_list = min(n_round - b0, (uint32_t)kWalkList);
+      for (uint32_t i0 = 0; i0 < n_list && err == 0; i0 += 32) {
+        bool act = i0 + lane < n_list;
+        const uint32_t r = act ? lds_u16(s_list + (i0 + lane) * 2) : 0u;
+        const uint64_t h = v.near(r);
+        const uint32_t type = hdr_type(h), size = hdr_size(h);
+        bool cnt = act && counted(type, tmask);
+        // hard size checks of consume() (CpuEventsGroup.h:1435-1440, 1451-1456) and of the handlers
+        int32_t e = 0;
+        if (cnt && (type == REC_SAMPLE || type == REC_READ)) {
+          const bool group = type == REC_READ || group_layout;
+          const uint64_t want = group ? 40 + 8 * v.near(r + 16) : d.ip_sample_bytes;
+          if ((uint64_t)size != want) e = -1;  // -EPERM
+        }
+        if (AGG == HBT_AGG_SWITCH_EVENTS && cnt && size < sw_min_size(type)) e = -1;  // the handler would read
+                                                                                       // past the record
+        // COUNT_DELTAS: the SAMPLE / LOST sequence (PerCpuCountSampleGenerator.h:122-195)
+        bool is_s = false, is_l = cnt && type == REC_LOST, row = false, regress = false;
+        uint32_t prev_kind = EV_NONE, prev_rel = kFarPrev, smask = 0, lmask = 0;
+        if (AGG == HBT_AGG_COUNT_DELTAS) {
+          is_s = cnt && e == 0 && type == REC_SAMPLE && ev_samples;
+          smask = __ballot_sync(FULL, is_s);
+          lmask = __ballot_sync(FULL, is_l);
+          // the event in front of me: the nearest SAMPLE / LOST below my lane, else what came before
+          const uint32_t below = (smask | lmask) & lt;
+          const uint32_t pl = below ? 31 - __clz(below) : 0;
+          const uint32_t r_pl = __shfl_sync(FULL, r, pl);
+          if (below) {
+            prev_kind = ((smask >> pl) & 1u) ? EV_SAMPLE : EV_LOST;
+            prev_rel = r_pl;
+          } else {
+            prev_kind = ev_kind(ev);
+            prev_rel = (ev != 0 && ev_pos(ev) >= base) ? (uint32_t)(ev_pos(ev) - base) : kFarPrev;
+          }
+          if (is_s && prev_kind == EV_SAMPLE) {
+            const uint64_t ts = v.near(r + 8);
+            const uint64_t pts = prev_rel == kFarPrev ? ring_word_g(ring, ev_pos(ev) + 8) : v.near(prev_rel + 8);
+            if (pts > ts) {  // :156-163: the interval is refused, consume() stops in front of the record
+              e = -1;
+              regress = true;
+            } else {
+              row = true;
+            }
+          }
+        }
+        // consume() stops in front of the first record that fails: it and everything behind it is dropped
+        bool invalidate = false;  // the failure came from the generator, which invalidates its interval
+        auto cut = [&](uint32_t f, int32_t code) {
+          err = code;
+          err_pos = base + __shfl_sync(FULL, r, f);
+          const bool keep = lane < f;
+          act = act && keep;
+          cnt = cnt && keep;
+          is_s = is_s && keep;
+          is_l = is_l && keep;
+          row = row && keep;
+          smask &= (1u << f) - 1u;
+          lmask &= (1u << f) - 1u;
+        };
+        const uint32_t em = __ballot_sync(FULL, e != 0);
+        if (em) {
+          const uint32_t f = __ffs(em) - 1;
+          invalidate = __shfl_sync(FULL, regress ? 1 : 0, f) != 0;
+          cut(f, __shfl_sync(FULL, e, f));
+        }
+        uint32_t rowmask = 0;
+        if (AGG == HBT_AGG_COUNT_DELTAS) {
+          rowmask = __ballot_sync(FULL, row);
+          // (only with nr != n_events records) the slab is a full output ring, :191-194
+          const uint32_t full = __ballot_sync(FULL, row && n_rows + __popc(rowmask & lt) >= seg.rows_cap);
+          if (full) {
+            invalidate = true;
+            cut(__ffs(full) - 1, -28);
+            rowmask = __ballot_sync(FULL, row);
+          }
+        }
+
+        // ---- counters ----------------------------------------------------------------------------
+        n_rec += __popc(__ballot_sync(FULL, act));
+        n_lost += __popc(__ballot_sync(FULL, is_l));
+        if (is_l) acc_lost += v.near(r + 16);
+        {
+          const uint32_t ci = (uint32_t)(kCiNib >> (4 * (type & 15))) & 15u;
+          const bool plain = cnt && !is_l;
+          acc_lo += (plain && ci < 8) ? 1ull << (8 * (ci & 7)) : 0ull;
+          acc_hi += (plain && ci >= 8) ? 1ull << (8 * (ci & 7)) : 0ull;
+        }
+
+        // ---- proto-events ------------------------------------------------------------------------
+        if (AGG == HBT_AGG_SWITCH_EVENTS) {
+          const uint32_t hm = __ballot_sync(FULL, cnt);
+          if (cnt) {
+            const uint64_t row_i = n_rows + __popc(hm & lt);
+            const ulonglong2 pe = sw_proto_flat(v, r, h, d.tid_level, p.cpu_base + seg.cpu);
+            if (row_i < seg.rows_cap) *reinterpret_cast<ulonglong2*>(seg.rows + (1 + row_i) * 2) = pe;
+          }
+          n_rows += __popc(hm);
+        }
+
+        // ---- delta rows --------------------------------------------------------------------------
+        if (AGG == HBT_AGG_COUNT_DELTAS) {
+          n_unknown += __popc(__ballot_sync(FULL, is_s && prev_kind == EV_LOST));  // re-seed, :135-154
+          const uint32_t evm = smask | lmask;
+          if (ev == 0 && evm != 0 && seg_first_ev == 0) {
+            // the segment's first event: a SAMPLE here is the seam k_finalize joins to the segment before
+            const uint32_t f = __ffs(evm) - 1;
+            const uint32_t r_f = __shfl_sync(FULL, r, f);
+            if ((smask >> f) & 1u) seg_first_ev = ev_make(base + r_f, EV_SAMPLE);
+          }
+          const uint32_t n_row = __popc(rowmask);
+          if (n_row) {
+            const uint64_t far_abs = ev_pos(ev);  // what kFarPrev names
+            if (row) sts_u32x2(s_desc + __popc(rowmask & lt) * 8, r, prev_rel);
+            __syncwarp();
+            // written by the whole warp: lane -> one word of a row
+            uint64_t* const out = seg.rows + (1 + n_rows) * row_words;
+            auto emit = [&](uint32_t rr, uint32_t col, uint32_t off, bool xf) {
+              const uint2 cp = lds_u32x2(s_desc + rr * 8);
+              uint64_t b = cp.y == kFarPrev ? ring_word_g(ring, far_abs + off) : v.far(cp.y + off);
+              uint64_t a = v.far(cp.x + off);
+              if (xf) {
+                a = tsc_to_ktime(a, d.tsc);
+                b = tsc_to_ktime(b, d.tsc);
               }
-              valid = true;
-              prev = q;
-            } else if (type == REC_LOST) {
-              valid = false;
-            }
-          }
-          q += hdr_size(h);
-        }
-      }
-      const uint32_t bad = __ballot_sync(FULL, late_err != 0);
-      uint32_t round_rows = __shfl_sync(FULL, incl_r, 31);
-      if (bad) {
-        // consume() stops in front of that SAMPLE: what my walk counted behind it, and every lane
-        // behind me, is dropped
-        const int l = __ffs(bad) - 1;
-        err = __shfl_sync(FULL, late_err, l);
-        const uint32_t e_r = __shfl_sync(FULL, late_r, l);
-        err_pos = base + e_r;
-        if ((int)lane == l) {
-          const uint32_t keep_entry = w.entry;
-          walk_chunk<AGG>(d, v, keep_entry, e_r, tmask, w);
-          derive();
-          w.last_ev = rev_make(e_r, EV_LOST);  // count_.tstamp = invalid
-        } else if ((int)lane > l) {
-          w.entry = kNoRel;
-          walk_clear(w);
-          my_rows = my_unknown = 0;
-          my_seam = 0;
-        }
-        round_rows = __reduce_add_sync(FULL, my_rows);
-        cur = e_r;
-      }
-      __syncwarp();  // the descriptors are complete
-
-      // rows of the round, written by the whole warp: lane -> one word of a row
-      if (rows_per_iter) {
-        for (uint32_t r0 = 0; r0 < round_rows; r0 += rows_per_iter) {
-          const uint32_t rr = r0 + sub_row;
-          if (sub_row < rows_per_iter && rr < round_rows) {
-            const uint2 cp = lds_u32x2(s_desc + rr * 8);
-            auto prev_word = [&](uint32_t off) {
-              return cp.y == kFarPrev ? ring_word_g(ring, ev_pos(ev) + off) : v.far(cp.y + off);
+              out[rr * row_words + col] = col == 0 ? b : a - b;
             };
-            uint64_t x;
-            if (sub_col == 0) x = prev_word(8);
-            else if (sub_col == 1) x = v.near(cp.x + 8) - prev_word(8);
-            else {
-              const uint32_t i = sub_col - 2;
-              x = xform(d, i, v.far(cp.x + 40 + 8 * i)) - xform(d, i, prev_word(40 + 8 * i));
+            if (rows_per_iter) {
+              for (uint32_t r0 = sub_row; r0 < n_row; r0 += rows_per_iter)
+                if (sub_row < rows_per_iter) emit(r0, sub_col, sub_off, sub_xf);
+            } else {
+              for (uint32_t rr = 0; rr < n_row; ++rr)
+                for (uint32_t col = lane; col < row_words; col += 32)
+                  emit(rr, col, col_off(col), col >= 2 && ((d.tsc_transform_mask >> (col - 2)) & 1));
             }
-            seg.rows[(1 + n_rows + rr) * row_words + sub_col] = x;
+            __syncwarp();  // the descriptors may be overwritten
+            n_rows += n_row;
           }
-        }
-      } else {
-        for (uint32_t rr = 0; rr < round_rows; ++rr) {
-          const uint2 cp = lds_u32x2(s_desc + rr * 8);
-          auto prev_word = [&](uint32_t off) {
-            return cp.y == kFarPrev ? ring_word_g(ring, ev_pos(ev) + off) : v.far(cp.y + off);
-          };
-          for (uint32_t col = lane; col < row_words; col += 32) {
-            uint64_t x;
-            if (col == 0) x = prev_word(8);
-            else if (col == 1) x = v.near(cp.x + 8) - prev_word(8);
-            else {
-              const uint32_t i = col - 2;
-              x = xform(d, i, v.far(cp.x + 40 + 8 * i)) - xform(d, i, prev_word(40 + 8 * i));
-            }
-            seg.rows[(1 + n_rows + rr) * row_words + col] = x;
+          if (evm) {
+            const uint32_t l = 31 - __clz(evm);
+            ev = ev_make(base + __shfl_sync(FULL, r, l), ((smask >> l) & 1u) ? EV_SAMPLE : EV_LOST);
           }
+          if (smask) last_sample = base + __shfl_sync(FULL, r, 31 - __clz(smask));
+          if (invalidate) ev = ev_make(err_pos, EV_LOST);  // count_.tstamp = invalid
         }
-      }
-      n_rows += round_rows;
-      acc_unknown += my_unknown;
-      const uint32_t le = __reduce_max_sync(FULL, w.last_ev);
-      if (le) ev = ev_make(base + rev_off(le), le & 3u);
-      const uint32_t ls = __reduce_max_sync(FULL, w.last_sample);
-      if (ls) last_sample = base + ls - 1;
-      if (seg_first_ev == 0) {
-        const uint32_t seam_r = __reduce_max_sync(FULL, my_seam ? rev_off(w.first_ev) + 1 : 0u);
-        if (seam_r) seg_first_ev = ev_make(base + seam_r - 1, EV_SAMPLE);
       }
     }
-
-    // ---- keep the lanes' counts ------------------------------------------------------------------
-    acc_rec += w.n_rec;
-    acc_lost_n += w.n_lost;
-    acc_lost += w.lost_sum;
-    acc_lo += w.cnt_lo;
-    acc_hi += w.cnt_hi;
-    if (++acc_rounds == 7) flush();  // 7 rounds x 32 records per lane stay below 256
+    if (err == 0 && bad_r != kNoRel) {
+      err = -74;  // -EBADMSG
+      err_pos = base + bad_r;
+    }
+    if (err) cur = (uint32_t)(err_pos - base);
+    if (++acc_rounds == 7) flush();  // 7 rounds x at most 32 records per lane stay below 256
     pos = cur == kNoRel ? kNone : base + cur;  // exact from here on
   }
 
   flush();
-  const uint64_t n_rec = warp_sum64(acc_rec);
-  const uint32_t n_lost = __reduce_add_sync(FULL, acc_lost_n);
   const uint64_t lost_sum = warp_sum64(acc_lost);
-  const uint32_t n_unknown = __reduce_add_sync(FULL, acc_unknown);
   SegResult& r = p.results[seg_index];
   if (lane < HBT_NUM_COUNTERS) r.counters[lane] = lane == HBT_CNT_LOST ? lost_sum : total;
   if (lane == 0) {
