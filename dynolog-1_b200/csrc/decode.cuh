@@ -1956,34 +1956,62 @@ __device__ __forceinline__ uint64_t merge_path(TA A, uint64_t la, TB B, uint64_t
 }
 
 // tile_prefix[p] = first CTA of pair p (host-computed from the offsets), [n_pairs] = grid size.
-// A CTA merges kMergeTile consecutive outputs of its pair: two binary searches in global
-// memory cut the pair's inputs at the tile's diagonals, the two input pieces (together
-// exactly one tile) are staged in shared memory with coalesced loads, and every thread
-// merges its kMergeK outputs from there.
+// A CTA merges kMergeTile consecutive outputs of its pair.  Where the tile's diagonals cut the pair's
+// two inputs is found by k_sw_cuts beforehand, one thread per tile: the ~20 dependent probes of that
+// binary search in global memory used to be most of a merge CTA's lifetime, with 254 of its threads
+// waiting at a barrier.
+struct MergePair {
+  uint64_t a0, la, lb;   // first input event of the pair, lengths of its two runs
+  uint32_t first_tile;   // first CTA of the pair
+  uint32_t last;         // 1: the CTA asked for is the pair's last
+};
+__device__ __forceinline__ MergePair merge_pair_of(uint32_t tile, const uint64_t* __restrict__ offsets, uint32_t n_cpus,
+                                                   uint32_t run, const uint32_t* __restrict__ tile_prefix,
+                                                   uint32_t n_pairs) {
+  uint32_t lo = 0, hi = n_pairs - 1;
+  while (lo < hi) {  // largest p with tile_prefix[p] <= tile
+    const uint32_t mid = (lo + hi + 1) >> 1;
+    if (tile_prefix[mid] <= tile) lo = mid;
+    else hi = mid - 1;
+  }
+  MergePair m;
+  m.a0 = offsets[min(2 * lo * run, n_cpus)];
+  const uint64_t b0 = offsets[min((2 * lo + 1) * run, n_cpus)];
+  const uint64_t b1 = offsets[min((2 * lo + 2) * run, n_cpus)];
+  m.la = b0 - m.a0;
+  m.lb = b1 - b0;
+  m.first_tile = tile_prefix[lo];
+  m.last = tile + 1 == tile_prefix[lo + 1];
+  return m;
+}
+
+static __global__ void __launch_bounds__(256)
+    k_sw_cuts(const ulonglong2* __restrict__ in, const uint64_t* __restrict__ offsets, uint32_t n_cpus, uint32_t run,
+              const uint32_t* __restrict__ tile_prefix, uint32_t n_pairs, uint32_t n_tiles,
+              uint64_t* __restrict__ cuts) {
+  const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= n_tiles) return;
+  const MergePair m = merge_pair_of(t, offsets, n_cpus, run, tile_prefix, n_pairs);
+  const ulonglong2* A = in + m.a0;
+  cuts[t] = merge_path(A, m.la, A + m.la, m.lb, (uint64_t)(t - m.first_tile) * kMergeTile);
+}
+
+// The two input pieces of the tile (together exactly one tile) are staged in shared memory with
+// coalesced loads, every thread merges its kMergeK outputs from there into registers, and the outputs
+// leave through the same shared memory (padded: one slot after every kMergeK, so that the threads'
+// strided stores spread over the banks) as coalesced stores.
 static __global__ void __launch_bounds__(256)
     k_sw_merge(const ulonglong2* __restrict__ in, ulonglong2* __restrict__ out,
                const uint64_t* __restrict__ offsets, uint32_t n_cpus, uint32_t run,
-               const uint32_t* __restrict__ tile_prefix, uint32_t n_pairs) {
-  __shared__ ulonglong2 s_ev[kMergeTile];
-  __shared__ uint64_t s_cut[2];
+               const uint32_t* __restrict__ tile_prefix, uint32_t n_pairs, const uint64_t* __restrict__ cuts) {
+  __shared__ ulonglong2 s_ev[kMergeTile + kMergeTile / kMergeK];
   const uint32_t tid = threadIdx.x;
-  uint32_t lo = 0, hi = n_pairs - 1;
-  while (lo < hi) {  // largest p with tile_prefix[p] <= blockIdx.x
-    const uint32_t mid = (lo + hi + 1) >> 1;
-    if (tile_prefix[mid] <= blockIdx.x) lo = mid;
-    else hi = mid - 1;
-  }
-  const uint64_t a0 = offsets[min(2 * lo * run, n_cpus)];
-  const uint64_t b0 = offsets[min((2 * lo + 1) * run, n_cpus)];
-  const uint64_t b1 = offsets[min((2 * lo + 2) * run, n_cpus)];
-  const uint64_t la = b0 - a0, lb = b1 - b0;
-  const ulonglong2* A = in + a0;
-  const ulonglong2* B = in + b0;
-  const uint64_t d0 = (uint64_t)(blockIdx.x - tile_prefix[lo]) * kMergeTile;
-  const uint64_t d1 = min(d0 + kMergeTile, la + lb);
-  if (tid < 2) s_cut[tid] = merge_path(A, la, B, lb, tid == 0 ? d0 : d1);
-  __syncthreads();
-  const uint64_t i0 = s_cut[0], i1 = s_cut[1];
+  const MergePair m = merge_pair_of(blockIdx.x, offsets, n_cpus, run, tile_prefix, n_pairs);
+  const ulonglong2* A = in + m.a0;
+  const ulonglong2* B = A + m.la;
+  const uint64_t d0 = (uint64_t)(blockIdx.x - m.first_tile) * kMergeTile;
+  const uint64_t d1 = min(d0 + kMergeTile, m.la + m.lb);
+  const uint64_t i0 = cuts[blockIdx.x], i1 = m.last ? m.la : cuts[blockIdx.x + 1];
   const uint32_t na = (uint32_t)(i1 - i0), n = (uint32_t)(d1 - d0), nb = n - na;
   for (uint32_t i = tid; i < n; i += 256) s_ev[i] = i < na ? A[i0 + i] : B[(d0 - i0) + (i - na)];
   __syncthreads();
@@ -1992,12 +2020,22 @@ static __global__ void __launch_bounds__(256)
   const uint32_t dd = min(tid * kMergeK, n);
   uint32_t ai = (uint32_t)merge_path(sA, (uint64_t)na, sB, (uint64_t)nb, (uint64_t)dd);
   uint32_t bi = dd - ai;
-  ulonglong2* o = out + a0 + d0 + dd;
   const uint32_t cnt = min(kMergeK, n - dd);
-  for (uint32_t j = 0; j < cnt; ++j) {
-    const bool take_a = bi >= nb || (ai < na && ev_before(sA[ai], sB[bi]));
-    o[j] = take_a ? sA[ai++] : sB[bi++];
+  ulonglong2 o[kMergeK];
+#pragma unroll
+  for (uint32_t j = 0; j < kMergeK; ++j) {
+    if (j < cnt) {
+      const bool take_a = bi >= nb || (ai < na && ev_before(sA[ai], sB[bi]));
+      o[j] = take_a ? sA[ai++] : sB[bi++];
+    }
   }
+  __syncthreads();  // every thread has read its inputs
+#pragma unroll
+  for (uint32_t j = 0; j < kMergeK; ++j)
+    if (j < cnt) s_ev[dd + j + tid] = o[j];  // (dd + j) + (dd + j) / kMergeK
+  __syncthreads();
+  ulonglong2* dst = out + m.a0 + d0;
+  for (uint32_t i = tid; i < n; i += 256) dst[i] = s_ev[i + i / kMergeK];
 }
 
 }  // namespace hbt

@@ -164,6 +164,7 @@ struct hbt_ctx {
   DevBuf<hbt_switch_event> sw_events;
   DevBuf<hbt_switch_event> sw_merge[2];       // ping-pong buffers of the Combinator tree levels
   DevBuf<uint32_t> d_merge_prefix;
+  DevBuf<uint64_t> d_merge_cuts;  // per merge tile: where its first diagonal cuts the pair's first run
   PinBuf<uint32_t> h_merge_prefix;
   const hbt_switch_event* sw_merged = nullptr;  // result of the last merge, nullptr = not merged yet
   bool sw_valid = false;  // sw_events / h_sw_off describe the last fetched decode
@@ -722,6 +723,7 @@ void hbt_destroy(hbt_ctx* ctx) {
   ctx->sw_merge[0].release();
   ctx->sw_merge[1].release();
   ctx->d_merge_prefix.release();
+  ctx->d_merge_cuts.release();
   ctx->h_merge_prefix.release();
   ctx->hist_entries.release();
   ctx->hist_cursors.release();
@@ -1399,17 +1401,29 @@ int hbt_switch_events_merged_dev(hbt_ctx* ctx, const hbt_switch_event** merged, 
       memcpy(ctx->h_merge_prefix.p, prefix.data(), prefix.size() * sizeof(uint32_t));
       CU(cudaMemcpyAsync(ctx->d_merge_prefix.p, ctx->h_merge_prefix.p, prefix.size() * sizeof(uint32_t),
                          cudaMemcpyHostToDevice, ctx->stream));
+      {
+        uint32_t max_grid = 1;
+        for (size_t l = 0; l < level_at.size(); ++l) {
+          const size_t end = l + 1 < level_at.size() ? level_at[l + 1] : prefix.size();
+          max_grid = std::max(max_grid, prefix[end - 1]);
+        }
+        CU(ctx->d_merge_cuts.reserve(max_grid));
+      }
       uint32_t level = 0;
       for (uint32_t run = 1; run < C; run *= 2, which ^= 1, ++level) {
         CU(ctx->sw_merge[which].reserve(total));
         const uint32_t n_pairs = (C + 2 * run - 1) / (2 * run);
         const uint32_t* pre = ctx->d_merge_prefix.p + level_at[level];
         const uint32_t grid = prefix[level_at[level] + n_pairs];
-        if (grid)
+        if (grid) {
+          k_sw_cuts<<<(grid + 255) / 256, 256, 0, ctx->stream>>>(reinterpret_cast<const ulonglong2*>(cur),
+                                                                 ctx->d_sw_off.p, C, run, pre, n_pairs, grid,
+                                                                 ctx->d_merge_cuts.p);
           k_sw_merge<<<grid, 256, 0, ctx->stream>>>(
-              reinterpret_cast<const ulonglong2*>(cur),
-              reinterpret_cast<ulonglong2*>(ctx->sw_merge[which].p), ctx->d_sw_off.p, C, run, pre, n_pairs);
-        ++ctx->launches;
+              reinterpret_cast<const ulonglong2*>(cur), reinterpret_cast<ulonglong2*>(ctx->sw_merge[which].p),
+              ctx->d_sw_off.p, C, run, pre, n_pairs, ctx->d_merge_cuts.p);
+          ctx->launches += 2;
+        }
         cur = ctx->sw_merge[which].p;
       }
       CU(cudaGetLastError());
