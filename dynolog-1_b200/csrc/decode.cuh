@@ -2013,29 +2013,51 @@ static __global__ void __launch_bounds__(256)
   const uint64_t d1 = min(d0 + kMergeTile, m.la + m.lb);
   const uint64_t i0 = cuts[blockIdx.x], i1 = m.last ? m.la : cuts[blockIdx.x + 1];
   const uint32_t na = (uint32_t)(i1 - i0), n = (uint32_t)(d1 - d0), nb = n - na;
-  for (uint32_t i = tid; i < n; i += 256) s_ev[i] = i < na ? A[i0 + i] : B[(d0 - i0) + (i - na)];
+  // element k of the tile lives at k + k / kMergeK: the threads walk the two runs at strides of a few
+  // elements, which without the padding puts a quarter-warp's 16-byte loads on the same banks
+  auto P = [](uint32_t k) { return k + k / kMergeK; };
+  for (uint32_t i = tid; i < n; i += 256) s_ev[P(i)] = i < na ? A[i0 + i] : B[(d0 - i0) + (i - na)];
   __syncthreads();
-  const ulonglong2* sA = s_ev;
-  const ulonglong2* sB = s_ev + na;
+  auto sA = [&](uint32_t i) -> const ulonglong2& { return s_ev[P(i)]; };
+  auto sB = [&](uint32_t i) -> const ulonglong2& { return s_ev[P(na + i)]; };
   const uint32_t dd = min(tid * kMergeK, n);
-  uint32_t ai = (uint32_t)merge_path(sA, (uint64_t)na, sB, (uint64_t)nb, (uint64_t)dd);
-  uint32_t bi = dd - ai;
+  uint32_t ai, bi;
+  {  // merge path inside the tile
+    uint32_t il = dd > nb ? dd - nb : 0, ih = min(dd, na);
+    while (il < ih) {
+      const uint32_t mid = (il + ih) >> 1;
+      if (ev_before(sA(mid), sB(dd - 1 - mid))) il = mid + 1;
+      else ih = mid;
+    }
+    ai = il;
+    bi = dd - il;
+  }
   const uint32_t cnt = min(kMergeK, n - dd);
   ulonglong2 o[kMergeK];
+  // the heads of the two runs stay in registers: one shared-memory load per output
+  ulonglong2 ha = ai < na ? sA(ai) : make_ulonglong2(~0ull, ~0ull);
+  ulonglong2 hb = bi < nb ? sB(bi) : make_ulonglong2(~0ull, ~0ull);
 #pragma unroll
   for (uint32_t j = 0; j < kMergeK; ++j) {
     if (j < cnt) {
-      const bool take_a = bi >= nb || (ai < na && ev_before(sA[ai], sB[bi]));
-      o[j] = take_a ? sA[ai++] : sB[bi++];
+      const bool take_a = bi >= nb || (ai < na && ev_before(ha, hb));
+      o[j] = take_a ? ha : hb;
+      if (take_a) {
+        ++ai;
+        if (ai < na) ha = sA(ai);
+      } else {
+        ++bi;
+        if (bi < nb) hb = sB(bi);
+      }
     }
   }
   __syncthreads();  // every thread has read its inputs
 #pragma unroll
   for (uint32_t j = 0; j < kMergeK; ++j)
-    if (j < cnt) s_ev[dd + j + tid] = o[j];  // (dd + j) + (dd + j) / kMergeK
+    if (j < cnt) s_ev[dd + j + tid] = o[j];  // P(dd + j)
   __syncthreads();
   ulonglong2* dst = out + m.a0 + d0;
-  for (uint32_t i = tid; i < n; i += 256) dst[i] = s_ev[i + i / kMergeK];
+  for (uint32_t i = tid; i < n; i += 256) dst[i] = s_ev[P(i)];
 }
 
 }  // namespace hbt
