@@ -261,6 +261,7 @@ class Context:
         if rc != 0:
             raise HbtError(rc, "hbt_create failed (no usable sm_100 CUDA device?)")
         self.h = h
+        self.kernel = KERNEL_AUTO
         self.device = device
 
     def close(self):
@@ -305,6 +306,7 @@ class Context:
     def set_decode_kernel(self, which: int = 0):
         """KERNEL_AUTO / KERNEL_TILES (k_decode) / KERNEL_WALK (k_walk)."""
         self._ck(self.lib.hbt_set_decode_kernel(self.h, which))
+        self.kernel = which
 
     def set_geometry(self, segs_per_cpu: int = 0, min_tiles_per_seg: int = 0):
         """Segments per CPU / tiles per segment of the decode (0 = automatic)."""

@@ -137,6 +137,8 @@ struct DecodeParams {
   uint32_t cpu_base;  // SWITCH_EVENTS: comp_unit_id = cpu_base + cpu
   // a re-run decodes only the segments listed here (null: CTA i decodes segment i)
   const uint32_t* run_list;
+  // k_walk's look-back: per segment, 1 once its exit is in results[] (null: no look-back)
+  uint32_t* seg_flag;
 };
 
 // ---------------------------------------------------------------------------

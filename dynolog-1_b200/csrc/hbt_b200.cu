@@ -139,6 +139,7 @@ struct hbt_ctx {
   PinBuf<uint32_t> h_run_list;
   uint32_t n_run = 0;
   DevBuf<uint8_t> d_cpu_done;
+  DevBuf<uint32_t> d_seg_flag;  // per segment: its exit is published (k_walk's look-back)
   PinBuf<uint8_t> h_cpu_done;
   uint64_t rerun_segments = 0;  // segments decoded again by the re-runs of the last decode
   uint32_t geo_segs_per_cpu = 0, geo_min_tiles = 0;  // hbt_set_geometry; 0 = automatic
@@ -406,6 +407,7 @@ int build_tables(hbt_ctx* ctx, const uint64_t* clamp_head, const int64_t* clamp_
   CU(ctx->d_forced.reserve(ns));
   CU(ctx->h_seam.reserve(ns));
   CU(ctx->d_run_list.reserve(ns));
+  CU(ctx->d_seg_flag.reserve(ns));
   CU(ctx->h_run_list.reserve(ns));
   if (!segs.empty()) memcpy(ctx->h_segs.p, segs.data(), segs.size() * sizeof(SegDesc));
   return 0;  // k_prepare (run_once) moves the tables to the device
@@ -424,6 +426,7 @@ struct PrepareParams {
   const uint32_t* cursors; uint32_t* cursors_snap; uint32_t n_lists;  // n_lists = 0: no snapshot
   const uint32_t* src_run; uint32_t* dst_run; uint32_t n_run;
   uint8_t* cpu_done; uint32_t n_done_reset;  // first attempt: every CPU is open again
+  uint32_t* seg_flag; uint32_t n_seg_flags;  // k_walk's look-back flags: all of them, or those of the re-run's segments
 };
 
 static __global__ void k_prepare(PrepareParams p) {
@@ -436,6 +439,11 @@ static __global__ void k_prepare(PrepareParams p) {
   for (uint32_t i = t0; i < p.n_lists; i += stride) p.cursors_snap[i] = p.cursors[i];
   for (uint32_t i = t0; i < p.n_run; i += stride) p.dst_run[i] = p.src_run[i];
   for (uint32_t i = t0; i < p.n_done_reset; i += stride) p.cpu_done[i] = 0;
+  if (p.n_run) {
+    for (uint32_t i = t0; i < p.n_run; i += stride) p.seg_flag[p.src_run[i]] = 0;
+  } else {
+    for (uint32_t i = t0; i < p.n_seg_flags; i += stride) p.seg_flag[i] = 0;
+  }
   if (t0 < 4) p.flags[t0] = 0;
 }
 
@@ -468,6 +476,7 @@ int launch_decode_agg(hbt_ctx* ctx) {
   p.hist.overflow = ctx->hist_overflow.p;
   p.cpu_base = ctx->cpu_base;
   p.run_list = ctx->n_run ? ctx->d_run_list.p : nullptr;
+  p.seg_flag = ctx->walk ? ctx->d_seg_flag.p : nullptr;
   if (ctx->n_segs == 0) return 0;
   const uint32_t n_launch = ctx->n_run ? ctx->n_run : ctx->n_segs;
   if (ctx->walk) {
@@ -560,6 +569,8 @@ int run_once(hbt_ctx* ctx, bool snapshot_cursors) {
   }
   pp.cpu_done = ctx->d_cpu_done.p;
   pp.n_done_reset = ctx->n_run ? 0 : ctx->n_cpus;  // the first attempt of a decode opens every CPU
+  pp.seg_flag = ctx->d_seg_flag.p;
+  pp.n_seg_flags = ctx->n_segs;
   if (ctx->n_run) {
     CU(cudaHostGetDevicePointer(&dp, ctx->h_run_list.p, 0));
     pp.src_run = static_cast<const uint32_t*>(dp);
@@ -704,6 +715,7 @@ void hbt_destroy(hbt_ctx* ctx) {
   ctx->d_run_list.release();
   ctx->h_run_list.release();
   ctx->d_cpu_done.release();
+  ctx->d_seg_flag.release();
   ctx->h_cpu_done.release();
   ctx->h_slabs.release();
   ctx->h_rings.release();

@@ -174,6 +174,14 @@ __device__ __forceinline__ ulonglong2 sw_proto_flat(const WalkView& v, uint32_t 
 __device__ __forceinline__ void prefetch_l2(const void* p) {
   asm volatile("prefetch.global.L2 [%0];" ::"l"(p));
 }
+__device__ __forceinline__ void st_release_u32(uint32_t* p, uint32_t v) {
+  asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ uint32_t ld_acquire_u32(const uint32_t* p) {
+  uint32_t v;
+  asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
 __device__ __forceinline__ void sts_u16(uint32_t saddr, uint32_t v) {
   asm volatile("st.shared.u16 [%0], %1;" ::"r"(saddr), "h"((unsigned short)v) : "memory");
 }
@@ -221,8 +229,15 @@ __global__ void __launch_bounds__(32 * kWalkWarps, 5) k_walk(const DecodeParams 
   const uint64_t seg_lo = max(seg.tile_begin * (uint64_t)kTile, ring.tail);
   const uint64_t seg_limit = min(seg.tile_end * (uint64_t)kTile, ring.head);
 
+  // Where the segment starts: exact for a CPU's first segment and for a forced re-run, else a guess
+  // (kNone).  A guess is checked twice: here, against the exit of the segment in front as soon as that
+  // one has published it (look-back below: a wrong guess is repaired by a second walk in the same
+  // launch), and by k_finalize, which stays the authority and walks the whole chain afterwards.
+  uint64_t start = seg.seg == 0 ? ring.tail : seg.forced_entry;
+  bool published = false;
+  for (uint32_t attempt = 0;; ++attempt) {
   // exact next record start, or kNone while the segment still guesses its entry
-  uint64_t pos = seg.seg == 0 ? ring.tail : seg.forced_entry;
+  uint64_t pos = start;
   uint64_t entry = kNone;  // first record start decoded (k_finalize checks it against the chain)
   int32_t err = 0;
   uint64_t err_pos = 0;
@@ -545,9 +560,45 @@ __global__ void __launch_bounds__(32 * kWalkWarps, 5) k_walk(const DecodeParams 
     r.last_sample = last_sample;
     r.err = err;
     r.err_pos = err_pos;
-    r.slow_tiles = 0;
+    r.slow_tiles = attempt;  // 1: the segment was walked twice (its entry guess was wrong)
     r.hist_overflow = 0;
     r.n_lost_recs = n_lost;
+  }
+  if (p.seg_flag == nullptr) break;
+  // ---- look-back ------------------------------------------------------------------------------
+  // Publish my exit for the segment behind me -- at once when it can be trusted (the walk went through
+  // to the segment's end: record chains that start apart meet again after a few records, so the exit
+  // rarely depends on the entry), otherwise (the walk stopped at an error, maybe only because its
+  // entry was wrong) after my own entry is settled.
+  auto publish = [&]() {
+    __syncwarp();
+    if (lane == 0 && !published) {
+      __threadfence();
+      st_release_u32(p.seg_flag + seg_index, 1u);
+    }
+    published = true;
+  };
+  if (err == 0 || attempt != 0 || seg.seg == 0 || start != kNone) publish();
+  if (attempt != 0 || seg.seg == 0 || start != kNone) break;  // my entry was exact, or is repaired
+  // Compare my guess with the exit of the segment in front (same CPU: the table keeps a CPU's segments
+  // together; it was launched before me, so it is running or done; the chain of waits ends at the
+  // CPU's first segment, whose entry is exact).  The wait is bounded: should the flag never come,
+  // k_finalize settles it the long way.
+  uint64_t want = kNone;
+  if (lane == 0) {
+    uint32_t f = 0;
+    for (uint32_t i = 0; i < (1u << 18) && !f; ++i) {
+      f = ld_acquire_u32(p.seg_flag + seg_index - 1);
+      if (!f) __nanosleep(100);
+    }
+    if (f) want = *reinterpret_cast<const volatile uint64_t*>(&p.results[seg_index - 1].exit);
+  }
+  want = __shfl_sync(FULL, want, 0);
+  if (want == kNone || (want >= seg_limit ? entry == kNone : entry == want)) {  // no answer, or the guess was right
+    publish();
+    break;
+  }
+  start = want;                                                       // walk again from the right place
   }
 }
 
