@@ -1824,53 +1824,104 @@ struct SwParams {
 
 __device__ __forceinline__ bool sw_is_lost(uint64_t w1) { return (uint32_t)(w1 & 0xFF) == HBT_SWEV_WRITE_ERRORS_START; }
 
-// launched as one CTA of >= n_cpus threads (n_cpus <= HBT_MAX_CPUS = 512)
-static __global__ void __launch_bounds__(512) k_sw_scan(const SwParams p) {
-  const uint32_t c = threadIdx.x;
-  uint64_t total = 0;
-  if (c < p.n_cpus) {
+// launched as ONE CTA of 1024 threads (n_cpus <= HBT_MAX_CPUS = 512): warp w chains the segments of CPUs
+// w, w + 32, ... 32 segments at a time -- every lane fetches one segment's numbers, ballots find each
+// segment's non-empty predecessor and a shuffle scan gives the offsets (the first version walked a CPU's
+// segments with one thread: three dependent global loads per segment, 0.2 ms with k_walk's many segments)
+static __global__ void __launch_bounds__(1024) k_sw_scan(const SwParams p) {
+  __shared__ uint64_t s_tot[512];
+  const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  constexpr unsigned FULL = 0xffffffffu;
+  for (uint32_t c = warp; c < 512; c += 32) {
+    if (c >= p.n_cpus) {
+      if (lane == 0) s_tot[c] = 0;
+      continue;
+    }
     const RingDesc ring = p.rings[c];
-    uint64_t prev_ts = p.state_ts[c];
+    uint64_t prev_ts = p.state_ts[c];      // of the last non-empty segment so far (warp-uniform)
     uint32_t prev_lost = p.state_err[c];
-    for (uint32_t s = 0; s < ring.n_seg; ++s) {
-      const uint32_t gi = ring.seg_begin + s;
-      SwSeg& w = p.sw[gi];
+    uint64_t total = 0;
+    for (uint32_t s0 = 0; s0 < ring.n_seg; s0 += 32) {
+      const uint32_t s = s0 + lane;
+      const bool in = s < ring.n_seg;
+      const uint32_t gi = ring.seg_begin + (in ? s : 0);
       // the segment's protos that belong to this call, its last proto, and the LOST protos in
       // front of that one (each gives its successor a WriteErrorsEnd)
-      w.n = (p.seg_flags[gi] & 2) ? (uint32_t)p.results[gi].n_rows : 0u;
-      if (w.n) {
-        const uint64_t* last = p.segs[gi].rows + 2 + 2 * (uint64_t)(w.n - 1);  // slot 0 = unused seam slot
-        w.last_ts = last[0];
-        w.last_lost = sw_is_lost(last[1]);
-        w.lost_inner = p.results[gi].n_lost_recs - w.last_lost;
+      uint32_t n = 0, last_lost = 0, lost_inner = 0;
+      uint64_t last_ts = 0;
+      if (in && (p.seg_flags[gi] & 2)) n = (uint32_t)p.results[gi].n_rows;
+      if (n) {
+        const uint64_t* last = p.segs[gi].rows + 2 + 2 * (uint64_t)(n - 1);  // slot 0 = unused seam slot
+        last_ts = last[0];
+        last_lost = sw_is_lost(last[1]);
+        lost_inner = p.results[gi].n_lost_recs - last_lost;
       }
-      w.base = total;
-      w.prev_ts = prev_ts;
-      w.prev_lost = prev_lost;
-      if (w.n) {
-        total += w.n + w.lost_inner + prev_lost;
-        prev_ts = w.last_ts;
-        prev_lost = w.last_lost;
+      // the non-empty segment in front of mine: the nearest lane below with protos, else the carry
+      const uint32_t have = __ballot_sync(FULL, n != 0);
+      const uint32_t below = have & ((1u << lane) - 1u);
+      const uint32_t pl = below ? 31 - __clz(below) : 0;
+      const uint64_t ts_pl = __shfl_sync(FULL, last_ts, pl);
+      const uint32_t lost_pl = __shfl_sync(FULL, last_lost, pl);
+      const uint64_t my_prev_ts = below ? ts_pl : prev_ts;
+      const uint32_t my_prev_lost = below ? lost_pl : prev_lost;
+      const uint64_t mine = n ? (uint64_t)n + lost_inner + my_prev_lost : 0;
+      uint64_t incl = mine;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        const uint64_t y = __shfl_up_sync(FULL, incl, o);
+        if (lane >= (unsigned)o) incl += y;
+      }
+      if (in) {
+        SwSeg& w = p.sw[gi];
+        w.n = n;
+        if (n) {
+          w.last_ts = last_ts;
+          w.last_lost = last_lost;
+          w.lost_inner = lost_inner;
+        }
+        w.base = total + (incl - mine);
+        w.prev_ts = my_prev_ts;
+        w.prev_lost = my_prev_lost;
+      }
+      total += __shfl_sync(FULL, incl, 31);
+      if (have) {
+        const uint32_t l = 31 - __clz(have);
+        prev_ts = __shfl_sync(FULL, last_ts, l);
+        prev_lost = __shfl_sync(FULL, last_lost, l);
       }
     }
-    p.state_ts[c] = prev_ts;
-    p.state_err[c] = prev_lost;
-    hbt_cpu_result& o = p.out[c];
-    o.n_rows = total;
-    o.carry_tstamp = prev_ts;                 // last_tstamp_
-    o.num_unknown_count_interval = prev_lost; // in_write_errors_
+    if (lane == 0) {
+      p.state_ts[c] = prev_ts;
+      p.state_err[c] = prev_lost;
+      hbt_cpu_result& o = p.out[c];
+      o.n_rows = total;
+      o.carry_tstamp = prev_ts;                 // last_tstamp_
+      o.num_unknown_count_interval = prev_lost; // in_write_errors_
+      s_tot[c] = total;
+    }
   }
-  // exclusive prefix sum of the totals over the CPUs
-  __shared__ uint64_t s_tot[512];
-  s_tot[threadIdx.x] = total;
   __syncthreads();
-  if (threadIdx.x == 0) {
-    uint64_t run = 0;
-    for (uint32_t i = 0; i < p.n_cpus; ++i) {
-      p.offsets[i] = run;
-      run += s_tot[i];
+  // exclusive prefix sum of the totals over the CPUs (warp 0, 16 CPUs per lane)
+  if (warp == 0) {
+    uint64_t loc[16], sum = 0;
+#pragma unroll
+    for (int k = 0; k < 16; ++k) {
+      loc[k] = sum;
+      sum += s_tot[lane * 16 + k];
     }
-    p.offsets[p.n_cpus] = run;
+    uint64_t incl = sum;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const uint64_t y = __shfl_up_sync(FULL, incl, o);
+      if (lane >= (unsigned)o) incl += y;
+    }
+    const uint64_t base = incl - sum;
+#pragma unroll
+    for (int k = 0; k < 16; ++k) {
+      const uint32_t c = lane * 16 + k;
+      if (c < p.n_cpus) p.offsets[c] = base + loc[k];
+    }
+    if (lane == 31) p.offsets[p.n_cpus] = incl;
   }
 }
 

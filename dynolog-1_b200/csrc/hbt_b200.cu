@@ -1140,7 +1140,7 @@ static int complete_decode(hbt_ctx* ctx) {
     sp.n_cpus = C;
     sp.n_segs = ctx->n_segs;
     sp.cpu_base = ctx->cpu_base;
-    k_sw_scan<<<1, 512, 0, ctx->stream>>>(sp);
+    k_sw_scan<<<1, 1024, 0, ctx->stream>>>(sp);
     ++ctx->launches;
     CU(cudaGetLastError());
     CU(cudaMemcpyAsync(ctx->h_sw_off.p, ctx->d_sw_off.p, (C + 1) * sizeof(uint64_t),
