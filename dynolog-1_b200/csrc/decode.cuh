@@ -1378,6 +1378,13 @@ __global__ void __launch_bounds__(32) k_finalize(const FinalizeParams p) {
   if (p.cpu_done[c]) return;  // settled by an earlier attempt of this decode
   __shared__ SegResult s_res[32];
   __shared__ SegDesc s_seg[32];
+  // Timestamps the chain walk compares, fetched by the whole warp before lane 0 walks the chunk (the walk
+  // itself then touches shared memory only), and the seam rows it decides on, written by the whole warp
+  // after it: global-memory latency is paid per chunk of 32 segments, not per segment.
+  __shared__ uint64_t s_ts_first[32];   // tstamp of the segment's first SAMPLE (when first_ev is one)
+  __shared__ uint64_t s_ts_last[32];    // tstamp of the segment's last SAMPLE (when there is one)
+  __shared__ uint64_t s_seam_prev[32];  // seam row wanted: the previous SAMPLE (kPrevCarry = carry arrays); kNone = no row
+  __shared__ uint64_t s_seam_pts[32];   // its tstamp
   const RingDesc ring = p.rings[c];
   const hbt_decode_desc& d = p.d;
   const CpuState& sin = p.state_in[c];
@@ -1395,9 +1402,8 @@ __global__ void __launch_bounds__(32) k_finalize(const FinalizeParams p) {
   int32_t err = 0;
   bool redo = false;
 
-  auto prev_ts = [&]() {
-    return prev_pos == kPrevCarry ? sin.carry_tstamp : ring_word_g(ring, prev_pos + 8);
-  };
+  uint64_t prev_ts_val = sin.carry_tstamp;  // tstamp of the SAMPLE prev_pos names
+  auto prev_ts = [&]() { return prev_ts_val; };
   auto prev_val = [&](uint32_t i) {
     return prev_pos == kPrevCarry ? sin.carry_last[i]
                                   : xform(d, i, ring_word_g(ring, prev_pos + 40 + 8ull * i));
@@ -1419,6 +1425,15 @@ __global__ void __launch_bounds__(32) k_finalize(const FinalizeParams p) {
       for (uint32_t w = lane; w < n_chunk * (uint32_t)(sizeof(SegDesc) / 8); w += 32) dst[w] = src[w];
     }
     __syncwarp();
+    if (p.agg == HBT_AGG_COUNT_DELTAS) {
+      s_seam_prev[lane] = kNone;
+      if (lane < n_chunk) {
+        const SegResult& r = s_res[lane];
+        if (ev_kind(r.first_ev) == EV_SAMPLE) s_ts_first[lane] = ring_word_g(ring, ev_pos(r.first_ev) + 8);
+        if (r.last_sample != kNone) s_ts_last[lane] = ring_word_g(ring, r.last_sample + 8);
+      }
+      __syncwarp();
+    }
     if (lane == 0) {
   for (uint32_t j = 0; j < n_chunk; ++j) {
     const uint32_t s = s0 + j;
@@ -1461,7 +1476,7 @@ __global__ void __launch_bounds__(32) k_finalize(const FinalizeParams p) {
       // whose timestamp check precedes the write: the seam row is only counted when it would be written)
       uint64_t seg_rows = r.n_rows;
       if (ev_kind(r.first_ev) == EV_SAMPLE && valid &&
-          !(prev_ts() > ring_word_g(ring, ev_pos(r.first_ev) + 8)))
+          !(prev_ts() > s_ts_first[j]))
         ++seg_rows;
       if (n_rows + seg_rows > p.rows_budget[c]) {
         p.clamp_head[c] = kClampLocate;
@@ -1476,7 +1491,7 @@ __global__ void __launch_bounds__(32) k_finalize(const FinalizeParams p) {
     // seam: the segment's first SAMPLE had no SAMPLE/LOST before it in the segment
     if (p.agg == HBT_AGG_COUNT_DELTAS && ev_kind(r.first_ev) == EV_SAMPLE) {
       const uint64_t sp = ev_pos(r.first_ev);
-      const uint64_t ts = ring_word_g(ring, sp + 8);
+      const uint64_t ts = s_ts_first[j];
       if (!valid) {
         ++unknown;  // re-seed (PerCpuCountSampleGenerator.h:135-154)
       } else {
@@ -1488,11 +1503,8 @@ __global__ void __launch_bounds__(32) k_finalize(const FinalizeParams p) {
           redo = true;
           { stop = true; break; }
         }
-        uint64_t* row = sd.rows;  // slot 0 of the slab
-        row[0] = pts;
-        row[1] = ts - pts;
-        for (uint32_t i = 0; i < d.n_events; ++i)
-          row[2 + i] = xform(d, i, ring_word_g(ring, sp + 40 + 8ull * i)) - prev_val(i);
+        s_seam_prev[j] = prev_pos;  // slot 0 of the slab: written by the whole warp below
+        s_seam_pts[j] = pts;
         p.seam_valid[gi] = 1;
         ++n_rows;
       }
@@ -1503,7 +1515,10 @@ __global__ void __launch_bounds__(32) k_finalize(const FinalizeParams p) {
     unknown += r.n_unknown;
     for (int i = 0; i < HBT_NUM_COUNTERS; ++i) counters[i] += r.counters[i];
     if (r.last_ev != 0) valid = ev_kind(r.last_ev) == EV_SAMPLE;
-    if (r.last_sample != kNone) prev_pos = r.last_sample;
+    if (r.last_sample != kNone) {
+      prev_pos = r.last_sample;
+      prev_ts_val = s_ts_last[j];
+    }
     pos = r.exit;
     if (r.err) {
       err = r.err;
@@ -1519,6 +1534,26 @@ __global__ void __launch_bounds__(32) k_finalize(const FinalizeParams p) {
   }
     }
     stop = __shfl_sync(0xffffffffu, stop ? 1 : 0, 0) != 0;
+    __syncwarp();
+    if (p.agg == HBT_AGG_COUNT_DELTAS) {
+      // the seam rows of this chunk: work item = (segment, word of its row), spread over the lanes
+      const uint32_t W = 2 + d.n_events;
+      for (uint32_t k = lane; k < n_chunk * W; k += 32) {
+        const uint32_t j = k / W, col = k - j * W;
+        const uint64_t pp = s_seam_prev[j];
+        if (pp == kNone) continue;
+        const uint64_t sp = ev_pos(s_res[j].first_ev);
+        uint64_t x;
+        if (col == 0) x = s_seam_pts[j];
+        else if (col == 1) x = s_ts_first[j] - s_seam_pts[j];
+        else {
+          const uint32_t i = col - 2;
+          const uint64_t pv = pp == kPrevCarry ? sin.carry_last[i] : xform(d, i, ring_word_g(ring, pp + 40 + 8ull * i));
+          x = xform(d, i, ring_word_g(ring, sp + 40 + 8ull * i)) - pv;
+        }
+        s_seg[j].rows[col] = x;
+      }
+    }
     __syncwarp();  // the staging buffers are reused by the next chunk
   }
   if (lane != 0) return;
