@@ -587,9 +587,9 @@ __global__ void __launch_bounds__(32 * kWalkWarps, 5) k_walk(const DecodeParams 
   uint64_t want = kNone;
   if (lane == 0) {
     uint32_t f = 0;
-    for (uint32_t i = 0; i < (1u << 18) && !f; ++i) {
+    for (uint32_t i = 0; i < (1u << 16) && !f; ++i) {
       f = ld_acquire_u32(p.seg_flag + seg_index - 1);
-      if (!f) __nanosleep(100);
+      if (!f) __nanosleep(400);
     }
     if (f) want = *reinterpret_cast<const volatile uint64_t*>(&p.results[seg_index - 1].exit);
   }
