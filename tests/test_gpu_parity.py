@@ -575,6 +575,35 @@ def test_unknown_types_and_giant_records(ctx):
     check_cpu(ctx, 0, res[0], orc.consume(ring, tail, head, desc), desc)
 
 
+@pytest.mark.parametrize("mode", [hbt.MODE_SAMPLING, hbt.MODE_MIXED])
+def test_tiny_records(ctx, mode):
+    """Runs of 8- and 16-byte records (THROTTLE / UNTHROTTLE are counted in every mode, type 70 is only
+    skipped): up to 1024 record starts per 8 KiB, the most k_walk's per-round record list and the 8-bit
+    per-lane type counters have to take, with ordinary samples in between."""
+    ds = 1 << 19
+    rng = np.random.default_rng(3)
+    words, total = [], 0
+    while total < (ds - 9000) // 8:
+        k = int(rng.integers(0, 6))
+        if k == 0:      # a long run of 8-byte THROTTLE records
+            rec = [tg.header(tg.REC_THROTTLE, 8)] * int(rng.integers(200, 3000))
+        elif k == 1:    # 16-byte UNTHROTTLE records
+            rec = [tg.header(tg.REC_UNTHROTTLE, 16), 5] * int(rng.integers(50, 800))
+        elif k == 2:    # 8-byte records of a type nobody handles
+            rec = [70 | (8 << 48)] * int(rng.integers(10, 600))
+        else:
+            rec = [tg.header(tg.REC_SAMPLE, 56), 1000 + total, 2, 5, 5, total, 2 * total]
+        words += rec
+        total += len(rec)
+    import torch
+    s = torch.tensor(np.array(words, dtype=np.uint64).view(np.int64))
+    tail = tg.random_tail(21, ds)
+    ring, head = ring_np(s, ds, tail)
+    for desc in (hbt.sampling_desc(2), hbt.count_desc(mode)):
+        res = gpu_decode(ctx, [(ring, tail, head)], desc, ds)
+        check_cpu(ctx, 0, res[0], orc.consume(ring, tail, head, desc), desc)
+
+
 def test_zero_size_record_stops(ctx):
     ds, E = 1 << 17, 8
     s = tg.group_sample_stream(5, 800, E).clone()
