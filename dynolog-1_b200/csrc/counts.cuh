@@ -191,8 +191,14 @@ __device__ __forceinline__ void counts_epilogue_narrow(const CountsArgs& a, uint
 // the epilogue themselves.  When a stage holds fewer than 8 intervals each interval
 // is cut into row slices so that all 8 warps have work; the slices meet in a small
 // shared-memory table.  Needs C*W even (16-byte aligned interval starts).
-constexpr int kCountsStageBytes = 48 * 1024;
-constexpr int kCountsStages = 2;
+#ifndef HBT_COUNTS_STAGE_KB
+#define HBT_COUNTS_STAGE_KB 48
+#endif
+#ifndef HBT_COUNTS_STAGES
+#define HBT_COUNTS_STAGES 2
+#endif
+constexpr int kCountsStageBytes = HBT_COUNTS_STAGE_KB * 1024;
+constexpr int kCountsStages = HBT_COUNTS_STAGES;
 
 static __global__ void __launch_bounds__(256, 2)
     k_counts_reduce_tma(const CountsArgs a, uint32_t per_stage) {
@@ -226,8 +232,7 @@ static __global__ void __launch_bounds__(256, 2)
     bulk_g2s_hint(cs_smem + s * kCountsStageBytes, a.reads + i0 * N, bytes, &bar[s], policy);
   };
   if (tid == 0) {
-    issue(0);
-    if (n_chunks > 1) issue(1);
+    for (int k0 = 0; k0 < kCountsStages && (uint64_t)k0 < n_chunks; ++k0) issue(k0);
   }
   uint32_t phase_bits = 0;
   for (uint64_t k = 0; k < n_chunks; ++k) {
