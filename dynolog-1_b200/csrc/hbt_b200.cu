@@ -1976,8 +1976,10 @@ int hbt_counts_pipeline_sharded_dev(hbt_ctx* ctx, const uint64_t* reads, uint64_
     scaled = ctx->c_scaled.p;
   }
   // Interval chunks: the collective of chunk k (own stream) runs while chunk k+1 is reduced.
-  // Chunks of >= 4 MiB of sums keep the all-reduce out of its latency-bound regime.
-  uint64_t n_chunks = n_intervals * W * 8 / (4u << 20);
+  // Chunks of >= 2 MiB of sums per rank keep the all-reduce out of its latency-bound regime (an
+  // all-reduce over 8 ranks costs ~100 us whatever its size below a few MiB: eight 4-MiB chunks made the
+  // exchange half of config 5's step at N=8).
+  uint64_t n_chunks = n_intervals * W * 8 / ((uint64_t)(2u << 20) * (uint64_t)std::max(ctx->n_ranks, 2));
   if (n_chunks < 1) n_chunks = 1;
   if (n_chunks > (uint64_t)kMaxCommChunks) n_chunks = kMaxCommChunks;
   const uint64_t per = (n_intervals + n_chunks - 1) / n_chunks;
