@@ -426,7 +426,8 @@ def bench_deltas(args, rank, world, local, dev, dist):
                            "l2": "inputs exceed L2; no flush needed", "slow_tiles": ctx.slow_tiles,
                            "reruns": ctx.reruns},
                 "roofline": {"bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
-                             "traffic": None, "kernel": "k_decode<SWITCH_EVENTS> + k_sw_count/scan/emit",
+                             "traffic": load_traffic("k_walk<SWITCH_EVENTS>"),
+                             "kernel": ("k_decode" if args.kernel == "tiles" else "k_walk") + "<SWITCH_EVENTS> + k_sw_scan/emit",
                              "kernel_ms": ms_step, "decode_kernel_ms": k_ms, "algorithmic_bytes": int(algo),
                              "peak_source": peak_src},
                 "gpu_launches": int(launches), "clocks": clocks,
@@ -456,8 +457,10 @@ def bench_deltas(args, rank, world, local, dev, dist):
                        "l2": "inputs exceed L2; no flush needed", "slow_tiles": ctx.slow_tiles,
                        "reruns": ctx.reruns, "rerun_segments": ctx.rerun_segments},
             "roofline": {"bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
-                         "traffic": (load_traffic(f"k_decode<COUNT_DELTAS>@{E}ev") if not mixed else None),
-                         "kernel": "k_decode<COUNT_DELTAS>",
+                         "traffic": (load_traffic(f"k_decode<COUNT_DELTAS>@{E}ev") if not mixed
+                                     else load_traffic("k_walk<COUNT_DELTAS>@mixed")),
+                         "kernel": ("k_walk<COUNT_DELTAS>" if (mixed and args.kernel != "tiles") or args.kernel == "walk"
+                                    else "k_decode<COUNT_DELTAS>"),
                          "kernel_ms": k_ms, "algorithmic_bytes": int(algo), "peak_source": peak_src},
             "gpu_launches": int(launches), "clocks": clocks}
     if cb:
