@@ -10,8 +10,8 @@
 // tile and lets it scan all of its words for a plausible header: the work is proportional to the
 // bytes (~28 issue cycles per record on config 4's streams).  Here one WARP owns a segment and works
 // through it in rounds of 8 KiB, staged in the warp's own slice of shared memory; each lane owns a
-// 256-byte chunk of the round, guesses the first record start in it (first header whose chain of
-// successors stays plausible) and then simply follows header.size from record to record -- work
+// 256-byte chunk of the round, guesses the first record start in it (first plausible header whose
+// successor is plausible too) and then simply follows header.size from record to record -- work
 // proportional to the RECORDS.  The seams between the 32 lanes are settled inside the warp: lane l's
 // walk must begin where the records before it end; a lane whose guess was wrong walks again from the
 // right place.  What leaves a round is exact, and the position after its last record carries into
