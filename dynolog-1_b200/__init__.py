@@ -415,6 +415,19 @@ class Context:
         n = self._ck(self.lib.hbt_fetch_rows_all(self.h, _ptr(out), out.shape[0], off.ctypes.data_as(_U64P)))
         return out[:n], off
 
+    def rows_packed_dev(self):
+        """(device pointer, offsets[n_cpus + 1]) of all CPUs' rows of the last decode, packed back to back."""
+        base = C.c_void_p()
+        off = np.zeros(self.n_cpus + 1, dtype=np.uint64)
+        self._ck(self.lib.hbt_rows_packed_dev(self.h, C.byref(base), off.ctypes.data_as(_U64P)))
+        return base.value or 0, off
+
+    def switch_events_merged_dev(self):
+        """(device pointer, number of events) of all CPUs' events in Combinator order."""
+        base, n = C.c_void_p(), C.c_uint64()
+        self._ck(self.lib.hbt_switch_events_merged_dev(self.h, C.byref(base), C.byref(n)))
+        return base.value or 0, int(n.value)
+
     def fetch_switch_events(self, cpu: int, n_events: int) -> np.ndarray:
         """Events of the last AGG_SWITCH_EVENTS decode for `cpu` (SWITCH_EVENT_DTYPE)."""
         out = np.zeros(max(1, n_events), dtype=SWITCH_EVENT_DTYPE)
