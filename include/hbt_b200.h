@@ -361,7 +361,9 @@ int64_t hbt_fetch_rows(hbt_ctx* ctx, uint32_t cpu, uint64_t* rows, uint64_t cap_
 /* The rows of ALL CPUs of the last decode in one array: the per-segment slabs are packed on the
  * device (one launch) into [total rows][2 + n_events], CPU c at rows [offsets[c], offsets[c+1])
  * (offsets: host array of n_cpus + 1 entries, filled by the call), each CPU's rows in the order
- * its generator writes them to its output ring.  hbt_fetch_rows_all then needs ONE device-to-host
+ * its generator writes them to its output ring.  The pack kernel is QUEUED on the ctx's stream when
+ * the call returns: consume the array in that stream's order, or call hbt_sync first when another
+ * stream reads it.  hbt_fetch_rows_all then needs ONE device-to-host
  * copy for the whole decode (hbt_fetch_rows issues one per slab); the packed array stays valid
  * until the next decode.  Returns the total number of rows, -ENOSPC if cap_rows is too small. */
 int hbt_rows_packed_dev(hbt_ctx* ctx, const uint64_t** rows, uint64_t* offsets);
@@ -380,7 +382,8 @@ int hbt_switch_events_dev(hbt_ctx* ctx, const hbt_switch_event** events, uint64_
  * makeBinaryTree :190-230): Event::happenedBefore = timestamp, then comp_unit_id
  * (Event.h:205-213).  Requires what the Combinator itself assumes: each CPU's stream is
  * timestamp-ordered.  The merge runs on the first call after a decode (log2(n_cpus)
- * launches) and the result stays valid until the next decode. */
+ * launches, queued on the ctx's stream when the call returns: read the result in that stream's
+ * order, or after hbt_sync) and the result stays valid until the next decode. */
 int hbt_switch_events_merged_dev(hbt_ctx* ctx, const hbt_switch_event** merged, uint64_t* n_events);
 int64_t hbt_fetch_switch_events_merged(hbt_ctx* ctx, hbt_switch_event* out, uint64_t cap);
 
