@@ -215,3 +215,50 @@ def test_c5_counter_groups_full_size(built):
         assert torch.equal(tot, sums)
     finally:
         ctx.close()
+
+
+@pytest.mark.parametrize("switch", [False, True], ids=["mixed_rows", "switch_events"])
+def test_c4_both_kernels_agree(built, switch):
+    """Config 4's streams at full size through the two independent decode kernels (k_decode: a CTA per
+    segment, tiles, guesses checked across sub-chunks; k_walk: a warp per segment, lanes following
+    header.size): the same per-CPU results, the same delta rows / events, bit for bit.  (At small sizes both
+    are held to the reference; its consume() needs minutes for 4 GiB.)"""
+    import torch
+    b = _bench()
+    dev = torch.device("cuda:0")
+    E = 8
+    if switch:
+        imgs, tails, heads, n_rec = b.make_switch_rings(CPUS, RING, 0, dev)
+        desc = hbt.switch_desc(tid_level=1)
+    else:
+        imgs, tails, heads, n_rec = b.make_mixed_rings(CPUS, RING, 0, dev, E)
+        desc = hbt.sampling_desc(E, handled=hbt.MODE_MIXED)
+    torch.cuda.synchronize()
+    out = []
+    for kernel in (hbt.KERNEL_TILES, hbt.KERNEL_WALK):
+        ctx = hbt.Context(0, max_cpus=CPUS)
+        try:
+            ctx.set_decode_kernel(kernel)
+            ctx.ring_configure(CPUS, 0)
+            ctx.reset_state(hbt.INVALID_TS)
+            _submit(ctx, imgs, tails, heads)
+            ctx.decode(desc)
+            res = ctx.fetch_results().copy()
+            assert int(res["n_records"].sum()) == n_rec and ctx.reruns == 0
+            if switch:
+                base, off = ctx.switch_events_dev()
+                width = 2
+            else:
+                base, off = ctx.rows_packed_dev()
+                width = 2 + E
+            ctx.sync()
+            data = torch.as_tensor(b._DevArray(base, (int(off[CPUS]), width), "<i8"), device=dev).clone()
+            out.append((res, off.copy(), data))
+        finally:
+            ctx.close()
+    (r0, o0, d0), (r1, o1, d1) = out
+    assert r0.tobytes() == r1.tobytes()
+    assert np.array_equal(o0, o1)
+    same = torch.equal(d0, d1)
+    assert same
+    assert d0.shape[0] > n_rec * 0.5
