@@ -1115,7 +1115,7 @@ def main():
         G = max(1, min(args.e2e_groups, args.cpus))
         per = (args.cpus + G - 1) // G
         groups = []
-        ent_dt = hbt.HIST_DTYPE.itemsize
+        ent_dt = hbt.HIST_PACKED_DTYPE.itemsize   # 16-byte entries + a per-CPU offset table (hbt_hist_fetch_packed)
         for g in range(G):
             lo, hi = g * per, min(args.cpus, (g + 1) * per)
             if lo >= hi:
@@ -1130,7 +1130,7 @@ def main():
             # copy of ~1 GB of entries the slowest part of the step)
             cap = int(distinct * 1.25 * (hi - lo) / args.cpus) + 4096
             pinned = torch.empty(cap * ent_dt, dtype=torch.uint8).pin_memory()
-            groups.append((cg, lo, hi, pinned.numpy().view(hbt.HIST_DTYPE), (pinned, sg)))
+            groups.append((cg, lo, hi, pinned.numpy().view(hbt.HIST_PACKED_DTYPE), (pinned, sg)))
 
         def e2e_step():
             uploaded = None
@@ -1153,7 +1153,7 @@ def main():
             for cg, lo, hi, buf, _ in groups:
                 rs.append(cg.fetch_results())
                 trace.append(time.perf_counter())
-                n_ent += len(cg.hist_fetch(out=buf))
+                n_ent += len(cg.hist_fetch_packed(0, hi - lo, out=buf)[0])
                 trace.append(time.perf_counter())
             if os.environ.get("HBT_BENCH_TRACE"):
                 print("e2e trace (ms since issue):",
@@ -1199,7 +1199,7 @@ def main():
             dist.all_reduce(tu, op=dist.ReduceOp.MAX)
         up = float(tu.item())
         e2e = {"value": n_rec * world / dt, "unit": UNIT, "h2d_bytes_per_step": int(window_bytes),
-               "d2h_bytes_per_step": int(n_ent * ent_dt + r.nbytes), "ms_per_step": dt * 1e3,
+               "d2h_bytes_per_step": int(n_ent * ent_dt + 8 * (args.cpus + len(groups)) + r.nbytes), "ms_per_step": dt * 1e3,
                "steps": e2e_steps,
                "upload_only_ms_per_step": up * 1e3,
                "upload_only_gbs_per_gpu": window_bytes / up / 1e9,

@@ -105,6 +105,8 @@ RESULT_DTYPE = np.dtype([("ret", "<i8"), ("n_records", "<u8"), ("new_tail", "<u8
 SWITCH_EVENT_DTYPE = np.dtype([("tstamp", "<u8"), ("type", "u1"), ("level", "u1"),
                                ("comp_unit_id", "<u2"), ("tag", "<u4")])
 assert SWITCH_EVENT_DTYPE.itemsize == 16
+HIST_PACKED_DTYPE = np.dtype([("ip", "<u8"), ("pid", "<u4"), ("count", "<u4")])   # hbt_hist_key_count
+assert HIST_PACKED_DTYPE.itemsize == 16
 assert HIST_DTYPE.itemsize == C.sizeof(HistEntry)
 assert RESULT_DTYPE.itemsize == C.sizeof(CpuResult)
 
@@ -151,6 +153,7 @@ EXPORTS = [
     ("hbt_hist_clear", C.c_int, [_P]),
     ("hbt_hist_size", C.c_int64, [_P]),
     ("hbt_hist_fetch", C.c_int64, [_P, _P, C.c_uint64]),
+    ("hbt_hist_fetch_packed", C.c_int64, [_P, C.c_uint32, C.c_uint32, _P, C.c_uint64, _U64P]),
     ("hbt_hist_fetch_cpus", C.c_int64, [_P, C.c_uint32, C.c_uint32, _P, C.c_uint64]),
     ("hbt_hist_lists_dev", C.c_int,
      [_P, C.POINTER(_P), C.POINTER(_P), C.POINTER(C.c_uint32), C.POINTER(C.c_uint32)]),
@@ -473,6 +476,19 @@ class Context:
             out = np.zeros(max(1, n), dtype=HIST_DTYPE)
         m = self._ck(self.lib.hbt_hist_fetch(self.h, _ptr(out), out.shape[0]))
         return out[:m]
+
+    def hist_fetch_packed(self, first_cpu: int = 0, n_cpus: int | None = None, out: np.ndarray | None = None):
+        """(entries [HIST_PACKED_DTYPE, 16 bytes each], offsets [n_cpus + 1]): the entries of ctx-local CPU
+        first_cpu + i are entries[offsets[i]:offsets[i + 1]].  `out`: optional caller-owned (pinned) array."""
+        if n_cpus is None:
+            n_cpus = self.n_cpus - first_cpu
+        off = np.zeros(n_cpus + 1, dtype=np.uint64)
+        if out is None:
+            n = self._ck(self.lib.hbt_hist_fetch_packed(self.h, first_cpu, n_cpus, None, 0, off.ctypes.data_as(_U64P)))
+            out = np.zeros(max(1, n), dtype=HIST_PACKED_DTYPE)
+        m = self._ck(self.lib.hbt_hist_fetch_packed(self.h, first_cpu, n_cpus, _ptr(out), out.shape[0],
+                                                    off.ctypes.data_as(_U64P)))
+        return out[:m], off
 
     def hist_fetch_cpus(self, first_cpu: int, n_cpus: int) -> np.ndarray:
         """Entries of the ctx-local CPUs [first_cpu, first_cpu + n_cpus)."""

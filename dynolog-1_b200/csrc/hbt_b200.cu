@@ -182,6 +182,11 @@ struct hbt_ctx {
   uint64_t hist_samples = 0;       // upper bound of samples added since the last clear
   DevBuf<hbt_hist_entry> hist_out;
   DevBuf<unsigned long long> hist_n;
+  // hbt_hist_fetch_packed: per-list offsets inside its CPU, per-CPU totals + their prefix, the packed entries
+  DevBuf<uint32_t> hist_list_off;
+  DevBuf<unsigned long long> hist_cpu_total;
+  PinBuf<unsigned long long> h_hist_off;
+  DevBuf<ulonglong2> hist_packed;
 
   // multi-GPU merge (NCCL communicator over the ranks of the box)
   void* comm = nullptr;       // ncclComm_t
@@ -743,6 +748,10 @@ void hbt_destroy(hbt_ctx* ctx) {
   ctx->hist_overflow.release();
   ctx->hist_out.release();
   ctx->hist_n.release();
+  ctx->hist_list_off.release();
+  ctx->hist_cpu_total.release();
+  ctx->h_hist_off.release();
+  ctx->hist_packed.release();
   comm_release(ctx);
   if (ctx->comm_stream) {
     cudaStreamDestroy(ctx->comm_stream);
@@ -1546,6 +1555,49 @@ int64_t hbt_hist_fetch(hbt_ctx* ctx, hbt_hist_entry* out, uint64_t cap) {
 int64_t hbt_hist_fetch_cpus(hbt_ctx* ctx, uint32_t first_cpu, uint32_t n_cpus, hbt_hist_entry* out,
                             uint64_t cap) {
   return hist_collect(ctx, out, out ? cap : 0, first_cpu, n_cpus);
+}
+
+int64_t hbt_hist_fetch_packed(hbt_ctx* ctx, uint32_t first_cpu, uint32_t n_cpus, hbt_hist_key_count* out,
+                              uint64_t cap, uint64_t* offsets) {
+  if (!ctx || ctx->hist_buckets == 0) return fail(ctx, -EINVAL, "no histogram configured");
+  if (!offsets) return fail(ctx, -EINVAL, "offsets is NULL");
+  if (int rc = complete_decode(ctx)) return rc;
+  if (n_cpus == 0 || first_cpu + (uint64_t)n_cpus > ctx->n_cpus)
+    return fail(ctx, -EINVAL, "CPU range outside the configured CPUs");
+  static_assert(sizeof(hbt_hist_key_count) == sizeof(ulonglong2), "the device's list entry IS the wire entry");
+  HistLists v = hist_view(ctx);
+  v.entries += (uint64_t)first_cpu * ctx->hist_buckets * ctx->hist_cap;
+  v.cursors += (uint64_t)first_cpu * ctx->hist_buckets;
+  const uint32_t n_lists = n_cpus * ctx->hist_buckets;
+  CU(ctx->hist_list_off.reserve(n_lists));
+  CU(ctx->hist_cpu_total.reserve(2 * (size_t)HBT_MAX_CPUS + 2));
+  CU(ctx->h_hist_off.reserve((size_t)HBT_MAX_CPUS + 1));
+  unsigned long long* d_tot = ctx->hist_cpu_total.p;
+  unsigned long long* d_off = d_tot + HBT_MAX_CPUS;
+  k_hist_offsets<<<n_cpus, 256, 0, ctx->stream>>>(v, ctx->hist_list_off.p, d_tot);
+  k_hist_cpu_scan<<<1, 512, 0, ctx->stream>>>(d_tot, n_cpus, d_off);
+  ctx->launches += 2;
+  CU(cudaGetLastError());
+  if (out) {
+    // packed on the device before the host knows how many entries there are (cap bounds the writes)
+    CU(ctx->hist_packed.reserve(cap ? cap : 1));
+    uint32_t grid = (uint32_t)ctx->sm_count * 16;
+    if (grid > n_lists) grid = n_lists;
+    k_hist_pack<<<grid, 128, 0, ctx->stream>>>(v, n_lists, ctx->hist_list_off.p, d_off, ctx->hist_packed.p, cap);
+    ++ctx->launches;
+    CU(cudaGetLastError());
+  }
+  CU(cudaMemcpyAsync(ctx->h_hist_off.p, d_off, (n_cpus + 1) * sizeof(unsigned long long), cudaMemcpyDeviceToHost,
+                     ctx->stream));
+  CU(cudaStreamSynchronize(ctx->stream));
+  for (uint32_t i = 0; i <= n_cpus; ++i) offsets[i] = ctx->h_hist_off.p[i];
+  const uint64_t n = offsets[n_cpus];
+  if (out) {
+    if (n > cap) return fail(ctx, -ENOSPC, "cap %llu < %llu entries", (unsigned long long)cap, (unsigned long long)n);
+    CU(cudaMemcpyAsync(out, ctx->hist_packed.p, n * sizeof(hbt_hist_key_count), cudaMemcpyDeviceToHost, ctx->stream));
+    CU(cudaStreamSynchronize(ctx->stream));
+  }
+  return (int64_t)n;
 }
 
 int hbt_hist_lists_dev(hbt_ctx* ctx, const void** entries, const uint32_t** cursors,

@@ -418,6 +418,19 @@ int64_t hbt_hist_fetch(hbt_ctx* ctx, hbt_hist_entry* out, uint64_t cap);
  * returns their number. */
 int64_t hbt_hist_fetch_cpus(hbt_ctx* ctx, uint32_t first_cpu, uint32_t n_cpus, hbt_hist_entry* out,
                             uint64_t cap);
+/* The same entries in the 16-byte form the device keeps them in, CPU after CPU: the entries of
+ * ctx-local CPU first_cpu + i are out[offsets[i] .. offsets[i + 1]) (offsets: host array of
+ * n_cpus + 1 entries, filled by the call; unordered inside a CPU).  The cpu id travels in the
+ * offset table instead of in every entry: a third fewer bytes over PCIe than hbt_hist_fetch_cpus,
+ * which is what a collection loop that reads the table every interval pays for.  Returns the
+ * number of entries, -ENOSPC if cap is too small; out = NULL only fills offsets. */
+typedef struct hbt_hist_key_count {
+  uint64_t ip;
+  uint32_t pid;
+  uint32_t count;
+} hbt_hist_key_count;
+int64_t hbt_hist_fetch_packed(hbt_ctx* ctx, uint32_t first_cpu, uint32_t n_cpus, hbt_hist_key_count* out,
+                              uint64_t cap, uint64_t* offsets);
 /* Device view for downstream kernels: list l = cpu * (*lists_per_cpu) + bucket
  * holds cursors[l] distinct entries at entries + l * (*list_capacity) * 16 bytes. */
 int hbt_hist_lists_dev(hbt_ctx* ctx, const void** entries, const uint32_t** cursors,

@@ -431,6 +431,20 @@ def test_ip_histogram(ctx, words, ds, n_cpus, n_pids, n_ips):
     got = orc.hist_to_dict(ctx.hist_fetch())
     assert len(got) == len(want_hist)
     assert got == want_hist
+    # the same table as 16-byte entries behind a per-CPU offset table (hbt_hist_fetch_packed), whole and
+    # for a sub-range of the CPUs
+    ent, off = ctx.hist_fetch_packed()
+    assert int(off[0]) == 0 and int(off[-1]) == len(ent) == len(want_hist)
+    packed = {(cpu, int(e["pid"]), int(e["ip"])): int(e["count"])
+              for cpu in range(n_cpus) for e in ent[int(off[cpu]):int(off[cpu + 1])]}
+    assert packed == want_hist
+    if n_cpus > 2:
+        ent, off = ctx.hist_fetch_packed(1, n_cpus - 2)
+        sub = {(1 + i, int(e["pid"]), int(e["ip"])): int(e["count"])
+               for i in range(n_cpus - 2) for e in ent[int(off[i]):int(off[i + 1])]}
+        assert sub == {k: v for k, v in want_hist.items() if 1 <= k[0] < n_cpus - 1}
+    with pytest.raises(hbt.HbtError):
+        ctx.hist_fetch_packed(0, n_cpus, out=np.zeros(3, dtype=hbt.HIST_PACKED_DTYPE))   # -ENOSPC
     # a second identical batch accumulates
     for cpu, (ring, tail, head) in enumerate(rings):
         ctx.submit_ring_image(cpu, ring, tail, head)
