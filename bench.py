@@ -1114,12 +1114,21 @@ def main():
         # decode, fold and D2H of group g (PCIe is full duplex; the copies dominate).
         G = max(1, min(args.e2e_groups, args.cpus))
         per = (args.cpus + G - 1) // G
+        # group boundaries: G groups of `per` CPUs, the last one tapered (halved down to 4 CPUs) -- what
+        # cannot overlap anything is the decode + download of the LAST group, so it is kept small
+        bounds, lo = [], 0
+        while lo < args.cpus:
+            hi = min(args.cpus, lo + per)
+            if hi == args.cpus:
+                while hi - lo > 4:
+                    mid = lo + (hi - lo + 1) // 2
+                    bounds.append((lo, mid))
+                    lo = mid
+            bounds.append((lo, hi))
+            lo = hi
         groups = []
         ent_dt = hbt.HIST_PACKED_DTYPE.itemsize   # 16-byte entries + a per-CPU offset table (hbt_hist_fetch_packed)
-        for g in range(G):
-            lo, hi = g * per, min(args.cpus, (g + 1) * per)
-            if lo >= hi:
-                break
+        for lo, hi in bounds:
             cg = hbt.Context(local, max_cpus=hi - lo)
             sg = torch.cuda.Stream(dev)
             cg.set_stream(sg.cuda_stream)
@@ -1204,8 +1213,8 @@ def main():
                "upload_only_ms_per_step": up * 1e3,
                "upload_only_gbs_per_gpu": window_bytes / up / 1e9,
                "frac_of_upload_floor": up / dt,
-               "pipeline": f"{len(groups)} CPU groups, one hbt_ctx + stream each: H2D of group g+1 "
-                           "overlaps decode + fold + D2H of group g",
+               "pipeline": f"{len(groups)} CPU groups ({per} CPUs each, the last one tapered down to 4), one hbt_ctx + "
+                           "stream each: H2D of group g+1 overlaps decode + fold + D2H of group g",
                "host_cpus_bound": len(numa) if numa else None}
         for cg, *_ in groups:
             cg.close()
