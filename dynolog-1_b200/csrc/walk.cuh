@@ -80,9 +80,9 @@ struct WalkLane {
   uint32_t bad;      // kNoRel, or the offset of a header that cannot be one (size < 8 or not a multiple of 8)
 };
 
-// Follow header.size from offset `from` while records start before `end` (both in the chunk that
-// begins at `chunk`), marking the starts.  Harmless on garbage (a guess may be wrong).
-__device__ __forceinline__ void walk_chunk(const WalkView& v, uint32_t chunk, uint32_t from, uint32_t end, WalkLane& w) {
+// Follow header.size from offset `from` while records start before `end` (both in one 256-byte
+// aligned chunk), marking the starts.  Harmless on garbage (a guess may be wrong).
+__device__ __forceinline__ void walk_chunk(const WalkView& v, uint32_t from, uint32_t end, WalkLane& w) {
   w.mask = 0;
   w.bad = kNoRel;
   uint32_t r = from;
@@ -92,7 +92,7 @@ __device__ __forceinline__ void walk_chunk(const WalkView& v, uint32_t chunk, ui
       w.bad = r;
       break;
     }
-    w.mask |= 1u << ((r - chunk) >> 3);
+    w.mask |= 1u << ((r >> 3) & 31u);  // word of my (256-byte aligned) chunk
     r += size;
   }
   w.exit = r;
@@ -148,6 +148,10 @@ __device__ __forceinline__ ulonglong2 ldg_stream_u64x2(const void* p) {
   asm volatile("ld.global.cs.v2.u64 {%0, %1}, [%2];" : "=l"(r.x), "=l"(r.y) : "l"(p));
   return r;
 }
+
+// sw_min_size(type) / 8 for every type 0..15 (LOST 40, EXIT / FORK 48, everything else 32 bytes)
+constexpr uint64_t kSwMinNib = 0x4444444444444444ull + (1ull << (4 * REC_LOST)) + (2ull << (4 * REC_EXIT)) +
+                               (2ull << (4 * REC_FORK));
 
 // The proto-event of a handled ContextSwitch record, without branches on the record type (the lanes
 // of a warp look at records of different types): same result as sw_proto.
@@ -315,7 +319,7 @@ __global__ void __launch_bounds__(32 * kWalkWarps, 5) k_walk(const DecodeParams 
       else if (pos_r != kNoRel && pos_r >= ce) w.entry = kNoRel;          // a record spans my whole chunk
       else w.entry = guess_entry(v, cs, ce, head_r);  // (the host's entry_hint is of no use here: it may
                                                       //  name a record that is not the FIRST one)
-      if (w.entry != kNoRel) walk_chunk(v, chunk, w.entry, ce, w);
+      if (w.entry != kNoRel) walk_chunk(v, w.entry, ce, w);
     }
 
     // ---- seams: lane l must start where the records before it end --------------------------------
@@ -356,7 +360,7 @@ __global__ void __launch_bounds__(32 * kWalkWarps, 5) k_walk(const DecodeParams 
           }
           if (lane == l && w.entry != cur) {  // wrong (or no) guess: walk again from the right place
             w.entry = cur;
-            walk_chunk(v, chunk, cur, ce, w);
+            walk_chunk(v, cur, ce, w);
           }
           cur = __shfl_sync(FULL, w.exit, l);
           bad_r = __shfl_sync(FULL, w.bad, l);
@@ -404,8 +408,8 @@ __global__ void __launch_bounds__(32 * kWalkWarps, 5) k_walk(const DecodeParams 
           const uint64_t want = group ? 40 + 8 * v.near(r + 16) : d.ip_sample_bytes;
           if ((uint64_t)size != want) e = -1;  // -EPERM
         }
-        if (AGG == HBT_AGG_SWITCH_EVENTS && cnt && size < sw_min_size(type)) e = -1;  // the handler would read
-                                                                                       // past the record
+        // (kSwMinNib: sw_min_size(type) / 8 in nibble `type`; the handler would read past a shorter record)
+        if (AGG == HBT_AGG_SWITCH_EVENTS && cnt && size < 8u * ((uint32_t)(kSwMinNib >> (4 * (type & 15))) & 15u)) e = -1;
         // COUNT_DELTAS: the SAMPLE / LOST sequence (PerCpuCountSampleGenerator.h:122-195)
         bool is_s = false, is_l = cnt && type == REC_LOST, row = false, regress = false;
         uint32_t prev_kind = EV_NONE, prev_rel = kFarPrev, smask = 0, lmask = 0;
